@@ -1,0 +1,248 @@
+"""TEST INFRASTRUCTURE ONLY: ctypes loader for oracle/_ref/libsphexa_ref.so.
+
+That library is the reference's own CPU code (cstone + sph header templates from
+/root/reference, compiled by oracle/Makefile behind oracle/ref_wrap.cpp).  It is
+the checker, never the product: only tests/, __graft_entry__.smoke() and
+bench.py's cpu_baseline / --impl reference legs import this module.
+"""
+import ctypes as C
+import os
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_PATH = os.path.join(_HERE, "_ref", "libsphexa_ref.so")
+_lib = None
+
+
+def available():
+    return os.path.exists(_PATH)
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        _lib = C.CDLL(_PATH)
+        for name in ("ref_momentum_energy_f64", "ref_momentum_energy_f32", "ref_rho_timestep_f64",
+                     "ref_rho_timestep_f32", "ref_sphynx_3D_k"):
+            getattr(_lib, name).restype = C.c_double
+    return _lib
+
+
+def P(a):
+    """pointer to a contiguous numpy array (or NULL)"""
+    if a is None:
+        return None
+    assert a.flags["C_CONTIGUOUS"]
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def _box(box):
+    lim = np.ascontiguousarray(box[0], dtype=np.float64)
+    bc = np.ascontiguousarray(box[1], dtype=np.int32)
+    return lim, bc
+
+
+class TreeArgs(C.Structure):
+    _fields_ = [("numLeaves", C.c_int), ("prefixes", C.c_void_p), ("childOffsets", C.c_void_p),
+                ("internalToLeaf", C.c_void_p), ("levelRange", C.c_void_p), ("leaves", C.c_void_p),
+                ("layout", C.c_void_p), ("centers", C.c_void_p), ("sizes", C.c_void_p)]
+
+
+def num_threads():
+    return lib().ref_num_threads()
+
+
+def set_num_threads(n):
+    lib().ref_set_num_threads(int(n))
+
+
+def hilbert_encode(ix, iy, iz):
+    ix, iy, iz = (np.ascontiguousarray(a, dtype=np.uint32) for a in (ix, iy, iz))
+    keys = np.empty(ix.size, np.uint64)
+    lib().ref_hilbert_encode(P(ix), P(iy), P(iz), C.c_size_t(ix.size), P(keys))
+    return keys
+
+
+def hilbert_decode(keys):
+    keys = np.ascontiguousarray(keys, dtype=np.uint64)
+    ix, iy, iz = (np.empty(keys.size, np.uint32) for _ in range(3))
+    lib().ref_hilbert_decode(P(keys), C.c_size_t(keys.size), P(ix), P(iy), P(iz))
+    return ix, iy, iz
+
+
+def compute_sfc_keys(x, y, z, box):
+    lim, bc = _box(box)
+    keys = np.empty(x.size, np.uint64)
+    lib().ref_compute_sfc_keys(P(x), P(y), P(z), C.c_size_t(x.size), P(lim), P(bc), P(keys))
+    return keys
+
+
+def sort_by_key(keys):
+    k = np.array(keys, dtype=np.uint64, copy=True)
+    perm = np.empty(k.size, np.uint32)
+    lib().ref_sort_by_key(P(k), C.c_size_t(k.size), P(perm))
+    return k, perm
+
+
+def compute_octree(keys, bucket, capacity=None):
+    cap = capacity or max(64, 8 * (keys.size // max(1, bucket)) + 4096)
+    leaves = np.empty(cap + 1, np.uint64)
+    counts = np.empty(cap, np.uint32)
+    it = C.c_int(0)
+    nl = lib().ref_compute_octree(P(keys), C.c_size_t(keys.size), C.c_uint(bucket), P(leaves), P(counts), cap,
+                                  C.byref(it))
+    assert nl >= 0
+    return leaves[:nl + 1].copy(), counts[:nl].copy(), it.value
+
+
+def update_octree(keys, bucket, leaves, counts):
+    nl = counts.size
+    cap = 8 * nl + 64
+    lv = np.empty(cap + 1, np.uint64)
+    ct = np.empty(cap, np.uint32)
+    lv[:nl + 1] = leaves
+    ct[:nl] = counts
+    conv = C.c_int(0)
+    nn = lib().ref_update_octree(P(keys), C.c_size_t(keys.size), C.c_uint(bucket), P(lv), P(ct), nl, cap,
+                                 C.byref(conv))
+    assert nn >= 0
+    return lv[:nn + 1].copy(), ct[:nn].copy(), bool(conv.value)
+
+
+def compute_node_counts(leaves, keys):
+    nl = leaves.size - 1
+    counts = np.empty(nl, np.uint32)
+    lib().ref_compute_node_counts(P(leaves), nl, P(keys), C.c_size_t(keys.size), P(counts))
+    return counts
+
+
+def rebalance_decision(leaves, counts, bucket):
+    nl = counts.size
+    ops = np.empty(nl + 1, np.int32)
+    conv = C.c_int(0)
+    lib().ref_rebalance_decision(P(leaves), P(counts), nl, C.c_uint(bucket), P(ops), C.byref(conv))
+    return ops[:nl], bool(conv.value)
+
+
+def build_octree(leaves):
+    nl = leaves.size - 1
+    ni = (nl - 1) // 7
+    nn = nl + ni
+    t = dict(prefixes=np.zeros(nn, np.uint64), childOffsets=np.zeros(nn + 1, np.int32),
+             parents=np.zeros(max(1, (nn - 1) // 8), np.int32), levelRange=np.zeros(23, np.int32),
+             internalToLeaf=np.zeros(nn, np.int32), leafToInternal=np.zeros(nn, np.int32))
+    lib().ref_build_octree(P(leaves), nl, P(t["prefixes"]), P(t["childOffsets"]), P(t["parents"]),
+                           P(t["levelRange"]), P(t["internalToLeaf"]), P(t["leafToInternal"]))
+    t["numLeaves"], t["numInternal"], t["numNodes"] = nl, ni, nn
+    t["leaves"] = leaves
+    return t
+
+
+def node_centers(prefixes, box):
+    lim, bc = _box(box)
+    n = prefixes.size
+    centers = np.empty((n, 3), np.float64)
+    sizes = np.empty((n, 3), np.float64)
+    lib().ref_node_centers(P(prefixes), n, P(lim), P(bc), P(centers), P(sizes))
+    return centers, sizes
+
+
+def _sfx(T):
+    return "f64" if np.dtype(T) == np.float64 else "f32"
+
+
+def find_neighbors(x, y, z, h, first, last, box, tree, layout, centers, sizes, ng0, ngmax, iterate_h):
+    """returns (neighbors[n,ngmax], nc[n] incl. self, h (modified copy))"""
+    lim, bc = _box(box)
+    h = h.copy()
+    n = last - first
+    nb = np.zeros((n, ngmax), np.uint32)
+    nc = np.zeros(n, np.uint32)
+    ta = TreeArgs(tree["numLeaves"], P(tree["prefixes"]), P(tree["childOffsets"]), P(tree["internalToLeaf"]),
+                  P(tree["levelRange"]), P(tree["leaves"]), P(layout), P(centers), P(sizes))
+    f = getattr(lib(), "ref_find_neighbors_" + _sfx(h.dtype))
+    f(P(x), P(y), P(z), P(h), C.c_uint32(first), C.c_uint32(last), P(lim), P(bc), C.byref(ta), C.c_uint(ng0),
+      C.c_uint(ngmax), P(nb), P(nc), int(iterate_h))
+    return nb, nc, h
+
+
+def tables(T, sinc_index=6.0):
+    wh = np.empty(20000, T)
+    whd = np.empty(20000, T)
+    K = C.c_double(0)
+    getattr(lib(), "ref_tables_" + _sfx(T))(C.c_double(sinc_index), P(wh), P(whd), C.byref(K))
+    return wh, whd, K.value
+
+
+def sphynx_3D_k(n):
+    return lib().ref_sphynx_3D_k(C.c_double(n))
+
+
+def _common(first, last, ngmax, K, box):
+    lim, bc = _box(box)
+    return (C.c_uint32(first), C.c_uint32(last), C.c_uint(ngmax), C.c_double(K), P(lim), P(bc)), (lim, bc)
+
+
+def xmass(first, last, ngmax, K, box, nb, nc, x, y, z, h, m, wh, whd, xm):
+    a, _k = _common(first, last, ngmax, K, box)
+    getattr(lib(), "ref_xmass_" + _sfx(h.dtype))(*a, P(nb), P(nc), P(x), P(y), P(z), P(h), P(m), P(wh), P(whd), P(xm))
+
+
+def ve_def_gradh(first, last, ngmax, K, box, nb, nc, x, y, z, h, m, wh, whd, xm, kx, gradh):
+    a, _k = _common(first, last, ngmax, K, box)
+    getattr(lib(), "ref_ve_def_gradh_" + _sfx(h.dtype))(*a, P(nb), P(nc), P(x), P(y), P(z), P(h), P(m), P(wh),
+                                                        P(whd), P(xm), P(kx), P(gradh))
+
+
+def eos(first, last, temp, m, kx, xm, gradh, mui, gamma, prho, c, rho=None, p=None):
+    getattr(lib(), "ref_eos_" + _sfx(m.dtype))(C.c_uint32(first), C.c_uint32(last), P(temp), P(m), P(kx), P(xm),
+                                               P(gradh), C.c_double(mui), C.c_double(gamma), P(prho), P(c), P(rho),
+                                               P(p))
+
+
+def iad_divv_curlv(first, last, ngmax, K, box, nb, nc, x, y, z, vx, vy, vz, h, wh, whd, xm, kx, c11, c12, c13, c22,
+                   c23, c33, divv, curlv, dV=None):
+    a, _k = _common(first, last, ngmax, K, box)
+    dV = dV or [None] * 6
+    getattr(lib(), "ref_iad_divv_curlv_" + _sfx(h.dtype))(*a, P(nb), P(nc), P(x), P(y), P(z), P(vx), P(vy), P(vz),
+                                                          P(h), P(wh), P(whd), P(xm), P(kx), P(c11), P(c12), P(c13),
+                                                          P(c22), P(c23), P(c33), P(divv), P(curlv),
+                                                          *[P(d) for d in dV])
+
+
+def av_switches(first, last, ngmax, K, box, nb, nc, x, y, z, vx, vy, vz, h, c, c11, c12, c13, c22, c23, c33, wh, whd,
+                kx, xm, divv, min_dt, alphamin, alphamax, decay_constant, alpha):
+    a, _k = _common(first, last, ngmax, K, box)
+    getattr(lib(), "ref_av_switches_" + _sfx(h.dtype))(*a, P(nb), P(nc), P(x), P(y), P(z), P(vx), P(vy), P(vz), P(h),
+                                                       P(c), P(c11), P(c12), P(c13), P(c22), P(c23), P(c33), P(wh),
+                                                       P(whd), P(kx), P(xm), P(divv), C.c_double(min_dt),
+                                                       C.c_double(alphamin), C.c_double(alphamax),
+                                                       C.c_double(decay_constant), P(alpha))
+
+
+def momentum_energy(first, last, ngmax, K, box, nb, nc, x, y, z, vx, vy, vz, h, m, prho, c, c11, c12, c13, c22, c23,
+                    c33, atmin, atmax, ramp, wh, kx, xm, alpha, dV, ax, ay, az, du, kcour, av_clean):
+    a, _k = _common(first, last, ngmax, K, box)
+    dV = dV or [None] * 6
+    return getattr(lib(), "ref_momentum_energy_" + _sfx(h.dtype))(
+        *a, P(nb), P(nc), P(x), P(y), P(z), P(vx), P(vy), P(vz), P(h), P(m), P(prho), P(c), P(c11), P(c12), P(c13),
+        P(c22), P(c23), P(c33), C.c_double(atmin), C.c_double(atmax), C.c_double(ramp), P(wh), P(kx), P(xm), P(alpha),
+        *[P(d) for d in dV], P(ax), P(ay), P(az), P(du), C.c_float(kcour), int(av_clean))
+
+
+def rho_timestep(first, last, divv, krho):
+    return getattr(lib(), "ref_rho_timestep_" + _sfx(divv.dtype))(C.c_uint32(first), C.c_uint32(last), P(divv),
+                                                                  C.c_double(krho))
+
+
+def positions(first, last, dt, dt_m1, box, x, y, z, vx, vy, vz, x_m1, y_m1, z_m1, ax, ay, az, temp, du, du_m1, h, mui,
+              gamma):
+    lim, bc = _box(box)
+    getattr(lib(), "ref_positions_" + _sfx(h.dtype))(C.c_uint32(first), C.c_uint32(last), C.c_double(dt),
+                                                     C.c_double(dt_m1), P(lim), P(bc), P(x), P(y), P(z), P(vx), P(vy),
+                                                     P(vz), P(x_m1), P(y_m1), P(z_m1), P(ax), P(ay), P(az), P(temp),
+                                                     P(du), P(du_m1), P(h), C.c_double(mui), C.c_double(gamma))
+
+
+def update_h(first, last, ng0, nc, h):
+    getattr(lib(), "ref_update_h_" + _sfx(h.dtype))(C.c_uint32(first), C.c_uint32(last), C.c_uint(ng0), P(nc), P(h))
