@@ -1,0 +1,268 @@
+/* sphexa_b200.h — C ABI of the B200-native (sm_100a) SPH-EXA hot path.
+ *
+ * The reference (lks1248/SPH-EXA) has no C ABI: its GPU boundary is a set of
+ * `extern` C++ function templates explicitly instantiated in .cu files and
+ * archived as cstone_gpu / sph_gpu.  Every entry point below names the
+ * reference interface it replaces (file:line relative to the reference root).
+ * A maintainer binds these from the reference's accelerator switch points
+ * (`if constexpr (HaveGpu<Acc>{})`), see INTEGRATION.md.
+ *
+ * Conventions
+ *  - all pointers are DEVICE pointers unless the name ends in _h / says "host"
+ *  - every call returns 0 on success, non-zero on error; sphb200_last_error()
+ *    gives the message (the C++ shim rethrows std::runtime_error like the reference)
+ *  - all work is issued on the context's stream; calls that return scalars to the
+ *    host synchronise that stream, all others are asynchronous
+ *  - KeyType = uint64_t (63-bit Hilbert keys), LocalIndex = uint32_t,
+ *    TreeNodeIndex = int32_t  (domain/include/cstone/tree/definitions.h:42)
+ *  - "real" fields: void* interpreted by `dtype`: SPHB200_F64 -> double (north-star
+ *    parity mode, T=Tm=double like sph/test/ve.cpp:53), SPHB200_MIXED -> float
+ *    (reference default HydroType, sph/include/sph/types.hpp:39-46).
+ *    Coordinates x,y,z, temp and du are always double (CoordinateType).
+ */
+#ifndef SPHEXA_B200_H
+#define SPHEXA_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SPHB200_F64 0
+#define SPHB200_MIXED 1
+
+#define SPHB200_OPEN 0
+#define SPHB200_PERIODIC 1
+#define SPHB200_FIXED 2
+
+/* mirrors cstone::Box<double> (domain/include/cstone/sfc/box.hpp:111-191) */
+typedef struct sphb200_box
+{
+    double lim[6]; /* xmin xmax ymin ymax zmin zmax */
+    double len[3]; /* xmax-xmin ...                 */
+    double inv[3]; /* 1/(xmax-xmin) ...             */
+    int bc[3];     /* SPHB200_OPEN / PERIODIC / FIXED */
+} sphb200_box;
+
+/* mirrors cstone::OctreeNsView<double,uint64_t> (domain/include/cstone/tree/octree.hpp:295-316) */
+typedef struct sphb200_tree_view
+{
+    int numLeafNodes;
+    int numNodes;
+    const uint64_t* prefixes;
+    const int32_t* childOffsets;
+    const int32_t* internalToLeaf;
+    const int32_t* levelRange;
+    const uint64_t* leaves;
+    const uint32_t* layout;
+    const double* centers; /* [numNodes][3] */
+    const double* sizes;   /* [numNodes][3] */
+} sphb200_tree_view;
+
+/* particle field table, mirrors the device half of sph::ParticlesData
+ * (sph/include/sph/particles_data.hpp:203-232, particles_data_gpu.cuh) */
+typedef struct sphb200_fields
+{
+    /* conserved */
+    double *x, *y, *z;
+    void *h, *m, *vx, *vy, *vz, *x_m1, *y_m1, *z_m1;
+    double* temp;
+    void *du_m1, *alpha;
+    /* dependent */
+    void *xm, *kx, *gradh, *prho, *c;
+    void *c11, *c12, *c13, *c22, *c23, *c33;
+    void *divv, *curlv;
+    void *ax, *ay, *az;
+    double* du;
+    uint32_t* nc;                               /* neighbor count + 1 (self), indexed by particle index */
+    void *dV11, *dV12, *dV13, *dV22, *dV23, *dV33; /* only with avClean, else NULL */
+} sphb200_fields;
+
+/* physics constants, mirrors the scalar members of sph::ParticlesData
+ * (sph/include/sph/particles_data.hpp:87-138) */
+typedef struct sphb200_hydro_const
+{
+    double K;        /* kernel normalisation (kernel_3D_k) */
+    unsigned ng0, ngmax;
+    double Kcour, Krho;
+    double gamma, muiConst;
+    double alphamin, alphamax, decay_constant;
+    double Atmin, Atmax, ramp;
+    double minDt, minDt_m1;
+    const void* wh;  /* device, 20000 entries of `real` */
+    const void* whd; /* device, 20000 entries of `real` */
+    int avClean;
+} sphb200_hydro_const;
+
+typedef struct sphb200_ctx sphb200_ctx;
+
+/* ---- context ---- */
+/* stream: a cudaStream_t (e.g. torch.cuda.current_stream().cuda_stream) or NULL for a private stream */
+int sphb200_create(int device, void* stream, sphb200_ctx** out);
+void sphb200_destroy(sphb200_ctx* ctx);
+const char* sphb200_last_error(void);
+int sphb200_sync(sphb200_ctx* ctx);
+/* number of kernels this library launched since creation (bench.py gpu_launches) */
+uint64_t sphb200_launch_count(const sphb200_ctx* ctx);
+/* host helper: fill len/inv like the cstone::Box constructor (box.hpp:128-141) */
+void sphb200_make_box(const double lim_h[6], const int bc_h[3], sphb200_box* out);
+
+/* ---- a2: computeSfcKeysGpu  (domain/include/cstone/sfc/sfc_gpu.h:39, sfc_gpu.cu:38-55) ---- */
+int sphb200_sfc_keys(sphb200_ctx*, const double* x, const double* y, const double* z, size_t n, const sphb200_box* box_h,
+                     uint64_t* keys);
+/* a1: MinMaxGpu / makeGlobalBox for open axes (primitives_gpu.h:52, box_mpi.hpp:84-119); minmax_h[6] host out */
+int sphb200_minmax3(sphb200_ctx*, const double* x, const double* y, const double* z, size_t n, double* minmax_h);
+
+/* ---- a3: sortByKeyGpu + sequenceGpu (primitives_gpu.h:87-111, primitives_gpu.cu:228-298) ----
+ * keys sorted ascending in place (stable), perm[i] = original index of sorted element i */
+int sphb200_sort_by_key(sphb200_ctx*, uint64_t* keys, uint32_t* perm, size_t n);
+
+/* ---- a4: gatherGpu (primitives_gpu.h:62, primitives_gpu.cu:85-101), all fields in one launch ----
+ * src_h/dst_h: host arrays of nfields device pointers; elem_bytes_h: 4 or 8 per field */
+int sphb200_gather(sphb200_ctx*, const uint32_t* perm, size_t n, int nfields, const void* const* src_h,
+                   void* const* dst_h, const int* elem_bytes_h);
+
+/* ---- a5: computeNodeCountsGpu (csarray_gpu.h:56-67, csarray_gpu.cu:49-130) ---- */
+int sphb200_node_counts(sphb200_ctx*, const uint64_t* leaves, int numLeaves, const uint64_t* keys, size_t n,
+                        uint32_t* counts);
+
+/* ---- a6/a7: updateOctreeGpu (tree/update_gpu.cuh:58-82) = rebalanceDecision + rebalanceTree + counts ----
+ * leaves/counts are updated in place (capacity entries available); *numLeaves in/out; *converged out (host) */
+int sphb200_update_octree(sphb200_ctx*, const uint64_t* keys, size_t n, unsigned bucketSize, uint64_t* leaves,
+                          uint32_t* counts, int capacity, int* numLeaves_h, int* converged_h);
+/* computeOctree (csarray.hpp:454-468): from {0, 2^63} until converged; *iterations_h = number of update steps */
+int sphb200_compute_octree(sphb200_ctx*, const uint64_t* keys, size_t n, unsigned bucketSize, uint64_t* leaves,
+                           uint32_t* counts, int capacity, int* numLeaves_h, int* iterations_h);
+/* rebalanceDecisionGpu alone (csarray_gpu.h:70-78): ops[numLeaves] in {0,1,8,64,512,4096} */
+int sphb200_rebalance_decision(sphb200_ctx*, const uint64_t* leaves, const uint32_t* counts, int numLeaves,
+                               unsigned bucketSize, int32_t* ops, int* converged_h);
+
+/* ---- a8: buildOctreeGpu (octree_gpu.h:50, octree_gpu.cu:55-175) ----
+ * sizes: prefixes/internalToLeaf/leafToInternal [numNodes], childOffsets [numNodes+1], parents [(numNodes-1)/8],
+ * levelRange [23]; numNodes = numLeaves + (numLeaves-1)/7 */
+int sphb200_build_octree(sphb200_ctx*, const uint64_t* leaves, int numLeaves, uint64_t* prefixes, int32_t* childOffsets,
+                         int32_t* parents, int32_t* levelRange, int32_t* internalToLeaf, int32_t* leafToInternal);
+/* a9: computeGeoCentersGpu (source_center_gpu.h:50, source_center_gpu.cu:116-137) */
+int sphb200_node_centers(sphb200_ctx*, const uint64_t* prefixes, int numNodes, const sphb200_box* box_h,
+                         double* centers, double* sizes);
+/* computeNodeLayout for one rank: exclusive scan of counts, layout[numLeaves+1] (domain/layout.hpp:150-163) */
+int sphb200_layout(sphb200_ctx*, const uint32_t* counts, int numLeaves, uint32_t* layout);
+
+/* ---- a13: neighbor search (traversal/find_neighbors.cuh:436-498 + xmass_gpu.cu:82-92 h iteration) ----
+ * For every i in [first,last): all j != i with PBC-folded |r_ij|^2 < (2 h_i)^2 (findneighbors.hpp:95-165),
+ * ascending j.  With iterate_h the coupled h/neighbor-count iteration of sph/find_neighbors.hpp:10-45 runs
+ * (h updated in place, <= 10 iterations).  nc[i - first] = count + 1.
+ * neighbors: "slab" layout, group g = (i-first)/32, lane = (i-first)%32:
+ *            neighbors[((size_t)g*ngmax + k)*32 + lane], k < min(count, ngmax)
+ * size in uint32: sphb200_neighbors_size(last-first, ngmax).  *numFails_h: non-converged particles. */
+size_t sphb200_neighbors_size(size_t numTargets, unsigned ngmax);
+int sphb200_find_neighbors(sphb200_ctx*, const sphb200_tree_view* tree_h, const double* x, const double* y,
+                           const double* z, void* h, int dtype, uint32_t first, uint32_t last,
+                           const sphb200_box* box_h, unsigned ng0, unsigned ngmax, int iterate_h, uint32_t* neighbors,
+                           uint32_t* nc, unsigned* numFails_h);
+/* slab layout -> reference CPU layout neighbors[(i-first)*ngmax + k] (particles_data.hpp:235) */
+int sphb200_neighbors_to_rowmajor(sphb200_ctx*, const uint32_t* slab, const uint32_t* nc, uint32_t numTargets,
+                                  unsigned ngmax, uint32_t* rowmajor);
+
+/* ---- a14..a19: SPH-VE operators (sph/include/sph/sph_gpu.hpp:13-82) ----
+ * nc is indexed like fields (nc = f->nc, entries [first,last) valid), neighbors in slab layout rel. to first */
+int sphb200_xmass(sphb200_ctx*, int dtype, uint32_t first, uint32_t last, const sphb200_box* box_h,
+                  const sphb200_hydro_const* hc_h, const uint32_t* neighbors, const sphb200_fields* f_h);
+int sphb200_ve_def_gradh(sphb200_ctx*, int dtype, uint32_t first, uint32_t last, const sphb200_box* box_h,
+                         const sphb200_hydro_const* hc_h, const uint32_t* neighbors, const sphb200_fields* f_h);
+int sphb200_eos(sphb200_ctx*, int dtype, uint32_t first, uint32_t last, const sphb200_hydro_const* hc_h,
+                const sphb200_fields* f_h);
+int sphb200_iad_divv_curlv(sphb200_ctx*, int dtype, uint32_t first, uint32_t last, const sphb200_box* box_h,
+                           const sphb200_hydro_const* hc_h, const uint32_t* neighbors, const sphb200_fields* f_h);
+int sphb200_av_switches(sphb200_ctx*, int dtype, uint32_t first, uint32_t last, const sphb200_box* box_h,
+                        const sphb200_hydro_const* hc_h, const uint32_t* neighbors, const sphb200_fields* f_h);
+/* *minDtCourant_h (host out, may be NULL -> stays on device for sphb200_timestep) */
+int sphb200_momentum_energy(sphb200_ctx*, int dtype, uint32_t first, uint32_t last, const sphb200_box* box_h,
+                            const sphb200_hydro_const* hc_h, const uint32_t* neighbors, const sphb200_fields* f_h,
+                            double* minDtCourant_h);
+
+/* ---- a20: rhoTimestep + computeTimestep local part (sph/include/sph/ts_global.hpp:71-112) ----
+ * out_h[0] = minDtCourant (from the last momentum_energy call), out_h[1] = Krho/|max divv|,
+ * out_h[2] = min(out[0], out[1], 1.1*minDt)  (the value fed to the global MIN all-reduce) */
+int sphb200_timestep(sphb200_ctx*, int dtype, uint32_t first, uint32_t last, const sphb200_hydro_const* hc_h,
+                     const sphb200_fields* f_h, double* out_h);
+/* device address of the 3 doubles above, for an in-stream ncclAllReduce(min) */
+double* sphb200_timestep_device_ptr(sphb200_ctx*);
+
+/* ---- a21: computePositionsGpu + updateSmoothingLengthGpu (positions_gpu.cu:119-192, update_h_gpu.cu:40-62) ---- */
+int sphb200_positions_update_h(sphb200_ctx*, int dtype, uint32_t first, uint32_t last, const sphb200_box* box_h,
+                               const sphb200_hydro_const* hc_h, double dt, double dt_m1, const sphb200_fields* f_h);
+
+/* ---- halo pack / unpack: gatherRanges / scatterRanges (halos/gather_halos_gpu.h:38-46) ----
+ * copies numRanges index ranges [rangeBegin[r], rangeEnd[r]) of nfields arrays into/out of one packed buffer
+ * (field-major, ranges concatenated).  range arrays are device pointers. */
+int sphb200_pack_ranges(sphb200_ctx*, const uint32_t* rangeScan, const uint32_t* rangeBegin, int numRanges,
+                        uint32_t totalElems, int nfields, const void* const* src_h, const int* elem_bytes_h,
+                        void* packed);
+int sphb200_unpack_ranges(sphb200_ctx*, const uint32_t* rangeScan, const uint32_t* rangeBegin, int numRanges,
+                          uint32_t totalElems, int nfields, void* const* dst_h, const int* elem_bytes_h,
+                          const void* packed);
+
+/* ======================= tier 2: domain + propagator ======================= */
+/* cstone::Domain<uint64_t,double,GpuTag> (domain/include/cstone/domain/domain.hpp:65-683) and
+ * sphexa::HydroVeProp (main/src/propagator/ve_hydro.hpp:54-219) for one rank of an SFC-partitioned run.
+ * The simulation object owns all device arrays ([halos|assigned|halos] layout, SFC order). */
+typedef struct sphb200_sim sphb200_sim;
+
+typedef struct sphb200_sim_config
+{
+    int dtype;            /* SPHB200_F64 | SPHB200_MIXED */
+    int rank, numRanks;   /* SFC partition; numRanks==1 -> no halos */
+    unsigned bucketSize;      /* global tree bucket, sphexa.cpp:133-135: max(64, N/(100 P)) */
+    unsigned bucketSizeFocus; /* 64 */
+    size_t capacity;      /* max particles incl. halos on this rank */
+    sphb200_box box;
+    sphb200_hydro_const hc; /* wh/whd are HOST pointers here (copied to device) */
+} sphb200_sim_config;
+
+/* host field table for upload/download: same names as sphb200_fields, host pointers; NULL = skip */
+int sphb200_sim_create(sphb200_ctx*, const sphb200_sim_config* cfg, sphb200_sim** out);
+void sphb200_sim_destroy(sphb200_sim*);
+/* upload n particles (conserved fields) into the assigned range; any order */
+int sphb200_sim_upload(sphb200_sim*, size_t n, const sphb200_fields* host_fields);
+/* download assigned range [startIndex,endIndex) of every non-NULL field */
+int sphb200_sim_download(sphb200_sim*, const sphb200_fields* host_fields, uint64_t* keys_h);
+/* Domain::sync (domain.hpp:196-244): keys, sort, gather, tree update, layout.  Multi-rank pieces
+ * (assignment, migration, halo discovery) are driven by the host through the calls further down. */
+int sphb200_sim_sync(sphb200_sim*);
+/* HydroVeProp::computeForces without the sync (ve_hydro.hpp:140-192), single rank */
+int sphb200_sim_compute_forces(sphb200_sim*);
+/* HydroVeProp::integrate (ve_hydro.hpp:207-217): computeTimestep + computePositions + updateSmoothingLength;
+ * globalMinDt < 0: use the local minimum */
+int sphb200_sim_integrate(sphb200_sim*, double globalMinDt);
+/* one full step = sync + computeForces + integrate (single rank) */
+int sphb200_sim_step(sphb200_sim*);
+/* step phases for multi-rank drivers: phase k runs the operators between halo exchanges k and k+1 of
+ * ve_hydro.hpp:149-192: 0: neighbors+XMass | 1: VeDefGradh+EOS | 2: IadDivvCurlv | 3: AVswitches | 4: MomentumEnergy */
+int sphb200_sim_forces_phase(sphb200_sim*, int phase);
+
+/* getters (domain.hpp:382-429) */
+uint32_t sphb200_sim_start_index(const sphb200_sim*);
+uint32_t sphb200_sim_end_index(const sphb200_sim*);
+uint32_t sphb200_sim_n_with_halos(const sphb200_sim*);
+int sphb200_sim_num_leaves(const sphb200_sim*);
+int sphb200_sim_num_global_leaves(const sphb200_sim*);
+double sphb200_sim_min_dt(const sphb200_sim*);
+double sphb200_sim_ttot(const sphb200_sim*);
+uint64_t sphb200_sim_total_neighbors(sphb200_sim*); /* sum of nc over assigned, the "Total Neighbors" check line */
+/* device field table of the simulation (for halo exchange / tests) */
+int sphb200_sim_fields(sphb200_sim*, sphb200_fields* out);
+int sphb200_sim_tree(sphb200_sim*, sphb200_tree_view* out);
+const uint64_t* sphb200_sim_keys(const sphb200_sim*);
+const uint32_t* sphb200_sim_neighbors(const sphb200_sim*);
+/* per-phase device times of the last step in ms: sync, neighbors, xmass, gradh, eos, iad, av, momentum, timestep+update */
+int sphb200_sim_phase_times(sphb200_sim*, float* ms_out9);
+/* set layout for multi-rank: arrays hold n particles, assigned = [start,end) */
+int sphb200_sim_set_layout(sphb200_sim*, uint32_t start, uint32_t end, uint32_t nWithHalos);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,155 @@
+"""ctypes binding of libsphexa_b200.so (the C ABI declared in include/sphexa_b200.h).
+
+The product path is the CUDA library; there is NO CPU fallback: importing works
+without a GPU (so that symbol checks can run), but creating a context raises if
+no CUDA device exists, and a missing library raises at import time.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libsphexa_b200.so")
+
+F64, MIXED = 0, 1
+OPEN, PERIODIC, FIXED = 0, 1, 2
+
+if not os.path.exists(LIB_PATH):
+    raise ImportError(f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                      "(the sm_100a CUDA library is the only implementation; there is no fallback)")
+
+lib = C.CDLL(LIB_PATH)
+
+vp = C.c_void_p
+
+
+class Box(C.Structure):
+    _fields_ = [("lim", C.c_double * 6), ("len", C.c_double * 3), ("inv", C.c_double * 3), ("bc", C.c_int * 3)]
+
+
+class TreeView(C.Structure):
+    _fields_ = [("numLeafNodes", C.c_int), ("numNodes", C.c_int), ("prefixes", vp), ("childOffsets", vp),
+                ("internalToLeaf", vp), ("levelRange", vp), ("leaves", vp), ("layout", vp), ("centers", vp),
+                ("sizes", vp)]
+
+
+FIELD_NAMES = ["x", "y", "z", "h", "m", "vx", "vy", "vz", "x_m1", "y_m1", "z_m1", "temp", "du_m1", "alpha",
+               "xm", "kx", "gradh", "prho", "c", "c11", "c12", "c13", "c22", "c23", "c33", "divv", "curlv",
+               "ax", "ay", "az", "du", "nc", "dV11", "dV12", "dV13", "dV22", "dV23", "dV33"]
+CONSERVED = FIELD_NAMES[:14]
+ALWAYS_F64 = {"x", "y", "z", "temp", "du"}
+
+
+class Fields(C.Structure):
+    _fields_ = [(n, vp) for n in FIELD_NAMES]
+
+
+class HydroConst(C.Structure):
+    _fields_ = [("K", C.c_double), ("ng0", C.c_uint), ("ngmax", C.c_uint), ("Kcour", C.c_double),
+                ("Krho", C.c_double), ("gamma", C.c_double), ("muiConst", C.c_double), ("alphamin", C.c_double),
+                ("alphamax", C.c_double), ("decay_constant", C.c_double), ("Atmin", C.c_double),
+                ("Atmax", C.c_double), ("ramp", C.c_double), ("minDt", C.c_double), ("minDt_m1", C.c_double),
+                ("wh", vp), ("whd", vp), ("avClean", C.c_int)]
+
+
+class SimConfig(C.Structure):
+    _fields_ = [("dtype", C.c_int), ("rank", C.c_int), ("numRanks", C.c_int), ("bucketSize", C.c_uint),
+                ("bucketSizeFocus", C.c_uint), ("capacity", C.c_size_t), ("box", Box), ("hc", HydroConst)]
+
+
+# every symbol include/sphexa_b200.h declares (checked by tests/test_abi.py)
+SYMBOLS = [
+    "sphb200_create", "sphb200_destroy", "sphb200_last_error", "sphb200_sync", "sphb200_launch_count",
+    "sphb200_make_box", "sphb200_sfc_keys", "sphb200_minmax3", "sphb200_sort_by_key", "sphb200_gather",
+    "sphb200_node_counts", "sphb200_update_octree", "sphb200_compute_octree", "sphb200_rebalance_decision",
+    "sphb200_build_octree", "sphb200_node_centers", "sphb200_layout", "sphb200_neighbors_size",
+    "sphb200_find_neighbors", "sphb200_neighbors_to_rowmajor", "sphb200_xmass", "sphb200_ve_def_gradh",
+    "sphb200_eos", "sphb200_iad_divv_curlv", "sphb200_av_switches", "sphb200_momentum_energy", "sphb200_timestep",
+    "sphb200_timestep_device_ptr", "sphb200_positions_update_h", "sphb200_pack_ranges", "sphb200_unpack_ranges",
+    "sphb200_sim_create", "sphb200_sim_destroy", "sphb200_sim_upload", "sphb200_sim_download", "sphb200_sim_sync",
+    "sphb200_sim_compute_forces", "sphb200_sim_integrate", "sphb200_sim_step", "sphb200_sim_forces_phase",
+    "sphb200_sim_start_index", "sphb200_sim_end_index", "sphb200_sim_n_with_halos", "sphb200_sim_num_leaves",
+    "sphb200_sim_num_global_leaves", "sphb200_sim_min_dt", "sphb200_sim_ttot", "sphb200_sim_total_neighbors",
+    "sphb200_sim_fields", "sphb200_sim_tree", "sphb200_sim_keys", "sphb200_sim_neighbors",
+    "sphb200_sim_phase_times", "sphb200_sim_set_layout", "sphb200_sim_local_timestep", "sphb200_sim_global_leaves",
+    "sphb200_sim_global_counts", "sphb200_sim_leaf_counts", "sphb200_sim_get_box", "sphb200_sim_set_dt",
+]
+
+lib.sphb200_last_error.restype = C.c_char_p
+lib.sphb200_launch_count.restype = C.c_uint64
+lib.sphb200_launch_count.argtypes = [vp]
+lib.sphb200_neighbors_size.restype = C.c_size_t
+lib.sphb200_neighbors_size.argtypes = [C.c_size_t, C.c_uint]
+lib.sphb200_timestep_device_ptr.restype = vp
+lib.sphb200_timestep_device_ptr.argtypes = [vp]
+for _n in ("sphb200_sim_start_index", "sphb200_sim_end_index", "sphb200_sim_n_with_halos"):
+    getattr(lib, _n).restype = C.c_uint32
+    getattr(lib, _n).argtypes = [vp]
+for _n in ("sphb200_sim_min_dt", "sphb200_sim_ttot"):
+    getattr(lib, _n).restype = C.c_double
+    getattr(lib, _n).argtypes = [vp]
+for _n in ("sphb200_sim_keys", "sphb200_sim_neighbors", "sphb200_sim_global_leaves", "sphb200_sim_global_counts",
+           "sphb200_sim_leaf_counts"):
+    getattr(lib, _n).restype = vp
+    getattr(lib, _n).argtypes = [vp]
+lib.sphb200_sim_total_neighbors.restype = C.c_uint64
+lib.sphb200_sim_total_neighbors.argtypes = [vp]
+for _n in ("sphb200_sim_num_leaves", "sphb200_sim_num_global_leaves"):
+    getattr(lib, _n).argtypes = [vp]
+lib.sphb200_destroy.argtypes = [vp]
+lib.sphb200_sim_destroy.argtypes = [vp]
+
+
+class SphError(RuntimeError):
+    """mirrors the std::runtime_error the reference throws on precondition violations"""
+
+
+def check(rc):
+    if rc != 0:
+        raise SphError(lib.sphb200_last_error().decode())
+
+
+def make_box(lim, bc):
+    b = Box()
+    lib.sphb200_make_box((C.c_double * 6)(*lim), (C.c_int * 3)(*bc), C.byref(b))
+    return b
+
+
+def ptr(t):
+    """device pointer of a torch tensor (or None)"""
+    if t is None:
+        return None
+    assert t.is_cuda and t.is_contiguous()
+    return vp(t.data_ptr())
+
+
+class Context:
+    """owns a sphb200_ctx bound to a CUDA stream (default: torch's current stream)"""
+
+    def __init__(self, device=0, stream=None):
+        import torch
+        if not torch.cuda.is_available():
+            raise SphError("sph-exa_b200 needs a CUDA device: there is no CPU fallback")
+        torch.cuda.set_device(device)
+        self.device = device
+        if stream is None:
+            stream = torch.cuda.current_stream(device).cuda_stream
+        self.h = vp()
+        check(lib.sphb200_create(device, vp(stream), C.byref(self.h)))
+
+    def close(self):
+        if self.h:
+            lib.sphb200_destroy(self.h)
+            self.h = vp()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def sync(self):
+        check(lib.sphb200_sync(self.h))
+
+    @property
+    def launches(self):
+        return lib.sphb200_launch_count(self.h)

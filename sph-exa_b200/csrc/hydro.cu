@@ -1,0 +1,809 @@
+// SPH-VE operators: XMass, VeDefGradh, EOS, IAD+divv/curlv, AV switches, momentum+energy,
+// time-step reduction, position/energy/smoothing-length update.
+//
+// One thread per target particle; neighbor indices come from the slab lists written by
+// findNeighborsKernel (k-th neighbor of lane l of slab g at nidx[(g*ngmax + k)*32 + l], so a warp
+// reads 128 contiguous bytes per k).  Neighbor fields are gathered through the read-only path;
+// lists are ascending in j and targets are SFC-consecutive, so a warp's gathers fall into a few
+// cache lines.  Pair arithmetic restates the reference J-loops (sph/include/sph/hydro_ve/*_kern.hpp)
+// expression by expression with T = double (f64 mode) or float (mixed mode, reference default).
+#include "common.cuh"
+
+namespace sphb200
+{
+
+constexpr int kHydroBlock = 128;
+
+template<class T>
+struct F
+{
+    const double *x, *y, *z;
+    T *h, *m, *vx, *vy, *vz, *x_m1, *y_m1, *z_m1;
+    double* temp;
+    T *du_m1, *alpha;
+    T *xm, *kx, *gradh, *prho, *c;
+    T *c11, *c12, *c13, *c22, *c23, *c33;
+    T *divv, *curlv, *ax, *ay, *az;
+    double* du;
+    uint32_t* nc;
+    T *dV11, *dV12, *dV13, *dV22, *dV23, *dV33;
+};
+
+template<class T>
+static F<T> typed(const sphb200_fields& f)
+{
+    F<T> r;
+    r.x = f.x; r.y = f.y; r.z = f.z;
+#define CP(n) r.n = static_cast<T*>(f.n)
+    CP(h); CP(m); CP(vx); CP(vy); CP(vz); CP(x_m1); CP(y_m1); CP(z_m1); CP(du_m1); CP(alpha);
+    CP(xm); CP(kx); CP(gradh); CP(prho); CP(c); CP(c11); CP(c12); CP(c13); CP(c22); CP(c23); CP(c33);
+    CP(divv); CP(curlv); CP(ax); CP(ay); CP(az); CP(dV11); CP(dV12); CP(dV13); CP(dV22); CP(dV23); CP(dV33);
+#undef CP
+    r.temp = f.temp; r.du = f.du; r.nc = f.nc;
+    return r;
+}
+
+struct PbcBox
+{
+    double lx, ly, lz;
+    bool px, py, pz;
+    bool fx, fy, fz;
+    double lim[6];
+};
+
+static PbcBox pbcBox(const sphb200_box& b)
+{
+    PbcBox p;
+    p.lx = b.len[0]; p.ly = b.len[1]; p.lz = b.len[2];
+    p.px = b.bc[0] == SPHB200_PERIODIC; p.py = b.bc[1] == SPHB200_PERIODIC; p.pz = b.bc[2] == SPHB200_PERIODIC;
+    p.fx = b.bc[0] == SPHB200_FIXED; p.fy = b.bc[1] == SPHB200_FIXED; p.fz = b.bc[2] == SPHB200_FIXED;
+    for (int k = 0; k < 6; ++k) p.lim[k] = b.lim[k];
+    return p;
+}
+
+//! @brief legacy minimum-image used inside the J-loops, cstone::applyPBC (sfc/box.hpp:234-255)
+template<class T>
+__device__ __forceinline__ void applyPBC(const PbcBox& b, T r, T& xx, T& yy, T& zz)
+{
+    if (b.px && xx > r) xx -= b.lx;
+    else if (b.px && xx < -r) xx += b.lx;
+    if (b.py && yy > r) yy -= b.ly;
+    else if (b.py && yy < -r) yy += b.ly;
+    if (b.pz && zz > r) zz -= b.lz;
+    else if (b.pz && zz < -r) zz += b.lz;
+}
+
+//! @brief tabulated kernel with linear interpolation, sph::lt::lookup (sph/table_lookup.hpp:13-25)
+template<class T>
+__device__ __forceinline__ T lookup(const T* __restrict__ table, T v)
+{
+    constexpr int numIntervals = kTableSize - 1;
+    constexpr T support        = 2.0;
+    constexpr T dx             = support / numIntervals;
+    constexpr T invDx          = T(1) / dx;
+
+    int idx = v * invDx;
+    if (idx >= numIntervals) return T(0);
+    T t0         = __ldg(table + idx);
+    T t1         = __ldg(table + idx + 1);
+    T derivative = (t1 - t0) * invDx;
+    return t0 + derivative * (v - T(idx) * dx);
+}
+
+struct NbList
+{
+    const uint32_t* base; // entry k at base[k * 32]
+    unsigned count;
+    __device__ __forceinline__ uint32_t operator[](unsigned k) const { return __ldg(base + size_t(k) * 32); }
+};
+
+__device__ __forceinline__ NbList nbList(const uint32_t* nidx, const uint32_t* nc, uint32_t first, uint32_t i,
+                                         unsigned ngmax)
+{
+    uint32_t ni = i - first;
+    NbList l;
+    l.base  = nidx + (size_t(ni >> 5) * ngmax) * 32 + (ni & 31);
+    l.count = min(nc[i] - 1, ngmax);
+    return l;
+}
+
+#define LD(p, j) __ldg((p) + (j))
+
+// ---------------------------------------------------------------- XMass (xmass_kern.hpp:50-78)
+template<class T>
+__global__ void __launch_bounds__(kHydroBlock)
+    xmassKernel(uint32_t first, uint32_t last, unsigned ngmax, double K, PbcBox box, const uint32_t* __restrict__ nidx,
+                F<T> f, const T* __restrict__ wh)
+{
+    uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= last) return;
+    NbList nb = nbList(nidx, f.nc, first, i, ngmax);
+
+    double xi = f.x[i], yi = f.y[i], zi = f.z[i];
+    T hi = f.h[i], mi = f.m[i];
+    T hInv  = 1.0 / hi;
+    T h3Inv = hInv * hInv * hInv;
+
+    T rho0i = mi;
+    for (unsigned pj = 0; pj < nb.count; ++pj)
+    {
+        uint32_t j = nb[pj];
+        T xx = xi - LD(f.x, j), yy = yi - LD(f.y, j), zz = zi - LD(f.z, j);
+        applyPBC(box, T(2) * hi, xx, yy, zz);
+        T dist = sqrt(xx * xx + yy * yy + zz * zz);
+        T vloc = dist * hInv;
+        T w    = lookup(wh, vloc);
+        rho0i += w * LD(f.m, j);
+    }
+    f.xm[i] = T(mi / (rho0i * K * h3Inv));
+}
+
+// ---------------------------------------------------------------- VeDefGradh (ve_def_gradh_kern.hpp:43-90)
+template<class T>
+__global__ void __launch_bounds__(kHydroBlock)
+    veDefGradhKernel(uint32_t first, uint32_t last, unsigned ngmax, double K, PbcBox box,
+                     const uint32_t* __restrict__ nidx, F<T> f, const T* __restrict__ wh, const T* __restrict__ whd)
+{
+    uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= last) return;
+    NbList nb = nbList(nidx, f.nc, first, i, ngmax);
+
+    double xi = f.x[i], yi = f.y[i], zi = f.z[i];
+    T hi = f.h[i], mi = f.m[i], xmassi = f.xm[i];
+    T hInv  = T(1) / hi;
+    T h3Inv = hInv * hInv * hInv;
+
+    T kxi      = xmassi;
+    T whomegai = -T(3) * xmassi;
+    T wrho0i   = -T(3) * mi;
+
+    for (unsigned pj = 0; pj < nb.count; ++pj)
+    {
+        uint32_t j = nb[pj];
+        T xx = xi - LD(f.x, j), yy = yi - LD(f.y, j), zz = zi - LD(f.z, j);
+        applyPBC(box, T(2) * hi, xx, yy, zz);
+        T dist   = sqrt(xx * xx + yy * yy + zz * zz);
+        T vloc   = dist * hInv;
+        T w      = lookup(wh, vloc);
+        T dw     = lookup(whd, vloc);
+        T dterh  = -(T(3) * w + vloc * dw);
+        T xmassj = LD(f.xm, j);
+
+        kxi += w * xmassj;
+        whomegai += dterh * xmassj;
+        wrho0i += dterh * LD(f.m, j);
+    }
+
+    // compound assignments exactly as ve_def_gradh_kern.hpp:78-80 (right-hand side evaluated first, K is Tc)
+    kxi *= K * h3Inv;
+    whomegai *= K * h3Inv * hInv;
+    wrho0i *= K * h3Inv * hInv;
+
+    whomegai = whomegai * mi / xmassi + (kxi - K * xmassi * h3Inv) * wrho0i;
+    T rhoi   = kxi * mi / xmassi;
+    T dhdrho = -hi / (rhoi * T(3));
+
+    f.kx[i]    = kxi;
+    f.gradh[i] = T(1) - dhdrho * whomegai;
+}
+
+// ---------------------------------------------------------------- EOS (hydro_ve/eos.hpp:52-76, sph/eos.hpp:13-40)
+template<class T>
+__global__ void eosKernel(uint32_t first, uint32_t last, F<T> f, T muiConst, double gamma)
+{
+    uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= last) return;
+    T rho = f.kx[i] * f.m[i] / f.xm[i];
+    // idealGasCv returns in the type of mui (Tmass)
+    const T R  = 8.317e7;
+    T cv       = T(R / muiConst / (gamma - T(1)));
+    double tmp = cv * f.temp[i] * (gamma - 1.0);
+    double p   = rho * tmp;
+    double c   = sqrt(tmp);
+    f.prho[i]  = T(p / (f.kx[i] * f.m[i] * f.m[i] * f.gradh[i]));
+    f.c[i]     = T(c);
+}
+
+// ---------------------------------------------------------------- IAD + divv/curlv (iad_kern.hpp:43-109, divv_curlv_kern.hpp:44-123)
+template<class T>
+__global__ void __launch_bounds__(kHydroBlock)
+    iadDivvCurlvKernel(uint32_t first, uint32_t last, unsigned ngmax, double K, PbcBox box,
+                       const uint32_t* __restrict__ nidx, F<T> f, const T* __restrict__ wh, bool doGradV)
+{
+    uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= last) return;
+    NbList nb = nbList(nidx, f.nc, first, i, ngmax);
+
+    double xi = f.x[i], yi = f.y[i], zi = f.z[i];
+    T hi    = f.h[i];
+    T hiInv = T(1) / hi;
+
+    T tau11 = 0.0, tau12 = 0.0, tau13 = 0.0, tau22 = 0.0, tau23 = 0.0, tau33 = 0.0;
+    for (unsigned pj = 0; pj < nb.count; ++pj)
+    {
+        uint32_t j = nb[pj];
+        T rx = xi - LD(f.x, j), ry = yi - LD(f.y, j), rz = zi - LD(f.z, j);
+        applyPBC(box, T(2) * hi, rx, ry, rz);
+        T dist   = sqrt(rx * rx + ry * ry + rz * rz);
+        T vloc   = dist * hiInv;
+        T w      = lookup(wh, vloc);
+        T volj_w = LD(f.xm, j) / LD(f.kx, j) * w;
+
+        tau11 += rx * rx * volj_w;
+        tau12 += rx * ry * volj_w;
+        tau13 += rx * rz * volj_w;
+        tau22 += ry * ry * volj_w;
+        tau23 += ry * rz * volj_w;
+        tau33 += rz * rz * volj_w;
+    }
+
+    auto getExp = [](T val) { return (val == T(0) ? 0 : ilogb(val)); };
+    int tauExpSum = getExp(tau11) + getExp(tau12) + getExp(tau13) + getExp(tau22) + getExp(tau23) + getExp(tau33);
+    T normalization = ldexp(T(1), -tauExpSum / 6);
+
+    tau11 *= normalization;
+    tau12 *= normalization;
+    tau13 *= normalization;
+    tau22 *= normalization;
+    tau23 *= normalization;
+    tau33 *= normalization;
+
+    T det = tau11 * tau22 * tau33 + T(2) * tau12 * tau23 * tau13 - tau11 * tau23 * tau23 - tau22 * tau13 * tau13 -
+            tau33 * tau12 * tau12;
+    T factor = normalization * (hi * hi * hi) / (det * K);
+
+    T c11i = (tau22 * tau33 - tau23 * tau23) * factor;
+    T c12i = (tau13 * tau23 - tau33 * tau12) * factor;
+    T c13i = (tau12 * tau23 - tau22 * tau13) * factor;
+    T c22i = (tau11 * tau33 - tau13 * tau13) * factor;
+    T c23i = (tau13 * tau12 - tau11 * tau23) * factor;
+    T c33i = (tau11 * tau22 - tau12 * tau12) * factor;
+    f.c11[i] = c11i; f.c12[i] = c12i; f.c13[i] = c13i; f.c22[i] = c22i; f.c23[i] = c23i; f.c33[i] = c33i;
+
+    // second pass over the same list: velocity gradient
+    T vxi = f.vx[i], vyi = f.vy[i], vzi = f.vz[i], kxi = f.kx[i];
+    T hiInv3 = hiInv * hiInv * hiInv;
+    T dVx[3] = {0, 0, 0}, dVy[3] = {0, 0, 0}, dVz[3] = {0, 0, 0};
+    for (unsigned pj = 0; pj < nb.count; ++pj)
+    {
+        uint32_t j = nb[pj];
+        T rx = xi - LD(f.x, j), ry = yi - LD(f.y, j), rz = zi - LD(f.z, j);
+        applyPBC(box, T(2) * hi, rx, ry, rz);
+        T r2   = rx * rx + ry * ry + rz * rz;
+        T dist = sqrt(r2);
+
+        T vx_ji = LD(f.vx, j) - vxi;
+        T vy_ji = LD(f.vy, j) - vyi;
+        T vz_ji = LD(f.vz, j) - vzi;
+
+        T v1 = dist * hiInv;
+        T Wi = lookup(wh, v1);
+
+        T tA0 = -(c11i * rx + c12i * ry + c13i * rz) * Wi;
+        T tA1 = -(c12i * rx + c22i * ry + c23i * rz) * Wi;
+        T tA2 = -(c13i * rx + c23i * ry + c33i * rz) * Wi;
+
+        T xmassj = LD(f.xm, j);
+        T sx = vx_ji * xmassj, sy = vy_ji * xmassj, sz = vz_ji * xmassj;
+        dVx[0] += sx * tA0; dVx[1] += sx * tA1; dVx[2] += sx * tA2;
+        dVy[0] += sy * tA0; dVy[1] += sy * tA1; dVy[2] += sy * tA2;
+        dVz[0] += sz * tA0; dVz[1] += sz * tA1; dVz[2] += sz * tA2;
+    }
+
+    T norm_kxi = K * hiInv3 / kxi;
+    f.divv[i]  = norm_kxi * (dVx[0] + dVy[1] + dVz[2]);
+    if (f.curlv)
+    {
+        T cx = dVz[1] - dVy[2], cy = dVx[2] - dVz[0], cz = dVy[0] - dVx[1];
+        f.curlv[i] = norm_kxi * sqrt(cx * cx + cy * cy + cz * cz);
+    }
+    if (doGradV)
+    {
+        f.dV11[i] = norm_kxi * dVx[0];
+        f.dV12[i] = norm_kxi * (dVx[1] + dVy[0]);
+        f.dV13[i] = norm_kxi * (dVx[2] + dVz[0]);
+        f.dV22[i] = norm_kxi * dVy[1];
+        f.dV23[i] = norm_kxi * (dVy[2] + dVz[1]);
+        f.dV33[i] = norm_kxi * dVz[2];
+    }
+}
+
+// ---------------------------------------------------------------- AV switches (av_switches_kern.hpp:44-137)
+template<class T>
+__global__ void __launch_bounds__(kHydroBlock)
+    avSwitchesKernel(uint32_t first, uint32_t last, unsigned ngmax, double K, PbcBox box,
+                     const uint32_t* __restrict__ nidx, F<T> f, const T* __restrict__ wh, double dt, T alphamin,
+                     T alphamax, T decay_constant)
+{
+    uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= last) return;
+    NbList nb = nbList(nidx, f.nc, first, i, ngmax);
+
+    double xi = f.x[i], yi = f.y[i], zi = f.z[i];
+    T vxi = f.vx[i], vyi = f.vy[i], vzi = f.vz[i];
+    T hi = f.h[i], ci = f.c[i];
+    T c11i = f.c11[i], c12i = f.c12[i], c13i = f.c13[i], c22i = f.c22[i], c23i = f.c23[i], c33i = f.c33[i];
+
+    T vijsignal_i = T(1.e-40) * ci;
+    T hiInv  = T(1) / hi;
+    T hiInv3 = hiInv * hiInv * hiInv;
+    T divv_i = f.divv[i];
+    T alpha_i = f.alpha[i];
+
+    T graddivv_x = 0.0, graddivv_y = 0.0, graddivv_z = 0.0;
+    for (unsigned pj = 0; pj < nb.count; ++pj)
+    {
+        uint32_t j = nb[pj];
+        T rx = xi - LD(f.x, j), ry = yi - LD(f.y, j), rz = zi - LD(f.z, j);
+        applyPBC(box, T(2) * hi, rx, ry, rz);
+        T r2   = rx * rx + ry * ry + rz * rz;
+        T dist = sqrt(r2);
+
+        T vx_ij = vxi - LD(f.vx, j);
+        T vy_ij = vyi - LD(f.vy, j);
+        T vz_ij = vzi - LD(f.vz, j);
+
+        T rv           = rx * vx_ij + ry * vy_ij + rz * vz_ij;
+        T vijsignal_ij = 0.0;
+        if (rv < T(0)) { vijsignal_ij = ci + LD(f.c, j) - T(3) * rv / dist; }
+        vijsignal_i = max(vijsignal_i, vijsignal_ij);
+
+        T v1 = dist * hiInv;
+        T Wi = K * hiInv3 * lookup(wh, v1);
+
+        T termA1 = -(c11i * rx + c12i * ry + c13i * rz) * Wi;
+        T termA2 = -(c12i * rx + c22i * ry + c23i * rz) * Wi;
+        T termA3 = -(c13i * rx + c23i * ry + c33i * rz) * Wi;
+
+        T volj   = LD(f.xm, j) / LD(f.kx, j);
+        T factor = volj * (divv_i - LD(f.divv, j));
+
+        graddivv_x += factor * termA1;
+        graddivv_y += factor * termA2;
+        graddivv_z += factor * termA3;
+    }
+
+    T graddivv = sqrt(graddivv_x * graddivv_x + graddivv_y * graddivv_y + graddivv_z * graddivv_z);
+
+    T alphaloc = 0.0;
+    if (divv_i < T(0))
+    {
+        T a_const = hi * hi * graddivv;
+        alphaloc  = alphamax * a_const / (a_const + hi * abs(divv_i) + T(0.05) * ci);
+    }
+
+    if (alphaloc >= alpha_i) { alpha_i = alphaloc; }
+    else
+    {
+        T decay    = hi / (decay_constant * vijsignal_i);
+        T alphadot = 0.0;
+        if (alphaloc >= alphamin) { alphadot = (alphaloc - alpha_i) / decay; }
+        else { alphadot = (alphamin - alpha_i) / decay; }
+        alpha_i += alphadot * dt;
+    }
+    f.alpha[i] = alpha_i;
+}
+
+// ---------------------------------------------------------------- momentum + energy (momentum_energy_kern.hpp:43-222)
+template<class T>
+__device__ __forceinline__ T avRvCorrection(T rx, T ry, T rz, T eta_ab, T eta_crit, const T* gi, const T* gj)
+{
+    // symv: upper-triangular product as written in sph/kernels.hpp:86-94
+    T s0 = gi[0] * rx + gi[1] * ry + gi[2] * rz, s1 = gi[3] * ry + gi[4] * rz, s2 = gi[5] * rz;
+    T dmy1 = rx * s0 + ry * s1 + rz * s2;
+    T t0 = gj[0] * rx + gj[1] * ry + gj[2] * rz, t1 = gj[3] * ry + gj[4] * rz, t2 = gj[5] * rz;
+    T dmy2 = rx * t0 + ry * t1 + rz * t2;
+    T dmy3 = T(1);
+    if (eta_ab < eta_crit)
+    {
+        T etaDiff = T(5) * (eta_ab - eta_crit);
+        dmy3      = exp(-etaDiff * etaDiff);
+    }
+    T A_ab   = (dmy2 != T(0)) ? dmy1 / dmy2 : T(0);
+    T A_abp1 = T(1) + A_ab;
+    T phi_ab = T(0.5) * dmy3 * max(T(0), min(T(1), T(4) * A_ab / (A_abp1 * A_abp1)));
+    return -phi_ab * (dmy1 + dmy2);
+}
+
+template<bool avClean, class T>
+__global__ void __launch_bounds__(kHydroBlock)
+    momentumEnergyKernel(uint32_t first, uint32_t last, unsigned ngmax, double K, PbcBox box,
+                         const uint32_t* __restrict__ nidx, F<T> f, const T* __restrict__ wh, T Atmin, T Atmax, T ramp,
+                         float Kcour, unsigned long long* __restrict__ minDtKey)
+{
+    uint32_t i  = first + blockIdx.x * blockDim.x + threadIdx.x;
+    T dt_i      = INFINITY;
+    if (i < last)
+    {
+        NbList nb = nbList(nidx, f.nc, first, i, ngmax);
+
+        double xi = f.x[i], yi = f.y[i], zi = f.z[i];
+        T vxi = f.vx[i], vyi = f.vy[i], vzi = f.vz[i];
+        T hi = f.h[i], mi = f.m[i], ci = f.c[i], kxi = f.kx[i];
+        T alpha_i = f.alpha[i];
+        T xmassi  = f.xm[i];
+        T rhoi    = kxi * mi / xmassi;
+        T prhoi   = f.prho[i];
+
+        T hiInv  = T(1) / hi;
+        T hiInv3 = hiInv * hiInv * hiInv;
+
+        T maxvsignali = 0.0;
+        T momentum_x = 0.0, momentum_y = 0.0, momentum_z = 0.0, energy = 0.0;
+        T a_visc_energy = 0.0;
+
+        T c11i = f.c11[i], c12i = f.c12[i], c13i = f.c13[i], c22i = f.c22[i], c23i = f.c23[i], c33i = f.c33[i];
+
+        T gradV_i[6];
+        if (avClean)
+        {
+            gradV_i[0] = f.dV11[i]; gradV_i[1] = f.dV12[i]; gradV_i[2] = f.dV13[i];
+            gradV_i[3] = f.dV22[i]; gradV_i[4] = f.dV23[i]; gradV_i[5] = f.dV33[i];
+        }
+
+        T eta_crit = cbrt(T(32) * M_PI / T(3) / T(nb.count + 1));
+
+        for (unsigned pj = 0; pj < nb.count; ++pj)
+        {
+            uint32_t j = nb[pj];
+
+            T rx = xi - LD(f.x, j), ry = yi - LD(f.y, j), rz = zi - LD(f.z, j);
+            T vxj = LD(f.vx, j), vyj = LD(f.vy, j), vzj = LD(f.vz, j);
+            applyPBC(box, T(2) * hi, rx, ry, rz);
+
+            T r2   = rx * rx + ry * ry + rz * rz;
+            T dist = sqrt(r2);
+
+            T vx_ij = vxi - vxj, vy_ij = vyi - vyj, vz_ij = vzi - vzj;
+
+            T hj    = LD(f.h, j);
+            T hjInv = T(1) / hj;
+
+            T v1 = dist * hiInv;
+            T v2 = dist * hjInv;
+
+            T hjInv3 = hjInv * hjInv * hjInv;
+            T Wi     = hiInv3 * lookup(wh, v1);
+            T Wj     = hjInv3 * lookup(wh, v2);
+
+            T termA1_i = -(c11i * rx + c12i * ry + c13i * rz) * Wi;
+            T termA2_i = -(c12i * rx + c22i * ry + c23i * rz) * Wi;
+            T termA3_i = -(c13i * rx + c23i * ry + c33i * rz) * Wi;
+
+            T c11j = LD(f.c11, j), c12j = LD(f.c12, j), c13j = LD(f.c13, j);
+            T c22j = LD(f.c22, j), c23j = LD(f.c23, j), c33j = LD(f.c33, j);
+
+            T termA1_j = -(c11j * rx + c12j * ry + c13j * rz) * Wj;
+            T termA2_j = -(c12j * rx + c22j * ry + c23j * rz) * Wj;
+            T termA3_j = -(c13j * rx + c23j * ry + c33j * rz) * Wj;
+
+            T mj = LD(f.m, j), cj = LD(f.c, j), kxj = LD(f.kx, j), xmassj = LD(f.xm, j);
+            T rhoj = kxj * mj / xmassj;
+
+            T rv = rx * vx_ij + ry * vy_ij + rz * vz_ij;
+            if (avClean)
+            {
+                T gradV_j[6] = {LD(f.dV11, j), LD(f.dV12, j), LD(f.dV13, j), LD(f.dV22, j), LD(f.dV23, j), LD(f.dV33, j)};
+                rv += avRvCorrection(rx, ry, rz, min(v1, v2), eta_crit, gradV_i, gradV_j);
+            }
+
+            T wij = rv / dist;
+            // artificial_viscosity (sph/kernels.hpp:70-83), beta = 2
+            T viscosity_ij = 0.0;
+            if (wij < 0.0)
+            {
+                T vij_signal = (alpha_i + LD(f.alpha, j)) / 4.0 * (ci + cj) - T(2.0) * wij;
+                viscosity_ij = -vij_signal * wij;
+            }
+
+            T vijsignal = T(0.5) * (ci + cj) - T(2) * wij;
+            maxvsignali = (vijsignal > maxvsignali) ? vijsignal : maxvsignali;
+
+            T a_mom, b_mom;
+            T Atwood = (abs(rhoi - rhoj)) / (rhoi + rhoj);
+            if (Atwood < Atmin)
+            {
+                a_mom = xmassi * xmassi;
+                b_mom = xmassj * xmassj;
+            }
+            else if (Atwood > Atmax)
+            {
+                a_mom = xmassi * xmassj;
+                b_mom = a_mom;
+            }
+            else
+            {
+                T sigma_ij = ramp * (Atwood - Atmin);
+                a_mom      = pow(xmassi, T(2) - sigma_ij) * pow(xmassj, sigma_ij);
+                b_mom      = pow(xmassj, T(2) - sigma_ij) * pow(xmassi, sigma_ij);
+            }
+
+            T a_visc   = mj / rhoi * viscosity_ij;
+            T b_visc   = mj / rhoj * viscosity_ij;
+            T a_visc_x = T(0.5) * (a_visc * termA1_i + b_visc * termA1_j);
+            T a_visc_y = T(0.5) * (a_visc * termA2_i + b_visc * termA2_j);
+            T a_visc_z = T(0.5) * (a_visc * termA3_i + b_visc * termA3_j);
+            a_visc_energy += a_visc_x * vx_ij + a_visc_y * vy_ij + a_visc_z * vz_ij;
+
+            energy += mj * a_mom * (vx_ij * termA1_i + vy_ij * termA2_i + vz_ij * termA3_i);
+
+            T momentum_i = mj * prhoi * a_mom;
+            T momentum_j = mj * LD(f.prho, j) * b_mom;
+            momentum_x += momentum_i * termA1_i + momentum_j * termA1_j + a_visc_x;
+            momentum_y += momentum_i * termA2_i + momentum_j * termA2_j + a_visc_y;
+            momentum_z += momentum_i * termA3_i + momentum_j * termA3_j + a_visc_z;
+        }
+
+        a_visc_energy = max(T(0), a_visc_energy);
+        f.du[i]       = K * (prhoi * energy + T(0.5) * a_visc_energy);
+        f.ax[i]       = -K * momentum_x;
+        f.ay[i]       = -K * momentum_y;
+        f.az[i]       = -K * momentum_z;
+
+        // tsKCourant (sph/kernels.hpp:10-16)
+        T v  = maxvsignali > T(0) ? maxvsignali : ci;
+        dt_i = T(Kcour * hi / v);
+    }
+
+    // block minimum -> one ordered-key atomic per warp
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+        dt_i = min(dt_i, __shfl_xor_sync(0xffffffffu, dt_i, o));
+    if ((threadIdx.x & 31) == 0) atomicMin(minDtKey, orderedKey(double(dt_i)));
+}
+
+// ---------------------------------------------------------------- timestep (ts_global.hpp:71-112)
+template<class T>
+__global__ void __launch_bounds__(256) maxDivvKernel(const T* __restrict__ divv, uint32_t first, uint32_t last,
+                                                     unsigned long long* __restrict__ maxKey)
+{
+    T m = -INFINITY;
+    for (size_t i = size_t(first) + size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < last;
+         i += size_t(gridDim.x) * blockDim.x)
+        m = max(m, divv[i]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+        m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0) atomicMax(maxKey, orderedKey(double(m)));
+}
+
+__global__ void initDtKeysKernel(unsigned long long* keys)
+{
+    keys[0] = ~0ull; // min courant
+    keys[1] = 0ull;  // max divv
+}
+
+__global__ void initCourantKeyKernel(unsigned long long* keys) { keys[0] = ~0ull; }
+__global__ void initDivvKeyKernel(unsigned long long* keys) { keys[1] = 0ull; }
+
+//! @brief out[0]=minDtCourant, out[1]=Krho/|maxDivv|, out[2]=min(out0,out1,1.1*minDt)
+__global__ void finalizeDtKernel(const unsigned long long* keys, double Krho, double maxDtIncrease, double minDt,
+                                 double* out, int isFloat)
+{
+    double courant = fromOrderedKey(keys[0]);
+    double maxDivv = fromOrderedKey(keys[1]);
+    double rhoDt;
+    if (isFloat) { rhoDt = Krho / double(fabsf(float(maxDivv))); }
+    else { rhoDt = Krho / fabs(maxDivv); }
+    out[0] = courant;
+    out[1] = rhoDt;
+    out[2] = fmin(fmin(courant, rhoDt), maxDtIncrease * minDt);
+}
+
+// ---------------------------------------------------------------- integrate (positions.hpp:54-138, update_h.hpp:12-24)
+template<class T>
+__device__ __forceinline__ T updateHT(unsigned ng0, unsigned nc, T h)
+{
+    const T c0  = T(1023.0);
+    const T exp = T(1.0 / 10.0);
+    return h * T(0.5) * pow(T(1) + c0 * T(ng0) / T(nc), exp);
+}
+
+__device__ __forceinline__ double putInBox1(double X, bool pbc, double lo, double hi, double l)
+{
+    if (pbc && X > hi) { X -= l; }
+    else if (pbc && X < lo) { X += l; }
+    return X;
+}
+
+template<class T>
+__global__ void __launch_bounds__(256)
+    positionsKernel(uint32_t first, uint32_t last, double dt, double dt_m1, PbcBox box, F<T> f, T muiConst,
+                    double gamma, unsigned ng0, double* __restrict__ xw, double* __restrict__ yw,
+                    double* __restrict__ zw)
+{
+    uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= last) return;
+
+    T hi      = f.h[i];
+    bool skip = false;
+    bool anyFBC = box.fx || box.fy || box.fz;
+    if (anyFBC && f.vx[i] == T(0) && f.vy[i] == T(0) && f.vz[i] == T(0))
+    {
+        auto fbc = [hi](double coord, double top, double bottom, bool on)
+        { return on && (fabs(top - coord) < T(2) * hi || fabs(bottom - coord) < T(2) * hi); };
+        skip = fbc(xw[i], box.lim[1], box.lim[0], box.fx) || fbc(yw[i], box.lim[3], box.lim[2], box.fy) ||
+               fbc(zw[i], box.lim[5], box.lim[4], box.fz);
+    }
+    if (!skip)
+    {
+        double A[3]   = {double(f.ax[i]), double(f.ay[i]), double(f.az[i])};
+        double X[3]   = {xw[i], yw[i], zw[i]};
+        double dXn[3] = {double(f.x_m1[i]), double(f.y_m1[i]), double(f.z_m1[i])};
+        double Xn[3], Vn1[3], dXn1[3];
+        const double lo[3] = {box.lim[0], box.lim[2], box.lim[4]}, hiL[3] = {box.lim[1], box.lim[3], box.lim[5]};
+        const double len[3] = {box.lx, box.ly, box.lz};
+        const bool pb[3]    = {box.px, box.py, box.pz};
+#pragma unroll
+        for (int d = 0; d < 3; ++d)
+        {
+            // positionUpdate (positions.hpp:77-88)
+            double Vnmhalf = dXn[d] * (1.0 / dt_m1);
+            double Vn      = Vnmhalf + 0.5 * dt_m1 * A[d];
+            Vn1[d]         = Vn + A[d] * dt;
+            dXn1[d]        = (Vn + 0.5 * A[d] * fabs(dt)) * dt;
+            Xn[d]          = putInBox1(X[d] + dXn1[d], pb[d], lo[d], hiL[d], len[d]);
+        }
+        xw[i] = Xn[0]; yw[i] = Xn[1]; zw[i] = Xn[2];
+        f.x_m1[i] = T(dXn1[0]); f.y_m1[i] = T(dXn1[1]); f.z_m1[i] = T(dXn1[2]);
+        f.vx[i] = T(Vn1[0]); f.vy[i] = T(Vn1[1]); f.vz[i] = T(Vn1[2]);
+    }
+
+    // updateTempHost with the intended value semantics (positions.hpp:124-138)
+    const T R    = 8.317e7;
+    T cv         = T(R / muiConst / (gamma - T(1)));
+    double u_old = cv * f.temp[i];
+    double du    = f.du[i];
+    double dum1  = double(f.du_m1[i]);
+    double u_new = u_old + du * dt + 0.5 * (du - dum1) / dt_m1 * fabs(dt) * dt;
+    if (u_new < 0.) { u_new = u_old * exp(u_new * dt / u_old); }
+    f.temp[i]  = u_new / cv;
+    f.du_m1[i] = T(du);
+
+    // updateSmoothingLength (update_h.hpp:12-24)
+    f.h[i] = updateHT(ng0, f.nc[i], hi);
+}
+
+} // namespace sphb200
+
+using namespace sphb200;
+
+#define SPHB200_TRY try {
+#define SPHB200_CATCH                                                                                                 \
+    return 0;                                                                                                         \
+    }                                                                                                                 \
+    catch (std::exception & e)                                                                                        \
+    {                                                                                                                 \
+        setError(e.what());                                                                                           \
+        return 1;                                                                                                     \
+    }
+
+#define DISPATCH(dtype, ...)                                                                                          \
+    if ((dtype) == SPHB200_F64) { using T = double; __VA_ARGS__ }                                                     \
+    else if ((dtype) == SPHB200_MIXED) { using T = float; __VA_ARGS__ }                                               \
+    else throw std::runtime_error("unknown dtype")
+
+static unsigned long long* dtKeys(sphb200_ctx* ctx) { return reinterpret_cast<unsigned long long*>(ctx->devDt + 4); }
+
+extern "C" int sphb200_xmass(sphb200_ctx* ctx, int dtype, uint32_t first, uint32_t last, const sphb200_box* box,
+                             const sphb200_hydro_const* hc, const uint32_t* neighbors, const sphb200_fields* f)
+{
+    SPHB200_TRY
+    if (last <= first) return 0;
+    DISPATCH(dtype, SPHB200_LAUNCH(ctx, xmassKernel<T>, gridFor(last - first, kHydroBlock), kHydroBlock, 0, first, last,
+                                   hc->ngmax, hc->K, pbcBox(*box), neighbors, typed<T>(*f),
+                                   static_cast<const T*>(hc->wh)););
+    SPHB200_CATCH
+}
+
+extern "C" int sphb200_ve_def_gradh(sphb200_ctx* ctx, int dtype, uint32_t first, uint32_t last, const sphb200_box* box,
+                                    const sphb200_hydro_const* hc, const uint32_t* neighbors, const sphb200_fields* f)
+{
+    SPHB200_TRY
+    if (last <= first) return 0;
+    DISPATCH(dtype, SPHB200_LAUNCH(ctx, veDefGradhKernel<T>, gridFor(last - first, kHydroBlock), kHydroBlock, 0, first,
+                                   last, hc->ngmax, hc->K, pbcBox(*box), neighbors, typed<T>(*f),
+                                   static_cast<const T*>(hc->wh), static_cast<const T*>(hc->whd)););
+    SPHB200_CATCH
+}
+
+extern "C" int sphb200_eos(sphb200_ctx* ctx, int dtype, uint32_t first, uint32_t last, const sphb200_hydro_const* hc,
+                           const sphb200_fields* f)
+{
+    SPHB200_TRY
+    if (last <= first) return 0;
+    DISPATCH(dtype, SPHB200_LAUNCH(ctx, eosKernel<T>, gridFor(last - first, 256), 256, 0, first, last, typed<T>(*f),
+                                   T(hc->muiConst), hc->gamma););
+    SPHB200_CATCH
+}
+
+extern "C" int sphb200_iad_divv_curlv(sphb200_ctx* ctx, int dtype, uint32_t first, uint32_t last,
+                                      const sphb200_box* box, const sphb200_hydro_const* hc, const uint32_t* neighbors,
+                                      const sphb200_fields* f)
+{
+    SPHB200_TRY
+    if (last <= first) return 0;
+    bool doGradV = f->dV11 != nullptr;
+    DISPATCH(dtype, SPHB200_LAUNCH(ctx, iadDivvCurlvKernel<T>, gridFor(last - first, kHydroBlock), kHydroBlock, 0,
+                                   first, last, hc->ngmax, hc->K, pbcBox(*box), neighbors, typed<T>(*f),
+                                   static_cast<const T*>(hc->wh), doGradV););
+    SPHB200_CATCH
+}
+
+extern "C" int sphb200_av_switches(sphb200_ctx* ctx, int dtype, uint32_t first, uint32_t last, const sphb200_box* box,
+                                   const sphb200_hydro_const* hc, const uint32_t* neighbors, const sphb200_fields* f)
+{
+    SPHB200_TRY
+    if (last <= first) return 0;
+    DISPATCH(dtype, SPHB200_LAUNCH(ctx, avSwitchesKernel<T>, gridFor(last - first, kHydroBlock), kHydroBlock, 0, first,
+                                   last, hc->ngmax, hc->K, pbcBox(*box), neighbors, typed<T>(*f),
+                                   static_cast<const T*>(hc->wh), hc->minDt, T(hc->alphamin), T(hc->alphamax),
+                                   T(hc->decay_constant)););
+    SPHB200_CATCH
+}
+
+extern "C" int sphb200_momentum_energy(sphb200_ctx* ctx, int dtype, uint32_t first, uint32_t last,
+                                       const sphb200_box* box, const sphb200_hydro_const* hc,
+                                       const uint32_t* neighbors, const sphb200_fields* f, double* minDtCourant_h)
+{
+    SPHB200_TRY
+    SPHB200_LAUNCH(ctx, initCourantKeyKernel, 1, 1, 0, dtKeys(ctx));
+    if (last > first)
+    {
+        int grid = gridFor(last - first, kHydroBlock);
+        if (hc->avClean && !f->dV11) throw std::runtime_error("momentum_energy: avClean requires dV11..dV33");
+        DISPATCH(dtype,
+                 if (hc->avClean) SPHB200_LAUNCH(ctx, (momentumEnergyKernel<true, T>), grid, kHydroBlock, 0, first, last,
+                                                 hc->ngmax, hc->K, pbcBox(*box), neighbors, typed<T>(*f),
+                                                 static_cast<const T*>(hc->wh), T(hc->Atmin), T(hc->Atmax), T(hc->ramp),
+                                                 float(hc->Kcour), dtKeys(ctx));
+                 else SPHB200_LAUNCH(ctx, (momentumEnergyKernel<false, T>), grid, kHydroBlock, 0, first, last, hc->ngmax,
+                                     hc->K, pbcBox(*box), neighbors, typed<T>(*f), static_cast<const T*>(hc->wh),
+                                     T(hc->Atmin), T(hc->Atmax), T(hc->ramp), float(hc->Kcour), dtKeys(ctx)););
+    }
+    if (minDtCourant_h)
+    {
+        unsigned long long key;
+        SPHB200_CUDA(cudaMemcpyAsync(&key, dtKeys(ctx), sizeof(key), cudaMemcpyDeviceToHost, ctx->stream));
+        SPHB200_CUDA(cudaStreamSynchronize(ctx->stream));
+        *minDtCourant_h = fromOrderedKey(key);
+    }
+    SPHB200_CATCH
+}
+
+extern "C" int sphb200_timestep(sphb200_ctx* ctx, int dtype, uint32_t first, uint32_t last,
+                                const sphb200_hydro_const* hc, const sphb200_fields* f, double* out_h)
+{
+    SPHB200_TRY
+    SPHB200_LAUNCH(ctx, initDivvKeyKernel, 1, 1, 0, dtKeys(ctx));
+    if (last > first)
+    {
+        int grid = persistentGrid(last - first, 256, 8);
+        DISPATCH(dtype, SPHB200_LAUNCH(ctx, maxDivvKernel<T>, grid, 256, 0, static_cast<const T*>(f->divv), first, last,
+                                       dtKeys(ctx) + 1););
+    }
+    SPHB200_LAUNCH(ctx, finalizeDtKernel, 1, 1, 0, dtKeys(ctx), hc->Krho, 1.1, hc->minDt, ctx->devDt,
+                   int(dtype == SPHB200_MIXED));
+    if (out_h)
+    {
+        SPHB200_CUDA(cudaMemcpyAsync(ctx->hostDt, ctx->devDt, 3 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+        SPHB200_CUDA(cudaStreamSynchronize(ctx->stream));
+        out_h[0] = ctx->hostDt[0];
+        out_h[1] = ctx->hostDt[1];
+        out_h[2] = ctx->hostDt[2];
+    }
+    SPHB200_CATCH
+}
+
+extern "C" double* sphb200_timestep_device_ptr(sphb200_ctx* ctx) { return ctx->devDt; }
+
+extern "C" int sphb200_positions_update_h(sphb200_ctx* ctx, int dtype, uint32_t first, uint32_t last,
+                                          const sphb200_box* box, const sphb200_hydro_const* hc, double dt,
+                                          double dt_m1, const sphb200_fields* f)
+{
+    SPHB200_TRY
+    if (last <= first) return 0;
+    DISPATCH(dtype, SPHB200_LAUNCH(ctx, positionsKernel<T>, gridFor(last - first, 256), 256, 0, first, last, dt, dt_m1,
+                                   pbcBox(*box), typed<T>(*f), T(hc->muiConst), hc->gamma, hc->ng0, f->x, f->y, f->z););
+    SPHB200_CATCH
+}

@@ -1,0 +1,303 @@
+// Neighbor search: ONE traversal per step that writes compact, ascending-j neighbor lists.
+//
+// The reference GPU path re-runs its warp traversal inside every pair kernel (5x per step) with a
+// ring-buffer queue in global memory (domain/include/cstone/traversal/find_neighbors.cuh:201-341).
+// Here one warp owns one slab of 32 SFC-consecutive targets, walks the linked octree depth-first in
+// ascending SFC order with its stack in shared memory, stages each overlapping leaf's particles in
+// shared memory with coalesced loads and tests them against all 32 targets via broadcast reads.
+// Membership arithmetic follows cstone::findNeighbors / distanceSq (findneighbors.hpp:51-165) in the
+// same operation order; this file is compiled with --fmad=false so that d^2 < 4h^2 is bit-exact
+// against the reference CPU build.
+#include "common.cuh"
+
+namespace sphb200
+{
+
+constexpr int kNbWarps     = 4;   // warps per CTA
+constexpr int kStackSize   = 160; // 7 * 21 levels + 8, singleTraversal uses 128 (traversal.hpp:80)
+constexpr int kMaxHIter    = 10;  // sph/find_neighbors.hpp:20
+
+struct DevTree
+{
+    const TreeNodeIndex* childOffsets;
+    const TreeNodeIndex* internalToLeaf;
+    const LocalIndex* layout;
+    const double* centers;
+    const double* sizes;
+};
+
+//! @brief sph::updateH (sph/include/sph/kernels.hpp:26-32)
+template<class T>
+__device__ __forceinline__ T updateH(unsigned ng0, unsigned nc, T h)
+{
+    const T c0  = T(1023.0);
+    const T exp = T(1.0 / 10.0);
+    return h * T(0.5) * pow(T(1) + c0 * T(ng0) / T(nc), exp);
+}
+
+template<bool UsePbc>
+__device__ __forceinline__ double distSq(double xj, double yj, double zj, double xi, double yi, double zi,
+                                         const sphb200_box& box)
+{
+    double dx = xj - xi;
+    double dy = yj - yi;
+    double dz = zj - zi;
+    if (UsePbc)
+    {
+        // fold into [-l/2, l/2]; factor pbc*l is l or 0 exactly (findneighbors.hpp:58-64)
+        if (box.bc[0] == SPHB200_PERIODIC) dx -= box.len[0] * rint(dx * box.inv[0]);
+        if (box.bc[1] == SPHB200_PERIODIC) dy -= box.len[1] * rint(dy * box.inv[1]);
+        if (box.bc[2] == SPHB200_PERIODIC) dz -= box.len[2] * rint(dz * box.inv[2]);
+    }
+    return dx * dx + dy * dy + dz * dz;
+}
+
+template<bool UsePbc>
+__device__ __forceinline__ void testLeaf(const double* __restrict__ x, const double* __restrict__ y,
+                                         const double* __restrict__ z, LocalIndex jb, LocalIndex je, double* cand,
+                                         int lane, bool active, LocalIndex i, double xi, double yi, double zi,
+                                         double radiusSq, const sphb200_box& box, unsigned ngmax, uint32_t* myList,
+                                         unsigned& count)
+{
+    for (LocalIndex base = jb; base < je; base += 32)
+    {
+        LocalIndex j = base + lane;
+        if (j < je)
+        {
+            cand[lane]      = x[j];
+            cand[32 + lane] = y[j];
+            cand[64 + lane] = z[j];
+        }
+        __syncwarp();
+        int cnt = min(32u, je - base);
+        if (active)
+        {
+#pragma unroll 4
+            for (int k = 0; k < cnt; ++k)
+            {
+                double d2     = distSq<UsePbc>(cand[k], cand[32 + k], cand[64 + k], xi, yi, zi, box);
+                LocalIndex jj = base + k;
+                if (d2 < radiusSq && jj != i)
+                {
+                    if (count < ngmax) myList[size_t(count) * 32] = jj;
+                    count++;
+                }
+            }
+        }
+        __syncwarp();
+    }
+}
+
+template<class Th>
+__global__ void __launch_bounds__(kNbWarps * 32)
+    findNeighborsKernel(DevTree tree, const double* __restrict__ x, const double* __restrict__ y,
+                        const double* __restrict__ z, Th* __restrict__ h, LocalIndex first, LocalIndex last,
+                        sphb200_box box, unsigned ng0, unsigned ngmax, int iterateH, uint32_t* __restrict__ nidx,
+                        uint32_t* __restrict__ nc, unsigned* __restrict__ numFails)
+{
+    __shared__ TreeNodeIndex stackMem[kNbWarps][kStackSize];
+    __shared__ double candMem[kNbWarps][96];
+
+    const int lane  = threadIdx.x & 31;
+    const int warp  = threadIdx.x >> 5;
+    const size_t group = size_t(blockIdx.x) * kNbWarps + warp;
+    const size_t gBase = size_t(first) + group * 32;
+    if (gBase >= last) return; // whole warp exits together
+
+    TreeNodeIndex* stack = stackMem[warp];
+    double* cand         = candMem[warp];
+
+    const bool valid   = gBase + lane < last;
+    const LocalIndex i = valid ? LocalIndex(gBase + lane) : last - 1;
+    const double xi = x[i], yi = y[i], zi = z[i];
+    Th hi           = h[i];
+    uint32_t* myList = nidx + (group * ngmax) * 32 + lane;
+
+    const bool anyPbc =
+        box.bc[0] == SPHB200_PERIODIC || box.bc[1] == SPHB200_PERIODIC || box.bc[2] == SPHB200_PERIODIC;
+    const unsigned ngmin = ng0 / 4;
+
+    bool active   = valid;
+    int iteration = 0;
+    unsigned count = 0;
+
+    while (__any_sync(0xffffffffu, active))
+    {
+        // membership radius in the type of h (findneighbors.hpp:111)
+        Th radiusSqT    = Th(4.0) * hi * hi;
+        double radiusSq = double(radiusSqT);
+        double r        = 2.0 * double(hi);
+
+        // bounding box of the active targets' search spheres
+        double lo[3] = {xi - r, yi - r, zi - r};
+        double hi3[3] = {xi + r, yi + r, zi + r};
+        if (!active)
+        {
+#pragma unroll
+            for (int d = 0; d < 3; ++d)
+            {
+                lo[d]  = INFINITY;
+                hi3[d] = -INFINITY;
+            }
+        }
+#pragma unroll
+        for (int d = 0; d < 3; ++d)
+        {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1)
+            {
+                lo[d]  = fmin(lo[d], __shfl_xor_sync(0xffffffffu, lo[d], o));
+                hi3[d] = fmax(hi3[d], __shfl_xor_sync(0xffffffffu, hi3[d], o));
+            }
+        }
+        double tc[3], ts[3];
+        bool inside = true;
+#pragma unroll
+        for (int d = 0; d < 3; ++d)
+        {
+            tc[d] = 0.5 * (hi3[d] + lo[d]);
+            // conservative: pruning only, membership is decided by the exact distance test
+            ts[d]  = 0.5 * (hi3[d] - lo[d]) * (1.0 + 1e-9) + 1e-13 * box.len[d];
+            inside = inside && (lo[d] >= box.lim[2 * d]) && (hi3[d] <= box.lim[2 * d + 1]);
+        }
+        // same switch as findneighbors.hpp:116-118 / find_neighbors.cuh:470-472: no fold needed if all search
+        // spheres lie inside the box (then rint(dx/l) == 0 for every possible neighbor)
+        const bool usePbc = anyPbc && !inside;
+
+        if (active) count = 0;
+        int sp = 0;
+        if (lane == 0) stack[0] = 0;
+        sp = 1;
+        __syncwarp();
+        while (sp > 0)
+        {
+            TreeNodeIndex node   = stack[--sp];
+            TreeNodeIndex child0 = tree.childOffsets[node];
+            __syncwarp();
+            if (child0 == 0)
+            {
+                TreeNodeIndex leafIdx = tree.internalToLeaf[node];
+                LocalIndex jb = tree.layout[leafIdx], je = tree.layout[leafIdx + 1];
+                if (usePbc) testLeaf<true>(x, y, z, jb, je, cand, lane, active, i, xi, yi, zi, radiusSq, box, ngmax, myList, count);
+                else testLeaf<false>(x, y, z, jb, je, cand, lane, active, i, xi, yi, zi, radiusSq, box, ngmax, myList, count);
+            }
+            else
+            {
+                bool ok = false;
+                if (lane < 8)
+                {
+                    TreeNodeIndex c = child0 + lane;
+                    ok              = true;
+#pragma unroll
+                    for (int d = 0; d < 3; ++d)
+                    {
+                        double dx = tree.centers[3 * size_t(c) + d] - tc[d];
+                        if (box.bc[d] == SPHB200_PERIODIC) dx -= box.len[d] * rint(dx * box.inv[d]);
+                        ok = ok && (fabs(dx) - tree.sizes[3 * size_t(c) + d] - ts[d] <= 0.0);
+                    }
+                }
+                unsigned m = __ballot_sync(0xffffffffu, ok);
+                // push in descending octant order so that children pop in ascending SFC order
+                if (ok)
+                {
+                    int above     = __popc(m >> (lane + 1)); // overlapping children with higher octant
+                    stack[sp + above] = child0 + lane;
+                }
+                sp += __popc(m);
+                __syncwarp();
+            }
+        }
+
+        // coupled h / neighbor-count iteration, per target (sph/find_neighbors.hpp:24-35)
+        if (active)
+        {
+            unsigned ncSph = count + 1;
+            bool need      = iterateH && (ngmin > ncSph || (ncSph - 1) > ngmax);
+            if (need && iteration++ < kMaxHIter) { hi = updateH(ng0, ncSph, hi); }
+            else { active = false; }
+        }
+    }
+
+    if (valid)
+    {
+        nc[i - first] = count + 1;
+        if (iterateH)
+        {
+            if (iteration > 0) h[i] = hi;
+            if (iteration >= kMaxHIter) atomicAdd(numFails, 1u);
+        }
+    }
+}
+
+//! @brief slab layout -> row-major [target][ngmax]
+__global__ void slabToRowMajorKernel(const uint32_t* __restrict__ slab, const uint32_t* __restrict__ nc,
+                                     uint32_t numTargets, unsigned ngmax, uint32_t* __restrict__ out)
+{
+    size_t t = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (t >= numTargets) return;
+    size_t g = t / 32, lane = t % 32;
+    unsigned cnt = min(nc[t] - 1, ngmax);
+    for (unsigned k = 0; k < cnt; ++k)
+        out[t * ngmax + k] = slab[(g * ngmax + k) * 32 + lane];
+}
+
+} // namespace sphb200
+
+using namespace sphb200;
+
+extern "C" size_t sphb200_neighbors_size(size_t numTargets, unsigned ngmax)
+{
+    return ((numTargets + 31) / 32) * size_t(ngmax) * 32;
+}
+
+extern "C" int sphb200_find_neighbors(sphb200_ctx* ctx, const sphb200_tree_view* t, const double* x, const double* y,
+                                      const double* z, void* h, int dtype, uint32_t first, uint32_t last,
+                                      const sphb200_box* box, unsigned ng0, unsigned ngmax, int iterateH,
+                                      uint32_t* neighbors, uint32_t* nc, unsigned* numFails_h)
+{
+    try
+    {
+        if (numFails_h) *numFails_h = 0;
+        if (last <= first) return 0;
+        DevTree tree{t->childOffsets, t->internalToLeaf, t->layout, t->centers, t->sizes};
+        unsigned* dFails = reinterpret_cast<unsigned*>(ctx->devScalars + 4);
+        SPHB200_CUDA(cudaMemsetAsync(dFails, 0, sizeof(unsigned), ctx->stream));
+        size_t numGroups = (size_t(last - first) + 31) / 32;
+        int grid         = int((numGroups + kNbWarps - 1) / kNbWarps);
+        if (dtype == SPHB200_F64)
+            SPHB200_LAUNCH(ctx, findNeighborsKernel<double>, grid, kNbWarps * 32, 0, tree, x, y, z,
+                           static_cast<double*>(h), first, last, *box, ng0, ngmax, iterateH, neighbors, nc, dFails);
+        else
+            SPHB200_LAUNCH(ctx, findNeighborsKernel<float>, grid, kNbWarps * 32, 0, tree, x, y, z,
+                           static_cast<float*>(h), first, last, *box, ng0, ngmax, iterateH, neighbors, nc, dFails);
+        if (numFails_h)
+        {
+            SPHB200_CUDA(cudaMemcpyAsync(ctx->hostScalars + 4, dFails, sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->stream));
+            SPHB200_CUDA(cudaStreamSynchronize(ctx->stream));
+            *numFails_h = unsigned(ctx->hostScalars[4]);
+        }
+        return 0;
+    }
+    catch (std::exception& e)
+    {
+        setError(e.what());
+        return 1;
+    }
+}
+
+extern "C" int sphb200_neighbors_to_rowmajor(sphb200_ctx* ctx, const uint32_t* slab, const uint32_t* nc,
+                                             uint32_t numTargets, unsigned ngmax, uint32_t* rowmajor)
+{
+    try
+    {
+        if (numTargets)
+            SPHB200_LAUNCH(ctx, slabToRowMajorKernel, gridFor(numTargets, 128), 128, 0, slab, nc, numTargets, ngmax,
+                           rowmajor);
+        return 0;
+    }
+    catch (std::exception& e)
+    {
+        setError(e.what());
+        return 1;
+    }
+}

@@ -1,0 +1,439 @@
+// Primitives: stable LSD radix sort (key u64, payload u32), exclusive scan, multi-field gather,
+// range pack/unpack.  Hand-written for sm_100a; replaces the reference's cub/thrust calls
+// (domain/include/cstone/primitives/primitives_gpu.cu:85-101,228-334).
+#include "common.cuh"
+#include "primitives.cuh"
+
+namespace sphb200
+{
+
+// ---------------------------------------------------------------- exclusive scan (uint32)
+constexpr int kScanThreads = 512;
+constexpr int kScanItems   = 8;
+constexpr int kScanTile    = kScanThreads * kScanItems;
+
+__device__ __forceinline__ uint32_t warpInclusiveScan(uint32_t v, int lane)
+{
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1)
+    {
+        uint32_t t = __shfl_up_sync(0xffffffffu, v, o);
+        if (lane >= o) v += t;
+    }
+    return v;
+}
+
+//! @brief block-wide exclusive scan of one value per thread; returns exclusive prefix, total in *blockTotal
+__device__ __forceinline__ uint32_t blockExclusiveScan(uint32_t v, uint32_t* smem /*>= 33*/, uint32_t* blockTotal)
+{
+    int lane     = threadIdx.x & 31;
+    int warp     = threadIdx.x >> 5;
+    int numWarps = blockDim.x >> 5;
+    uint32_t inc = warpInclusiveScan(v, lane);
+    if (lane == 31) smem[warp] = inc;
+    __syncthreads();
+    if (warp == 0)
+    {
+        uint32_t w  = (lane < numWarps) ? smem[lane] : 0;
+        uint32_t wi = warpInclusiveScan(w, lane);
+        smem[lane]  = wi - w;
+        if (lane == 31) smem[32] = wi;
+    }
+    __syncthreads();
+    uint32_t res = smem[warp] + inc - v;
+    *blockTotal  = smem[32];
+    __syncthreads();
+    return res;
+}
+
+__global__ void __launch_bounds__(kScanThreads) scanTileSumsKernel(const uint32_t* __restrict__ in, size_t n,
+                                                                   uint32_t* __restrict__ tileSums)
+{
+    __shared__ uint32_t smem[33];
+    size_t base  = size_t(blockIdx.x) * kScanTile + size_t(threadIdx.x) * kScanItems;
+    uint32_t sum = 0;
+#pragma unroll
+    for (int k = 0; k < kScanItems; ++k)
+        if (base + k < n) sum += in[base + k];
+    uint32_t total;
+    blockExclusiveScan(sum, smem, &total);
+    if (threadIdx.x == 0) tileSums[blockIdx.x] = total;
+}
+
+//! @brief scans each tile; adds tileOffsets[tile] if given; in == out allowed
+__global__ void __launch_bounds__(kScanThreads) scanTilesKernel(const uint32_t* __restrict__ in, size_t n,
+                                                                const uint32_t* __restrict__ tileOffsets,
+                                                                uint32_t* __restrict__ out, uint32_t* totalOut)
+{
+    __shared__ uint32_t smem[33];
+    size_t base = size_t(blockIdx.x) * kScanTile + size_t(threadIdx.x) * kScanItems;
+    uint32_t v[kScanItems];
+    uint32_t sum = 0;
+#pragma unroll
+    for (int k = 0; k < kScanItems; ++k)
+    {
+        v[k] = (base + k < n) ? in[base + k] : 0;
+        sum += v[k];
+    }
+    uint32_t total;
+    uint32_t excl = blockExclusiveScan(sum, smem, &total);
+    uint32_t off  = excl + (tileOffsets ? tileOffsets[blockIdx.x] : 0);
+#pragma unroll
+    for (int k = 0; k < kScanItems; ++k)
+    {
+        if (base + k < n) out[base + k] = off;
+        off += v[k];
+    }
+    if (totalOut && blockIdx.x == gridDim.x - 1 && threadIdx.x == blockDim.x - 1) *totalOut = off;
+}
+
+void exclusiveScan(sphb200_ctx* ctx, const uint32_t* in, uint32_t* out, size_t n, uint32_t* totalOut)
+{
+    if (n == 0)
+    {
+        if (totalOut) SPHB200_CUDA(cudaMemsetAsync(totalOut, 0, sizeof(uint32_t), ctx->stream));
+        return;
+    }
+    size_t numTiles = (n + kScanTile - 1) / kScanTile;
+    if (numTiles == 1)
+    {
+        SPHB200_LAUNCH(ctx, scanTilesKernel, 1, kScanThreads, 0, in, n, (const uint32_t*)nullptr, out, totalOut);
+        return;
+    }
+    // tile sums live in scanTmp: level 0 needs numTiles entries, deeper levels stacked behind
+    size_t need = 0;
+    for (size_t t = numTiles; t > 1; t = (t + kScanTile - 1) / kScanTile)
+        need += t + 1;
+    need += 2;
+    uint32_t* tmp = static_cast<uint32_t*>(ctx->scanTmp.get(need * sizeof(uint32_t)));
+
+    // recursive lambda via explicit level loop
+    std::vector<std::pair<uint32_t*, size_t>> levels; // (sums array, count)
+    uint32_t* cursor = tmp;
+    size_t cnt       = numTiles;
+    const uint32_t* src = in;
+    size_t srcN         = n;
+    while (true)
+    {
+        SPHB200_LAUNCH(ctx, scanTileSumsKernel, int(cnt), kScanThreads, 0, src, srcN, cursor);
+        levels.push_back({cursor, cnt});
+        if (cnt <= size_t(kScanTile)) break;
+        src  = cursor;
+        srcN = cnt;
+        cursor += cnt + 1;
+        cnt = (cnt + kScanTile - 1) / kScanTile;
+    }
+    // scan top level in place (single tile)
+    {
+        auto [arr, c] = levels.back();
+        SPHB200_LAUNCH(ctx, scanTilesKernel, 1, kScanThreads, 0, arr, c, (const uint32_t*)nullptr, arr,
+                       (uint32_t*)nullptr);
+    }
+    for (int l = int(levels.size()) - 2; l >= 0; --l)
+    {
+        auto [arr, c]   = levels[l];
+        auto [offs, oc] = levels[l + 1];
+        SPHB200_LAUNCH(ctx, scanTilesKernel, int(oc), kScanThreads, 0, arr, c, offs, arr, (uint32_t*)nullptr);
+    }
+    SPHB200_LAUNCH(ctx, scanTilesKernel, int(numTiles), kScanThreads, 0, in, n, levels[0].first, out, totalOut);
+}
+
+// ---------------------------------------------------------------- radix sort
+constexpr int kSortThreads = 256;
+constexpr int kSortWarps   = kSortThreads / 32;
+constexpr int kSortItems   = 16;                        // keys per thread
+constexpr int kSortTile    = kSortThreads * kSortItems; // 4096 keys per CTA
+constexpr int kRadixBits   = 8;
+constexpr int kRadix       = 1 << kRadixBits;
+
+//! @brief per-tile digit histogram, written digit-major: hist[digit * numTiles + tile]
+__global__ void __launch_bounds__(kSortThreads) radixCountKernel(const KeyType* __restrict__ keys, size_t n, int shift,
+                                                                 uint32_t* __restrict__ hist, int numTiles)
+{
+    __shared__ uint32_t sh[kRadix];
+    sh[threadIdx.x] = 0; // kSortThreads == kRadix
+    __syncthreads();
+    size_t base = size_t(blockIdx.x) * kSortTile;
+#pragma unroll 4
+    for (int k = 0; k < kSortItems; ++k)
+    {
+        size_t i = base + size_t(k) * kSortThreads + threadIdx.x;
+        if (i < n) atomicAdd(&sh[(keys[i] >> shift) & (kRadix - 1)], 1u);
+    }
+    __syncthreads();
+    hist[size_t(threadIdx.x) * numTiles + blockIdx.x] = sh[threadIdx.x];
+}
+
+/*! @brief stable scatter of one tile
+ *
+ * Order inside a tile is (warp, chunk, lane); each warp ranks its 32-key chunks with
+ * __match_any_sync (peers with the same digit), keeping a private digit counter row in
+ * shared memory, so no atomics are needed and the ranking is deterministic and stable.
+ */
+__global__ void __launch_bounds__(kSortThreads)
+    radixScatterKernel(const KeyType* __restrict__ keysIn, const uint32_t* __restrict__ valsIn,
+                       KeyType* __restrict__ keysOut, uint32_t* __restrict__ valsOut, size_t n, int shift,
+                       const uint32_t* __restrict__ scannedHist, int numTiles)
+{
+    __shared__ uint32_t warpHist[kSortWarps][kRadix];
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    for (int k = threadIdx.x; k < kSortWarps * kRadix; k += kSortThreads)
+        (&warpHist[0][0])[k] = 0;
+    __syncthreads();
+
+    const size_t warpBase = size_t(blockIdx.x) * kSortTile + size_t(warp) * (32 * kSortItems);
+    KeyType key[kSortItems];
+    uint32_t rank[kSortItems];
+    const unsigned ltMask = (1u << lane) - 1;
+
+#pragma unroll
+    for (int c = 0; c < kSortItems; ++c)
+    {
+        size_t i      = warpBase + size_t(c) * 32 + lane;
+        bool valid    = i < n;
+        key[c]        = valid ? keysIn[i] : ~KeyType(0);
+        unsigned d    = (key[c] >> shift) & (kRadix - 1);
+        unsigned act  = __ballot_sync(0xffffffffu, valid);
+        unsigned peer = __match_any_sync(0xffffffffu, valid ? d : (kRadix + lane)) & act;
+        if (valid)
+        {
+            int leader    = __ffs(peer) - 1;
+            uint32_t base = 0;
+            if (lane == leader)
+            {
+                base           = warpHist[warp][d];
+                warpHist[warp][d] = base + __popc(peer);
+            }
+            base    = __shfl_sync(peer, base, leader);
+            rank[c] = base + __popc(peer & ltMask);
+        }
+        __syncwarp();
+    }
+    __syncthreads();
+    {
+        // digit = threadIdx.x: exclusive scan over the warps of this tile on top of the global offset
+        int d            = threadIdx.x;
+        uint32_t running = scannedHist[size_t(d) * numTiles + blockIdx.x];
+#pragma unroll
+        for (int w = 0; w < kSortWarps; ++w)
+        {
+            uint32_t t     = warpHist[w][d];
+            warpHist[w][d] = running;
+            running += t;
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int c = 0; c < kSortItems; ++c)
+    {
+        size_t i = warpBase + size_t(c) * 32 + lane;
+        if (i < n)
+        {
+            unsigned d    = (key[c] >> shift) & (kRadix - 1);
+            uint32_t pos  = warpHist[warp][d] + rank[c];
+            keysOut[pos]  = key[c];
+            valsOut[pos]  = valsIn ? valsIn[i] : uint32_t(i);
+        }
+    }
+}
+
+void radixSortPairs(sphb200_ctx* ctx, KeyType* keys, uint32_t* vals, size_t n, bool valsAreIota, int beginBit,
+                    int endBit)
+{
+    if (n == 0) return;
+    int numTiles    = int((n + kSortTile - 1) / kSortTile);
+    size_t histSize = size_t(kRadix) * numTiles;
+    // temp: alt keys, alt vals, hist
+    size_t bytes = n * sizeof(KeyType) + n * sizeof(uint32_t) + histSize * sizeof(uint32_t) + 512;
+    char* tmp    = static_cast<char*>(ctx->sortTmp.get(bytes));
+    KeyType* keysAlt  = reinterpret_cast<KeyType*>(tmp);
+    uint32_t* valsAlt = reinterpret_cast<uint32_t*>(tmp + n * sizeof(KeyType));
+    uint32_t* hist    = reinterpret_cast<uint32_t*>(tmp + n * sizeof(KeyType) + ((n * sizeof(uint32_t) + 255) & ~size_t(255)));
+
+    int numPasses = (endBit - beginBit + kRadixBits - 1) / kRadixBits;
+    KeyType* kIn  = keys;
+    KeyType* kOut = keysAlt;
+    uint32_t* vIn = vals;
+    uint32_t* vOut = valsAlt;
+    for (int p = 0; p < numPasses; ++p)
+    {
+        int shift = beginBit + p * kRadixBits;
+        SPHB200_LAUNCH(ctx, radixCountKernel, numTiles, kSortThreads, 0, kIn, n, shift, hist, numTiles);
+        exclusiveScan(ctx, hist, hist, histSize, nullptr);
+        const uint32_t* vSrc = (p == 0 && valsAreIota) ? nullptr : vIn;
+        SPHB200_LAUNCH(ctx, radixScatterKernel, numTiles, kSortThreads, 0, kIn, vSrc, kOut, vOut, n, shift, hist,
+                       numTiles);
+        std::swap(kIn, kOut);
+        std::swap(vIn, vOut);
+    }
+    if (kIn != keys)
+    {
+        SPHB200_CUDA(cudaMemcpyAsync(keys, kIn, n * sizeof(KeyType), cudaMemcpyDeviceToDevice, ctx->stream));
+        SPHB200_CUDA(cudaMemcpyAsync(vals, vIn, n * sizeof(uint32_t), cudaMemcpyDeviceToDevice, ctx->stream));
+    }
+}
+
+// ---------------------------------------------------------------- multi-field gather
+constexpr int kMaxGatherFields = 24;
+struct GatherArgs
+{
+    const void* src[kMaxGatherFields];
+    void* dst[kMaxGatherFields];
+    unsigned char is8[kMaxGatherFields];
+    int nfields;
+};
+
+/*! @brief dst_f[i] = src_f[perm[i]] for all fields in one launch
+ *
+ * perm is read once per particle (the reference launches one gather per field and re-reads it,
+ * primitives_gpu.cu:85-101); all random reads of a particle are issued back-to-back for MLP.
+ */
+__global__ void __launch_bounds__(256) gatherFieldsKernel(const uint32_t* __restrict__ perm, size_t n, GatherArgs a)
+{
+    size_t stride = size_t(gridDim.x) * blockDim.x;
+    for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride)
+    {
+        uint32_t s = perm[i];
+#pragma unroll 4
+        for (int f = 0; f < a.nfields; ++f)
+        {
+            if (a.is8[f]) { static_cast<uint64_t*>(a.dst[f])[i] = __ldg(static_cast<const uint64_t*>(a.src[f]) + s); }
+            else { static_cast<uint32_t*>(a.dst[f])[i] = __ldg(static_cast<const uint32_t*>(a.src[f]) + s); }
+        }
+    }
+}
+
+// ---------------------------------------------------------------- range pack / unpack (halo buffers)
+struct RangeArgs
+{
+    void* field[kMaxGatherFields];
+    unsigned char is8[kMaxGatherFields];
+    size_t packedOffset[kMaxGatherFields]; // byte offset of field f inside the packed buffer
+    int nfields;
+};
+
+/*! @brief element e of the concatenated ranges <-> array index rangeBegin[r] + (e - rangeScan[r])
+ *  (gatherRangesKernel / scatterRangesKernel, halos/gather_halos_gpu.cu:41-117; here all fields per launch) */
+template<bool Pack>
+__global__ void __launch_bounds__(256) rangesKernel(const uint32_t* __restrict__ rangeScan,
+                                                    const uint32_t* __restrict__ rangeBegin, int numRanges,
+                                                    uint32_t total, RangeArgs a, char* __restrict__ packed)
+{
+    uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= total) return;
+    // last range with rangeScan[r] <= e
+    int r        = int(upperBound(rangeScan, size_t(numRanges), e)) - 1;
+    uint32_t idx = rangeBegin[r] + (e - rangeScan[r]);
+    for (int f = 0; f < a.nfields; ++f)
+    {
+        if (a.is8[f])
+        {
+            auto* p = reinterpret_cast<uint64_t*>(packed + a.packedOffset[f]);
+            auto* q = static_cast<uint64_t*>(a.field[f]);
+            if (Pack) p[e] = q[idx];
+            else q[idx] = p[e];
+        }
+        else
+        {
+            auto* p = reinterpret_cast<uint32_t*>(packed + a.packedOffset[f]);
+            auto* q = static_cast<uint32_t*>(a.field[f]);
+            if (Pack) p[e] = q[idx];
+            else q[idx] = p[e];
+        }
+    }
+}
+
+} // namespace sphb200
+
+using namespace sphb200;
+
+extern "C" int sphb200_sort_by_key(sphb200_ctx* ctx, uint64_t* keys, uint32_t* perm, size_t n)
+{
+    try
+    {
+        radixSortPairs(ctx, keys, perm, n, true, 0, 64);
+        return 0;
+    }
+    catch (std::exception& e)
+    {
+        setError(e.what());
+        return 1;
+    }
+}
+
+extern "C" int sphb200_gather(sphb200_ctx* ctx, const uint32_t* perm, size_t n, int nfields, const void* const* src,
+                              void* const* dst, const int* elemBytes)
+{
+    try
+    {
+        if (n == 0 || nfields == 0) return 0;
+        for (int f0 = 0; f0 < nfields; f0 += kMaxGatherFields)
+        {
+            GatherArgs a;
+            a.nfields = std::min(kMaxGatherFields, nfields - f0);
+            for (int f = 0; f < a.nfields; ++f)
+            {
+                if (elemBytes[f0 + f] != 4 && elemBytes[f0 + f] != 8) throw std::runtime_error("gather: element size must be 4 or 8");
+                a.src[f] = src[f0 + f];
+                a.dst[f] = dst[f0 + f];
+                a.is8[f] = elemBytes[f0 + f] == 8;
+            }
+            SPHB200_LAUNCH(ctx, gatherFieldsKernel, persistentGrid(n, 256, 8), 256, 0, perm, n, a);
+        }
+        return 0;
+    }
+    catch (std::exception& e)
+    {
+        setError(e.what());
+        return 1;
+    }
+}
+
+static int rangesImpl(sphb200_ctx* ctx, bool pack, const uint32_t* rangeScan, const uint32_t* rangeBegin, int numRanges,
+                      uint32_t total, int nfields, void* const* fields, const int* elemBytes, void* packed)
+{
+    try
+    {
+        if (total == 0 || nfields == 0) return 0;
+        if (nfields > kMaxGatherFields) throw std::runtime_error("pack_ranges: too many fields");
+        RangeArgs a;
+        a.nfields  = nfields;
+        size_t off = 0;
+        for (int f = 0; f < nfields; ++f)
+        {
+            a.field[f]        = fields[f];
+            a.is8[f]          = elemBytes[f] == 8;
+            a.packedOffset[f] = off;
+            off += (size_t(total) * elemBytes[f] + 7) & ~size_t(7); // 8-byte aligned like exchange_halos_gpu.cuh:58
+        }
+        if (pack)
+            SPHB200_LAUNCH(ctx, rangesKernel<true>, gridFor(total, 256), 256, 0, rangeScan, rangeBegin, numRanges, total,
+                           a, static_cast<char*>(packed));
+        else
+            SPHB200_LAUNCH(ctx, rangesKernel<false>, gridFor(total, 256), 256, 0, rangeScan, rangeBegin, numRanges,
+                           total, a, static_cast<char*>(packed));
+        return 0;
+    }
+    catch (std::exception& e)
+    {
+        setError(e.what());
+        return 1;
+    }
+}
+
+extern "C" int sphb200_pack_ranges(sphb200_ctx* ctx, const uint32_t* rangeScan, const uint32_t* rangeBegin,
+                                   int numRanges, uint32_t total, int nfields, const void* const* src,
+                                   const int* elemBytes, void* packed)
+{
+    return rangesImpl(ctx, true, rangeScan, rangeBegin, numRanges, total, nfields, const_cast<void* const*>(src),
+                      elemBytes, packed);
+}
+
+extern "C" int sphb200_unpack_ranges(sphb200_ctx* ctx, const uint32_t* rangeScan, const uint32_t* rangeBegin,
+                                     int numRanges, uint32_t total, int nfields, void* const* dst, const int* elemBytes,
+                                     const void* packed)
+{
+    return rangesImpl(ctx, false, rangeScan, rangeBegin, numRanges, total, nfields, dst, elemBytes,
+                      const_cast<void*>(packed));
+}

@@ -1,0 +1,269 @@
+"""Host-side mirror of the reference's GPU operator interface for the hot path.
+
+Names and argument meaning follow the reference's `extern` GPU functions
+(cstone/*_gpu.h, sph/sph_gpu.hpp); every function forwards to the C ABI of
+libsphexa_b200.so with raw device pointers.  torch is only the device allocator.
+"""
+import ctypes as C
+import torch
+
+from . import binding as B
+from .binding import lib, check, ptr, vp
+
+
+def _i32(n):
+    return C.c_int(int(n))
+
+
+def real_dtype(dtype):
+    return torch.float64 if dtype == B.F64 else torch.float32
+
+
+# ---------------------------------------------------------------- cstone: sfc / primitives
+def computeSfcKeysGpu(ctx, x, y, z, box, keys=None):
+    """cstone::computeSfcKeysGpu (sfc/sfc_gpu.h:39)"""
+    n = x.numel()
+    if keys is None:
+        keys = torch.empty(n, dtype=torch.int64, device=x.device)
+    check(lib.sphb200_sfc_keys(ctx.h, ptr(x), ptr(y), ptr(z), C.c_size_t(n), C.byref(box), ptr(keys)))
+    return keys
+
+
+def minMaxGpu(ctx, x, y, z):
+    """MinMaxGpu per axis (primitives_gpu.h:52) -> [xmin,xmax,ymin,ymax,zmin,zmax]"""
+    out = (C.c_double * 6)()
+    check(lib.sphb200_minmax3(ctx.h, ptr(x), ptr(y), ptr(z), C.c_size_t(x.numel()), out))
+    return list(out)
+
+
+def sortByKeyGpu(ctx, keys):
+    """sequenceGpu + sortByKeyGpu (primitives_gpu.h:87-111): keys sorted in place, returns the ordering"""
+    n = keys.numel()
+    perm = torch.empty(n, dtype=torch.int32, device=keys.device)
+    check(lib.sphb200_sort_by_key(ctx.h, ptr(keys), ptr(perm), C.c_size_t(n)))
+    return perm
+
+
+def gatherGpu(ctx, perm, srcs):
+    """gatherGpu for a list of fields in one launch (primitives_gpu.h:62)"""
+    n = perm.numel()
+    dsts = [torch.empty_like(s) for s in srcs]
+    k = len(srcs)
+    sp = (vp * k)(*[s.data_ptr() for s in srcs])
+    dp = (vp * k)(*[d.data_ptr() for d in dsts])
+    eb = (C.c_int * k)(*[s.element_size() for s in srcs])
+    check(lib.sphb200_gather(ctx.h, ptr(perm), C.c_size_t(n), k, sp, dp, eb))
+    return dsts
+
+
+# ---------------------------------------------------------------- cstone: tree
+def computeNodeCountsGpu(ctx, leaves, keys):
+    """computeNodeCountsGpu (tree/csarray_gpu.h:56)"""
+    nl = leaves.numel() - 1
+    counts = torch.empty(nl, dtype=torch.int32, device=keys.device)
+    check(lib.sphb200_node_counts(ctx.h, ptr(leaves), nl, ptr(keys), C.c_size_t(keys.numel()), ptr(counts)))
+    return counts
+
+
+def rebalanceDecisionGpu(ctx, leaves, counts, bucket):
+    nl = counts.numel()
+    ops = torch.empty(nl, dtype=torch.int32, device=leaves.device)
+    conv = C.c_int(0)
+    check(lib.sphb200_rebalance_decision(ctx.h, ptr(leaves), ptr(counts), nl, C.c_uint(bucket), ptr(ops),
+                                         C.byref(conv)))
+    return ops, bool(conv.value)
+
+
+def computeOctreeGpu(ctx, keys, bucket, capacity=None):
+    """computeOctree (tree/csarray.hpp:454-468) on the device: returns (leaves, counts, iterations)"""
+    n = keys.numel()
+    cap = capacity or max(4096, 16 * (n // max(1, bucket)) + 4096)
+    leaves = torch.empty(cap + 2, dtype=torch.int64, device=keys.device)
+    counts = torch.empty(cap + 2, dtype=torch.int32, device=keys.device)
+    nl, it = C.c_int(0), C.c_int(0)
+    check(lib.sphb200_compute_octree(ctx.h, ptr(keys), C.c_size_t(n), C.c_uint(bucket), ptr(leaves), ptr(counts), cap,
+                                     C.byref(nl), C.byref(it)))
+    return leaves[:nl.value + 1].clone(), counts[:nl.value].clone(), it.value
+
+
+def updateOctreeGpu(ctx, keys, bucket, leaves, counts):
+    """updateOctreeGpu (tree/update_gpu.cuh:58-82): one rebalance + recount; returns (leaves, counts, converged)"""
+    nl0 = counts.numel()
+    cap = 8 * nl0 + 64
+    lv = torch.empty(cap + 2, dtype=torch.int64, device=keys.device)
+    ct = torch.empty(cap + 2, dtype=torch.int32, device=keys.device)
+    lv[:nl0 + 1] = leaves
+    ct[:nl0] = counts
+    nl, conv = C.c_int(nl0), C.c_int(0)
+    check(lib.sphb200_update_octree(ctx.h, ptr(keys), C.c_size_t(keys.numel()), C.c_uint(bucket), ptr(lv), ptr(ct),
+                                    cap, C.byref(nl), C.byref(conv)))
+    return lv[:nl.value + 1].clone(), ct[:nl.value].clone(), bool(conv.value)
+
+
+class Octree:
+    """device twin of cstone::OctreeData (tree/octree.hpp:318-386) + geometry + layout"""
+
+    def __init__(self, ctx, leaves, box=None, counts=None):
+        dev = leaves.device
+        self.leaves = leaves
+        self.numLeaves = nl = leaves.numel() - 1
+        self.numInternal = ni = (nl - 1) // 7
+        self.numNodes = nn = nl + ni
+        i32 = dict(dtype=torch.int32, device=dev)
+        self.prefixes = torch.zeros(nn, dtype=torch.int64, device=dev)
+        self.childOffsets = torch.zeros(nn + 1, **i32)
+        self.parents = torch.zeros(max(1, (nn - 1) // 8), **i32)
+        self.levelRange = torch.zeros(23, **i32)
+        self.internalToLeaf = torch.zeros(nn, **i32)
+        self.leafToInternal = torch.zeros(nn, **i32)
+        check(lib.sphb200_build_octree(ctx.h, ptr(leaves), nl, ptr(self.prefixes), ptr(self.childOffsets),
+                                       ptr(self.parents), ptr(self.levelRange), ptr(self.internalToLeaf),
+                                       ptr(self.leafToInternal)))
+        self.centers = self.sizes = self.layout = None
+        if box is not None:
+            self.centers = torch.empty((nn, 3), dtype=torch.float64, device=dev)
+            self.sizes = torch.empty((nn, 3), dtype=torch.float64, device=dev)
+            check(lib.sphb200_node_centers(ctx.h, ptr(self.prefixes), nn, C.byref(box), ptr(self.centers),
+                                           ptr(self.sizes)))
+        if counts is not None:
+            self.layout = torch.empty(nl + 1, **i32)
+            check(lib.sphb200_layout(ctx.h, ptr(counts), nl, ptr(self.layout)))
+
+    def view(self):
+        t = B.TreeView()
+        t.numLeafNodes, t.numNodes = self.numLeaves, self.numNodes
+        t.prefixes, t.childOffsets = ptr(self.prefixes), ptr(self.childOffsets)
+        t.internalToLeaf, t.levelRange = ptr(self.internalToLeaf), ptr(self.levelRange)
+        t.leaves, t.layout = ptr(self.leaves), ptr(self.layout)
+        t.centers, t.sizes = ptr(self.centers), ptr(self.sizes)
+        return t
+
+
+# ---------------------------------------------------------------- neighbors
+def neighborsSize(num_targets, ngmax):
+    return lib.sphb200_neighbors_size(num_targets, ngmax)
+
+
+def findNeighbors(ctx, tree, x, y, z, h, first, last, box, ng0, ngmax, iterate_h=True):
+    """neighbor search + coupled h iteration (sph/find_neighbors.hpp:10-45); h is updated in place.
+
+    returns (slab neighbor lists, nc[last-first] incl. self, numFails)"""
+    dev = x.device
+    nt = last - first
+    nb = torch.empty(max(1, neighborsSize(nt, ngmax)), dtype=torch.int32, device=dev)
+    nc = torch.zeros(max(1, nt), dtype=torch.int32, device=dev)
+    fails = C.c_uint(0)
+    dtype = B.F64 if h.dtype == torch.float64 else B.MIXED
+    tv = tree.view()
+    check(lib.sphb200_find_neighbors(ctx.h, C.byref(tv), ptr(x), ptr(y), ptr(z), ptr(h), dtype, C.c_uint32(first),
+                                     C.c_uint32(last), C.byref(box), C.c_uint(ng0), C.c_uint(ngmax), int(iterate_h),
+                                     ptr(nb), ptr(nc), C.byref(fails)))
+    return nb, nc[:nt], fails.value
+
+
+def neighborsRowMajor(ctx, nb, nc, ngmax):
+    nt = nc.numel()
+    out = torch.zeros((max(nt, 1), ngmax), dtype=torch.int32, device=nb.device)
+    check(lib.sphb200_neighbors_to_rowmajor(ctx.h, ptr(nb), ptr(nc), C.c_uint32(nt), C.c_uint(ngmax), ptr(out)))
+    return out[:nt]
+
+
+# ---------------------------------------------------------------- SPH-VE operators
+def fields_struct(d):
+    """dict name -> torch tensor  =>  sphb200_fields"""
+    f = B.Fields()
+    for n in B.FIELD_NAMES:
+        t = d.get(n)
+        setattr(f, n, t.data_ptr() if t is not None else None)
+    return f
+
+
+def hydro_const(K, wh, whd, ng0=100, ngmax=150, Kcour=0.2, Krho=0.06, gamma=5.0 / 3.0, muiConst=10.0, alphamin=0.05,
+                alphamax=1.0, decay_constant=0.2, Atmin=0.1, Atmax=0.2, ramp=None, minDt=1e-6, minDt_m1=1e-6,
+                avClean=False):
+    hc = B.HydroConst()
+    hc.K, hc.ng0, hc.ngmax, hc.Kcour, hc.Krho, hc.gamma, hc.muiConst = K, ng0, ngmax, Kcour, Krho, gamma, muiConst
+    hc.alphamin, hc.alphamax, hc.decay_constant = alphamin, alphamax, decay_constant
+    hc.Atmin, hc.Atmax, hc.ramp = Atmin, Atmax, (1.0 / (Atmax - Atmin) if ramp is None else ramp)
+    hc.minDt, hc.minDt_m1 = minDt, minDt_m1
+    hc.wh = wh.data_ptr() if hasattr(wh, "data_ptr") else wh
+    hc.whd = whd.data_ptr() if hasattr(whd, "data_ptr") else whd
+    hc.avClean = int(avClean)
+    return hc
+
+
+def _dt(d):
+    return B.F64 if d["h"].dtype == torch.float64 else B.MIXED
+
+
+def computeXMass(ctx, first, last, d, box, hc, nb):
+    f = fields_struct(d)
+    check(lib.sphb200_xmass(ctx.h, _dt(d), C.c_uint32(first), C.c_uint32(last), C.byref(box), C.byref(hc), ptr(nb),
+                            C.byref(f)))
+
+
+def computeVeDefGradh(ctx, first, last, d, box, hc, nb):
+    f = fields_struct(d)
+    check(lib.sphb200_ve_def_gradh(ctx.h, _dt(d), C.c_uint32(first), C.c_uint32(last), C.byref(box), C.byref(hc),
+                                   ptr(nb), C.byref(f)))
+
+
+def computeEOS(ctx, first, last, d, hc):
+    f = fields_struct(d)
+    check(lib.sphb200_eos(ctx.h, _dt(d), C.c_uint32(first), C.c_uint32(last), C.byref(hc), C.byref(f)))
+
+
+def computeIadDivvCurlv(ctx, first, last, d, box, hc, nb):
+    f = fields_struct(d)
+    check(lib.sphb200_iad_divv_curlv(ctx.h, _dt(d), C.c_uint32(first), C.c_uint32(last), C.byref(box), C.byref(hc),
+                                     ptr(nb), C.byref(f)))
+
+
+def computeAVswitches(ctx, first, last, d, box, hc, nb):
+    f = fields_struct(d)
+    check(lib.sphb200_av_switches(ctx.h, _dt(d), C.c_uint32(first), C.c_uint32(last), C.byref(box), C.byref(hc),
+                                  ptr(nb), C.byref(f)))
+
+
+def computeMomentumEnergy(ctx, first, last, d, box, hc, nb):
+    """returns minDtCourant"""
+    f = fields_struct(d)
+    out = C.c_double(0)
+    check(lib.sphb200_momentum_energy(ctx.h, _dt(d), C.c_uint32(first), C.c_uint32(last), C.byref(box), C.byref(hc),
+                                      ptr(nb), C.byref(f), C.byref(out)))
+    return out.value
+
+
+def computeTimestep(ctx, first, last, d, hc):
+    """(minDtCourant, minDtRho, local min incl. 1.1*minDt) — ts_global.hpp:71-112 before the global MIN"""
+    f = fields_struct(d)
+    out = (C.c_double * 3)()
+    check(lib.sphb200_timestep(ctx.h, _dt(d), C.c_uint32(first), C.c_uint32(last), C.byref(hc), C.byref(f), out))
+    return tuple(out)
+
+
+def computePositionsAndH(ctx, first, last, d, box, hc, dt, dt_m1):
+    f = fields_struct(d)
+    check(lib.sphb200_positions_update_h(ctx.h, _dt(d), C.c_uint32(first), C.c_uint32(last), C.byref(box),
+                                         C.byref(hc), C.c_double(dt), C.c_double(dt_m1), C.byref(f)))
+
+
+# ---------------------------------------------------------------- halo pack / unpack
+def packRanges(ctx, range_scan, range_begin, total, srcs, packed):
+    k = len(srcs)
+    sp = (vp * k)(*[s.data_ptr() for s in srcs])
+    eb = (C.c_int * k)(*[s.element_size() for s in srcs])
+    check(lib.sphb200_pack_ranges(ctx.h, ptr(range_scan), ptr(range_begin), range_begin.numel(), C.c_uint32(total), k,
+                                  sp, eb, ptr(packed)))
+
+
+def unpackRanges(ctx, range_scan, range_begin, total, dsts, packed):
+    k = len(dsts)
+    dp = (vp * k)(*[s.data_ptr() for s in dsts])
+    eb = (C.c_int * k)(*[s.element_size() for s in dsts])
+    check(lib.sphb200_unpack_ranges(ctx.h, ptr(range_scan), ptr(range_begin), range_begin.numel(), C.c_uint32(total),
+                                    k, dp, eb, ptr(packed)))
+
+
+def packedBytes(total, srcs):
+    return sum((total * s.element_size() + 7) // 8 * 8 for s in srcs)

@@ -1,0 +1,205 @@
+"""Python mirror of the Propagator / Domain boundary over the tier-2 C ABI.
+
+`HydroVeProp` follows sphexa::HydroVeProp (main/src/propagator/ve_hydro.hpp:54-219): sync(),
+computeForces(), integrate(); `Domain`-style getters startIndex/endIndex/nParticlesWithHalos
+follow cstone::Domain (domain/include/cstone/domain/domain.hpp:382-429).  All device state lives in
+the C library (sphb200_sim); this class only marshals host buffers.
+"""
+import ctypes as C
+import numpy as np
+
+from . import binding as B
+from . import ic
+from .binding import lib, check, vp
+
+PHASES = ["domain::sync", "FindNeighbors", "XMass", "Normalization & Gradh", "EquationOfState",
+          "IadVelocityDivCurl", "AVswitches", "MomentumAndEnergy", "Timestep+UpdateQuantities"]
+
+
+def _host_fields(arrays, real):
+    """dict name -> numpy array => sphb200_fields of host pointers (keeps references alive in `keep`)"""
+    f = B.Fields()
+    keep = []
+    for n in B.FIELD_NAMES:
+        a = arrays.get(n)
+        if a is None:
+            setattr(f, n, None)
+            continue
+        want = np.float64 if n in B.ALWAYS_F64 else (np.uint32 if n == "nc" else real)
+        a = np.ascontiguousarray(a, dtype=want)
+        keep.append(a)
+        setattr(f, n, a.ctypes.data)
+    return f, keep
+
+
+class HydroVeProp:
+    """one rank of an SPH-VE run; data stays resident on the GPU between steps"""
+
+    def __init__(self, ctx, box, settings, capacity, dtype=B.F64, rank=0, num_ranks=1, bucket_size=None,
+                 bucket_size_focus=64, av_clean=False, tables=None):
+        self.ctx = ctx
+        self.dtype = dtype
+        self.real = np.float64 if dtype == B.F64 else np.float32
+        self.settings = dict(settings)
+        n_glob = settings.get("numParticlesGlobal", capacity)
+        if bucket_size is None:
+            # sphexa.cpp:133-135
+            bucket_size = max(bucket_size_focus, n_glob // (100 * num_ranks))
+        wh, whd, K = tables if tables is not None else ic.kernel_tables(self.real)
+        self._tables = (np.ascontiguousarray(wh, self.real), np.ascontiguousarray(whd, self.real))
+        cfg = B.SimConfig()
+        cfg.dtype, cfg.rank, cfg.numRanks = dtype, rank, num_ranks
+        cfg.bucketSize, cfg.bucketSizeFocus, cfg.capacity = int(bucket_size), int(bucket_size_focus), int(capacity)
+        cfg.box = B.make_box(*box)
+        hc = cfg.hc
+        hc.K, hc.ng0, hc.ngmax = K, int(settings.get("ng0", 100)), int(settings.get("ngmax", 150))
+        hc.Kcour, hc.Krho = settings.get("Kcour", 0.2), settings.get("Krho", 0.06)
+        hc.gamma, hc.muiConst = settings["gamma"], settings["mui"]
+        hc.alphamin, hc.alphamax, hc.decay_constant = 0.05, 1.0, 0.2
+        hc.Atmin, hc.Atmax, hc.ramp = 0.1, 0.2, 1.0 / (0.2 - 0.1)
+        hc.minDt, hc.minDt_m1 = settings["minDt"], settings["minDt_m1"]
+        hc.wh, hc.whd = self._tables[0].ctypes.data, self._tables[1].ctypes.data
+        hc.avClean = int(av_clean)
+        self.K = K
+        self.capacity = capacity
+        self.h = vp()
+        check(lib.sphb200_sim_create(ctx.h, C.byref(cfg), C.byref(self.h)))
+
+    def close(self):
+        if self.h:
+            lib.sphb200_sim_destroy(self.h)
+            self.h = vp()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- data movement across the boundary
+    def upload(self, arrays):
+        n = len(arrays["x"])
+        f, keep = _host_fields(arrays, self.real)
+        check(lib.sphb200_sim_upload(self.h, C.c_size_t(n), C.byref(f)))
+        self.ctx.sync()
+        del keep
+
+    def upload_async(self, f_struct, n):
+        check(lib.sphb200_sim_upload(self.h, C.c_size_t(n), C.byref(f_struct)))
+
+    def download(self, names=None, with_keys=False):
+        names = names or B.CONSERVED
+        cnt = self.endIndex - self.startIndex
+        out = {}
+        for n in names:
+            want = np.float64 if n in B.ALWAYS_F64 else (np.uint32 if n == "nc" else self.real)
+            out[n] = np.empty(cnt, want)
+        f, keep = _host_fields(out, self.real)
+        # _host_fields may copy; make sure we hand out the arrays that were written
+        for n, a in zip([n for n in B.FIELD_NAMES if n in out], keep):
+            out[n] = a
+        keys = np.empty(cnt, np.uint64) if with_keys else None
+        check(lib.sphb200_sim_download(self.h, C.byref(f), keys.ctypes.data_as(vp) if with_keys else None))
+        if with_keys:
+            out["keys"] = keys
+        return out
+
+    def download_into(self, f_struct):
+        check(lib.sphb200_sim_download(self.h, C.byref(f_struct), None))
+
+    # ---- Propagator interface
+    def sync(self):
+        check(lib.sphb200_sim_sync(self.h))
+
+    def computeForces(self):
+        check(lib.sphb200_sim_sync(self.h))
+        check(lib.sphb200_sim_compute_forces(self.h))
+
+    def forcesPhase(self, k):
+        check(lib.sphb200_sim_forces_phase(self.h, k))
+
+    def integrate(self, global_min_dt=-1.0):
+        check(lib.sphb200_sim_integrate(self.h, C.c_double(global_min_dt)))
+
+    def step(self):
+        check(lib.sphb200_sim_step(self.h))
+
+    def localTimestep(self):
+        out = (C.c_double * 3)()
+        check(lib.sphb200_sim_local_timestep(self.h, out))
+        return tuple(out)
+
+    # ---- Domain getters
+    @property
+    def startIndex(self):
+        return lib.sphb200_sim_start_index(self.h)
+
+    @property
+    def endIndex(self):
+        return lib.sphb200_sim_end_index(self.h)
+
+    @property
+    def nParticlesWithHalos(self):
+        return lib.sphb200_sim_n_with_halos(self.h)
+
+    @property
+    def numLeaves(self):
+        return lib.sphb200_sim_num_leaves(self.h)
+
+    @property
+    def numGlobalLeaves(self):
+        return lib.sphb200_sim_num_global_leaves(self.h)
+
+    @property
+    def minDt(self):
+        return lib.sphb200_sim_min_dt(self.h)
+
+    @property
+    def ttot(self):
+        return lib.sphb200_sim_ttot(self.h)
+
+    def totalNeighbors(self):
+        return lib.sphb200_sim_total_neighbors(self.h)
+
+    def phaseTimes(self):
+        ms = (C.c_float * 9)()
+        check(lib.sphb200_sim_phase_times(self.h, ms))
+        return dict(zip(PHASES, list(ms)))
+
+    def deviceFields(self):
+        f = B.Fields()
+        check(lib.sphb200_sim_fields(self.h, C.byref(f)))
+        return f
+
+    def treeView(self):
+        t = B.TreeView()
+        check(lib.sphb200_sim_tree(self.h, C.byref(t)))
+        return t
+
+    def _d2h(self, dev_ptr, count, dtype):
+        """copy `count` elements from a raw device pointer (tests / diagnostics)"""
+        import torch
+        out = np.empty(count, dtype)
+        if count == 0:
+            return out
+        nbytes = out.nbytes
+        rt = C.CDLL("libcudart.so.12") if not hasattr(HydroVeProp, "_rt") else HydroVeProp._rt
+        HydroVeProp._rt = rt
+        self.ctx.sync()
+        rc = rt.cudaMemcpy(out.ctypes.data_as(vp), vp(dev_ptr), C.c_size_t(nbytes), 2)
+        if rc != 0:
+            raise B.SphError(f"cudaMemcpy D2H failed: {rc}")
+        return out
+
+    def leaves(self):
+        t = self.treeView()
+        return self._d2h(t.leaves, t.numLeafNodes + 1, np.uint64)
+
+    def leafCounts(self):
+        return self._d2h(lib.sphb200_sim_leaf_counts(self.h), self.numLeaves, np.uint32)
+
+    def globalLeaves(self):
+        return self._d2h(lib.sphb200_sim_global_leaves(self.h), self.numGlobalLeaves + 1, np.uint64)
+
+    def globalCounts(self):
+        return self._d2h(lib.sphb200_sim_global_counts(self.h), self.numGlobalLeaves, np.uint32)

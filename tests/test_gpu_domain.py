@@ -1,0 +1,327 @@
+"""GPU parity of the Cornerstone domain layer against the reference CPU build (oracle/_ref).
+
+Bit-exact for keys, permutations, leaves, counts, links and neighbor sets — mirrors the reference's
+own tests: domain/test/unit/sfc/hilbert.cpp, unit_cuda/primitives/primitives_gpu.cu,
+unit/tree/{csarray,octree}.cpp, unit_cuda/tree/*.cu, unit/neighbors/findneighbors.cpp.
+"""
+import numpy as np
+import pytest
+
+from conftest import to_dev, to_host, sorted_sets_equal
+
+pytestmark = pytest.mark.gpu
+
+
+def random_coords(n, box, seed, gaussian=False):
+    rng = np.random.Generator(np.random.MT19937(seed))
+    lim = box[0]
+    out = []
+    for d in range(3):
+        lo, hi = lim[2 * d], lim[2 * d + 1]
+        if gaussian:
+            a = rng.normal((lo + hi) / 2, (hi - lo) / 5, n)
+            a = np.clip(a, lo, np.nextafter(hi, lo))
+        else:
+            a = rng.uniform(lo, hi, n)
+        out.append(np.ascontiguousarray(a))
+    return out
+
+
+BOXES = [
+    ([0.0, 1.0, 0.0, 1.0, 0.0, 1.0], [0, 0, 0]),
+    ([-0.5, 0.5, -0.5, 0.5, -0.5, 0.5], [1, 1, 1]),
+    ([0.0, 1.0, 0.0, 2.0, 0.0, 3.0], [1, 1, 1]),          # non-cubic, findneighbors.cpp:127-147
+    ([-1.2, 1.5, 0.3, 0.9, -2.0, 4.0], [0, 1, 0]),
+    ([0.0, 1.0, 0.0, 1.0, 0.0, 0.0625], [1, 1, 1]),       # Kelvin-Helmholtz slab
+]
+
+
+@pytest.mark.parametrize("box", BOXES)
+def test_sfc_keys_random(pkg, ctx, ref, box):
+    from sph_exa_b200 import ops
+    n = 200_003
+    x, y, z = random_coords(n, box, 42)
+    # include points exactly on the limits (clamp path, sfc.hpp:166-168)
+    x[0], y[0], z[0] = box[0][1], box[0][3], box[0][5]
+    x[1], y[1], z[1] = box[0][0], box[0][2], box[0][4]
+    want = ref.compute_sfc_keys(x, y, z, box)
+    got = to_host(ops.computeSfcKeysGpu(ctx, to_dev(x), to_dev(y), to_dev(z), pkg.make_box(*box)), np.uint64)
+    assert np.array_equal(got, want)
+
+
+def test_sfc_keys_sedov_lattice(pkg, ctx, ref):
+    from sph_exa_b200 import ops
+    f, box, _ = pkg.ic.sedov(50)
+    want = ref.compute_sfc_keys(f["x"], f["y"], f["z"], box)
+    got = to_host(ops.computeSfcKeysGpu(ctx, to_dev(f["x"]), to_dev(f["y"]), to_dev(f["z"]), pkg.make_box(*box)),
+                  np.uint64)
+    assert np.array_equal(got, want)
+    assert np.unique(got).size == got.size
+
+
+def test_sfc_keys_empty(pkg, ctx):
+    import torch
+    from sph_exa_b200 import ops
+    e = torch.empty(0, dtype=torch.float64, device="cuda")
+    k = ops.computeSfcKeysGpu(ctx, e, e, e, pkg.make_box([0, 1, 0, 1, 0, 1], [0, 0, 0]))
+    assert k.numel() == 0
+
+
+@pytest.mark.parametrize("n", [1, 31, 4096, 4097, 100_000, 1_000_003])
+def test_sort_by_key(pkg, ctx, ref, n):
+    from sph_exa_b200 import ops
+    rng = np.random.Generator(np.random.MT19937(n))
+    keys = rng.integers(0, 1 << 63, n, dtype=np.uint64)
+    if n > 100:
+        keys[n // 2:n // 2 + 50] = keys[3]  # duplicates: stability check
+    dk = to_dev(keys.copy())
+    perm = to_host(ops.sortByKeyGpu(ctx, dk), np.uint32)
+    got = to_host(dk, np.uint64)
+    want_k, _ = ref.sort_by_key(keys)
+    assert np.array_equal(got, want_k)
+    assert np.array_equal(keys[perm], got)
+    # stable: equal keys keep their input order (the GPU reference sort is stable, primitives_gpu.cu:267-298)
+    same = got[1:] == got[:-1]
+    assert np.all(perm[1:][same] > perm[:-1][same])
+    assert np.array_equal(perm, np.argsort(keys, kind="stable").astype(np.uint32))
+
+
+def test_gather(pkg, ctx):
+    from sph_exa_b200 import ops
+    n = 50_001
+    rng = np.random.Generator(np.random.MT19937(1))
+    perm = rng.permutation(n).astype(np.uint32)
+    a = rng.normal(size=n)
+    b = rng.normal(size=n).astype(np.float32)
+    c = rng.integers(0, 1 << 62, n, dtype=np.uint64)
+    da, db, dc = ops.gatherGpu(ctx, to_dev(perm), [to_dev(a), to_dev(b), to_dev(c)])
+    assert np.array_equal(to_host(da), a[perm])
+    assert np.array_equal(to_host(db), b[perm])
+    assert np.array_equal(to_host(dc, np.uint64), c[perm])
+
+
+def sorted_keys(ref, n, box, seed, gaussian):
+    x, y, z = random_coords(n, box, seed, gaussian)
+    keys, perm = ref.sort_by_key(ref.compute_sfc_keys(x, y, z, box))
+    return keys, x[perm], y[perm], z[perm]
+
+
+@pytest.mark.parametrize("gaussian", [False, True])
+@pytest.mark.parametrize("bucket", [1, 16, 64, 1000])
+def test_compute_octree(pkg, ctx, ref, gaussian, bucket):
+    """computeOctree invariants + equality with the CPU build (unit/tree/csarray.cpp, unit_cuda/tree/csarray.cu)"""
+    from sph_exa_b200 import ops
+    n = 100_000 if bucket > 1 else 3000
+    keys, *_ = sorted_keys(ref, n, BOXES[1], 7, gaussian)
+    want_l, want_c, want_it = ref.compute_octree(keys, bucket)
+    lv, ct, it = ops.computeOctreeGpu(ctx, to_dev(keys), bucket)
+    assert np.array_equal(to_host(lv, np.uint64), want_l)
+    assert np.array_equal(to_host(ct, np.uint32), want_c)
+    assert it == want_it
+    assert int(to_host(ct, np.uint32).sum()) == n
+
+
+def test_node_counts_and_rebalance_decision(pkg, ctx, ref):
+    from sph_exa_b200 import ops
+    keys, *_ = sorted_keys(ref, 50_000, BOXES[0], 3, True)
+    leaves, counts, _ = ref.compute_octree(keys, 64)
+    # counts of a tree built for other particles: exercises empty and overfull leaves
+    keys2, *_ = sorted_keys(ref, 80_000, BOXES[0], 4, False)
+    want = ref.compute_node_counts(leaves, keys2)
+    got = to_host(ops.computeNodeCountsGpu(ctx, to_dev(leaves), to_dev(keys2)), np.uint32)
+    assert np.array_equal(got, want)
+    for bucket in (8, 64, 512):
+        want_ops, want_conv = ref.rebalance_decision(leaves, want, bucket)
+        ops_d, conv = ops.rebalanceDecisionGpu(ctx, to_dev(leaves), to_dev(want), bucket)
+        assert np.array_equal(to_host(ops_d), want_ops)
+        assert conv == want_conv
+
+
+def test_update_octree_sequence(pkg, ctx, ref):
+    """history-dependent updates: one rebalance step per 'time step' on drifting particles"""
+    from sph_exa_b200 import ops
+    box = BOXES[1]
+    x, y, z = random_coords(60_000, box, 11, True)
+    keys, _ = ref.sort_by_key(ref.compute_sfc_keys(x, y, z, box))
+    lv, ct, _ = ref.compute_octree(keys, 64)
+    dl, dc = to_dev(lv), to_dev(ct)
+    rng = np.random.Generator(np.random.MT19937(5))
+    for step in range(6):
+        x = np.clip(x * 0.93 + rng.normal(0, 0.004, x.size), -0.5, 0.4999999)
+        y = np.clip(y * 0.97, -0.5, 0.4999999)
+        keys, _ = ref.sort_by_key(ref.compute_sfc_keys(x, y, z, box))
+        lv, ct, conv = ref.update_octree(keys, 64, lv, ct)
+        dl, dc, dconv = ops.updateOctreeGpu(ctx, to_dev(keys), 64, dl, dc)
+        assert np.array_equal(to_host(dl, np.uint64), lv), f"step {step}"
+        assert np.array_equal(to_host(dc, np.uint32), ct), f"step {step}"
+        assert conv == dconv
+
+
+@pytest.mark.parametrize("gaussian", [False, True])
+def test_build_octree_and_centers(pkg, ctx, ref, gaussian):
+    from sph_exa_b200 import ops
+    box = BOXES[3]
+    keys, *_ = sorted_keys(ref, 70_000, box, 9, gaussian)
+    leaves, counts, _ = ref.compute_octree(keys, 32)
+    want = ref.build_octree(leaves)
+    wc, ws = ref.node_centers(want["prefixes"], box)
+    t = ops.Octree(ctx, to_dev(leaves), pkg.make_box(*box), to_dev(counts))
+    assert np.array_equal(to_host(t.prefixes, np.uint64), want["prefixes"])
+    assert np.array_equal(to_host(t.childOffsets), want["childOffsets"])
+    assert np.array_equal(to_host(t.internalToLeaf), want["internalToLeaf"])
+    assert np.array_equal(to_host(t.leafToInternal), want["leafToInternal"])
+    assert np.array_equal(to_host(t.levelRange), want["levelRange"])
+    ni = want["numInternal"]
+    if ni:
+        # parents[(child-1)/8] is defined for every sibling group
+        ng = (want["numNodes"] - 1) // 8
+        assert np.array_equal(to_host(t.parents)[:ng], want["parents"][:ng])
+    assert np.array_equal(to_host(t.centers), wc)
+    assert np.array_equal(to_host(t.sizes), ws)
+    lay = to_host(t.layout, np.uint32)
+    assert lay[0] == 0 and np.array_equal(np.diff(lay.astype(np.int64)), counts)
+
+
+def test_single_leaf_tree(pkg, ctx, ref):
+    """root-only tree: singleTraversal's 'root is the endpoint' branch (traversal.hpp:73-78)"""
+    from sph_exa_b200 import ops
+    box = BOXES[0]
+    x, y, z = random_coords(40, box, 2)
+    keys, perm = ref.sort_by_key(ref.compute_sfc_keys(x, y, z, box))
+    x, y, z = x[perm], y[perm], z[perm]
+    leaves, counts, _ = ref.compute_octree(keys, 64)
+    assert counts.size == 1
+    h = np.full(40, 0.2)
+    tr = ref.build_octree(leaves)
+    c, s = ref.node_centers(tr["prefixes"], box)
+    lay = np.array([0, 40], np.uint32)
+    wnb, wnc, _ = ref.find_neighbors(x, y, z, h, 0, 40, box, tr, lay, c, s, 100, 150, False)
+    t = ops.Octree(ctx, to_dev(leaves), pkg.make_box(*box), to_dev(counts))
+    nb, nc, _ = ops.findNeighbors(ctx, t, to_dev(x), to_dev(y), to_dev(z), to_dev(h), 0, 40, pkg.make_box(*box), 100,
+                                  150, False)
+    rm = to_host(ops.neighborsRowMajor(ctx, nb, nc, 150), np.uint32)
+    assert sorted_sets_equal(rm, to_host(nc, np.uint32), wnb, wnc, 150)
+
+
+def neighbor_case(pkg, ctx, ref, n, box, radius, seed, gaussian, ngmax, iterate_h, real=np.float64, first=0, last=None,
+                  bucket=64):
+    from sph_exa_b200 import ops
+    x, y, z = random_coords(n, box, seed, gaussian)
+    keys, perm = ref.sort_by_key(ref.compute_sfc_keys(x, y, z, box))
+    x, y, z = x[perm], y[perm], z[perm]
+    leaves, counts, _ = ref.compute_octree(keys, bucket)
+    tr = ref.build_octree(leaves)
+    c, s = ref.node_centers(tr["prefixes"], box)
+    lay = np.zeros(counts.size + 1, np.uint32)
+    np.cumsum(counts, out=lay[1:])
+    h = np.full(n, radius / 2, real)
+    last = n if last is None else last
+    wnb, wnc, wh = ref.find_neighbors(x, y, z, h, first, last, box, tr, lay, c, s, 100, ngmax, iterate_h)
+    t = ops.Octree(ctx, to_dev(leaves), pkg.make_box(*box), to_dev(counts))
+    dh = to_dev(h)
+    nb, nc, fails = ops.findNeighbors(ctx, t, to_dev(x), to_dev(y), to_dev(z), dh, first, last, pkg.make_box(*box), 100,
+                                      ngmax, iterate_h)
+    rm = to_host(ops.neighborsRowMajor(ctx, nb, nc, ngmax), np.uint32)
+    gnc = to_host(nc, np.uint32)
+    return rm, gnc, to_host(dh), wnb, wnc, wh
+
+
+@pytest.mark.parametrize("box", [BOXES[0], BOXES[1], BOXES[2]])
+@pytest.mark.parametrize("radius", [0.124, 0.0624])
+@pytest.mark.parametrize("gaussian", [False, True])
+def test_find_neighbors_small(pkg, ctx, ref, box, radius, gaussian):
+    """2500 particles, radii as in unit/neighbors/findneighbors.cpp:127-147, open + periodic, non-cubic"""
+    n, ngmax = 2500, 2500
+    rm, gnc, _, wnb, wnc, _ = neighbor_case(pkg, ctx, ref, n, box, radius, 42, gaussian, ngmax, False)
+    assert np.array_equal(gnc, wnc)
+    assert sorted_sets_equal(rm, gnc, wnb, wnc, ngmax)
+    # ascending-j order is part of this implementation's contract
+    cnt = gnc.astype(np.int64) - 1
+    k = np.arange(ngmax)[None, :]
+    valid = (k[:, 1:] < cnt[:, None])
+    assert np.all((rm[:, 1:].astype(np.int64) > rm[:, :-1].astype(np.int64)) | ~valid)
+
+
+def test_find_neighbors_all_pairs(pkg, ctx, ref):
+    """radius 3.0 in the unit box: every particle is a neighbor of every other (findneighbors.cpp radius 3.0 case)"""
+    n, ngmax = 600, 600
+    for box in (BOXES[0], BOXES[1]):
+        rm, gnc, _, wnb, wnc, _ = neighbor_case(pkg, ctx, ref, n, box, 3.0, 1, False, ngmax, False)
+        assert np.all(gnc == n)
+        assert sorted_sets_equal(rm, gnc, wnb, wnc, ngmax)
+
+
+@pytest.mark.parametrize("real", [np.float64, np.float32])
+def test_find_neighbors_h_iteration(pkg, ctx, ref, real):
+    """coupled h/neighbor-count iteration (sph/find_neighbors.hpp:10-45): start with h far off target"""
+    n, ngmax = 20_000, 150
+    box = BOXES[1]
+    for radius in (0.02, 0.3):  # too few / too many neighbors at the start
+        rm, gnc, gh, wnb, wnc, wh = neighbor_case(pkg, ctx, ref, n, box, radius, 5, True, ngmax, True, real)
+        # h after iteration: pow() differs by <= 2 ulp between libm and CUDA
+        tol = 1e-13 if real == np.float64 else 1e-5
+        assert np.allclose(gh, wh, rtol=tol, atol=0)
+        same_h = gh == wh
+        assert same_h.mean() > 0.9
+        assert np.array_equal(gnc[same_h], wnc[same_h])
+        assert sorted_sets_equal(rm[same_h], gnc[same_h], wnb[same_h], wnc[same_h], ngmax)
+
+
+def test_find_neighbors_subrange_and_ragged(pkg, ctx, ref):
+    """targets [first,last) not aligned to 32, sources include 'halo' particles outside the range"""
+    n, ngmax = 30_011, 200
+    rm, gnc, _, wnb, wnc, _ = neighbor_case(pkg, ctx, ref, n, BOXES[2], 0.09, 8, False, ngmax, False, first=1003,
+                                            last=20_002)
+    assert sorted_sets_equal(rm, gnc, wnb, wnc, ngmax)
+
+
+def test_find_neighbors_kh_like_density_contrast(pkg, ctx, ref):
+    """high neighbor-count variance: gaussian blob, bucket 16, per-particle radii"""
+    from sph_exa_b200 import ops
+    n, ngmax = 40_000, 400
+    box = BOXES[4]
+    x, y, z = random_coords(n, box, 3, False)
+    y = np.where(y > 0.5, 0.5 + (y - 0.5) * 0.5, y)  # denser band
+    keys, perm = ref.sort_by_key(ref.compute_sfc_keys(x, y, z, box))
+    x, y, z = x[perm], y[perm], z[perm]
+    leaves, counts, _ = ref.compute_octree(keys, 16)
+    tr = ref.build_octree(leaves)
+    c, s = ref.node_centers(tr["prefixes"], box)
+    lay = np.zeros(counts.size + 1, np.uint32)
+    np.cumsum(counts, out=lay[1:])
+    rng = np.random.Generator(np.random.MT19937(1))
+    h = rng.uniform(0.004, 0.012, n)
+    wnb, wnc, _ = ref.find_neighbors(x, y, z, h, 0, n, box, tr, lay, c, s, 100, ngmax, False)
+    t = ops.Octree(ctx, to_dev(leaves), pkg.make_box(*box), to_dev(counts))
+    nb, nc, _ = ops.findNeighbors(ctx, t, to_dev(x), to_dev(y), to_dev(z), to_dev(h), 0, n, pkg.make_box(*box), 100,
+                                  ngmax, False)
+    rm = to_host(ops.neighborsRowMajor(ctx, nb, nc, ngmax), np.uint32)
+    assert sorted_sets_equal(rm, to_host(nc, np.uint32), wnb, wnc, ngmax)
+
+
+def test_pack_unpack_ranges(pkg, ctx):
+    """gatherRanges/scatterRanges round trip (unit_cuda/halos/gather_halos_gpu.cu)"""
+    import torch
+    from sph_exa_b200 import ops
+    n = 10_000
+    rng = np.random.Generator(np.random.MT19937(0))
+    a = rng.normal(size=n)
+    b = rng.normal(size=n).astype(np.float32)
+    begins = np.array([5, 100, 4000, 9990], np.uint32)
+    lens = np.array([17, 1, 2500, 10], np.uint32)
+    scan = np.zeros(4, np.uint32)
+    scan[1:] = np.cumsum(lens)[:-1]
+    total = int(lens.sum())
+    da, db = to_dev(a), to_dev(b)
+    packed = torch.zeros(ops.packedBytes(total, [da, db]), dtype=torch.uint8, device="cuda")
+    ops.packRanges(ctx, to_dev(scan), to_dev(begins), total, [da, db], packed)
+    idx = np.concatenate([np.arange(s, s + l) for s, l in zip(begins, lens)])
+    ph = packed.cpu().numpy()
+    assert np.array_equal(ph[:total * 8].view(np.float64), a[idx])
+    off = (total * 8 + 7) // 8 * 8
+    assert np.array_equal(ph[off:off + total * 4].view(np.float32), b[idx])
+    da2, db2 = torch.zeros_like(da), torch.zeros_like(db)
+    ops.unpackRanges(ctx, to_dev(scan), to_dev(begins), total, [da2, db2], packed)
+    wa = np.zeros(n)
+    wa[idx] = a[idx]
+    assert np.array_equal(to_host(da2), wa)
