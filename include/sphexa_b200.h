@@ -99,7 +99,9 @@ typedef struct sphb200_hydro_const
 typedef struct sphb200_ctx sphb200_ctx;
 
 /* ---- context ---- */
-/* stream: a cudaStream_t (e.g. torch.cuda.current_stream().cuda_stream) or NULL for a private stream */
+/* stream: a cudaStream_t (e.g. torch.cuda.current_stream().cuda_stream; NULL = the legacy default stream) or
+ * SPHB200_PRIVATE_STREAM to let the context create its own non-blocking stream */
+#define SPHB200_PRIVATE_STREAM ((void*)(intptr_t)-1)
 int sphb200_create(int device, void* stream, sphb200_ctx** out);
 void sphb200_destroy(sphb200_ctx* ctx);
 const char* sphb200_last_error(void);

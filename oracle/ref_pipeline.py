@@ -95,6 +95,7 @@ class RefSim:
         self.minDtRho = ref.rho_timestep(0, n, f["divv"], self.s.get("Krho", 0.06))
         self.times["IadVelocityDivCurl"] = T() - t
         t = T()
+        self.alpha_pre = f["alpha"].copy()  # alpha entering AVswitches, in this step's SFC order (for tests)
         ref.av_switches(0, n, ngmax, K, box, nb, nc, f["x"], f["y"], f["z"], f["vx"], f["vy"], f["vz"], f["h"],
                         f["c"], f["c11"], f["c12"], f["c13"], f["c22"], f["c23"], f["c33"], wh, whd, f["kx"], f["xm"],
                         f["divv"], self.minDt, 0.05, 1.0, 0.2, f["alpha"])

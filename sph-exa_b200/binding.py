@@ -125,13 +125,15 @@ def ptr(t):
 class Context:
     """owns a sphb200_ctx bound to a CUDA stream (default: torch's current stream)"""
 
-    def __init__(self, device=0, stream=None):
+    def __init__(self, device=0, stream=None, private_stream=False):
         import torch
         if not torch.cuda.is_available():
             raise SphError("sph-exa_b200 needs a CUDA device: there is no CPU fallback")
         torch.cuda.set_device(device)
         self.device = device
-        if stream is None:
+        if private_stream:
+            stream = -1  # SPHB200_PRIVATE_STREAM
+        elif stream is None:
             stream = torch.cuda.current_stream(device).cuda_stream
         self.h = vp()
         check(lib.sphb200_create(device, vp(stream), C.byref(self.h)))

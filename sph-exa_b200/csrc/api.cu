@@ -46,7 +46,7 @@ extern "C" int sphb200_create(int device, void* stream, sphb200_ctx** out)
     SPHB200_CUDA(cudaSetDevice(device));
     auto* ctx   = new sphb200_ctx;
     ctx->device = device;
-    if (stream) { ctx->stream = static_cast<cudaStream_t>(stream); }
+    if (stream != SPHB200_PRIVATE_STREAM) { ctx->stream = static_cast<cudaStream_t>(stream); }
     else
     {
         SPHB200_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));

@@ -83,12 +83,16 @@ def test_operators_one_by_one(pkg, ctx, ref, real, case, side, steps):
     outs = ["c11", "c12", "c13", "c22", "c23", "c33", "divv", "curlv"] + (names[-6:] if av_clean else [])
     d = fresh(outs)
     ops.computeIadDivvCurlv(ctx, 0, n, d, b, hc, nb)
+    # the off-diagonal c_ij (and dV_ij) of a near-lattice are cancellation residuals: scale by the whole tensor
+    cscale = max(np.abs(want[k]).max() for k in ("c11", "c12", "c13", "c22", "c23", "c33"))
     for k in outs:
-        assert rel_err(to_host(d[k]), want[k]) < tol * 10, k
+        scale = cscale if k.startswith("c") and k != "curlv" else max(np.abs(want[k]).max(), 1e-300)
+        err = np.abs(to_host(d[k]).astype(np.float64) - want[k]).max() / scale
+        assert err < tol * 10, (k, err)
 
     # AV switches update alpha in place: start from the pre-force alpha
     d = fresh([])
-    d["alpha"] = to_dev(pre["alpha"])
+    d["alpha"] = to_dev(sim.alpha_pre)
     ops.computeAVswitches(ctx, 0, n, d, b, hc, nb)
     assert rel_err(to_host(d["alpha"]), want["alpha"]) < tol
 
@@ -122,7 +126,7 @@ def test_golden_ve_fixture(pkg, ctx):
     g = np.load(os.path.join(GOLDEN, "ve_fixture.npz"))
     n = 99
     f = {k: np.ascontiguousarray(g[k]) for k in g.files}
-    K = float(f["K"])
+    K = float(f["K"].item())
     mpart = 3.781038064465603e26
     m = np.full(n, mpart)
     xm = mpart / f["rho0"]
