@@ -1,0 +1,303 @@
+#!/usr/bin/env python
+"""bench.py — SPH particle-steps/sec of the SPH-VE full time step (domain sync + neighbors + all hydro
+kernels + integrate) on synthetic Sedov ICs, BASELINE.json's metric.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--side S] [--dtype f64|mixed] [--impl reference]
+
+N = 1: Sedov 200^3 (8.0 M particles, BASELINE.json configs[1]) on one B200.
+N > 1: launched by torchrun, one rank per GPU; the particle set is partitioned by SFC key ranges
+       (sph-exa_b200/dist.py), weak scaling: 200^3 particles per GPU (global lattice side = round(200 * N^(1/3))).
+--impl reference: the reference's own OpenMP CPU path (oracle/_ref = the reference headers compiled where they
+       lie) on the host cores of this box, on a bounded sample of the same workload.
+One JSON line on stdout (rank 0).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "SPH particle-steps/sec (Sedov, SPH-VE full timestep: domain sync + neighbors + hydro + integrate)"
+UNIT = "particle-steps/s"
+
+# algorithmic bytes per particle per launch (compulsory field traffic), f64 / mixed
+ALGO_BYTES = {
+    "domain::sync": (464, 384), "FindNeighbors": (32 + 4, 28 + 4), "XMass": (60, 44),
+    "Normalization & Gradh": (64, 44), "EquationOfState": (56, 32), "IadVelocityDivCurl": (136, 80),
+    "AVswitches": (152, 88), "MomentumAndEnergy": (184, 108), "Timestep+UpdateQuantities": (244, 140),
+}
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return json.load(f).get("hbm_gbs", 6650.0), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """samples nvidia-smi clocks / throttle reasons during the timed region"""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.rows = []
+        self.proc = None
+        self.index = index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            parts = [p.strip() for p in r.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                sm.append(float(parts[0]))
+                mx = float(parts[1])
+            except ValueError:
+                continue
+            for n, v in zip(names, parts[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        med = sm[len(sm) // 2] if sm else None
+        return {"sm_mhz": med, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def reference_arm(args):
+    """the reference's CPU implementation of the path (oracle/_ref), all host threads, bounded sample"""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    import sphexa_b200_loader
+    pkg = sphexa_b200_loader.load()
+    from oracle import ref
+    from oracle.ref_pipeline import RefSim
+    import numpy as np
+    real = np.float64 if args.dtype == "f64" else np.float32
+    side = args.ref_side
+    f, box, s = pkg.ic.sedov(side, args.dtype)
+    n = f["x"].size
+    sim = RefSim(f, box, s, real=real)
+    for _ in range(args.warmup):
+        sim.step()
+    t0 = time.perf_counter()
+    nb_ms = 0.0
+    for _ in range(args.steps):
+        sim.step()
+        nb_ms += sim.times["FindNeighbors"] * 1e3
+    dt = time.perf_counter() - t0
+    value = n * args.steps / dt
+    cores = ref.num_threads()
+    sample = (f"Sedov {side}^3 ({n} particles, same IC formulas, {args.dtype} types) per step instead of 200^3: "
+              f"particle-steps/s is size-independent to within the log N of the tree")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
+        "config": {"workload": f"Sedov blast wave 200^3 SPH-VE full step; reference CPU arm timed on a {side}^3 sample",
+                   "l2": "n/a (CPU)"},
+        "find_neighbors_ms": nb_ms / args.steps,
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def cpu_baseline(pkg, dtype, side=80, steps=2):
+    """bounded CPU sample for the default run's JSON line (rank 0, N=1)"""
+    import numpy as np
+    from oracle import ref
+    from oracle.ref_pipeline import RefSim
+    real = np.float64 if dtype == "f64" else np.float32
+    f, box, s = pkg.ic.sedov(side, dtype)
+    sim = RefSim(f, box, s, real=real)
+    sim.step()  # warm-up: tree convergence from scratch, page faults
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        sim.step()
+    dt = time.perf_counter() - t0
+    n = f["x"].size
+    return {"value": n * steps / dt, "unit": UNIT, "cores": ref.num_threads(), "kind": "reference",
+            "sample": f"{steps} steps of Sedov {side}^3 ({n} particles) after 1 warm-up step, oracle/_ref (reference "
+                      f"headers, g++ -O3 -fopenmp), all host threads",
+            "find_neighbors_ms": sim.times["FindNeighbors"] * 1e3}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--side", type=int, default=200, help="lattice side per GPU (200 -> 8.0 M particles)")
+    ap.add_argument("--dtype", default="f64", choices=["f64", "mixed"])
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--ref-side", type=int, default=100, help="lattice side of the CPU reference sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else max(args.warmup, 1)
+
+    if args.impl == "reference":
+        return reference_arm(args)
+
+    import numpy as np
+    import torch
+    import sphexa_b200_loader
+    pkg = sphexa_b200_loader.load()
+    from sph_exa_b200 import sim as S, binding as B
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.gpus > 1 or world > 1:
+        from sph_exa_b200 import dist as D
+        return D.bench_main(args, pkg, METRIC, UNIT, ALGO_BYTES, load_peaks, ClockSampler)
+
+    torch.cuda.set_device(local_rank)
+    dtype = B.F64 if args.dtype == "f64" else B.MIXED
+    f, box, s = pkg.ic.sedov(args.side, args.dtype)
+    n = f["x"].size
+    ctx = pkg.Context(local_rank)
+    gs = S.HydroVeProp(ctx, box, s, capacity=n, dtype=dtype)
+    gs.upload(f)
+
+    def sync():
+        torch.cuda.synchronize()
+
+    # ---------------- device-resident throughput ("value")
+    for _ in range(args.warmup):
+        gs.step()
+    sync()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    launches0 = ctx.launches
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    phase_ms = {}
+    e0.record()
+    for _ in range(args.steps):
+        gs.step()
+    e1.record()
+    sync()
+    total_ms = e0.elapsed_time(e1)
+    launches = ctx.launches - launches0
+    clocks = sampler.stop()
+    # per-phase device times (cudaEvents recorded by the library on its launch stream), averaged over extra steps
+    reps = 3
+    for _ in range(reps):
+        gs.step()
+        for k, v in gs.phaseTimes().items():
+            phase_ms[k] = phase_ms.get(k, 0.0) + v / reps
+    ms_per_step = total_ms / args.steps
+    value = n * args.steps / (total_ms * 1e-3)
+    total_nb = gs.totalNeighbors()
+
+    # ---------------- roofline of the dominant kernel
+    peak, peak_src = load_peaks()
+    kernels = {k: v for k, v in phase_ms.items() if k not in ("domain::sync",)}
+    dom = max(kernels, key=kernels.get)
+    col = 0 if args.dtype == "f64" else 1
+    algo = ALGO_BYTES[dom][col] * n
+    achieved = algo / (phase_ms[dom] * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": algo, "kernel_ms": phase_ms[dom],
+                "share_of_step": phase_ms[dom] / sum(phase_ms.values())}
+    # whole-step algorithmic traffic (1360 B f64 / 920 B mixed per particle-step)
+    step_bytes = (1360 if args.dtype == "f64" else 920) * n
+    roofline["step_achieved_gbs"] = step_bytes / (ms_per_step * 1e-3) / 1e9
+    roofline["step_frac"] = roofline["step_achieved_gbs"] / peak
+
+    # ---------------- end to end through the C ABI with host buffers
+    e2e = None
+    if not args.no_e2e:
+        real = np.float64 if args.dtype == "f64" else np.float32
+        host_in, host_out = {}, {}
+        state = gs.download()
+        for k in B.CONSERVED:
+            want = np.float64 if k in B.ALWAYS_F64 else real
+            tin = torch.empty(n, dtype=torch.float64 if want == np.float64 else torch.float32).pin_memory()
+            tout = torch.empty_like(tin).pin_memory()
+            tin.numpy()[:] = state[k]
+            host_in[k], host_out[k] = tin, tout
+        fin, fout = B.Fields(), B.Fields()
+        for k in B.FIELD_NAMES:
+            setattr(fin, k, host_in[k].data_ptr() if k in host_in else None)
+            setattr(fout, k, host_out[k].data_ptr() if k in host_out else None)
+        h2d = sum(t.numel() * t.element_size() for t in host_in.values())
+        d2h = sum(t.numel() * t.element_size() for t in host_out.values())
+        e2e_steps = max(2, min(args.steps, 5))
+        for it in range(1 + e2e_steps):
+            if it == 1:
+                sync()
+                t0 = time.perf_counter()
+            gs.upload_async(fin, n)      # H2D of this step's inputs from pinned memory
+            gs.step()
+            gs.download_into(fout)       # D2H of the step's result (synchronises)
+            for k in host_in:            # next step's input = this step's output
+                host_in[k], host_out[k] = host_out[k], host_in[k]
+            for k in B.FIELD_NAMES:
+                setattr(fin, k, host_in[k].data_ptr() if k in host_in else None)
+                setattr(fout, k, host_out[k].data_ptr() if k in host_out else None)
+        sync()
+        dt = time.perf_counter() - t0
+        e2e = {"value": n * e2e_steps / dt, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+               "ms_per_step": dt / e2e_steps * 1e3, "steps": e2e_steps}
+
+    cpu = None
+    if not args.no_cpu_baseline:
+        try:
+            cpu = cpu_baseline(pkg, args.dtype)
+        except Exception as ex:  # the checker library is absent: report it, never substitute
+            cpu = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": f"unavailable: {ex}"}
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": args.dtype, "data": "synthetic",
+        "config": {"workload": f"Sedov blast wave {args.side}^3 ({n} particles) SPH-VE on 1 B200, full step",
+                   "l2": "inputs larger than L2 (particle state >= 2.5 GB, neighbor lists 4.8 GB)",
+                   "ng0": 100, "ngmax": 150, "bucket_focus": 64},
+        "find_neighbors_ms": phase_ms.get("FindNeighbors"),
+        "phase_ms": phase_ms, "total_neighbors": total_nb, "leaves": gs.numLeaves,
+        "clocks": clocks, "gpu_launches": launches, "roofline": roofline, "e2e": e2e, "cpu_baseline": cpu,
+    }
+    print(json.dumps(line), flush=True)
+    gs.close()
+    ctx.close()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())
