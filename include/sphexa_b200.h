@@ -207,6 +207,16 @@ int sphb200_unpack_ranges(sphb200_ctx*, const uint32_t* rangeScan, const uint32_
                           uint32_t totalElems, int nfields, void* const* dst_h, const int* elem_bytes_h,
                           const void* packed);
 
+/* ---- halo discovery (multi-GPU) ----
+ * segmentMaxGpu (primitives_gpu.h:76, primitives_gpu.cu:180-207): out[s] = max h over [layout[s], layout[s+1]) */
+int sphb200_segment_max(sphb200_ctx*, const void* h, int dtype, const uint32_t* layout, int numSegments, double* out);
+/* owner-side findHalos (traversal/collisions_gpu.h:59, collisions_gpu.cu:39-66): mask[leaf] bit q set if the leaf box
+ * (center/half-size, [numLeaves][3]) overlaps one of peer q's query boxes; boxes: [numPeers][maxBoxes][6]
+ * (center xyz, half-size xyz), boxCount[numPeers] (device) */
+int sphb200_mark_halo_leaves(sphb200_ctx*, const double* leafCenters, const double* leafSizes, int numLeaves,
+                             const double* boxes, const int* boxCount, int numPeers, int maxBoxes, int myRank,
+                             const sphb200_box* box_h, uint32_t* mask);
+
 /* ======================= tier 2: domain + propagator ======================= */
 /* cstone::Domain<uint64_t,double,GpuTag> (domain/include/cstone/domain/domain.hpp:65-683) and
  * sphexa::HydroVeProp (main/src/propagator/ve_hydro.hpp:54-219) for one rank of an SFC-partitioned run.

@@ -72,6 +72,7 @@ SYMBOLS = [
     "sphb200_sim_fields", "sphb200_sim_tree", "sphb200_sim_keys", "sphb200_sim_neighbors",
     "sphb200_sim_phase_times", "sphb200_sim_set_layout", "sphb200_sim_local_timestep", "sphb200_sim_global_leaves",
     "sphb200_sim_global_counts", "sphb200_sim_leaf_counts", "sphb200_sim_get_box", "sphb200_sim_set_dt",
+    "sphb200_segment_max", "sphb200_mark_halo_leaves",
 ]
 
 lib.sphb200_last_error.restype = C.c_char_p

@@ -113,6 +113,35 @@ def sedov(side, dtype="f64"):
     return f, box, settings
 
 
+def sedov_range(side, first, last, dtype="f64"):
+    """lattice sites [first,last) of the side^3 Sedov IC (one rank's slab, sedov_init.hpp:106-133 + partitionRange)"""
+    T = _real(dtype)
+    c = dict(SEDOV)
+    ener0 = c["energyTotal"] / math.pow(math.pi, 1.5) / 1.0 / math.pow(c["width"], 3.0)
+    n_glob = side ** 3
+    r = c["r1"]
+    step = (2.0 * r) / side
+    r_ini = -r + 0.5 * step
+    idx = np.arange(first, last, dtype=np.int64)
+    k = idx % side
+    j = (idx // side) % side
+    i = idx // (side * side)
+    x = r_ini + k.astype(np.float64) * step
+    y = r_ini + j.astype(np.float64) * step
+    z = r_ini + i.astype(np.float64) * step
+    n = idx.size
+    h_init = np.cbrt(3.0 / (4 * math.pi) * c["ng0"] * math.pow(2 * r, 3) / n_glob) * 0.5
+    cv = float(ideal_gas_cv(c["mui"], c["gamma"], T))
+    r2 = x * x + y * y + z * z
+    temp = (ener0 * np.exp(-(r2 / (c["width"] * c["width"]))) + c["u0"]) / cv
+    f = dict(x=x, y=y, z=z, h=np.full(n, h_init, T), m=np.full(n, c["mTotal"] / n_glob, T), vx=np.zeros(n, T),
+             vy=np.zeros(n, T), vz=np.zeros(n, T), x_m1=np.zeros(n, T), y_m1=np.zeros(n, T), z_m1=np.zeros(n, T),
+             temp=temp, du_m1=np.zeros(n, T), alpha=np.full(n, 0.05, T))
+    box = ([-r, r, -r, r, -r, r], [1, 1, 1])
+    settings = dict(c, Kcour=0.2, Krho=0.06, numParticlesGlobal=n_glob)
+    return f, box, settings
+
+
 def _jittered_lattice(side, lo, hi, jitter, seed):
     """seeded jittered lattice replacing the unavailable glass blocks"""
     rng = np.random.Generator(np.random.MT19937(seed))

@@ -89,7 +89,7 @@ def computeOctreeGpu(ctx, keys, bucket, capacity=None):
 def updateOctreeGpu(ctx, keys, bucket, leaves, counts):
     """updateOctreeGpu (tree/update_gpu.cuh:58-82): one rebalance + recount; returns (leaves, counts, converged)"""
     nl0 = counts.numel()
-    cap = 8 * nl0 + 64
+    cap = 4096 * min(nl0, 64) + 8 * nl0 + 64  # a leaf can split into up to 4096 (csarray.hpp:305)
     lv = torch.empty(cap + 2, dtype=torch.int64, device=keys.device)
     ct = torch.empty(cap + 2, dtype=torch.int32, device=keys.device)
     lv[:nl0 + 1] = leaves

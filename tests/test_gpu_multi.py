@@ -1,0 +1,25 @@
+"""Multi-GPU parity: runs tests/dist_check.py under torchrun when >= 2 GPUs are visible."""
+import os
+import subprocess
+import sys
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _ngpu():
+    import torch
+    return torch.cuda.device_count() if torch.cuda.is_available() else 0
+
+
+@pytest.mark.parametrize("case,side", [("sedov", 40), ("noh", 40), ("kh", 64)])
+def test_two_ranks_equal_one_rank(case, side):
+    if _ngpu() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+           "127.0.0.1", "--master-port", "29533", os.path.join(ROOT, "tests", "dist_check.py"), "--case", case,
+           "--side", str(side), "--steps", "3"]
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
+    assert res.returncode == 0 and "DIST_CHECK PASS" in res.stdout, res.stdout[-3000:] + res.stderr[-3000:]
