@@ -271,6 +271,15 @@ const uint64_t* sphb200_sim_keys(const sphb200_sim*);
 const uint32_t* sphb200_sim_neighbors(const sphb200_sim*);
 /* per-phase device times of the last step in ms: sync, neighbors, xmass, gradh, eos, iad, av, momentum, timestep+update */
 int sphb200_sim_phase_times(sphb200_sim*, float* ms_out9);
+/* local (pre-all-reduce) time step of the last computeForces: out3 = {minDtCourant, minDtRho, min incl. 1.1*minDt} */
+int sphb200_sim_local_timestep(sphb200_sim*, double* out3_h);
+/* device views of the trees: replicated global tree (assignment.hpp:62-113) and focus-tree leaf counts */
+const uint64_t* sphb200_sim_global_leaves(const sphb200_sim*);
+const uint32_t* sphb200_sim_global_counts(const sphb200_sim*);
+const uint32_t* sphb200_sim_leaf_counts(const sphb200_sim*);
+void sphb200_sim_get_box(const sphb200_sim*, sphb200_box* out);
+/* override minDt / minDt_m1 (restart, tests) */
+void sphb200_sim_set_dt(sphb200_sim*, double minDt, double minDt_m1);
 /* set layout for multi-rank: arrays hold n particles, assigned = [start,end) */
 int sphb200_sim_set_layout(sphb200_sim*, uint32_t start, uint32_t end, uint32_t nWithHalos);
 

@@ -62,16 +62,16 @@ def sedov_steps():
     for step in range(3):
         sim.step()
         pre = f"s{step}_"
-        out[pre + "keys"] = sim.keys
+        out[pre + "keys"] = sim.keys.copy()
         out[pre + "leaves"] = sim.ftree[0]
         out[pre + "counts"] = sim.ftree[1]
-        out[pre + "nc"] = sim.nc
+        out[pre + "nc"] = sim.nc.copy()
         out[pre + "nbsum"] = np.array([np.sort(sim.nb[i, :sim.nc[i] - 1]).astype(np.uint64).sum() for i in range(sim.n)],
                                       np.uint64)
         out[pre + "dt"] = np.float64(sim.minDt)
         for k in ("x", "y", "z", "h", "vx", "vy", "vz", "temp", "alpha", "xm", "kx", "gradh", "prho", "c", "c11",
                   "c12", "c13", "c22", "c23", "c33", "divv", "curlv", "ax", "ay", "az", "du"):
-            out[pre + k] = sim.f[k]
+            out[pre + k] = sim.f[k].copy()
     np.savez_compressed(os.path.join(HERE, "sedov12_steps.npz"), **out)
 
 

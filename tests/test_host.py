@@ -1,0 +1,128 @@
+"""CPU tests of the host-side logic: IC formulas, SFC assignment, halo layout, and a world_size-2 gloo run of the
+multi-rank bookkeeping (counts all-reduce -> identical assignment on every rank -> migration counts)."""
+import math
+import os
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_sedov_ic_formulas(pkg):
+    """sedov_init.hpp:48-92, sedov_constants.hpp:11-21, grid.hpp:102-131"""
+    f, box, s = pkg.ic.sedov(50)
+    n = 125000
+    assert f["x"].size == n
+    assert abs(f["h"][0] - 0.5 * np.cbrt(3 / (4 * math.pi) * 100 / n)) < 1e-16
+    assert abs(f["h"][0] - 0.02879) < 1e-5
+    assert f["m"][0] == 1.0 / n
+    assert f["x"][0] == -0.5 + 0.5 / 50 and f["x"][1] == -0.5 + 0.5 / 50 + 1.0 / 50
+    assert f["y"][49] == f["y"][0] and f["y"][50] != f["y"][0]      # x fastest
+    cv = 8.317e7 / 10.0 / (5.0 / 3.0 - 1.0)
+    ener0 = 1.0 / math.pi ** 1.5 / 0.1 ** 3
+    r2 = f["x"] ** 2 + f["y"] ** 2 + f["z"] ** 2
+    assert np.allclose(f["temp"], (ener0 * np.exp(-r2 / 0.01) + 1e-8) / cv, rtol=1e-14)
+    assert box == ([-0.5, 0.5] * 3, [1, 1, 1]) and s["minDt"] == 1e-6
+    # a rank's slab equals the corresponding slice of the global IC
+    g, _, _ = pkg.ic.sedov_range(50, 1000, 5000)
+    for k in f:
+        assert np.array_equal(g[k], f[k][1000:5000]), k
+
+
+def test_other_ics_are_seeded_and_inside_box(pkg):
+    for case, side in (("noh", 20), ("turbulence", 16), ("kh", 32)):
+        a, box, s = pkg.ic.CASES[case](side)
+        b, _, _ = pkg.ic.CASES[case](side)
+        for k in a:
+            assert np.array_equal(a[k], b[k]), (case, k)
+        for d, k in enumerate("xyz"):
+            assert a[k].min() >= box[0][2 * d] and a[k].max() <= box[0][2 * d + 1]
+        assert len({v.size for v in a.values()}) == 1
+    noh, _, _ = pkg.ic.noh(20)
+    r = np.sqrt(noh["x"] ** 2 + noh["y"] ** 2 + noh["z"] ** 2)
+    assert r.max() <= 0.5
+    assert np.allclose(noh["vx"] * noh["x"] + noh["vy"] * noh["y"] + noh["vz"] * noh["z"], -r, atol=1e-6)
+
+
+def test_uniform_bins_and_assignment(pkg):
+    """uniformBins / makeSfcAssignment (domaindecomp.hpp:49-125), cases of unit/domain/domaindecomp.cpp"""
+    from sph_exa_b200 import dist as D
+    bins, cnt = D.uniform_bins([4, 3, 4, 3, 4, 3, 4, 3, 4, 3], 2)
+    assert list(bins) == [0, 5, 10] and list(cnt) == [18, 17]
+    bins, cnt = D.uniform_bins([1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1], 4)
+    assert list(bins) == [0, 4, 8, 12, 16] and list(cnt) == [4, 4, 4, 4]
+    leaves = (np.arange(9, dtype=np.uint64) << np.uint64(60))
+    b, c = D.make_sfc_assignment(2, [10, 0, 0, 0, 0, 0, 0, 30], leaves)
+    assert b[0] == 0 and b[-1] == leaves[-1] and c.sum() == 40
+    assert list(D.key_splits(np.array([1, 5, 9, 13], np.uint64), np.array([0, 6, 20], np.uint64))) == [0, 2, 4]
+
+
+def test_halo_layout(pkg):
+    from sph_exa_b200 import dist as D
+    assert D.halo_layout(0, 10, [0, 4, 2]) == (0, 10, 16, [-1, 10, 14])
+    assert D.halo_layout(1, 10, [3, 0, 2]) == (3, 13, 15, [0, -1, 13])
+    assert D.halo_layout(2, 10, [3, 4, 0]) == (7, 17, 17, [0, 3, -1])
+    assert D.partition_range(10, 0, 3) == (0, 4) and D.partition_range(10, 2, 3) == (7, 10)
+
+
+def _gloo_worker(rank, world, port, q):
+    import torch
+    import torch.distributed as dist
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import sphexa_b200_loader
+    pkg = sphexa_b200_loader.load()
+    from sph_exa_b200 import dist as D
+    from oracle import orc
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    # each rank holds a slab of a Sedov lattice; global tree counts are summed over ranks (update_mpi.hpp:81-104)
+    f, box, _ = pkg.ic.sedov(16)
+    n = f["x"].size
+    a, b = D.partition_range(n, rank, world)
+    keys, _ = orc.sort_by_key(orc.sfc_keys(f["x"][a:b], f["y"][a:b], f["z"][a:b], box))
+    all_keys, _ = orc.sort_by_key(orc.sfc_keys(f["x"], f["y"], f["z"], box))
+    leaves, gcounts, _ = orc.compute_octree(all_keys, 64)
+    local = orc.lib() and np.zeros(gcounts.size, np.uint32)
+    orc.lib().orc_node_counts(orc.P(leaves), gcounts.size, orc.P(keys), __import__("ctypes").c_size_t(keys.size),
+                              orc.P(local))
+    t = torch.from_numpy(local.astype(np.int64))
+    dist.all_reduce(t)
+    assert np.array_equal(t.numpy(), gcounts.astype(np.int64)), "summed local counts != global counts"
+    bounds, bc = D.make_sfc_assignment(world, t.numpy(), leaves)
+    splits = D.key_splits(keys, bounds)
+    send = torch.tensor([int(splits[q + 1] - splits[q]) for q in range(world)])
+    recv = torch.empty_like(send)
+    dist.all_to_all_single(recv, send) if dist.get_backend() != "gloo" else None
+    gathered = [torch.empty_like(send) for _ in range(world)]
+    dist.all_gather(gathered, send)
+    recv = torch.stack(gathered)[:, rank]
+    # after migration every rank owns exactly the particles of its key range
+    own = int(recv.sum())
+    want = int(np.searchsorted(all_keys, bounds[rank + 1]) - np.searchsorted(all_keys, bounds[rank]))
+    start, end, total, off = D.halo_layout(rank, own, [0] * world)
+    q.put((rank, own, want, int(bc[rank]), (start, end, total)))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_rank_bookkeeping_gloo(pkg):
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29600 + os.getpid() % 300
+    procs = [ctx.Process(target=_gloo_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=180) for _ in range(2))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    total = 0
+    for rank, own, want, assigned, lay in res:
+        assert own == want == assigned
+        assert lay == (0, own, own)
+        total += own
+    assert total == 16 ** 3
