@@ -1,0 +1,206 @@
+/*! @file C++20 host shim over the C ABI (include/sphexa_b200.h).
+ *
+ * Mirrors the reference's boundary for the hot path so that front-end code written against
+ * cstone::Domain<KeyType,T,GpuTag> (domain/include/cstone/domain/domain.hpp:65-683) and
+ * sphexa::HydroVeProp (main/src/propagator/ve_hydro.hpp:54-219) reads the same:
+ *
+ *   sphb200::host::HydroVeProp prop(ctx, cfg);      // propagatorFactory("ve"), factory.hpp:52
+ *   prop.upload(n, hostFields);                     // transferAllocatedToDevice, sphexa.cpp:122
+ *   prop.sync(); prop.computeForces(); prop.integrate();
+ *   prop.startIndex(); prop.endIndex(); prop.nParticlesWithHalos();   // domain.hpp:382-429
+ *
+ * Error behaviour: every non-zero C status becomes std::runtime_error carrying sphb200_last_error(),
+ * like the reference's throws (domain.hpp:110,449; xmass_gpu.cu:126-127).
+ */
+#pragma once
+
+#include <stdexcept>
+#include <string>
+#include <array>
+#include <utility>
+
+#include "sphexa_b200.h"
+
+namespace sphb200::host
+{
+
+inline void check(int rc)
+{
+    if (rc != 0) { throw std::runtime_error(sphb200_last_error()); }
+}
+
+//! @brief cstone::Box<double> twin (sfc/box.hpp:111-191)
+struct Box : sphb200_box
+{
+    Box(double xmin, double xmax, double ymin, double ymax, double zmin, double zmax, int bx = SPHB200_OPEN,
+        int by = SPHB200_OPEN, int bz = SPHB200_OPEN)
+    {
+        const double l[6] = {xmin, xmax, ymin, ymax, zmin, zmax};
+        const int b[3]    = {bx, by, bz};
+        sphb200_make_box(l, b, this);
+    }
+    Box(double lo, double hi, int b = SPHB200_OPEN)
+        : Box(lo, hi, lo, hi, lo, hi, b, b, b)
+    {
+    }
+    double xmin() const { return lim[0]; }
+    double xmax() const { return lim[1]; }
+    double lx() const { return len[0]; }
+    double ilx() const { return inv[0]; }
+};
+
+class Context
+{
+public:
+    explicit Context(int device = 0, void* stream = SPHB200_PRIVATE_STREAM) { check(sphb200_create(device, stream, &ctx_)); }
+    ~Context() { sphb200_destroy(ctx_); }
+    Context(const Context&)            = delete;
+    Context& operator=(const Context&) = delete;
+    sphb200_ctx* get() const { return ctx_; }
+    void sync() const { check(sphb200_sync(ctx_)); }
+    uint64_t launches() const { return sphb200_launch_count(ctx_); }
+
+private:
+    sphb200_ctx* ctx_{nullptr};
+};
+
+// ---- operator level: same names as the reference's extern GPU functions -------------------------------------------
+
+//! @brief cstone::computeSfcKeysGpu (sfc/sfc_gpu.h:39)
+inline void computeSfcKeysGpu(const Context& c, const double* x, const double* y, const double* z, uint64_t* keys,
+                              size_t n, const Box& box)
+{
+    check(sphb200_sfc_keys(c.get(), x, y, z, n, &box, keys));
+}
+
+//! @brief cstone::sortByKeyGpu with a sequence payload (primitives_gpu.h:87-111)
+inline void sortByKeyGpu(const Context& c, uint64_t* keys, uint32_t* ordering, size_t n)
+{
+    check(sphb200_sort_by_key(c.get(), keys, ordering, n));
+}
+
+//! @brief cstone::computeNodeCountsGpu (tree/csarray_gpu.h:56)
+inline void computeNodeCountsGpu(const Context& c, const uint64_t* tree, uint32_t* counts, int numNodes,
+                                 const uint64_t* keys, size_t n)
+{
+    check(sphb200_node_counts(c.get(), tree, numNodes, keys, n, counts));
+}
+
+//! @brief cstone::updateOctreeGpu (tree/update_gpu.cuh:58-82); returns converged
+inline bool updateOctreeGpu(const Context& c, const uint64_t* keys, size_t n, unsigned bucketSize, uint64_t* tree,
+                            uint32_t* counts, int capacity, int& numLeaves)
+{
+    int conv = 0;
+    check(sphb200_update_octree(c.get(), keys, n, bucketSize, tree, counts, capacity, &numLeaves, &conv));
+    return conv != 0;
+}
+
+//! @brief cstone::buildOctreeGpu (tree/octree_gpu.h:50)
+inline void buildOctreeGpu(const Context& c, const uint64_t* leaves, int numLeaves, uint64_t* prefixes,
+                           int32_t* childOffsets, int32_t* parents, int32_t* levelRange, int32_t* internalToLeaf,
+                           int32_t* leafToInternal)
+{
+    check(sphb200_build_octree(c.get(), leaves, numLeaves, prefixes, childOffsets, parents, levelRange, internalToLeaf,
+                               leafToInternal));
+}
+
+//! @brief sph::computeXMass ... computeMomentumEnergy (sph/sph_gpu.hpp:13-82) on [first,last)
+struct Hydro
+{
+    const Context& c;
+    int dtype;
+    const Box& box;
+    sphb200_hydro_const hc;
+    const uint32_t* neighbors;
+
+    void computeXMass(uint32_t first, uint32_t last, const sphb200_fields& d) const
+    {
+        check(sphb200_xmass(c.get(), dtype, first, last, &box, &hc, neighbors, &d));
+    }
+    void computeVeDefGradh(uint32_t first, uint32_t last, const sphb200_fields& d) const
+    {
+        check(sphb200_ve_def_gradh(c.get(), dtype, first, last, &box, &hc, neighbors, &d));
+    }
+    void computeEOS(uint32_t first, uint32_t last, const sphb200_fields& d) const
+    {
+        check(sphb200_eos(c.get(), dtype, first, last, &hc, &d));
+    }
+    void computeIadDivvCurlv(uint32_t first, uint32_t last, const sphb200_fields& d) const
+    {
+        check(sphb200_iad_divv_curlv(c.get(), dtype, first, last, &box, &hc, neighbors, &d));
+    }
+    void computeAVswitches(uint32_t first, uint32_t last, const sphb200_fields& d) const
+    {
+        check(sphb200_av_switches(c.get(), dtype, first, last, &box, &hc, neighbors, &d));
+    }
+    double computeMomentumEnergy(uint32_t first, uint32_t last, const sphb200_fields& d) const
+    {
+        double dt = 0;
+        check(sphb200_momentum_energy(c.get(), dtype, first, last, &box, &hc, neighbors, &d, &dt));
+        return dt;
+    }
+};
+
+// ---- propagator level -------------------------------------------------------------------------------------------------
+
+//! @brief sphexa::HydroVeProp + cstone::Domain for one rank; owns the device state
+class HydroVeProp
+{
+public:
+    HydroVeProp(const Context& c, const sphb200_sim_config& cfg)
+        : ctx_(c)
+    {
+        check(sphb200_sim_create(c.get(), &cfg, &sim_));
+    }
+    ~HydroVeProp() { sphb200_sim_destroy(sim_); }
+    HydroVeProp(const HydroVeProp&)            = delete;
+    HydroVeProp& operator=(const HydroVeProp&) = delete;
+
+    void upload(size_t n, const sphb200_fields& host) { check(sphb200_sim_upload(sim_, n, &host)); }
+    void download(const sphb200_fields& host, uint64_t* keys = nullptr) { check(sphb200_sim_download(sim_, &host, keys)); }
+
+    //! @brief Propagator::sync -> Domain::sync (ve_hydro.hpp:116-130)
+    void sync() { check(sphb200_sim_sync(sim_)); }
+    //! @brief Propagator::computeForces (ve_hydro.hpp:132-205)
+    void computeForces()
+    {
+        sync();
+        check(sphb200_sim_compute_forces(sim_));
+    }
+    //! @brief Propagator::integrate (ve_hydro.hpp:207-217); globalMinDt < 0: single rank
+    void integrate(double globalMinDt = -1.0) { check(sphb200_sim_integrate(sim_, globalMinDt)); }
+
+    // cstone::Domain getters (domain.hpp:382-429)
+    uint32_t startIndex() const { return sphb200_sim_start_index(sim_); }
+    uint32_t endIndex() const { return sphb200_sim_end_index(sim_); }
+    uint32_t nParticles() const { return endIndex() - startIndex(); }
+    uint32_t nParticlesWithHalos() const { return sphb200_sim_n_with_halos(sim_); }
+    Box box() const
+    {
+        sphb200_box b;
+        sphb200_sim_get_box(sim_, &b);
+        return Box(b.lim[0], b.lim[1], b.lim[2], b.lim[3], b.lim[4], b.lim[5], b.bc[0], b.bc[1], b.bc[2]);
+    }
+    sphb200_tree_view octreeProperties() const
+    {
+        sphb200_tree_view t;
+        check(sphb200_sim_tree(sim_, &t));
+        return t;
+    }
+    double minDt() const { return sphb200_sim_min_dt(sim_); }
+    double ttot() const { return sphb200_sim_ttot(sim_); }
+    uint64_t totalNeighbors() { return sphb200_sim_total_neighbors(sim_); }
+    //! @brief the "# name: t" lines of ipropagator.hpp:100-128, in ms
+    std::array<float, 9> phaseTimes()
+    {
+        std::array<float, 9> t{};
+        check(sphb200_sim_phase_times(sim_, t.data()));
+        return t;
+    }
+
+private:
+    const Context& ctx_;
+    sphb200_sim* sim_{nullptr};
+};
+
+} // namespace sphb200::host
