@@ -78,6 +78,7 @@ typedef struct sphb200_fields
     double* du;
     uint32_t* nc;                               /* neighbor count + 1 (self), indexed by particle index */
     void *dV11, *dV12, *dV13, *dV22, *dV23, *dV33; /* only with avClean, else NULL */
+    size_t n; /* length of every array (owned + halo particles); neighbor indices are < n */
 } sphb200_fields;
 
 /* physics constants, mirrors the scalar members of sph::ParticlesData
@@ -192,6 +193,12 @@ int sphb200_timestep(sphb200_ctx*, int dtype, uint32_t first, uint32_t last, con
                      const sphb200_fields* f_h, double* out_h);
 /* device address of the 3 doubles above, for an in-stream ncclAllReduce(min) */
 double* sphb200_timestep_device_ptr(sphb200_ctx*);
+
+/* The pair operators gather neighbor data from packed copies ("gather records") of the field arrays kept in the
+ * context.  Stand-alone operator calls repack on every call; a sphb200_sim reuses them across operators and
+ * invalidates them itself.  Call this after writing to a sim's device arrays obtained through sphb200_sim_fields()
+ * at a later time than the getter call itself. */
+void sphb200_invalidate_records(sphb200_ctx*);
 
 /* ---- a21: computePositionsGpu + updateSmoothingLengthGpu (positions_gpu.cu:119-192, update_h_gpu.cu:40-62) ---- */
 int sphb200_positions_update_h(sphb200_ctx*, int dtype, uint32_t first, uint32_t last, const sphb200_box* box_h,

@@ -8,7 +8,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libsphexa_b200.so")
+LIB_PATH = os.environ.get("SPHB200_LIB") or os.path.join(_HERE, "libsphexa_b200.so")
 
 F64, MIXED = 0, 1
 OPEN, PERIODIC, FIXED = 0, 1, 2
@@ -40,7 +40,8 @@ ALWAYS_F64 = {"x", "y", "z", "temp", "du"}
 
 
 class Fields(C.Structure):
-    _fields_ = [(n, vp) for n in FIELD_NAMES]
+    # n: length of every array (owned + halos); the pair operators pack gather records over [0, n)
+    _fields_ = [(n, vp) for n in FIELD_NAMES] + [("n", C.c_size_t)]
 
 
 class HydroConst(C.Structure):
@@ -58,7 +59,7 @@ class SimConfig(C.Structure):
 
 # every symbol include/sphexa_b200.h declares (checked by tests/test_abi.py)
 SYMBOLS = [
-    "sphb200_create", "sphb200_destroy", "sphb200_last_error", "sphb200_sync", "sphb200_launch_count",
+    "sphb200_create", "sphb200_destroy", "sphb200_invalidate_records", "sphb200_last_error", "sphb200_sync", "sphb200_launch_count",
     "sphb200_make_box", "sphb200_sfc_keys", "sphb200_minmax3", "sphb200_sort_by_key", "sphb200_gather",
     "sphb200_node_counts", "sphb200_update_octree", "sphb200_compute_octree", "sphb200_rebalance_decision",
     "sphb200_build_octree", "sphb200_node_centers", "sphb200_layout", "sphb200_neighbors_size",

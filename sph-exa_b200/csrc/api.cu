@@ -71,6 +71,10 @@ extern "C" void sphb200_destroy(sphb200_ctx* ctx)
     ctx->treeTmp.release();
     ctx->scanTmp.release();
     ctx->miscTmp.release();
+    for (auto& a : ctx->rec)
+        a.release();
+    ctx->tabPairs.release();
+    ctx->tabQuads.release();
     cudaFreeHost(ctx->hostScalars);
     cudaFree(ctx->devScalars);
     cudaFree(ctx->devDt);
@@ -234,6 +238,7 @@ struct sphb200_sim
         std::memset(&f, 0, sizeof(f));
         for (int id = 0; id < kNumFields; ++id)
             *fieldSlot(f, id) = field[id];
+        f.n = n;
         return f;
     }
 
@@ -277,6 +282,11 @@ extern "C" int sphb200_sim_create(sphb200_ctx* ctx, const sphb200_sim_config* cf
     if (cfg->hc.ng0 > cfg->hc.ngmax) throw std::runtime_error("ng0 should be smaller than ngmax\n"); // find_neighbors.hpp:52
     auto* s     = new sphb200_sim;
     s->ctx      = ctx;
+    // the sim owns the field arrays: gather records (hydro.cu) stay valid between operator calls and are
+    // invalidated below wherever a packed field is rewritten
+    ctx->packReuse = true;
+    ctx->packValid = 0;
+    ctx->tabValid  = false;
     s->cfg      = *cfg;
     s->capacity = cfg->capacity;
     s->box      = cfg->box;
@@ -329,6 +339,9 @@ extern "C" void sphb200_sim_destroy(sphb200_sim* s)
 {
     if (!s) return;
     cudaStreamSynchronize(s->ctx->stream);
+    s->ctx->packReuse = false;
+    s->ctx->packValid = 0;
+    s->ctx->tabValid  = false;
     for (auto p : s->field) cudaFree(p);
     for (auto p : s->fieldAlt) cudaFree(p);
     cudaFree(s->keys); cudaFree(s->perm); cudaFree(s->neighbors); cudaFree(s->wh); cudaFree(s->whd);
@@ -344,6 +357,7 @@ extern "C" int sphb200_sim_upload(sphb200_sim* s, size_t n, const sphb200_fields
 {
     SPHB200_TRY
     if (n > s->capacity) throw std::runtime_error("sim_upload: n exceeds capacity");
+    s->ctx->packValid = 0;
     sphb200_fields h = *host;
     for (int id = 0; id < kNumFields; ++id)
     {
@@ -396,6 +410,7 @@ extern "C" int sphb200_sim_sync(sphb200_sim* s)
 {
     SPHB200_TRY
     auto* ctx = s->ctx;
+    ctx->packValid = 0;
     s->mark(0);
     size_t numAssigned = s->end - s->start;
     auto* x = static_cast<double*>(s->field[F_x]) + s->start;
@@ -469,6 +484,7 @@ extern "C" int sphb200_sim_forces_phase(sphb200_sim* s, int phase)
         case 0:
             CHECK_RC(sphb200_find_neighbors(ctx, &tv, f.x, f.y, f.z, f.h, dt, a, b, &s->box, hc.ng0, hc.ngmax, 1,
                                             s->neighbors, f.nc + a, nullptr));
+            ctx->packValid = 0; // h changed
             s->mark(2);
             CHECK_RC(sphb200_xmass(ctx, dt, a, b, &s->box, &hc, s->neighbors, &f));
             s->mark(3);
@@ -568,6 +584,7 @@ extern "C" void sphb200_sim_set_dt(sphb200_sim* s, double minDt, double minDt_m1
 extern "C" int sphb200_sim_fields(sphb200_sim* s, sphb200_fields* out)
 {
     *out = s->table();
+    s->ctx->packValid = 0; // the caller may write through these pointers
     return 0;
 }
 
@@ -584,6 +601,7 @@ extern "C" int sphb200_sim_set_layout(sphb200_sim* s, uint32_t start, uint32_t e
     s->start = start;
     s->end   = end;
     s->n     = nWithHalos;
+    s->ctx->packValid = 0;
     SPHB200_CATCH
 }
 

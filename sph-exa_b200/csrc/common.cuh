@@ -71,6 +71,14 @@ struct sphb200_ctx
     bool ownStream       = false;
     uint64_t launches    = 0;
     sphb200::Arena sortTmp, treeTmp, scanTmp, miscTmp;
+    // gather records of the pair operators (hydro.cu) and the repacked kernel tables
+    static constexpr int kMaxRecs = 8;
+    sphb200::Arena rec[kMaxRecs], tabPairs, tabQuads;
+    uint32_t packValid = 0;    // bit k: rec[k] mirrors the current field arrays
+    bool packReuse     = false; // set by sphb200_sim: records stay valid across operator calls
+    bool tabValid      = false;
+    const void *tabWh = nullptr, *tabWhd = nullptr;
+    int tabElem = 0;
     // pinned host + device scalars
     int* hostScalars     = nullptr; // pinned, 64 ints
     int* devScalars      = nullptr; // 64 ints

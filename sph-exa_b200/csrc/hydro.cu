@@ -13,6 +13,10 @@ namespace sphb200
 {
 
 constexpr int kHydroBlock = 128;
+#ifndef SPHB200_MOMENTUM_MIN_BLOCKS
+#define SPHB200_MOMENTUM_MIN_BLOCKS 4
+#endif
+constexpr int kMomentumMinBlocks = SPHB200_MOMENTUM_MIN_BLOCKS;
 
 template<class T>
 struct F
@@ -90,11 +94,155 @@ __device__ __forceinline__ T lookup(const T* __restrict__ table, T v)
     return t0 + derivative * (v - T(idx) * dx);
 }
 
+// ---------------------------------------------------------------- gather records
+// The J-loops are bound by L1 gather throughput (one tag lookup per touched line, one data cycle per touched
+// sector), not by DRAM.  Each operator therefore first packs the neighbor-side fields it reads into 32-byte
+// (f64) / 16-byte (mixed) records with one streaming pass, so that a pair costs one 256-bit load per record instead
+// of four 64-bit loads that each touch their own lines:
+//   R0 {x, y, z, m}   R1 {vx, vy, vz, h}   R2 {xm, kx, c, prho}   R3 {c11, c12, c13, c22}   R4 {c23, c33, alpha, -}
+//   R5 {dV11, dV12, dV13, dV22}   R6 {dV23, dV33, -, -}   (avClean only)
+// The tabulated kernel is repacked the same way: entry idx holds {t[idx], t[idx+1]} (and for gradh the derivative
+// table's pair as well), so an interpolation is one load.  Values are copies, arithmetic is unchanged.
+template<class T>
+struct alignas(32) PosRec
+{
+    double x, y, z;
+    T m;
+};
+
+template<class T>
+struct alignas(4 * sizeof(T)) Rec4
+{
+    T a, b, c, d;
+};
+
+template<class T>
+struct alignas(2 * sizeof(T)) Rec2
+{
+    T a, b;
+};
+
+// __ldg has no overloads for user structs: go through the matching built-in vector types
+__device__ __forceinline__ Rec4<double> ldRec(const Rec4<double>* __restrict__ p, uint32_t j)
+{
+    Rec4<double> r;
+    asm("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(r.a), "=d"(r.b), "=d"(r.c), "=d"(r.d) : "l"(p + j));
+    return r;
+}
+__device__ __forceinline__ Rec4<float> ldRec(const Rec4<float>* __restrict__ p, uint32_t j)
+{
+    float4 v = __ldg(reinterpret_cast<const float4*>(p) + j);
+    return {v.x, v.y, v.z, v.w};
+}
+__device__ __forceinline__ Rec2<double> ldRec(const Rec2<double>* __restrict__ p, uint32_t j)
+{
+    double2 v = __ldg(reinterpret_cast<const double2*>(p) + j);
+    return {v.x, v.y};
+}
+__device__ __forceinline__ Rec2<float> ldRec(const Rec2<float>* __restrict__ p, uint32_t j)
+{
+    float2 v = __ldg(reinterpret_cast<const float2*>(p) + j);
+    return {v.x, v.y};
+}
+__device__ __forceinline__ PosRec<double> ldRec(const PosRec<double>* __restrict__ p, uint32_t j)
+{
+    PosRec<double> r;
+    asm("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(r.x), "=d"(r.y), "=d"(r.z), "=d"(r.m) : "l"(p + j));
+    return r;
+}
+__device__ __forceinline__ PosRec<float> ldRec(const PosRec<float>* __restrict__ p, uint32_t j)
+{
+    PosRec<float> r;
+    double w;
+    asm("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(r.x), "=d"(r.y), "=d"(r.z), "=d"(w) : "l"(p + j));
+    r.m = __int_as_float(__double2loint(w));
+    return r;
+}
+//! @brief first half of a Rec4 (for operators that need only {a, b})
+template<class T>
+__device__ __forceinline__ Rec2<T> ldHalf(const Rec4<T>* __restrict__ p, uint32_t j)
+{
+    return ldRec(reinterpret_cast<const Rec2<T>*>(p + j), 0);
+}
+
+template<class T>
+__global__ void __launch_bounds__(256) packPosKernel(size_t n, const double* __restrict__ x,
+                                                     const double* __restrict__ y, const double* __restrict__ z,
+                                                     const T* __restrict__ m, PosRec<T>* __restrict__ out)
+{
+    size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    PosRec<T> r;
+    r.x = x[i]; r.y = y[i]; r.z = z[i]; r.m = m[i];
+    out[i] = r;
+}
+
+template<class T>
+__global__ void __launch_bounds__(256) pack4Kernel(size_t n, const T* __restrict__ a, const T* __restrict__ b,
+                                                   const T* __restrict__ c, const T* __restrict__ d,
+                                                   Rec4<T>* __restrict__ out)
+{
+    size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Rec4<T> r;
+    r.a = a ? a[i] : T(0); r.b = b ? b[i] : T(0); r.c = c ? c[i] : T(0); r.d = d ? d[i] : T(0);
+    out[i] = r;
+}
+
+//! @brief out[idx] = {wh[idx], wh[idx+1], whd[idx], whd[idx+1]}
+template<class T>
+__global__ void packTableKernel(const T* __restrict__ wh, const T* __restrict__ whd, Rec2<T>* __restrict__ pairs,
+                                Rec4<T>* __restrict__ quads)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= kTableSize) return;
+    int i1 = min(i + 1, kTableSize - 1);
+    pairs[i] = {wh[i], wh[i1]};
+    if (whd) quads[i] = {wh[i], wh[i1], whd[i], whd[i1]};
+}
+
+//! @brief tabulated kernel with linear interpolation, sph::lt::lookup (sph/table_lookup.hpp:13-25)
+template<class T>
+__device__ __forceinline__ T lookup(const Rec2<T>* __restrict__ table, T v)
+{
+    constexpr int numIntervals = kTableSize - 1;
+    constexpr T support        = 2.0;
+    constexpr T dx             = support / numIntervals;
+    constexpr T invDx          = T(1) / dx;
+
+    int idx = v * invDx;
+    if (idx >= numIntervals) return T(0);
+    Rec2<T> t    = ldRec(table, idx);
+    T derivative = (t.b - t.a) * invDx;
+    return t.a + derivative * (v - T(idx) * dx);
+}
+
+//! @brief both tables at the same abscissa (wh and whd), one load
+template<class T>
+__device__ __forceinline__ void lookup2(const Rec4<T>* __restrict__ table, T v, T& w, T& dw)
+{
+    constexpr int numIntervals = kTableSize - 1;
+    constexpr T support        = 2.0;
+    constexpr T dx             = support / numIntervals;
+    constexpr T invDx          = T(1) / dx;
+
+    int idx = v * invDx;
+    w = dw = T(0);
+    if (idx >= numIntervals) return;
+    Rec4<T> t = ldRec(table, idx);
+    T frac    = v - T(idx) * dx;
+    w         = t.a + (t.b - t.a) * invDx * frac;
+    dw        = t.c + (t.d - t.c) * invDx * frac;
+}
+
+#define LD(p, j) __ldg((p) + (j))
+
 struct NbList
 {
     const uint32_t* base; // entry k at base[k * 32]
     unsigned count;
-    __device__ __forceinline__ uint32_t operator[](unsigned k) const { return __ldg(base + size_t(k) * 32); }
+    // lists are streamed exactly once per operator: keep them out of L1 so the gathered records stay resident
+    __device__ __forceinline__ uint32_t operator[](unsigned k) const { return __ldcs(base + size_t(k) * 32); }
 };
 
 __device__ __forceinline__ NbList nbList(const uint32_t* nidx, const uint32_t* nc, uint32_t first, uint32_t i,
@@ -107,33 +255,39 @@ __device__ __forceinline__ NbList nbList(const uint32_t* nidx, const uint32_t* n
     return l;
 }
 
-#define LD(p, j) __ldg((p) + (j))
+//! @brief J-loop with the next index fetched one iteration ahead (hides the list-load latency behind the pair math)
+#define FOR_NEIGHBORS(nb, j)                                                                                          \
+    uint32_t j##_next = (nb).count ? (nb)[0] : 0u;                                                                    \
+    for (unsigned pj = 0, j = j##_next; pj < (nb).count;                                                             \
+         ++pj, j = j##_next)                                                                                          \
+        if (j##_next = (pj + 1 < (nb).count) ? (nb)[pj + 1] : 0u, true)
 
 // ---------------------------------------------------------------- XMass (xmass_kern.hpp:50-78)
 template<class T>
 __global__ void __launch_bounds__(kHydroBlock)
     xmassKernel(uint32_t first, uint32_t last, unsigned ngmax, double K, PbcBox box, const uint32_t* __restrict__ nidx,
-                F<T> f, const T* __restrict__ wh)
+                F<T> f, const PosRec<T>* __restrict__ r0, const Rec2<T>* __restrict__ wh)
 {
     uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= last) return;
     NbList nb = nbList(nidx, f.nc, first, i, ngmax);
 
-    double xi = f.x[i], yi = f.y[i], zi = f.z[i];
-    T hi = f.h[i], mi = f.m[i];
+    PosRec<T> pi = r0[i];
+    double xi = pi.x, yi = pi.y, zi = pi.z;
+    T hi = f.h[i], mi = pi.m;
     T hInv  = 1.0 / hi;
     T h3Inv = hInv * hInv * hInv;
 
     T rho0i = mi;
-    for (unsigned pj = 0; pj < nb.count; ++pj)
+    FOR_NEIGHBORS(nb, j)
     {
-        uint32_t j = nb[pj];
-        T xx = xi - LD(f.x, j), yy = yi - LD(f.y, j), zz = zi - LD(f.z, j);
+        PosRec<T> pj_ = ldRec(r0, j);
+        T xx = xi - pj_.x, yy = yi - pj_.y, zz = zi - pj_.z;
         applyPBC(box, T(2) * hi, xx, yy, zz);
         T dist = sqrt(xx * xx + yy * yy + zz * zz);
         T vloc = dist * hInv;
         T w    = lookup(wh, vloc);
-        rho0i += w * LD(f.m, j);
+        rho0i += w * pj_.m;
     }
     f.xm[i] = T(mi / (rho0i * K * h3Inv));
 }
@@ -142,14 +296,16 @@ __global__ void __launch_bounds__(kHydroBlock)
 template<class T>
 __global__ void __launch_bounds__(kHydroBlock)
     veDefGradhKernel(uint32_t first, uint32_t last, unsigned ngmax, double K, PbcBox box,
-                     const uint32_t* __restrict__ nidx, F<T> f, const T* __restrict__ wh, const T* __restrict__ whd)
+                     const uint32_t* __restrict__ nidx, F<T> f, const PosRec<T>* __restrict__ r0,
+                     const Rec4<T>* __restrict__ whq)
 {
     uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= last) return;
     NbList nb = nbList(nidx, f.nc, first, i, ngmax);
 
-    double xi = f.x[i], yi = f.y[i], zi = f.z[i];
-    T hi = f.h[i], mi = f.m[i], xmassi = f.xm[i];
+    PosRec<T> pi = r0[i];
+    double xi = pi.x, yi = pi.y, zi = pi.z;
+    T hi = f.h[i], mi = pi.m, xmassi = f.xm[i];
     T hInv  = T(1) / hi;
     T h3Inv = hInv * hInv * hInv;
 
@@ -157,21 +313,21 @@ __global__ void __launch_bounds__(kHydroBlock)
     T whomegai = -T(3) * xmassi;
     T wrho0i   = -T(3) * mi;
 
-    for (unsigned pj = 0; pj < nb.count; ++pj)
+    FOR_NEIGHBORS(nb, j)
     {
-        uint32_t j = nb[pj];
-        T xx = xi - LD(f.x, j), yy = yi - LD(f.y, j), zz = zi - LD(f.z, j);
-        applyPBC(box, T(2) * hi, xx, yy, zz);
-        T dist   = sqrt(xx * xx + yy * yy + zz * zz);
-        T vloc   = dist * hInv;
-        T w      = lookup(wh, vloc);
-        T dw     = lookup(whd, vloc);
-        T dterh  = -(T(3) * w + vloc * dw);
+        PosRec<T> pj_ = ldRec(r0, j);
         T xmassj = LD(f.xm, j);
+        T xx = xi - pj_.x, yy = yi - pj_.y, zz = zi - pj_.z;
+        applyPBC(box, T(2) * hi, xx, yy, zz);
+        T dist = sqrt(xx * xx + yy * yy + zz * zz);
+        T vloc = dist * hInv;
+        T w, dw;
+        lookup2(whq, vloc, w, dw);
+        T dterh = -(T(3) * w + vloc * dw);
 
         kxi += w * xmassj;
         whomegai += dterh * xmassj;
-        wrho0i += dterh * LD(f.m, j);
+        wrho0i += dterh * pj_.m;
     }
 
     // compound assignments exactly as ve_def_gradh_kern.hpp:78-80 (right-hand side evaluated first, K is Tc)
@@ -205,29 +361,39 @@ __global__ void eosKernel(uint32_t first, uint32_t last, F<T> f, T muiConst, dou
 }
 
 // ---------------------------------------------------------------- IAD + divv/curlv (iad_kern.hpp:43-109, divv_curlv_kern.hpp:44-123)
+// One sweep: besides tau_ab = sum_j r_a r_b V_j W the sweep accumulates S_ab = sum_j (v_ji,a xm_j) W r_b; the
+// velocity gradient of divv_curlv_kern.hpp, dV_a[b] = sum_j (v_ji,a xm_j) * (-(C_i r)_b W), equals -(C_i S_a)_b
+// because C_i does not depend on j.  Same sums in the same order, C_i applied after instead of inside the loop.
 template<class T>
 __global__ void __launch_bounds__(kHydroBlock)
     iadDivvCurlvKernel(uint32_t first, uint32_t last, unsigned ngmax, double K, PbcBox box,
-                       const uint32_t* __restrict__ nidx, F<T> f, const T* __restrict__ wh, bool doGradV)
+                       const uint32_t* __restrict__ nidx, F<T> f, const PosRec<T>* __restrict__ r0,
+                       const Rec4<T>* __restrict__ r1, const Rec4<T>* __restrict__ r2,
+                       const Rec2<T>* __restrict__ wh, bool doGradV)
 {
     uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= last) return;
     NbList nb = nbList(nidx, f.nc, first, i, ngmax);
 
-    double xi = f.x[i], yi = f.y[i], zi = f.z[i];
-    T hi    = f.h[i];
+    PosRec<T> pi = r0[i];
+    Rec4<T> vi   = r1[i];
+    double xi = pi.x, yi = pi.y, zi = pi.z;
+    T vxi = vi.a, vyi = vi.b, vzi = vi.c, hi = vi.d;
     T hiInv = T(1) / hi;
 
     T tau11 = 0.0, tau12 = 0.0, tau13 = 0.0, tau22 = 0.0, tau23 = 0.0, tau33 = 0.0;
-    for (unsigned pj = 0; pj < nb.count; ++pj)
+    T Sx[3] = {0, 0, 0}, Sy[3] = {0, 0, 0}, Sz[3] = {0, 0, 0};
+    FOR_NEIGHBORS(nb, j)
     {
-        uint32_t j = nb[pj];
-        T rx = xi - LD(f.x, j), ry = yi - LD(f.y, j), rz = zi - LD(f.z, j);
+        PosRec<T> pj_ = ldRec(r0, j);
+        Rec4<T> vj    = ldRec(r1, j);
+        Rec2<T> xk    = ldHalf(r2, j); // {xm_j, kx_j}
+        T rx = xi - pj_.x, ry = yi - pj_.y, rz = zi - pj_.z;
         applyPBC(box, T(2) * hi, rx, ry, rz);
         T dist   = sqrt(rx * rx + ry * ry + rz * rz);
         T vloc   = dist * hiInv;
         T w      = lookup(wh, vloc);
-        T volj_w = LD(f.xm, j) / LD(f.kx, j) * w;
+        T volj_w = xk.a / xk.b * w;
 
         tau11 += rx * rx * volj_w;
         tau12 += rx * ry * volj_w;
@@ -235,6 +401,12 @@ __global__ void __launch_bounds__(kHydroBlock)
         tau22 += ry * ry * volj_w;
         tau23 += ry * rz * volj_w;
         tau33 += rz * rz * volj_w;
+
+        T wx = w * rx, wy = w * ry, wz = w * rz;
+        T sx = (vj.a - vxi) * xk.a, sy = (vj.b - vyi) * xk.a, sz = (vj.c - vzi) * xk.a;
+        Sx[0] += sx * wx; Sx[1] += sx * wy; Sx[2] += sx * wz;
+        Sy[0] += sy * wx; Sy[1] += sy * wy; Sy[2] += sy * wz;
+        Sz[0] += sz * wx; Sz[1] += sz * wy; Sz[2] += sz * wz;
     }
 
     auto getExp = [](T val) { return (val == T(0) ? 0 : ilogb(val)); };
@@ -260,36 +432,20 @@ __global__ void __launch_bounds__(kHydroBlock)
     T c33i = (tau11 * tau22 - tau12 * tau12) * factor;
     f.c11[i] = c11i; f.c12[i] = c12i; f.c13[i] = c13i; f.c22[i] = c22i; f.c23[i] = c23i; f.c33[i] = c33i;
 
-    // second pass over the same list: velocity gradient
-    T vxi = f.vx[i], vyi = f.vy[i], vzi = f.vz[i], kxi = f.kx[i];
-    T hiInv3 = hiInv * hiInv * hiInv;
-    T dVx[3] = {0, 0, 0}, dVy[3] = {0, 0, 0}, dVz[3] = {0, 0, 0};
-    for (unsigned pj = 0; pj < nb.count; ++pj)
+    // dV_a[b] = -(C_i S_a)_b
+    T dVx[3], dVy[3], dVz[3];
+    auto applyC = [&](const T* S, T* dV)
     {
-        uint32_t j = nb[pj];
-        T rx = xi - LD(f.x, j), ry = yi - LD(f.y, j), rz = zi - LD(f.z, j);
-        applyPBC(box, T(2) * hi, rx, ry, rz);
-        T r2   = rx * rx + ry * ry + rz * rz;
-        T dist = sqrt(r2);
+        dV[0] = -(c11i * S[0] + c12i * S[1] + c13i * S[2]);
+        dV[1] = -(c12i * S[0] + c22i * S[1] + c23i * S[2]);
+        dV[2] = -(c13i * S[0] + c23i * S[1] + c33i * S[2]);
+    };
+    applyC(Sx, dVx);
+    applyC(Sy, dVy);
+    applyC(Sz, dVz);
 
-        T vx_ji = LD(f.vx, j) - vxi;
-        T vy_ji = LD(f.vy, j) - vyi;
-        T vz_ji = LD(f.vz, j) - vzi;
-
-        T v1 = dist * hiInv;
-        T Wi = lookup(wh, v1);
-
-        T tA0 = -(c11i * rx + c12i * ry + c13i * rz) * Wi;
-        T tA1 = -(c12i * rx + c22i * ry + c23i * rz) * Wi;
-        T tA2 = -(c13i * rx + c23i * ry + c33i * rz) * Wi;
-
-        T xmassj = LD(f.xm, j);
-        T sx = vx_ji * xmassj, sy = vy_ji * xmassj, sz = vz_ji * xmassj;
-        dVx[0] += sx * tA0; dVx[1] += sx * tA1; dVx[2] += sx * tA2;
-        dVy[0] += sy * tA0; dVy[1] += sy * tA1; dVy[2] += sy * tA2;
-        dVz[0] += sz * tA0; dVz[1] += sz * tA1; dVz[2] += sz * tA2;
-    }
-
+    T kxi      = f.kx[i];
+    T hiInv3   = hiInv * hiInv * hiInv;
     T norm_kxi = K * hiInv3 / kxi;
     f.divv[i]  = norm_kxi * (dVx[0] + dVy[1] + dVz[2]);
     if (f.curlv)
@@ -309,62 +465,69 @@ __global__ void __launch_bounds__(kHydroBlock)
 }
 
 // ---------------------------------------------------------------- AV switches (av_switches_kern.hpp:44-137)
+// graddivv_b = sum_j factor_j * (-(C_i r)_b K h^-3 W): C_i, K h^-3 are constant in j and applied after the sweep.
 template<class T>
 __global__ void __launch_bounds__(kHydroBlock)
     avSwitchesKernel(uint32_t first, uint32_t last, unsigned ngmax, double K, PbcBox box,
-                     const uint32_t* __restrict__ nidx, F<T> f, const T* __restrict__ wh, double dt, T alphamin,
-                     T alphamax, T decay_constant)
+                     const uint32_t* __restrict__ nidx, F<T> f, const PosRec<T>* __restrict__ r0,
+                     const Rec4<T>* __restrict__ r1, const Rec4<T>* __restrict__ r2, const Rec2<T>* __restrict__ wh,
+                     double dt, T alphamin, T alphamax, T decay_constant)
 {
     uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= last) return;
     NbList nb = nbList(nidx, f.nc, first, i, ngmax);
 
-    double xi = f.x[i], yi = f.y[i], zi = f.z[i];
-    T vxi = f.vx[i], vyi = f.vy[i], vzi = f.vz[i];
-    T hi = f.h[i], ci = f.c[i];
-    T c11i = f.c11[i], c12i = f.c12[i], c13i = f.c13[i], c22i = f.c22[i], c23i = f.c23[i], c33i = f.c33[i];
+    PosRec<T> pi = r0[i];
+    Rec4<T> vi   = r1[i];
+    double xi = pi.x, yi = pi.y, zi = pi.z;
+    T vxi = vi.a, vyi = vi.b, vzi = vi.c, hi = vi.d;
+    T ci = f.c[i];
 
     T vijsignal_i = T(1.e-40) * ci;
     T hiInv  = T(1) / hi;
     T hiInv3 = hiInv * hiInv * hiInv;
     T divv_i = f.divv[i];
-    T alpha_i = f.alpha[i];
 
-    T graddivv_x = 0.0, graddivv_y = 0.0, graddivv_z = 0.0;
-    for (unsigned pj = 0; pj < nb.count; ++pj)
+    T gx = 0.0, gy = 0.0, gz = 0.0;
+    FOR_NEIGHBORS(nb, j)
     {
-        uint32_t j = nb[pj];
-        T rx = xi - LD(f.x, j), ry = yi - LD(f.y, j), rz = zi - LD(f.z, j);
+        PosRec<T> pj_ = ldRec(r0, j);
+        Rec4<T> vj    = ldRec(r1, j);
+        Rec4<T> sj    = ldRec(r2, j); // {xm, kx, c, prho}
+        T divv_j      = LD(f.divv, j);
+        T rx = xi - pj_.x, ry = yi - pj_.y, rz = zi - pj_.z;
         applyPBC(box, T(2) * hi, rx, ry, rz);
-        T r2   = rx * rx + ry * ry + rz * rz;
-        T dist = sqrt(r2);
+        T r2_  = rx * rx + ry * ry + rz * rz;
+        T dist = sqrt(r2_);
 
-        T vx_ij = vxi - LD(f.vx, j);
-        T vy_ij = vyi - LD(f.vy, j);
-        T vz_ij = vzi - LD(f.vz, j);
+        T vx_ij = vxi - vj.a;
+        T vy_ij = vyi - vj.b;
+        T vz_ij = vzi - vj.c;
 
         T rv           = rx * vx_ij + ry * vy_ij + rz * vz_ij;
         T vijsignal_ij = 0.0;
-        if (rv < T(0)) { vijsignal_ij = ci + LD(f.c, j) - T(3) * rv / dist; }
+        if (rv < T(0)) { vijsignal_ij = ci + sj.c - T(3) * rv / dist; }
         vijsignal_i = max(vijsignal_i, vijsignal_ij);
 
         T v1 = dist * hiInv;
-        T Wi = K * hiInv3 * lookup(wh, v1);
+        T w  = lookup(wh, v1);
 
-        T termA1 = -(c11i * rx + c12i * ry + c13i * rz) * Wi;
-        T termA2 = -(c12i * rx + c22i * ry + c23i * rz) * Wi;
-        T termA3 = -(c13i * rx + c23i * ry + c33i * rz) * Wi;
+        T volj   = sj.a / sj.b;
+        T factor = volj * (divv_i - divv_j) * w;
 
-        T volj   = LD(f.xm, j) / LD(f.kx, j);
-        T factor = volj * (divv_i - LD(f.divv, j));
-
-        graddivv_x += factor * termA1;
-        graddivv_y += factor * termA2;
-        graddivv_z += factor * termA3;
+        gx += factor * rx;
+        gy += factor * ry;
+        gz += factor * rz;
     }
 
-    T graddivv = sqrt(graddivv_x * graddivv_x + graddivv_y * graddivv_y + graddivv_z * graddivv_z);
+    T c11i = f.c11[i], c12i = f.c12[i], c13i = f.c13[i], c22i = f.c22[i], c23i = f.c23[i], c33i = f.c33[i];
+    T Kh3        = K * hiInv3;
+    T graddivv_x = -(c11i * gx + c12i * gy + c13i * gz) * Kh3;
+    T graddivv_y = -(c12i * gx + c22i * gy + c23i * gz) * Kh3;
+    T graddivv_z = -(c13i * gx + c23i * gy + c33i * gz) * Kh3;
+    T graddivv   = sqrt(graddivv_x * graddivv_x + graddivv_y * graddivv_y + graddivv_z * graddivv_z);
 
+    T alpha_i  = f.alpha[i];
     T alphaloc = 0.0;
     if (divv_i < T(0))
     {
@@ -405,11 +568,18 @@ __device__ __forceinline__ T avRvCorrection(T rx, T ry, T rz, T eta_ab, T eta_cr
     return -phi_ab * (dmy1 + dmy2);
 }
 
+template<class T>
+struct MomRecs
+{
+    const PosRec<T>* r0;
+    const Rec4<T>*r1, *r2, *r3, *r4, *r5, *r6;
+};
+
 template<bool avClean, class T>
-__global__ void __launch_bounds__(kHydroBlock)
+__global__ void __launch_bounds__(kHydroBlock, kMomentumMinBlocks)
     momentumEnergyKernel(uint32_t first, uint32_t last, unsigned ngmax, double K, PbcBox box,
-                         const uint32_t* __restrict__ nidx, F<T> f, const T* __restrict__ wh, T Atmin, T Atmax, T ramp,
-                         float Kcour, unsigned long long* __restrict__ minDtKey)
+                         const uint32_t* __restrict__ nidx, F<T> f, MomRecs<T> rec, const Rec2<T>* __restrict__ wh,
+                         T Atmin, T Atmax, T ramp, float Kcour, unsigned long long* __restrict__ minDtKey)
 {
     uint32_t i  = first + blockIdx.x * blockDim.x + threadIdx.x;
     T dt_i      = INFINITY;
@@ -417,13 +587,14 @@ __global__ void __launch_bounds__(kHydroBlock)
     {
         NbList nb = nbList(nidx, f.nc, first, i, ngmax);
 
-        double xi = f.x[i], yi = f.y[i], zi = f.z[i];
-        T vxi = f.vx[i], vyi = f.vy[i], vzi = f.vz[i];
-        T hi = f.h[i], mi = f.m[i], ci = f.c[i], kxi = f.kx[i];
+        PosRec<T> pi = rec.r0[i];
+        Rec4<T> vi   = rec.r1[i];
+        Rec4<T> si   = rec.r2[i];
+        double xi = pi.x, yi = pi.y, zi = pi.z;
+        T vxi = vi.a, vyi = vi.b, vzi = vi.c, hi = vi.d;
+        T mi = pi.m, xmassi = si.a, kxi = si.b, ci = si.c, prhoi = si.d;
         T alpha_i = f.alpha[i];
-        T xmassi  = f.xm[i];
         T rhoi    = kxi * mi / xmassi;
-        T prhoi   = f.prho[i];
 
         T hiInv  = T(1) / hi;
         T hiInv3 = hiInv * hiInv * hiInv;
@@ -443,20 +614,24 @@ __global__ void __launch_bounds__(kHydroBlock)
 
         T eta_crit = cbrt(T(32) * M_PI / T(3) / T(nb.count + 1));
 
-        for (unsigned pj = 0; pj < nb.count; ++pj)
+        FOR_NEIGHBORS(nb, j)
         {
-            uint32_t j = nb[pj];
+            PosRec<T> pj_ = ldRec(rec.r0, j);
+            Rec4<T> vj    = ldRec(rec.r1, j);
+            Rec4<T> sj    = ldRec(rec.r2, j);
+            Rec4<T> ca    = ldRec(rec.r3, j);
+            Rec4<T> cb    = ldRec(rec.r4, j);
 
-            T rx = xi - LD(f.x, j), ry = yi - LD(f.y, j), rz = zi - LD(f.z, j);
-            T vxj = LD(f.vx, j), vyj = LD(f.vy, j), vzj = LD(f.vz, j);
+            T rx = xi - pj_.x, ry = yi - pj_.y, rz = zi - pj_.z;
+            T vxj = vj.a, vyj = vj.b, vzj = vj.c;
             applyPBC(box, T(2) * hi, rx, ry, rz);
 
-            T r2   = rx * rx + ry * ry + rz * rz;
-            T dist = sqrt(r2);
+            T r2_  = rx * rx + ry * ry + rz * rz;
+            T dist = sqrt(r2_);
 
             T vx_ij = vxi - vxj, vy_ij = vyi - vyj, vz_ij = vzi - vzj;
 
-            T hj    = LD(f.h, j);
+            T hj    = vj.d;
             T hjInv = T(1) / hj;
 
             T v1 = dist * hiInv;
@@ -470,20 +645,21 @@ __global__ void __launch_bounds__(kHydroBlock)
             T termA2_i = -(c12i * rx + c22i * ry + c23i * rz) * Wi;
             T termA3_i = -(c13i * rx + c23i * ry + c33i * rz) * Wi;
 
-            T c11j = LD(f.c11, j), c12j = LD(f.c12, j), c13j = LD(f.c13, j);
-            T c22j = LD(f.c22, j), c23j = LD(f.c23, j), c33j = LD(f.c33, j);
+            T c11j = ca.a, c12j = ca.b, c13j = ca.c, c22j = ca.d, c23j = cb.a, c33j = cb.b;
 
             T termA1_j = -(c11j * rx + c12j * ry + c13j * rz) * Wj;
             T termA2_j = -(c12j * rx + c22j * ry + c23j * rz) * Wj;
             T termA3_j = -(c13j * rx + c23j * ry + c33j * rz) * Wj;
 
-            T mj = LD(f.m, j), cj = LD(f.c, j), kxj = LD(f.kx, j), xmassj = LD(f.xm, j);
+            T mj = pj_.m, cj = sj.c, kxj = sj.b, xmassj = sj.a;
             T rhoj = kxj * mj / xmassj;
 
             T rv = rx * vx_ij + ry * vy_ij + rz * vz_ij;
             if (avClean)
             {
-                T gradV_j[6] = {LD(f.dV11, j), LD(f.dV12, j), LD(f.dV13, j), LD(f.dV22, j), LD(f.dV23, j), LD(f.dV33, j)};
+                Rec4<T> ga = ldRec(rec.r5, j);
+                Rec2<T> gb = ldHalf(rec.r6, j);
+                T gradV_j[6] = {ga.a, ga.b, ga.c, ga.d, gb.a, gb.b};
                 rv += avRvCorrection(rx, ry, rz, min(v1, v2), eta_crit, gradV_i, gradV_j);
             }
 
@@ -492,7 +668,7 @@ __global__ void __launch_bounds__(kHydroBlock)
             T viscosity_ij = 0.0;
             if (wij < 0.0)
             {
-                T vij_signal = (alpha_i + LD(f.alpha, j)) / 4.0 * (ci + cj) - T(2.0) * wij;
+                T vij_signal = (alpha_i + cb.c) / 4.0 * (ci + cj) - T(2.0) * wij;
                 viscosity_ij = -vij_signal * wij;
             }
 
@@ -528,7 +704,7 @@ __global__ void __launch_bounds__(kHydroBlock)
             energy += mj * a_mom * (vx_ij * termA1_i + vy_ij * termA2_i + vz_ij * termA3_i);
 
             T momentum_i = mj * prhoi * a_mom;
-            T momentum_j = mj * LD(f.prho, j) * b_mom;
+            T momentum_j = mj * sj.d * b_mom;
             momentum_x += momentum_i * termA1_i + momentum_j * termA1_j + a_visc_x;
             momentum_y += momentum_i * termA2_i + momentum_j * termA2_j + a_visc_y;
             momentum_z += momentum_i * termA3_i + momentum_j * termA3_j + a_visc_z;
@@ -685,14 +861,81 @@ using namespace sphb200;
 
 static unsigned long long* dtKeys(sphb200_ctx* ctx) { return reinterpret_cast<unsigned long long*>(ctx->devDt + 4); }
 
+// ---- gather-record management ------------------------------------------------------------------------------------
+// Records live in grow-only context arenas.  A stand-alone operator call (tier 1) repacks what it reads on every call
+// because the caller may have changed the arrays in between; a sphb200_sim (tier 2) sets ctx->packReuse and
+// invalidates records itself whenever a member field is rewritten (see invalidate() calls below and in api.cu).
+enum RecId { R_POS, R_VEL, R_STATE, R_CA, R_CB, R_GA, R_GB, kNumRecs };
+static_assert(kNumRecs <= sphb200_ctx::kMaxRecs, "record arenas");
+
+static void beginOp(sphb200_ctx* ctx)
+{
+    if (!ctx->packReuse) { ctx->packValid = 0; ctx->tabValid = false; }
+}
+static void invalidate(sphb200_ctx* ctx, std::initializer_list<int> ids)
+{
+    for (int k : ids)
+        ctx->packValid &= ~(1u << k);
+}
+
+template<class T>
+static const void* ensureRec(sphb200_ctx* ctx, int k, const sphb200_fields& f)
+{
+    size_t n = f.n;
+    if (n == 0) throw std::runtime_error("sphb200_fields.n (array length incl. halos) must be set");
+    size_t bytes = n * (k == R_POS ? sizeof(PosRec<T>) : sizeof(Rec4<T>));
+    void* out    = ctx->rec[k].get(bytes);
+    if (ctx->packValid & (1u << k)) return out;
+    F<T> t   = typed<T>(f);
+    int grid = gridFor(n, 256);
+    auto p4  = [&](const T* a, const T* b, const T* c, const T* d)
+    { SPHB200_LAUNCH(ctx, pack4Kernel<T>, grid, 256, 0, n, a, b, c, d, static_cast<Rec4<T>*>(out)); };
+    switch (k)
+    {
+        case R_POS:
+            SPHB200_LAUNCH(ctx, packPosKernel<T>, grid, 256, 0, n, t.x, t.y, t.z, t.m, static_cast<PosRec<T>*>(out));
+            break;
+        case R_VEL: p4(t.vx, t.vy, t.vz, t.h); break;
+        case R_STATE: p4(t.xm, t.kx, t.c, t.prho); break;
+        case R_CA: p4(t.c11, t.c12, t.c13, t.c22); break;
+        case R_CB: p4(t.c23, t.c33, t.alpha, nullptr); break;
+        case R_GA: p4(t.dV11, t.dV12, t.dV13, t.dV22); break;
+        case R_GB: p4(t.dV23, t.dV33, nullptr, nullptr); break;
+    }
+    ctx->packValid |= 1u << k;
+    return out;
+}
+
+template<class T>
+static void ensureTables(sphb200_ctx* ctx, const sphb200_hydro_const* hc, const Rec2<T>*& pairs, const Rec4<T>*& quads)
+{
+    auto* p = static_cast<Rec2<T>*>(ctx->tabPairs.get(kTableSize * sizeof(Rec2<T>)));
+    auto* q = static_cast<Rec4<T>*>(ctx->tabQuads.get(kTableSize * sizeof(Rec4<T>)));
+    bool hit = ctx->tabValid && ctx->tabWh == hc->wh && ctx->tabWhd == hc->whd && ctx->tabElem == int(sizeof(T));
+    if (!hit)
+    {
+        if (!hc->wh) throw std::runtime_error("hydro_const.wh must point to the device kernel table");
+        SPHB200_LAUNCH(ctx, packTableKernel<T>, gridFor(kTableSize, 256), 256, 0, static_cast<const T*>(hc->wh),
+                       static_cast<const T*>(hc->whd), p, q);
+        ctx->tabValid = true; ctx->tabWh = hc->wh; ctx->tabWhd = hc->whd; ctx->tabElem = int(sizeof(T));
+    }
+    pairs = p;
+    quads = q;
+}
+
+extern "C" void sphb200_invalidate_records(sphb200_ctx* ctx) { ctx->packValid = 0; }
+
 extern "C" int sphb200_xmass(sphb200_ctx* ctx, int dtype, uint32_t first, uint32_t last, const sphb200_box* box,
                              const sphb200_hydro_const* hc, const uint32_t* neighbors, const sphb200_fields* f)
 {
     SPHB200_TRY
     if (last <= first) return 0;
-    DISPATCH(dtype, SPHB200_LAUNCH(ctx, xmassKernel<T>, gridFor(last - first, kHydroBlock), kHydroBlock, 0, first, last,
-                                   hc->ngmax, hc->K, pbcBox(*box), neighbors, typed<T>(*f),
-                                   static_cast<const T*>(hc->wh)););
+    beginOp(ctx);
+    DISPATCH(dtype, const Rec2<T>* wh; const Rec4<T>* whq; ensureTables<T>(ctx, hc, wh, whq);
+             auto* r0 = static_cast<const PosRec<T>*>(ensureRec<T>(ctx, R_POS, *f));
+             SPHB200_LAUNCH(ctx, xmassKernel<T>, gridFor(last - first, kHydroBlock), kHydroBlock, 0, first, last,
+                            hc->ngmax, hc->K, pbcBox(*box), neighbors, typed<T>(*f), r0, wh););
+    invalidate(ctx, {R_STATE});
     SPHB200_CATCH
 }
 
@@ -701,9 +944,13 @@ extern "C" int sphb200_ve_def_gradh(sphb200_ctx* ctx, int dtype, uint32_t first,
 {
     SPHB200_TRY
     if (last <= first) return 0;
-    DISPATCH(dtype, SPHB200_LAUNCH(ctx, veDefGradhKernel<T>, gridFor(last - first, kHydroBlock), kHydroBlock, 0, first,
-                                   last, hc->ngmax, hc->K, pbcBox(*box), neighbors, typed<T>(*f),
-                                   static_cast<const T*>(hc->wh), static_cast<const T*>(hc->whd)););
+    beginOp(ctx);
+    if (!hc->whd) throw std::runtime_error("ve_def_gradh: hydro_const.whd must be set");
+    DISPATCH(dtype, const Rec2<T>* wh; const Rec4<T>* whq; ensureTables<T>(ctx, hc, wh, whq);
+             auto* r0 = static_cast<const PosRec<T>*>(ensureRec<T>(ctx, R_POS, *f));
+             SPHB200_LAUNCH(ctx, veDefGradhKernel<T>, gridFor(last - first, kHydroBlock), kHydroBlock, 0, first, last,
+                            hc->ngmax, hc->K, pbcBox(*box), neighbors, typed<T>(*f), r0, whq););
+    invalidate(ctx, {R_STATE});
     SPHB200_CATCH
 }
 
@@ -714,6 +961,7 @@ extern "C" int sphb200_eos(sphb200_ctx* ctx, int dtype, uint32_t first, uint32_t
     if (last <= first) return 0;
     DISPATCH(dtype, SPHB200_LAUNCH(ctx, eosKernel<T>, gridFor(last - first, 256), 256, 0, first, last, typed<T>(*f),
                                    T(hc->muiConst), hc->gamma););
+    invalidate(ctx, {R_STATE});
     SPHB200_CATCH
 }
 
@@ -723,10 +971,15 @@ extern "C" int sphb200_iad_divv_curlv(sphb200_ctx* ctx, int dtype, uint32_t firs
 {
     SPHB200_TRY
     if (last <= first) return 0;
+    beginOp(ctx);
     bool doGradV = f->dV11 != nullptr;
-    DISPATCH(dtype, SPHB200_LAUNCH(ctx, iadDivvCurlvKernel<T>, gridFor(last - first, kHydroBlock), kHydroBlock, 0,
-                                   first, last, hc->ngmax, hc->K, pbcBox(*box), neighbors, typed<T>(*f),
-                                   static_cast<const T*>(hc->wh), doGradV););
+    DISPATCH(dtype, const Rec2<T>* wh; const Rec4<T>* whq; ensureTables<T>(ctx, hc, wh, whq);
+             auto* r0 = static_cast<const PosRec<T>*>(ensureRec<T>(ctx, R_POS, *f));
+             auto* r1 = static_cast<const Rec4<T>*>(ensureRec<T>(ctx, R_VEL, *f));
+             auto* r2 = static_cast<const Rec4<T>*>(ensureRec<T>(ctx, R_STATE, *f));
+             SPHB200_LAUNCH(ctx, iadDivvCurlvKernel<T>, gridFor(last - first, kHydroBlock), kHydroBlock, 0, first,
+                            last, hc->ngmax, hc->K, pbcBox(*box), neighbors, typed<T>(*f), r0, r1, r2, wh, doGradV););
+    invalidate(ctx, {R_CA, R_CB, R_GA, R_GB});
     SPHB200_CATCH
 }
 
@@ -735,10 +988,15 @@ extern "C" int sphb200_av_switches(sphb200_ctx* ctx, int dtype, uint32_t first, 
 {
     SPHB200_TRY
     if (last <= first) return 0;
-    DISPATCH(dtype, SPHB200_LAUNCH(ctx, avSwitchesKernel<T>, gridFor(last - first, kHydroBlock), kHydroBlock, 0, first,
-                                   last, hc->ngmax, hc->K, pbcBox(*box), neighbors, typed<T>(*f),
-                                   static_cast<const T*>(hc->wh), hc->minDt, T(hc->alphamin), T(hc->alphamax),
-                                   T(hc->decay_constant)););
+    beginOp(ctx);
+    DISPATCH(dtype, const Rec2<T>* wh; const Rec4<T>* whq; ensureTables<T>(ctx, hc, wh, whq);
+             auto* r0 = static_cast<const PosRec<T>*>(ensureRec<T>(ctx, R_POS, *f));
+             auto* r1 = static_cast<const Rec4<T>*>(ensureRec<T>(ctx, R_VEL, *f));
+             auto* r2 = static_cast<const Rec4<T>*>(ensureRec<T>(ctx, R_STATE, *f));
+             SPHB200_LAUNCH(ctx, avSwitchesKernel<T>, gridFor(last - first, kHydroBlock), kHydroBlock, 0, first, last,
+                            hc->ngmax, hc->K, pbcBox(*box), neighbors, typed<T>(*f), r0, r1, r2, wh, hc->minDt,
+                            T(hc->alphamin), T(hc->alphamax), T(hc->decay_constant)););
+    invalidate(ctx, {R_CB});
     SPHB200_CATCH
 }
 
@@ -750,16 +1008,28 @@ extern "C" int sphb200_momentum_energy(sphb200_ctx* ctx, int dtype, uint32_t fir
     SPHB200_LAUNCH(ctx, initCourantKeyKernel, 1, 1, 0, dtKeys(ctx));
     if (last > first)
     {
+        beginOp(ctx);
         int grid = gridFor(last - first, kHydroBlock);
         if (hc->avClean && !f->dV11) throw std::runtime_error("momentum_energy: avClean requires dV11..dV33");
-        DISPATCH(dtype,
-                 if (hc->avClean) SPHB200_LAUNCH(ctx, (momentumEnergyKernel<true, T>), grid, kHydroBlock, 0, first, last,
-                                                 hc->ngmax, hc->K, pbcBox(*box), neighbors, typed<T>(*f),
-                                                 static_cast<const T*>(hc->wh), T(hc->Atmin), T(hc->Atmax), T(hc->ramp),
-                                                 float(hc->Kcour), dtKeys(ctx));
+        DISPATCH(dtype, const Rec2<T>* wh; const Rec4<T>* whq; ensureTables<T>(ctx, hc, wh, whq);
+                 MomRecs<T> rec;
+                 rec.r0 = static_cast<const PosRec<T>*>(ensureRec<T>(ctx, R_POS, *f));
+                 rec.r1 = static_cast<const Rec4<T>*>(ensureRec<T>(ctx, R_VEL, *f));
+                 rec.r2 = static_cast<const Rec4<T>*>(ensureRec<T>(ctx, R_STATE, *f));
+                 rec.r3 = static_cast<const Rec4<T>*>(ensureRec<T>(ctx, R_CA, *f));
+                 rec.r4 = static_cast<const Rec4<T>*>(ensureRec<T>(ctx, R_CB, *f));
+                 rec.r5 = rec.r6 = nullptr;
+                 if (hc->avClean)
+                 {
+                     rec.r5 = static_cast<const Rec4<T>*>(ensureRec<T>(ctx, R_GA, *f));
+                     rec.r6 = static_cast<const Rec4<T>*>(ensureRec<T>(ctx, R_GB, *f));
+                     SPHB200_LAUNCH(ctx, (momentumEnergyKernel<true, T>), grid, kHydroBlock, 0, first, last, hc->ngmax,
+                                    hc->K, pbcBox(*box), neighbors, typed<T>(*f), rec, wh, T(hc->Atmin), T(hc->Atmax),
+                                    T(hc->ramp), float(hc->Kcour), dtKeys(ctx));
+                 }
                  else SPHB200_LAUNCH(ctx, (momentumEnergyKernel<false, T>), grid, kHydroBlock, 0, first, last, hc->ngmax,
-                                     hc->K, pbcBox(*box), neighbors, typed<T>(*f), static_cast<const T*>(hc->wh),
-                                     T(hc->Atmin), T(hc->Atmax), T(hc->ramp), float(hc->Kcour), dtKeys(ctx)););
+                                     hc->K, pbcBox(*box), neighbors, typed<T>(*f), rec, wh, T(hc->Atmin), T(hc->Atmax),
+                                     T(hc->ramp), float(hc->Kcour), dtKeys(ctx)););
     }
     if (minDtCourant_h)
     {
@@ -803,6 +1073,7 @@ extern "C" int sphb200_positions_update_h(sphb200_ctx* ctx, int dtype, uint32_t 
 {
     SPHB200_TRY
     if (last <= first) return 0;
+    ctx->packValid = 0;
     DISPATCH(dtype, SPHB200_LAUNCH(ctx, positionsKernel<T>, gridFor(last - first, 256), 256, 0, first, last, dt, dt_m1,
                                    pbcBox(*box), typed<T>(*f), T(hc->muiConst), hc->gamma, hc->ng0, f->x, f->y, f->z););
     SPHB200_CATCH

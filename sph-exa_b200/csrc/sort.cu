@@ -434,6 +434,7 @@ extern "C" int sphb200_unpack_ranges(sphb200_ctx* ctx, const uint32_t* rangeScan
                                      int numRanges, uint32_t total, int nfields, void* const* dst, const int* elemBytes,
                                      const void* packed)
 {
+    ctx->packValid = 0; // halo values changed under the gather records (hydro.cu)
     return rangesImpl(ctx, false, rangeScan, rangeBegin, numRanges, total, nfields, dst, elemBytes,
                       const_cast<void*>(packed));
 }

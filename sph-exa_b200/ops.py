@@ -175,6 +175,7 @@ def fields_struct(d):
     for n in B.FIELD_NAMES:
         t = d.get(n)
         setattr(f, n, t.data_ptr() if t is not None else None)
+    f.n = d["x"].numel()
     return f
 
 

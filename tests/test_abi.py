@@ -28,7 +28,7 @@ def test_struct_layouts_match_header(pkg):
     import ctypes as C
     B = pkg.binding
     assert C.sizeof(B.Box) == 6 * 8 + 3 * 8 + 3 * 8 + 3 * 4 + 4
-    assert C.sizeof(B.Fields) == 38 * 8
+    assert C.sizeof(B.Fields) == 38 * 8 + 8
     assert C.sizeof(B.TreeView) == 8 + 8 * 8
     assert C.sizeof(B.HydroConst) == 8 + 8 + 12 * 8 + 16 + 8
 
