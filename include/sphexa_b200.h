@@ -157,20 +157,23 @@ int sphb200_layout(sphb200_ctx*, const uint32_t* counts, int numLeaves, uint32_t
  * For every i in [first,last): all j != i with PBC-folded |r_ij|^2 < (2 h_i)^2 (findneighbors.hpp:95-165),
  * ascending j.  With iterate_h the coupled h/neighbor-count iteration of sph/find_neighbors.hpp:10-45 runs
  * (h updated in place, <= 10 iterations).  nc[i - first] = count + 1.
- * neighbors: "slab" layout, group g = (i-first)/32, lane = (i-first)%32:
- *            neighbors[((size_t)g*ngmax + k)*32 + lane], k < min(count, ngmax)
- * size in uint32: sphb200_neighbors_size(last-first, ngmax).  *numFails_h: non-converged particles. */
+ * neighbors: opaque device buffer of sphb200_neighbors_size(last-first, ngmax) uint32 in the layout the pair
+ *            operators read (lists interleaved per warp so that each warp-wide read is one 128-byte line; the layout
+ *            is internal, convert with sphb200_neighbors_to_rowmajor / _from_rowmajor).
+ * *numFails_h: non-converged particles. */
 size_t sphb200_neighbors_size(size_t numTargets, unsigned ngmax);
 int sphb200_find_neighbors(sphb200_ctx*, const sphb200_tree_view* tree_h, const double* x, const double* y,
                            const double* z, void* h, int dtype, uint32_t first, uint32_t last,
                            const sphb200_box* box_h, unsigned ng0, unsigned ngmax, int iterate_h, uint32_t* neighbors,
                            uint32_t* nc, unsigned* numFails_h);
-/* slab layout -> reference CPU layout neighbors[(i-first)*ngmax + k] (particles_data.hpp:235) */
-int sphb200_neighbors_to_rowmajor(sphb200_ctx*, const uint32_t* slab, const uint32_t* nc, uint32_t numTargets,
+/* internal layout <-> reference CPU layout neighbors[(i-first)*ngmax + k] (particles_data.hpp:235); nc[t] = count+1 */
+int sphb200_neighbors_to_rowmajor(sphb200_ctx*, const uint32_t* neighbors, const uint32_t* nc, uint32_t numTargets,
                                   unsigned ngmax, uint32_t* rowmajor);
+int sphb200_neighbors_from_rowmajor(sphb200_ctx*, const uint32_t* rowmajor, const uint32_t* nc, uint32_t numTargets,
+                                    unsigned ngmax, uint32_t* neighbors);
 
 /* ---- a14..a19: SPH-VE operators (sph/include/sph/sph_gpu.hpp:13-82) ----
- * nc is indexed like fields (nc = f->nc, entries [first,last) valid), neighbors in slab layout rel. to first */
+ * nc is indexed like fields (nc = f->nc, entries [first,last) valid), neighbors as written by sphb200_find_neighbors for the same [first,last) */
 int sphb200_xmass(sphb200_ctx*, int dtype, uint32_t first, uint32_t last, const sphb200_box* box_h,
                   const sphb200_hydro_const* hc_h, const uint32_t* neighbors, const sphb200_fields* f_h);
 int sphb200_ve_def_gradh(sphb200_ctx*, int dtype, uint32_t first, uint32_t last, const sphb200_box* box_h,

@@ -62,7 +62,7 @@ SYMBOLS = [
     "sphb200_create", "sphb200_destroy", "sphb200_invalidate_records", "sphb200_last_error", "sphb200_sync", "sphb200_launch_count",
     "sphb200_make_box", "sphb200_sfc_keys", "sphb200_minmax3", "sphb200_sort_by_key", "sphb200_gather",
     "sphb200_node_counts", "sphb200_update_octree", "sphb200_compute_octree", "sphb200_rebalance_decision",
-    "sphb200_build_octree", "sphb200_node_centers", "sphb200_layout", "sphb200_neighbors_size",
+    "sphb200_build_octree", "sphb200_node_centers", "sphb200_layout", "sphb200_neighbors_size", "sphb200_neighbors_from_rowmajor",
     "sphb200_find_neighbors", "sphb200_neighbors_to_rowmajor", "sphb200_xmass", "sphb200_ve_def_gradh",
     "sphb200_eos", "sphb200_iad_divv_curlv", "sphb200_av_switches", "sphb200_momentum_energy", "sphb200_timestep",
     "sphb200_timestep_device_ptr", "sphb200_positions_update_h", "sphb200_pack_ranges", "sphb200_unpack_ranges",

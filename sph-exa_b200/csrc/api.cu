@@ -71,6 +71,7 @@ extern "C" void sphb200_destroy(sphb200_ctx* ctx)
     ctx->treeTmp.release();
     ctx->scanTmp.release();
     ctx->miscTmp.release();
+    ctx->nbTmp.release();
     for (auto& a : ctx->rec)
         a.release();
     ctx->tabPairs.release();

@@ -20,6 +20,15 @@ constexpr int kMaxTreeLevel = 21;              // maxTreeLevel<uint64_t>, sfc/co
 constexpr int kNumSms       = 148;             // B200: 2 dies x 74 SMs
 constexpr int kTableSize    = 20000;           // sph/table_lookup.hpp:11
 
+// Neighbor-list layout shared by the search (neighbors.cu) and the J-loops (hydro.cu): one lane per target, a warp
+// covers 32 SFC-consecutive targets and entry k of all 32 lanes is one 128-byte line.
+// (Measured alternatives, Sedov 200^3 on B200: 2/4/8 lanes per target and 16-byte index blocks with 2-4 gathers in
+// flight per lane were all slower -- fewer L1 wavefronts or more ILP did not pay for the lost occupancy.)
+__host__ __device__ inline size_t nbOffset(size_t t, unsigned k, unsigned ngmax)
+{
+    return ((t >> 5) * ngmax + k) * 32 + (t & 31);
+}
+
 void setError(const std::string& msg);
 
 struct CudaError : std::runtime_error
@@ -70,9 +79,9 @@ struct sphb200_ctx
     cudaStream_t stream  = nullptr;
     bool ownStream       = false;
     uint64_t launches    = 0;
-    sphb200::Arena sortTmp, treeTmp, scanTmp, miscTmp;
+    sphb200::Arena sortTmp, treeTmp, scanTmp, miscTmp, nbTmp;
     // gather records of the pair operators (hydro.cu) and the repacked kernel tables
-    static constexpr int kMaxRecs = 8;
+    static constexpr int kMaxRecs = 12;
     sphb200::Arena rec[kMaxRecs], tabPairs, tabQuads;
     uint32_t packValid = 0;    // bit k: rec[k] mirrors the current field arrays
     bool packReuse     = false; // set by sphb200_sim: records stay valid across operator calls

@@ -99,8 +99,12 @@ __device__ __forceinline__ T lookup(const T* __restrict__ table, T v)
 // sector), not by DRAM.  Each operator therefore first packs the neighbor-side fields it reads into 32-byte
 // (f64) / 16-byte (mixed) records with one streaming pass, so that a pair costs one 256-bit load per record instead
 // of four 64-bit loads that each touch their own lines:
-//   R0 {x, y, z, m}   R1 {vx, vy, vz, h}   R2 {xm, kx, c, prho}   R3 {c11, c12, c13, c22}   R4 {c23, c33, alpha, -}
+//   R0 {x, y, z, m}   R1 {vx, vy, vz, h}   R2 {xm, xm/kx, c, prho}   R3 {c11, c12, c13, c22}
 //   R5 {dV11, dV12, dV13, dV22}   R6 {dV23, dV33, -, -}   (avClean only)
+//   momentum only: M1 {vx, vy, vz, 1/h}   M2 {xm, c, prho, rho}   M4 {c23, c33, alpha, m/rho}
+// Quantities of the reference J-loops that depend on j alone (V_j = xm_j/kx_j, 1/h_j, rho_j = kx_j m_j/xm_j, m_j/rho_j)
+// are evaluated once per particle by the pack kernels with the reference's expression, instead of once per pair:
+// same bits, ~100x fewer divisions.
 // The tabulated kernel is repacked the same way: entry idx holds {t[idx], t[idx+1]} (and for gradh the derivative
 // table's pair as well), so an interpolation is one load.  Values are copies, arithmetic is unchanged.
 template<class T>
@@ -189,6 +193,33 @@ __global__ void __launch_bounds__(256) pack4Kernel(size_t n, const T* __restrict
     out[i] = r;
 }
 
+//! @brief R2 = {xm, V = xm/kx, c, prho}; volume element as in iad_kern.hpp:75 / av_switches_kern.hpp:103
+template<class T>
+__global__ void __launch_bounds__(256) packStateKernel(size_t n, const T* __restrict__ xm, const T* __restrict__ kx,
+                                                       const T* __restrict__ c, const T* __restrict__ prho,
+                                                       Rec4<T>* __restrict__ out)
+{
+    size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Rec4<T> r;
+    r.a = xm[i]; r.b = xm[i] / kx[i]; r.c = c ? c[i] : T(0); r.d = prho ? prho[i] : T(0);
+    out[i] = r;
+}
+
+//! @brief momentum records M1, M2, M4 with the j-only terms of momentum_energy_kern.hpp:96-97,116-117,165
+template<class T>
+__global__ void __launch_bounds__(256) packMomentumKernel(size_t n, F<T> f, Rec4<T>* __restrict__ m1,
+                                                          Rec4<T>* __restrict__ m2, Rec4<T>* __restrict__ m4)
+{
+    size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    T m = f.m[i], xm = f.xm[i];
+    T rho = f.kx[i] * m / xm;
+    m1[i] = {f.vx[i], f.vy[i], f.vz[i], T(1) / f.h[i]};
+    m2[i] = {xm, f.c[i], f.prho[i], rho};
+    m4[i] = {f.c23[i], f.c33[i], f.alpha[i], m / rho};
+}
+
 //! @brief out[idx] = {wh[idx], wh[idx+1], whd[idx], whd[idx+1]}
 template<class T>
 __global__ void packTableKernel(const T* __restrict__ wh, const T* __restrict__ whd, Rec2<T>* __restrict__ pairs,
@@ -263,7 +294,7 @@ __device__ __forceinline__ NbList nbList(const uint32_t* nidx, const uint32_t* n
         if (j##_next = (pj + 1 < (nb).count) ? (nb)[pj + 1] : 0u, true)
 
 // ---------------------------------------------------------------- XMass (xmass_kern.hpp:50-78)
-template<class T>
+template<bool Pbc, class T>
 __global__ void __launch_bounds__(kHydroBlock)
     xmassKernel(uint32_t first, uint32_t last, unsigned ngmax, double K, PbcBox box, const uint32_t* __restrict__ nidx,
                 F<T> f, const PosRec<T>* __restrict__ r0, const Rec2<T>* __restrict__ wh)
@@ -283,7 +314,7 @@ __global__ void __launch_bounds__(kHydroBlock)
     {
         PosRec<T> pj_ = ldRec(r0, j);
         T xx = xi - pj_.x, yy = yi - pj_.y, zz = zi - pj_.z;
-        applyPBC(box, T(2) * hi, xx, yy, zz);
+        if (Pbc) applyPBC(box, T(2) * hi, xx, yy, zz);
         T dist = sqrt(xx * xx + yy * yy + zz * zz);
         T vloc = dist * hInv;
         T w    = lookup(wh, vloc);
@@ -293,7 +324,7 @@ __global__ void __launch_bounds__(kHydroBlock)
 }
 
 // ---------------------------------------------------------------- VeDefGradh (ve_def_gradh_kern.hpp:43-90)
-template<class T>
+template<bool Pbc, class T>
 __global__ void __launch_bounds__(kHydroBlock)
     veDefGradhKernel(uint32_t first, uint32_t last, unsigned ngmax, double K, PbcBox box,
                      const uint32_t* __restrict__ nidx, F<T> f, const PosRec<T>* __restrict__ r0,
@@ -318,7 +349,7 @@ __global__ void __launch_bounds__(kHydroBlock)
         PosRec<T> pj_ = ldRec(r0, j);
         T xmassj = LD(f.xm, j);
         T xx = xi - pj_.x, yy = yi - pj_.y, zz = zi - pj_.z;
-        applyPBC(box, T(2) * hi, xx, yy, zz);
+        if (Pbc) applyPBC(box, T(2) * hi, xx, yy, zz);
         T dist = sqrt(xx * xx + yy * yy + zz * zz);
         T vloc = dist * hInv;
         T w, dw;
@@ -364,7 +395,7 @@ __global__ void eosKernel(uint32_t first, uint32_t last, F<T> f, T muiConst, dou
 // One sweep: besides tau_ab = sum_j r_a r_b V_j W the sweep accumulates S_ab = sum_j (v_ji,a xm_j) W r_b; the
 // velocity gradient of divv_curlv_kern.hpp, dV_a[b] = sum_j (v_ji,a xm_j) * (-(C_i r)_b W), equals -(C_i S_a)_b
 // because C_i does not depend on j.  Same sums in the same order, C_i applied after instead of inside the loop.
-template<class T>
+template<bool Pbc, class T>
 __global__ void __launch_bounds__(kHydroBlock)
     iadDivvCurlvKernel(uint32_t first, uint32_t last, unsigned ngmax, double K, PbcBox box,
                        const uint32_t* __restrict__ nidx, F<T> f, const PosRec<T>* __restrict__ r0,
@@ -387,13 +418,13 @@ __global__ void __launch_bounds__(kHydroBlock)
     {
         PosRec<T> pj_ = ldRec(r0, j);
         Rec4<T> vj    = ldRec(r1, j);
-        Rec2<T> xk    = ldHalf(r2, j); // {xm_j, kx_j}
+        Rec2<T> xk    = ldHalf(r2, j); // {xm_j, V_j}
         T rx = xi - pj_.x, ry = yi - pj_.y, rz = zi - pj_.z;
-        applyPBC(box, T(2) * hi, rx, ry, rz);
+        if (Pbc) applyPBC(box, T(2) * hi, rx, ry, rz);
         T dist   = sqrt(rx * rx + ry * ry + rz * rz);
         T vloc   = dist * hiInv;
         T w      = lookup(wh, vloc);
-        T volj_w = xk.a / xk.b * w;
+        T volj_w = xk.b * w;
 
         tau11 += rx * rx * volj_w;
         tau12 += rx * ry * volj_w;
@@ -466,7 +497,7 @@ __global__ void __launch_bounds__(kHydroBlock)
 
 // ---------------------------------------------------------------- AV switches (av_switches_kern.hpp:44-137)
 // graddivv_b = sum_j factor_j * (-(C_i r)_b K h^-3 W): C_i, K h^-3 are constant in j and applied after the sweep.
-template<class T>
+template<bool Pbc, class T>
 __global__ void __launch_bounds__(kHydroBlock)
     avSwitchesKernel(uint32_t first, uint32_t last, unsigned ngmax, double K, PbcBox box,
                      const uint32_t* __restrict__ nidx, F<T> f, const PosRec<T>* __restrict__ r0,
@@ -493,10 +524,10 @@ __global__ void __launch_bounds__(kHydroBlock)
     {
         PosRec<T> pj_ = ldRec(r0, j);
         Rec4<T> vj    = ldRec(r1, j);
-        Rec4<T> sj    = ldRec(r2, j); // {xm, kx, c, prho}
+        Rec4<T> sj    = ldRec(r2, j); // {xm, V, c, prho}
         T divv_j      = LD(f.divv, j);
         T rx = xi - pj_.x, ry = yi - pj_.y, rz = zi - pj_.z;
-        applyPBC(box, T(2) * hi, rx, ry, rz);
+        if (Pbc) applyPBC(box, T(2) * hi, rx, ry, rz);
         T r2_  = rx * rx + ry * ry + rz * rz;
         T dist = sqrt(r2_);
 
@@ -512,7 +543,7 @@ __global__ void __launch_bounds__(kHydroBlock)
         T v1 = dist * hiInv;
         T w  = lookup(wh, v1);
 
-        T volj   = sj.a / sj.b;
+        T volj   = sj.b;
         T factor = volj * (divv_i - divv_j) * w;
 
         gx += factor * rx;
@@ -575,7 +606,7 @@ struct MomRecs
     const Rec4<T>*r1, *r2, *r3, *r4, *r5, *r6;
 };
 
-template<bool avClean, class T>
+template<bool Pbc, bool avClean, class T>
 __global__ void __launch_bounds__(kHydroBlock, kMomentumMinBlocks)
     momentumEnergyKernel(uint32_t first, uint32_t last, unsigned ngmax, double K, PbcBox box,
                          const uint32_t* __restrict__ nidx, F<T> f, MomRecs<T> rec, const Rec2<T>* __restrict__ wh,
@@ -588,15 +619,14 @@ __global__ void __launch_bounds__(kHydroBlock, kMomentumMinBlocks)
         NbList nb = nbList(nidx, f.nc, first, i, ngmax);
 
         PosRec<T> pi = rec.r0[i];
-        Rec4<T> vi   = rec.r1[i];
-        Rec4<T> si   = rec.r2[i];
+        Rec4<T> vi   = rec.r1[i]; // {v, 1/h}
+        Rec4<T> si   = rec.r2[i]; // {xm, c, prho, rho}
         double xi = pi.x, yi = pi.y, zi = pi.z;
-        T vxi = vi.a, vyi = vi.b, vzi = vi.c, hi = vi.d;
-        T mi = pi.m, xmassi = si.a, kxi = si.b, ci = si.c, prhoi = si.d;
+        T vxi = vi.a, vyi = vi.b, vzi = vi.c, hi = f.h[i];
+        T xmassi = si.a, ci = si.b, prhoi = si.c, rhoi = si.d;
         T alpha_i = f.alpha[i];
-        T rhoi    = kxi * mi / xmassi;
 
-        T hiInv  = T(1) / hi;
+        T hiInv  = vi.d;
         T hiInv3 = hiInv * hiInv * hiInv;
 
         T maxvsignali = 0.0;
@@ -624,15 +654,14 @@ __global__ void __launch_bounds__(kHydroBlock, kMomentumMinBlocks)
 
             T rx = xi - pj_.x, ry = yi - pj_.y, rz = zi - pj_.z;
             T vxj = vj.a, vyj = vj.b, vzj = vj.c;
-            applyPBC(box, T(2) * hi, rx, ry, rz);
+            if (Pbc) applyPBC(box, T(2) * hi, rx, ry, rz);
 
             T r2_  = rx * rx + ry * ry + rz * rz;
             T dist = sqrt(r2_);
 
             T vx_ij = vxi - vxj, vy_ij = vyi - vyj, vz_ij = vzi - vzj;
 
-            T hj    = vj.d;
-            T hjInv = T(1) / hj;
+            T hjInv = vj.d;
 
             T v1 = dist * hiInv;
             T v2 = dist * hjInv;
@@ -651,8 +680,7 @@ __global__ void __launch_bounds__(kHydroBlock, kMomentumMinBlocks)
             T termA2_j = -(c12j * rx + c22j * ry + c23j * rz) * Wj;
             T termA3_j = -(c13j * rx + c23j * ry + c33j * rz) * Wj;
 
-            T mj = pj_.m, cj = sj.c, kxj = sj.b, xmassj = sj.a;
-            T rhoj = kxj * mj / xmassj;
+            T mj = pj_.m, cj = sj.b, xmassj = sj.a, rhoj = sj.d;
 
             T rv = rx * vx_ij + ry * vy_ij + rz * vz_ij;
             if (avClean)
@@ -695,7 +723,7 @@ __global__ void __launch_bounds__(kHydroBlock, kMomentumMinBlocks)
             }
 
             T a_visc   = mj / rhoi * viscosity_ij;
-            T b_visc   = mj / rhoj * viscosity_ij;
+            T b_visc   = cb.d * viscosity_ij; // (m_j / rho_j) * viscosity_ij
             T a_visc_x = T(0.5) * (a_visc * termA1_i + b_visc * termA1_j);
             T a_visc_y = T(0.5) * (a_visc * termA2_i + b_visc * termA2_j);
             T a_visc_z = T(0.5) * (a_visc * termA3_i + b_visc * termA3_j);
@@ -704,7 +732,7 @@ __global__ void __launch_bounds__(kHydroBlock, kMomentumMinBlocks)
             energy += mj * a_mom * (vx_ij * termA1_i + vy_ij * termA2_i + vz_ij * termA3_i);
 
             T momentum_i = mj * prhoi * a_mom;
-            T momentum_j = mj * sj.d * b_mom;
+            T momentum_j = mj * sj.c * b_mom;
             momentum_x += momentum_i * termA1_i + momentum_j * termA1_j + a_visc_x;
             momentum_y += momentum_i * termA2_i + momentum_j * termA2_j + a_visc_y;
             momentum_z += momentum_i * termA3_i + momentum_j * termA3_j + a_visc_z;
@@ -854,6 +882,15 @@ using namespace sphb200;
         return 1;                                                                                                     \
     }
 
+//! @brief instantiate KERNEL<Pbc, T> for the box at hand (open boxes skip the minimum-image test in the J-loops)
+#define LAUNCH_PBC(ctx, box, KERNEL, grid, ...)                                                                       \
+    do                                                                                                                \
+    {                                                                                                                 \
+        PbcBox pb__ = pbcBox(box);                                                                                    \
+        if (pb__.px || pb__.py || pb__.pz) SPHB200_LAUNCH(ctx, (KERNEL<true, T>), grid, kHydroBlock, 0, __VA_ARGS__); \
+        else SPHB200_LAUNCH(ctx, (KERNEL<false, T>), grid, kHydroBlock, 0, __VA_ARGS__);                              \
+    } while (0)
+
 #define DISPATCH(dtype, ...)                                                                                          \
     if ((dtype) == SPHB200_F64) { using T = double; __VA_ARGS__ }                                                     \
     else if ((dtype) == SPHB200_MIXED) { using T = float; __VA_ARGS__ }                                               \
@@ -865,7 +902,7 @@ static unsigned long long* dtKeys(sphb200_ctx* ctx) { return reinterpret_cast<un
 // Records live in grow-only context arenas.  A stand-alone operator call (tier 1) repacks what it reads on every call
 // because the caller may have changed the arrays in between; a sphb200_sim (tier 2) sets ctx->packReuse and
 // invalidates records itself whenever a member field is rewritten (see invalidate() calls below and in api.cu).
-enum RecId { R_POS, R_VEL, R_STATE, R_CA, R_CB, R_GA, R_GB, kNumRecs };
+enum RecId { R_POS, R_VEL, R_STATE, R_CA, R_GA, R_GB, R_MVEL, R_MSTATE, R_MCB, kNumRecs };
 static_assert(kNumRecs <= sphb200_ctx::kMaxRecs, "record arenas");
 
 static void beginOp(sphb200_ctx* ctx)
@@ -896,11 +933,13 @@ static const void* ensureRec(sphb200_ctx* ctx, int k, const sphb200_fields& f)
             SPHB200_LAUNCH(ctx, packPosKernel<T>, grid, 256, 0, n, t.x, t.y, t.z, t.m, static_cast<PosRec<T>*>(out));
             break;
         case R_VEL: p4(t.vx, t.vy, t.vz, t.h); break;
-        case R_STATE: p4(t.xm, t.kx, t.c, t.prho); break;
+        case R_STATE:
+            SPHB200_LAUNCH(ctx, packStateKernel<T>, grid, 256, 0, n, t.xm, t.kx, t.c, t.prho, static_cast<Rec4<T>*>(out));
+            break;
         case R_CA: p4(t.c11, t.c12, t.c13, t.c22); break;
-        case R_CB: p4(t.c23, t.c33, t.alpha, nullptr); break;
         case R_GA: p4(t.dV11, t.dV12, t.dV13, t.dV22); break;
         case R_GB: p4(t.dV23, t.dV33, nullptr, nullptr); break;
+        default: throw std::runtime_error("ensureRec: momentum records are packed by packMomentum");
     }
     ctx->packValid |= 1u << k;
     return out;
@@ -923,6 +962,50 @@ static void ensureTables(sphb200_ctx* ctx, const sphb200_hydro_const* hc, const 
     quads = q;
 }
 
+//! @brief the three momentum-only records, always repacked (momentum is their only reader, once per step)
+template<class T>
+static void packMomentum(sphb200_ctx* ctx, const sphb200_fields& f, MomRecs<T>& rec)
+{
+    size_t n = f.n;
+    if (n == 0) throw std::runtime_error("sphb200_fields.n (array length incl. halos) must be set");
+    auto* m1 = static_cast<Rec4<T>*>(ctx->rec[R_MVEL].get(n * sizeof(Rec4<T>)));
+    auto* m2 = static_cast<Rec4<T>*>(ctx->rec[R_MSTATE].get(n * sizeof(Rec4<T>)));
+    auto* m4 = static_cast<Rec4<T>*>(ctx->rec[R_MCB].get(n * sizeof(Rec4<T>)));
+    SPHB200_LAUNCH(ctx, packMomentumKernel<T>, gridFor(n, 256), 256, 0, n, typed<T>(f), m1, m2, m4);
+    rec.r1 = m1;
+    rec.r2 = m2;
+    rec.r4 = m4;
+}
+
+template<class T>
+static void launchMomentum(sphb200_ctx* ctx, uint32_t first, uint32_t last, const sphb200_box* box,
+                           const sphb200_hydro_const* hc, const uint32_t* neighbors, const sphb200_fields* f,
+                           const Rec2<T>* wh)
+{
+    MomRecs<T> rec;
+    rec.r0 = static_cast<const PosRec<T>*>(ensureRec<T>(ctx, R_POS, *f));
+    rec.r3 = static_cast<const Rec4<T>*>(ensureRec<T>(ctx, R_CA, *f));
+    packMomentum<T>(ctx, *f, rec);
+    rec.r5 = rec.r6 = nullptr;
+    if (hc->avClean)
+    {
+        rec.r5 = static_cast<const Rec4<T>*>(ensureRec<T>(ctx, R_GA, *f));
+        rec.r6 = static_cast<const Rec4<T>*>(ensureRec<T>(ctx, R_GB, *f));
+    }
+    PbcBox pb = pbcBox(*box);
+    bool pbc  = pb.px || pb.py || pb.pz;
+    int grid  = gridFor(last - first, kHydroBlock);
+    auto go   = [&](auto kernel)
+    {
+        SPHB200_LAUNCH(ctx, kernel, grid, kHydroBlock, 0, first, last, hc->ngmax, hc->K, pb, neighbors, typed<T>(*f),
+                       rec, wh, T(hc->Atmin), T(hc->Atmax), T(hc->ramp), float(hc->Kcour), dtKeys(ctx));
+    };
+    if (pbc && hc->avClean) go(momentumEnergyKernel<true, true, T>);
+    else if (pbc) go(momentumEnergyKernel<true, false, T>);
+    else if (hc->avClean) go(momentumEnergyKernel<false, true, T>);
+    else go(momentumEnergyKernel<false, false, T>);
+}
+
 extern "C" void sphb200_invalidate_records(sphb200_ctx* ctx) { ctx->packValid = 0; }
 
 extern "C" int sphb200_xmass(sphb200_ctx* ctx, int dtype, uint32_t first, uint32_t last, const sphb200_box* box,
@@ -933,8 +1016,8 @@ extern "C" int sphb200_xmass(sphb200_ctx* ctx, int dtype, uint32_t first, uint32
     beginOp(ctx);
     DISPATCH(dtype, const Rec2<T>* wh; const Rec4<T>* whq; ensureTables<T>(ctx, hc, wh, whq);
              auto* r0 = static_cast<const PosRec<T>*>(ensureRec<T>(ctx, R_POS, *f));
-             SPHB200_LAUNCH(ctx, xmassKernel<T>, gridFor(last - first, kHydroBlock), kHydroBlock, 0, first, last,
-                            hc->ngmax, hc->K, pbcBox(*box), neighbors, typed<T>(*f), r0, wh););
+             LAUNCH_PBC(ctx, *box, xmassKernel, gridFor(last - first, kHydroBlock), first, last, hc->ngmax, hc->K,
+                        pbcBox(*box), neighbors, typed<T>(*f), r0, wh););
     invalidate(ctx, {R_STATE});
     SPHB200_CATCH
 }
@@ -948,8 +1031,8 @@ extern "C" int sphb200_ve_def_gradh(sphb200_ctx* ctx, int dtype, uint32_t first,
     if (!hc->whd) throw std::runtime_error("ve_def_gradh: hydro_const.whd must be set");
     DISPATCH(dtype, const Rec2<T>* wh; const Rec4<T>* whq; ensureTables<T>(ctx, hc, wh, whq);
              auto* r0 = static_cast<const PosRec<T>*>(ensureRec<T>(ctx, R_POS, *f));
-             SPHB200_LAUNCH(ctx, veDefGradhKernel<T>, gridFor(last - first, kHydroBlock), kHydroBlock, 0, first, last,
-                            hc->ngmax, hc->K, pbcBox(*box), neighbors, typed<T>(*f), r0, whq););
+             LAUNCH_PBC(ctx, *box, veDefGradhKernel, gridFor(last - first, kHydroBlock), first, last, hc->ngmax, hc->K,
+                        pbcBox(*box), neighbors, typed<T>(*f), r0, whq););
     invalidate(ctx, {R_STATE});
     SPHB200_CATCH
 }
@@ -977,9 +1060,9 @@ extern "C" int sphb200_iad_divv_curlv(sphb200_ctx* ctx, int dtype, uint32_t firs
              auto* r0 = static_cast<const PosRec<T>*>(ensureRec<T>(ctx, R_POS, *f));
              auto* r1 = static_cast<const Rec4<T>*>(ensureRec<T>(ctx, R_VEL, *f));
              auto* r2 = static_cast<const Rec4<T>*>(ensureRec<T>(ctx, R_STATE, *f));
-             SPHB200_LAUNCH(ctx, iadDivvCurlvKernel<T>, gridFor(last - first, kHydroBlock), kHydroBlock, 0, first,
-                            last, hc->ngmax, hc->K, pbcBox(*box), neighbors, typed<T>(*f), r0, r1, r2, wh, doGradV););
-    invalidate(ctx, {R_CA, R_CB, R_GA, R_GB});
+             LAUNCH_PBC(ctx, *box, iadDivvCurlvKernel, gridFor(last - first, kHydroBlock), first, last, hc->ngmax,
+                        hc->K, pbcBox(*box), neighbors, typed<T>(*f), r0, r1, r2, wh, doGradV););
+    invalidate(ctx, {R_CA, R_GA, R_GB});
     SPHB200_CATCH
 }
 
@@ -993,10 +1076,9 @@ extern "C" int sphb200_av_switches(sphb200_ctx* ctx, int dtype, uint32_t first, 
              auto* r0 = static_cast<const PosRec<T>*>(ensureRec<T>(ctx, R_POS, *f));
              auto* r1 = static_cast<const Rec4<T>*>(ensureRec<T>(ctx, R_VEL, *f));
              auto* r2 = static_cast<const Rec4<T>*>(ensureRec<T>(ctx, R_STATE, *f));
-             SPHB200_LAUNCH(ctx, avSwitchesKernel<T>, gridFor(last - first, kHydroBlock), kHydroBlock, 0, first, last,
-                            hc->ngmax, hc->K, pbcBox(*box), neighbors, typed<T>(*f), r0, r1, r2, wh, hc->minDt,
-                            T(hc->alphamin), T(hc->alphamax), T(hc->decay_constant)););
-    invalidate(ctx, {R_CB});
+             LAUNCH_PBC(ctx, *box, avSwitchesKernel, gridFor(last - first, kHydroBlock), first, last, hc->ngmax, hc->K,
+                        pbcBox(*box), neighbors, typed<T>(*f), r0, r1, r2, wh, hc->minDt, T(hc->alphamin),
+                        T(hc->alphamax), T(hc->decay_constant)););
     SPHB200_CATCH
 }
 
@@ -1009,27 +1091,9 @@ extern "C" int sphb200_momentum_energy(sphb200_ctx* ctx, int dtype, uint32_t fir
     if (last > first)
     {
         beginOp(ctx);
-        int grid = gridFor(last - first, kHydroBlock);
         if (hc->avClean && !f->dV11) throw std::runtime_error("momentum_energy: avClean requires dV11..dV33");
         DISPATCH(dtype, const Rec2<T>* wh; const Rec4<T>* whq; ensureTables<T>(ctx, hc, wh, whq);
-                 MomRecs<T> rec;
-                 rec.r0 = static_cast<const PosRec<T>*>(ensureRec<T>(ctx, R_POS, *f));
-                 rec.r1 = static_cast<const Rec4<T>*>(ensureRec<T>(ctx, R_VEL, *f));
-                 rec.r2 = static_cast<const Rec4<T>*>(ensureRec<T>(ctx, R_STATE, *f));
-                 rec.r3 = static_cast<const Rec4<T>*>(ensureRec<T>(ctx, R_CA, *f));
-                 rec.r4 = static_cast<const Rec4<T>*>(ensureRec<T>(ctx, R_CB, *f));
-                 rec.r5 = rec.r6 = nullptr;
-                 if (hc->avClean)
-                 {
-                     rec.r5 = static_cast<const Rec4<T>*>(ensureRec<T>(ctx, R_GA, *f));
-                     rec.r6 = static_cast<const Rec4<T>*>(ensureRec<T>(ctx, R_GB, *f));
-                     SPHB200_LAUNCH(ctx, (momentumEnergyKernel<true, T>), grid, kHydroBlock, 0, first, last, hc->ngmax,
-                                    hc->K, pbcBox(*box), neighbors, typed<T>(*f), rec, wh, T(hc->Atmin), T(hc->Atmax),
-                                    T(hc->ramp), float(hc->Kcour), dtKeys(ctx));
-                 }
-                 else SPHB200_LAUNCH(ctx, (momentumEnergyKernel<false, T>), grid, kHydroBlock, 0, first, last, hc->ngmax,
-                                     hc->K, pbcBox(*box), neighbors, typed<T>(*f), rec, wh, T(hc->Atmin), T(hc->Atmax),
-                                     T(hc->ramp), float(hc->Kcour), dtKeys(ctx)););
+                 launchMomentum<T>(ctx, first, last, box, hc, neighbors, f, wh););
     }
     if (minDtCourant_h)
     {

@@ -24,7 +24,42 @@ struct DevTree
     const LocalIndex* layout;
     const double* centers;
     const double* sizes;
+    const double* leafBounds; // [numLeaves][6] tight particle extents: xlo ylo zlo xhi yhi zhi
 };
+
+//! @brief tight bounding box of the particles in every leaf (one warp per leaf); empty leaf: lo=+inf, hi=-inf
+__global__ void __launch_bounds__(128) leafBoundsKernel(const LocalIndex* __restrict__ layout, int numLeaves,
+                                                        const double* __restrict__ x, const double* __restrict__ y,
+                                                        const double* __restrict__ z, double* __restrict__ bounds)
+{
+    int leaf = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    int lane = threadIdx.x & 31;
+    if (leaf >= numLeaves) return;
+    LocalIndex jb = layout[leaf], je = layout[leaf + 1];
+    double lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    for (LocalIndex j = jb + lane; j < je; j += 32)
+    {
+        double p[3] = {x[j], y[j], z[j]};
+#pragma unroll
+        for (int d = 0; d < 3; ++d)
+        {
+            lo[d] = fmin(lo[d], p[d]);
+            hi[d] = fmax(hi[d], p[d]);
+        }
+    }
+#pragma unroll
+    for (int d = 0; d < 3; ++d)
+    {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1)
+        {
+            lo[d] = fmin(lo[d], __shfl_xor_sync(0xffffffffu, lo[d], o));
+            hi[d] = fmax(hi[d], __shfl_xor_sync(0xffffffffu, hi[d], o));
+        }
+    }
+    if (lane < 3) bounds[6 * size_t(leaf) + lane] = lo[lane];
+    else if (lane < 6) bounds[6 * size_t(leaf) + lane] = hi[lane - 3];
+}
 
 //! @brief sph::updateH (sph/include/sph/kernels.hpp:26-32)
 template<class T>
@@ -111,7 +146,7 @@ __global__ void __launch_bounds__(kNbWarps * 32)
     const LocalIndex i = valid ? LocalIndex(gBase + lane) : last - 1;
     const double xi = x[i], yi = y[i], zi = z[i];
     Th hi           = h[i];
-    uint32_t* myList = nidx + (group * ngmax) * 32 + lane;
+    uint32_t* myList = nidx + nbOffset(group * 32 + lane, 0, ngmax);
 
     const bool anyPbc =
         box.bc[0] == SPHB200_PERIODIC || box.bc[1] == SPHB200_PERIODIC || box.bc[2] == SPHB200_PERIODIC;
@@ -179,7 +214,19 @@ __global__ void __launch_bounds__(kNbWarps * 32)
                 TreeNodeIndex leafIdx = tree.internalToLeaf[node];
                 LocalIndex jb = tree.layout[leafIdx], je = tree.layout[leafIdx + 1];
                 if (usePbc) testLeaf<true>(x, y, z, jb, je, cand, lane, active, i, xi, yi, zi, radiusSq, box, ngmax, myList, count);
-                else testLeaf<false>(x, y, z, jb, je, cand, lane, active, i, xi, yi, zi, radiusSq, box, ngmax, myList, count);
+                else
+                {
+                    // per-target cull against the tight leaf extents.  Every particle of the leaf has
+                    // lo <= x_j <= hi, rounding is monotone and the sum below associates like distSq, so the computed
+                    // box distance never exceeds the computed particle distance: a leaf skipped here holds no neighbor.
+                    const double* lb = tree.leafBounds + 6 * size_t(leafIdx);
+                    double ex = fmax(fmax(lb[0] - xi, xi - lb[3]), 0.0);
+                    double ey = fmax(fmax(lb[1] - yi, yi - lb[4]), 0.0);
+                    double ez = fmax(fmax(lb[2] - zi, zi - lb[5]), 0.0);
+                    bool hit  = active && (ex * ex + ey * ey + ez * ez < radiusSq);
+                    if (__any_sync(0xffffffffu, hit))
+                        testLeaf<false>(x, y, z, jb, je, cand, lane, hit, i, xi, yi, zi, radiusSq, box, ngmax, myList, count);
+                }
             }
             else
             {
@@ -229,16 +276,19 @@ __global__ void __launch_bounds__(kNbWarps * 32)
     }
 }
 
-//! @brief slab layout -> row-major [target][ngmax]
-__global__ void slabToRowMajorKernel(const uint32_t* __restrict__ slab, const uint32_t* __restrict__ nc,
-                                     uint32_t numTargets, unsigned ngmax, uint32_t* __restrict__ out)
+//! @brief list buffer <-> row-major [target][ngmax]
+template<bool ToRowMajor>
+__global__ void convertListsKernel(uint32_t* __restrict__ lists, const uint32_t* __restrict__ nc, uint32_t numTargets,
+                                   unsigned ngmax, uint32_t* __restrict__ rowMajor)
 {
     size_t t = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
     if (t >= numTargets) return;
-    size_t g = t / 32, lane = t % 32;
     unsigned cnt = min(nc[t] - 1, ngmax);
     for (unsigned k = 0; k < cnt; ++k)
-        out[t * ngmax + k] = slab[(g * ngmax + k) * 32 + lane];
+    {
+        if (ToRowMajor) rowMajor[t * ngmax + k] = lists[nbOffset(t, k, ngmax)];
+        else lists[nbOffset(t, k, ngmax)] = rowMajor[t * ngmax + k];
+    }
 }
 
 } // namespace sphb200
@@ -259,7 +309,10 @@ extern "C" int sphb200_find_neighbors(sphb200_ctx* ctx, const sphb200_tree_view*
     {
         if (numFails_h) *numFails_h = 0;
         if (last <= first) return 0;
-        DevTree tree{t->childOffsets, t->internalToLeaf, t->layout, t->centers, t->sizes};
+        auto* bounds = static_cast<double*>(ctx->nbTmp.get(size_t(t->numLeafNodes) * 6 * sizeof(double)));
+        SPHB200_LAUNCH(ctx, leafBoundsKernel, gridFor(t->numLeafNodes, 4), 128, 0, t->layout, t->numLeafNodes, x, y, z,
+                       bounds);
+        DevTree tree{t->childOffsets, t->internalToLeaf, t->layout, t->centers, t->sizes, bounds};
         unsigned* dFails = reinterpret_cast<unsigned*>(ctx->devScalars + 4);
         SPHB200_CUDA(cudaMemsetAsync(dFails, 0, sizeof(unsigned), ctx->stream));
         size_t numGroups = (size_t(last - first) + 31) / 32;
@@ -291,8 +344,25 @@ extern "C" int sphb200_neighbors_to_rowmajor(sphb200_ctx* ctx, const uint32_t* s
     try
     {
         if (numTargets)
-            SPHB200_LAUNCH(ctx, slabToRowMajorKernel, gridFor(numTargets, 128), 128, 0, slab, nc, numTargets, ngmax,
-                           rowmajor);
+            SPHB200_LAUNCH(ctx, convertListsKernel<true>, gridFor(numTargets, 128), 128, 0,
+                           const_cast<uint32_t*>(slab), nc, numTargets, ngmax, rowmajor);
+        return 0;
+    }
+    catch (std::exception& e)
+    {
+        setError(e.what());
+        return 1;
+    }
+}
+
+extern "C" int sphb200_neighbors_from_rowmajor(sphb200_ctx* ctx, const uint32_t* rowmajor, const uint32_t* nc,
+                                               uint32_t numTargets, unsigned ngmax, uint32_t* neighbors)
+{
+    try
+    {
+        if (numTargets)
+            SPHB200_LAUNCH(ctx, convertListsKernel<false>, gridFor(numTargets, 128), 128, 0, neighbors, nc, numTargets,
+                           ngmax, const_cast<uint32_t*>(rowmajor));
         return 0;
     }
     catch (std::exception& e)

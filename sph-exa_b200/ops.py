@@ -147,7 +147,7 @@ def neighborsSize(num_targets, ngmax):
 def findNeighbors(ctx, tree, x, y, z, h, first, last, box, ng0, ngmax, iterate_h=True):
     """neighbor search + coupled h iteration (sph/find_neighbors.hpp:10-45); h is updated in place.
 
-    returns (slab neighbor lists, nc[last-first] incl. self, numFails)"""
+    returns (neighbor list buffer, nc[last-first] incl. self, numFails)"""
     dev = x.device
     nt = last - first
     nb = torch.empty(max(1, neighborsSize(nt, ngmax)), dtype=torch.int32, device=dev)
@@ -166,6 +166,14 @@ def neighborsRowMajor(ctx, nb, nc, ngmax):
     out = torch.zeros((max(nt, 1), ngmax), dtype=torch.int32, device=nb.device)
     check(lib.sphb200_neighbors_to_rowmajor(ctx.h, ptr(nb), ptr(nc), C.c_uint32(nt), C.c_uint(ngmax), ptr(out)))
     return out[:nt]
+
+
+def neighborsFromRowMajor(ctx, rowmajor, nc, ngmax):
+    """reference CPU layout [nt, ngmax] (+ nc incl. self) -> list buffer read by the pair operators"""
+    nt = nc.numel()
+    nb = torch.zeros(max(1, neighborsSize(nt, ngmax)), dtype=torch.int32, device=rowmajor.device)
+    check(lib.sphb200_neighbors_from_rowmajor(ctx.h, ptr(rowmajor), ptr(nc), C.c_uint32(nt), C.c_uint(ngmax), ptr(nb)))
+    return nb
 
 
 # ---------------------------------------------------------------- SPH-VE operators

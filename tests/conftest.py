@@ -54,15 +54,11 @@ def to_host(t, dtype=None):
     return a
 
 
-def slab_from_rowmajor(nb, nc, ngmax):
-    """row-major neighbor lists [n, ngmax] -> slab layout used by the CUDA kernels"""
-    n = nb.shape[0]
-    ng = (n + 31) // 32
-    slab = np.zeros((ng, ngmax, 32), np.uint32)
-    pad = np.zeros((ng * 32, ngmax), np.uint32)
-    pad[:n] = nb
-    slab[:] = pad.reshape(ng, 32, ngmax).transpose(0, 2, 1)
-    return slab.ravel()
+def slab_from_rowmajor(ctx, nb, nc, ngmax):
+    """row-major neighbor lists [n, ngmax] (reference CPU layout) -> device list buffer of the CUDA kernels"""
+    from sph_exa_b200 import ops
+    rm = to_dev(np.ascontiguousarray(nb[:, :ngmax], np.uint32))
+    return ops.neighborsFromRowMajor(ctx, rm, to_dev(np.ascontiguousarray(nc, np.uint32)), ngmax)
 
 
 def sorted_sets_equal(nb_a, nc_a, nb_b, nc_b, ngmax):

@@ -4,6 +4,7 @@ Tolerance (north star): <= 1e-10 relative per step in fp64 mode, measured as max
 per field (lattice forces cancel to ~0, a per-element relative error is undefined there).  Mixed mode
 (reference default precision) is compared at float accuracy.
 """
+import ctypes as C
 import os
 
 import numpy as np
@@ -54,7 +55,7 @@ def test_operators_one_by_one(pkg, ctx, ref, real, case, side, steps):
     b = pkg.make_box(*sim.box)
     names = ALL + (["dV11", "dV12", "dV13", "dV22", "dV23", "dV33"] if av_clean else [])
     want = sim.f
-    nb = to_dev(slab_from_rowmajor(sim.nb, sim.nc, ngmax))
+    nb = slab_from_rowmajor(ctx, sim.nb, sim.nc, ngmax)
     wh, whd = to_dev(sim.wh), to_dev(sim.whd)
     hc = ops.hydro_const(sim.K, wh, whd, gamma=s["gamma"], muiConst=s["mui"], Kcour=s.get("Kcour", 0.2),
                          minDt=pre_dt[0], minDt_m1=pre_dt[1], avClean=av_clean)
@@ -136,7 +137,7 @@ def test_golden_ve_fixture(pkg, ctx):
     nbrow[0] = np.arange(1, 99)
     nc = np.ones(n, np.uint32)
     nc[0] = 99
-    nb = to_dev(slab_from_rowmajor(nbrow, nc, 98))
+    nb = slab_from_rowmajor(ctx, nbrow, nc, 98)
     wh, whd, _ = pkg.ic.kernel_tables(np.float64)
     dwh, dwhd = to_dev(wh), to_dev(whd)
     box = pkg.make_box([-1e9, 1e9] * 3, [0, 0, 0])
@@ -274,10 +275,13 @@ def test_neighbor_lists_of_a_step(pkg, ctx, ref):
     rs.step()
     gs.step()
     n, ngmax = rs.n, rs.ngmax
-    slab = gs._d2h(B.lib.sphb200_sim_neighbors(gs.h), B.lib.sphb200_neighbors_size(n, ngmax), np.uint32)
     nc = gs.download(names=["nc"])["nc"]
-    ng = (n + 31) // 32
-    rm = slab.reshape(ng, ngmax, 32).transpose(0, 2, 1).reshape(ng * 32, ngmax)[:n]
+    import torch
+    rm_d = torch.zeros((n, ngmax), dtype=torch.int32, device="cuda")
+    assert B.lib.sphb200_neighbors_to_rowmajor(ctx.h, C.c_void_p(B.lib.sphb200_sim_neighbors(gs.h)),
+                                               C.c_void_p(to_dev(nc).data_ptr()), C.c_uint32(n), C.c_uint(ngmax),
+                                               C.c_void_p(rm_d.data_ptr())) == 0
+    rm = to_host(rm_d, np.uint32)
     assert sorted_sets_equal(rm.copy(), nc, rs.nb.copy(), rs.nc, ngmax)
     gs.close()
 
