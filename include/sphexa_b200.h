@@ -132,7 +132,10 @@ int sphb200_node_counts(sphb200_ctx*, const uint64_t* leaves, int numLeaves, con
                         uint32_t* counts);
 
 /* ---- a6/a7: updateOctreeGpu (tree/update_gpu.cuh:58-82) = rebalanceDecision + rebalanceTree + counts ----
- * leaves/counts are updated in place (capacity entries available); *numLeaves in/out; *converged out (host) */
+ * leaves/counts are updated in place (capacity entries available); *numLeaves in/out; *converged out (host).
+ * A leaf can split into up to 4096 (csarray.hpp:305): if the new tree does not fit, SPHB200_ERR_CAPACITY is returned
+ * with *numLeaves_h = required number of leaves and leaves/counts untouched, so the call can be repeated. */
+#define SPHB200_ERR_CAPACITY 2
 int sphb200_update_octree(sphb200_ctx*, const uint64_t* keys, size_t n, unsigned bucketSize, uint64_t* leaves,
                           uint32_t* counts, int capacity, int* numLeaves_h, int* converged_h);
 /* computeOctree (csarray.hpp:454-468): from {0, 2^63} until converged; *iterations_h = number of update steps */

@@ -105,6 +105,9 @@ class SphError(RuntimeError):
     """mirrors the std::runtime_error the reference throws on precondition violations"""
 
 
+ERR_CAPACITY = 2  # SPHB200_ERR_CAPACITY
+
+
 def check(rc):
     if rc != 0:
         raise SphError(lib.sphb200_last_error().decode())

@@ -36,6 +36,11 @@ struct CudaError : std::runtime_error
     using std::runtime_error::runtime_error;
 };
 
+struct CapacityError : std::runtime_error
+{
+    using std::runtime_error::runtime_error;
+};
+
 #define SPHB200_CUDA(call)                                                                                            \
     do                                                                                                                \
     {                                                                                                                 \

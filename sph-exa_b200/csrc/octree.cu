@@ -210,7 +210,13 @@ static void updateOctreeImpl(sphb200_ctx* ctx, const KeyType* keys, size_t n, un
     SPHB200_CUDA(cudaStreamSynchronize(ctx->stream));
     int changed = ctx->hostScalars[0];
     int newL    = ctx->hostScalars[1];
-    if (newL > capacity) throw std::runtime_error("update_octree: leaf capacity exceeded (" + std::to_string(newL) + " > " + std::to_string(capacity) + ")");
+    if (newL > capacity)
+    {
+        // nothing has been modified yet: report the required size so that the caller can retry with larger arrays
+        *numLeaves = newL;
+        throw CapacityError("update_octree: leaf capacity exceeded (" + std::to_string(newL) + " > " +
+                            std::to_string(capacity) + ")");
+    }
     if (changed)
     {
         SPHB200_LAUNCH(ctx, processNodesKernel, gridFor(L + 1, 256), 256, 0, leaves, ops, L, newLeaves);
@@ -264,9 +270,21 @@ extern "C" int sphb200_update_octree(sphb200_ctx* ctx, const uint64_t* keys, siz
                                      uint64_t* leaves, uint32_t* counts, int capacity, int* numLeaves_h,
                                      int* converged_h)
 {
-    SPHB200_TRY
-    updateOctreeImpl(ctx, keys, n, bucket, leaves, counts, capacity, numLeaves_h, converged_h);
-    SPHB200_CATCH
+    try
+    {
+        updateOctreeImpl(ctx, keys, n, bucket, leaves, counts, capacity, numLeaves_h, converged_h);
+        return 0;
+    }
+    catch (CapacityError& e)
+    {
+        setError(e.what());
+        return SPHB200_ERR_CAPACITY; // *numLeaves_h = required number of leaves, inputs untouched
+    }
+    catch (std::exception& e)
+    {
+        setError(e.what());
+        return 1;
+    }
 }
 
 extern "C" int sphb200_compute_octree(sphb200_ctx* ctx, const uint64_t* keys, size_t n, unsigned bucket,

@@ -486,6 +486,41 @@ def bench_main(args, pkg, METRIC, UNIT, ALGO_BYTES, load_peaks, ClockSampler):
     phase_ms = {k: v / reps * 1e3 for k, v in sim.times.items()}
     sim.profile = False
 
+    # end to end: every step uploads the owned conserved fields from pinned host memory and reads the new state back
+    e2e = None
+    if not getattr(args, "no_e2e", False):
+        e2e_steps = max(2, min(args.steps, 5))
+        cap = int((sim.end - sim.start) * 1.25) + 1024
+        host = {k: torch.empty(cap, dtype=sim.f[k].dtype).pin_memory() for k in sim.CONSERVED}
+        n_h = sim.end - sim.start
+        for k in sim.CONSERVED:
+            host[k][:n_h].copy_(sim.f[k][:n_h])
+        torch.cuda.synchronize()
+        h2d = d2h = 0
+        for it in range(1 + e2e_steps):
+            if it == 1:
+                barrier()
+                h2d = d2h = 0
+                t0 = time.perf_counter()
+            for k in sim.CONSERVED:
+                sim.f[k] = host[k][:n_h].to(sim.dev, non_blocking=True)
+                h2d += n_h * host[k].element_size()
+            sim.step()
+            n_h = sim.end - sim.start
+            if n_h > cap:
+                raise RuntimeError("e2e host buffers too small")
+            for k in sim.CONSERVED:
+                host[k][:n_h].copy_(sim.f[k][:n_h], non_blocking=True)
+                d2h += n_h * host[k].element_size()
+            torch.cuda.synchronize()
+        barrier()
+        dt_e = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+        dist.all_reduce(dt_e, op=dist.ReduceOp.MAX)
+        dt_e = float(dt_e.item())
+        e2e = {"value": n_global * e2e_steps / dt_e, "unit": UNIT, "h2d_bytes_per_step": h2d // e2e_steps,
+               "d2h_bytes_per_step": d2h // e2e_steps, "ms_per_step": dt_e / e2e_steps * 1e3, "steps": e2e_steps,
+               "note": "bytes are rank 0's; every rank moves its own share"}
+
     if rank == 0:
         peak, peak_src = load_peaks()
         value = n_global * args.steps / (total_ms * 1e-3)
@@ -508,7 +543,7 @@ def bench_main(args, pkg, METRIC, UNIT, ALGO_BYTES, load_peaks, ClockSampler):
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                          "kernel_ms": phase_ms[dom]},
-            "e2e": None, "cpu_baseline": None,
+            "e2e": e2e, "cpu_baseline": None,
         }
         print(json.dumps(line), flush=True)
     barrier()

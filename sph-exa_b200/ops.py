@@ -89,15 +89,20 @@ def computeOctreeGpu(ctx, keys, bucket, capacity=None):
 def updateOctreeGpu(ctx, keys, bucket, leaves, counts):
     """updateOctreeGpu (tree/update_gpu.cuh:58-82): one rebalance + recount; returns (leaves, counts, converged)"""
     nl0 = counts.numel()
-    cap = 4096 * min(nl0, 64) + 8 * nl0 + 64  # a leaf can split into up to 4096 (csarray.hpp:305)
-    lv = torch.empty(cap + 2, dtype=torch.int64, device=keys.device)
-    ct = torch.empty(cap + 2, dtype=torch.int32, device=keys.device)
-    lv[:nl0 + 1] = leaves
-    ct[:nl0] = counts
-    nl, conv = C.c_int(nl0), C.c_int(0)
-    check(lib.sphb200_update_octree(ctx.h, ptr(keys), C.c_size_t(keys.numel()), C.c_uint(bucket), ptr(lv), ptr(ct),
-                                    cap, C.byref(nl), C.byref(conv)))
-    return lv[:nl.value + 1].clone(), ct[:nl.value].clone(), bool(conv.value)
+    cap = 8 * nl0 + 4096  # usual growth; a leaf may split into up to 4096 (csarray.hpp:305) -> retry below
+    while True:
+        lv = torch.empty(cap + 2, dtype=torch.int64, device=keys.device)
+        ct = torch.empty(cap + 2, dtype=torch.int32, device=keys.device)
+        lv[:nl0 + 1] = leaves
+        ct[:nl0] = counts
+        nl, conv = C.c_int(nl0), C.c_int(0)
+        rc = lib.sphb200_update_octree(ctx.h, ptr(keys), C.c_size_t(keys.numel()), C.c_uint(bucket), ptr(lv), ptr(ct),
+                                       cap, C.byref(nl), C.byref(conv))
+        if rc == B.ERR_CAPACITY and nl.value > cap:
+            cap = nl.value + 64
+            continue
+        check(rc)
+        return lv[:nl.value + 1].clone(), ct[:nl.value].clone(), bool(conv.value)
 
 
 class Octree:
