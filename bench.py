@@ -262,9 +262,9 @@ def main():
             if it == 1:
                 sync()
                 t0 = time.perf_counter()
-            gs.upload_async(fin, n)      # H2D of this step's inputs from pinned memory
-            gs.step()
-            gs.download_into(fout)       # D2H of the step's result (synchronises)
+            # H2D of this step's inputs from pinned memory, the step, D2H of the new state (synchronises); the
+            # library stages the copies beside the kernels (sphb200_sim_step_host)
+            gs.step_host(fin, fout, n)
             for k in host_in:            # next step's input = this step's output
                 host_in[k], host_out[k] = host_out[k], host_in[k]
             for k in B.FIELD_NAMES:

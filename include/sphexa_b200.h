@@ -254,6 +254,10 @@ void sphb200_sim_destroy(sphb200_sim*);
 int sphb200_sim_upload(sphb200_sim*, size_t n, const sphb200_fields* host_fields);
 /* download assigned range [startIndex,endIndex) of every non-NULL field */
 int sphb200_sim_download(sphb200_sim*, const sphb200_fields* host_fields, uint64_t* keys_h);
+/* One time step on host-resident state: same results as upload + step + download, with the PCIe transfers staged
+ * beside the kernels ({x,y,z} first, {h,m,temp} next, the rest behind the neighbor search; m and alpha return while
+ * MomentumEnergy runs).  host_in/host_out: all 14 conserved fields, pinned memory for overlap.  Single rank only. */
+int sphb200_sim_step_host(sphb200_sim*, size_t n, const sphb200_fields* host_in, const sphb200_fields* host_out);
 /* Domain::sync (domain.hpp:196-244): keys, sort, gather, tree update, layout.  Multi-rank pieces
  * (assignment, migration, halo discovery) are driven by the host through the calls further down. */
 int sphb200_sim_sync(sphb200_sim*);

@@ -225,6 +225,10 @@ struct sphb200_sim
     cudaEvent_t ev[kNumPhases + 1];
     bool evValid[kNumPhases + 1] = {};
 
+    // sphb200_sim_step_host: copy engines run beside the compute stream
+    cudaStream_t copyIn = nullptr, copyOut = nullptr;
+    cudaEvent_t evUp[3] = {}, evDown[2] = {};
+
     int elemBytes(int id) const
     {
         int k = kKind[id];
@@ -351,6 +355,13 @@ extern "C" void sphb200_sim_destroy(sphb200_sim* s)
     cudaFree(s->internalToLeaf); cudaFree(s->leafToInternal); cudaFree(s->centers); cudaFree(s->sizes);
     cudaFree(s->layout);
     for (auto& e : s->ev) cudaEventDestroy(e);
+    if (s->copyIn)
+    {
+        cudaStreamDestroy(s->copyIn);
+        cudaStreamDestroy(s->copyOut);
+        for (auto& e : s->evUp) cudaEventDestroy(e);
+        for (auto& e : s->evDown) cudaEventDestroy(e);
+    }
     delete s;
 }
 
@@ -407,12 +418,11 @@ static void updateTree(sphb200_sim* s, Tree& t, unsigned bucket, const uint64_t*
     }
 }
 
-extern "C" int sphb200_sim_sync(sphb200_sim* s)
+// ---- Domain::sync split into the parts that sphb200_sim_step_host overlaps with the upload of later field groups
+//! @brief global box, SFC keys, sort permutation, global tree (needs x, y, z only)
+static void syncKeys(sphb200_sim* s)
 {
-    SPHB200_TRY
     auto* ctx = s->ctx;
-    ctx->packValid = 0;
-    s->mark(0);
     size_t numAssigned = s->end - s->start;
     auto* x = static_cast<double*>(s->field[F_x]) + s->start;
     auto* y = static_cast<double*>(s->field[F_y]) + s->start;
@@ -442,24 +452,33 @@ extern "C" int sphb200_sim_sync(sphb200_sim* s)
 
     // low-res global tree (assignment, load balance); single rank: no reduction needed
     updateTree(s, s->global, s->cfg.bucketSize, keys, numAssigned);
+}
 
-    // reorder all conserved fields into SFC order (gatherArrays, domain/layout.hpp:209)
+//! @brief reorder the given conserved fields into SFC order (gatherArrays, domain/layout.hpp:209)
+static void gatherConserved(sphb200_sim* s, const int* ids, int count)
+{
+    size_t numAssigned = s->end - s->start;
+    const void* src[kNumConserved];
+    void* dst[kNumConserved];
+    int eb[kNumConserved];
+    for (int k = 0; k < count; ++k)
     {
-        const void* src[kNumConserved];
-        void* dst[kNumConserved];
-        int eb[kNumConserved];
-        for (int id = 0; id < kNumConserved; ++id)
-        {
-            eb[id]  = s->elemBytes(id);
-            src[id] = static_cast<char*>(s->field[id]) + size_t(s->start) * eb[id];
-            dst[id] = static_cast<char*>(s->fieldAlt[id]) + size_t(s->start) * eb[id];
-        }
-        CHECK_RC(sphb200_gather(ctx, s->perm, numAssigned, kNumConserved, src, dst, eb));
-        for (int id = 0; id < kNumConserved; ++id)
-            std::swap(s->field[id], s->fieldAlt[id]);
+        int id = ids[k];
+        eb[k]  = s->elemBytes(id);
+        src[k] = static_cast<char*>(s->field[id]) + size_t(s->start) * eb[k];
+        dst[k] = static_cast<char*>(s->fieldAlt[id]) + size_t(s->start) * eb[k];
     }
+    CHECK_RC(sphb200_gather(s->ctx, s->perm, numAssigned, count, src, dst, eb));
+    for (int k = 0; k < count; ++k)
+        std::swap(s->field[ids[k]], s->fieldAlt[ids[k]]);
+}
 
-    // focus tree = bucketSizeFocus tree over the assigned keys (single rank: whole SFC range is in focus)
+//! @brief focus tree = bucketSizeFocus tree over the assigned keys (single rank: whole SFC range is in focus)
+static void syncFocus(sphb200_sim* s)
+{
+    auto* ctx = s->ctx;
+    size_t numAssigned = s->end - s->start;
+    uint64_t* keys     = s->keys + s->start;
     updateTree(s, s->focus, s->cfg.bucketSizeFocus, keys, numAssigned);
     int L = s->focus.numLeaves;
     CHECK_RC(sphb200_build_octree(ctx, s->focus.leaves, L, s->prefixes, s->childOffsets, s->parents, s->levelRange,
@@ -467,6 +486,19 @@ extern "C" int sphb200_sim_sync(sphb200_sim* s)
     CHECK_RC(sphb200_node_centers(ctx, s->prefixes, L + (L - 1) / 7, &s->box, s->centers, s->sizes));
     CHECK_RC(sphb200_layout(ctx, s->focus.counts, L, s->layout));
     s->n = s->end; // single rank: no halos
+}
+
+extern "C" int sphb200_sim_sync(sphb200_sim* s)
+{
+    SPHB200_TRY
+    s->ctx->packValid = 0;
+    s->mark(0);
+    syncKeys(s);
+    int all[kNumConserved];
+    for (int id = 0; id < kNumConserved; ++id)
+        all[id] = id;
+    gatherConserved(s, all, kNumConserved);
+    syncFocus(s);
     s->mark(1);
     SPHB200_CATCH
 }
@@ -560,6 +592,91 @@ extern "C" int sphb200_sim_step(sphb200_sim* s)
     CHECK_RC(sphb200_sim_sync(s));
     CHECK_RC(sphb200_sim_compute_forces(s));
     CHECK_RC(sphb200_sim_integrate(s, -1.0));
+    SPHB200_CATCH
+}
+
+/*! @brief one time step on host-resident state: upload, Propagator::sync/computeForces/integrate, download
+ *
+ * Same work and same results as upload + step + download, but the three transfers are staged so that the PCIe copies
+ * run beside the kernels: {x,y,z} go first (keys and sort need nothing else), {h,m,temp} next (tree, neighbor search,
+ * XMass, gradh, EOS), the velocity/history/alpha group is only needed from IAD on and rides behind ~20 ms of compute.
+ * m is final after the reorder and alpha after AVswitches, so they are sent back while MomentumEnergy runs; the other
+ * fields are rewritten by the position update, the last kernel of the step (its time step is a global minimum over
+ * MomentumEnergy), and follow after it.
+ */
+extern "C" int sphb200_sim_step_host(sphb200_sim* s, size_t n, const sphb200_fields* host_in,
+                                     const sphb200_fields* host_out)
+{
+    SPHB200_TRY
+    if (n > s->capacity) throw std::runtime_error("sim_step_host: n exceeds capacity");
+    auto* ctx = s->ctx;
+    if (!s->copyIn)
+    {
+        SPHB200_CUDA(cudaStreamCreateWithFlags(&s->copyIn, cudaStreamNonBlocking));
+        SPHB200_CUDA(cudaStreamCreateWithFlags(&s->copyOut, cudaStreamNonBlocking));
+        for (auto& e : s->evUp) SPHB200_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        for (auto& e : s->evDown) SPHB200_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    }
+    // everything issued earlier on the compute stream (e.g. a previous step) must be done before fields are overwritten
+    SPHB200_CUDA(cudaStreamSynchronize(ctx->stream));
+    ctx->packValid = 0;
+    s->n = s->end = uint32_t(n);
+    s->start      = 0;
+
+    static const int groupA[] = {F_x, F_y, F_z};
+    static const int groupB[] = {F_h, F_m, F_temp};
+    static const int groupC[] = {F_vx, F_vy, F_vz, F_x_m1, F_y_m1, F_z_m1, F_du_m1, F_alpha};
+    static const int groupAB[] = {F_x, F_y, F_z, F_h, F_m, F_temp};
+    sphb200_fields hin = *host_in, hout = *host_out;
+    auto upload = [&](const int* ids, int count, cudaEvent_t done)
+    {
+        for (int k = 0; k < count; ++k)
+        {
+            void* src = *fieldSlot(hin, ids[k]);
+            if (!src) throw std::runtime_error("sim_step_host: all conserved fields are required in host_in");
+            SPHB200_CUDA(cudaMemcpyAsync(s->field[ids[k]], src, n * s->elemBytes(ids[k]), cudaMemcpyHostToDevice,
+                                         s->copyIn));
+        }
+        SPHB200_CUDA(cudaEventRecord(done, s->copyIn));
+    };
+    auto download = [&](int id, cudaStream_t stream)
+    {
+        void* dst = *fieldSlot(hout, id);
+        if (dst)
+            SPHB200_CUDA(cudaMemcpyAsync(dst, s->field[id], n * s->elemBytes(id), cudaMemcpyDeviceToHost, stream));
+    };
+    upload(groupA, 3, s->evUp[0]);
+    upload(groupB, 3, s->evUp[1]);
+    upload(groupC, 8, s->evUp[2]);
+
+    SPHB200_CUDA(cudaStreamWaitEvent(ctx->stream, s->evUp[0], 0));
+    s->mark(0);
+    syncKeys(s);
+    SPHB200_CUDA(cudaStreamWaitEvent(ctx->stream, s->evUp[1], 0));
+    gatherConserved(s, groupAB, 6);
+    syncFocus(s);
+    s->mark(1);
+    SPHB200_CUDA(cudaEventRecord(s->evDown[0], ctx->stream));
+    SPHB200_CUDA(cudaStreamWaitEvent(s->copyOut, s->evDown[0], 0));
+    download(F_m, s->copyOut);
+
+    CHECK_RC(sphb200_sim_forces_phase(s, 0));
+    CHECK_RC(sphb200_sim_forces_phase(s, 1));
+    SPHB200_CUDA(cudaStreamWaitEvent(ctx->stream, s->evUp[2], 0));
+    gatherConserved(s, groupC, 8);
+    ctx->packValid &= 1u; // only the position record (x, y, z, m) is still current
+    CHECK_RC(sphb200_sim_forces_phase(s, 2));
+    CHECK_RC(sphb200_sim_forces_phase(s, 3));
+    SPHB200_CUDA(cudaEventRecord(s->evDown[1], ctx->stream));
+    SPHB200_CUDA(cudaStreamWaitEvent(s->copyOut, s->evDown[1], 0));
+    download(F_alpha, s->copyOut);
+    CHECK_RC(sphb200_sim_forces_phase(s, 4));
+    CHECK_RC(sphb200_sim_integrate(s, -1.0));
+
+    for (int id = 0; id < kNumConserved; ++id)
+        if (id != F_m && id != F_alpha) download(id, ctx->stream);
+    SPHB200_CUDA(cudaStreamSynchronize(ctx->stream));
+    SPHB200_CUDA(cudaStreamSynchronize(s->copyOut));
     SPHB200_CATCH
 }
 

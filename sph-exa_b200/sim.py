@@ -104,6 +104,11 @@ class HydroVeProp:
             out["keys"] = keys
         return out
 
+    def step_host(self, fin, fout, n):
+        """one time step on host-resident state (transfers overlapped with the kernels); fin/fout: binding.Fields of
+        pinned host pointers for the 14 conserved fields"""
+        check(lib.sphb200_sim_step_host(self.h, C.c_size_t(n), C.byref(fin), C.byref(fout)))
+
     def download_into(self, f_struct):
         check(lib.sphb200_sim_download(self.h, C.byref(f_struct), None))
 

@@ -297,3 +297,43 @@ def test_errors_are_reported(pkg, ctx):
     with pytest.raises(pkg.SphError, match="capacity"):
         gs.upload(f)
     gs.close()
+
+
+@pytest.mark.parametrize("real", [np.float64, np.float32])
+def test_step_host_equals_upload_step_download(pkg, ctx, real):
+    """sphb200_sim_step_host stages the PCIe copies beside the kernels; the state it returns must be bit-identical to
+    upload + step + download on the same inputs, step after step"""
+    import torch
+    from sph_exa_b200 import sim as S, binding as B
+    dtype = pkg.F64 if real == np.float64 else pkg.MIXED
+    f, box, s = pkg.ic.sedov(24, "f64" if real == np.float64 else "mixed")
+    n = f["x"].size
+    a = S.HydroVeProp(ctx, box, s, capacity=n, dtype=dtype)
+    b = S.HydroVeProp(ctx, box, s, capacity=n, dtype=dtype)
+    a.upload(f)
+    bufs = []
+    for _ in range(2):
+        d = {}
+        for k in B.CONSERVED:
+            want = np.float64 if k in B.ALWAYS_F64 else real
+            d[k] = torch.empty(n, dtype=torch.float64 if want == np.float64 else torch.float32).pin_memory()
+        bufs.append(d)
+    for k in B.CONSERVED:
+        bufs[0][k].numpy()[:] = f[k]
+
+    def struct(d):
+        st = B.Fields()
+        for k in B.FIELD_NAMES:
+            setattr(st, k, d[k].data_ptr() if k in d else None)
+        return st
+
+    for step in range(3):
+        a.step()
+        want = a.download()
+        b.step_host(struct(bufs[0]), struct(bufs[1]), n)
+        for k in B.CONSERVED:
+            assert np.array_equal(bufs[1][k].numpy(), want[k]), (step, k)
+        assert b.minDt == a.minDt
+        bufs.reverse()
+    a.close()
+    b.close()
