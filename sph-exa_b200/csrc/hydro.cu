@@ -99,7 +99,8 @@ __device__ __forceinline__ T lookup(const T* __restrict__ table, T v)
 // sector), not by DRAM.  Each operator therefore first packs the neighbor-side fields it reads into 32-byte
 // (f64) / 16-byte (mixed) records with one streaming pass, so that a pair costs one 256-bit load per record instead
 // of four 64-bit loads that each touch their own lines:
-//   R0 {x, y, z, m}   R1 {vx, vy, vz, h}   R2 {xm, xm/kx, c, prho}   R3 {c11, c12, c13, c22}
+//   P {x, y, z, m} (XMass, gradh, momentum)   Pxm {x, y, z, xm} + VV {vx, vy, vz, xm/kx} (IAD)
+//   Pc {x, y, z, c} + VV (AV switches)   R3 {c11, c12, c13, c22}
 //   R5 {dV11, dV12, dV13, dV22}   R6 {dV23, dV33, -, -}   (avClean only)
 //   momentum only: M1 {vx, vy, vz, 1/h}   M2 {xm, c, prho, rho}   M4 {c23, c33, alpha, m/rho}
 // Quantities of the reference J-loops that depend on j alone (V_j = xm_j/kx_j, 1/h_j, rho_j = kx_j m_j/xm_j, m_j/rho_j)
@@ -193,17 +194,15 @@ __global__ void __launch_bounds__(256) pack4Kernel(size_t n, const T* __restrict
     out[i] = r;
 }
 
-//! @brief R2 = {xm, V = xm/kx, c, prho}; volume element as in iad_kern.hpp:75 / av_switches_kern.hpp:103
+//! @brief VV = {vx, vy, vz, V = xm/kx}; volume element as in iad_kern.hpp:75 / av_switches_kern.hpp:103
 template<class T>
-__global__ void __launch_bounds__(256) packStateKernel(size_t n, const T* __restrict__ xm, const T* __restrict__ kx,
-                                                       const T* __restrict__ c, const T* __restrict__ prho,
-                                                       Rec4<T>* __restrict__ out)
+__global__ void __launch_bounds__(256) packVelVolKernel(size_t n, const T* __restrict__ vx, const T* __restrict__ vy,
+                                                        const T* __restrict__ vz, const T* __restrict__ xm,
+                                                        const T* __restrict__ kx, Rec4<T>* __restrict__ out)
 {
     size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    Rec4<T> r;
-    r.a = xm[i]; r.b = xm[i] / kx[i]; r.c = c ? c[i] : T(0); r.d = prho ? prho[i] : T(0);
-    out[i] = r;
+    out[i] = {vx[i], vy[i], vz[i], xm[i] / kx[i]};
 }
 
 //! @brief momentum records M1, M2, M4 with the j-only terms of momentum_energy_kern.hpp:96-97,116-117,165
@@ -294,8 +293,11 @@ __device__ __forceinline__ NbList nbList(const uint32_t* nidx, const uint32_t* n
         if (j##_next = (pj + 1 < (nb).count) ? (nb)[pj + 1] : 0u, true)
 
 // ---------------------------------------------------------------- XMass (xmass_kern.hpp:50-78)
+#ifndef SPHB200_XMASS_MIN_BLOCKS
+#define SPHB200_XMASS_MIN_BLOCKS 1
+#endif
 template<bool Pbc, class T>
-__global__ void __launch_bounds__(kHydroBlock)
+__global__ void __launch_bounds__(kHydroBlock, SPHB200_XMASS_MIN_BLOCKS)
     xmassKernel(uint32_t first, uint32_t last, unsigned ngmax, double K, PbcBox box, const uint32_t* __restrict__ nidx,
                 F<T> f, const PosRec<T>* __restrict__ r0, const Rec2<T>* __restrict__ wh)
 {
@@ -324,8 +326,11 @@ __global__ void __launch_bounds__(kHydroBlock)
 }
 
 // ---------------------------------------------------------------- VeDefGradh (ve_def_gradh_kern.hpp:43-90)
+#ifndef SPHB200_GRADH_MIN_BLOCKS
+#define SPHB200_GRADH_MIN_BLOCKS 1
+#endif
 template<bool Pbc, class T>
-__global__ void __launch_bounds__(kHydroBlock)
+__global__ void __launch_bounds__(kHydroBlock, SPHB200_GRADH_MIN_BLOCKS)
     veDefGradhKernel(uint32_t first, uint32_t last, unsigned ngmax, double K, PbcBox box,
                      const uint32_t* __restrict__ nidx, F<T> f, const PosRec<T>* __restrict__ r0,
                      const Rec4<T>* __restrict__ whq)
@@ -395,21 +400,23 @@ __global__ void eosKernel(uint32_t first, uint32_t last, F<T> f, T muiConst, dou
 // One sweep: besides tau_ab = sum_j r_a r_b V_j W the sweep accumulates S_ab = sum_j (v_ji,a xm_j) W r_b; the
 // velocity gradient of divv_curlv_kern.hpp, dV_a[b] = sum_j (v_ji,a xm_j) * (-(C_i r)_b W), equals -(C_i S_a)_b
 // because C_i does not depend on j.  Same sums in the same order, C_i applied after instead of inside the loop.
+#ifndef SPHB200_IAD_MIN_BLOCKS
+#define SPHB200_IAD_MIN_BLOCKS 6 // <= 80 registers: 24 warps/SM instead of 16 (measured 6.9 -> 5.75 ms)
+#endif
 template<bool Pbc, class T>
-__global__ void __launch_bounds__(kHydroBlock)
+__global__ void __launch_bounds__(kHydroBlock, SPHB200_IAD_MIN_BLOCKS)
     iadDivvCurlvKernel(uint32_t first, uint32_t last, unsigned ngmax, double K, PbcBox box,
                        const uint32_t* __restrict__ nidx, F<T> f, const PosRec<T>* __restrict__ r0,
-                       const Rec4<T>* __restrict__ r1, const Rec4<T>* __restrict__ r2,
-                       const Rec2<T>* __restrict__ wh, bool doGradV)
+                       const Rec4<T>* __restrict__ r1, const Rec2<T>* __restrict__ wh, bool doGradV)
 {
     uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= last) return;
     NbList nb = nbList(nidx, f.nc, first, i, ngmax);
 
-    PosRec<T> pi = r0[i];
-    Rec4<T> vi   = r1[i];
+    PosRec<T> pi = r0[i]; // {x, y, z, xm}
+    Rec4<T> vi   = r1[i]; // {vx, vy, vz, V}
     double xi = pi.x, yi = pi.y, zi = pi.z;
-    T vxi = vi.a, vyi = vi.b, vzi = vi.c, hi = vi.d;
+    T vxi = vi.a, vyi = vi.b, vzi = vi.c, hi = f.h[i];
     T hiInv = T(1) / hi;
 
     T tau11 = 0.0, tau12 = 0.0, tau13 = 0.0, tau22 = 0.0, tau23 = 0.0, tau33 = 0.0;
@@ -418,13 +425,13 @@ __global__ void __launch_bounds__(kHydroBlock)
     {
         PosRec<T> pj_ = ldRec(r0, j);
         Rec4<T> vj    = ldRec(r1, j);
-        Rec2<T> xk    = ldHalf(r2, j); // {xm_j, V_j}
+        T xmassj = pj_.m, volj = vj.d; // 4th slots: xm_j and V_j = xm_j / kx_j
         T rx = xi - pj_.x, ry = yi - pj_.y, rz = zi - pj_.z;
         if (Pbc) applyPBC(box, T(2) * hi, rx, ry, rz);
         T dist   = sqrt(rx * rx + ry * ry + rz * rz);
         T vloc   = dist * hiInv;
         T w      = lookup(wh, vloc);
-        T volj_w = xk.b * w;
+        T volj_w = volj * w;
 
         tau11 += rx * rx * volj_w;
         tau12 += rx * ry * volj_w;
@@ -434,7 +441,7 @@ __global__ void __launch_bounds__(kHydroBlock)
         tau33 += rz * rz * volj_w;
 
         T wx = w * rx, wy = w * ry, wz = w * rz;
-        T sx = (vj.a - vxi) * xk.a, sy = (vj.b - vyi) * xk.a, sz = (vj.c - vzi) * xk.a;
+        T sx = (vj.a - vxi) * xmassj, sy = (vj.b - vyi) * xmassj, sz = (vj.c - vzi) * xmassj;
         Sx[0] += sx * wx; Sx[1] += sx * wy; Sx[2] += sx * wz;
         Sy[0] += sy * wx; Sy[1] += sy * wy; Sy[2] += sy * wz;
         Sz[0] += sz * wx; Sz[1] += sz * wy; Sz[2] += sz * wz;
@@ -497,35 +504,37 @@ __global__ void __launch_bounds__(kHydroBlock)
 
 // ---------------------------------------------------------------- AV switches (av_switches_kern.hpp:44-137)
 // graddivv_b = sum_j factor_j * (-(C_i r)_b K h^-3 W): C_i, K h^-3 are constant in j and applied after the sweep.
+#ifndef SPHB200_AV_MIN_BLOCKS
+#define SPHB200_AV_MIN_BLOCKS 7 // <= 72 registers: 28 warps/SM (measured 6.6 -> 6.2 ms)
+#endif
 template<bool Pbc, class T>
-__global__ void __launch_bounds__(kHydroBlock)
+__global__ void __launch_bounds__(kHydroBlock, SPHB200_AV_MIN_BLOCKS)
     avSwitchesKernel(uint32_t first, uint32_t last, unsigned ngmax, double K, PbcBox box,
                      const uint32_t* __restrict__ nidx, F<T> f, const PosRec<T>* __restrict__ r0,
-                     const Rec4<T>* __restrict__ r1, const Rec4<T>* __restrict__ r2, const Rec2<T>* __restrict__ wh,
-                     double dt, T alphamin, T alphamax, T decay_constant)
+                     const Rec4<T>* __restrict__ r1, const Rec2<T>* __restrict__ wh, double dt, T alphamin, T alphamax,
+                     T decay_constant)
 {
     uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= last) return;
     NbList nb = nbList(nidx, f.nc, first, i, ngmax);
 
-    PosRec<T> pi = r0[i];
-    Rec4<T> vi   = r1[i];
+    PosRec<T> pi = r0[i]; // {x, y, z, divv}
+    Rec4<T> vi   = r1[i]; // {vx, vy, vz, V}
     double xi = pi.x, yi = pi.y, zi = pi.z;
-    T vxi = vi.a, vyi = vi.b, vzi = vi.c, hi = vi.d;
+    T vxi = vi.a, vyi = vi.b, vzi = vi.c, hi = f.h[i];
     T ci = f.c[i];
 
     T vijsignal_i = T(1.e-40) * ci;
     T hiInv  = T(1) / hi;
     T hiInv3 = hiInv * hiInv * hiInv;
-    T divv_i = f.divv[i];
+    T divv_i = pi.m;
 
     T gx = 0.0, gy = 0.0, gz = 0.0;
     FOR_NEIGHBORS(nb, j)
     {
         PosRec<T> pj_ = ldRec(r0, j);
         Rec4<T> vj    = ldRec(r1, j);
-        Rec4<T> sj    = ldRec(r2, j); // {xm, V, c, prho}
-        T divv_j      = LD(f.divv, j);
+        T divv_j      = pj_.m; // 4th slot of the position record
         T rx = xi - pj_.x, ry = yi - pj_.y, rz = zi - pj_.z;
         if (Pbc) applyPBC(box, T(2) * hi, rx, ry, rz);
         T r2_  = rx * rx + ry * ry + rz * rz;
@@ -537,13 +546,13 @@ __global__ void __launch_bounds__(kHydroBlock)
 
         T rv           = rx * vx_ij + ry * vy_ij + rz * vz_ij;
         T vijsignal_ij = 0.0;
-        if (rv < T(0)) { vijsignal_ij = ci + sj.c - T(3) * rv / dist; }
+        if (rv < T(0)) { vijsignal_ij = ci + LD(f.c, j) - T(3) * rv / dist; } // c_j only for approaching pairs
         vijsignal_i = max(vijsignal_i, vijsignal_ij);
 
         T v1 = dist * hiInv;
         T w  = lookup(wh, v1);
 
-        T volj   = sj.b;
+        T volj   = vj.d;
         T factor = volj * (divv_i - divv_j) * w;
 
         gx += factor * rx;
@@ -902,7 +911,7 @@ static unsigned long long* dtKeys(sphb200_ctx* ctx) { return reinterpret_cast<un
 // Records live in grow-only context arenas.  A stand-alone operator call (tier 1) repacks what it reads on every call
 // because the caller may have changed the arrays in between; a sphb200_sim (tier 2) sets ctx->packReuse and
 // invalidates records itself whenever a member field is rewritten (see invalidate() calls below and in api.cu).
-enum RecId { R_POS, R_VEL, R_STATE, R_CA, R_GA, R_GB, R_MVEL, R_MSTATE, R_MCB, kNumRecs };
+enum RecId { R_POS, R_PXM, R_PDIVV, R_VV, R_CA, R_GA, R_GB, R_MVEL, R_MSTATE, R_MCB, kNumRecs };
 static_assert(kNumRecs <= sphb200_ctx::kMaxRecs, "record arenas");
 
 static void beginOp(sphb200_ctx* ctx)
@@ -920,7 +929,8 @@ static const void* ensureRec(sphb200_ctx* ctx, int k, const sphb200_fields& f)
 {
     size_t n = f.n;
     if (n == 0) throw std::runtime_error("sphb200_fields.n (array length incl. halos) must be set");
-    size_t bytes = n * (k == R_POS ? sizeof(PosRec<T>) : sizeof(Rec4<T>));
+    bool isPos   = k == R_POS || k == R_PXM || k == R_PDIVV;
+    size_t bytes = n * (isPos ? sizeof(PosRec<T>) : sizeof(Rec4<T>));
     void* out    = ctx->rec[k].get(bytes);
     if (ctx->packValid & (1u << k)) return out;
     F<T> t   = typed<T>(f);
@@ -930,11 +940,16 @@ static const void* ensureRec(sphb200_ctx* ctx, int k, const sphb200_fields& f)
     switch (k)
     {
         case R_POS:
-            SPHB200_LAUNCH(ctx, packPosKernel<T>, grid, 256, 0, n, t.x, t.y, t.z, t.m, static_cast<PosRec<T>*>(out));
+        case R_PXM:
+        case R_PDIVV:
+        {
+            const T* fourth = k == R_POS ? t.m : (k == R_PXM ? t.xm : t.divv);
+            SPHB200_LAUNCH(ctx, packPosKernel<T>, grid, 256, 0, n, t.x, t.y, t.z, fourth, static_cast<PosRec<T>*>(out));
             break;
-        case R_VEL: p4(t.vx, t.vy, t.vz, t.h); break;
-        case R_STATE:
-            SPHB200_LAUNCH(ctx, packStateKernel<T>, grid, 256, 0, n, t.xm, t.kx, t.c, t.prho, static_cast<Rec4<T>*>(out));
+        }
+        case R_VV:
+            SPHB200_LAUNCH(ctx, packVelVolKernel<T>, grid, 256, 0, n, t.vx, t.vy, t.vz, t.xm, t.kx,
+                           static_cast<Rec4<T>*>(out));
             break;
         case R_CA: p4(t.c11, t.c12, t.c13, t.c22); break;
         case R_GA: p4(t.dV11, t.dV12, t.dV13, t.dV22); break;
@@ -1018,7 +1033,7 @@ extern "C" int sphb200_xmass(sphb200_ctx* ctx, int dtype, uint32_t first, uint32
              auto* r0 = static_cast<const PosRec<T>*>(ensureRec<T>(ctx, R_POS, *f));
              LAUNCH_PBC(ctx, *box, xmassKernel, gridFor(last - first, kHydroBlock), first, last, hc->ngmax, hc->K,
                         pbcBox(*box), neighbors, typed<T>(*f), r0, wh););
-    invalidate(ctx, {R_STATE});
+    invalidate(ctx, {R_PXM, R_VV}); // xm rewritten
     SPHB200_CATCH
 }
 
@@ -1033,7 +1048,7 @@ extern "C" int sphb200_ve_def_gradh(sphb200_ctx* ctx, int dtype, uint32_t first,
              auto* r0 = static_cast<const PosRec<T>*>(ensureRec<T>(ctx, R_POS, *f));
              LAUNCH_PBC(ctx, *box, veDefGradhKernel, gridFor(last - first, kHydroBlock), first, last, hc->ngmax, hc->K,
                         pbcBox(*box), neighbors, typed<T>(*f), r0, whq););
-    invalidate(ctx, {R_STATE});
+    invalidate(ctx, {R_VV}); // kx rewritten
     SPHB200_CATCH
 }
 
@@ -1044,7 +1059,6 @@ extern "C" int sphb200_eos(sphb200_ctx* ctx, int dtype, uint32_t first, uint32_t
     if (last <= first) return 0;
     DISPATCH(dtype, SPHB200_LAUNCH(ctx, eosKernel<T>, gridFor(last - first, 256), 256, 0, first, last, typed<T>(*f),
                                    T(hc->muiConst), hc->gamma););
-    invalidate(ctx, {R_STATE});
     SPHB200_CATCH
 }
 
@@ -1057,12 +1071,11 @@ extern "C" int sphb200_iad_divv_curlv(sphb200_ctx* ctx, int dtype, uint32_t firs
     beginOp(ctx);
     bool doGradV = f->dV11 != nullptr;
     DISPATCH(dtype, const Rec2<T>* wh; const Rec4<T>* whq; ensureTables<T>(ctx, hc, wh, whq);
-             auto* r0 = static_cast<const PosRec<T>*>(ensureRec<T>(ctx, R_POS, *f));
-             auto* r1 = static_cast<const Rec4<T>*>(ensureRec<T>(ctx, R_VEL, *f));
-             auto* r2 = static_cast<const Rec4<T>*>(ensureRec<T>(ctx, R_STATE, *f));
+             auto* r0 = static_cast<const PosRec<T>*>(ensureRec<T>(ctx, R_PXM, *f));
+             auto* r1 = static_cast<const Rec4<T>*>(ensureRec<T>(ctx, R_VV, *f));
              LAUNCH_PBC(ctx, *box, iadDivvCurlvKernel, gridFor(last - first, kHydroBlock), first, last, hc->ngmax,
-                        hc->K, pbcBox(*box), neighbors, typed<T>(*f), r0, r1, r2, wh, doGradV););
-    invalidate(ctx, {R_CA, R_GA, R_GB});
+                        hc->K, pbcBox(*box), neighbors, typed<T>(*f), r0, r1, wh, doGradV););
+    invalidate(ctx, {R_PDIVV, R_CA, R_GA, R_GB}); // divv and c_ab rewritten
     SPHB200_CATCH
 }
 
@@ -1073,11 +1086,10 @@ extern "C" int sphb200_av_switches(sphb200_ctx* ctx, int dtype, uint32_t first, 
     if (last <= first) return 0;
     beginOp(ctx);
     DISPATCH(dtype, const Rec2<T>* wh; const Rec4<T>* whq; ensureTables<T>(ctx, hc, wh, whq);
-             auto* r0 = static_cast<const PosRec<T>*>(ensureRec<T>(ctx, R_POS, *f));
-             auto* r1 = static_cast<const Rec4<T>*>(ensureRec<T>(ctx, R_VEL, *f));
-             auto* r2 = static_cast<const Rec4<T>*>(ensureRec<T>(ctx, R_STATE, *f));
+             auto* r0 = static_cast<const PosRec<T>*>(ensureRec<T>(ctx, R_PDIVV, *f));
+             auto* r1 = static_cast<const Rec4<T>*>(ensureRec<T>(ctx, R_VV, *f));
              LAUNCH_PBC(ctx, *box, avSwitchesKernel, gridFor(last - first, kHydroBlock), first, last, hc->ngmax, hc->K,
-                        pbcBox(*box), neighbors, typed<T>(*f), r0, r1, r2, wh, hc->minDt, T(hc->alphamin),
+                        pbcBox(*box), neighbors, typed<T>(*f), r0, r1, wh, hc->minDt, T(hc->alphamin),
                         T(hc->alphamax), T(hc->decay_constant)););
     SPHB200_CATCH
 }
