@@ -155,6 +155,29 @@ def cpu_baseline(pkg, dtype, side=80, steps=2):
             "find_neighbors_ms": sim.times["FindNeighbors"] * 1e3}
 
 
+NCU_KERNEL = {"MomentumAndEnergy": "momentumEnergyKernel", "AVswitches": "avSwitchesKernel",
+              "IadVelocityDivCurl": "iadDivvCurlvKernel", "FindNeighbors": "findNeighborsKernel",
+              "XMass": "xmassKernel", "Normalization & Gradh": "veDefGradhKernel"}
+
+
+def ncu_traffic(phase, args):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed
+    `ncu --set full` capture of this same workload (profiles/ncu_full_r01c_summary.csv: Sedov 200^3, f64).
+    None for any other workload: the capture does not transfer."""
+    import csv
+    path = os.path.join(ROOT, "profiles", "ncu_full_r01c_summary.csv")
+    if args.side != 200 or args.dtype != "f64" or phase not in NCU_KERNEL or not os.path.exists(path):
+        return None, None
+    with open(path) as fh:
+        rows = list(csv.reader(fh))
+    hdr = rows[0]
+    ir, iw = hdr.index("dram_read [Gbyte]"), hdr.index("dram_write [Gbyte]")
+    for r in rows[1:]:
+        if NCU_KERNEL[phase] in r[0]:
+            return (float(r[ir]) + float(r[iw])) * 1e9, "profiles/ncu_full_r01c_summary.csv"
+    return None, None
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -230,8 +253,9 @@ def main():
     col = 0 if args.dtype == "f64" else 1
     algo = ALGO_BYTES[dom][col] * n
     achieved = algo / (phase_ms[dom] * 1e-3) / 1e9
+    traffic, traffic_src = ncu_traffic(dom, args)
     roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": algo, "kernel_ms": phase_ms[dom],
                 "share_of_step": phase_ms[dom] / sum(phase_ms.values())}
     # whole-step algorithmic traffic (1360 B f64 / 920 B mixed per particle-step)
