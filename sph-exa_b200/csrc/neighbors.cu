@@ -123,6 +123,229 @@ __device__ __forceinline__ void testLeaf(const double* __restrict__ x, const dou
     }
 }
 
+constexpr int kFrontier = 256; // nodes per level of the breadth-first walk; larger walks fall back to the DFS
+
+//! @brief extents of the warp's (active) target positions and its largest squared search radius
+struct TargetGroup
+{
+    double lo[3], hi[3];
+    double rmaxSq;
+};
+
+//! @brief inclusive warp prefix sum
+__device__ __forceinline__ int warpInclusiveScan(int v, int lane)
+{
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1)
+    {
+        int t = __shfl_up_sync(0xffffffffu, v, o);
+        if (lane >= o) v += t;
+    }
+    return v;
+}
+
+/*! @brief level-wise tree walk + pipelined, prefiltered leaf tests (the main search path)
+ *
+ * 1. The octree is walked breadth-first with one lane per frontier node (8 independent child tests per lane instead
+ *    of one dependent node visit per step); children replace their parent in place, so the frontier stays in
+ *    ascending SFC order and so do the neighbor lists.
+ * 2. One lane per leaf: particle range + cull of the leaf's tight extents against the box of the target positions.
+ * 3. The surviving ranges are streamed in 32-particle chunks; the loads of chunk c+1 are in flight while chunk c is
+ *    tested.  Each lane first checks ITS candidate against the target box: a candidate farther than the largest
+ *    search radius from that box is nobody's neighbor (about 70 % of the staged particles: the leaves cover a box,
+ *    the neighbors a rounded box).  Survivors are broadcast and tested against all 32 targets with the reference
+ *    arithmetic (distSq).
+ * Both culls are conservative in floating point: for lo <= x_i <= hi, |fl(x_j - x_i)| >= fl(max(lo - x_j, x_j - hi, 0))
+ * since rounding is monotone, and squaring and the left-associated sum of distSq preserve the ordering, so a computed
+ * box distance never exceeds the computed distance to any target inside the box.
+ * With periodic folding (UsePbc) the node tests fold like the DFS and the leaf cull of step 2 is skipped.
+ * @return false if the frontier overflowed (nothing usable was written; the caller runs the DFS instead)
+ */
+template<bool UsePbc>
+__device__ __forceinline__ bool searchBfs(const DevTree& tree, const double* __restrict__ x,
+                                          const double* __restrict__ y, const double* __restrict__ z, int* bufA,
+                                          int* bufB, int* bufC, double* cand, int lane, bool active, LocalIndex i,
+                                           double xi, double yi, double zi, double radiusSq, const double* tc,
+                                           const double* ts, const TargetGroup& tg, const sphb200_box& box,
+                                           unsigned ngmax, uint32_t* myList, unsigned& count)
+{
+    // ---- 1. level-wise walk
+    int* cur = bufA;
+    int* nxt = bufB;
+    int n    = 1;
+    if (lane == 0) cur[0] = 0;
+    __syncwarp();
+    while (true)
+    {
+        int nOut         = 0;
+        bool anyInternal = false;
+        for (int b = 0; b < n; b += 32)
+        {
+            int e      = b + lane;
+            bool have  = e < n;
+            int node   = have ? cur[e] : 0;
+            int child0 = have ? tree.childOffsets[node] : 0;
+            unsigned childMask = 0;
+            if (have && child0 != 0)
+            {
+#pragma unroll
+                for (int c = 0; c < 8; ++c)
+                {
+                    const double* ctr = tree.centers + 3 * size_t(child0 + c);
+                    const double* sz  = tree.sizes + 3 * size_t(child0 + c);
+                    bool ok = true;
+#pragma unroll
+                    for (int d = 0; d < 3; ++d)
+                    {
+                        double dx = ctr[d] - tc[d];
+                        if (UsePbc && box.bc[d] == SPHB200_PERIODIC) dx -= box.len[d] * rint(dx * box.inv[d]);
+                        ok = ok && (fabs(dx) - sz[d] - ts[d] <= 0.0);
+                    }
+                    childMask |= unsigned(ok) << c;
+                }
+            }
+            int emit    = have ? (child0 == 0 ? 1 : __popc(childMask)) : 0;
+            anyInternal = anyInternal || __any_sync(0xffffffffu, have && child0 != 0);
+            int incl    = warpInclusiveScan(emit, lane);
+            int total   = __shfl_sync(0xffffffffu, incl, 31);
+            if (nOut + total > kFrontier) return false;
+            int pos = nOut + incl - emit;
+            if (have)
+            {
+                if (child0 == 0) nxt[pos] = node;
+                else
+                {
+#pragma unroll
+                    for (int c = 0; c < 8; ++c)
+                        if (childMask >> c & 1u) nxt[pos++] = child0 + c;
+                }
+            }
+            nOut += total;
+        }
+        __syncwarp();
+        int* t = cur;
+        cur    = nxt;
+        nxt    = t;
+        n      = nOut;
+        if (!anyInternal) break;
+    }
+
+    // ---- 2. leaves -> particle ranges, culled against the target box
+    int* rb = nxt;
+    int* re = bufC;
+    int nR  = 0;
+    for (int b = 0; b < n; b += 32)
+    {
+        int e     = b + lane;
+        bool keep = false;
+        LocalIndex jb = 0, je = 0;
+        if (e < n)
+        {
+            TreeNodeIndex leafIdx = tree.internalToLeaf[cur[e]];
+            jb = tree.layout[leafIdx];
+            je = tree.layout[leafIdx + 1];
+            const double* lb = tree.leafBounds + 6 * size_t(leafIdx);
+            double ex = fmax(fmax(lb[0] - tg.hi[0], tg.lo[0] - lb[3]), 0.0);
+            double ey = fmax(fmax(lb[1] - tg.hi[1], tg.lo[1] - lb[4]), 0.0);
+            double ez = fmax(fmax(lb[2] - tg.hi[2], tg.lo[2] - lb[5]), 0.0);
+            // (periodic folding: leaf extents are not folded, the per-candidate prefilter below does the work)
+            keep      = je > jb && (UsePbc || ex * ex + ey * ey + ez * ez < tg.rmaxSq);
+        }
+        unsigned m = __ballot_sync(0xffffffffu, keep);
+        if (keep)
+        {
+            int pos = nR + __popc(m & ((1u << lane) - 1));
+            rb[pos] = int(jb);
+            re[pos] = int(je);
+        }
+        nR += __popc(m);
+    }
+    __syncwarp();
+    if (nR == 0) return true;
+
+    // ---- 3. stream the ranges, one chunk ahead
+    // periodic case: candidates are moved to the image nearest to the centre of the target box for the prefilter only
+    // (the caller guarantees box half-size + search radius < len/4, so that image is the one every target would
+    // pick); the 1e-9 margin covers the different rounding order, membership is decided by distSq<true> as always
+    const double tgc[3]  = {0.5 * (tg.lo[0] + tg.hi[0]), 0.5 * (tg.lo[1] + tg.hi[1]), 0.5 * (tg.lo[2] + tg.hi[2])};
+    const double rFilter = UsePbc ? tg.rmaxSq * (1.0 + 1e-9) : tg.rmaxSq;
+    int* candIdx         = cur; // the frontier is no longer needed
+    int li = 0;
+    LocalIndex base = LocalIndex(rb[0]), end = LocalIndex(re[0]);
+    double X = 0, Y = 0, Z = 0;
+    bool have = base + lane < end;
+    if (have)
+    {
+        X = x[base + lane];
+        Y = y[base + lane];
+        Z = z[base + lane];
+    }
+    while (li < nR)
+    {
+        // prefilter the chunk whose loads were issued one iteration ago and compact the survivors in shared memory
+        bool pass = false;
+        if (have)
+        {
+            double Xs = X, Ys = Y, Zs = Z;
+            if (UsePbc)
+            {
+                if (box.bc[0] == SPHB200_PERIODIC) Xs -= box.len[0] * rint((X - tgc[0]) * box.inv[0]);
+                if (box.bc[1] == SPHB200_PERIODIC) Ys -= box.len[1] * rint((Y - tgc[1]) * box.inv[1]);
+                if (box.bc[2] == SPHB200_PERIODIC) Zs -= box.len[2] * rint((Z - tgc[2]) * box.inv[2]);
+            }
+            double ex = fmax(fmax(tg.lo[0] - Xs, Xs - tg.hi[0]), 0.0);
+            double ey = fmax(fmax(tg.lo[1] - Ys, Ys - tg.hi[1]), 0.0);
+            double ez = fmax(fmax(tg.lo[2] - Zs, Zs - tg.hi[2]), 0.0);
+            pass      = ex * ex + ey * ey + ez * ez < rFilter;
+        }
+        unsigned survivors = __ballot_sync(0xffffffffu, pass);
+        if (pass)
+        {
+            int pos       = __popc(survivors & ((1u << lane) - 1));
+            cand[pos]      = X;
+            cand[32 + pos] = Y;
+            cand[64 + pos] = Z;
+            candIdx[pos]   = int(base + lane);
+        }
+        int ns = __popc(survivors);
+
+        // issue the next chunk's loads
+        base += 32;
+        if (base >= end)
+        {
+            ++li;
+            if (li < nR)
+            {
+                base = LocalIndex(rb[li]);
+                end  = LocalIndex(re[li]);
+            }
+        }
+        have = li < nR && base + lane < end;
+        if (have)
+        {
+            X = x[base + lane];
+            Y = y[base + lane];
+            Z = z[base + lane];
+        }
+        __syncwarp();
+
+        if (active)
+        {
+#pragma unroll 4
+            for (int k = 0; k < ns; ++k)
+            {
+                double d2     = distSq<UsePbc>(cand[k], cand[32 + k], cand[64 + k], xi, yi, zi, box);
+                LocalIndex jj = LocalIndex(candIdx[k]);
+                bool in       = d2 < radiusSq && jj != i;
+                if (in && count < ngmax) myList[size_t(count) * 32] = jj;
+                count += in;
+            }
+        }
+        __syncwarp();
+    }
+    return true;
+}
+
 template<class Th>
 __global__ void __launch_bounds__(kNbWarps * 32)
     findNeighborsKernel(DevTree tree, const double* __restrict__ x, const double* __restrict__ y,
@@ -132,6 +355,7 @@ __global__ void __launch_bounds__(kNbWarps * 32)
 {
     __shared__ TreeNodeIndex stackMem[kNbWarps][kStackSize];
     __shared__ double candMem[kNbWarps][96];
+    __shared__ int frontierMem[kNbWarps][3][kFrontier];
 
     const int lane  = threadIdx.x & 31;
     const int warp  = threadIdx.x >> 5;
@@ -163,27 +387,36 @@ __global__ void __launch_bounds__(kNbWarps * 32)
         double radiusSq = double(radiusSqT);
         double r        = 2.0 * double(hi);
 
-        // bounding box of the active targets' search spheres
+        // bounding box of the active targets' search spheres, and of their positions (candidate prefilter)
         double lo[3] = {xi - r, yi - r, zi - r};
         double hi3[3] = {xi + r, yi + r, zi + r};
+        TargetGroup tg;
+        tg.lo[0] = tg.hi[0] = xi;
+        tg.lo[1] = tg.hi[1] = yi;
+        tg.lo[2] = tg.hi[2] = zi;
+        tg.rmaxSq = radiusSq;
         if (!active)
         {
 #pragma unroll
             for (int d = 0; d < 3; ++d)
             {
-                lo[d]  = INFINITY;
-                hi3[d] = -INFINITY;
+                lo[d] = tg.lo[d] = INFINITY;
+                hi3[d] = tg.hi[d] = -INFINITY;
             }
+            tg.rmaxSq = 0.0;
         }
 #pragma unroll
-        for (int d = 0; d < 3; ++d)
+        for (int o = 16; o > 0; o >>= 1)
         {
 #pragma unroll
-            for (int o = 16; o > 0; o >>= 1)
+            for (int d = 0; d < 3; ++d)
             {
-                lo[d]  = fmin(lo[d], __shfl_xor_sync(0xffffffffu, lo[d], o));
-                hi3[d] = fmax(hi3[d], __shfl_xor_sync(0xffffffffu, hi3[d], o));
+                lo[d]    = fmin(lo[d], __shfl_xor_sync(0xffffffffu, lo[d], o));
+                hi3[d]   = fmax(hi3[d], __shfl_xor_sync(0xffffffffu, hi3[d], o));
+                tg.lo[d] = fmin(tg.lo[d], __shfl_xor_sync(0xffffffffu, tg.lo[d], o));
+                tg.hi[d] = fmax(tg.hi[d], __shfl_xor_sync(0xffffffffu, tg.hi[d], o));
             }
+            tg.rmaxSq = fmax(tg.rmaxSq, __shfl_xor_sync(0xffffffffu, tg.rmaxSq, o));
         }
         double tc[3], ts[3];
         bool inside = true;
@@ -200,9 +433,28 @@ __global__ void __launch_bounds__(kNbWarps * 32)
         const bool usePbc = anyPbc && !inside;
 
         if (active) count = 0;
+        bool done = false;
+        int *fa = frontierMem[warp][0], *fb = frontierMem[warp][1], *fc = frontierMem[warp][2];
+        if (!usePbc)
+        {
+            done = searchBfs<false>(tree, x, y, z, fa, fb, fc, cand, lane, active, i, xi, yi, zi, radiusSq, tc, ts, tg,
+                                    box, ngmax, myList, count);
+        }
+        else
+        {
+            // nearest-image prefilter needs the target box plus the search radius well inside half a period
+            bool small = true;
+#pragma unroll
+            for (int d = 0; d < 3; ++d)
+                small = small && (box.bc[d] != SPHB200_PERIODIC || ts[d] < 0.25 * box.len[d]);
+            if (small)
+                done = searchBfs<true>(tree, x, y, z, fa, fb, fc, cand, lane, active, i, xi, yi, zi, radiusSq, tc, ts,
+                                       tg, box, ngmax, myList, count);
+        }
+        if (!done && active) count = 0;
         int sp = 0;
         if (lane == 0) stack[0] = 0;
-        sp = 1;
+        sp = done ? 0 : 1;
         __syncwarp();
         while (sp > 0)
         {
