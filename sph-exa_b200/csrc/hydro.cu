@@ -637,6 +637,7 @@ __global__ void __launch_bounds__(kHydroBlock, kMomentumMinBlocks)
 
         T hiInv  = vi.d;
         T hiInv3 = hiInv * hiInv * hiInv;
+        T rhoiInv = T(1) / rhoi;
 
         T maxvsignali = 0.0;
         T momentum_x = 0.0, momentum_y = 0.0, momentum_z = 0.0, energy = 0.0;
@@ -712,26 +713,30 @@ __global__ void __launch_bounds__(kHydroBlock, kMomentumMinBlocks)
             T vijsignal = T(0.5) * (ci + cj) - T(2) * wij;
             maxvsignali = (vijsignal > maxvsignali) ? vijsignal : maxvsignali;
 
+            // Atwood = |rho_i - rho_j| / (rho_i + rho_j) selects the branch; the quotient itself is only needed inside
+            // the ramp, so the two common branches compare against Atmin/Atmax * (rho_i + rho_j) without dividing
+            // (the ramp is continuous at both ends, a tie decided the other way changes nothing beyond rounding)
             T a_mom, b_mom;
-            T Atwood = (abs(rhoi - rhoj)) / (rhoi + rhoj);
-            if (Atwood < Atmin)
+            T rhoDiff = abs(rhoi - rhoj), rhoSum = rhoi + rhoj;
+            if (rhoDiff < Atmin * rhoSum)
             {
                 a_mom = xmassi * xmassi;
                 b_mom = xmassj * xmassj;
             }
-            else if (Atwood > Atmax)
+            else if (rhoDiff > Atmax * rhoSum)
             {
                 a_mom = xmassi * xmassj;
                 b_mom = a_mom;
             }
             else
             {
+                T Atwood   = rhoDiff / rhoSum;
                 T sigma_ij = ramp * (Atwood - Atmin);
                 a_mom      = pow(xmassi, T(2) - sigma_ij) * pow(xmassj, sigma_ij);
                 b_mom      = pow(xmassj, T(2) - sigma_ij) * pow(xmassi, sigma_ij);
             }
 
-            T a_visc   = mj / rhoi * viscosity_ij;
+            T a_visc   = mj * rhoiInv * viscosity_ij; // m_j / rho_i with the reciprocal taken once per target
             T b_visc   = cb.d * viscosity_ij; // (m_j / rho_j) * viscosity_ij
             T a_visc_x = T(0.5) * (a_visc * termA1_i + b_visc * termA1_j);
             T a_visc_y = T(0.5) * (a_visc * termA2_i + b_visc * termA2_j);
