@@ -65,6 +65,17 @@ static PbcBox pbcBox(const sphb200_box& b)
     return p;
 }
 
+//! @brief true if the search sphere of a target reaches a periodic face.  Only then can a neighbor be a periodic image
+//!        (the image lies outside the box, the sphere inside), i.e. only then does applyPBC ever shift anything; the
+//!        1e-6 widening keeps the decision on the safe side of rounding and never changes a value.
+template<class T>
+__device__ __forceinline__ bool reachesPeriodicFace(const PbcBox& b, double x, double y, double z, T r)
+{
+    double rr = double(r) * 1.000001;
+    return (b.px && (x - rr <= b.lim[0] || x + rr >= b.lim[1])) || (b.py && (y - rr <= b.lim[2] || y + rr >= b.lim[3])) ||
+           (b.pz && (z - rr <= b.lim[4] || z + rr >= b.lim[5]));
+}
+
 //! @brief legacy minimum-image used inside the J-loops, cstone::applyPBC (sfc/box.hpp:234-255)
 template<class T>
 __device__ __forceinline__ void applyPBC(const PbcBox& b, T r, T& xx, T& yy, T& zz)
@@ -219,16 +230,20 @@ __global__ void __launch_bounds__(256) packMomentumKernel(size_t n, F<T> f, Rec4
     m4[i] = {f.c23[i], f.c33[i], f.alpha[i], m / rho};
 }
 
-//! @brief out[idx] = {wh[idx], wh[idx+1], whd[idx], whd[idx+1]}
+//! @brief out[idx] = {wh[idx], slope of wh on [idx, idx+1], whd[idx], slope of whd}; the slope is the `derivative` of
+//!        sph::lt::lookup (table_lookup.hpp:21), evaluated here once per interval instead of once per pair
 template<class T>
 __global__ void packTableKernel(const T* __restrict__ wh, const T* __restrict__ whd, Rec2<T>* __restrict__ pairs,
                                 Rec4<T>* __restrict__ quads)
 {
+    constexpr T dx    = T(2.0) / (kTableSize - 1);
+    constexpr T invDx = T(1) / dx;
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= kTableSize) return;
-    int i1 = min(i + 1, kTableSize - 1);
-    pairs[i] = {wh[i], wh[i1]};
-    if (whd) quads[i] = {wh[i], wh[i1], whd[i], whd[i1]};
+    int i1   = min(i + 1, kTableSize - 1);
+    T slope  = (wh[i1] - wh[i]) * invDx;
+    pairs[i] = {wh[i], slope};
+    if (whd) quads[i] = {wh[i], slope, whd[i], (whd[i1] - whd[i]) * invDx};
 }
 
 //! @brief tabulated kernel with linear interpolation, sph::lt::lookup (sph/table_lookup.hpp:13-25)
@@ -242,9 +257,8 @@ __device__ __forceinline__ T lookup(const Rec2<T>* __restrict__ table, T v)
 
     int idx = v * invDx;
     if (idx >= numIntervals) return T(0);
-    Rec2<T> t    = ldRec(table, idx);
-    T derivative = (t.b - t.a) * invDx;
-    return t.a + derivative * (v - T(idx) * dx);
+    Rec2<T> t = ldRec(table, idx); // {t[idx], derivative}
+    return t.a + t.b * (v - T(idx) * dx);
 }
 
 //! @brief both tables at the same abscissa (wh and whd), one load
@@ -261,8 +275,8 @@ __device__ __forceinline__ void lookup2(const Rec4<T>* __restrict__ table, T v, 
     if (idx >= numIntervals) return;
     Rec4<T> t = ldRec(table, idx);
     T frac    = v - T(idx) * dx;
-    w         = t.a + (t.b - t.a) * invDx * frac;
-    dw        = t.c + (t.d - t.c) * invDx * frac;
+    w         = t.a + t.b * frac;
+    dw        = t.c + t.d * frac;
 }
 
 #define LD(p, j) __ldg((p) + (j))
@@ -312,11 +326,12 @@ __global__ void __launch_bounds__(kHydroBlock, SPHB200_XMASS_MIN_BLOCKS)
     T h3Inv = hInv * hInv * hInv;
 
     T rho0i = mi;
+    const bool pbcI = Pbc && reachesPeriodicFace(box, xi, yi, zi, T(2) * hi);
     FOR_NEIGHBORS(nb, j)
     {
         PosRec<T> pj_ = ldRec(r0, j);
         T xx = xi - pj_.x, yy = yi - pj_.y, zz = zi - pj_.z;
-        if (Pbc) applyPBC(box, T(2) * hi, xx, yy, zz);
+        if (pbcI) applyPBC(box, T(2) * hi, xx, yy, zz);
         T dist = sqrt(xx * xx + yy * yy + zz * zz);
         T vloc = dist * hInv;
         T w    = lookup(wh, vloc);
@@ -349,12 +364,13 @@ __global__ void __launch_bounds__(kHydroBlock, SPHB200_GRADH_MIN_BLOCKS)
     T whomegai = -T(3) * xmassi;
     T wrho0i   = -T(3) * mi;
 
+    const bool pbcI = Pbc && reachesPeriodicFace(box, xi, yi, zi, T(2) * hi);
     FOR_NEIGHBORS(nb, j)
     {
         PosRec<T> pj_ = ldRec(r0, j);
         T xmassj = LD(f.xm, j);
         T xx = xi - pj_.x, yy = yi - pj_.y, zz = zi - pj_.z;
-        if (Pbc) applyPBC(box, T(2) * hi, xx, yy, zz);
+        if (pbcI) applyPBC(box, T(2) * hi, xx, yy, zz);
         T dist = sqrt(xx * xx + yy * yy + zz * zz);
         T vloc = dist * hInv;
         T w, dw;
@@ -421,13 +437,14 @@ __global__ void __launch_bounds__(kHydroBlock, SPHB200_IAD_MIN_BLOCKS)
 
     T tau11 = 0.0, tau12 = 0.0, tau13 = 0.0, tau22 = 0.0, tau23 = 0.0, tau33 = 0.0;
     T Sx[3] = {0, 0, 0}, Sy[3] = {0, 0, 0}, Sz[3] = {0, 0, 0};
+    const bool pbcI = Pbc && reachesPeriodicFace(box, xi, yi, zi, T(2) * hi);
     FOR_NEIGHBORS(nb, j)
     {
         PosRec<T> pj_ = ldRec(r0, j);
         Rec4<T> vj    = ldRec(r1, j);
         T xmassj = pj_.m, volj = vj.d; // 4th slots: xm_j and V_j = xm_j / kx_j
         T rx = xi - pj_.x, ry = yi - pj_.y, rz = zi - pj_.z;
-        if (Pbc) applyPBC(box, T(2) * hi, rx, ry, rz);
+        if (pbcI) applyPBC(box, T(2) * hi, rx, ry, rz);
         T dist   = sqrt(rx * rx + ry * ry + rz * rz);
         T vloc   = dist * hiInv;
         T w      = lookup(wh, vloc);
@@ -530,13 +547,14 @@ __global__ void __launch_bounds__(kHydroBlock, SPHB200_AV_MIN_BLOCKS)
     T divv_i = pi.m;
 
     T gx = 0.0, gy = 0.0, gz = 0.0;
+    const bool pbcI = Pbc && reachesPeriodicFace(box, xi, yi, zi, T(2) * hi);
     FOR_NEIGHBORS(nb, j)
     {
         PosRec<T> pj_ = ldRec(r0, j);
         Rec4<T> vj    = ldRec(r1, j);
         T divv_j      = pj_.m; // 4th slot of the position record
         T rx = xi - pj_.x, ry = yi - pj_.y, rz = zi - pj_.z;
-        if (Pbc) applyPBC(box, T(2) * hi, rx, ry, rz);
+        if (pbcI) applyPBC(box, T(2) * hi, rx, ry, rz);
         T r2_  = rx * rx + ry * ry + rz * rz;
         T dist = sqrt(r2_);
 
@@ -654,6 +672,7 @@ __global__ void __launch_bounds__(kHydroBlock, kMomentumMinBlocks)
 
         T eta_crit = cbrt(T(32) * M_PI / T(3) / T(nb.count + 1));
 
+        const bool pbcI = Pbc && reachesPeriodicFace(box, xi, yi, zi, T(2) * hi);
         FOR_NEIGHBORS(nb, j)
         {
             PosRec<T> pj_ = ldRec(rec.r0, j);
@@ -664,7 +683,7 @@ __global__ void __launch_bounds__(kHydroBlock, kMomentumMinBlocks)
 
             T rx = xi - pj_.x, ry = yi - pj_.y, rz = zi - pj_.z;
             T vxj = vj.a, vyj = vj.b, vzj = vj.c;
-            if (Pbc) applyPBC(box, T(2) * hi, rx, ry, rz);
+            if (pbcI) applyPBC(box, T(2) * hi, rx, ry, rz);
 
             T r2_  = rx * rx + ry * ry + rz * rz;
             T dist = sqrt(r2_);
