@@ -219,6 +219,16 @@ int sphb200_pack_ranges(sphb200_ctx*, const uint32_t* rangeScan, const uint32_t*
 int sphb200_unpack_ranges(sphb200_ctx*, const uint32_t* rangeScan, const uint32_t* rangeBegin, int numRanges,
                           uint32_t totalElems, int nfields, void* const* dst_h, const int* elem_bytes_h,
                           const void* packed);
+/* All peers of one halo exchange in one launch.  Ranges are concatenated in peer order (peerCount_h[q] elements
+ * belong to peer q); the packed buffer holds one block per peer, inside a block the fields follow one another, each
+ * 8-byte aligned -- exactly the split sizes of an all-to-all (returned in bytesPerPeer_h, may be NULL; packed may be
+ * NULL to query the sizes only). */
+int sphb200_pack_ranges_peers(sphb200_ctx*, const uint32_t* rangeScan, const uint32_t* rangeBegin, int numRanges,
+                              int numPeers, const uint32_t* peerCount_h, int nfields, const void* const* src_h,
+                              const int* elem_bytes_h, void* packed, size_t* bytesPerPeer_h);
+int sphb200_unpack_ranges_peers(sphb200_ctx*, const uint32_t* rangeScan, const uint32_t* rangeBegin, int numRanges,
+                                int numPeers, const uint32_t* peerCount_h, int nfields, void* const* dst_h,
+                                const int* elem_bytes_h, const void* packed, size_t* bytesPerPeer_h);
 
 /* ---- halo discovery (multi-GPU) ----
  * segmentMaxGpu (primitives_gpu.h:76, primitives_gpu.cu:180-207): out[s] = max h over [layout[s], layout[s+1]) */

@@ -344,9 +344,127 @@ __global__ void __launch_bounds__(256) rangesKernel(const uint32_t* __restrict__
     }
 }
 
+constexpr int kMaxPeers = 64;
+
+struct PeerArgs
+{
+    uint32_t scan[kMaxPeers + 1]; // element prefix over peers
+    size_t byteBase[kMaxPeers];   // start of each peer's block in the packed buffer
+    int numPeers;
+};
+
+/*! @brief all peers of one halo exchange in one launch
+ *
+ * Packed buffer = per-peer blocks in peer order (what all_to_all_single splits on); inside a block the fields follow
+ * one another, each 8-byte aligned (exchange_halos_gpu.cuh:58).  Element e of the concatenated ranges belongs to the
+ * peer q with scan[q] <= e < scan[q+1].
+ */
+template<bool Pack>
+__global__ void __launch_bounds__(256) rangesMultiKernel(const uint32_t* __restrict__ rangeScan,
+                                                         const uint32_t* __restrict__ rangeBegin, int numRanges,
+                                                         uint32_t total, PeerArgs peers, RangeArgs a,
+                                                         char* __restrict__ packed)
+{
+    uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= total) return;
+    int r        = int(upperBound(rangeScan, size_t(numRanges), e)) - 1;
+    uint32_t idx = rangeBegin[r] + (e - rangeScan[r]);
+    int q = 0;
+    while (q + 1 < peers.numPeers && peers.scan[q + 1] <= e)
+        ++q;
+    uint32_t cnt = peers.scan[q + 1] - peers.scan[q];
+    uint32_t el  = e - peers.scan[q];
+    size_t off   = peers.byteBase[q];
+    for (int f = 0; f < a.nfields; ++f)
+    {
+        if (a.is8[f])
+        {
+            auto* p = reinterpret_cast<uint64_t*>(packed + off);
+            auto* q8 = static_cast<uint64_t*>(a.field[f]);
+            if (Pack) p[el] = q8[idx];
+            else q8[idx] = p[el];
+            off += size_t(cnt) * 8;
+        }
+        else
+        {
+            auto* p = reinterpret_cast<uint32_t*>(packed + off);
+            auto* q4 = static_cast<uint32_t*>(a.field[f]);
+            if (Pack) p[el] = q4[idx];
+            else q4[idx] = p[el];
+            off += (size_t(cnt) * 4 + 7) & ~size_t(7);
+        }
+    }
+}
+
 } // namespace sphb200
 
 using namespace sphb200;
+
+static int rangesMultiImpl(sphb200_ctx* ctx, bool pack, const uint32_t* rangeScan, const uint32_t* rangeBegin,
+                           int numRanges, int numPeers, const uint32_t* peerCount_h, int nfields, void* const* fields,
+                           const int* elemBytes, void* packed, size_t* bytesPerPeer_h)
+{
+    try
+    {
+        if (nfields > kMaxGatherFields) throw std::runtime_error("ranges_multi: too many fields");
+        if (numPeers > kMaxPeers) throw std::runtime_error("ranges_multi: too many peers");
+        PeerArgs peers;
+        peers.numPeers = numPeers;
+        peers.scan[0]  = 0;
+        size_t base    = 0;
+        for (int q = 0; q < numPeers; ++q)
+        {
+            peers.scan[q + 1] = peers.scan[q] + peerCount_h[q];
+            peers.byteBase[q] = base;
+            size_t blk        = 0;
+            for (int f = 0; f < nfields; ++f)
+                blk += (size_t(peerCount_h[q]) * elemBytes[f] + 7) & ~size_t(7);
+            if (bytesPerPeer_h) bytesPerPeer_h[q] = blk;
+            base += blk;
+        }
+        uint32_t total = peers.scan[numPeers];
+        if (total == 0 || nfields == 0 || !packed) return 0;
+        RangeArgs a;
+        a.nfields = nfields;
+        for (int f = 0; f < nfields; ++f)
+        {
+            a.field[f]        = fields[f];
+            a.is8[f]          = elemBytes[f] == 8;
+            a.packedOffset[f] = 0;
+        }
+        if (pack)
+            SPHB200_LAUNCH(ctx, rangesMultiKernel<true>, gridFor(total, 256), 256, 0, rangeScan, rangeBegin, numRanges,
+                           total, peers, a, static_cast<char*>(packed));
+        else
+            SPHB200_LAUNCH(ctx, rangesMultiKernel<false>, gridFor(total, 256), 256, 0, rangeScan, rangeBegin, numRanges,
+                           total, peers, a, static_cast<char*>(packed));
+        return 0;
+    }
+    catch (std::exception& e)
+    {
+        setError(e.what());
+        return 1;
+    }
+}
+
+extern "C" int sphb200_pack_ranges_peers(sphb200_ctx* ctx, const uint32_t* rangeScan, const uint32_t* rangeBegin,
+                                         int numRanges, int numPeers, const uint32_t* peerCount_h, int nfields,
+                                         const void* const* src, const int* elemBytes, void* packed,
+                                         size_t* bytesPerPeer_h)
+{
+    return rangesMultiImpl(ctx, true, rangeScan, rangeBegin, numRanges, numPeers, peerCount_h, nfields,
+                           const_cast<void* const*>(src), elemBytes, packed, bytesPerPeer_h);
+}
+
+extern "C" int sphb200_unpack_ranges_peers(sphb200_ctx* ctx, const uint32_t* rangeScan, const uint32_t* rangeBegin,
+                                           int numRanges, int numPeers, const uint32_t* peerCount_h, int nfields,
+                                           void* const* dst, const int* elemBytes, const void* packed,
+                                           size_t* bytesPerPeer_h)
+{
+    ctx->packValid = 0; // halo values changed under the gather records (hydro.cu)
+    return rangesMultiImpl(ctx, false, rangeScan, rangeBegin, numRanges, numPeers, peerCount_h, nfields, dst,
+                           elemBytes, const_cast<void*>(packed), bytesPerPeer_h);
+}
 
 extern "C" int sphb200_sort_by_key(sphb200_ctx* ctx, uint64_t* keys, uint32_t* perm, size_t n)
 {

@@ -115,6 +115,8 @@ class DistHydroVeProp:
         self.assignment = None
         self.times = {}
         self.halo_bytes = 0
+        self._sync_profile = bool(int(os.environ.get("SPHB200_SYNC_PROFILE", "0")))
+        self.sync_times = {}
 
     # ---- helpers
     def upload(self, arrays):
@@ -154,9 +156,20 @@ class DistHydroVeProp:
         return leaves, counts
 
     # ---- Domain::sync
+    def _st(self, name):
+        """optional fine-grained timers of sync() (SPHB200_SYNC_PROFILE=1), synchronising"""
+        if not self._sync_profile:
+            return
+        self.torch.cuda.synchronize()
+        now = time.perf_counter()
+        if name is not None:
+            self.sync_times[name] = self.sync_times.get(name, 0.0) + (now - self._st0)
+        self._st0 = now
+
     def sync(self):
         t, ops, dist, f = self.torch, self.ops, self.dist, self.f
         P, me = self.world, self.rank
+        self._st(None)
         # 1. global box for open axes (makeGlobalBox, box_mpi.hpp:84-119)
         if any(b != 1 for b in self.bc):
             mm = ops.minMaxGpu(self.ctx, f["x"], f["y"], f["z"])
@@ -168,15 +181,24 @@ class DistHydroVeProp:
                     self.lim[2 * d], self.lim[2 * d + 1] = v[2 * d], -v[2 * d + 1]
             self.box = self.pkg.make_box(self.lim, self.bc)
 
+        self._st("box")
         # 2. keys, sort, reorder
         keys = ops.computeSfcKeysGpu(self.ctx, f["x"], f["y"], f["z"], self.box)
         perm = ops.sortByKeyGpu(self.ctx, keys)
-        out = ops.gatherGpu(self.ctx, perm, [f[k] for k in self.CONSERVED])
-        for k, a in zip(self.CONSERVED, out):
-            f[k] = a
+        # the reorder of the fields is deferred until the halo layout is known, so that it can write straight into the
+        # [halos | owned | halos] arrays; only h is needed before that (halo discovery)
+        pending = dict(f) if P > 1 else None
+        if P > 1:
+            f["h"] = ops.gatherGpu(self.ctx, perm, [f["h"]])[0]
+        else:
+            out = ops.gatherGpu(self.ctx, perm, [f[k] for k in self.CONSERVED])
+            for k, a in zip(self.CONSERVED, out):
+                f[k] = a
 
+        self._st("keys+sort+gather")
         # 3. replicated global tree + assignment
         self.gtree = self._update_tree(self.gtree, keys, self.bucket, True)
+        self._st("global tree")
         if P > 1:
             g_leaves = self.gtree[0].cpu().numpy().view(np.uint64)
             g_counts = self.gtree[1].cpu().numpy().view(np.uint32)
@@ -187,12 +209,19 @@ class DistHydroVeProp:
             # keys are < 2^63 so signed compare is fine; the terminal boundary 2^63 wraps negative -> use n
             splits = t.searchsorted(keys, bd[:-1].contiguous()).tolist() + [keys.numel()]
             send = [splits[q + 1] - splits[q] for q in range(P)]
+            # every rank sees the whole send matrix: the migration collectives below must be entered by all ranks or none
             send_t = t.tensor(send, dtype=t.int64, device=self.dev)
-            recv_t = t.empty_like(send_t)
-            dist.all_to_all_single(recv_t, send_t, group=self.group)
-            recv = recv_t.tolist()
-            moved = sum(send) - send[me] + sum(recv) - recv[me]
+            mat = t.empty((P, P), dtype=t.int64, device=self.dev)
+            dist.all_gather_into_tensor(mat, send_t, group=self.group)
+            mat = mat.tolist()
+            recv = [mat[q][me] for q in range(P)]
+            moved = sum(mat[q][r] for q in range(P) for r in range(P) if q != r)
+            self._st("assignment")
             if moved:
+                out = ops.gatherGpu(self.ctx, perm, [pending[k] for k in self.CONSERVED])
+                for k, a in zip(self.CONSERVED, out):
+                    f[k] = a
+                pending = None
                 for k in self.CONSERVED:
                     src = f[k]
                     dst = t.empty(sum(recv), dtype=src.dtype, device=self.dev)
@@ -203,6 +232,7 @@ class DistHydroVeProp:
                 out = ops.gatherGpu(self.ctx, perm, [f[k] for k in self.CONSERVED])
                 for k, a in zip(self.CONSERVED, out):
                     f[k] = a
+        self._st("migration")
         self.own_keys = keys
         n_own = keys.numel()
 
@@ -216,6 +246,7 @@ class DistHydroVeProp:
         # 5. local tree over owned keys, halo discovery
         self.ftree = self._update_tree(self.ftree, keys, self.bucket_focus, False)
         ftree = ops.Octree(self.ctx, self.ftree[0], self.box, self.ftree[1])
+        self._st("focus tree")
         L, ni = ftree.numLeaves, ftree.numInternal
         hmax = t.empty(L, dtype=t.float64, device=self.dev)
         self.B.check(self.B.lib.sphb200_segment_max(self.ctx.h, self.B.ptr(f["h"]), self.dtype, self.B.ptr(ftree.layout),
@@ -228,13 +259,14 @@ class DistHydroVeProp:
         lo, hi = leaf_c - half, leaf_c + half
         # union of the halo boxes per coarse SFC block so that at most MAX_QUERY_BOXES boxes are published
         lk = self.ftree[0][:-1]
-        level = 7
+        level = getattr(self, "_qb_level", 7)  # start from last step's level: the tree changes slowly
         while True:
             gid = lk >> (3 * (21 - level))
             uniq, inv = t.unique_consecutive(gid, return_inverse=True)
             if uniq.numel() <= MAX_QUERY_BOXES or level == 0:
                 break
             level -= 1
+        self._qb_level = level
         G = uniq.numel()
         big = 1e300
         lo_m = t.where(occupied.unsqueeze(1), lo, t.full_like(lo, big))
@@ -249,6 +281,7 @@ class DistHydroVeProp:
         qb = t.zeros((MAX_QUERY_BOXES, 6), dtype=t.float64, device=self.dev)
         qb[:G, :3] = 0.5 * (glo + ghi)
         qb[:G, 3:] = 0.5 * (ghi - glo) * (1 + 1e-12)
+        self._st("query boxes")
         all_qb = t.empty((P, MAX_QUERY_BOXES, 6), dtype=t.float64, device=self.dev)
         all_cnt = t.empty(P, dtype=t.int32, device=self.dev)
         dist.all_gather_into_tensor(all_qb, qb, group=self.group)
@@ -257,40 +290,57 @@ class DistHydroVeProp:
         self.B.check(self.B.lib.sphb200_mark_halo_leaves(self.ctx.h, self.B.ptr(leaf_c), self.B.ptr(leaf_s), L,
                                                          self.B.ptr(all_qb), self.B.ptr(all_cnt), P, MAX_QUERY_BOXES, me,
                                                          C.byref(self.box), self.B.ptr(mask)))
+        self._st("gather boxes + mark")
         layout = ftree.layout
         counts = self.ftree[1]
-        self.send_lists, send = [], []
-        for q in range(P):
-            if q == me:
-                self.send_lists.append(None)
-                send.append(0)
-                continue
-            sel = t.nonzero(((mask >> q) & 1) & occupied.int()).flatten()
-            lens = counts[sel]
-            begins = layout[:-1][sel].contiguous()
-            scan = (t.cumsum(lens, 0) - lens).int().contiguous()
-            total = int(lens.sum().item()) if sel.numel() else 0
-            self.send_lists.append((scan, begins, total))
-            send.append(total)
-        send_t = t.tensor(send, dtype=t.int64, device=self.dev)
-        recv_t = t.empty_like(send_t)
-        dist.all_to_all_single(recv_t, send_t, group=self.group)
-        self.halo_send, self.halo_recv = send, recv_t.tolist()
+        # send lists of all peers at once: (peer, leaf) pairs in peer-major order, one range per marked leaf
+        qs = t.arange(P, device=self.dev, dtype=t.int32)
+        bits = (((mask.unsqueeze(0) >> qs.unsqueeze(1)) & 1) > 0) & occupied.unsqueeze(0)
+        bits[me] = False
+        pl = t.nonzero(bits)
+        leaf = pl[:, 1]
+        lens = counts[leaf].long()
+        self.send_scan = (t.cumsum(lens, 0) - lens).int().contiguous()
+        send_begins = layout[:-1][leaf]
+        per_peer = t.zeros(P, dtype=t.int64, device=self.dev).index_add_(0, pl[:, 0], lens)
+        recv_t = t.empty_like(per_peer)
+        dist.all_to_all_single(recv_t, per_peer, group=self.group)
+        both = t.stack([per_peer, recv_t]).tolist()
+        self.halo_send, self.halo_recv = both[0], both[1]
         self.start, self.end, self.n_total, self.halo_off = halo_layout(me, n_own, self.halo_recv)
         # send ranges were found in the owned-only arrays: shift them to the [halos | owned | halos] layout
-        self.send_lists = [None if sl is None else (sl[0], (sl[1] + self.start).int().contiguous(), sl[2])
-                           for sl in self.send_lists]
-
+        self.send_begins = (send_begins + self.start).int().contiguous()
+        # receive side: one contiguous range per peer
+        rc = t.tensor(self.halo_recv, dtype=t.int64)
+        self.recv_scan = (t.cumsum(rc, 0) - rc).int().to(self.dev)
+        self.recv_begins = t.tensor([max(0, o) for o in self.halo_off], dtype=t.int32, device=self.dev)
+        self._st("send lists")
         # 6. grow every conserved field to [halos | owned | halos]; exchange x,y,z,h,m (setupHalos, domain.hpp:512-529)
-        for k in self.CONSERVED:
-            a = t.zeros(self.n_total, dtype=f[k].dtype, device=self.dev)
-            a[self.start:self.end] = f[k]
-            f[k] = a
+        if pending is not None:
+            srcs = [pending[k] for k in self.CONSERVED]
+            grown = [t.empty(self.n_total, dtype=a.dtype, device=self.dev) for a in srcs]
+            ops.gatherGpu(self.ctx, perm, srcs, [g[self.start:self.end] for g in grown])
+            for k, g in zip(self.CONSERVED, grown):
+                f[k] = g
+        else:
+            for k in self.CONSERVED:
+                a = t.empty(self.n_total, dtype=f[k].dtype, device=self.dev)
+                a[self.start:self.end] = f[k]
+                f[k] = a
+        self._st("grow arrays")
         self.exchange_halos(["x", "y", "z", "h", "m"])
+        self._st("halo xyzhm")
         # 7. search tree over owned + halo keys (already SFC-ordered: peers' key ranges are ordered by rank)
-        self.all_keys = ops.computeSfcKeysGpu(self.ctx, f["x"], f["y"], f["z"], self.box)
+        a, b, n = self.start, self.end, self.n_total
+        self.all_keys = t.empty(n, dtype=keys.dtype, device=self.dev)
+        self.all_keys[a:b] = keys
+        if a > 0:
+            self.all_keys[:a] = ops.computeSfcKeysGpu(self.ctx, f["x"][:a], f["y"][:a], f["z"][:a], self.box)
+        if n > b:
+            self.all_keys[b:] = ops.computeSfcKeysGpu(self.ctx, f["x"][b:], f["y"][b:], f["z"][b:], self.box)
         self.stree = self._update_tree(self.stree, self.all_keys, self.bucket_focus, False)
         self.tree = ops.Octree(self.ctx, self.stree[0], self.box, self.stree[1])
+        self._st("search tree")
 
     def exchange_halos(self, names):
         """haloExchangeGpu (halos/exchange_halos_gpu.cuh:50-143): pack ranges per peer with one kernel, one NCCL
@@ -300,27 +350,14 @@ class DistHydroVeProp:
         t, ops, dist, f = self.torch, self.ops, self.dist, self.f
         P, me = self.world, self.rank
         arrs = [f[k] for k in names]
-        sb = [ops.packedBytes(self.halo_send[q], arrs) if q != me else 0 for q in range(P)]
-        rb = [ops.packedBytes(self.halo_recv[q], arrs) if q != me else 0 for q in range(P)]
+        sb = [ops.packedBytes(self.halo_send[q], arrs) for q in range(P)]
+        rb = [ops.packedBytes(self.halo_recv[q], arrs) for q in range(P)]
         sendbuf = t.empty(max(1, sum(sb)), dtype=t.uint8, device=self.dev)
         recvbuf = t.empty(max(1, sum(rb)), dtype=t.uint8, device=self.dev)
-        off = 0
-        for q in range(P):
-            if q == me or self.halo_send[q] == 0:
-                continue
-            scan, begins, total = self.send_lists[q]
-            ops.packRanges(self.ctx, scan, begins, total, arrs, sendbuf[off:off + sb[q]])
-            off += sb[q]
+        ops.packRangesPeers(self.ctx, self.send_scan, self.send_begins, self.halo_send, arrs, sendbuf)
         dist.all_to_all_single(recvbuf[:sum(rb)], sendbuf[:sum(sb)], output_split_sizes=rb, input_split_sizes=sb,
                                group=self.group)
-        off = 0
-        zero = t.zeros(1, dtype=t.int32, device=self.dev)
-        for q in range(P):
-            if q == me or self.halo_recv[q] == 0:
-                continue
-            begin = t.tensor([self.halo_off[q]], dtype=t.int32, device=self.dev)
-            ops.unpackRanges(self.ctx, zero, begin, self.halo_recv[q], arrs, recvbuf[off:off + rb[q]])
-            off += rb[q]
+        ops.unpackRangesPeers(self.ctx, self.recv_scan, self.recv_begins, self.halo_recv, arrs, recvbuf)
         self.halo_bytes += sum(sb)
 
     # ---- HydroVeProp::computeForces / integrate

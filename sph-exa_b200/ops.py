@@ -44,10 +44,12 @@ def sortByKeyGpu(ctx, keys):
     return perm
 
 
-def gatherGpu(ctx, perm, srcs):
-    """gatherGpu for a list of fields in one launch (primitives_gpu.h:62)"""
+def gatherGpu(ctx, perm, srcs, dsts=None):
+    """gatherGpu for a list of fields in one launch (primitives_gpu.h:62); dsts: optional preallocated outputs
+    (contiguous views of perm.numel() elements)"""
     n = perm.numel()
-    dsts = [torch.empty_like(s) for s in srcs]
+    if dsts is None:
+        dsts = [torch.empty_like(s) for s in srcs]
     k = len(srcs)
     sp = (vp * k)(*[s.data_ptr() for s in srcs])
     dp = (vp * k)(*[d.data_ptr() for d in dsts])
@@ -277,6 +279,25 @@ def unpackRanges(ctx, range_scan, range_begin, total, dsts, packed):
     eb = (C.c_int * k)(*[s.element_size() for s in dsts])
     check(lib.sphb200_unpack_ranges(ctx.h, ptr(range_scan), ptr(range_begin), range_begin.numel(), C.c_uint32(total),
                                     k, dp, eb, ptr(packed)))
+
+
+def packRangesPeers(ctx, range_scan, range_begin, peer_counts, srcs, packed):
+    """all peers of one halo exchange in one launch (sphb200_pack_ranges_peers); peer_counts: host list"""
+    k, P = len(srcs), len(peer_counts)
+    sp = (vp * k)(*[s.data_ptr() for s in srcs])
+    eb = (C.c_int * k)(*[s.element_size() for s in srcs])
+    pc = (C.c_uint32 * P)(*peer_counts)
+    check(lib.sphb200_pack_ranges_peers(ctx.h, ptr(range_scan), ptr(range_begin), range_begin.numel(), P, pc, k, sp, eb,
+                                        ptr(packed), None))
+
+
+def unpackRangesPeers(ctx, range_scan, range_begin, peer_counts, dsts, packed):
+    k, P = len(dsts), len(peer_counts)
+    dp = (vp * k)(*[s.data_ptr() for s in dsts])
+    eb = (C.c_int * k)(*[s.element_size() for s in dsts])
+    pc = (C.c_uint32 * P)(*peer_counts)
+    check(lib.sphb200_unpack_ranges_peers(ctx.h, ptr(range_scan), ptr(range_begin), range_begin.numel(), P, pc, k, dp,
+                                          eb, ptr(packed), None))
 
 
 def packedBytes(total, srcs):
