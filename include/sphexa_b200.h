@@ -200,6 +200,14 @@ int sphb200_timestep(sphb200_ctx*, int dtype, uint32_t first, uint32_t last, con
 /* device address of the 3 doubles above, for an in-stream ncclAllReduce(min) */
 double* sphb200_timestep_device_ptr(sphb200_ctx*);
 
+/* ---- observables: computeConservedQuantities (main/src/observables/conserved_quantities.hpp:50-180) ----
+ * out[10] = { eKin = 1/2 sum m v^2, eInt = sum cv T m, egrav (0), linmom[3], angmom[3], sum of nc } over [first,last),
+ * accumulated in double in a fixed order (reproducible).  out_h may be NULL: the values stay on the device
+ * (sphb200_conserved_device_ptr) for an in-stream all-reduce over ranks. */
+int sphb200_conserved_quantities(sphb200_ctx*, int dtype, uint32_t first, uint32_t last,
+                                 const sphb200_hydro_const* hc_h, const sphb200_fields* f_h, double* out_h);
+double* sphb200_conserved_device_ptr(sphb200_ctx*);
+
 /* The pair operators gather neighbor data from packed copies ("gather records") of the field arrays kept in the
  * context.  Stand-alone operator calls repack on every call; a sphb200_sim reuses them across operators and
  * invalidates them itself.  Call this after writing to a sim's device arrays obtained through sphb200_sim_fields()
@@ -264,6 +272,8 @@ void sphb200_sim_destroy(sphb200_sim*);
 int sphb200_sim_upload(sphb200_sim*, size_t n, const sphb200_fields* host_fields);
 /* download assigned range [startIndex,endIndex) of every non-NULL field */
 int sphb200_sim_download(sphb200_sim*, const sphb200_fields* host_fields, uint64_t* keys_h);
+/* computeConservedQuantities for the owned particles (see sphb200_conserved_quantities) */
+int sphb200_sim_conserved(sphb200_sim*, double* out10_h);
 /* One time step on host-resident state: same results as upload + step + download, with the PCIe transfers staged
  * beside the kernels ({x,y,z} first, {h,m,temp} next, the rest behind the neighbor search; m and alpha return while
  * MomentumEnergy runs).  host_in/host_out: all 14 conserved fields, pinned memory for overlap.  Single rank only. */

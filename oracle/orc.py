@@ -213,3 +213,14 @@ class OracleSim:
         L.orc_positions_update_h(C.c_uint32(0), C.c_uint32(n), C.c_double(self.minDt), C.c_double(self.minDt_m1),
                                  C.byref(b), C.byref(fs), C.c_double(self.s["mui"]), C.c_double(self.s["gamma"]),
                                  C.c_uint(self.ng0), P(self.nc))
+
+
+def conserved_quantities(f, first, last, mui, gamma, nc=None):
+    """[eKin, eInt, egrav, linmom(3), angmom(3), ncsum] over [first,last) (conserved_quantities.hpp:48-159)"""
+    out = np.zeros(10)
+    a = {k: np.ascontiguousarray(f[k], np.float64) for k in ("x", "y", "z", "vx", "vy", "vz", "m", "temp")}
+    ncp = P(np.ascontiguousarray(nc, np.uint32)) if nc is not None else None
+    lib().orc_conserved_quantities(C.c_uint32(first), C.c_uint32(last), P(a["x"]), P(a["y"]), P(a["z"]), P(a["vx"]),
+                                   P(a["vy"]), P(a["vz"]), P(a["m"]), P(a["temp"]), ncp, C.c_double(mui),
+                                   C.c_double(gamma), P(out))
+    return out

@@ -246,3 +246,17 @@ def positions(first, last, dt, dt_m1, box, x, y, z, vx, vy, vz, x_m1, y_m1, z_m1
 
 def update_h(first, last, ng0, nc, h):
     getattr(lib(), "ref_update_h_" + _sfx(h.dtype))(C.c_uint32(first), C.c_uint32(last), C.c_uint(ng0), P(nc), P(h))
+
+
+def conserved_quantities(x, y, z, vx, vy, vz, m, temp, mui, gamma):
+    """sphexa::localConservedQuantities (main/src/observables/conserved_quantities.hpp:48-107) ->
+    [eKin, eInt, 0, linmom(3), angmom(3)]"""
+    out = np.zeros(9)
+    real = m.dtype
+    fn = lib().ref_conserved_f64 if real == np.float64 else lib().ref_conserved_f32
+    a = [np.ascontiguousarray(v, np.float64) for v in (x, y, z)]
+    b = [np.ascontiguousarray(v, real) for v in (vx, vy, vz, m)]
+    t = np.ascontiguousarray(temp, np.float64)
+    fn(P(a[0]), P(a[1]), P(a[2]), P(b[0]), P(b[1]), P(b[2]), P(b[3]), P(t), C.c_size_t(m.size), C.c_double(mui),
+       C.c_double(gamma), P(out))
+    return out

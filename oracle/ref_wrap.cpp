@@ -58,6 +58,9 @@
 #include "sph/hydro_ve/av_switches_kern.hpp"
 #include "sph/hydro_ve/momentum_energy_kern.hpp"
 #include "sph/positions.hpp"
+#include "cstone/primitives/mpi_wrappers.hpp" // MpiType, against oracle/stub/mpi.h (single rank)
+#include "cstone/tree/accel_switch.hpp"
+#include "observables/conserved_quantities.hpp"
 
 using KeyType = uint64_t;
 using SfcKey  = cstone::HilbertKey<KeyType>;
@@ -506,3 +509,43 @@ EXPORT_HYDRO(f64, double)
 EXPORT_HYDRO(f32, float)
 
 extern "C" double ref_sphynx_3D_k(double n) { return sph::sphynx_3D_k(n); }
+
+// ---- observables: sphexa::localConservedQuantities (main/src/observables/conserved_quantities.hpp:48-107)
+namespace
+{
+template<class T>
+struct ObsDataset
+{
+    using AcceleratorType = cstone::CpuTag;
+    std::vector<double> x, y, z, temp;
+    std::vector<T> vx, vy, vz, m, u, mui;
+    double muiConst, gamma;
+};
+
+template<class T>
+void refConserved(const double* x, const double* y, const double* z, const T* vx, const T* vy, const T* vz, const T* m,
+                  const double* temp, size_t n, double mui, double gamma, double* out)
+{
+    ObsDataset<T> d;
+    d.x.assign(x, x + n); d.y.assign(y, y + n); d.z.assign(z, z + n); d.temp.assign(temp, temp + n);
+    d.vx.assign(vx, vx + n); d.vy.assign(vy, vy + n); d.vz.assign(vz, vz + n); d.m.assign(m, m + n);
+    d.muiConst = mui;
+    d.gamma    = gamma;
+    auto [eKin, eInt, linmom, angmom] = sphexa::localConservedQuantities(0, n, d);
+    out[0] = eKin; out[1] = eInt; out[2] = 0.0;
+    for (int k = 0; k < 3; ++k) { out[3 + k] = linmom[k]; out[6 + k] = angmom[k]; }
+}
+} // namespace
+
+extern "C" void ref_conserved_f64(const double* x, const double* y, const double* z, const double* vx, const double* vy,
+                                  const double* vz, const double* m, const double* temp, size_t n, double mui,
+                                  double gamma, double* out)
+{
+    refConserved<double>(x, y, z, vx, vy, vz, m, temp, n, mui, gamma, out);
+}
+extern "C" void ref_conserved_f32(const double* x, const double* y, const double* z, const float* vx, const float* vy,
+                                  const float* vz, const float* m, const double* temp, size_t n, double mui,
+                                  double gamma, double* out)
+{
+    refConserved<float>(x, y, z, vx, vy, vz, m, temp, n, mui, gamma, out);
+}

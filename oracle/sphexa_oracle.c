@@ -758,3 +758,28 @@ void orc_tables(double n, double* wh, double* whd, double* K)
     double fa = 0.0, fb = 4.0 * M_PI * 4.0 * pow(wharm(2.0), n);
     *K = 1.0 / (h / 3.0 * (fa + fb + 4.0 * so + 2.0 * se));
 }
+
+/* ---- observables: localConservedQuantities (main/src/observables/conserved_quantities.hpp:48-107), f64 types.
+ * out = { eKin, eInt, 0 (egrav), linmom[3], angmom[3], sum nc }; sequential sums in index order */
+void orc_conserved_quantities(uint32_t first, uint32_t last, const double* x, const double* y, const double* z,
+                              const double* vx, const double* vy, const double* vz, const double* m, const double* temp,
+                              const uint32_t* nc, double mui, double gamma, double* out)
+{
+    const double R = 8.317e7;                 /* sph/eos.hpp:13-21 idealGasCv */
+    double cv = R / mui / (gamma - 1.0);
+    double eKin = 0, eInt = 0, lin[3] = {0, 0, 0}, ang[3] = {0, 0, 0}, ncsum = 0;
+    for (uint32_t i = first; i < last; ++i)
+    {
+        double mi = m[i];
+        eKin += mi * (vx[i] * vx[i] + vy[i] * vy[i] + vz[i] * vz[i]);           /* :75 mi * norm2(V) */
+        lin[0] += mi * vx[i]; lin[1] += mi * vy[i]; lin[2] += mi * vz[i];         /* :76 */
+        ang[0] += mi * (y[i] * vz[i] - z[i] * vy[i]);                             /* :77 mi * cross(X, V) */
+        ang[1] += mi * (z[i] * vx[i] - x[i] * vz[i]);
+        ang[2] += mi * (x[i] * vy[i] - y[i] * vx[i]);
+        eInt += cv * temp[i] * mi;                                                /* :101 */
+        if (nc) ncsum += (double)nc[i];                                           /* :137-141 */
+    }
+    out[0] = 0.5 * eKin; out[1] = eInt; out[2] = 0.0;
+    for (int k = 0; k < 3; ++k) { out[3 + k] = lin[k]; out[6 + k] = ang[k]; }
+    out[9] = ncsum;
+}

@@ -70,7 +70,8 @@ SYMBOLS = [
     "sphb200_sim_compute_forces", "sphb200_sim_integrate", "sphb200_sim_step", "sphb200_sim_forces_phase",
     "sphb200_sim_start_index", "sphb200_sim_end_index", "sphb200_sim_n_with_halos", "sphb200_sim_num_leaves",
     "sphb200_sim_num_global_leaves", "sphb200_sim_min_dt", "sphb200_sim_ttot", "sphb200_sim_total_neighbors",
-    "sphb200_pack_ranges_peers", "sphb200_unpack_ranges_peers", "sphb200_sim_step_host", "sphb200_sim_fields", "sphb200_sim_tree", "sphb200_sim_keys", "sphb200_sim_neighbors",
+    "sphb200_pack_ranges_peers", "sphb200_unpack_ranges_peers", "sphb200_sim_step_host", "sphb200_sim_conserved", "sphb200_conserved_quantities",
+    "sphb200_conserved_device_ptr", "sphb200_sim_fields", "sphb200_sim_tree", "sphb200_sim_keys", "sphb200_sim_neighbors",
     "sphb200_sim_phase_times", "sphb200_sim_set_layout", "sphb200_sim_local_timestep", "sphb200_sim_global_leaves",
     "sphb200_sim_global_counts", "sphb200_sim_leaf_counts", "sphb200_sim_get_box", "sphb200_sim_set_dt",
     "sphb200_segment_max", "sphb200_mark_halo_leaves",
@@ -82,6 +83,8 @@ lib.sphb200_launch_count.argtypes = [vp]
 lib.sphb200_neighbors_size.restype = C.c_size_t
 lib.sphb200_neighbors_size.argtypes = [C.c_size_t, C.c_uint]
 lib.sphb200_timestep_device_ptr.restype = vp
+lib.sphb200_conserved_device_ptr.restype = vp
+lib.sphb200_conserved_device_ptr.argtypes = [vp]
 lib.sphb200_timestep_device_ptr.argtypes = [vp]
 for _n in ("sphb200_sim_start_index", "sphb200_sim_end_index", "sphb200_sim_n_with_halos"):
     getattr(lib, _n).restype = C.c_uint32

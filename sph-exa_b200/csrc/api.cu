@@ -72,6 +72,7 @@ extern "C" void sphb200_destroy(sphb200_ctx* ctx)
     ctx->scanTmp.release();
     ctx->miscTmp.release();
     ctx->nbTmp.release();
+    ctx->obsTmp.release();
     for (auto& a : ctx->rec)
         a.release();
     ctx->tabPairs.release();
@@ -677,6 +678,16 @@ extern "C" int sphb200_sim_step_host(sphb200_sim* s, size_t n, const sphb200_fie
         if (id != F_m && id != F_alpha) download(id, ctx->stream);
     SPHB200_CUDA(cudaStreamSynchronize(ctx->stream));
     SPHB200_CUDA(cudaStreamSynchronize(s->copyOut));
+    SPHB200_CATCH
+}
+
+//! @brief computeConservedQuantities for the owned particles of this rank (out10 may be NULL: result stays on device)
+extern "C" int sphb200_sim_conserved(sphb200_sim* s, double* out10)
+{
+    SPHB200_TRY
+    sphb200_fields f       = s->table();
+    sphb200_hydro_const hc = s->hydroConst();
+    CHECK_RC(sphb200_conserved_quantities(s->ctx, s->cfg.dtype, s->start, s->end, &hc, &f, out10));
     SPHB200_CATCH
 }
 

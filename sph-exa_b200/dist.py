@@ -440,6 +440,31 @@ class DistHydroVeProp:
         self.computeForces()
         self.integrate()
 
+    def conserved(self):
+        """computeConservedQuantities (conserved_quantities.hpp:113-180): local fp64 reduction on the device, then one
+        in-stream all-reduce of the 10 sums (the reference reduces to rank 0 with MPI_Reduce)"""
+        t, ops = self.torch, self.ops
+        f = dict(self.f)
+        f.setdefault("nc", None)
+        n_own = self.end - self.start
+        a, b = (0, n_own) if f["x"].numel() == n_own else (self.start, self.end)
+        if f.get("nc") is not None and f["nc"].numel() != f["x"].numel():
+            f["nc"] = None
+        fs = ops.fields_struct(f)
+        self.B.check(self.B.lib.sphb200_conserved_quantities(self.ctx.h, self.dtype, C.c_uint32(a), C.c_uint32(b),
+                                                             C.byref(self._hc()), C.byref(fs), None))
+        dptr = self.B.lib.sphb200_conserved_device_ptr(self.ctx.h)
+
+        class _Holder:
+            pass
+
+        h = _Holder()
+        h.__cuda_array_interface__ = {"shape": (10,), "typestr": "<f8", "data": (int(dptr), False), "version": 3}
+        v = t.as_tensor(h, device=self.dev).clone()
+        if self.world > 1:
+            self.dist.all_reduce(v, op=self.dist.ReduceOp.SUM, group=self.group)
+        return ops.conserved_dict(v.tolist())
+
     def _tick(self, name):
         if not getattr(self, "profile", False):
             return

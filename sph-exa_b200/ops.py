@@ -302,3 +302,25 @@ def unpackRangesPeers(ctx, range_scan, range_begin, peer_counts, dsts, packed):
 
 def packedBytes(total, srcs):
     return sum((total * s.element_size() + 7) // 8 * 8 for s in srcs)
+
+
+# ---------------------------------------------------------------- observables
+CONSERVED_NAMES = ["ecin", "eint", "egrav", "linmom_x", "linmom_y", "linmom_z", "angmom_x", "angmom_y", "angmom_z", "ncsum"]
+
+
+def computeConservedQuantities(ctx, first, last, d, hc):
+    """local part of sphexa::computeConservedQuantities (conserved_quantities.hpp:50-180): dict of the 10 sums over
+    [first, last) plus etot, |linmom|, |angmom| as the reference derives them (lines 165-175)"""
+    f = fields_struct(d)
+    out = (C.c_double * 10)()
+    check(lib.sphb200_conserved_quantities(ctx.h, _dt(d), C.c_uint32(first), C.c_uint32(last), C.byref(hc), C.byref(f),
+                                           out))
+    return conserved_dict(list(out))
+
+
+def conserved_dict(v):
+    r = dict(zip(CONSERVED_NAMES, v))
+    r["etot"] = r["ecin"] + r["eint"] + r["egrav"]
+    r["linmom"] = (r["linmom_x"] ** 2 + r["linmom_y"] ** 2 + r["linmom_z"] ** 2) ** 0.5
+    r["angmom"] = (r["angmom_x"] ** 2 + r["angmom_y"] ** 2 + r["angmom_z"] ** 2) ** 0.5
+    return r

@@ -109,6 +109,13 @@ class HydroVeProp:
         pinned host pointers for the 14 conserved fields"""
         check(lib.sphb200_sim_step_host(self.h, C.c_size_t(n), C.byref(fin), C.byref(fout)))
 
+    def conserved(self):
+        """computeConservedQuantities over the owned particles (observables/conserved_quantities.hpp:113-180)"""
+        from . import ops
+        out = (C.c_double * 10)()
+        check(lib.sphb200_sim_conserved(self.h, out))
+        return ops.conserved_dict(list(out))
+
     def download_into(self, f_struct):
         check(lib.sphb200_sim_download(self.h, C.byref(f_struct), None))
 

@@ -49,6 +49,7 @@ def main():
         sim.computeForces()
         mid = sim.download_owned(names)
         sim.integrate()
+        cons = sim.conserved()  # collective: device reduction per rank + all-reduce
         counts = [None] * world
         dist.all_gather_object(counts, (len(mid["keys"]), sim.n_total))
         gathered = [None] * world
@@ -57,6 +58,11 @@ def main():
             ref_sim.computeForces()
             want = ref_sim.download_owned(names)
             ref_sim.integrate()
+            cons1 = ref_sim.conserved()
+            for k in ("ecin", "eint", "etot"):
+                if abs(cons[k] - cons1[k]) > 1e-12 * abs(cons1["etot"]):
+                    ok = False
+                    print("MISMATCH conserved", k, cons[k], cons1[k], flush=True)
             keys = np.concatenate([g["keys"] for g in gathered])
             order = np.argsort(keys, kind="stable")
             assert np.array_equal(keys[order], want["keys"]), "key sets differ"

@@ -337,3 +337,34 @@ def test_step_host_equals_upload_step_download(pkg, ctx, real):
         bufs.reverse()
     a.close()
     b.close()
+
+
+@pytest.mark.parametrize("real", [np.float64, np.float32])
+def test_conserved_quantities(pkg, ctx, ref, real):
+    """device reduction of computeConservedQuantities vs the reference template (oracle/_ref), f64 and mixed types;
+    tolerance: 1e-13 of the absolute-value sums (different but fixed summation order), ncsum exact"""
+    from sph_exa_b200 import ops
+    f, box, s = pkg.ic.turbulence(20, "f64" if real == np.float64 else "mixed")
+    n = f["x"].size
+    rng = np.random.default_rng(5)
+    for k in ("vx", "vy", "vz"):
+        f[k] = rng.normal(size=n).astype(real)
+    nc = rng.integers(50, 150, n).astype(np.uint32)
+    first, last = 17, n - 5
+    want = ref.conserved_quantities(*[f[k][first:last] for k in ("x", "y", "z", "vx", "vy", "vz", "m", "temp")],
+                                    s["mui"], s["gamma"])
+    d = {k: to_dev(np.ascontiguousarray(f[k], np.float64 if k in ("x", "y", "z", "temp") else real))
+         for k in ("x", "y", "z", "h", "m", "vx", "vy", "vz", "temp")}
+    d["nc"] = to_dev(nc)
+    hc = ops.hydro_const(1.0, 0, 0, gamma=s["gamma"], muiConst=s["mui"])
+    got = ops.computeConservedQuantities(ctx, first, last, d, hc)
+    mv = float(np.abs(f["m"].astype(np.float64) * f["vx"]).sum())
+    tol = 1e-13 if real == np.float64 else 1e-6
+    assert abs(got["ecin"] - want[0]) <= tol * want[0]
+    assert abs(got["eint"] - want[1]) <= tol * want[1]
+    for k, name in enumerate(("linmom_x", "linmom_y", "linmom_z")):
+        assert abs(got[name] - want[3 + k]) <= tol * mv
+    for k, name in enumerate(("angmom_x", "angmom_y", "angmom_z")):
+        assert abs(got[name] - want[6 + k]) <= tol * mv * float(np.abs(f["x"]).max())
+    assert got["ncsum"] == float(nc[first:last].sum())
+    assert got["etot"] == got["ecin"] + got["eint"]
