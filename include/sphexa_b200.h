@@ -200,6 +200,37 @@ int sphb200_timestep(sphb200_ctx*, int dtype, uint32_t first, uint32_t last, con
 /* device address of the 3 doubles above, for an in-stream ncclAllReduce(min) */
 double* sphb200_timestep_device_ptr(sphb200_ctx*);
 
+/* ---- turbulence stirring (sph/include/sph/hydro_turb/*, main/src/propagator/turb_ve.hpp:113-118) ----
+ * Operator level: computeStirringGpu (stirring_gpu.cu:43-93).  modes[numModes][3], phaseReal/phaseImag[numModes][3],
+ * amplitudes[numModes] are device arrays of double; ax, ay, az of `real` type get solWeightNorm * sum over modes added. */
+int sphb200_stirring(sphb200_ctx*, int dtype, uint32_t first, uint32_t last, const double* x, const double* y,
+                     const double* z, void* ax, void* ay, void* az, int numModes, const double* modes,
+                     const double* phaseReal, const double* phaseImag, const double* amplitudes, double solWeightNorm);
+
+/* Driver level: sph::TurbulenceData + driveTurbulence (turbulence_data.hpp:57-183, driver.hpp:79-130).  The mode
+ * table, the Ornstein-Uhlenbeck sequence (std::mt19937 / std::normal_distribution, same stream as the reference when
+ * built against the same C++ library) and the phase projection live on the host. */
+typedef struct sphb200_turb_config
+{
+    double solWeight, Lbox, stEnergyPrefac, stMachVelocity, epsilon, powerLawExp, anglesExp;
+    uint64_t stMaxModes, rngSeed;
+    int stSpectForm; /* 0 band, 1 parabola, 2 power law */
+} sphb200_turb_config;
+typedef struct sphb200_turb sphb200_turb;
+int sphb200_turb_create(const sphb200_turb_config*, sphb200_turb** out);
+void sphb200_turb_destroy(sphb200_turb*);
+int sphb200_turb_num_modes(const sphb200_turb*);
+/* host copies; any pointer may be NULL.  scalars4 = {variance, decayTime, solWeight, solWeightNorm};
+ * modes[3n], amplitudes[n], phases[6n] (OU state), phasesReal[3n], phasesImag[3n] */
+int sphb200_turb_get(const sphb200_turb*, double* scalars4, double* modes, double* amplitudes, double* phases,
+                     double* phasesReal, double* phasesImag);
+/* restart (TurbulenceData::loadOrStore): OU state and/or the text form of the random engine */
+int sphb200_turb_set_state(sphb200_turb*, const double* phases, const char* rngState);
+int sphb200_turb_rng_state(const sphb200_turb*, char* buf, size_t bufSize); /* returns the size needed */
+/* driveTurbulence: advance the OU phases by dt, project, upload, add the stirring accelerations on [first,last) */
+int sphb200_turb_drive(sphb200_turb*, sphb200_ctx*, int dtype, uint32_t first, uint32_t last, const double* x,
+                       const double* y, const double* z, void* ax, void* ay, void* az, double dt);
+
 /* ---- observables: computeConservedQuantities (main/src/observables/conserved_quantities.hpp:50-180) ----
  * out[10] = { eKin = 1/2 sum m v^2, eInt = sum cv T m, egrav (0), linmom[3], angmom[3], sum of nc } over [first,last),
  * accumulated in double in a fixed order (reproducible).  out_h may be NULL: the values stay on the device
@@ -272,6 +303,9 @@ void sphb200_sim_destroy(sphb200_sim*);
 int sphb200_sim_upload(sphb200_sim*, size_t n, const sphb200_fields* host_fields);
 /* download assigned range [startIndex,endIndex) of every non-NULL field */
 int sphb200_sim_download(sphb200_sim*, const sphb200_fields* host_fields, uint64_t* keys_h);
+/* TurbVeProp: stir after the hydro forces of every step with dt = minDt (turb_ve.hpp:113-118); NULL detaches.
+ * The sim does not own the turbulence object. */
+int sphb200_sim_attach_turbulence(sphb200_sim*, sphb200_turb*);
 /* computeConservedQuantities for the owned particles (see sphb200_conserved_quantities) */
 int sphb200_sim_conserved(sphb200_sim*, double* out10_h);
 /* One time step on host-resident state: same results as upload + step + download, with the PCIe transfers staged

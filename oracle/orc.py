@@ -224,3 +224,18 @@ def conserved_quantities(f, first, last, mui, gamma, nc=None):
                                    P(a["vy"]), P(a["vz"]), P(a["m"]), P(a["temp"]), ncp, C.c_double(mui),
                                    C.c_double(gamma), P(out))
     return out
+
+
+def turb_phases(ou, sol_weight, modes):
+    """computePhases (hydro_turb/phases.hpp:46-72) -> (phasesReal, phasesImag)"""
+    n = modes.size // 3
+    pr, pi = np.zeros(3 * n), np.zeros(3 * n)
+    lib().orc_turb_phases(n, 3, P(np.ascontiguousarray(ou)), C.c_double(sol_weight), P(np.ascontiguousarray(modes)),
+                          P(pr), P(pi))
+    return pr, pi
+
+
+def stirring(first, last, x, y, z, ax, ay, az, modes, pr, pi, amplitudes, sol_weight_norm):
+    """computeStirring (hydro_turb/stirring.hpp:99-122), in place on ax, ay, az (float64)"""
+    lib().orc_stirring(C.c_uint32(first), C.c_uint32(last), P(x), P(y), P(z), P(ax), P(ay), P(az), int(amplitudes.size),
+                       P(modes), P(pr), P(pi), P(amplitudes), C.c_double(sol_weight_norm))

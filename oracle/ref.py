@@ -260,3 +260,36 @@ def conserved_quantities(x, y, z, vx, vy, vz, m, temp, mui, gamma):
     fn(P(a[0]), P(a[1]), P(a[2]), P(b[0]), P(b[1]), P(b[2]), P(b[3]), P(t), C.c_size_t(m.size), C.c_double(mui),
        C.c_double(gamma), P(out))
     return out
+
+
+class RefTurbulence:
+    """sph::TurbulenceData<double, CpuTag> + the CPU branch of driveTurbulence (sph/include/sph/hydro_turb/*)"""
+
+    def __init__(self, solWeight=0.5, stMaxModes=100000, Lbox=1.0, stEnergyPrefac=5.0e-3, stMachVelocity=0.3,
+                 epsilon=1e-15, rngSeed=251299, stSpectForm=1, powerLawExp=5.0 / 3.0, anglesExp=2.0):
+        L = lib()
+        L.ref_turb_create.restype = C.c_void_p
+        self.h = C.c_void_p(L.ref_turb_create(*[C.c_double(float(v)) for v in (
+            solWeight, stMaxModes, Lbox, stEnergyPrefac, stMachVelocity, epsilon, rngSeed, stSpectForm, powerLawExp,
+            anglesExp)]))
+        self.numModes = L.ref_turb_num_modes(self.h)
+
+    def state(self):
+        n = self.numModes
+        sc = np.zeros(4)
+        out = dict(modes=np.zeros(3 * n), amplitudes=np.zeros(n), phases=np.zeros(6 * n), phasesReal=np.zeros(3 * n),
+                   phasesImag=np.zeros(3 * n))
+        lib().ref_turb_get(self.h, P(sc), P(out["modes"]), P(out["amplitudes"]), P(out["phases"]), P(out["phasesReal"]),
+                           P(out["phasesImag"]))
+        out.update(variance=sc[0], decayTime=sc[1], solWeight=sc[2], solWeightNorm=sc[3], numModes=n)
+        return out
+
+    def drive(self, first, last, x, y, z, ax, ay, az, dt):
+        """in place on ax, ay, az (float64 or float32 numpy arrays)"""
+        fn = lib().ref_turb_drive_f64 if ax.dtype == np.float64 else lib().ref_turb_drive_f32
+        fn(self.h, C.c_uint32(first), C.c_uint32(last), P(x), P(y), P(z), P(ax), P(ay), P(az), C.c_double(dt))
+
+    def close(self):
+        if self.h:
+            lib().ref_turb_destroy(self.h)
+            self.h = None

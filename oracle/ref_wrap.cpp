@@ -61,6 +61,13 @@
 #include "cstone/primitives/mpi_wrappers.hpp" // MpiType, against oracle/stub/mpi.h (single rank)
 #include "cstone/tree/accel_switch.hpp"
 #include "observables/conserved_quantities.hpp"
+#include <map>
+#include <sstream>
+#include <iostream>
+#include "sph/hydro_turb/turbulence_data.hpp"
+#include "sph/hydro_turb/phases.hpp"
+#include "sph/hydro_turb/stirring.hpp"
+#include "sph/hydro_turb/driver.hpp"
 
 using KeyType = uint64_t;
 using SfcKey  = cstone::HilbertKey<KeyType>;
@@ -548,4 +555,58 @@ extern "C" void ref_conserved_f32(const double* x, const double* y, const double
                                   double gamma, double* out)
 {
     refConserved<float>(x, y, z, vx, vy, vz, m, temp, n, mui, gamma, out);
+}
+
+// ---- turbulence stirring: sph::TurbulenceData / updateNoise / computePhases / computeStirring (hydro_turb/*)
+namespace
+{
+using RefTurb = sph::TurbulenceData<double, cstone::CpuTag>;
+}
+
+extern "C" void* ref_turb_create(double solWeight, double stMaxModes, double Lbox, double stEnergyPrefac,
+                                 double stMachVelocity, double epsilon, double rngSeed, double stSpectForm,
+                                 double powerLawExp, double anglesExp)
+{
+    std::map<std::string, double> c{{"solWeight", solWeight}, {"stMaxModes", stMaxModes}, {"Lbox", Lbox},
+                                    {"stEnergyPrefac", stEnergyPrefac}, {"stMachVelocity", stMachVelocity},
+                                    {"epsilon", epsilon}, {"rngSeed", rngSeed}, {"stSpectForm", stSpectForm},
+                                    {"powerLawExp", powerLawExp}, {"anglesExp", anglesExp}};
+    return new RefTurb(c, false);
+}
+extern "C" void ref_turb_destroy(void* t) { delete static_cast<RefTurb*>(t); }
+extern "C" int ref_turb_num_modes(void* t) { return int(static_cast<RefTurb*>(t)->numModes); }
+extern "C" void ref_turb_get(void* tp, double* scalars4, double* modes, double* amplitudes, double* phases,
+                             double* phasesReal, double* phasesImag)
+{
+    auto* t     = static_cast<RefTurb*>(tp);
+    scalars4[0] = t->variance; scalars4[1] = t->decayTime; scalars4[2] = t->solWeight; scalars4[3] = t->solWeightNorm;
+    std::copy(t->modes.begin(), t->modes.end(), modes);
+    std::copy(t->amplitudes.begin(), t->amplitudes.end(), amplitudes);
+    std::copy(t->phases.begin(), t->phases.end(), phases);
+    std::copy(t->phasesReal.begin(), t->phasesReal.end(), phasesReal);
+    std::copy(t->phasesImag.begin(), t->phasesImag.end(), phasesImag);
+}
+//! @brief the CPU branch of driveTurbulence (driver.hpp:101-128) with a one-group view (the CPU
+//!        computeGroups never sets numGroups)
+template<class Ta>
+static void refTurbDrive(void* tp, uint32_t first, uint32_t last, const double* x, const double* y, const double* z,
+                         Ta* ax, Ta* ay, Ta* az, double dt)
+{
+    auto* t = static_cast<RefTurb*>(tp);
+    sph::updateNoise(t->phases, t->variance, dt, t->decayTime, t->gen);
+    sph::computePhases(t->numModes, t->numDim, t->phases, t->solWeight, t->modes, t->phasesReal, t->phasesImag);
+    cstone::LocalIndex gs = first, ge = last;
+    cstone::GroupView grp{first, last, 1, &gs, &ge};
+    sph::computeStirring(grp, t->numDim, x, y, z, ax, ay, az, t->numModes, t->modes.data(), t->phasesReal.data(),
+                         t->phasesImag.data(), t->amplitudes.data(), t->solWeightNorm);
+}
+extern "C" void ref_turb_drive_f64(void* t, uint32_t first, uint32_t last, const double* x, const double* y,
+                                   const double* z, double* ax, double* ay, double* az, double dt)
+{
+    refTurbDrive<double>(t, first, last, x, y, z, ax, ay, az, dt);
+}
+extern "C" void ref_turb_drive_f32(void* t, uint32_t first, uint32_t last, const double* x, const double* y,
+                                   const double* z, float* ax, float* ay, float* az, double dt)
+{
+    refTurbDrive<float>(t, first, last, x, y, z, ax, ay, az, dt);
 }

@@ -783,3 +783,54 @@ void orc_conserved_quantities(uint32_t first, uint32_t last, const double* x, co
     for (int k = 0; k < 3; ++k) { out[3 + k] = lin[k]; out[6 + k] = ang[k]; }
     out[9] = ncsum;
 }
+
+/* ---- turbulence stirring, f64 types ----
+ * computePhases (sph/include/sph/hydro_turb/phases.hpp:46-72): projection of the OU phases */
+void orc_turb_phases(int numModes, int numDim, const double* ou, double solWeight, const double* modes,
+                     double* phasesReal, double* phasesImag)
+{
+    for (int i = 0; i < numModes; ++i)
+    {
+        double ka = 0.0, kb = 0.0, kk = 0.0;
+        for (int j = 0; j < numDim; ++j)
+        {
+            kk = kk + modes[3 * i + j] * modes[3 * i + j];
+            ka = ka + modes[3 * i + j] * ou[6 * i + 2 * j + 1];
+            kb = kb + modes[3 * i + j] * ou[6 * i + 2 * j];
+        }
+        for (int j = 0; j < numDim; ++j)
+        {
+            double diva  = modes[3 * i + j] * ka / kk;
+            double divb  = modes[3 * i + j] * kb / kk;
+            double curla = ou[6 * i + 2 * j] - divb;
+            double curlb = ou[6 * i + 2 * j + 1] - diva;
+            phasesReal[3 * i + j] = solWeight * curla + (1.0 - solWeight) * divb;
+            phasesImag[3 * i + j] = solWeight * curlb + (1.0 - solWeight) * diva;
+        }
+    }
+}
+
+/* stirParticle + computeStirring (stirring.hpp:43-122) */
+void orc_stirring(uint32_t first, uint32_t last, const double* x, const double* y, const double* z, double* ax,
+                  double* ay, double* az, int numModes, const double* modes, const double* phaseReal,
+                  const double* phaseImag, const double* amplitudes, double solWeightNorm)
+{
+    for (uint32_t i = first; i < last; ++i)
+    {
+        double tx = 0.0, ty = 0.0, tz = 0.0;
+        for (int m = 0; m < numModes; ++m)
+        {
+            double ck = cos(modes[3 * m + 2] * z[i]), sk = sin(modes[3 * m + 2] * z[i]);
+            double cj = cos(modes[3 * m + 1] * y[i]), sj = sin(modes[3 * m + 1] * y[i]);
+            double ci = cos(modes[3 * m] * x[i]), si = sin(modes[3 * m] * x[i]);
+            double re = (ci * cj - si * sj) * ck - (si * cj + ci * sj) * sk;
+            double im = ci * (cj * sk + sj * ck) + si * (cj * ck - sj * sk);
+            tx += amplitudes[m] * (phaseReal[3 * m] * re - phaseImag[3 * m] * im);
+            ty += amplitudes[m] * (phaseReal[3 * m + 1] * re - phaseImag[3 * m + 1] * im);
+            tz += amplitudes[m] * (phaseReal[3 * m + 2] * re - phaseImag[3 * m + 2] * im);
+        }
+        ax[i] += solWeightNorm * tx;
+        ay[i] += solWeightNorm * ty;
+        az[i] += solWeightNorm * tz;
+    }
+}

@@ -52,6 +52,12 @@ class HydroConst(C.Structure):
                 ("wh", vp), ("whd", vp), ("avClean", C.c_int)]
 
 
+class TurbConfig(C.Structure):
+    _fields_ = [("solWeight", C.c_double), ("Lbox", C.c_double), ("stEnergyPrefac", C.c_double),
+                ("stMachVelocity", C.c_double), ("epsilon", C.c_double), ("powerLawExp", C.c_double),
+                ("anglesExp", C.c_double), ("stMaxModes", C.c_uint64), ("rngSeed", C.c_uint64), ("stSpectForm", C.c_int)]
+
+
 class SimConfig(C.Structure):
     _fields_ = [("dtype", C.c_int), ("rank", C.c_int), ("numRanks", C.c_int), ("bucketSize", C.c_uint),
                 ("bucketSizeFocus", C.c_uint), ("capacity", C.c_size_t), ("box", Box), ("hc", HydroConst)]
@@ -70,7 +76,9 @@ SYMBOLS = [
     "sphb200_sim_compute_forces", "sphb200_sim_integrate", "sphb200_sim_step", "sphb200_sim_forces_phase",
     "sphb200_sim_start_index", "sphb200_sim_end_index", "sphb200_sim_n_with_halos", "sphb200_sim_num_leaves",
     "sphb200_sim_num_global_leaves", "sphb200_sim_min_dt", "sphb200_sim_ttot", "sphb200_sim_total_neighbors",
-    "sphb200_pack_ranges_peers", "sphb200_unpack_ranges_peers", "sphb200_sim_step_host", "sphb200_sim_conserved", "sphb200_conserved_quantities",
+    "sphb200_pack_ranges_peers", "sphb200_unpack_ranges_peers", "sphb200_sim_step_host", "sphb200_sim_conserved", "sphb200_sim_attach_turbulence", "sphb200_stirring", "sphb200_turb_create",
+    "sphb200_turb_destroy", "sphb200_turb_num_modes", "sphb200_turb_get", "sphb200_turb_set_state",
+    "sphb200_turb_rng_state", "sphb200_turb_drive", "sphb200_conserved_quantities",
     "sphb200_conserved_device_ptr", "sphb200_sim_fields", "sphb200_sim_tree", "sphb200_sim_keys", "sphb200_sim_neighbors",
     "sphb200_sim_phase_times", "sphb200_sim_set_layout", "sphb200_sim_local_timestep", "sphb200_sim_global_leaves",
     "sphb200_sim_global_counts", "sphb200_sim_leaf_counts", "sphb200_sim_get_box", "sphb200_sim_set_dt",

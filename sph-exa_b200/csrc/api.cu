@@ -227,6 +227,8 @@ struct sphb200_sim
     bool evValid[kNumPhases + 1] = {};
 
     // sphb200_sim_step_host: copy engines run beside the compute stream
+    sphb200_turb* turb = nullptr; // TurbVeProp: stirring after the hydro forces
+
     cudaStream_t copyIn = nullptr, copyOut = nullptr;
     cudaEvent_t evUp[3] = {}, evDown[2] = {};
 
@@ -540,6 +542,8 @@ extern "C" int sphb200_sim_forces_phase(sphb200_sim* s, int phase)
         case 4:
             CHECK_RC(sphb200_momentum_energy(ctx, dt, a, b, &s->box, &hc, s->neighbors, &f, nullptr));
             s->mark(8);
+            // TurbVeProp::computeForces (turb_ve.hpp:113-118): stirring with the current minDt
+            if (s->turb) CHECK_RC(sphb200_turb_drive(s->turb, ctx, dt, a, b, f.x, f.y, f.z, f.ax, f.ay, f.az, s->minDt));
             break;
         default: throw std::runtime_error("forces_phase: phase must be 0..4");
     }
@@ -679,6 +683,12 @@ extern "C" int sphb200_sim_step_host(sphb200_sim* s, size_t n, const sphb200_fie
     SPHB200_CUDA(cudaStreamSynchronize(ctx->stream));
     SPHB200_CUDA(cudaStreamSynchronize(s->copyOut));
     SPHB200_CATCH
+}
+
+extern "C" int sphb200_sim_attach_turbulence(sphb200_sim* s, sphb200_turb* t)
+{
+    s->turb = t;
+    return 0;
 }
 
 //! @brief computeConservedQuantities for the owned particles of this rank (out10 may be NULL: result stays on device)

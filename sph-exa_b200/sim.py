@@ -109,6 +109,11 @@ class HydroVeProp:
         pinned host pointers for the 14 conserved fields"""
         check(lib.sphb200_sim_step_host(self.h, C.c_size_t(n), C.byref(fin), C.byref(fout)))
 
+    def attachTurbulence(self, turb):
+        """TurbVeProp (main/src/propagator/turb_ve.hpp:96-118): stir after the hydro forces of every step"""
+        check(lib.sphb200_sim_attach_turbulence(self.h, turb.h if turb is not None else None))
+        self._turb = turb
+
     def conserved(self):
         """computeConservedQuantities over the owned particles (observables/conserved_quantities.hpp:113-180)"""
         from . import ops
