@@ -141,6 +141,37 @@ struct Hydro
     }
 };
 
+//! @brief sph::TurbulenceData + driveTurbulence (sph/include/sph/hydro_turb/turbulence_data.hpp:57-183, driver.hpp:101-128)
+class Turbulence
+{
+public:
+    explicit Turbulence(const sphb200_turb_config& cfg) { check(sphb200_turb_create(&cfg, &t_)); }
+    ~Turbulence() { sphb200_turb_destroy(t_); }
+    Turbulence(const Turbulence&)            = delete;
+    Turbulence& operator=(const Turbulence&) = delete;
+    sphb200_turb* get() const { return t_; }
+    int numModes() const { return sphb200_turb_num_modes(t_); }
+    //! @brief driveTurbulence on device arrays
+    void drive(const Context& c, int dtype, uint32_t first, uint32_t last, const double* x, const double* y,
+               const double* z, void* ax, void* ay, void* az, double dt)
+    {
+        check(sphb200_turb_drive(t_, c.get(), dtype, first, last, x, y, z, ax, ay, az, dt));
+    }
+
+private:
+    sphb200_turb* t_{nullptr};
+};
+
+//! @brief sphexa::computeConservedQuantities, local part (observables/conserved_quantities.hpp:113-159):
+//!        {eKin, eInt, egrav, linmom[3], angmom[3], ncsum}
+inline std::array<double, 10> conservedQuantities(const Context& c, int dtype, uint32_t first, uint32_t last,
+                                                  const sphb200_hydro_const& hc, const sphb200_fields& d)
+{
+    std::array<double, 10> q{};
+    check(sphb200_conserved_quantities(c.get(), dtype, first, last, &hc, &d, q.data()));
+    return q;
+}
+
 // ---- propagator level -------------------------------------------------------------------------------------------------
 
 //! @brief sphexa::HydroVeProp + cstone::Domain for one rank; owns the device state
@@ -169,6 +200,20 @@ public:
     }
     //! @brief Propagator::integrate (ve_hydro.hpp:207-217); globalMinDt < 0: single rank
     void integrate(double globalMinDt = -1.0) { check(sphb200_sim_integrate(sim_, globalMinDt)); }
+    //! @brief one step on host-resident state (pinned buffers): transfers staged beside the kernels
+    void stepHost(size_t n, const sphb200_fields& in, const sphb200_fields& out)
+    {
+        check(sphb200_sim_step_host(sim_, n, &in, &out));
+    }
+    //! @brief TurbVeProp (propagator/turb_ve.hpp:96-118): stir after the hydro forces; nullptr detaches
+    void attachTurbulence(Turbulence* t) { check(sphb200_sim_attach_turbulence(sim_, t ? t->get() : nullptr)); }
+    //! @brief computeConservedQuantities over the owned particles
+    std::array<double, 10> conserved()
+    {
+        std::array<double, 10> q{};
+        check(sphb200_sim_conserved(sim_, q.data()));
+        return q;
+    }
 
     // cstone::Domain getters (domain.hpp:382-429)
     uint32_t startIndex() const { return sphb200_sim_start_index(sim_); }
