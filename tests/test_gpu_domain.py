@@ -332,3 +332,136 @@ def test_pack_unpack_ranges(pkg, ctx):
     wa = np.zeros(n)
     wa[idx] = a[idx]
     assert np.array_equal(to_host(da2), wa)
+
+
+@pytest.mark.parametrize("box", [BOXES[0], BOXES[1]])
+def test_find_neighbors_wide_radius_many_leaves(pkg, ctx, ref, box):
+    """bucket 8 on 60k particles gives ~10^4 leaves and radius 0.3 makes every target box overlap thousands of them:
+    the level-wise walk runs out of frontier slots and the depth-first walk has to produce the same sets.
+    Lists are truncated at ngmax (counts stay exact), as findNeighbors does in traversal.hpp:190-200."""
+    n, ngmax = 60_000, 64
+    first, last = 20_000, 20_400
+    rm, gnc, _, wnb, wnc, _ = neighbor_case(pkg, ctx, ref, n, box, 0.3, 11, False, ngmax, False, first=first,
+                                            last=last, bucket=8)
+    assert np.array_equal(gnc, wnc)
+    assert gnc.min() > 1000
+    # the stored part of a truncated list is implementation-ordered in the reference (traversal order), ascending-j
+    # here: every stored index must be a true neighbor
+    x, y, z = random_coords(n, box, 11, False)
+    keys, perm = ref.sort_by_key(ref.compute_sfc_keys(x, y, z, box))
+    x, y, z = x[perm], y[perm], z[perm]
+    lim = box[0]
+    L = np.array([lim[1] - lim[0], lim[3] - lim[2], lim[5] - lim[4]])
+    pbc = np.array(box[1], bool)
+    for t in range(0, last - first, 37):
+        i = first + t
+        j = rm[t, :ngmax].astype(np.int64)
+        d = np.stack([x[j] - x[i], y[j] - y[i], z[j] - z[i]], 1)
+        d = np.where(pbc[None, :], d - L * np.rint(d / L), d)
+        assert np.all((d * d).sum(1) < 0.3 ** 2)
+        assert np.all(j != i)
+
+
+def test_find_neighbors_coincident_particles(pkg, ctx, ref):
+    """clusters of particles at identical positions: identical SFC keys, leaves that cannot be split below the bucket
+    size, and pairs at distance exactly zero (which are neighbors of each other but not of themselves)"""
+    from sph_exa_b200 import ops
+    box = BOXES[1]
+    rng = np.random.Generator(np.random.MT19937(5))
+    base = rng.uniform(-0.45, 0.45, size=(300, 3))
+    pts = np.repeat(base, 7, axis=0)  # 7 copies of each point
+    x, y, z = (np.ascontiguousarray(pts[:, k]) for k in range(3))
+    n = x.size
+    unsorted = ref.compute_sfc_keys(x, y, z, box)
+    # ties: the device radix sort is stable like the reference's GPU sort (primitives_gpu.cu, cub radix sort); the
+    # reference's CPU sort_by_key is not, so the expected ordering is the stable one
+    perm = np.argsort(unsorted, kind="stable").astype(np.uint32)
+    keys = unsorted[perm]
+    gk = ops.computeSfcKeysGpu(ctx, to_dev(x), to_dev(y), to_dev(z), pkg.make_box(*box))
+    gperm = ops.sortByKeyGpu(ctx, gk)
+    assert np.array_equal(to_host(gk, np.uint64), keys)
+    assert np.array_equal(to_host(gperm, np.uint32), perm)
+    x, y, z = x[perm], y[perm], z[perm]
+    leaves, counts, _ = ref.compute_octree(keys, 4, capacity=100_000)  # bucket 4 < 7 copies: leaves at maximum depth
+    gl, gc, _ = ops.computeOctreeGpu(ctx, gk, 4, capacity=100_000)
+    assert np.array_equal(to_host(gl, np.uint64), leaves)
+    assert np.array_equal(to_host(gc, np.uint32), counts)
+    tr = ref.build_octree(leaves)
+    c, s = ref.node_centers(tr["prefixes"], box)
+    lay = np.zeros(counts.size + 1, np.uint32)
+    np.cumsum(counts, out=lay[1:])
+    h = np.full(n, 0.05)
+    ngmax = 200
+    wnb, wnc, _ = ref.find_neighbors(x, y, z, h, 0, n, box, tr, lay, c, s, 100, ngmax, False)
+    t = ops.Octree(ctx, gl, pkg.make_box(*box), gc)
+    nb, nc, _ = ops.findNeighbors(ctx, t, to_dev(x), to_dev(y), to_dev(z), to_dev(h), 0, n, pkg.make_box(*box), 100,
+                                  ngmax, False)
+    gnc = to_host(nc, np.uint32)
+    assert np.array_equal(gnc, wnc)
+    assert gnc.min() >= 7  # self + 6 coincident copies
+    rm = to_host(ops.neighborsRowMajor(ctx, nb, nc, ngmax), np.uint32)
+    assert sorted_sets_equal(rm, gnc, wnb, wnc, ngmax)
+
+
+def test_sfc_keys_on_box_faces(pkg, ctx, ref):
+    """coordinates exactly on the lower/upper faces and corners: the upper face folds into the last cell
+    (sfc/sfc.hpp:96-110 clamps the integer coordinate at 2^21 - 1)"""
+    from sph_exa_b200 import ops
+    for box in BOXES:
+        lo, hi = np.array(box[0][0:6:2], float), np.array(box[0][1:6:2], float)
+        corners = np.array([[lo[0] if (k & 1) == 0 else hi[0], lo[1] if (k & 2) == 0 else hi[1],
+                             lo[2] if (k & 4) == 0 else hi[2]] for k in range(8)])
+        mid = 0.5 * (lo + hi)
+        pts = np.concatenate([corners, mid[None, :], np.nextafter(hi, lo)[None, :], np.nextafter(lo, hi)[None, :]])
+        x, y, z = (np.ascontiguousarray(pts[:, k]) for k in range(3))
+        want = ref.compute_sfc_keys(x, y, z, box)
+        got = to_host(ops.computeSfcKeysGpu(ctx, to_dev(x), to_dev(y), to_dev(z), pkg.make_box(*box)), np.uint64)
+        assert np.array_equal(got, want)
+
+
+def test_pack_unpack_ranges_peers(pkg, ctx):
+    """all peers of one exchange in a single launch: peer p's segment starts at the 8-byte aligned running offset and
+    holds its fields back to back, exactly what one packRanges call per peer produces; peers without ranges and
+    ranges of length one are included"""
+    import torch
+    from sph_exa_b200 import ops
+    n = 50_000
+    rng = np.random.Generator(np.random.MT19937(3))
+    a = rng.normal(size=n)
+    b = rng.normal(size=n).astype(np.float32)
+    c = rng.integers(0, 2 ** 63, size=n, dtype=np.uint64)
+    peers = [  # (begins, lens) per peer
+        (np.array([5, 100, 4000], np.uint32), np.array([17, 1, 2501], np.uint32)),
+        (np.zeros(0, np.uint32), np.zeros(0, np.uint32)),
+        (np.array([49_999], np.uint32), np.array([1], np.uint32)),
+        (np.array([0, 20_000, 30_000, 45_000], np.uint32), np.array([3, 333, 4097, 31], np.uint32)),
+    ]
+    da, db, dc = to_dev(a), to_dev(b), to_dev(c)
+    srcs = [da, db, dc]
+    # expected: one single-peer pack per peer, blocks concatenated in peer order
+    chunks, counts = [], []
+    for begins, lens in peers:
+        total = int(lens.sum())
+        counts.append(total)
+        if total == 0:
+            continue
+        scan = np.zeros(lens.size, np.uint32)
+        scan[1:] = np.cumsum(lens)[:-1]
+        buf = torch.zeros(ops.packedBytes(total, srcs), dtype=torch.uint8, device="cuda")
+        ops.packRanges(ctx, to_dev(scan), to_dev(begins), total, srcs, buf)
+        chunks.append(buf.cpu().numpy())
+    want = np.concatenate(chunks)
+    begins = np.concatenate([p[0] for p in peers])
+    lens = np.concatenate([p[1] for p in peers])
+    scan = np.zeros(lens.size, np.uint32)
+    scan[1:] = np.cumsum(lens)[:-1]
+    packed = torch.zeros(want.size, dtype=torch.uint8, device="cuda")
+    ops.packRangesPeers(ctx, to_dev(scan), to_dev(begins), counts, srcs, packed)
+    assert np.array_equal(packed.cpu().numpy(), want)
+    dsts = [torch.zeros_like(t) for t in srcs]
+    ops.unpackRangesPeers(ctx, to_dev(scan), to_dev(begins), counts, dsts, packed)
+    idx = np.concatenate([np.arange(s0, s0 + l) for s0, l in zip(begins, lens)])
+    for got, src, dt in zip(dsts, (a, b, c), (np.float64, np.float32, np.uint64)):
+        w = np.zeros(n, dt)
+        w[idx] = src[idx]
+        assert np.array_equal(to_host(got, dt), w)
