@@ -354,6 +354,55 @@ void sphb200_sim_set_dt(sphb200_sim*, double minDt, double minDt_m1);
 /* set layout for multi-rank: arrays hold n particles, assigned = [start,end) */
 int sphb200_sim_set_layout(sphb200_sim*, uint32_t start, uint32_t end, uint32_t nWithHalos);
 
+/* ---- f4: restart files ----
+ * The reference checkpoints through H5Part/HDF5 (main/src/io/ifile_io_hdf5.cpp, sphexa.cpp:232-246): per dump one
+ * "Step#k" group with the step attributes of ParticlesData::loadOrStoreAttributes (sph/particles_data.hpp:142-193),
+ * Box::loadOrStore (cstone/sfc/box.hpp:168-175), TurbulenceData::loadOrStore (hydro_turb/turbulence_data.hpp:90-125)
+ * and one dataset per conserved field (Propagator::conservedFields).  HDF5 is not available on this box, so the same
+ * content goes into a self-describing little-endian binary file: a directory of named attributes followed by named
+ * SoA field blocks, one file per rank.  Attribute and field names are the reference's.  A restarted run continues
+ * bit-identically (tests/test_gpu_restart.py). */
+int sphb200_sim_get_config(const sphb200_sim*, sphb200_sim_config* out); /* hc.wh/whd: device pointers */
+/* replace the scalar constants (Kcour, Krho, gamma, muiConst, alpha*, decay_constant, ng0, At*, ramp);
+ * ngmax, K, avClean and the kernel tables are fixed at creation and must agree */
+int sphb200_sim_set_constants(sphb200_sim*, const sphb200_hydro_const*);
+void sphb200_sim_set_time(sphb200_sim*, double ttot);
+void sphb200_sim_set_box(sphb200_sim*, const sphb200_box*);
+sphb200_turb* sphb200_sim_turbulence(const sphb200_sim*);
+
+typedef struct sphb200_restart sphb200_restart;
+typedef struct sphb200_restart_info
+{
+    uint64_t iteration, numParticlesGlobal, numParticles; /* numParticles: in this file */
+    int dtype;                                            /* precision the fields were written in */
+    int hasTurbulence;
+    double time, minDt, minDt_m1;
+    sphb200_box box;
+} sphb200_restart_info;
+/* the writer underneath sphb200_sim_save, for drivers that keep their particle state outside a sphb200_sim (the
+ * multi-rank host): host_fields = the 14 conserved fields of info->numParticles particles in precision info->dtype;
+ * turb may be NULL */
+int sphb200_restart_write(const char* path, const sphb200_restart_info* info, const sphb200_hydro_const* hc,
+                          const sphb200_turb* turb, int rank, int numRanks, const sphb200_fields* host_fields);
+/* write the owned particles [startIndex,endIndex): attributes + the 14 conserved fields (+ turbulence state when a
+ * driver is attached).  iteration / numParticlesGlobal are the caller's (they live in the reference's main loop). */
+int sphb200_sim_save(sphb200_sim*, const char* path, uint64_t iteration, uint64_t numParticlesGlobal);
+
+int sphb200_restart_open(const char* path, sphb200_restart** out);
+void sphb200_restart_close(sphb200_restart*);
+int sphb200_restart_get_info(const sphb200_restart*, sphb200_restart_info* out);
+/* generic attribute access (H5Part stepAttribute): returns the element count, -1 if absent; copies at most
+ * `capacity` elements of the stored type (8-byte double/int64 or bytes) */
+int64_t sphb200_restart_attribute(const sphb200_restart*, const char* name, void* out, size_t capacity);
+/* read particles [first, first+count) of every field with a non-NULL host pointer, converted to `dtype` when the
+ * file holds the other precision (fileutils readField semantics); a rank assembles its slice from several files by
+ * offsetting the pointers */
+int sphb200_restart_read_fields(const sphb200_restart*, uint64_t first, uint64_t count, int dtype,
+                                const sphb200_fields* host_fields);
+/* time, minDt, minDt_m1, the optional constants found in the file, the box, and the turbulence state (when the file
+ * has one and a driver is attached) */
+int sphb200_restart_apply(const sphb200_restart*, sphb200_sim*);
+
 #ifdef __cplusplus
 }
 #endif

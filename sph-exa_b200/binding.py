@@ -63,6 +63,12 @@ class SimConfig(C.Structure):
                 ("bucketSizeFocus", C.c_uint), ("capacity", C.c_size_t), ("box", Box), ("hc", HydroConst)]
 
 
+class RestartInfo(C.Structure):
+    _fields_ = [("iteration", C.c_uint64), ("numParticlesGlobal", C.c_uint64), ("numParticles", C.c_uint64),
+                ("dtype", C.c_int), ("hasTurbulence", C.c_int), ("time", C.c_double), ("minDt", C.c_double),
+                ("minDt_m1", C.c_double), ("box", Box)]
+
+
 # every symbol include/sphexa_b200.h declares (checked by tests/test_abi.py)
 SYMBOLS = [
     "sphb200_create", "sphb200_destroy", "sphb200_invalidate_records", "sphb200_last_error", "sphb200_sync", "sphb200_launch_count",
@@ -83,6 +89,9 @@ SYMBOLS = [
     "sphb200_sim_phase_times", "sphb200_sim_set_layout", "sphb200_sim_local_timestep", "sphb200_sim_global_leaves",
     "sphb200_sim_global_counts", "sphb200_sim_leaf_counts", "sphb200_sim_get_box", "sphb200_sim_set_dt",
     "sphb200_segment_max", "sphb200_mark_halo_leaves",
+    "sphb200_sim_get_config", "sphb200_sim_set_constants", "sphb200_sim_set_time", "sphb200_sim_set_box",
+    "sphb200_sim_turbulence", "sphb200_sim_save", "sphb200_restart_write", "sphb200_restart_open", "sphb200_restart_close",
+    "sphb200_restart_get_info", "sphb200_restart_attribute", "sphb200_restart_read_fields", "sphb200_restart_apply",
 ]
 
 lib.sphb200_last_error.restype = C.c_char_p
@@ -109,6 +118,22 @@ lib.sphb200_sim_total_neighbors.argtypes = [vp]
 for _n in ("sphb200_sim_num_leaves", "sphb200_sim_num_global_leaves"):
     getattr(lib, _n).argtypes = [vp]
 lib.sphb200_destroy.argtypes = [vp]
+lib.sphb200_sim_turbulence.restype = vp
+lib.sphb200_sim_turbulence.argtypes = [vp]
+lib.sphb200_sim_set_time.restype = None
+lib.sphb200_sim_set_time.argtypes = [vp, C.c_double]
+lib.sphb200_sim_set_box.restype = None
+lib.sphb200_sim_set_box.argtypes = [vp, vp]
+lib.sphb200_sim_save.argtypes = [vp, C.c_char_p, C.c_uint64, C.c_uint64]
+lib.sphb200_restart_write.argtypes = [C.c_char_p, vp, vp, vp, C.c_int, C.c_int, vp]
+lib.sphb200_restart_open.argtypes = [C.c_char_p, vp]
+lib.sphb200_restart_close.restype = None
+lib.sphb200_restart_close.argtypes = [vp]
+lib.sphb200_restart_get_info.argtypes = [vp, vp]
+lib.sphb200_restart_attribute.restype = C.c_int64
+lib.sphb200_restart_attribute.argtypes = [vp, C.c_char_p, vp, C.c_size_t]
+lib.sphb200_restart_read_fields.argtypes = [vp, C.c_uint64, C.c_uint64, C.c_int, vp]
+lib.sphb200_restart_apply.argtypes = [vp, vp]
 lib.sphb200_sim_destroy.argtypes = [vp]
 
 

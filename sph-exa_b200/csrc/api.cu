@@ -720,6 +720,32 @@ extern "C" void sphb200_sim_set_dt(sphb200_sim* s, double minDt, double minDt_m1
     s->minDt_m1 = minDt_m1;
 }
 
+extern "C" int sphb200_sim_get_config(const sphb200_sim* s, sphb200_sim_config* out)
+{
+    *out     = s->cfg;
+    out->box = s->box;
+    out->hc  = s->hydroConst();
+    return 0;
+}
+
+extern "C" int sphb200_sim_set_constants(sphb200_sim* s, const sphb200_hydro_const* hc)
+{
+    SPHB200_TRY
+    sphb200_hydro_const& c = s->cfg.hc;
+    if (hc->ngmax != c.ngmax) throw std::runtime_error("sim_set_constants: ngmax is fixed at creation");
+    if (hc->K != c.K) throw std::runtime_error("sim_set_constants: kernel normalisation differs from the tables");
+    if (hc->avClean != c.avClean) throw std::runtime_error("sim_set_constants: avClean is fixed at creation");
+    const void *wh = c.wh, *whd = c.whd;
+    c     = *hc;
+    c.wh  = wh;
+    c.whd = whd;
+    SPHB200_CATCH
+}
+
+extern "C" void sphb200_sim_set_time(sphb200_sim* s, double ttot) { s->ttot = ttot; }
+extern "C" void sphb200_sim_set_box(sphb200_sim* s, const sphb200_box* box) { s->box = *box; }
+extern "C" sphb200_turb* sphb200_sim_turbulence(const sphb200_sim* s) { return s->turb; }
+
 extern "C" int sphb200_sim_fields(sphb200_sim* s, sphb200_fields* out)
 {
     *out = s->table();

@@ -487,6 +487,73 @@ class DistHydroVeProp:
         return out
 
 
+    # ---- restart files (restart.py, csrc/checkpoint.cu)
+    def save_restart(self, path, iteration):
+        """every rank dumps its owned particles to `<path>.<rank>` (sphexa.cpp:232-246 writes the same content through
+        parallel HDF5); collective only in the sense that all ranks should call it at the same step"""
+        from . import restart
+        B = self.B
+        own = self.download_owned()
+        n = len(own["x"])
+        info = B.RestartInfo()
+        info.iteration, info.numParticlesGlobal, info.numParticles = iteration, self.n_global, n
+        info.dtype = self.dtype
+        info.time, info.minDt, info.minDt_m1 = self.ttot, self.minDt, self.minDt_m1
+        info.box = self.box
+        fs = B.Fields()
+        for k in B.FIELD_NAMES:
+            setattr(fs, k, None)
+        keep = []
+        for k in self.CONSERVED:
+            a = np.ascontiguousarray(own[k])
+            keep.append(a)
+            setattr(fs, k, a.ctypes.data)
+        p = restart.rank_path(path, self.rank, self.world)
+        hc = self._hc()
+        B.check(B.lib.sphb200_restart_write(p.encode(), C.byref(info), C.byref(hc), None, self.rank, self.world,
+                                            C.byref(fs)))
+        return p
+
+    def load_restart(self, path):
+        """this rank's share of a dump written by any number of ranks (file_init.hpp:93-140); the next sync
+        redistributes.  Returns the iteration stored in the dump."""
+        from . import restart
+        B = self.B
+        files = [restart.RestartFile(p) for p in restart.find_files(path)]
+        try:
+            counts = [int(f.info.numParticles) for f in files]
+            total = sum(counts)
+            if total != int(files[0].info.numParticlesGlobal):
+                raise B.SphError("restart: the files of the dump are incomplete")
+            if len(files) == self.world:
+                first, count = sum(counts[:self.rank]), counts[self.rank]
+            else:
+                first, count = restart.slice_for_rank(total, self.rank, self.world)
+            real = np.float64 if self.dtype == B.F64 else np.float32
+            arrays = {k: np.empty(count, np.float64 if k in B.ALWAYS_F64 else real) for k in self.CONSERVED}
+            filled, start = 0, 0
+            for f, c in zip(files, counts):
+                lo, hi = max(first, start), min(first + count, start + c)
+                if hi > lo:
+                    f.read_fields(lo - start, hi - lo, self.dtype, arrays, offset=filled)
+                    filled += hi - lo
+                start += c
+            info = files[0].info
+            self.n_global = total
+            self.minDt, self.minDt_m1, self.ttot = info.minDt, info.minDt_m1, info.time
+            self.lim, self.bc = list(info.box.lim), list(info.box.bc)
+            self.box = self.pkg.make_box(self.lim, self.bc)
+            for name, key in (("Kcour", "Kcour"), ("Krho", "Krho"), ("gamma", "gamma"), ("muiConst", "mui")):
+                v = files[0].attribute(name)
+                if v is not None:
+                    self.s[key] = float(v[0])
+            self.upload(arrays)
+            return int(info.iteration)
+        finally:
+            for f in files:
+                f.close()
+
+
 # ---------------------------------------------------------------------------------------------- bench entry (N > 1)
 def bench_main(args, pkg, METRIC, UNIT, ALGO_BYTES, load_peaks, ClockSampler):
     import torch

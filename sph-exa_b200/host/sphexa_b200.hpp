@@ -17,6 +17,9 @@
 #include <stdexcept>
 #include <string>
 #include <array>
+#include <memory>
+#include <vector>
+#include <algorithm>
 #include <utility>
 
 #include "sphexa_b200.h"
@@ -213,6 +216,44 @@ public:
         std::array<double, 10> q{};
         check(sphb200_sim_conserved(sim_, q.data()));
         return q;
+    }
+
+    //! @brief restart dump of the owned particles (sphexa.cpp:232-246; container: csrc/checkpoint.cu)
+    void saveRestart(const std::string& path, uint64_t iteration, uint64_t numParticlesGlobal)
+    {
+        check(sphb200_sim_save(sim_, path.c_str(), iteration, numParticlesGlobal));
+    }
+    /*! @brief restart from a single-file dump (file_init.hpp:93-140): reads particles [first, first+count), uploads
+     *         them and applies time, time steps, constants, box and turbulence state.  @return stored iteration */
+    uint64_t loadRestart(const std::string& path, int dtype, uint64_t first = 0, uint64_t count = ~uint64_t(0))
+    {
+        sphb200_restart* r = nullptr;
+        check(sphb200_restart_open(path.c_str(), &r));
+        std::unique_ptr<sphb200_restart, void (*)(sphb200_restart*)> guard(r, sphb200_restart_close);
+        sphb200_restart_info info;
+        check(sphb200_restart_get_info(r, &info));
+        if (count == ~uint64_t(0)) count = info.numParticles - first;
+        size_t eb = dtype == SPHB200_F64 ? 8 : 4;
+        std::vector<std::vector<char>> buf(14);
+        sphb200_fields h{};
+        void** realSlots[]  = {&h.h, &h.m, &h.vx, &h.vy, &h.vz, &h.x_m1, &h.y_m1, &h.z_m1, &h.du_m1, &h.alpha};
+        double** dblSlots[] = {&h.x, &h.y, &h.z, &h.temp};
+        int k = 0;
+        for (auto** slot : dblSlots)
+        {
+            buf[k].resize(std::max<size_t>(count * 8, 8));
+            *slot = reinterpret_cast<double*>(buf[k++].data());
+        }
+        for (auto** slot : realSlots)
+        {
+            buf[k].resize(std::max<size_t>(count * eb, 8));
+            *slot = buf[k++].data();
+        }
+        check(sphb200_restart_read_fields(r, first, count, dtype, &h));
+        check(sphb200_sim_upload(sim_, count, &h));
+        ctx_.sync();
+        check(sphb200_restart_apply(r, sim_));
+        return info.iteration;
     }
 
     // cstone::Domain getters (domain.hpp:382-429)

@@ -1,6 +1,7 @@
 // Compile/link check of the C++ host shim (and, on a GPU box, a 2-step Sedov 12^3 run through it).
 #include <cmath>
 #include <cstdio>
+#include <string>
 #include <vector>
 #include "sphexa_b200.hpp"
 
@@ -59,6 +60,27 @@ int main(int argc, char** argv)
         }
         std::printf("shim ok: n=%u leaves=%d neighbors=%llu minDt=%.6e\n", prop.nParticles(),
                     prop.octreeProperties().numLeafNodes, (unsigned long long)prop.totalNeighbors(), prop.minDt());
+        // restart: dump, reload into a second propagator, one more step on both, same time step and neighbor sum
+        {
+            std::string path = std::string(argc > 2 ? argv[2] : "/tmp") + "/sphb200_shim_restart.bin";
+            prop.saveRestart(path, 2, n);
+            HydroVeProp again(ctx, cfg);
+            uint64_t it = again.loadRestart(path, SPHB200_F64);
+            prop.computeForces();
+            prop.integrate();
+            again.computeForces();
+            again.integrate();
+            bool same = it == 2 && again.minDt() == prop.minDt() && again.ttot() == prop.ttot() &&
+                        again.totalNeighbors() == prop.totalNeighbors();
+            std::remove(path.c_str());
+            if (!same)
+            {
+                std::fprintf(stderr, "restart mismatch: it=%llu dt %.17g vs %.17g\n", (unsigned long long)it,
+                             again.minDt(), prop.minDt());
+                return 3;
+            }
+            std::printf("restart ok\n");
+        }
         // error path: precondition violation -> std::runtime_error
         bool threw = false;
         try

@@ -82,6 +82,44 @@ def main():
             if bad or abs(sim.minDt - ref_sim.minDt) > 1e-12 * ref_sim.minDt:
                 ok = False
                 print("MISMATCH", bad, flush=True)
+    # ---- restart: dump, reload on the same ranks (bit-identical continuation) and on one rank (same particles)
+    import tempfile
+    base = [tempfile.mkdtemp(prefix="sphb200_restart_") if rank == 0 else None]
+    dist.broadcast_object_list(base, 0)
+    path = os.path.join(base[0], "dump")
+    sim.save_restart(path, args.steps)
+    dist.barrier()
+    again = D.DistHydroVeProp(pkg, ctx, box, s, B.F64, rank, world, n)
+    it = again.load_restart(path)
+    ok = ok and it == args.steps and (again.minDt, again.minDt_m1, again.ttot) == (sim.minDt, sim.minDt_m1, sim.ttot)
+    for _ in range(2):
+        sim.step()
+        again.step()
+    a, b = sim.download_owned(), again.download_owned()
+    same = all(np.array_equal(a[k], b[k]) for k in a) and again.minDt == sim.minDt
+    flags = [None] * world
+    dist.all_gather_object(flags, bool(same))
+    gathered = [None] * world
+    dist.gather_object(a, gathered if rank == 0 else None, dst=0)
+    if rank == 0:
+        print(f"restart on {world} ranks bit-identical per rank: {flags}", flush=True)
+        ok = ok and all(flags)
+        one = D.DistHydroVeProp(pkg, ctx, box, s, B.F64, 0, 1, n)
+        one.load_restart(path)  # reads both files
+        for _ in range(2):
+            one.step()
+        w = one.download_owned()
+        keys = np.concatenate([g["keys"] for g in gathered])
+        order = np.argsort(keys, kind="stable")
+        ok = ok and np.array_equal(keys[order], w["keys"])
+        worst = 0.0
+        for k in sim.CONSERVED:
+            got = np.concatenate([g[k] for g in gathered])[order]
+            worst = max(worst, float(np.abs(got - w[k]).max() / max(np.abs(w[k]).max(), 1e-300)))
+        print(f"restart of the {world}-rank dump on 1 rank: max rel err {worst:.2e}", flush=True)
+        ok = ok and worst <= 1e-10
+        import shutil
+        shutil.rmtree(base[0], ignore_errors=True)
     flag = torch.tensor([1 if ok else 0], device="cuda")
     dist.broadcast(flag, 0)
     dist.barrier()

@@ -25,11 +25,12 @@ def test_shim_compiles_and_links(pkg):
 
 
 @pytest.mark.gpu
-def test_shim_runs_two_steps(pkg, ctx):
+def test_shim_runs_two_steps(pkg, ctx, tmp_path):
     build()
-    res = subprocess.run([EXE, "run"], capture_output=True, text=True, timeout=300)
+    res = subprocess.run([EXE, "run", str(tmp_path)], capture_output=True, text=True, timeout=300)
     assert res.returncode == 0, res.stdout + res.stderr
     assert "shim ok: n=1728" in res.stdout
+    assert "restart ok" in res.stdout
     # 12^3 lattice with h from ng0=100: every particle sees the same neighbor count (parity with tests/golden)
     import numpy as np
     g = np.load(os.path.join(ROOT, "tests", "golden", "sedov12_steps.npz"))

@@ -1,0 +1,100 @@
+"""Restart parity on the GPU: a run that is dumped and reloaded continues bit-identically.
+
+Reference behaviour: `sphexa --init dump.h5:k` resumes from step k of a dump written by the main loop
+(main/src/sphexa/sphexa.cpp:232-246, main/src/init/file_init.hpp:93-140); conserved fields, time-step history, box and
+the turbulence driver state are what travels (ve_hydro.hpp:75, particles_data.hpp:142-193, turbulence_data.hpp:90-125).
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def run_and_compare(pkg, ctx, tmp_path, f, box, s, dtype, before, after, turb_factory=None, tag="dump"):
+    from sph_exa_b200 import sim as S, restart, binding as B
+    n = f["x"].size
+    a = S.HydroVeProp(ctx, box, s, capacity=n, dtype=dtype)
+    ta = turb_factory() if turb_factory else None
+    if ta:
+        a.attachTurbulence(ta)
+    a.upload(f)
+    for _ in range(before):
+        a.step()
+    path = str(tmp_path / tag)
+    restart.save(a, path, iteration=before, num_particles_global=n)
+    for _ in range(after):
+        a.step()
+    want = a.download(with_keys=True)
+
+    b = S.HydroVeProp(ctx, box, s, capacity=n, dtype=dtype)
+    tb = turb_factory() if turb_factory else None
+    if tb:
+        b.attachTurbulence(tb)
+    it, n_glob = restart.load(b, path)
+    assert (it, n_glob) == (before, n)
+    assert b.ttot > 0
+    for _ in range(after):
+        b.step()
+    got = b.download(with_keys=True)
+    for k in list(B.CONSERVED) + ["keys"]:
+        assert np.array_equal(got[k], want[k]), k
+    assert (b.minDt, b.ttot) == (a.minDt, a.ttot)
+    if ta:
+        assert np.array_equal(ta.state()["phases"], tb.state()["phases"])
+        assert ta.rngState() == tb.rngState()
+        ta.close()
+        tb.close()
+    a.close()
+    b.close()
+
+
+@pytest.mark.parametrize("real", [np.float64, np.float32])
+def test_sedov_restart_continues_bit_identically(pkg, ctx, tmp_path, real):
+    dtype = pkg.F64 if real == np.float64 else pkg.MIXED
+    f, box, s = pkg.ic.sedov(24, "f64" if real == np.float64 else "mixed")
+    run_and_compare(pkg, ctx, tmp_path, f, box, s, dtype, before=3, after=3)
+
+
+def test_open_box_restart(pkg, ctx, tmp_path):
+    """Noh: open boundaries, the global box follows the particles and is part of the dump (box.hpp:168-175)"""
+    f, box, s = pkg.ic.noh(20)
+    run_and_compare(pkg, ctx, tmp_path, f, box, s, pkg.F64, before=2, after=2)
+
+
+def test_turbulence_restart_carries_the_driver_state(pkg, ctx, tmp_path):
+    """stirred run: the OU phases and the random engine resume where the dump left them"""
+    from sph_exa_b200.turbulence import Turbulence
+    f, box, s = pkg.ic.turbulence(20)
+    run_and_compare(pkg, ctx, tmp_path, f, box, s, pkg.F64, before=2, after=3, turb_factory=Turbulence)
+
+
+def test_restart_into_other_precision(pkg, ctx, tmp_path):
+    """an f64 dump starts a mixed-precision run: the reader converts, and the result equals a mixed run started from
+    the rounded state"""
+    from sph_exa_b200 import sim as S, restart, binding as B
+    f, box, s = pkg.ic.sedov(20, "f64")
+    n = f["x"].size
+    a = S.HydroVeProp(ctx, box, s, capacity=n, dtype=pkg.F64)
+    a.upload(f)
+    a.step()
+    path = str(tmp_path / "d64")
+    restart.save(a, path, iteration=1, num_particles_global=n)
+    state = a.download()
+    a.close()
+
+    b = S.HydroVeProp(ctx, box, s, capacity=n, dtype=pkg.MIXED)
+    restart.load(b, path)
+    b.step()
+    got = b.download()
+    b.close()
+
+    with restart.RestartFile(path) as rf:
+        info = rf.info
+        s2 = dict(s, minDt=info.minDt, minDt_m1=info.minDt_m1)
+    c = S.HydroVeProp(ctx, box, s2, capacity=n, dtype=pkg.MIXED)
+    c.upload({k: (v if k in B.ALWAYS_F64 else v.astype(np.float32)) for k, v in state.items()})
+    c.step()
+    want = c.download()
+    c.close()
+    for k in B.CONSERVED:
+        assert np.array_equal(got[k], want[k]), k
