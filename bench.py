@@ -162,10 +162,10 @@ NCU_KERNEL = {"MomentumAndEnergy": "momentumEnergyKernel", "AVswitches": "avSwit
 
 def ncu_traffic(phase, args):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed
-    `ncu --set full` capture of this same workload (profiles/ncu_full_r01c_summary.csv: Sedov 200^3, f64).
+    `ncu --set full` capture of this same workload (profiles/ncu_full_r01d_summary.csv: Sedov 200^3, f64).
     None for any other workload: the capture does not transfer."""
     import csv
-    path = os.path.join(ROOT, "profiles", "ncu_full_r01c_summary.csv")
+    path = os.path.join(ROOT, "profiles", "ncu_full_r01d_summary.csv")
     if args.side != 200 or args.dtype != "f64" or phase not in NCU_KERNEL or not os.path.exists(path):
         return None, None
     with open(path) as fh:
@@ -174,8 +174,24 @@ def ncu_traffic(phase, args):
     ir, iw = hdr.index("dram_read [Gbyte]"), hdr.index("dram_write [Gbyte]")
     for r in rows[1:]:
         if NCU_KERNEL[phase] in r[0]:
-            return (float(r[ir]) + float(r[iw])) * 1e9, "profiles/ncu_full_r01c_summary.csv"
+            return (float(r[ir]) + float(r[iw])) * 1e9, "profiles/ncu_full_r01d_summary.csv"
     return None, None
+
+
+def ncu_column(phase, args, column):
+    """one column of the committed ncu summary for the dominant kernel (None for other workloads)"""
+    import csv
+    path = os.path.join(ROOT, "profiles", "ncu_full_r01d_summary.csv")
+    if args.side != 200 or args.dtype != "f64" or phase not in NCU_KERNEL or not os.path.exists(path):
+        return None
+    with open(path) as fh:
+        rows = list(csv.reader(fh))
+    if column not in rows[0]:
+        return None
+    for r in rows[1:]:
+        if NCU_KERNEL[phase] in r[0]:
+            return float(r[rows[0].index(column)])
+    return None
 
 
 def main():
@@ -262,6 +278,16 @@ def main():
     step_bytes = (1360 if args.dtype == "f64" else 920) * n
     roofline["step_achieved_gbs"] = step_bytes / (ms_per_step * 1e-3) / 1e9
     roofline["step_frac"] = roofline["step_achieved_gbs"] / peak
+    # what actually limits the pair kernels: the L1 gather stage and the fp64 pipe.  Pair math
+    # per SURVEY 8d (flop per neighbor pair); L1 figure from the committed ncu capture of this workload.
+    pair_flop = {"XMass": 22, "Normalization & Gradh": 36, "IadVelocityDivCurl": 96, "AVswitches": 58,
+                 "MomentumAndEnergy": 150}
+    if dom in pair_flop:
+        tf = pair_flop[dom] * float(total_nb) / (phase_ms[dom] * 1e-3) / 1e12
+        roofline["limiter"] = {"unit": "L1 data-stage wavefronts (gather) + fp64 pipe",
+                               "pair_tflops": tf, "precision": "fp64" if args.dtype == "f64" else "fp32+fp64",
+                               "fp64_vector_peak_nominal_tflops": 37.0,
+                               "l1_wavefront_pct_of_peak": ncu_column(dom, args, "l1_data_wavefronts_pct [%]")}
 
     # ---------------- end to end through the C ABI with host buffers
     e2e = None
