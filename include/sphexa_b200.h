@@ -403,6 +403,40 @@ int sphb200_restart_read_fields(const sphb200_restart*, uint64_t first, uint64_t
  * has one and a driver is attached) */
 int sphb200_restart_apply(const sphb200_restart*, sphb200_sim*);
 
+/* ---- f3: block time steps (HydroVeBdtProp, main/src/propagator/ve_hydro_bdt.hpp) ----
+ * cstone::GroupView (domain/include/cstone/traversal/groups.hpp): numGroups runs [groupStart[g], groupEnd[g]) of
+ * SFC-consecutive particles inside [firstBody, lastBody); device arrays */
+typedef struct sphb200_group_view
+{
+    uint32_t firstBody, lastBody, numGroups;
+    const uint32_t* groupStart;
+    const uint32_t* groupEnd;
+} sphb200_group_view;
+/* computeSpatialGroups (sph/include/sph/groups.cu:30-47 -> cstone::computeGroupSplits, traversal/groups.cuh:266-330):
+ * runs of 32 from `first`, cut where consecutive particles are further apart than tolFactor x the smallest leaf edge
+ * under the run.  groups[0..numGroups] = delimiters (groupStart = groups, groupEnd = groups + 1); capacity in groups;
+ * SPHB200_ERR_CAPACITY with the required count in *numGroups_h when it does not fit */
+int sphb200_compute_groups(sphb200_ctx*, uint32_t first, uint32_t last, const double* x, const double* y, const double* z,
+                           const uint64_t* leaves, int numLeaves, const uint32_t* layout, const sphb200_box* box_h,
+                           float tolFactor, uint32_t* groups, uint32_t capacity, uint32_t* numGroups_h);
+/* groupDivvTimestepGpu / groupAccTimestepGpu (sph/include/sph/ts_groups.cu:16-78): groupDt[g] = min(groupDt[g], ...) */
+int sphb200_group_divv_timestep(sphb200_ctx*, int dtype, float Krho, const sphb200_group_view* grp_h, const void* divv,
+                                float* groupDt);
+int sphb200_group_acc_timestep(sphb200_ctx*, int dtype, float etaAcc, const sphb200_group_view* grp_h, const void* ax,
+                               const void* ay, const void* az, float* groupDt);
+/* the group minimum momentumAndEnergyGpu folds into groupDt (hydro_ve/momentum_energy_gpu.cu:98-104), from the
+ * per-particle Courant steps sphb200_momentum_energy_targets leaves in dtParticle (indexed like the fields) */
+int sphb200_group_min_timestep(sphb200_ctx*, int dtype, const sphb200_group_view* grp_h, const void* dtParticle,
+                               float* groupDt);
+/* storeRungGpu (ts_groups.cu:80-103) */
+int sphb200_store_rung(sphb200_ctx*, const sphb200_group_view* grp_h, uint8_t rung, uint8_t* particleRungs);
+/* extractGroupGpu (sph/include/sph/groups.hpp:32-47): out[k] = grp[indices[first + k]], k < last - first */
+int sphb200_extract_groups(sphb200_ctx*, const sphb200_group_view* grp_h, const uint32_t* indices, uint32_t first,
+                           uint32_t last, uint32_t* outStart, uint32_t* outEnd);
+/* the particles of a set of groups as an ascending index list: what the *_targets operators below take.
+ * targets: device, room for lastBody - firstBody entries */
+int sphb200_targets_from_groups(sphb200_ctx*, const sphb200_group_view* grp_h, uint32_t* targets, uint32_t* numTargets_h);
+
 #ifdef __cplusplus
 }
 #endif

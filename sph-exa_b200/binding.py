@@ -63,6 +63,12 @@ class SimConfig(C.Structure):
                 ("bucketSizeFocus", C.c_uint), ("capacity", C.c_size_t), ("box", Box), ("hc", HydroConst)]
 
 
+class GroupView(C.Structure):
+    """cstone::GroupView (domain/include/cstone/traversal/groups.hpp)"""
+    _fields_ = [("firstBody", C.c_uint32), ("lastBody", C.c_uint32), ("numGroups", C.c_uint32),
+                ("groupStart", vp), ("groupEnd", vp)]
+
+
 class RestartInfo(C.Structure):
     _fields_ = [("iteration", C.c_uint64), ("numParticlesGlobal", C.c_uint64), ("numParticles", C.c_uint64),
                 ("dtype", C.c_int), ("hasTurbulence", C.c_int), ("time", C.c_double), ("minDt", C.c_double),
@@ -92,6 +98,8 @@ SYMBOLS = [
     "sphb200_sim_get_config", "sphb200_sim_set_constants", "sphb200_sim_set_time", "sphb200_sim_set_box",
     "sphb200_sim_turbulence", "sphb200_sim_save", "sphb200_restart_write", "sphb200_restart_open", "sphb200_restart_close",
     "sphb200_restart_get_info", "sphb200_restart_attribute", "sphb200_restart_read_fields", "sphb200_restart_apply",
+    "sphb200_compute_groups", "sphb200_group_divv_timestep", "sphb200_group_acc_timestep",
+    "sphb200_group_min_timestep", "sphb200_store_rung", "sphb200_extract_groups", "sphb200_targets_from_groups",
 ]
 
 lib.sphb200_last_error.restype = C.c_char_p
@@ -134,6 +142,14 @@ lib.sphb200_restart_attribute.restype = C.c_int64
 lib.sphb200_restart_attribute.argtypes = [vp, C.c_char_p, vp, C.c_size_t]
 lib.sphb200_restart_read_fields.argtypes = [vp, C.c_uint64, C.c_uint64, C.c_int, vp]
 lib.sphb200_restart_apply.argtypes = [vp, vp]
+lib.sphb200_compute_groups.argtypes = [vp, C.c_uint32, C.c_uint32, vp, vp, vp, vp, C.c_int, vp, vp, C.c_float, vp,
+                                       C.c_uint32, vp]
+lib.sphb200_group_divv_timestep.argtypes = [vp, C.c_int, C.c_float, vp, vp, vp]
+lib.sphb200_group_acc_timestep.argtypes = [vp, C.c_int, C.c_float, vp, vp, vp, vp, vp]
+lib.sphb200_group_min_timestep.argtypes = [vp, C.c_int, vp, vp, vp]
+lib.sphb200_store_rung.argtypes = [vp, vp, C.c_uint8, vp]
+lib.sphb200_extract_groups.argtypes = [vp, vp, vp, C.c_uint32, C.c_uint32, vp, vp]
+lib.sphb200_targets_from_groups.argtypes = [vp, vp, vp, vp]
 lib.sphb200_sim_destroy.argtypes = [vp]
 
 

@@ -324,3 +324,79 @@ def conserved_dict(v):
     r["linmom"] = (r["linmom_x"] ** 2 + r["linmom_y"] ** 2 + r["linmom_z"] ** 2) ** 0.5
     r["angmom"] = (r["angmom_x"] ** 2 + r["angmom_y"] ** 2 + r["angmom_z"] ** 2) ** 0.5
     return r
+
+
+# ---------------------------------------------------------------- groups / block time steps (csrc/groups.cu)
+class Groups:
+    """device twin of sph::GroupData (sph/include/sph/groups.hpp): delimiters or separate start/end arrays"""
+
+    def __init__(self, first, last, start, end):
+        self.firstBody, self.lastBody = int(first), int(last)
+        self.start, self.end = start, end
+        self.numGroups = start.numel()
+
+    def view(self, lo=0, hi=None):
+        """makeSlicedView (groups.hpp:50-58): groups [lo, hi)"""
+        hi = self.numGroups if hi is None else hi
+        v = B.GroupView()
+        v.firstBody, v.lastBody, v.numGroups = self.firstBody, self.lastBody, hi - lo
+        v.groupStart = self.start.data_ptr() + 4 * lo
+        v.groupEnd = self.end.data_ptr() + 4 * lo
+        return v
+
+
+def computeGroups(ctx, first, last, x, y, z, tree, box, tolFactor=2.0):
+    """computeSpatialGroups (sph/include/sph/groups.cu:30-47); tree: ops.Octree with layout"""
+    n = last - first
+    cap = n // 32 + 2
+    while True:
+        delim = torch.empty(cap + 1, dtype=torch.int32, device=x.device)
+        ng = C.c_uint32(0)
+        rc = lib.sphb200_compute_groups(ctx.h, first, last, ptr(x), ptr(y), ptr(z), ptr(tree.leaves), tree.numLeaves,
+                                        ptr(tree.layout), C.byref(box), C.c_float(tolFactor), ptr(delim), cap,
+                                        C.byref(ng))
+        if rc == B.ERR_CAPACITY:
+            cap = ng.value + 1
+            continue
+        check(rc)
+        break
+    delim = delim[:ng.value + 1]
+    return Groups(first, last, delim[:-1], delim[1:])
+
+
+def groupDivvTimestep(ctx, Krho, grp_view, divv, groupDt):
+    check(lib.sphb200_group_divv_timestep(ctx.h, B.F64 if divv.dtype == torch.float64 else B.MIXED, C.c_float(Krho),
+                                          C.byref(grp_view), ptr(divv), ptr(groupDt)))
+
+
+def groupAccTimestep(ctx, etaAcc, grp_view, ax, ay, az, groupDt):
+    check(lib.sphb200_group_acc_timestep(ctx.h, B.F64 if ax.dtype == torch.float64 else B.MIXED, C.c_float(etaAcc),
+                                         C.byref(grp_view), ptr(ax), ptr(ay), ptr(az), ptr(groupDt)))
+
+
+def groupMinTimestep(ctx, grp_view, dtParticle, groupDt):
+    check(lib.sphb200_group_min_timestep(ctx.h, B.F64 if dtParticle.dtype == torch.float64 else B.MIXED,
+                                         C.byref(grp_view), ptr(dtParticle), ptr(groupDt)))
+
+
+def storeRung(ctx, grp_view, rung, particleRungs):
+    check(lib.sphb200_store_rung(ctx.h, C.byref(grp_view), C.c_uint8(rung), ptr(particleRungs)))
+
+
+def extractGroups(ctx, grp, indices, first, last):
+    """extractGroupGpu (groups.hpp:32-47): Groups made of grp[indices[first:last]]"""
+    n = last - first
+    out = torch.empty(2 * max(n, 1), dtype=torch.int32, device=indices.device)
+    v = grp.view()
+    check(lib.sphb200_extract_groups(ctx.h, C.byref(v), ptr(indices), first, last, ptr(out), ptr(out[max(n, 1):])))
+    return Groups(grp.firstBody, grp.lastBody, out[:n], out[max(n, 1):max(n, 1) + n])
+
+
+def targetsFromGroups(ctx, grp_view):
+    """ascending index list of the particles in the groups of grp_view"""
+    n = grp_view.lastBody - grp_view.firstBody
+    dev = torch.device("cuda", torch.cuda.current_device())
+    t = torch.empty(max(n, 1), dtype=torch.int32, device=dev)
+    nt = C.c_uint32(0)
+    check(lib.sphb200_targets_from_groups(ctx.h, C.byref(grp_view), ptr(t), C.byref(nt)))
+    return t[:nt.value]
