@@ -437,6 +437,77 @@ int sphb200_extract_groups(sphb200_ctx*, const sphb200_group_view* grp_h, const 
  * targets: device, room for lastBody - firstBody entries */
 int sphb200_targets_from_groups(sphb200_ctx*, const sphb200_group_view* grp_h, uint32_t* targets, uint32_t* numTargets_h);
 
+/* GroupView scope of the target-range operators.  The reference's GPU operators take a GroupView (sph_gpu.hpp:13-82)
+ * and the tree view carries searchExtFactor (octree.hpp:315); here both are context state: while a scope is set,
+ * sphb200_find_neighbors, _xmass, _ve_def_gradh, _iad_divv_curlv, _av_switches and _momentum_energy only process the
+ * targets i of [first,last) with active[i] != 0 (indexed like the fields) and leave every output of the others
+ * untouched.  NULL resets (all targets, factor 1, no per-target Courant output). */
+typedef struct sphb200_op_scope
+{
+    const uint8_t* active;  /* device, NULL = all of [first,last) */
+    float searchExtFactor;  /* <= 0: 1.  > 1 while particles have drifted since the tree was built */
+    void* dtParticle;       /* device T[...] indexed like the fields or NULL: Courant step of every processed target,
+                               written by sphb200_momentum_energy */
+} sphb200_op_scope;
+int sphb200_set_scope(sphb200_ctx*, const sphb200_op_scope* scope_h);
+/* active[0..n) = 0, then active[i] = 1 for the members of the groups */
+int sphb200_mark_groups(sphb200_ctx*, const sphb200_group_view* grp_h, uint32_t n, uint8_t* active);
+
+/* sortGroupDt (sph/include/sph/ts_rungs.hpp:55-66): stable ascending sort of groupDt[0..numGroups) in place,
+ * groupIndices[k] = previous position of the k-th smallest */
+int sphb200_sort_group_dt(sphb200_ctx*, float* groupDt, uint32_t* groupIndices, uint32_t numGroups);
+/* cstone::sequenceGpu (primitives_gpu.h:55): out[k] = first + k */
+int sphb200_sequence(sphb200_ctx*, uint32_t* out, uint32_t n, uint32_t first);
+/* findRungRanges (ts_rungs.hpp:115-129) on sorted groupDt: rungRanges_h[0] = 0, [r] = lower_bound(2^r minDt) for
+ * r < numRungs, numGroups for the rest (5 entries); minDt < 0: use groupDt[0].  minGroupDt_h (may be NULL) =
+ * timestepRangeGpu (:69-75): {groupDt[0], groupDt[uint32(fastFraction * numGroups)]} */
+int sphb200_rung_ranges(sphb200_ctx*, float minDt, const float* groupDt, uint32_t numGroups, int numRungs,
+                        float fastFraction, uint32_t* rungRanges_h, float* minGroupDt_h);
+
+/* driftPositionsGpu (sph/include/sph/positions_gpu.cu:47-111): drift the groups' particles back by dt_back to where
+ * their accelerations were evaluated, then forward by dt: x,y,z,v,temp rewritten, x_m1/du_m1 kept, no fold into the
+ * box.  dt_m1_h: 4 floats (Timestep::dt_m1), rung: device per-particle rung or NULL (= rung 0) */
+int sphb200_drift_positions(sphb200_ctx*, int dtype, const sphb200_group_view* grp_h, float dt, float dt_back,
+                            const float* dt_m1_h, const uint8_t* rung, const sphb200_hydro_const* hc_h,
+                            const sphb200_fields* f_h);
+/* computePositionsGpu (positions_gpu.cu:118-180): advance the groups' particles by dt (x,y,z,v,x_m1,temp,du_m1) */
+int sphb200_compute_positions_groups(sphb200_ctx*, int dtype, const sphb200_group_view* grp_h, float dt,
+                                     const float* dt_m1_h, const uint8_t* rung, const sphb200_box* box_h,
+                                     const sphb200_hydro_const* hc_h, const sphb200_fields* f_h);
+/* updateSmoothingLengthGpu (sph/include/sph/update_h_gpu.cu:39-60); nc indexed like h */
+int sphb200_update_h_groups(sphb200_ctx*, int dtype, const sphb200_group_view* grp_h, unsigned ng0, const uint32_t* nc,
+                            void* h);
+
+/* ---- HydroVeBdtProp for one rank on a sphb200_sim (main/src/propagator/ve_hydro_bdt.hpp:51-420, g = 0) ----
+ * sphb200_sim_bdt_enable switches the sim to block time steps: per-group time steps sorted into <= 4 power-of-two
+ * rungs; a hierarchy of 2^(numRungs-1) substeps of length nextDt starts with a full sync (domain sync + new spatial
+ * groups), the substeps in between only touch the groups of the rungs that are due (partialSync: no re-sort, search
+ * extent factor x1.012 per substep), every other particle is drifted.  safetySteps > 0 forces numRungs = 1 for that
+ * many hierarchies (HydroVeBdtProp::load after a split restart). */
+typedef struct sphb200_bdt_info
+{
+    float nextDt, elapsedDt, totDt;
+    int numRungs, substep;
+    uint32_t rungRanges[5];
+    float dt_m1[4], dt_drift[4];
+    uint32_t numGroups;       /* spatial groups of the last full sync */
+    uint32_t numActiveGroups; /* groups whose forces were evaluated in the last computeForces */
+    float searchExtFactor;
+    int isSynced; /* Propagator::isSynced: the next computeForces starts with a full sync */
+} sphb200_bdt_info;
+/* etaAcc, eps <= 0: ParticlesData defaults 0.2 and 0.005 (acceleration criterion etaAcc * sqrt(eps) / sqrt(|a|)) */
+int sphb200_sim_bdt_enable(sphb200_sim*, int safetySteps, double etaAcc, double eps);
+int sphb200_sim_bdt_compute_forces(sphb200_sim*); /* sync (full or partial) + forces of the active rungs */
+int sphb200_sim_bdt_integrate(sphb200_sim*);      /* computeRungs + advance/drift + updateSmoothingLength */
+int sphb200_sim_bdt_step(sphb200_sim*);
+int sphb200_sim_bdt_info(const sphb200_sim*, sphb200_bdt_info* out);
+/* device views for tests: per-particle rung [nWithHalos], groupDt [numGroups], and the active-target mask */
+const uint8_t* sphb200_sim_bdt_rungs(const sphb200_sim*);
+const float* sphb200_sim_bdt_group_dt(const sphb200_sim*);
+const uint8_t* sphb200_sim_bdt_active(const sphb200_sim*);
+/* groups of the last full sync in time-step order (tsGroups_): start/end device arrays of info.numGroups entries */
+int sphb200_sim_bdt_groups(const sphb200_sim*, sphb200_group_view* out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -244,6 +244,30 @@ def positions(first, last, dt, dt_m1, box, x, y, z, vx, vy, vz, x_m1, y_m1, z_m1
                                                      P(du), P(du_m1), P(h), C.c_double(mui), C.c_double(gamma))
 
 
+def drift(idx, dt, dt_back, dt_m1, rung, x, y, z, vx, vy, vz, x_m1, y_m1, z_m1, ax, ay, az, temp, du, du_m1, mui, gamma):
+    """driftKernel (sph/include/sph/positions_gpu.cu:47-90) for the particles idx (uint32), built from the reference's
+    positionUpdate / energyUpdate"""
+    idx = np.ascontiguousarray(idx, np.uint32)
+    dt_m1 = np.ascontiguousarray(dt_m1, np.float32)
+    getattr(lib(), "ref_drift_" + _sfx(vx.dtype))(P(idx), C.c_uint32(idx.size), C.c_float(dt), C.c_float(dt_back),
+                                                  P(dt_m1), P(rung), P(x), P(y), P(z), P(vx), P(vy), P(vz), P(x_m1),
+                                                  P(y_m1), P(z_m1), P(ax), P(ay), P(az), P(temp), P(du), P(du_m1),
+                                                  C.c_double(mui), C.c_double(gamma))
+
+
+def positions_rung(idx, dt, dt_m1, rung, box, x, y, z, vx, vy, vz, x_m1, y_m1, z_m1, ax, ay, az, temp, du, du_m1, h,
+                   mui, gamma):
+    """computePositionsKernel (positions_gpu.cu:118-161) for the particles idx"""
+    idx = np.ascontiguousarray(idx, np.uint32)
+    dt_m1 = np.ascontiguousarray(dt_m1, np.float32)
+    lim, bc = _box(box)
+    getattr(lib(), "ref_positions_rung_" + _sfx(h.dtype))(P(idx), C.c_uint32(idx.size), C.c_float(dt), P(dt_m1),
+                                                          P(rung), P(lim), P(bc), P(x), P(y), P(z), P(vx), P(vy),
+                                                          P(vz), P(x_m1), P(y_m1), P(z_m1), P(ax), P(ay), P(az),
+                                                          P(temp), P(du), P(du_m1), P(h), C.c_double(mui),
+                                                          C.c_double(gamma))
+
+
 def update_h(first, last, ng0, nc, h):
     getattr(lib(), "ref_update_h_" + _sfx(h.dtype))(C.c_uint32(first), C.c_uint32(last), C.c_uint(ng0), P(nc), P(h))
 

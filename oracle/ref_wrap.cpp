@@ -409,6 +409,74 @@ struct Hydro
         }
     }
 
+
+    // driftKernel (sph/include/sph/positions_gpu.cu:47-90) on an index list: the block-time-step propagator exists only
+    // as CUDA kernels in the reference; the two functions below call the same host-callable building blocks
+    // (sph::positionUpdate, sph::energyUpdate) in the kernels' order
+    static void drift(const uint32_t* idx, uint32_t count, float dt, float dt_back, const float* dt_m1,
+                      const uint8_t* rung, double* x, double* y, double* z, T* vx, T* vy, T* vz, const T* x_m1,
+                      const T* y_m1, const T* z_m1, const T* ax, const T* ay, const T* az, double* temp,
+                      const double* du, const T* du_m1, T muiConst, double gamma)
+    {
+        using cstone::Vec3;
+        cstone::Box<double> noPbc(0, 1, cstone::BoundaryType::open);
+        T constCv = sph::idealGasCv(muiConst, gamma);
+        for (uint32_t k = 0; k < count; ++k)
+        {
+            uint32_t i       = idx[k];
+            float dt_m1_rung = rung ? dt_m1[rung[i]] : dt_m1[0];
+            Vec3<double> An{double(ax[i]), double(ay[i]), double(az[i])};
+            Vec3<double> Xnback{x[i], y[i], z[i]};
+            Vec3<double> dXn{double(x_m1[i]), double(y_m1[i]), double(z_m1[i])};
+            auto [Xn_recov, ig0, ig1] = sph::positionUpdate(-dt_back, dt_m1_rung, Xnback, An, dXn, noPbc);
+            auto [Xnp1, Vnp1, ig2]    = sph::positionUpdate(dt, dt_m1_rung, Xn_recov, An, dXn, noPbc);
+            x[i] = Xnp1[0]; y[i] = Xnp1[1]; z[i] = Xnp1[2];
+            vx[i] = Vnp1[0]; vy[i] = Vnp1[1]; vz[i] = Vnp1[2];
+            T cv         = constCv;
+            auto u_recov = sph::energyUpdate(double(temp[i] * cv), -dt_back, dt_m1_rung, du[i], double(du_m1[i]));
+            temp[i]      = sph::energyUpdate(u_recov, dt, dt_m1_rung, du[i], double(du_m1[i])) / cv;
+        }
+    }
+
+    // computePositionsKernel (positions_gpu.cu:118-161) on an index list
+    static void positionsRung(const uint32_t* idx, uint32_t count, float dt, const float* dt_m1, const uint8_t* rung,
+                              const cstone::Box<double>& box, double* x, double* y, double* z, T* vx, T* vy, T* vz,
+                              T* x_m1, T* y_m1, T* z_m1, const T* ax, const T* ay, const T* az, double* temp,
+                              const double* du, T* du_m1, const T* h, T muiConst, double gamma)
+    {
+        using cstone::Vec3;
+        bool fbcX   = (box.boundaryX() == cstone::BoundaryType::fixed);
+        bool fbcY   = (box.boundaryY() == cstone::BoundaryType::fixed);
+        bool fbcZ   = (box.boundaryZ() == cstone::BoundaryType::fixed);
+        bool anyFBC = fbcX || fbcY || fbcZ;
+        T constCv   = sph::idealGasCv(muiConst, gamma);
+        for (uint32_t k = 0; k < count; ++k)
+        {
+            uint32_t i = idx[k];
+            if (anyFBC && vx[i] == T(0) && vy[i] == T(0) && vz[i] == T(0))
+            {
+                if (sph::fbcCheck(x[i], h[i], box.xmax(), box.xmin(), fbcX) ||
+                    sph::fbcCheck(y[i], h[i], box.ymax(), box.ymin(), fbcY) ||
+                    sph::fbcCheck(z[i], h[i], box.zmax(), box.zmin(), fbcZ))
+                {
+                    continue;
+                }
+            }
+            float dt_m1_rung = rung ? dt_m1[rung[i]] : dt_m1[0];
+            Vec3<double> A{double(ax[i]), double(ay[i]), double(az[i])};
+            Vec3<double> X{x[i], y[i], z[i]};
+            Vec3<double> X_m1{double(x_m1[i]), double(y_m1[i]), double(z_m1[i])};
+            auto [Xnp1, Vnp1, dXnp1] = sph::positionUpdate(dt, dt_m1_rung, X, A, X_m1, box);
+            x[i] = Xnp1[0]; y[i] = Xnp1[1]; z[i] = Xnp1[2];
+            x_m1[i] = dXnp1[0]; y_m1[i] = dXnp1[1]; z_m1[i] = dXnp1[2];
+            vx[i] = Vnp1[0]; vy[i] = Vnp1[1]; vz[i] = Vnp1[2];
+            T cv       = constCv;
+            auto u_old = temp[i] * cv;
+            temp[i]    = sph::energyUpdate(double(u_old), dt, dt_m1_rung, du[i], double(du_m1[i])) / cv;
+            du_m1[i]   = du[i];
+        }
+    }
+
     static void updateH(uint32_t first, uint32_t last, unsigned ng0, const unsigned* nc, T* h)
     {
 #pragma omp parallel for schedule(static)
@@ -506,6 +574,25 @@ struct Hydro
         BOX;                                                                                                          \
         Hydro<T>::positions(first, last, dt, dt_m1, box, x, y, z, vx, vy, vz, x_m1, y_m1, z_m1, ax, ay, az, temp,    \
                             du, du_m1, h, T(muiConst), gamma);                                                       \
+    }                                                                                                                 \
+    extern "C" void ref_drift_##SUF(const uint32_t* idx, uint32_t count, float dt, float dt_back, const float* dt_m1, \
+                                    const uint8_t* rung, double* x, double* y, double* z, T* vx, T* vy, T* vz,       \
+                                    const T* x_m1, const T* y_m1, const T* z_m1, const T* ax, const T* ay,           \
+                                    const T* az, double* temp, const double* du, const T* du_m1, double muiConst,    \
+                                    double gamma)                                                                     \
+    {                                                                                                                 \
+        Hydro<T>::drift(idx, count, dt, dt_back, dt_m1, rung, x, y, z, vx, vy, vz, x_m1, y_m1, z_m1, ax, ay, az,     \
+                        temp, du, du_m1, T(muiConst), gamma);                                                        \
+    }                                                                                                                 \
+    extern "C" void ref_positions_rung_##SUF(const uint32_t* idx, uint32_t count, float dt, const float* dt_m1,      \
+                                             const uint8_t* rung, const double* lim, const int* bc, double* x,       \
+                                             double* y, double* z, T* vx, T* vy, T* vz, T* x_m1, T* y_m1, T* z_m1,   \
+                                             const T* ax, const T* ay, const T* az, double* temp, const double* du,  \
+                                             T* du_m1, const T* h, double muiConst, double gamma)                    \
+    {                                                                                                                 \
+        BOX;                                                                                                          \
+        Hydro<T>::positionsRung(idx, count, dt, dt_m1, rung, box, x, y, z, vx, vy, vz, x_m1, y_m1, z_m1, ax, ay, az, \
+                                temp, du, du_m1, h, T(muiConst), gamma);                                             \
     }                                                                                                                 \
     extern "C" void ref_update_h_##SUF(uint32_t first, uint32_t last, unsigned ng0, const unsigned* nc, T* h)        \
     {                                                                                                                 \

@@ -69,6 +69,19 @@ class GroupView(C.Structure):
                 ("groupStart", vp), ("groupEnd", vp)]
 
 
+class OpScope(C.Structure):
+    """sphb200_op_scope: the GroupView argument / searchExtFactor of the reference's GPU operators"""
+    _fields_ = [("active", vp), ("searchExtFactor", C.c_float), ("dtParticle", vp)]
+
+
+class BdtInfo(C.Structure):
+    """sphb200_bdt_info: sph::Timestep (sph/include/sph/timestep.h:42-66) + group counts"""
+    _fields_ = [("nextDt", C.c_float), ("elapsedDt", C.c_float), ("totDt", C.c_float), ("numRungs", C.c_int),
+                ("substep", C.c_int), ("rungRanges", C.c_uint32 * 5), ("dt_m1", C.c_float * 4),
+                ("dt_drift", C.c_float * 4), ("numGroups", C.c_uint32), ("numActiveGroups", C.c_uint32),
+                ("searchExtFactor", C.c_float), ("isSynced", C.c_int)]
+
+
 class RestartInfo(C.Structure):
     _fields_ = [("iteration", C.c_uint64), ("numParticlesGlobal", C.c_uint64), ("numParticles", C.c_uint64),
                 ("dtype", C.c_int), ("hasTurbulence", C.c_int), ("time", C.c_double), ("minDt", C.c_double),
@@ -100,6 +113,11 @@ SYMBOLS = [
     "sphb200_restart_get_info", "sphb200_restart_attribute", "sphb200_restart_read_fields", "sphb200_restart_apply",
     "sphb200_compute_groups", "sphb200_group_divv_timestep", "sphb200_group_acc_timestep",
     "sphb200_group_min_timestep", "sphb200_store_rung", "sphb200_extract_groups", "sphb200_targets_from_groups",
+    "sphb200_set_scope", "sphb200_mark_groups", "sphb200_sort_group_dt", "sphb200_sequence", "sphb200_rung_ranges",
+    "sphb200_drift_positions", "sphb200_compute_positions_groups", "sphb200_update_h_groups",
+    "sphb200_sim_bdt_enable", "sphb200_sim_bdt_compute_forces", "sphb200_sim_bdt_integrate", "sphb200_sim_bdt_step",
+    "sphb200_sim_bdt_info", "sphb200_sim_bdt_rungs", "sphb200_sim_bdt_group_dt", "sphb200_sim_bdt_active",
+    "sphb200_sim_bdt_groups",
 ]
 
 lib.sphb200_last_error.restype = C.c_char_p
@@ -151,6 +169,22 @@ lib.sphb200_store_rung.argtypes = [vp, vp, C.c_uint8, vp]
 lib.sphb200_extract_groups.argtypes = [vp, vp, vp, C.c_uint32, C.c_uint32, vp, vp]
 lib.sphb200_targets_from_groups.argtypes = [vp, vp, vp, vp]
 lib.sphb200_sim_destroy.argtypes = [vp]
+lib.sphb200_set_scope.argtypes = [vp, vp]
+lib.sphb200_mark_groups.argtypes = [vp, vp, C.c_uint32, vp]
+lib.sphb200_sort_group_dt.argtypes = [vp, vp, vp, C.c_uint32]
+lib.sphb200_sequence.argtypes = [vp, vp, C.c_uint32, C.c_uint32]
+lib.sphb200_rung_ranges.argtypes = [vp, C.c_float, vp, C.c_uint32, C.c_int, C.c_float, vp, vp]
+lib.sphb200_drift_positions.argtypes = [vp, C.c_int, vp, C.c_float, C.c_float, vp, vp, vp, vp]
+lib.sphb200_compute_positions_groups.argtypes = [vp, C.c_int, vp, C.c_float, vp, vp, vp, vp, vp]
+lib.sphb200_update_h_groups.argtypes = [vp, C.c_int, vp, C.c_uint, vp, vp]
+lib.sphb200_sim_bdt_enable.argtypes = [vp, C.c_int, C.c_double, C.c_double]
+for _n in ("sphb200_sim_bdt_compute_forces", "sphb200_sim_bdt_integrate", "sphb200_sim_bdt_step"):
+    getattr(lib, _n).argtypes = [vp]
+lib.sphb200_sim_bdt_info.argtypes = [vp, vp]
+lib.sphb200_sim_bdt_groups.argtypes = [vp, vp]
+for _n in ("sphb200_sim_bdt_rungs", "sphb200_sim_bdt_group_dt", "sphb200_sim_bdt_active"):
+    getattr(lib, _n).restype = vp
+    getattr(lib, _n).argtypes = [vp]
 
 
 class SphError(RuntimeError):

@@ -4,6 +4,8 @@
 // plus sphexa::HydroVeProp (main/src/propagator/ve_hydro.hpp) for one rank: it owns the SFC-sorted SoA
 // particle arrays, both cornerstone trees, the neighbor lists, and sequences the operators of tier 1.
 #include <cmath>
+#include <limits>
+#include <algorithm>
 #include <array>
 #include <mutex>
 #include "common.cuh"
@@ -229,6 +231,33 @@ struct sphb200_sim
     // sphb200_sim_step_host: copy engines run beside the compute stream
     sphb200_turb* turb = nullptr; // TurbVeProp: stirring after the hydro forces
 
+
+    // ---- HydroVeBdtProp state (block time steps), see the bdt section at the end of this file
+    struct Timestep // sph::Timestep (sph/include/sph/timestep.h:42-66)
+    {
+        float nextDt = 0, elapsedDt = 0, totDt = 0;
+        int numRungs = 1, substep = 0;
+        uint32_t rungRanges[5] = {0, 0, 0, 0, 0};
+        float dt_m1[4]         = {0, 0, 0, 0};
+        float dt_drift[4]      = {0, 0, 0, 0};
+    };
+    struct Bdt
+    {
+        bool enabled    = false;
+        int safetySteps = 0;
+        float etaAccEps = 0;
+        Timestep ts, prev;
+        uint32_t capGroups = 0;
+        uint32_t* buf[2]   = {nullptr, nullptr}; // group delimiters / [start | end] pairs, 2 * capGroups + 2 each
+        sphb200_group_view groups{}, tsGroups{}, activeRungs{}, rungs[4]{};
+        float* groupDt         = nullptr;
+        uint32_t* groupIndices = nullptr;
+        uint8_t *rung = nullptr, *rungAlt = nullptr, *active = nullptr;
+        void* dtParticle     = nullptr;
+        float searchExt      = 1.0f;
+        bool allActive       = true;
+    } bdt;
+
     cudaStream_t copyIn = nullptr, copyOut = nullptr;
     cudaEvent_t evUp[3] = {}, evDown[2] = {};
 
@@ -357,6 +386,9 @@ extern "C" void sphb200_sim_destroy(sphb200_sim* s)
     cudaFree(s->prefixes); cudaFree(s->childOffsets); cudaFree(s->parents); cudaFree(s->levelRange);
     cudaFree(s->internalToLeaf); cudaFree(s->leafToInternal); cudaFree(s->centers); cudaFree(s->sizes);
     cudaFree(s->layout);
+    for (auto p : s->bdt.buf) cudaFree(p);
+    cudaFree(s->bdt.groupDt); cudaFree(s->bdt.groupIndices); cudaFree(s->bdt.rung); cudaFree(s->bdt.rungAlt);
+    cudaFree(s->bdt.active); cudaFree(s->bdt.dtParticle);
     for (auto& e : s->ev) cudaEventDestroy(e);
     if (s->copyIn)
     {
@@ -815,4 +847,342 @@ extern "C" uint64_t sphb200_sim_total_neighbors(sphb200_sim* s)
         setError(e.what());
         return 0;
     }
+}
+
+// =====================================================================================================
+// HydroVeBdtProp (main/src/propagator/ve_hydro_bdt.hpp:51-420) for one rank, g = 0
+// =====================================================================================================
+namespace
+{
+
+//! @brief cstone::butterfly (domain/include/cstone/primitives/math.hpp:26-31)
+int butterfly(int i) { return i == 0 ? 0 : __builtin_ctz(unsigned(i)) + 1; }
+
+//! @brief HydroVeBdtProp::activeRung (ve_hydro_bdt.hpp:106-110)
+int activeRung(int substep, int numRungs)
+{
+    if (substep == 0 || substep >= (1 << (numRungs - 1))) return 0;
+    return butterfly(substep);
+}
+
+//! @brief makeSlicedView (sph/include/sph/groups.hpp:50-58)
+sphb200_group_view slicedView(const sphb200_group_view& g, uint32_t first, uint32_t last)
+{
+    sphb200_group_view r = g;
+    r.numGroups          = last - first;
+    r.groupStart += first;
+    r.groupEnd += first;
+    return r;
+}
+
+__global__ void gatherBytesKernel(const uint32_t* __restrict__ perm, size_t n, const uint8_t* __restrict__ src,
+                                  uint8_t* __restrict__ dst)
+{
+    size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i < n) dst[i] = src[perm[i]];
+}
+
+__global__ void fillFloatKernel(float* __restrict__ a, size_t n, float v)
+{
+    size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i < n) a[i] = v;
+}
+
+void bdtAllocGroups(sphb200_sim* s, uint32_t cap)
+{
+    auto& b = s->bdt;
+    SPHB200_CUDA(cudaStreamSynchronize(s->ctx->stream));
+    for (auto& p : b.buf)
+    {
+        cudaFree(p);
+        p = devAlloc<uint32_t>(2 * size_t(cap) + 2);
+    }
+    cudaFree(b.groupDt);
+    cudaFree(b.groupIndices);
+    b.groupDt      = devAlloc<float>(cap);
+    b.groupIndices = devAlloc<uint32_t>(cap);
+    b.capGroups    = cap;
+}
+
+//! @brief HydroVeBdtProp::fullSync (ve_hydro_bdt.hpp:172-194)
+void bdtFullSync(sphb200_sim* s)
+{
+    auto* ctx = s->ctx;
+    auto& b   = s->bdt;
+    CHECK_RC(sphb200_sim_sync(s));
+    // "rung" is a conserved field of this propagator (ve_hydro_bdt.hpp:90): it follows the particles
+    uint32_t numAssigned = s->end - s->start;
+    if (numAssigned)
+        SPHB200_LAUNCH(ctx, gatherBytesKernel, gridFor(numAssigned, 256), 256, 0, s->perm, size_t(numAssigned),
+                       b.rung + s->start, b.rungAlt + s->start);
+    std::swap(b.rung, b.rungAlt);
+    b.searchExt = 1.0f; // d.treeView = domain.octreeProperties()
+
+    sphb200_fields f = s->table();
+    uint32_t numGroups = 0;
+    for (int attempt = 0; attempt < 2; ++attempt)
+    {
+        int rc = sphb200_compute_groups(ctx, s->start, s->end, f.x, f.y, f.z, s->focus.leaves, s->focus.numLeaves,
+                                        s->layout, &s->box, 2.0f, b.buf[0], 2 * b.capGroups + 1, &numGroups);
+        if (rc == SPHB200_ERR_CAPACITY || numGroups > b.capGroups)
+        {
+            if (attempt == 1) throw std::runtime_error("bdt: group capacity");
+            bdtAllocGroups(s, numGroups + numGroups / 16 + 64);
+            continue;
+        }
+        if (rc != 0) throw std::runtime_error(sphb200_last_error());
+        break;
+    }
+    b.groups      = sphb200_group_view{s->start, s->end, numGroups, b.buf[0], b.buf[0] + 1};
+    b.tsGroups    = sphb200_group_view{0, 0, 0, b.buf[1], b.buf[1] + numGroups};
+    b.activeRungs = b.groups;
+    b.allActive   = true;
+    if (numGroups)
+        SPHB200_LAUNCH(ctx, fillFloatKernel, gridFor(numGroups, 256), 256, 0, b.groupDt, size_t(numGroups),
+                       std::numeric_limits<float>::max());
+}
+
+//! @brief HydroVeBdtProp::partialSync (ve_hydro_bdt.hpp:196-211); one rank: no halo exchange
+void bdtPartialSync(sphb200_sim* s)
+{
+    auto& b = s->bdt;
+    s->ctx->packValid = 0;
+    s->mark(0);
+    b.searchExt *= 1.012f;
+    int highestRung = butterfly(b.ts.substep);
+    b.activeRungs   = slicedView(b.tsGroups, b.ts.rungRanges[0], b.ts.rungRanges[highestRung]);
+    b.allActive     = false;
+    s->mark(1);
+}
+
+//! @brief rungTimestep (sph/include/sph/ts_rungs.hpp:131-145), one rank
+sphb200_sim::Timestep rungTimestep(sphb200_sim* s, uint32_t numGroups, float maxDt)
+{
+    auto& b = s->bdt;
+    CHECK_RC(sphb200_sort_group_dt(s->ctx, b.groupDt, b.groupIndices, numGroups));
+    uint32_t rr[5];
+    float mdt[2];
+    CHECK_RC(sphb200_rung_ranges(s->ctx, -1.0f, b.groupDt, numGroups, 1, 0.4f, rr, mdt));
+    int numRungs = std::min(int(log2f(mdt[1] / mdt[0])) + 1, 4);
+    CHECK_RC(sphb200_rung_ranges(s->ctx, mdt[0], b.groupDt, numGroups, numRungs, 0.4f, rr, nullptr));
+    float minDt = std::min(maxDt, mdt[0]);
+    sphb200_sim::Timestep ret;
+    ret.nextDt   = minDt;
+    ret.totDt    = minDt * float(1 << numRungs);
+    ret.numRungs = numRungs;
+    std::copy(rr, rr + 5, ret.rungRanges);
+    return ret;
+}
+
+//! @brief HydroVeBdtProp::computeRungs (ve_hydro_bdt.hpp:285-327)
+void bdtComputeRungs(sphb200_sim* s)
+{
+    auto* ctx    = s->ctx;
+    auto& b      = s->bdt;
+    auto& ts     = b.ts;
+    int highRung = activeRung(ts.substep, ts.numRungs);
+
+    if (highRung == 0)
+    {
+        b.prev      = ts;
+        float maxDt = ts.dt_m1[0] * 1.1f; // d.maxDtIncrease
+        ts          = rungTimestep(s, b.groups.numGroups, maxDt);
+        if (b.safetySteps > 0)
+        {
+            ts.numRungs = 1;
+            std::fill(ts.rungRanges + 1, ts.rungRanges + 5, b.groups.numGroups);
+            b.safetySteps--;
+        }
+    }
+    else
+    {
+        // minimumGroupDt (ts_rungs.hpp:147-157)
+        uint32_t numGroups = ts.rungRanges[highRung], numTot = ts.rungRanges[4];
+        CHECK_RC(sphb200_sort_group_dt(ctx, b.groupDt, b.groupIndices, numGroups));
+        CHECK_RC(sphb200_sequence(ctx, b.groupIndices + numGroups, numTot - numGroups, numGroups));
+        uint32_t rr[5];
+        float mdt[2];
+        CHECK_RC(sphb200_rung_ranges(ctx, -1.0f, b.groupDt, numGroups, 4, 0.4f, rr, mdt));
+        float timeLeft   = ts.totDt - ts.elapsedDt;
+        int substepsLeft = (1 << ts.numRungs) - ts.substep;
+        ts.nextDt        = std::min(mdt[0], timeLeft / float(substepsLeft));
+        std::copy(rr, rr + highRung, ts.rungRanges);
+    }
+
+    if (highRung == 0 || highRung > 1)
+    {
+        if (highRung > 1) std::swap(b.groups, b.tsGroups);
+        uint32_t numOut = ts.rungRanges[4];
+        // the output must not overwrite its input: take the buffer the input does not live in
+        uint32_t* out = (b.groups.groupStart >= b.buf[0] && b.groups.groupStart < b.buf[0] + 2 * size_t(b.capGroups) + 2)
+                            ? b.buf[1]
+                            : b.buf[0];
+        b.tsGroups = sphb200_group_view{0, 0, numOut, out, out + numOut};
+        CHECK_RC(sphb200_extract_groups(ctx, &b.groups, b.groupIndices, 0, numOut, out, out + numOut));
+    }
+    for (int r = 0; r < ts.numRungs; ++r)
+        b.rungs[r] = slicedView(b.tsGroups, ts.rungRanges[r], ts.rungRanges[r + 1]);
+}
+
+} // namespace
+
+extern "C" int sphb200_sim_bdt_enable(sphb200_sim* s, int safetySteps, double etaAcc, double eps)
+{
+    SPHB200_TRY
+    auto& b = s->bdt;
+    if (!b.enabled)
+    {
+        b.rung       = devAlloc<uint8_t>(s->capacity);
+        b.rungAlt    = devAlloc<uint8_t>(s->capacity);
+        b.active     = devAlloc<uint8_t>(s->capacity);
+        b.dtParticle = devAlloc<char>(s->capacity * size_t(s->cfg.dtype == SPHB200_F64 ? 8 : 4));
+        SPHB200_CUDA(cudaMemset(b.rung, 0, s->capacity));
+        SPHB200_CUDA(cudaMemset(b.rungAlt, 0, s->capacity));
+        bdtAllocGroups(s, uint32_t(s->capacity / 16 + 1024));
+    }
+    b.enabled     = true;
+    b.safetySteps = safetySteps;
+    if (etaAcc <= 0) etaAcc = 0.2; // ParticlesData::etaAcc, eps (particles_data.hpp:111-113)
+    if (eps <= 0) eps = 0.005;
+    b.etaAccEps = float(etaAcc * std::sqrt(eps)); // groupAccTimestep (ts_rungs.hpp:59)
+    b.ts        = sphb200_sim::Timestep{};
+    for (float& v : b.ts.dt_m1)
+        v = float(s->minDt); // HydroVeBdtProp(): timestep_.dt_m1[0] = settings.at("minDt")
+    b.prev = b.ts;
+    SPHB200_CATCH
+}
+
+extern "C" int sphb200_sim_bdt_compute_forces(sphb200_sim* s)
+{
+    SPHB200_TRY
+    auto* ctx = s->ctx;
+    auto& b   = s->bdt;
+    if (!b.enabled) throw std::runtime_error("bdt_compute_forces: call sphb200_sim_bdt_enable first");
+    // HydroVeBdtProp::sync (ve_hydro_bdt.hpp:213-218)
+    if (activeRung(b.ts.substep, b.ts.numRungs) == 0) bdtFullSync(s);
+    else bdtPartialSync(s);
+
+    sphb200_op_scope scope{nullptr, b.searchExt, b.dtParticle};
+    if (!b.allActive)
+    {
+        CHECK_RC(sphb200_mark_groups(ctx, &b.activeRungs, s->n, b.active));
+        scope.active = b.active;
+    }
+    CHECK_RC(sphb200_set_scope(ctx, &scope));
+    int rc = 0;
+    try
+    {
+        sphb200_fields f = s->table();
+        int dt           = s->cfg.dtype;
+        for (int p = 0; p < 5; ++p)
+        {
+            CHECK_RC(sphb200_sim_forces_phase(s, p));
+            if (p == 2) // groupDivvTimestep after IadVelocityDivCurl (ve_hydro_bdt.hpp:252-253)
+                CHECK_RC(sphb200_group_divv_timestep(ctx, dt, float(s->cfg.hc.Krho), &b.activeRungs, f.divv, b.groupDt));
+        }
+        // Courant minimum per group (momentum_energy_gpu.cu:98-104), then groupAccTimestep (ve_hydro_bdt.hpp:282)
+        CHECK_RC(sphb200_group_min_timestep(ctx, dt, &b.activeRungs, b.dtParticle, b.groupDt));
+        CHECK_RC(sphb200_group_acc_timestep(ctx, dt, b.etaAccEps, &b.activeRungs, f.ax, f.ay, f.az, b.groupDt));
+    }
+    catch (std::exception& e)
+    {
+        setError(e.what());
+        rc = 1;
+    }
+    sphb200_set_scope(ctx, nullptr);
+    if (rc) throw std::runtime_error(sphb200_last_error());
+    SPHB200_CATCH
+}
+
+extern "C" int sphb200_sim_bdt_integrate(sphb200_sim* s)
+{
+    SPHB200_TRY
+    auto* ctx = s->ctx;
+    auto& b   = s->bdt;
+    if (!b.enabled) throw std::runtime_error("bdt_integrate: call sphb200_sim_bdt_enable first");
+    bdtComputeRungs(s);
+    auto& ts = b.ts;
+
+    // HydroVeBdtProp::integrate (ve_hydro_bdt.hpp:329-376)
+    sphb200_fields f       = s->table();
+    sphb200_hydro_const hc = s->hydroConst();
+    int dtype              = s->cfg.dtype;
+    auto driftBack         = [](int subStep, int rung) { return subStep % (1 << rung); };
+    int lowestDriftRung    = butterfly(ts.substep + 1);
+    bool isLastSubstep     = activeRung(ts.substep + 1, ts.numRungs) == 0;
+    sphb200_box openBox;
+    {
+        double lim[6] = {0, 1, 0, 1, 0, 1};
+        int bc[3]     = {SPHB200_OPEN, SPHB200_OPEN, SPHB200_OPEN};
+        sphb200_make_box(lim, bc, &openBox);
+    }
+    const sphb200_box* substepBox = isLastSubstep ? &s->box : &openBox;
+
+    for (int i = 0; i < ts.numRungs; ++i)
+    {
+        bool useRung = ts.substep == driftBack(ts.substep, i); // drift back to the start of the hierarchy
+        bool advance = i < lowestDriftRung;
+        float dt     = ts.nextDt;
+        float dt_m1[4];
+        std::copy(useRung ? b.prev.dt_m1 : ts.dt_m1, (useRung ? b.prev.dt_m1 : ts.dt_m1) + 4, dt_m1);
+        if (advance)
+        {
+            if (ts.dt_drift[i] > 0)
+                CHECK_RC(sphb200_drift_positions(ctx, dtype, &b.rungs[i], 0.0f, ts.dt_drift[i], dt_m1, b.rung, &hc, &f));
+            CHECK_RC(sphb200_compute_positions_groups(ctx, dtype, &b.rungs[i], ts.dt_drift[i] + dt, dt_m1, b.rung,
+                                                      substepBox, &hc, &f));
+            ts.dt_m1[i]    = ts.dt_drift[i] + dt;
+            ts.dt_drift[i] = 0;
+            CHECK_RC(sphb200_store_rung(ctx, &b.rungs[i], uint8_t(i), b.rung));
+        }
+        else
+        {
+            CHECK_RC(sphb200_drift_positions(ctx, dtype, &b.rungs[i], ts.dt_drift[i] + dt, ts.dt_drift[i], dt_m1, b.rung,
+                                             &hc, &f));
+            ts.dt_drift[i] += dt;
+        }
+    }
+    CHECK_RC(sphb200_update_h_groups(ctx, dtype, &b.activeRungs, hc.ng0, f.nc, f.h));
+
+    ts.substep++;
+    ts.elapsedDt += ts.nextDt;
+    s->ttot += ts.nextDt;
+    s->minDt_m1 = s->minDt;
+    s->minDt    = ts.nextDt;
+    s->mark(9);
+    SPHB200_CATCH
+}
+
+extern "C" int sphb200_sim_bdt_step(sphb200_sim* s)
+{
+    SPHB200_TRY
+    CHECK_RC(sphb200_sim_bdt_compute_forces(s));
+    CHECK_RC(sphb200_sim_bdt_integrate(s));
+    SPHB200_CATCH
+}
+
+extern "C" int sphb200_sim_bdt_info(const sphb200_sim* s, sphb200_bdt_info* out)
+{
+    SPHB200_TRY
+    const auto& b = s->bdt;
+    out->nextDt = b.ts.nextDt; out->elapsedDt = b.ts.elapsedDt; out->totDt = b.ts.totDt;
+    out->numRungs = b.ts.numRungs; out->substep = b.ts.substep;
+    std::copy(b.ts.rungRanges, b.ts.rungRanges + 5, out->rungRanges);
+    std::copy(b.ts.dt_m1, b.ts.dt_m1 + 4, out->dt_m1);
+    std::copy(b.ts.dt_drift, b.ts.dt_drift + 4, out->dt_drift);
+    out->numGroups       = b.tsGroups.numGroups;
+    out->numActiveGroups = b.activeRungs.numGroups;
+    out->searchExtFactor = b.searchExt;
+    out->isSynced        = activeRung(b.ts.substep, b.ts.numRungs) == 0;
+    SPHB200_CATCH
+}
+
+extern "C" const uint8_t* sphb200_sim_bdt_rungs(const sphb200_sim* s) { return s->bdt.rung; }
+extern "C" const float* sphb200_sim_bdt_group_dt(const sphb200_sim* s) { return s->bdt.groupDt; }
+extern "C" const uint8_t* sphb200_sim_bdt_active(const sphb200_sim* s) { return s->bdt.allActive ? nullptr : s->bdt.active; }
+extern "C" int sphb200_sim_bdt_groups(const sphb200_sim* s, sphb200_group_view* out)
+{
+    SPHB200_TRY
+    *out = s->bdt.tsGroups;
+    SPHB200_CATCH
 }

@@ -99,6 +99,10 @@ struct sphb200_ctx
     int* devScalars      = nullptr; // 64 ints
     double* devDt        = nullptr; // [0] courant, [1] rho, [2] local min, [3..] scratch
     double* hostDt       = nullptr; // pinned
+    // GroupView scope of the target-range operators (sphb200_set_scope)
+    const uint8_t* scopeActive = nullptr;
+    float searchExtFactor      = 1.0f;
+    void* scopeDtParticle      = nullptr;
 };
 
 namespace sphb200

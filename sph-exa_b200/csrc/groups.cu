@@ -19,6 +19,7 @@
 namespace sphb200
 {
 
+constexpr int kMaxRungs = 4;       // Timestep::maxNumRungs (sph/include/sph/timestep.h:44)
 constexpr unsigned kGroupSize = 32; // TravConfig::targetSize = GpuConfig::warpSize (traversal/find_neighbors.cuh:62)
 
 /*! @brief mark the particles that start a group
@@ -169,6 +170,72 @@ __global__ void __launch_bounds__(256)
     targets[scan[t]] = base + t;
 }
 
+
+//! @brief active[i] = 1 for the members of the groups (one warp per group)
+__global__ void __launch_bounds__(256)
+    markActiveKernel(const LocalIndex* __restrict__ grpStart, const LocalIndex* __restrict__ grpEnd,
+                     LocalIndex numGroups, uint8_t* __restrict__ active)
+{
+    LocalIndex lane = threadIdx.x & 31;
+    LocalIndex g    = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (g >= numGroups) return;
+    for (LocalIndex i = grpStart[g] + lane; i < grpEnd[g]; i += 32)
+        active[i] = 1;
+}
+
+//! @brief positive floats order like their bit patterns: radix-sort keys for sortGroupDt
+__global__ void __launch_bounds__(256) dtToKeysKernel(const float* __restrict__ dt, LocalIndex n, KeyType* __restrict__ keys)
+{
+    LocalIndex g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g < n) keys[g] = KeyType(__float_as_uint(dt[g]));
+}
+
+__global__ void __launch_bounds__(256) keysToDtKernel(const KeyType* __restrict__ keys, LocalIndex n, float* __restrict__ dt)
+{
+    LocalIndex g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g < n) dt[g] = __uint_as_float(uint32_t(keys[g]));
+}
+
+__global__ void __launch_bounds__(256) iotaKernel(LocalIndex* __restrict__ out, LocalIndex n, LocalIndex first)
+{
+    LocalIndex g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g < n) out[g] = first + g;
+}
+
+/*! @brief findRungRanges (ts_rungs.hpp:115-129) + timestepRangeGpu (:69-75) in one launch
+ *
+ * out[0] = 0, out[r] = lower_bound(groupDt, float(1 << r) * minDt) for 1 <= r < numRungs, numGroups otherwise.  With
+ * minDt < 0 the minimum groupDt[0] itself is used (the caller has not seen it yet).  dtOut = {groupDt[0],
+ * groupDt[fastIndex]}.
+ */
+__global__ void rungRangesKernel(const float* __restrict__ groupDt, LocalIndex numGroups, float minDt, int numRungs,
+                                 LocalIndex fastIndex, LocalIndex* __restrict__ out, float* __restrict__ dtOut)
+{
+    int r = threadIdx.x;
+    if (r == 0)
+    {
+        dtOut[0] = groupDt[0];
+        dtOut[1] = groupDt[fastIndex];
+    }
+    if (r > kMaxRungs) return;
+    if (minDt < 0) minDt = groupDt[0];
+    LocalIndex res = numGroups;
+    if (r == 0) res = 0;
+    else if (r < numRungs)
+    {
+        float maxDtRung = float(1 << r) * minDt;
+        LocalIndex lo = 0, hi = numGroups;
+        while (lo < hi)
+        {
+            LocalIndex mid = lo + (hi - lo) / 2;
+            if (groupDt[mid] < maxDtRung) lo = mid + 1;
+            else hi = mid;
+        }
+        res = lo;
+    }
+    out[r] = res;
+}
+
 } // namespace sphb200
 
 using namespace sphb200;
@@ -296,5 +363,67 @@ extern "C" int sphb200_targets_from_groups(sphb200_ctx* ctx, const sphb200_group
     SPHB200_CUDA(cudaMemcpyAsync(ctx->hostScalars, total, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
     SPHB200_CUDA(cudaStreamSynchronize(ctx->stream));
     *numTargets_h = uint32_t(ctx->hostScalars[0]);
+    GROUPS_CATCH
+}
+
+extern "C" int sphb200_mark_groups(sphb200_ctx* ctx, const sphb200_group_view* grp, uint32_t n, uint8_t* active)
+{
+    GROUPS_TRY
+    if (n) SPHB200_CUDA(cudaMemsetAsync(active, 0, n, ctx->stream));
+    if (grp->numGroups == 0) return 0;
+    SPHB200_LAUNCH(ctx, markActiveKernel, gridFor(size_t(grp->numGroups) * 32, 256), 256, 0, grp->groupStart,
+                   grp->groupEnd, grp->numGroups, active);
+    GROUPS_CATCH
+}
+
+extern "C" int sphb200_set_scope(sphb200_ctx* ctx, const sphb200_op_scope* scope)
+{
+    GROUPS_TRY
+    ctx->scopeActive     = scope ? scope->active : nullptr;
+    ctx->searchExtFactor = (scope && scope->searchExtFactor > 0) ? scope->searchExtFactor : 1.0f;
+    ctx->scopeDtParticle = scope ? scope->dtParticle : nullptr;
+    GROUPS_CATCH
+}
+
+extern "C" int sphb200_sort_group_dt(sphb200_ctx* ctx, float* groupDt, uint32_t* groupIndices, uint32_t numGroups)
+{
+    GROUPS_TRY
+    if (numGroups == 0) return 0;
+    auto* keys = static_cast<KeyType*>(ctx->miscTmp.get(size_t(numGroups) * sizeof(KeyType)));
+    SPHB200_LAUNCH(ctx, dtToKeysKernel, gridFor(numGroups, 256), 256, 0, groupDt, numGroups, keys);
+    // stable, like the cub radix sort behind sortByKeyGpu: equal time steps keep their SFC order
+    radixSortPairs(ctx, keys, groupIndices, numGroups, true, 0, 32);
+    SPHB200_LAUNCH(ctx, keysToDtKernel, gridFor(numGroups, 256), 256, 0, keys, numGroups, groupDt);
+    GROUPS_CATCH
+}
+
+extern "C" int sphb200_sequence(sphb200_ctx* ctx, uint32_t* out, uint32_t n, uint32_t first)
+{
+    GROUPS_TRY
+    if (n) SPHB200_LAUNCH(ctx, iotaKernel, gridFor(n, 256), 256, 0, out, n, first);
+    GROUPS_CATCH
+}
+
+extern "C" int sphb200_rung_ranges(sphb200_ctx* ctx, float minDt, const float* groupDt, uint32_t numGroups, int numRungs,
+                                   float fastFraction, uint32_t* rungRanges_h, float* minGroupDt_h)
+{
+    GROUPS_TRY
+    if (numGroups == 0)
+    {
+        for (int r = 0; r <= kMaxRungs; ++r)
+            rungRanges_h[r] = 0;
+        if (minGroupDt_h) minGroupDt_h[0] = minGroupDt_h[1] = INFINITY;
+        return 0;
+    }
+    auto* dOut = reinterpret_cast<uint32_t*>(ctx->devScalars + 8);
+    auto* dDt  = reinterpret_cast<float*>(ctx->devScalars + 16);
+    SPHB200_LAUNCH(ctx, rungRangesKernel, 1, 32, 0, groupDt, numGroups, minDt, numRungs,
+                   LocalIndex(fastFraction * numGroups), dOut, dDt);
+    SPHB200_CUDA(cudaMemcpyAsync(ctx->hostScalars + 8, ctx->devScalars + 8, 10 * sizeof(int), cudaMemcpyDeviceToHost,
+                                 ctx->stream));
+    SPHB200_CUDA(cudaStreamSynchronize(ctx->stream));
+    for (int r = 0; r <= kMaxRungs; ++r)
+        rungRanges_h[r] = uint32_t(ctx->hostScalars[8 + r]);
+    if (minGroupDt_h) std::memcpy(minGroupDt_h, ctx->hostScalars + 16, 2 * sizeof(float));
     GROUPS_CATCH
 }

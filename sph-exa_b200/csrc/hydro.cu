@@ -31,12 +31,16 @@ struct F
     double* du;
     uint32_t* nc;
     T *dV11, *dV12, *dV13, *dV22, *dV23, *dV33;
+    const uint8_t* active; // GroupView scope (sphb200_set_scope): NULL = every target of [first,last)
+    T* dtParticle;         // per-target Courant step of momentumEnergy, NULL = not stored
 };
 
 template<class T>
 static F<T> typed(const sphb200_fields& f)
 {
     F<T> r;
+    r.active     = nullptr;
+    r.dtParticle = nullptr;
     r.x = f.x; r.y = f.y; r.z = f.z;
 #define CP(n) r.n = static_cast<T*>(f.n)
     CP(h); CP(m); CP(vx); CP(vy); CP(vz); CP(x_m1); CP(y_m1); CP(z_m1); CP(du_m1); CP(alpha);
@@ -44,6 +48,16 @@ static F<T> typed(const sphb200_fields& f)
     CP(divv); CP(curlv); CP(ax); CP(ay); CP(az); CP(dV11); CP(dV12); CP(dV13); CP(dV22); CP(dV23); CP(dV33);
 #undef CP
     r.temp = f.temp; r.du = f.du; r.nc = f.nc;
+    return r;
+}
+
+//! @brief field table restricted to the active targets of the context's scope
+template<class T>
+static F<T> scoped(const sphb200_ctx* ctx, const sphb200_fields& f)
+{
+    F<T> r       = typed<T>(f);
+    r.active     = ctx->scopeActive;
+    r.dtParticle = static_cast<T*>(ctx->scopeDtParticle);
     return r;
 }
 
@@ -316,7 +330,7 @@ __global__ void __launch_bounds__(kHydroBlock, SPHB200_XMASS_MIN_BLOCKS)
                 F<T> f, const PosRec<T>* __restrict__ r0, const Rec2<T>* __restrict__ wh)
 {
     uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= last) return;
+    if (i >= last || (f.active && !f.active[i])) return;
     NbList nb = nbList(nidx, f.nc, first, i, ngmax);
 
     PosRec<T> pi = r0[i];
@@ -351,7 +365,7 @@ __global__ void __launch_bounds__(kHydroBlock, SPHB200_GRADH_MIN_BLOCKS)
                      const Rec4<T>* __restrict__ whq)
 {
     uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= last) return;
+    if (i >= last || (f.active && !f.active[i])) return;
     NbList nb = nbList(nidx, f.nc, first, i, ngmax);
 
     PosRec<T> pi = r0[i];
@@ -426,7 +440,7 @@ __global__ void __launch_bounds__(kHydroBlock, SPHB200_IAD_MIN_BLOCKS)
                        const Rec4<T>* __restrict__ r1, const Rec2<T>* __restrict__ wh, bool doGradV)
 {
     uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= last) return;
+    if (i >= last || (f.active && !f.active[i])) return;
     NbList nb = nbList(nidx, f.nc, first, i, ngmax);
 
     PosRec<T> pi = r0[i]; // {x, y, z, xm}
@@ -532,7 +546,7 @@ __global__ void __launch_bounds__(kHydroBlock, SPHB200_AV_MIN_BLOCKS)
                      T decay_constant)
 {
     uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= last) return;
+    if (i >= last || (f.active && !f.active[i])) return;
     NbList nb = nbList(nidx, f.nc, first, i, ngmax);
 
     PosRec<T> pi = r0[i]; // {x, y, z, divv}
@@ -641,7 +655,7 @@ __global__ void __launch_bounds__(kHydroBlock, kMomentumMinBlocks)
 {
     uint32_t i  = first + blockIdx.x * blockDim.x + threadIdx.x;
     T dt_i      = INFINITY;
-    if (i < last)
+    if (i < last && (!f.active || f.active[i]))
     {
         NbList nb = nbList(nidx, f.nc, first, i, ngmax);
 
@@ -780,6 +794,7 @@ __global__ void __launch_bounds__(kHydroBlock, kMomentumMinBlocks)
         // tsKCourant (sph/kernels.hpp:10-16)
         T v  = maxvsignali > T(0) ? maxvsignali : ci;
         dt_i = T(Kcour * hi / v);
+        if (f.dtParticle) f.dtParticle[i] = dt_i;
     }
 
     // block minimum -> one ordered-key atomic per warp
@@ -899,6 +914,131 @@ __global__ void __launch_bounds__(256)
 
     // updateSmoothingLength (update_h.hpp:12-24)
     f.h[i] = updateHT(ng0, f.nc[i], hi);
+}
+
+// ---------------------------------------------------------------- block time steps (positions_gpu.cu:47-180)
+struct RungDt
+{
+    float v[4]; // Timestep::dt_m1 per rung (sph/include/sph/timestep.h:44-52)
+};
+
+//! @brief positionUpdate (positions.hpp:77-88) for one axis; open box when !pbc
+__device__ __forceinline__ void positionUpdate1(double dt, double dt_m1, double X, double A, double dXn, bool pbc,
+                                                double lo, double hi, double len, double& Xn1, double& Vn1,
+                                                double& dXn1)
+{
+    double Vnmhalf = dXn * (1.0 / dt_m1);
+    double Vn      = Vnmhalf + 0.5 * dt_m1 * A;
+    Vn1            = Vn + A * dt;
+    dXn1           = (Vn + 0.5 * A * fabs(dt)) * dt;
+    Xn1            = putInBox1(X + dXn1, pbc, lo, hi, len);
+}
+
+//! @brief energyUpdate (positions.hpp:54-61)
+__device__ __forceinline__ double energyUpdate1(double u_old, double dt, double dt_m1, double du, double du_m1)
+{
+    double u_new = u_old + du * dt + 0.5 * (du - du_m1) / dt_m1 * fabs(dt) * dt;
+    if (u_new < 0.) { u_new = u_old * exp(u_new * dt / u_old); }
+    return u_new;
+}
+
+/*! @brief driftKernel (positions_gpu.cu:47-90): drift back by dt_back to where the accelerations were evaluated, then
+ *         forward by dt, without touching x_m1 / du_m1 and without folding into the box (the tree is not rebuilt)
+ */
+template<class T>
+__global__ void __launch_bounds__(256)
+    driftGroupsKernel(const uint32_t* __restrict__ grpStart, const uint32_t* __restrict__ grpEnd, uint32_t numGroups,
+                      float dt, float dt_back, RungDt dt_m1, const uint8_t* __restrict__ rung, F<T> f, T muiConst,
+                      double gamma, double* __restrict__ xw, double* __restrict__ yw, double* __restrict__ zw)
+{
+    uint32_t lane = threadIdx.x & 31;
+    uint32_t g    = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (g >= numGroups) return;
+    uint32_t i = grpStart[g] + lane;
+    if (i >= grpEnd[g]) return;
+
+    float dt_m1_rung = rung ? dt_m1.v[rung[i]] : dt_m1.v[0];
+    double A[3]      = {double(f.ax[i]), double(f.ay[i]), double(f.az[i])};
+    double X[3]      = {xw[i], yw[i], zw[i]};
+    double dXn[3]    = {double(f.x_m1[i]), double(f.y_m1[i]), double(f.z_m1[i])};
+    double Xn[3], Vn[3];
+#pragma unroll
+    for (int d = 0; d < 3; ++d)
+    {
+        double Xrecov, ign0, ign1;
+        positionUpdate1(-double(dt_back), dt_m1_rung, X[d], A[d], dXn[d], false, 0, 0, 0, Xrecov, ign0, ign1);
+        positionUpdate1(dt, dt_m1_rung, Xrecov, A[d], dXn[d], false, 0, 0, 0, Xn[d], Vn[d], ign1);
+    }
+    xw[i] = Xn[0]; yw[i] = Xn[1]; zw[i] = Xn[2];
+    f.vx[i] = T(Vn[0]); f.vy[i] = T(Vn[1]); f.vz[i] = T(Vn[2]);
+
+    const T R      = 8.317e7;
+    T cv           = T(R / muiConst / (gamma - T(1)));
+    double du      = f.du[i];
+    double dum1    = double(f.du_m1[i]);
+    double u_recov = energyUpdate1(double(f.temp[i] * cv), -double(dt_back), dt_m1_rung, du, dum1);
+    f.temp[i]      = energyUpdate1(u_recov, dt, dt_m1_rung, du, dum1) / cv;
+}
+
+//! @brief computePositionsKernel (positions_gpu.cu:118-161): advance the groups' particles by dt from their rung's dt_m1
+template<class T>
+__global__ void __launch_bounds__(256)
+    positionsGroupsKernel(const uint32_t* __restrict__ grpStart, const uint32_t* __restrict__ grpEnd, uint32_t numGroups,
+                          float dt, RungDt dt_m1, const uint8_t* __restrict__ rung, PbcBox box, F<T> f, T muiConst,
+                          double gamma, double* __restrict__ xw, double* __restrict__ yw, double* __restrict__ zw)
+{
+    uint32_t lane = threadIdx.x & 31;
+    uint32_t g    = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (g >= numGroups) return;
+    uint32_t i = grpStart[g] + lane;
+    if (i >= grpEnd[g]) return;
+
+    T hi        = f.h[i];
+    bool anyFBC = box.fx || box.fy || box.fz;
+    if (anyFBC && f.vx[i] == T(0) && f.vy[i] == T(0) && f.vz[i] == T(0))
+    {
+        auto fbc = [hi](double coord, double top, double bottom, bool on)
+        { return on && (fabs(top - coord) < T(2) * hi || fabs(bottom - coord) < T(2) * hi); };
+        if (fbc(xw[i], box.lim[1], box.lim[0], box.fx) || fbc(yw[i], box.lim[3], box.lim[2], box.fy) ||
+            fbc(zw[i], box.lim[5], box.lim[4], box.fz))
+            return;
+    }
+
+    float dt_m1_rung = rung ? dt_m1.v[rung[i]] : dt_m1.v[0];
+    double A[3]      = {double(f.ax[i]), double(f.ay[i]), double(f.az[i])};
+    double X[3]      = {xw[i], yw[i], zw[i]};
+    double dXn[3]    = {double(f.x_m1[i]), double(f.y_m1[i]), double(f.z_m1[i])};
+    double Xn[3], Vn1[3], dXn1[3];
+    const double lo[3] = {box.lim[0], box.lim[2], box.lim[4]}, hiL[3] = {box.lim[1], box.lim[3], box.lim[5]};
+    const double len[3] = {box.lx, box.ly, box.lz};
+    const bool pb[3]    = {box.px, box.py, box.pz};
+#pragma unroll
+    for (int d = 0; d < 3; ++d)
+        positionUpdate1(dt, dt_m1_rung, X[d], A[d], dXn[d], pb[d], lo[d], hiL[d], len[d], Xn[d], Vn1[d], dXn1[d]);
+    xw[i] = Xn[0]; yw[i] = Xn[1]; zw[i] = Xn[2];
+    f.x_m1[i] = T(dXn1[0]); f.y_m1[i] = T(dXn1[1]); f.z_m1[i] = T(dXn1[2]);
+    f.vx[i] = T(Vn1[0]); f.vy[i] = T(Vn1[1]); f.vz[i] = T(Vn1[2]);
+
+    const T R    = 8.317e7;
+    T cv         = T(R / muiConst / (gamma - T(1)));
+    double du    = f.du[i];
+    double u_old = f.temp[i] * cv;
+    f.temp[i]    = energyUpdate1(u_old, dt, dt_m1_rung, du, double(f.du_m1[i])) / cv;
+    f.du_m1[i]   = T(du);
+}
+
+//! @brief updateSmoothingLengthGpuKernel (update_h_gpu.cu:39-50)
+template<class T>
+__global__ void __launch_bounds__(256)
+    updateHGroupsKernel(const uint32_t* __restrict__ grpStart, const uint32_t* __restrict__ grpEnd, uint32_t numGroups,
+                        unsigned ng0, const uint32_t* __restrict__ nc, T* __restrict__ h)
+{
+    uint32_t lane = threadIdx.x & 31;
+    uint32_t g    = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (g >= numGroups) return;
+    uint32_t i = grpStart[g] + lane;
+    if (i >= grpEnd[g]) return;
+    h[i] = updateHT(ng0, nc[i], h[i]);
 }
 
 } // namespace sphb200
@@ -1036,7 +1176,7 @@ static void launchMomentum(sphb200_ctx* ctx, uint32_t first, uint32_t last, cons
     int grid  = gridFor(last - first, kHydroBlock);
     auto go   = [&](auto kernel)
     {
-        SPHB200_LAUNCH(ctx, kernel, grid, kHydroBlock, 0, first, last, hc->ngmax, hc->K, pb, neighbors, typed<T>(*f),
+        SPHB200_LAUNCH(ctx, kernel, grid, kHydroBlock, 0, first, last, hc->ngmax, hc->K, pb, neighbors, scoped<T>(ctx, *f),
                        rec, wh, T(hc->Atmin), T(hc->Atmax), T(hc->ramp), float(hc->Kcour), dtKeys(ctx));
     };
     if (pbc && hc->avClean) go(momentumEnergyKernel<true, true, T>);
@@ -1056,7 +1196,7 @@ extern "C" int sphb200_xmass(sphb200_ctx* ctx, int dtype, uint32_t first, uint32
     DISPATCH(dtype, const Rec2<T>* wh; const Rec4<T>* whq; ensureTables<T>(ctx, hc, wh, whq);
              auto* r0 = static_cast<const PosRec<T>*>(ensureRec<T>(ctx, R_POS, *f));
              LAUNCH_PBC(ctx, *box, xmassKernel, gridFor(last - first, kHydroBlock), first, last, hc->ngmax, hc->K,
-                        pbcBox(*box), neighbors, typed<T>(*f), r0, wh););
+                        pbcBox(*box), neighbors, scoped<T>(ctx, *f), r0, wh););
     invalidate(ctx, {R_PXM, R_VV}); // xm rewritten
     SPHB200_CATCH
 }
@@ -1071,7 +1211,7 @@ extern "C" int sphb200_ve_def_gradh(sphb200_ctx* ctx, int dtype, uint32_t first,
     DISPATCH(dtype, const Rec2<T>* wh; const Rec4<T>* whq; ensureTables<T>(ctx, hc, wh, whq);
              auto* r0 = static_cast<const PosRec<T>*>(ensureRec<T>(ctx, R_POS, *f));
              LAUNCH_PBC(ctx, *box, veDefGradhKernel, gridFor(last - first, kHydroBlock), first, last, hc->ngmax, hc->K,
-                        pbcBox(*box), neighbors, typed<T>(*f), r0, whq););
+                        pbcBox(*box), neighbors, scoped<T>(ctx, *f), r0, whq););
     invalidate(ctx, {R_VV}); // kx rewritten
     SPHB200_CATCH
 }
@@ -1098,7 +1238,7 @@ extern "C" int sphb200_iad_divv_curlv(sphb200_ctx* ctx, int dtype, uint32_t firs
              auto* r0 = static_cast<const PosRec<T>*>(ensureRec<T>(ctx, R_PXM, *f));
              auto* r1 = static_cast<const Rec4<T>*>(ensureRec<T>(ctx, R_VV, *f));
              LAUNCH_PBC(ctx, *box, iadDivvCurlvKernel, gridFor(last - first, kHydroBlock), first, last, hc->ngmax,
-                        hc->K, pbcBox(*box), neighbors, typed<T>(*f), r0, r1, wh, doGradV););
+                        hc->K, pbcBox(*box), neighbors, scoped<T>(ctx, *f), r0, r1, wh, doGradV););
     invalidate(ctx, {R_PDIVV, R_CA, R_GA, R_GB}); // divv and c_ab rewritten
     SPHB200_CATCH
 }
@@ -1113,7 +1253,7 @@ extern "C" int sphb200_av_switches(sphb200_ctx* ctx, int dtype, uint32_t first, 
              auto* r0 = static_cast<const PosRec<T>*>(ensureRec<T>(ctx, R_PDIVV, *f));
              auto* r1 = static_cast<const Rec4<T>*>(ensureRec<T>(ctx, R_VV, *f));
              LAUNCH_PBC(ctx, *box, avSwitchesKernel, gridFor(last - first, kHydroBlock), first, last, hc->ngmax, hc->K,
-                        pbcBox(*box), neighbors, typed<T>(*f), r0, r1, wh, hc->minDt, T(hc->alphamin),
+                        pbcBox(*box), neighbors, scoped<T>(ctx, *f), r0, r1, wh, hc->minDt, T(hc->alphamin),
                         T(hc->alphamax), T(hc->decay_constant)););
     SPHB200_CATCH
 }
@@ -1176,5 +1316,52 @@ extern "C" int sphb200_positions_update_h(sphb200_ctx* ctx, int dtype, uint32_t 
     ctx->packValid = 0;
     DISPATCH(dtype, SPHB200_LAUNCH(ctx, positionsKernel<T>, gridFor(last - first, 256), 256, 0, first, last, dt, dt_m1,
                                    pbcBox(*box), typed<T>(*f), T(hc->muiConst), hc->gamma, hc->ng0, f->x, f->y, f->z););
+    SPHB200_CATCH
+}
+
+// ---------------------------------------------------------------- block time steps: group operators
+extern "C" int sphb200_drift_positions(sphb200_ctx* ctx, int dtype, const sphb200_group_view* grp, float dt,
+                                       float dt_back, const float* dt_m1_h, const uint8_t* rung,
+                                       const sphb200_hydro_const* hc, const sphb200_fields* f)
+{
+    SPHB200_TRY
+    if (grp->numGroups == 0) return 0;
+    RungDt r;
+    for (int k = 0; k < 4; ++k)
+        r.v[k] = dt_m1_h[k];
+    int grid = gridFor(size_t(grp->numGroups) * 32, 256);
+    DISPATCH(dtype, SPHB200_LAUNCH(ctx, driftGroupsKernel<T>, grid, 256, 0, grp->groupStart, grp->groupEnd,
+                                   grp->numGroups, dt, dt_back, r, rung, typed<T>(*f), T(hc->muiConst), hc->gamma, f->x,
+                                   f->y, f->z););
+    ctx->packValid = 0; // positions, velocities changed
+    SPHB200_CATCH
+}
+
+extern "C" int sphb200_compute_positions_groups(sphb200_ctx* ctx, int dtype, const sphb200_group_view* grp, float dt,
+                                                const float* dt_m1_h, const uint8_t* rung, const sphb200_box* box,
+                                                const sphb200_hydro_const* hc, const sphb200_fields* f)
+{
+    SPHB200_TRY
+    if (grp->numGroups == 0) return 0;
+    RungDt r;
+    for (int k = 0; k < 4; ++k)
+        r.v[k] = dt_m1_h[k];
+    int grid = gridFor(size_t(grp->numGroups) * 32, 256);
+    DISPATCH(dtype, SPHB200_LAUNCH(ctx, positionsGroupsKernel<T>, grid, 256, 0, grp->groupStart, grp->groupEnd,
+                                   grp->numGroups, dt, r, rung, pbcBox(*box), typed<T>(*f), T(hc->muiConst), hc->gamma,
+                                   f->x, f->y, f->z););
+    ctx->packValid = 0;
+    SPHB200_CATCH
+}
+
+extern "C" int sphb200_update_h_groups(sphb200_ctx* ctx, int dtype, const sphb200_group_view* grp, unsigned ng0,
+                                       const uint32_t* nc, void* h)
+{
+    SPHB200_TRY
+    if (grp->numGroups == 0) return 0;
+    int grid = gridFor(size_t(grp->numGroups) * 32, 256);
+    DISPATCH(dtype, SPHB200_LAUNCH(ctx, updateHGroupsKernel<T>, grid, 256, 0, grp->groupStart, grp->groupEnd,
+                                   grp->numGroups, ng0, nc, static_cast<T*>(h)););
+    ctx->packValid = 0;
     SPHB200_CATCH
 }

@@ -351,7 +351,8 @@ __global__ void __launch_bounds__(kNbWarps * 32)
     findNeighborsKernel(DevTree tree, const double* __restrict__ x, const double* __restrict__ y,
                         const double* __restrict__ z, Th* __restrict__ h, LocalIndex first, LocalIndex last,
                         sphb200_box box, unsigned ng0, unsigned ngmax, int iterateH, uint32_t* __restrict__ nidx,
-                        uint32_t* __restrict__ nc, unsigned* __restrict__ numFails)
+                        uint32_t* __restrict__ nc, unsigned* __restrict__ numFails,
+                        const uint8_t* __restrict__ activeMask, double extFactor)
 {
     __shared__ TreeNodeIndex stackMem[kNbWarps][kStackSize];
     __shared__ double candMem[kNbWarps][96];
@@ -366,8 +367,11 @@ __global__ void __launch_bounds__(kNbWarps * 32)
     TreeNodeIndex* stack = stackMem[warp];
     double* cand         = candMem[warp];
 
-    const bool valid   = gBase + lane < last;
-    const LocalIndex i = valid ? LocalIndex(gBase + lane) : last - 1;
+    // GroupView scope (block time steps): only the marked targets are searched, a slab without any is skipped
+    const bool inRange = gBase + lane < last;
+    const bool valid   = inRange && (!activeMask || activeMask[gBase + lane]);
+    if (!__any_sync(0xffffffffu, valid)) return;
+    const LocalIndex i = inRange ? LocalIndex(gBase + lane) : last - 1;
     const double xi = x[i], yi = y[i], zi = z[i];
     Th hi           = h[i];
     uint32_t* myList = nidx + nbOffset(group * 32 + lane, 0, ngmax);
@@ -425,7 +429,9 @@ __global__ void __launch_bounds__(kNbWarps * 32)
         {
             tc[d] = 0.5 * (hi3[d] + lo[d]);
             // conservative: pruning only, membership is decided by the exact distance test
-            ts[d]  = 0.5 * (hi3[d] - lo[d]) * (1.0 + 1e-9) + 1e-13 * box.len[d];
+            // extFactor: OctreeNsView::searchExtFactor (find_neighbors.cuh:462), > 1 while particles have drifted
+            // out of the cells of a tree that was not rebuilt (HydroVeBdtProp::partialSync)
+            ts[d]  = 0.5 * (hi3[d] - lo[d]) * (1.0 + 1e-9) * extFactor + 1e-13 * box.len[d];
             inside = inside && (lo[d] >= box.lim[2 * d]) && (hi3[d] <= box.lim[2 * d + 1]);
         }
         // same switch as findneighbors.hpp:116-118 / find_neighbors.cuh:470-472: no fold needed if all search
@@ -571,10 +577,12 @@ extern "C" int sphb200_find_neighbors(sphb200_ctx* ctx, const sphb200_tree_view*
         int grid         = int((numGroups + kNbWarps - 1) / kNbWarps);
         if (dtype == SPHB200_F64)
             SPHB200_LAUNCH(ctx, findNeighborsKernel<double>, grid, kNbWarps * 32, 0, tree, x, y, z,
-                           static_cast<double*>(h), first, last, *box, ng0, ngmax, iterateH, neighbors, nc, dFails);
+                           static_cast<double*>(h), first, last, *box, ng0, ngmax, iterateH, neighbors, nc, dFails,
+                           ctx->scopeActive, double(ctx->searchExtFactor));
         else
             SPHB200_LAUNCH(ctx, findNeighborsKernel<float>, grid, kNbWarps * 32, 0, tree, x, y, z,
-                           static_cast<float*>(h), first, last, *box, ng0, ngmax, iterateH, neighbors, nc, dFails);
+                           static_cast<float*>(h), first, last, *box, ng0, ngmax, iterateH, neighbors, nc, dFails,
+                           ctx->scopeActive, double(ctx->searchExtFactor));
         if (numFails_h)
         {
             SPHB200_CUDA(cudaMemcpyAsync(ctx->hostScalars + 4, dFails, sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->stream));

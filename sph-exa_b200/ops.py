@@ -400,3 +400,71 @@ def targetsFromGroups(ctx, grp_view):
     nt = C.c_uint32(0)
     check(lib.sphb200_targets_from_groups(ctx.h, C.byref(grp_view), ptr(t), C.byref(nt)))
     return t[:nt.value]
+
+
+def markGroups(ctx, grp_view, n):
+    """uint8 mask [n]: 1 for the members of the groups"""
+    dev = torch.device("cuda", torch.cuda.current_device())
+    mask = torch.empty(max(n, 1), dtype=torch.uint8, device=dev)
+    check(lib.sphb200_mark_groups(ctx.h, C.byref(grp_view), C.c_uint32(n), ptr(mask)))
+    return mask[:n]
+
+
+class scope:
+    """with ops.scope(ctx, active=mask, searchExtFactor=f, dtParticle=t): the GroupView argument of the reference's GPU
+    operators (sph_gpu.hpp:13-82) and OctreeNsView::searchExtFactor as context state (sphb200_set_scope)"""
+
+    def __init__(self, ctx, active=None, searchExtFactor=1.0, dtParticle=None):
+        self.ctx = ctx
+        self.s = B.OpScope()
+        self.s.active = active.data_ptr() if active is not None else None
+        self.s.searchExtFactor = searchExtFactor
+        self.s.dtParticle = dtParticle.data_ptr() if dtParticle is not None else None
+        self.keep = (active, dtParticle)
+
+    def __enter__(self):
+        check(lib.sphb200_set_scope(self.ctx.h, C.byref(self.s)))
+        return self
+
+    def __exit__(self, *exc):
+        check(lib.sphb200_set_scope(self.ctx.h, None))
+        return False
+
+
+def sortGroupDt(ctx, groupDt, numGroups=None):
+    """sortGroupDt (sph/include/sph/ts_rungs.hpp:55-66): sorts groupDt[:numGroups] in place, returns the ordering"""
+    n = groupDt.numel() if numGroups is None else numGroups
+    idx = torch.empty(max(n, 1), dtype=torch.int32, device=groupDt.device)
+    check(lib.sphb200_sort_group_dt(ctx.h, ptr(groupDt), ptr(idx), C.c_uint32(n)))
+    return idx[:n]
+
+
+def rungRanges(ctx, minDt, groupDt, numGroups, numRungs, fastFraction=0.4):
+    """findRungRanges + timestepRangeGpu (ts_rungs.hpp:69-75,115-129): ([5 ranges], (dt[0], dt[fast]))"""
+    rr = (C.c_uint32 * 5)()
+    mdt = (C.c_float * 2)()
+    check(lib.sphb200_rung_ranges(ctx.h, C.c_float(minDt), ptr(groupDt), C.c_uint32(numGroups), int(numRungs),
+                                  C.c_float(fastFraction), rr, mdt))
+    return list(rr), (mdt[0], mdt[1])
+
+
+def _dt4(dt_m1):
+    return (C.c_float * 4)(*[float(v) for v in dt_m1])
+
+
+def driftPositions(ctx, dtype, grp_view, dt, dt_back, dt_m1, rung, hc, f):
+    """driftPositionsGpu (sph/include/sph/positions_gpu.cu:47-111)"""
+    check(lib.sphb200_drift_positions(ctx.h, dtype, C.byref(grp_view), C.c_float(dt), C.c_float(dt_back), _dt4(dt_m1),
+                                      ptr(rung), C.byref(hc), C.byref(f)))
+
+
+def computePositionsGroups(ctx, dtype, grp_view, dt, dt_m1, rung, box, hc, f):
+    """computePositionsGpu (positions_gpu.cu:118-180)"""
+    check(lib.sphb200_compute_positions_groups(ctx.h, dtype, C.byref(grp_view), C.c_float(dt), _dt4(dt_m1), ptr(rung),
+                                               C.byref(box), C.byref(hc), C.byref(f)))
+
+
+def updateSmoothingLengthGroups(ctx, grp_view, ng0, nc, h):
+    """updateSmoothingLengthGpu (sph/include/sph/update_h_gpu.cu:39-60)"""
+    check(lib.sphb200_update_h_groups(ctx.h, B.F64 if h.dtype == torch.float64 else B.MIXED, C.byref(grp_view),
+                                      C.c_uint(ng0), ptr(nc), ptr(h)))

@@ -220,3 +220,48 @@ class HydroVeProp:
 
     def globalCounts(self):
         return self._d2h(lib.sphb200_sim_global_counts(self.h), self.numGlobalLeaves, np.uint32)
+
+
+class HydroVeBdtProp(HydroVeProp):
+    """sphexa::HydroVeBdtProp (main/src/propagator/ve_hydro_bdt.hpp:51-420): SPH-VE with block time steps.
+
+    Groups of <= 32 SFC-consecutive particles get their own time step (Courant, divv and acceleration criteria), the
+    steps are binned into <= 4 power-of-two rungs, and between two full syncs only the groups of the rungs that are
+    due are re-evaluated (sync() = fullSync or partialSync); the others are drifted."""
+
+    def __init__(self, *args, safety_steps=0, eta_acc=0.0, eps=0.0, **kw):
+        super().__init__(*args, **kw)
+        check(lib.sphb200_sim_bdt_enable(self.h, int(safety_steps), C.c_double(eta_acc), C.c_double(eps)))
+
+    def computeForces(self):
+        check(lib.sphb200_sim_bdt_compute_forces(self.h))
+
+    def integrate(self, global_min_dt=-1.0):
+        check(lib.sphb200_sim_bdt_integrate(self.h))
+
+    def step(self):
+        check(lib.sphb200_sim_bdt_step(self.h))
+
+    def timestep(self):
+        """sph::Timestep of the running hierarchy + group counts (binding.BdtInfo)"""
+        info = B.BdtInfo()
+        check(lib.sphb200_sim_bdt_info(self.h, C.byref(info)))
+        return info
+
+    def isSynced(self):
+        """Propagator::isSynced (ve_hydro_bdt.hpp:220): the next computeForces starts with a full sync"""
+        return bool(self.timestep().isSynced)
+
+    def rungs(self):
+        """per-particle rung of the owned particles"""
+        p = lib.sphb200_sim_bdt_rungs(self.h)
+        return self._d2h(p + self.startIndex, self.endIndex - self.startIndex, np.uint8)
+
+    def groupDt(self):
+        return self._d2h(lib.sphb200_sim_bdt_group_dt(self.h), self.timestep().numGroups, np.float32)
+
+    def tsGroups(self):
+        """groups of the last full sync in time-step order: (start, end) index arrays"""
+        v = B.GroupView()
+        check(lib.sphb200_sim_bdt_groups(self.h, C.byref(v)))
+        return self._d2h(v.groupStart, v.numGroups, np.uint32), self._d2h(v.groupEnd, v.numGroups, np.uint32)
