@@ -937,7 +937,10 @@ __device__ __forceinline__ void positionUpdate1(double dt, double dt_m1, double 
 //! @brief energyUpdate (positions.hpp:54-61)
 __device__ __forceinline__ double energyUpdate1(double u_old, double dt, double dt_m1, double du, double du_m1)
 {
-    double u_new = u_old + du * dt + 0.5 * (du - du_m1) / dt_m1 * fabs(dt) * dt;
+    // No FMA contraction here: drifting back to an almost-zero energy (Noh: u = 1e-20) leaves a rounding residual
+    // whose sign selects the branch below, so the operation sequence has to be the reference's, rounding by rounding
+    double second = __dmul_rn(__dmul_rn(__dmul_rn(0.5, du - du_m1) / dt_m1, fabs(dt)), dt);
+    double u_new  = __dadd_rn(__dadd_rn(u_old, __dmul_rn(du, dt)), second);
     if (u_new < 0.) { u_new = u_old * exp(u_new * dt / u_old); }
     return u_new;
 }
@@ -976,7 +979,7 @@ __global__ void __launch_bounds__(256)
     T cv           = T(R / muiConst / (gamma - T(1)));
     double du      = f.du[i];
     double dum1    = double(f.du_m1[i]);
-    double u_recov = energyUpdate1(double(f.temp[i] * cv), -double(dt_back), dt_m1_rung, du, dum1);
+    double u_recov = energyUpdate1(__dmul_rn(f.temp[i], double(cv)), -double(dt_back), dt_m1_rung, du, dum1);
     f.temp[i]      = energyUpdate1(u_recov, dt, dt_m1_rung, du, dum1) / cv;
 }
 
@@ -1022,7 +1025,7 @@ __global__ void __launch_bounds__(256)
     const T R    = 8.317e7;
     T cv         = T(R / muiConst / (gamma - T(1)));
     double du    = f.du[i];
-    double u_old = f.temp[i] * cv;
+    double u_old = __dmul_rn(f.temp[i], double(cv));
     f.temp[i]    = energyUpdate1(u_old, dt, dt_m1_rung, du, double(f.du_m1[i])) / cv;
     f.du_m1[i]   = T(du);
 }

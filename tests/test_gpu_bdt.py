@@ -147,8 +147,11 @@ def test_scoped_operators_touch_only_active_targets(pkg, ctx, ref):
     full["du"] = to_dev(sim.f["du"])
     full["alpha"] = to_dev(sim.alpha_pre)
     full["nc"] = nc_all
-    for op in (ops.computeXMass, ops.computeVeDefGradh, ops.computeIadDivvCurlv, ops.computeAVswitches):
-        op(ctx, 0, n, full, b, hc, nb_all)
+    ops.computeXMass(ctx, 0, n, full, b, hc, nb_all)
+    ops.computeVeDefGradh(ctx, 0, n, full, b, hc, nb_all)
+    ops.computeEOS(ctx, 0, n, full, hc)
+    ops.computeIadDivvCurlv(ctx, 0, n, full, b, hc, nb_all)
+    ops.computeAVswitches(ctx, 0, n, full, b, hc, nb_all)
     ops.computeMomentumEnergy(ctx, 0, n, full, b, hc, nb_all)
 
     outs = ["xm", "kx", "gradh", "c11", "c12", "c13", "c22", "c23", "c33", "divv", "curlv", "alpha", "ax", "ay", "az",
@@ -220,6 +223,14 @@ def run_pair(pkg, ctx, case, side, steps, **kw):
     from oracle.bdt import RefBdtSim
     from sph_exa_b200 import sim as S
     f, box, s = pkg.ic.CASES[case](side)
+    if case == "noh":
+        # The Noh IC starts at u = 1e-20.  Drifting a particle back to the start of its hierarchy (driftKernel) then
+        # recovers u = O(rounding noise of du * dt), and the sign of that residual selects the u < 0 branch of
+        # energyUpdate (positions.hpp:58-59): the reference's result is discontinuous in the last bit of du there, on
+        # any two implementations.  A floor of u = 1e-10 (still 7 orders below the post-shock energies) keeps the test
+        # on the continuous side.
+        cv = 8.317e7 / s["mui"] / (s["gamma"] - 1.0)
+        f["temp"] = np.full_like(f["temp"], 1e-10 / cv)
     rs = RefBdtSim(f, box, s, **kw)
     gs = S.HydroVeBdtProp(ctx, box, s, capacity=f["x"].size, tables=(rs.rs.wh, rs.rs.whd, rs.rs.K), **kw)
     gs.upload(f)
@@ -259,6 +270,7 @@ def test_bdt_propagator_vs_reference_sequence(pkg, ctx, ref, case, side, steps):
         seen_partial += not was_synced
         assert abs(gs.minDt - rs.rs.minDt) <= 1e-6 * rs.rs.minDt and abs(gs.ttot - rs.rs.ttot) <= 1e-6 * rs.rs.ttot
     assert max(seen_rungs) >= 2 and seen_partial >= 3, (seen_rungs, seen_partial)
+    gs.close()
 
 
 @pytest.mark.parametrize("case,side,safety", [("sedov", 16, 100), ("kh", 24, 0)])
@@ -278,3 +290,4 @@ def test_bdt_single_rung(pkg, ctx, ref, case, side, safety):
         c = gs.conserved()
         e0 = e0 or c["etot"]
         assert abs(c["etot"] - e0) < 1e-4 * abs(e0)
+    gs.close()
