@@ -205,6 +205,7 @@ def main():
     ap.add_argument("--ref-side", type=int, default=100, help="lattice side of the CPU reference sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-bdt", action="store_true", help="skip the block-time-step (ve-bdt) hierarchy report")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else max(args.warmup, 1)
 
@@ -332,6 +333,40 @@ def main():
         except Exception as ex:  # the checker library is absent: report it, never substitute
             cpu = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": f"unavailable: {ex}"}
 
+    # ---------------- block time steps (HydroVeBdtProp): two hierarchies on the same IC, reported
+    # beside the headline (the headline itself stays the global-time-step propagator BASELINE.json names)
+    bdt = None
+    if not args.no_bdt:
+        gs.close()
+        gs = S.HydroVeBdtProp(ctx, box, s, capacity=n, dtype=dtype)
+        gs.upload(f)
+        sub = []
+        hierarchies = 0
+        while hierarchies < 2 and len(sub) < 40:
+            full = gs.isSynced()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            gs.step()
+            b.record()
+            sync()
+            info = gs.timestep()
+            sub.append({"full_sync": full, "ms": a.elapsed_time(b), "active_groups": info.numActiveGroups,
+                        "groups": info.numGroups, "rungs": info.numRungs, "dt": info.nextDt})
+            hierarchies += bool(info.isSynced)
+        last = [x for x in sub if x["rungs"] == sub[-1]["rungs"]][-(1 << (sub[-1]["rungs"] - 1)):]
+        part = [x for x in last if not x["full_sync"]]
+        hier_ms = sum(x["ms"] for x in last)
+        bdt = {"propagator": "ve-bdt", "rungs": last[-1]["rungs"], "substeps_per_hierarchy": len(last),
+               "rung_ranges": list(gs.timestep().rungRanges), "groups": last[-1]["groups"],
+               "full_sync_substep_ms": next((x["ms"] for x in last if x["full_sync"]), None),
+               "partial_substep_ms": (sum(x["ms"] for x in part) / len(part)) if part else None,
+               "active_group_fraction_partial": (sum(x["active_groups"] for x in part) / len(part) / last[-1]["groups"])
+               if part else None,
+               "hierarchy_ms": hier_ms,
+               # the same simulated time with the global-time-step propagator: one full step per substep
+               "global_dt_equivalent_ms": len(last) * ms_per_step,
+               "speedup_vs_global_dt": len(last) * ms_per_step / hier_ms if hier_ms > 0 else None}
+
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -342,6 +377,7 @@ def main():
         "find_neighbors_ms": phase_ms.get("FindNeighbors"),
         "phase_ms": phase_ms, "total_neighbors": total_nb, "leaves": gs.numLeaves,
         "clocks": clocks, "gpu_launches": launches, "roofline": roofline, "e2e": e2e, "cpu_baseline": cpu,
+        "block_time_steps": bdt,
     }
     print(json.dumps(line), flush=True)
     gs.close()

@@ -284,9 +284,37 @@ public:
         return t;
     }
 
-private:
+protected:
     const Context& ctx_;
     sphb200_sim* sim_{nullptr};
+};
+
+/*! @brief sphexa::HydroVeBdtProp (main/src/propagator/ve_hydro_bdt.hpp:51-420): SPH-VE with block time steps
+ *
+ * Same interface as HydroVeProp; computeForces() runs fullSync or partialSync itself like the reference's sync()
+ * (ve_hydro_bdt.hpp:213-218) and evaluates the forces of the groups whose rungs are due, integrate() re-bins the
+ * groups (computeRungs), advances the due rungs, drifts the others and updates h of the active groups.
+ */
+class HydroVeBdtProp : public HydroVeProp
+{
+public:
+    HydroVeBdtProp(const Context& c, const sphb200_sim_config& cfg, int safetySteps = 0, double etaAcc = 0.2,
+                   double eps = 0.005)
+        : HydroVeProp(c, cfg)
+    {
+        check(sphb200_sim_bdt_enable(sim_, safetySteps, etaAcc, eps));
+    }
+    void computeForces() { check(sphb200_sim_bdt_compute_forces(sim_)); }
+    void integrate() { check(sphb200_sim_bdt_integrate(sim_)); }
+    //! @brief Propagator::isSynced (ve_hydro_bdt.hpp:220): output / observables are only consistent then
+    bool isSynced() const { return timestep().isSynced != 0; }
+    //! @brief sph::Timestep of the running hierarchy (sph/include/sph/timestep.h:42-66) + group counts
+    sphb200_bdt_info timestep() const
+    {
+        sphb200_bdt_info info;
+        check(sphb200_sim_bdt_info(sim_, &info));
+        return info;
+    }
 };
 
 } // namespace sphb200::host

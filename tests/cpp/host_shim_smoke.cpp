@@ -81,6 +81,23 @@ int main(int argc, char** argv)
             }
             std::printf("restart ok\n");
         }
+        // block time steps: one hierarchy of HydroVeBdtProp (full sync, then partial syncs until the next full one)
+        {
+            HydroVeBdtProp bdt(ctx, cfg);
+            bdt.upload(n, f);
+            int substeps = 0, partial = 0;
+            do
+            {
+                partial += !bdt.isSynced();
+                bdt.computeForces();
+                bdt.integrate();
+                ++substeps;
+            } while (!bdt.isSynced() && substeps < 64);
+            auto ts = bdt.timestep();
+            std::printf("bdt ok: rungs=%d substeps=%d partial=%d groups=%u nextDt=%.6e\n", ts.numRungs, substeps, partial,
+                        ts.numGroups, double(ts.nextDt));
+            if (substeps != (1 << (ts.numRungs - 1))) return 4;
+        }
         // error path: precondition violation -> std::runtime_error
         bool threw = false;
         try
