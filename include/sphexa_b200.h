@@ -192,6 +192,25 @@ int sphb200_momentum_energy(sphb200_ctx*, int dtype, uint32_t first, uint32_t la
                             const sphb200_hydro_const* hc_h, const uint32_t* neighbors, const sphb200_fields* f_h,
                             double* minDtCourant_h);
 
+/* The same operator for the targets [begin,end) of [first,last) (begin - first a multiple of 128; lists and nc are
+ * addressed relative to first like above).  pack != 0 rebuilds the gather records from the current field arrays;
+ * pack == 0 reuses those of the previous call, so a caller may integrate [begin,end) of an earlier call in between
+ * (sphb200_positions_update_h on that range): later ranges still see the pre-integration state of their neighbors.
+ * Used with sphb200_av_switches_courant, which makes the time step known before this operator starts. */
+int sphb200_momentum_energy_range(sphb200_ctx*, int dtype, uint32_t first, uint32_t last, uint32_t begin, uint32_t end,
+                                  int pack, const sphb200_box* box_h, const sphb200_hydro_const* hc_h,
+                                  const uint32_t* neighbors, const sphb200_fields* f_h);
+/* hNew[i] = updateH(ng0, nc[i], h[i]) for [first,last) without touching h (update_h.hpp:12-24): the smoothing length
+ * of the next step only depends on the neighbor counts, so a host-resident front-end can have it back early; nc, h,
+ * hNew indexed like the fields */
+int sphb200_update_h_into(sphb200_ctx*, int dtype, uint32_t first, uint32_t last, unsigned ng0, const uint32_t* nc,
+                          const void* h, void* hNew);
+/* sphb200_av_switches that also evaluates the Courant step of momentumEnergy (same vijsignal = 0.5 (c_i + c_j) - 2 w_ij
+ * over the same pairs, bit-identical to what sphb200_momentum_energy finds) and leaves it on the device for
+ * sphb200_timestep.  Not available with avClean (there w_ij needs the velocity-gradient correction). */
+int sphb200_av_switches_courant(sphb200_ctx*, int dtype, uint32_t first, uint32_t last, const sphb200_box* box_h,
+                                const sphb200_hydro_const* hc_h, const uint32_t* neighbors, const sphb200_fields* f_h);
+
 /* ---- a20: rhoTimestep + computeTimestep local part (sph/include/sph/ts_global.hpp:71-112) ----
  * out_h[0] = minDtCourant (from the last momentum_energy call), out_h[1] = Krho/|max divv|,
  * out_h[2] = min(out[0], out[1], 1.1*minDt)  (the value fed to the global MIN all-reduce) */

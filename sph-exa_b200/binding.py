@@ -117,7 +117,7 @@ SYMBOLS = [
     "sphb200_drift_positions", "sphb200_compute_positions_groups", "sphb200_update_h_groups",
     "sphb200_sim_bdt_enable", "sphb200_sim_bdt_compute_forces", "sphb200_sim_bdt_integrate", "sphb200_sim_bdt_step",
     "sphb200_sim_bdt_info", "sphb200_sim_bdt_rungs", "sphb200_sim_bdt_group_dt", "sphb200_sim_bdt_active",
-    "sphb200_sim_bdt_groups",
+    "sphb200_sim_bdt_groups", "sphb200_momentum_energy_range", "sphb200_av_switches_courant", "sphb200_update_h_into",
 ]
 
 lib.sphb200_last_error.restype = C.c_char_p

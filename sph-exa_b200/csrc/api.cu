@@ -8,6 +8,9 @@
 #include <algorithm>
 #include <array>
 #include <mutex>
+#include <cstdlib>
+#include <utility>
+#include <vector>
 #include "common.cuh"
 
 namespace sphb200
@@ -259,7 +262,7 @@ struct sphb200_sim
     } bdt;
 
     cudaStream_t copyIn = nullptr, copyOut = nullptr;
-    cudaEvent_t evUp[3] = {}, evDown[2] = {};
+    cudaEvent_t evUp[4] = {}, evDown[3] = {}, evRange[16] = {};
 
     int elemBytes(int id) const
     {
@@ -396,6 +399,8 @@ extern "C" void sphb200_sim_destroy(sphb200_sim* s)
         cudaStreamDestroy(s->copyOut);
         for (auto& e : s->evUp) cudaEventDestroy(e);
         for (auto& e : s->evDown) cudaEventDestroy(e);
+        for (auto& e : s->evRange)
+            if (e) cudaEventDestroy(e);
     }
     delete s;
 }
@@ -656,14 +661,27 @@ extern "C" int sphb200_sim_step_host(sphb200_sim* s, size_t n, const sphb200_fie
     }
     // everything issued earlier on the compute stream (e.g. a previous step) must be done before fields are overwritten
     SPHB200_CUDA(cudaStreamSynchronize(ctx->stream));
+    // SPHB200_HOST_PROFILE=1: timeline of the transfers and kernels of this call on stderr
+    static const bool profile = std::getenv("SPHB200_HOST_PROFILE") != nullptr;
+    std::vector<std::pair<const char*, cudaEvent_t>> tl;
+    auto stamp = [&](const char* name, cudaStream_t st)
+    {
+        if (!profile) return;
+        cudaEvent_t e;
+        SPHB200_CUDA(cudaEventCreate(&e));
+        SPHB200_CUDA(cudaEventRecord(e, st));
+        tl.emplace_back(name, e);
+    };
+    stamp("start", ctx->stream);
     ctx->packValid = 0;
     s->n = s->end = uint32_t(n);
     s->start      = 0;
 
     static const int groupA[] = {F_x, F_y, F_z};
-    static const int groupB[] = {F_h, F_m, F_temp};
+    static const int groupH[]  = {F_h};
+    static const int groupMT[] = {F_m, F_temp};
+    static const int groupAH[] = {F_x, F_y, F_z, F_h};
     static const int groupC[] = {F_vx, F_vy, F_vz, F_x_m1, F_y_m1, F_z_m1, F_du_m1, F_alpha};
-    static const int groupAB[] = {F_x, F_y, F_z, F_h, F_m, F_temp};
     sphb200_fields hin = *host_in, hout = *host_out;
     auto upload = [&](const int* ids, int count, cudaEvent_t done)
     {
@@ -682,38 +700,146 @@ extern "C" int sphb200_sim_step_host(sphb200_sim* s, size_t n, const sphb200_fie
         if (dst)
             SPHB200_CUDA(cudaMemcpyAsync(dst, s->field[id], n * s->elemBytes(id), cudaMemcpyDeviceToHost, stream));
     };
+    // upload order = order of first use: {x,y,z} (keys, sort), h (tree search), {m,temp} (XMass, EOS), the rest (IAD on)
     upload(groupA, 3, s->evUp[0]);
-    upload(groupB, 3, s->evUp[1]);
+    stamp("up xyz", s->copyIn);
+    upload(groupH, 1, s->evUp[1]);
+    stamp("up h", s->copyIn);
+    upload(groupMT, 2, s->evUp[3]);
+    stamp("up m,temp", s->copyIn);
     upload(groupC, 8, s->evUp[2]);
+    stamp("up rest", s->copyIn);
 
     SPHB200_CUDA(cudaStreamWaitEvent(ctx->stream, s->evUp[0], 0));
     s->mark(0);
     syncKeys(s);
     SPHB200_CUDA(cudaStreamWaitEvent(ctx->stream, s->evUp[1], 0));
-    gatherConserved(s, groupAB, 6);
+    gatherConserved(s, groupAH, 4);
     syncFocus(s);
     s->mark(1);
-    SPHB200_CUDA(cudaEventRecord(s->evDown[0], ctx->stream));
-    SPHB200_CUDA(cudaStreamWaitEvent(s->copyOut, s->evDown[0], 0));
-    download(F_m, s->copyOut);
-
-    CHECK_RC(sphb200_sim_forces_phase(s, 0));
+    {
+        // forces phase 0 (FindNeighbors, XMass) with the reorder of m and temp slipped in between: the search needs
+        // positions and h only
+        sphb200_fields f       = s->table();
+        sphb200_hydro_const hc = s->hydroConst();
+        sphb200_tree_view tv   = s->treeView();
+        CHECK_RC(sphb200_find_neighbors(ctx, &tv, f.x, f.y, f.z, f.h, s->cfg.dtype, s->start, s->end, &s->box, hc.ng0,
+                                        hc.ngmax, 1, s->neighbors, f.nc + s->start, nullptr));
+        ctx->packValid = 0; // h changed
+        s->mark(2);
+        SPHB200_CUDA(cudaStreamWaitEvent(ctx->stream, s->evUp[3], 0));
+        gatherConserved(s, groupMT, 2);
+        SPHB200_CUDA(cudaEventRecord(s->evDown[0], ctx->stream));
+        SPHB200_CUDA(cudaStreamWaitEvent(s->copyOut, s->evDown[0], 0));
+        download(F_m, s->copyOut);
+        f = s->table();
+        CHECK_RC(sphb200_xmass(ctx, s->cfg.dtype, s->start, s->end, &s->box, &hc, s->neighbors, &f));
+        s->mark(3);
+    }
+    const bool ranged = !s->cfg.hc.avClean && n >= 16 * 128;
+    if (ranged && *fieldSlot(hout, F_h))
+    {
+        // the next step's h = updateH(ng0, nc, h) is known once the neighbors are counted: evaluate it into the spare
+        // buffer of h (free since the reorder) and send it now; the position update recomputes the same value in place
+        sphb200_fields f = s->table();
+        CHECK_RC(sphb200_update_h_into(ctx, s->cfg.dtype, s->start, s->end, s->cfg.hc.ng0, f.nc, f.h, s->fieldAlt[F_h]));
+        SPHB200_CUDA(cudaEventRecord(s->evDown[2], ctx->stream));
+        SPHB200_CUDA(cudaStreamWaitEvent(s->copyOut, s->evDown[2], 0));
+        SPHB200_CUDA(cudaMemcpyAsync(*fieldSlot(hout, F_h), s->fieldAlt[F_h], n * s->elemBytes(F_h),
+                                     cudaMemcpyDeviceToHost, s->copyOut));
+    }
     CHECK_RC(sphb200_sim_forces_phase(s, 1));
     SPHB200_CUDA(cudaStreamWaitEvent(ctx->stream, s->evUp[2], 0));
     gatherConserved(s, groupC, 8);
     ctx->packValid &= 1u; // only the position record (x, y, z, m) is still current
+    stamp("gradh+eos done", ctx->stream);
     CHECK_RC(sphb200_sim_forces_phase(s, 2));
-    CHECK_RC(sphb200_sim_forces_phase(s, 3));
-    SPHB200_CUDA(cudaEventRecord(s->evDown[1], ctx->stream));
-    SPHB200_CUDA(cudaStreamWaitEvent(s->copyOut, s->evDown[1], 0));
-    download(F_alpha, s->copyOut);
-    CHECK_RC(sphb200_sim_forces_phase(s, 4));
-    CHECK_RC(sphb200_sim_integrate(s, -1.0));
+    stamp("iad done", ctx->stream);
+    // Early Courant step: AVswitches evaluates momentumEnergy's signal velocity over the same pairs, so dt is known
+    // before the last pair kernel starts; that kernel then runs range by range, each range is integrated right away
+    // and leaves for the host while the next one computes (the final download no longer waits for the whole kernel).
+    if (!ranged)
+    {
+        CHECK_RC(sphb200_sim_forces_phase(s, 3));
+        SPHB200_CUDA(cudaEventRecord(s->evDown[1], ctx->stream));
+        SPHB200_CUDA(cudaStreamWaitEvent(s->copyOut, s->evDown[1], 0));
+        download(F_alpha, s->copyOut);
+        CHECK_RC(sphb200_sim_forces_phase(s, 4));
+        CHECK_RC(sphb200_sim_integrate(s, -1.0));
+        for (int id = 0; id < kNumConserved; ++id)
+            if (id != F_m && id != F_alpha) download(id, ctx->stream);
+    }
+    else
+    {
+        sphb200_fields f       = s->table();
+        sphb200_hydro_const hc = s->hydroConst();
+        int dtype              = s->cfg.dtype;
+        uint32_t a = s->start, b = s->end;
+        CHECK_RC(sphb200_av_switches_courant(ctx, dtype, a, b, &s->box, &hc, s->neighbors, &f));
+        s->mark(7);
+        stamp("av+courant done", ctx->stream);
+        // computeTimestep (ts_global.hpp:96-112): Courant key from AVswitches, divv limit, growth cap.  Read back
+        // before alpha is queued on the device-to-host engine: the 24 bytes would wait behind its 64 MB
+        CHECK_RC(sphb200_timestep(ctx, dtype, a, b, &hc, &f, s->dtLocal));
+        stamp("dt known", ctx->stream);
+        SPHB200_CUDA(cudaEventRecord(s->evDown[1], ctx->stream));
+        SPHB200_CUDA(cudaStreamWaitEvent(s->copyOut, s->evDown[1], 0));
+        download(F_alpha, s->copyOut);
+        double dt   = s->dtLocal[2];
+        s->ttot += dt;
+        s->minDt_m1 = s->minDt;
+        double dtStir = s->minDt; // TurbVeProp stirs with the time step of the previous iteration (turb_ve.hpp:113-118)
+        s->minDt    = dt;
 
-    for (int id = 0; id < kNumConserved; ++id)
-        if (id != F_m && id != F_alpha) download(id, ctx->stream);
+        constexpr int kRanges = 16;
+        if (!s->evRange[0])
+            for (auto& e : s->evRange) SPHB200_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        uint32_t per = ((b - a + kRanges - 1) / kRanges + 127) / 128 * 128;
+        for (int r = 0; r < kRanges; ++r)
+        {
+            uint32_t rb = std::min(b, a + r * per), re = std::min(b, rb + per);
+            if (re <= rb) break;
+            CHECK_RC(sphb200_momentum_energy_range(ctx, dtype, a, b, rb, re, r == 0, &s->box, &hc, s->neighbors, &f));
+            if (s->turb)
+                CHECK_RC(sphb200_turb_drive(s->turb, ctx, dtype, rb, re, f.x, f.y, f.z, f.ax, f.ay, f.az, dtStir));
+            CHECK_RC(sphb200_positions_update_h(ctx, dtype, rb, re, &s->box, &hc, s->minDt, s->minDt_m1, &f));
+            SPHB200_CUDA(cudaEventRecord(s->evRange[r], ctx->stream));
+            if (r == 0) stamp("range 0 computed", ctx->stream);
+            SPHB200_CUDA(cudaStreamWaitEvent(s->copyOut, s->evRange[r], 0));
+            for (int id = 0; id < kNumConserved; ++id)
+            {
+                if (id == F_m || id == F_alpha || id == F_h) continue;
+                void* dst = *fieldSlot(hout, id);
+                if (!dst) continue;
+                size_t eb = s->elemBytes(id);
+                SPHB200_CUDA(cudaMemcpyAsync(static_cast<char*>(dst) + size_t(rb) * eb,
+                                             static_cast<char*>(s->field[id]) + size_t(rb) * eb, size_t(re - rb) * eb,
+                                             cudaMemcpyDeviceToHost, s->copyOut));
+            }
+        }
+        s->mark(8);
+        s->mark(9);
+        stamp("last range computed", ctx->stream);
+        stamp("last range down", s->copyOut);
+    }
     SPHB200_CUDA(cudaStreamSynchronize(ctx->stream));
     SPHB200_CUDA(cudaStreamSynchronize(s->copyOut));
+    if (profile)
+    {
+        std::string line = "step_host timeline (ms):";
+        for (auto& [name, e] : tl)
+        {
+            float ms = 0;
+            cudaEventSynchronize(e);
+            cudaEventElapsedTime(&ms, tl[0].second, e);
+            char buf[96];
+            std::snprintf(buf, sizeof(buf), " [%s %.2f]", name, ms);
+            line += buf;
+            if (e != tl[0].second) cudaEventDestroy(e);
+        }
+        cudaEventDestroy(tl[0].second);
+        std::fprintf(stderr, "%s\n", line.c_str());
+    }
     SPHB200_CATCH
 }
 

@@ -533,20 +533,37 @@ __global__ void __launch_bounds__(kHydroBlock, SPHB200_IAD_MIN_BLOCKS)
     }
 }
 
+// ---------------------------------------------------------------- pair quantities shared by AVswitches and momentum
+// The Courant signal velocity can be evaluated in either kernel (sphb200_av_switches_courant lets the step know its
+// time step before momentumEnergy starts); explicit fused multiply-adds make both evaluations the same bits.
+__device__ __forceinline__ double fmaT(double a, double b, double c) { return __fma_rn(a, b, c); }
+__device__ __forceinline__ float fmaT(float a, float b, float c) { return __fmaf_rn(a, b, c); }
+
+template<class T>
+__device__ __forceinline__ T dot3(T ax, T ay, T az, T bx, T by, T bz)
+{
+    return fmaT(az, bz, fmaT(ay, by, ax * bx));
+}
+
+//! @brief vijsignal of momentum_energy_kern.hpp: 0.5 (c_i + c_j) - 2 w_ij
+template<class T>
+__device__ __forceinline__ T courantSignal(T ci, T cj, T wij)
+{
+    return fmaT(T(-2), wij, T(0.5) * (ci + cj));
+}
+
 // ---------------------------------------------------------------- AV switches (av_switches_kern.hpp:44-137)
 // graddivv_b = sum_j factor_j * (-(C_i r)_b K h^-3 W): C_i, K h^-3 are constant in j and applied after the sweep.
 #ifndef SPHB200_AV_MIN_BLOCKS
 #define SPHB200_AV_MIN_BLOCKS 7 // <= 72 registers: 28 warps/SM (measured 6.6 -> 6.2 ms)
 #endif
-template<bool Pbc, class T>
-__global__ void __launch_bounds__(kHydroBlock, SPHB200_AV_MIN_BLOCKS)
-    avSwitchesKernel(uint32_t first, uint32_t last, unsigned ngmax, double K, PbcBox box,
-                     const uint32_t* __restrict__ nidx, F<T> f, const PosRec<T>* __restrict__ r0,
-                     const Rec4<T>* __restrict__ r1, const Rec2<T>* __restrict__ wh, double dt, T alphamin, T alphamax,
-                     T decay_constant)
+template<bool Pbc, bool Courant, class T>
+__device__ __forceinline__ void avSwitchesBody(uint32_t i, uint32_t first, unsigned ngmax, double K, const PbcBox& box,
+                                               const uint32_t* __restrict__ nidx, const F<T>& f,
+                                               const PosRec<T>* __restrict__ r0, const Rec4<T>* __restrict__ r1,
+                                               const Rec2<T>* __restrict__ wh, double dt, T alphamin, T alphamax,
+                                               T decay_constant, T& maxvsignal_i)
 {
-    uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= last || (f.active && !f.active[i])) return;
     NbList nb = nbList(nidx, f.nc, first, i, ngmax);
 
     PosRec<T> pi = r0[i]; // {x, y, z, divv}
@@ -569,16 +586,24 @@ __global__ void __launch_bounds__(kHydroBlock, SPHB200_AV_MIN_BLOCKS)
         T divv_j      = pj_.m; // 4th slot of the position record
         T rx = xi - pj_.x, ry = yi - pj_.y, rz = zi - pj_.z;
         if (pbcI) applyPBC(box, T(2) * hi, rx, ry, rz);
-        T r2_  = rx * rx + ry * ry + rz * rz;
+        T r2_  = dot3(rx, ry, rz, rx, ry, rz);
         T dist = sqrt(r2_);
 
         T vx_ij = vxi - vj.a;
         T vy_ij = vyi - vj.b;
         T vz_ij = vzi - vj.c;
 
-        T rv           = rx * vx_ij + ry * vy_ij + rz * vz_ij;
+        T rv           = dot3(rx, ry, rz, vx_ij, vy_ij, vz_ij);
         T vijsignal_ij = 0.0;
-        if (rv < T(0)) { vijsignal_ij = ci + LD(f.c, j) - T(3) * rv / dist; } // c_j only for approaching pairs
+        if (Courant)
+        {
+            // the Courant signal of momentumEnergy needs c_j of every neighbor
+            T cj = LD(f.c, j);
+            if (rv < T(0)) { vijsignal_ij = ci + cj - T(3) * rv / dist; }
+            T vs         = courantSignal(ci, cj, rv / dist);
+            maxvsignal_i = (vs > maxvsignal_i) ? vs : maxvsignal_i;
+        }
+        else if (rv < T(0)) { vijsignal_ij = ci + LD(f.c, j) - T(3) * rv / dist; } // c_j only for approaching pairs
         vijsignal_i = max(vijsignal_i, vijsignal_ij);
 
         T v1 = dist * hiInv;
@@ -619,6 +644,47 @@ __global__ void __launch_bounds__(kHydroBlock, SPHB200_AV_MIN_BLOCKS)
     f.alpha[i] = alpha_i;
 }
 
+template<bool Pbc, class T>
+__global__ void __launch_bounds__(kHydroBlock, SPHB200_AV_MIN_BLOCKS)
+    avSwitchesKernel(uint32_t first, uint32_t last, unsigned ngmax, double K, PbcBox box,
+                     const uint32_t* __restrict__ nidx, F<T> f, const PosRec<T>* __restrict__ r0,
+                     const Rec4<T>* __restrict__ r1, const Rec2<T>* __restrict__ wh, double dt, T alphamin, T alphamax,
+                     T decay_constant)
+{
+    uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= last || (f.active && !f.active[i])) return;
+    T unused = 0;
+    avSwitchesBody<Pbc, false, T>(i, first, ngmax, K, box, nidx, f, r0, r1, wh, dt, alphamin, alphamax, decay_constant,
+                                  unused);
+}
+
+/*! @brief AVswitches that also evaluates the Courant time step of momentumEnergy (tsKCourant over the same
+ *         vijsignal, momentum_energy_kern.hpp / sph/kernels.hpp:10-16): the step then knows dt before its last pair
+ *         kernel starts and can integrate and ship particle ranges while that kernel is still running
+ */
+template<bool Pbc, class T>
+__global__ void __launch_bounds__(kHydroBlock, 5)
+    avSwitchesCourantKernel(uint32_t first, uint32_t last, unsigned ngmax, double K, PbcBox box,
+                            const uint32_t* __restrict__ nidx, F<T> f, const PosRec<T>* __restrict__ r0,
+                            const Rec4<T>* __restrict__ r1, const Rec2<T>* __restrict__ wh, double dt, T alphamin,
+                            T alphamax, T decay_constant, float Kcour, unsigned long long* __restrict__ minDtKey)
+{
+    uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x;
+    T dt_i     = INFINITY;
+    if (i < last && (!f.active || f.active[i]))
+    {
+        T maxvsignal = 0;
+        avSwitchesBody<Pbc, true, T>(i, first, ngmax, K, box, nidx, f, r0, r1, wh, dt, alphamin, alphamax,
+                                     decay_constant, maxvsignal);
+        T v  = maxvsignal > T(0) ? maxvsignal : f.c[i];
+        dt_i = T(Kcour * f.h[i] / v);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+        dt_i = min(dt_i, __shfl_xor_sync(0xffffffffu, dt_i, o));
+    if ((threadIdx.x & 31) == 0) atomicMin(minDtKey, orderedKey(double(dt_i)));
+}
+
 // ---------------------------------------------------------------- momentum + energy (momentum_energy_kern.hpp:43-222)
 template<class T>
 __device__ __forceinline__ T avRvCorrection(T rx, T ry, T rz, T eta_ab, T eta_crit, const T* gi, const T* gj)
@@ -651,9 +717,11 @@ template<bool Pbc, bool avClean, class T>
 __global__ void __launch_bounds__(kHydroBlock, kMomentumMinBlocks)
     momentumEnergyKernel(uint32_t first, uint32_t last, unsigned ngmax, double K, PbcBox box,
                          const uint32_t* __restrict__ nidx, F<T> f, MomRecs<T> rec, const Rec2<T>* __restrict__ wh,
-                         T Atmin, T Atmax, T ramp, float Kcour, unsigned long long* __restrict__ minDtKey)
+                         T Atmin, T Atmax, T ramp, float Kcour, unsigned long long* __restrict__ minDtKey,
+                         uint32_t begin)
 {
-    uint32_t i  = first + blockIdx.x * blockDim.x + threadIdx.x;
+    // targets [begin, last); the lists are addressed relative to first (begin - first is a multiple of the block size)
+    uint32_t i  = begin + blockIdx.x * blockDim.x + threadIdx.x;
     T dt_i      = INFINITY;
     if (i < last && (!f.active || f.active[i]))
     {
@@ -699,7 +767,7 @@ __global__ void __launch_bounds__(kHydroBlock, kMomentumMinBlocks)
             T vxj = vj.a, vyj = vj.b, vzj = vj.c;
             if (pbcI) applyPBC(box, T(2) * hi, rx, ry, rz);
 
-            T r2_  = rx * rx + ry * ry + rz * rz;
+            T r2_  = dot3(rx, ry, rz, rx, ry, rz);
             T dist = sqrt(r2_);
 
             T vx_ij = vxi - vxj, vy_ij = vyi - vyj, vz_ij = vzi - vzj;
@@ -725,7 +793,7 @@ __global__ void __launch_bounds__(kHydroBlock, kMomentumMinBlocks)
 
             T mj = pj_.m, cj = sj.b, xmassj = sj.a, rhoj = sj.d;
 
-            T rv = rx * vx_ij + ry * vy_ij + rz * vz_ij;
+            T rv = dot3(rx, ry, rz, vx_ij, vy_ij, vz_ij);
             if (avClean)
             {
                 Rec4<T> ga = ldRec(rec.r5, j);
@@ -743,7 +811,7 @@ __global__ void __launch_bounds__(kHydroBlock, kMomentumMinBlocks)
                 viscosity_ij = -vij_signal * wij;
             }
 
-            T vijsignal = T(0.5) * (ci + cj) - T(2) * wij;
+            T vijsignal = courantSignal(ci, cj, wij);
             maxvsignali = (vijsignal > maxvsignali) ? vijsignal : maxvsignali;
 
             // Atwood = |rho_i - rho_j| / (rho_i + rho_j) selects the branch; the quotient itself is only needed inside
@@ -1030,6 +1098,16 @@ __global__ void __launch_bounds__(256)
     f.du_m1[i]   = T(du);
 }
 
+//! @brief out[i] = updateH(ng0, nc[i], h[i]) for a range (update_h.hpp:12-24), h itself untouched
+template<class T>
+__global__ void __launch_bounds__(256)
+    updateHRangeKernel(uint32_t first, uint32_t last, unsigned ng0, const uint32_t* __restrict__ nc,
+                       const T* __restrict__ h, T* __restrict__ out)
+{
+    uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < last) out[i] = updateHT(ng0, nc[i], h[i]);
+}
+
 //! @brief updateSmoothingLengthGpuKernel (update_h_gpu.cu:39-50)
 template<class T>
 __global__ void __launch_bounds__(256)
@@ -1159,28 +1237,47 @@ static void packMomentum(sphb200_ctx* ctx, const sphb200_fields& f, MomRecs<T>& 
     rec.r4 = m4;
 }
 
+/*! @brief momentumEnergy for the targets [begin, end) of [first, last)
+ *
+ * pack: (re)build the gather records from the current field arrays.  A caller that integrates particle ranges between
+ * launches (sphb200_momentum_energy_range) packs with the first range only: later ranges must still see the
+ * pre-integration state of their neighbors, which is what the records hold.
+ */
 template<class T>
-static void launchMomentum(sphb200_ctx* ctx, uint32_t first, uint32_t last, const sphb200_box* box,
-                           const sphb200_hydro_const* hc, const uint32_t* neighbors, const sphb200_fields* f,
-                           const Rec2<T>* wh)
+static void launchMomentum(sphb200_ctx* ctx, uint32_t first, uint32_t begin, uint32_t end, bool pack,
+                           const sphb200_box* box, const sphb200_hydro_const* hc, const uint32_t* neighbors,
+                           const sphb200_fields* f, const Rec2<T>* wh)
 {
     MomRecs<T> rec;
-    rec.r0 = static_cast<const PosRec<T>*>(ensureRec<T>(ctx, R_POS, *f));
-    rec.r3 = static_cast<const Rec4<T>*>(ensureRec<T>(ctx, R_CA, *f));
-    packMomentum<T>(ctx, *f, rec);
+    size_t n = f->n;
+    if (pack)
+    {
+        rec.r0 = static_cast<const PosRec<T>*>(ensureRec<T>(ctx, R_POS, *f));
+        rec.r3 = static_cast<const Rec4<T>*>(ensureRec<T>(ctx, R_CA, *f));
+        packMomentum<T>(ctx, *f, rec);
+    }
+    else
+    {
+        rec.r0 = static_cast<const PosRec<T>*>(ctx->rec[R_POS].get(n * sizeof(PosRec<T>)));
+        rec.r3 = static_cast<const Rec4<T>*>(ctx->rec[R_CA].get(n * sizeof(Rec4<T>)));
+        rec.r1 = static_cast<const Rec4<T>*>(ctx->rec[R_MVEL].get(n * sizeof(Rec4<T>)));
+        rec.r2 = static_cast<const Rec4<T>*>(ctx->rec[R_MSTATE].get(n * sizeof(Rec4<T>)));
+        rec.r4 = static_cast<const Rec4<T>*>(ctx->rec[R_MCB].get(n * sizeof(Rec4<T>)));
+    }
     rec.r5 = rec.r6 = nullptr;
     if (hc->avClean)
     {
+        if (!pack) throw std::runtime_error("momentum_energy_range: avClean is not supported with unpacked ranges");
         rec.r5 = static_cast<const Rec4<T>*>(ensureRec<T>(ctx, R_GA, *f));
         rec.r6 = static_cast<const Rec4<T>*>(ensureRec<T>(ctx, R_GB, *f));
     }
     PbcBox pb = pbcBox(*box);
     bool pbc  = pb.px || pb.py || pb.pz;
-    int grid  = gridFor(last - first, kHydroBlock);
+    int grid  = gridFor(end - begin, kHydroBlock);
     auto go   = [&](auto kernel)
     {
-        SPHB200_LAUNCH(ctx, kernel, grid, kHydroBlock, 0, first, last, hc->ngmax, hc->K, pb, neighbors, scoped<T>(ctx, *f),
-                       rec, wh, T(hc->Atmin), T(hc->Atmax), T(hc->ramp), float(hc->Kcour), dtKeys(ctx));
+        SPHB200_LAUNCH(ctx, kernel, grid, kHydroBlock, 0, first, end, hc->ngmax, hc->K, pb, neighbors, scoped<T>(ctx, *f),
+                       rec, wh, T(hc->Atmin), T(hc->Atmax), T(hc->ramp), float(hc->Kcour), dtKeys(ctx), begin);
     };
     if (pbc && hc->avClean) go(momentumEnergyKernel<true, true, T>);
     else if (pbc) go(momentumEnergyKernel<true, false, T>);
@@ -1272,7 +1369,7 @@ extern "C" int sphb200_momentum_energy(sphb200_ctx* ctx, int dtype, uint32_t fir
         beginOp(ctx);
         if (hc->avClean && !f->dV11) throw std::runtime_error("momentum_energy: avClean requires dV11..dV33");
         DISPATCH(dtype, const Rec2<T>* wh; const Rec4<T>* whq; ensureTables<T>(ctx, hc, wh, whq);
-                 launchMomentum<T>(ctx, first, last, box, hc, neighbors, f, wh););
+                 launchMomentum<T>(ctx, first, first, last, true, box, hc, neighbors, f, wh););
     }
     if (minDtCourant_h)
     {
@@ -1281,6 +1378,39 @@ extern "C" int sphb200_momentum_energy(sphb200_ctx* ctx, int dtype, uint32_t fir
         SPHB200_CUDA(cudaStreamSynchronize(ctx->stream));
         *minDtCourant_h = fromOrderedKey(key);
     }
+    SPHB200_CATCH
+}
+
+extern "C" int sphb200_momentum_energy_range(sphb200_ctx* ctx, int dtype, uint32_t first, uint32_t last, uint32_t begin,
+                                             uint32_t end, int pack, const sphb200_box* box,
+                                             const sphb200_hydro_const* hc, const uint32_t* neighbors,
+                                             const sphb200_fields* f)
+{
+    SPHB200_TRY
+    if (begin < first || end > last || (begin - first) % kHydroBlock != 0)
+        throw std::runtime_error("momentum_energy_range: [begin,end) must lie in [first,last), begin - first a multiple of 128");
+    if (end <= begin) return 0;
+    beginOp(ctx);
+    DISPATCH(dtype, const Rec2<T>* wh; const Rec4<T>* whq; ensureTables<T>(ctx, hc, wh, whq);
+             launchMomentum<T>(ctx, first, begin, end, pack != 0, box, hc, neighbors, f, wh););
+    SPHB200_CATCH
+}
+
+extern "C" int sphb200_av_switches_courant(sphb200_ctx* ctx, int dtype, uint32_t first, uint32_t last,
+                                           const sphb200_box* box, const sphb200_hydro_const* hc,
+                                           const uint32_t* neighbors, const sphb200_fields* f)
+{
+    SPHB200_TRY
+    if (hc->avClean) throw std::runtime_error("av_switches_courant: not available with avClean (rv needs grad v)");
+    SPHB200_LAUNCH(ctx, initCourantKeyKernel, 1, 1, 0, dtKeys(ctx));
+    if (last <= first) return 0;
+    beginOp(ctx);
+    DISPATCH(dtype, const Rec2<T>* wh; const Rec4<T>* whq; ensureTables<T>(ctx, hc, wh, whq);
+             auto* r0 = static_cast<const PosRec<T>*>(ensureRec<T>(ctx, R_PDIVV, *f));
+             auto* r1 = static_cast<const Rec4<T>*>(ensureRec<T>(ctx, R_VV, *f));
+             LAUNCH_PBC(ctx, *box, avSwitchesCourantKernel, gridFor(last - first, kHydroBlock), first, last, hc->ngmax,
+                        hc->K, pbcBox(*box), neighbors, scoped<T>(ctx, *f), r0, r1, wh, hc->minDt, T(hc->alphamin),
+                        T(hc->alphamax), T(hc->decay_constant), float(hc->Kcour), dtKeys(ctx)););
     SPHB200_CATCH
 }
 
@@ -1366,5 +1496,15 @@ extern "C" int sphb200_update_h_groups(sphb200_ctx* ctx, int dtype, const sphb20
     DISPATCH(dtype, SPHB200_LAUNCH(ctx, updateHGroupsKernel<T>, grid, 256, 0, grp->groupStart, grp->groupEnd,
                                    grp->numGroups, ng0, nc, static_cast<T*>(h)););
     ctx->packValid = 0;
+    SPHB200_CATCH
+}
+
+extern "C" int sphb200_update_h_into(sphb200_ctx* ctx, int dtype, uint32_t first, uint32_t last, unsigned ng0,
+                                     const uint32_t* nc, const void* h, void* hNew)
+{
+    SPHB200_TRY
+    if (last <= first) return 0;
+    DISPATCH(dtype, SPHB200_LAUNCH(ctx, updateHRangeKernel<T>, gridFor(last - first, 256), 256, 0, first, last, ng0, nc,
+                                   static_cast<const T*>(h), static_cast<T*>(hNew)););
     SPHB200_CATCH
 }

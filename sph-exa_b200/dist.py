@@ -20,6 +20,7 @@ import ctypes as C
 import json
 import math
 import os
+import sys
 import time
 
 import numpy as np
@@ -586,6 +587,7 @@ def bench_main(args, pkg, METRIC, UNIT, ALGO_BYTES, load_peaks, ClockSampler):
     for _ in range(args.warmup):
         sim.step()
     barrier()
+    sim.sync_times = {}
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
@@ -675,6 +677,11 @@ def bench_main(args, pkg, METRIC, UNIT, ALGO_BYTES, load_peaks, ClockSampler):
             "e2e": e2e, "cpu_baseline": None,
         }
         print(json.dumps(line), flush=True)
+        if sim._sync_profile:
+            calls = args.steps + reps + (0 if e2e is None else 1 + e2e["steps"])
+            print("sync profile (ms per call): " + json.dumps({k: round(v / calls * 1e3, 3)
+                                                                 for k, v in sim.sync_times.items()}),
+                  file=sys.stderr, flush=True)
     barrier()
     dist.destroy_process_group()
     return 0
