@@ -257,6 +257,13 @@ int sphb200_turb_drive(sphb200_turb*, sphb200_ctx*, int dtype, uint32_t first, u
 int sphb200_conserved_quantities(sphb200_ctx*, int dtype, uint32_t first, uint32_t last,
                                  const sphb200_hydro_const* hc_h, const sphb200_fields* f_h, double* out_h);
 double* sphb200_conserved_device_ptr(sphb200_ctx*);
+/* localMachSquareSum / machSquareSumGpu (main/src/observables/turbulence_mach_rms.hpp:38-56, gpu_reductions.cu:110-122):
+ * sum over [first,last) of |v|^2 / c^2 (c as left by sphb200_eos); the RMS Mach number of TurbulenceMachRMS is
+ * sqrt(sum over ranks / numParticlesGlobal) (:70-83).  Fixed-order fp64 reduction; the sum also stays on the device
+ * (sphb200_mach_device_ptr) for an in-stream all-reduce. */
+int sphb200_mach_square_sum(sphb200_ctx*, int dtype, uint32_t first, uint32_t last, const sphb200_fields* f_h,
+                            double* out_h);
+double* sphb200_mach_device_ptr(sphb200_ctx*);
 
 /* The pair operators gather neighbor data from packed copies ("gather records") of the field arrays kept in the
  * context.  Stand-alone operator calls repack on every call; a sphb200_sim reuses them across operators and
@@ -327,6 +334,9 @@ int sphb200_sim_download(sphb200_sim*, const sphb200_fields* host_fields, uint64
 int sphb200_sim_attach_turbulence(sphb200_sim*, sphb200_turb*);
 /* computeConservedQuantities for the owned particles (see sphb200_conserved_quantities) */
 int sphb200_sim_conserved(sphb200_sim*, double* out10_h);
+/* TurbulenceMachRMS::computeAndWrite for one rank: sqrt(machSquareSum / numParticlesGlobal); numParticlesGlobal = 0:
+ * the owned count */
+int sphb200_sim_mach_rms(sphb200_sim*, uint64_t numParticlesGlobal, double* out_h);
 /* One time step on host-resident state: same results as upload + step + download, with the PCIe transfers staged
  * beside the kernels ({x,y,z} first, {h,m,temp} next, the rest behind the neighbor search; m and alpha return while
  * MomentumEnergy runs).  host_in/host_out: all 14 conserved fields, pinned memory for overlap.  Single rank only. */

@@ -239,3 +239,17 @@ def stirring(first, last, x, y, z, ax, ay, az, modes, pr, pi, amplitudes, sol_we
     """computeStirring (hydro_turb/stirring.hpp:99-122), in place on ax, ay, az (float64)"""
     lib().orc_stirring(C.c_uint32(first), C.c_uint32(last), P(x), P(y), P(z), P(ax), P(ay), P(az), int(amplitudes.size),
                        P(modes), P(pr), P(pi), P(amplitudes), C.c_double(sol_weight_norm))
+
+
+def mach_square_sum(vx, vy, vz, c):
+    """localMachSquareSum (main/src/observables/turbulence_mach_rms.hpp:38-56): sum of norm2(V) / (c*c) with V in
+    double and c*c in the storage type of c.  Restated (5 lines): the header pulls in sph/particles_data.hpp, which
+    does not compile in this fork (stray #endif, :270), so it cannot be built into oracle/_ref; no reference test
+    holds a value for it (parity unpinned)."""
+    v2 = vx.astype(np.float64) ** 2 + vy.astype(np.float64) ** 2 + vz.astype(np.float64) ** 2
+    return float(np.sum(v2 / (c * c).astype(np.float64)))
+
+
+def mach_rms(vx, vy, vz, c, num_particles_global):
+    """calculateMachRMS (turbulence_mach_rms.hpp:70-83), one rank"""
+    return float(np.sqrt(mach_square_sum(vx, vy, vz, c) / num_particles_global))

@@ -117,7 +117,8 @@ SYMBOLS = [
     "sphb200_drift_positions", "sphb200_compute_positions_groups", "sphb200_update_h_groups",
     "sphb200_sim_bdt_enable", "sphb200_sim_bdt_compute_forces", "sphb200_sim_bdt_integrate", "sphb200_sim_bdt_step",
     "sphb200_sim_bdt_info", "sphb200_sim_bdt_rungs", "sphb200_sim_bdt_group_dt", "sphb200_sim_bdt_active",
-    "sphb200_sim_bdt_groups", "sphb200_momentum_energy_range", "sphb200_av_switches_courant", "sphb200_update_h_into",
+    "sphb200_sim_bdt_groups", "sphb200_momentum_energy_range", "sphb200_av_switches_courant", "sphb200_update_h_into", "sphb200_mach_square_sum", "sphb200_mach_device_ptr",
+    "sphb200_sim_mach_rms",
 ]
 
 lib.sphb200_last_error.restype = C.c_char_p
@@ -128,6 +129,9 @@ lib.sphb200_neighbors_size.argtypes = [C.c_size_t, C.c_uint]
 lib.sphb200_timestep_device_ptr.restype = vp
 lib.sphb200_conserved_device_ptr.restype = vp
 lib.sphb200_conserved_device_ptr.argtypes = [vp]
+lib.sphb200_mach_device_ptr.restype = vp
+lib.sphb200_mach_device_ptr.argtypes = [vp]
+lib.sphb200_sim_mach_rms.argtypes = [vp, C.c_uint64, vp]
 lib.sphb200_timestep_device_ptr.argtypes = [vp]
 for _n in ("sphb200_sim_start_index", "sphb200_sim_end_index", "sphb200_sim_n_with_halos"):
     getattr(lib, _n).restype = C.c_uint32

@@ -78,6 +78,7 @@ extern "C" void sphb200_destroy(sphb200_ctx* ctx)
     ctx->miscTmp.release();
     ctx->nbTmp.release();
     ctx->obsTmp.release();
+    ctx->machTmp.release();
     for (auto& a : ctx->rec)
         a.release();
     ctx->tabPairs.release();
@@ -856,6 +857,17 @@ extern "C" int sphb200_sim_conserved(sphb200_sim* s, double* out10)
     sphb200_fields f       = s->table();
     sphb200_hydro_const hc = s->hydroConst();
     CHECK_RC(sphb200_conserved_quantities(s->ctx, s->cfg.dtype, s->start, s->end, &hc, &f, out10));
+    SPHB200_CATCH
+}
+
+extern "C" int sphb200_sim_mach_rms(sphb200_sim* s, uint64_t numParticlesGlobal, double* out_h)
+{
+    SPHB200_TRY
+    sphb200_fields f = s->table();
+    double sum       = 0;
+    CHECK_RC(sphb200_mach_square_sum(s->ctx, s->cfg.dtype, s->start, s->end, &f, &sum));
+    uint64_t ng = numParticlesGlobal ? numParticlesGlobal : uint64_t(s->end - s->start);
+    *out_h      = std::sqrt(sum / double(ng));
     SPHB200_CATCH
 }
 

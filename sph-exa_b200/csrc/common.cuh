@@ -84,8 +84,9 @@ struct sphb200_ctx
     cudaStream_t stream  = nullptr;
     bool ownStream       = false;
     uint64_t launches    = 0;
-    sphb200::Arena sortTmp, treeTmp, scanTmp, miscTmp, nbTmp, obsTmp;
+    sphb200::Arena sortTmp, treeTmp, scanTmp, miscTmp, nbTmp, obsTmp, machTmp;
     double* devObs = nullptr; // last result of sphb200_conserved_quantities (10 doubles, inside obsTmp)
+    double* devMach = nullptr; // last result of sphb200_mach_square_sum (1 double, inside obsTmp)
     // gather records of the pair operators (hydro.cu) and the repacked kernel tables
     static constexpr int kMaxRecs = 12;
     sphb200::Arena rec[kMaxRecs], tabPairs, tabQuads;

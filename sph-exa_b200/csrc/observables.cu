@@ -71,6 +71,45 @@ __global__ void conservedFinalKernel(const double* __restrict__ partials, int nu
     out[k] = (k == 0) ? 0.5 * v : v;
 }
 
+/*! @brief localMachSquareSum (main/src/observables/turbulence_mach_rms.hpp:38-56, machSquareSumGpu gpu_reductions.cu:
+ *         110-122): sum of |v|^2 / c^2 over the owned particles, same fixed-order reduction as above (slot 0)
+ */
+template<class T>
+__global__ void __launch_bounds__(kObsThreads)
+    machPartialsKernel(uint32_t first, uint32_t last, const T* __restrict__ vx, const T* __restrict__ vy,
+                       const T* __restrict__ vz, const T* __restrict__ c, double* __restrict__ partials)
+{
+    double acc = 0;
+    for (size_t i = size_t(first) + size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < last;
+         i += size_t(gridDim.x) * blockDim.x)
+    {
+        double V[3] = {double(vx[i]), double(vy[i]), double(vz[i])};
+        acc += (V[0] * V[0] + V[1] * V[1] + V[2] * V[2]) / (c[i] * c[i]);
+    }
+    __shared__ double sh[kObsThreads / 32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+        acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (lane == 0) sh[warp] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0)
+    {
+        double v = 0;
+        for (int w = 0; w < kObsThreads / 32; ++w)
+            v += sh[w];
+        partials[blockIdx.x] = v;
+    }
+}
+
+__global__ void machFinalKernel(const double* __restrict__ partials, int numBlocks, double* __restrict__ out)
+{
+    double v = 0;
+    for (int b = 0; b < numBlocks; ++b)
+        v += partials[b];
+    out[0] = v;
+}
+
 } // namespace sphb200
 
 using namespace sphb200;
@@ -117,3 +156,39 @@ extern "C" int sphb200_conserved_quantities(sphb200_ctx* ctx, int dtype, uint32_
 }
 
 extern "C" double* sphb200_conserved_device_ptr(sphb200_ctx* ctx) { return ctx->devObs; }
+
+extern "C" int sphb200_mach_square_sum(sphb200_ctx* ctx, int dtype, uint32_t first, uint32_t last,
+                                       const sphb200_fields* f, double* out_h)
+{
+    try
+    {
+        int grid       = last > first ? persistentGrid(last - first, kObsThreads, 4) : 1;
+        auto* partials = static_cast<double*>(ctx->machTmp.get((size_t(grid) + 2) * sizeof(double)));
+        double* out      = partials + grid;
+        if (dtype == SPHB200_F64)
+            SPHB200_LAUNCH(ctx, machPartialsKernel<double>, grid, kObsThreads, 0, first, last,
+                           static_cast<const double*>(f->vx), static_cast<const double*>(f->vy),
+                           static_cast<const double*>(f->vz), static_cast<const double*>(f->c), partials);
+        else if (dtype == SPHB200_MIXED)
+            SPHB200_LAUNCH(ctx, machPartialsKernel<float>, grid, kObsThreads, 0, first, last,
+                           static_cast<const float*>(f->vx), static_cast<const float*>(f->vy),
+                           static_cast<const float*>(f->vz), static_cast<const float*>(f->c), partials);
+        else throw std::runtime_error("unknown dtype");
+        SPHB200_LAUNCH(ctx, machFinalKernel, 1, 1, 0, partials, grid, out);
+        ctx->devMach = out;
+        if (out_h)
+        {
+            SPHB200_CUDA(cudaMemcpyAsync(ctx->hostDt + 20, out, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+            SPHB200_CUDA(cudaStreamSynchronize(ctx->stream));
+            *out_h = ctx->hostDt[20];
+        }
+        return 0;
+    }
+    catch (std::exception& e)
+    {
+        setError(e.what());
+        return 1;
+    }
+}
+
+extern "C" double* sphb200_mach_device_ptr(sphb200_ctx* ctx) { return ctx->devMach; }

@@ -468,3 +468,33 @@ def updateSmoothingLengthGroups(ctx, grp_view, ng0, nc, h):
     """updateSmoothingLengthGpu (sph/include/sph/update_h_gpu.cu:39-60)"""
     check(lib.sphb200_update_h_groups(ctx.h, B.F64 if h.dtype == torch.float64 else B.MIXED, C.byref(grp_view),
                                       C.c_uint(ng0), ptr(nc), ptr(h)))
+
+
+# ---------------------------------------------------------------- early Courant step / ranged last stage
+def computeAVswitchesCourant(ctx, first, last, d, box, hc, nb):
+    """AVswitches that also leaves momentumEnergy's Courant step on the device (read it with computeTimestep)"""
+    f = fields_struct(d)
+    check(lib.sphb200_av_switches_courant(ctx.h, _dt(d), C.c_uint32(first), C.c_uint32(last), C.byref(box),
+                                          C.byref(hc), ptr(nb), C.byref(f)))
+
+
+def computeMomentumEnergyRange(ctx, first, last, begin, end, pack, d, box, hc, nb):
+    """momentumEnergy for the targets [begin,end) of [first,last); pack=False reuses the previous call's records"""
+    f = fields_struct(d)
+    check(lib.sphb200_momentum_energy_range(ctx.h, _dt(d), C.c_uint32(first), C.c_uint32(last), C.c_uint32(begin),
+                                            C.c_uint32(end), int(bool(pack)), C.byref(box), C.byref(hc), ptr(nb),
+                                            C.byref(f)))
+
+
+def updateSmoothingLengthInto(ctx, first, last, ng0, nc, h, h_new):
+    """h_new[i] = updateH(ng0, nc[i], h[i]) for [first,last), h untouched"""
+    check(lib.sphb200_update_h_into(ctx.h, B.F64 if h.dtype == torch.float64 else B.MIXED, C.c_uint32(first),
+                                    C.c_uint32(last), C.c_uint(ng0), ptr(nc), ptr(h), ptr(h_new)))
+
+
+def machSquareSum(ctx, first, last, d):
+    """localMachSquareSum (main/src/observables/turbulence_mach_rms.hpp:38-56) over [first,last)"""
+    f = fields_struct(d)
+    out = C.c_double(0)
+    check(lib.sphb200_mach_square_sum(ctx.h, _dt(d), C.c_uint32(first), C.c_uint32(last), C.byref(f), C.byref(out)))
+    return out.value

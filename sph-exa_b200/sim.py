@@ -121,6 +121,12 @@ class HydroVeProp:
         check(lib.sphb200_sim_conserved(self.h, out))
         return ops.conserved_dict(list(out))
 
+    def machRMS(self, num_particles_global=0):
+        """TurbulenceMachRMS (main/src/observables/turbulence_mach_rms.hpp:70-83): sqrt(sum |v|^2/c^2 / N)"""
+        out = C.c_double(0)
+        check(lib.sphb200_sim_mach_rms(self.h, C.c_uint64(num_particles_global), C.byref(out)))
+        return out.value
+
     def download_into(self, f_struct):
         check(lib.sphb200_sim_download(self.h, C.byref(f_struct), None))
 

@@ -368,3 +368,94 @@ def test_conserved_quantities(pkg, ctx, ref, real):
         assert abs(got[name] - want[6 + k]) <= tol * mv * float(np.abs(f["x"]).max())
     assert got["ncsum"] == float(nc[first:last].sum())
     assert got["etot"] == got["ecin"] + got["eint"]
+
+
+@pytest.mark.parametrize("real", [np.float64, np.float32])
+@pytest.mark.parametrize("case,side", [("sedov", 20), ("noh", 24)])
+def test_early_courant_and_ranged_momentum(pkg, ctx, ref, real, case, side):
+    """the operator-level pieces of sphb200_sim_step_host's schedule: AVswitches + Courant == AVswitches followed by
+    momentumEnergy's Courant step (bit for bit) and == the reference's value; momentumEnergy in ranges with the
+    finished ranges integrated in between == one launch followed by one position update (bit for bit)"""
+    import torch
+    from sph_exa_b200 import ops
+    sim, pre, pre_dt, box, s = ref_state(pkg, case, side, real, 2)
+    n, ngmax = sim.n, sim.ngmax
+    b = pkg.make_box(*sim.box)
+    nb = slab_from_rowmajor(ctx, sim.nb, sim.nc, ngmax)
+    wh, whd = to_dev(sim.wh), to_dev(sim.whd)
+    hc = ops.hydro_const(sim.K, wh, whd, gamma=s["gamma"], muiConst=s["mui"], Kcour=s.get("Kcour", 0.2),
+                         minDt=pre_dt[0], minDt_m1=pre_dt[1])
+
+    def state():
+        d = device_fields(sim, ALL, real)
+        d["du"] = to_dev(sim.f["du"])
+        d["alpha"] = to_dev(sim.alpha_pre)
+        return d
+
+    one = state()
+    ops.computeAVswitches(ctx, 0, n, one, b, hc, nb)
+    dt_mom = ops.computeMomentumEnergy(ctx, 0, n, one, b, hc, nb)
+    dts_one = ops.computeTimestep(ctx, 0, n, one, hc)
+
+    two = state()
+    ops.computeAVswitchesCourant(ctx, 0, n, two, b, hc, nb)
+    dts_two = ops.computeTimestep(ctx, 0, n, two, hc)
+    assert dts_two == dts_one and dts_two[0] == dt_mom
+    assert abs(dt_mom - sim.minDtCourant) <= TOL[real] * sim.minDtCourant
+    assert np.array_equal(to_host(two["alpha"]), to_host(one["alpha"]))
+
+    # ranged: uneven ranges (multiples of 128 from `first`), each integrated before the next one starts
+    first, last = 128, n - 5
+    ref_run = state()
+    ops.computeAVswitches(ctx, first, last, ref_run, b, hc, nb[first // 32 * ngmax * 32:].contiguous())
+    nb1 = nb[first // 32 * ngmax * 32:].contiguous()
+    ref_run["nc"] = one["nc"]
+    ops.computeMomentumEnergy(ctx, first, last, ref_run, b, hc, nb1)
+    dt, dt_m1 = 0.9 * pre_dt[0], pre_dt[0]
+    ops.computePositionsAndH(ctx, first, last, ref_run, b, hc, dt, dt_m1)
+
+    rng_run = state()
+    ops.computeAVswitches(ctx, first, last, rng_run, b, hc, nb1)
+    cuts = [first, first + 128, first + 128 * 9, first + 128 * 10, last]
+    for k, (rb, re) in enumerate(zip(cuts[:-1], cuts[1:])):
+        ops.computeMomentumEnergyRange(ctx, first, last, rb, re, k == 0, rng_run, b, hc, nb1)
+        ops.computePositionsAndH(ctx, rb, re, rng_run, b, hc, dt, dt_m1)
+    for k in ("x", "y", "z", "vx", "vy", "vz", "x_m1", "temp", "du_m1", "h", "ax", "ay", "az", "du"):
+        assert np.array_equal(to_host(rng_run[k]), to_host(ref_run[k])), k
+    with pytest.raises(pkg.binding.SphError):
+        ops.computeMomentumEnergyRange(ctx, first, last, first + 7, last, True, rng_run, b, hc, nb1)
+
+    # next-step h into a separate array
+    h_new = torch.full_like(one["h"], -1.0)
+    ops.updateSmoothingLengthInto(ctx, first, last, sim.ng0, one["nc"], one["h"], h_new)
+    got = to_host(h_new)
+    assert np.array_equal(got[first:last], to_host(ref_run["h"])[first:last])
+    assert np.all(got[:first] == -1.0) and np.all(got[last:] == -1.0)
+    assert np.array_equal(to_host(one["h"]), sim.f["h"].astype(real))
+
+
+@pytest.mark.parametrize("real", [np.float64, np.float32])
+def test_mach_rms(pkg, ctx, ref, real):
+    """machSquareSumGpu / TurbulenceMachRMS against the restated localMachSquareSum; run-to-run reproducible"""
+    from oracle import orc
+    from sph_exa_b200 import ops, sim as S
+    sim, pre, pre_dt, box, s = ref_state(pkg, "turbulence", 20, real, 2)
+    n = sim.n
+    d = device_fields(sim, ["x", "h", "vx", "vy", "vz", "c"], real)
+    first, last = 37, n - 11
+    want = orc.mach_square_sum(*(sim.f[k][first:last] for k in ("vx", "vy", "vz", "c")))
+    got = ops.machSquareSum(ctx, first, last, d)
+    assert abs(got - want) <= (1e-13 if real == np.float64 else 1e-6) * want
+    assert ops.machSquareSum(ctx, first, last, d) == got
+    assert ops.machSquareSum(ctx, 5, 5, d) == 0.0
+    # through the sim: after a step, c holds the EOS sound speed of that step
+    f, box, st = pkg.ic.CASES["turbulence"](16, "f64" if real == np.float64 else "mixed")
+    gs = S.HydroVeProp(ctx, box, st, capacity=f["x"].size, dtype=pkg.F64 if real == np.float64 else pkg.MIXED)
+    gs.upload(f)
+    gs.step()
+    gs.step()
+    out = gs.download(names=["vx", "vy", "vz", "c"])
+    want = orc.mach_rms(out["vx"], out["vy"], out["vz"], out["c"], f["x"].size)
+    assert abs(gs.machRMS() - want) <= 1e-6 * want
+    assert abs(gs.machRMS(8 * f["x"].size) - want / np.sqrt(8)) <= 1e-6 * want
+    gs.close()
