@@ -1,0 +1,18 @@
+#!/bin/bash
+# Profile capture of the bench workload (Sedov 200^3, f64, 1 B200), run on the GPU box through gpurun:
+#   gpurun --timeout 1500 -- 'bash profiles/capture.sh r01e'
+# Writes gpurun_out/launches_<tag>.csv (every launch with its device time), gpurun_out/full_<tag>.ncu-rep (ncu --set
+# full of one launch of each pair kernel + the neighbor search, 4th step) and gpurun_out/courant_<tag>.ncu-rep (the
+# AVswitches+Courant kernel of sphb200_sim_step_host).  profiles/summarize.py turns them into the committed summaries.
+set -u
+TAG=${1:-r01e}
+CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-bdt"
+$CMD --no-e2e > gpurun_out/plain_$TAG.log 2>&1 || exit 1
+ncu --metrics gpu__time_duration.sum --clock-control none -c 700 --csv --log-file gpurun_out/launches_$TAG.csv \
+    $CMD --no-e2e > gpurun_out/ncu_launches_$TAG.log 2>&1
+ncu --set full --clock-control none --import-source on \
+    -k regex:'findNeighborsKernel|xmassKernel|veDefGradhKernel|iadDivvCurlvKernel|avSwitchesKernel|momentumEnergyKernel' \
+    --launch-skip 18 -c 6 -f -o gpurun_out/full_$TAG $CMD --no-e2e > gpurun_out/ncu_full_$TAG.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:'avSwitchesCourantKernel' --launch-skip 1 -c 1 \
+    -f -o gpurun_out/courant_$TAG $CMD > gpurun_out/ncu_courant_$TAG.log 2>&1
+ls -la gpurun_out/*.ncu-rep

@@ -167,7 +167,14 @@ class DistHydroVeProp:
             self.sync_times[name] = self.sync_times.get(name, 0.0) + (now - self._st0)
         self._st0 = now
 
-    def sync(self):
+    def sync(self, lazy=False):
+        """cstone::Domain::sync (domain/domain.hpp:196-244).  lazy: leave the fields that nothing needs before EOS
+        un-reordered until _finish_reorder() (computeForces does that)"""
+        self._sync_impl()
+        if not lazy:
+            self._finish_reorder()
+
+    def _sync_impl(self):
         t, ops, dist, f = self.torch, self.ops, self.dist, self.f
         P, me = self.world, self.rank
         self._st(None)
@@ -189,7 +196,9 @@ class DistHydroVeProp:
         # the reorder of the fields is deferred until the halo layout is known, so that it can write straight into the
         # [halos | owned | halos] arrays; only h is needed before that (halo discovery)
         pending = dict(f) if P > 1 else None
+        self._late = None
         if P > 1:
+            self._wait_upload("h")
             f["h"] = ops.gatherGpu(self.ctx, perm, [f["h"]])[0]
         else:
             out = ops.gatherGpu(self.ctx, perm, [f[k] for k in self.CONSERVED])
@@ -219,6 +228,8 @@ class DistHydroVeProp:
             moved = sum(mat[q][r] for q in range(P) for r in range(P) if q != r)
             self._st("assignment")
             if moved:
+                self._wait_upload("m")
+                self._wait_upload("late")
                 out = ops.gatherGpu(self.ctx, perm, [pending[k] for k in self.CONSERVED])
                 for k, a in zip(self.CONSERVED, out):
                     f[k] = a
@@ -318,11 +329,15 @@ class DistHydroVeProp:
         self._st("send lists")
         # 6. grow every conserved field to [halos | owned | halos]; exchange x,y,z,h,m (setupHalos, domain.hpp:512-529)
         if pending is not None:
-            srcs = [pending[k] for k in self.CONSERVED]
+            # only what the halo discovery, the search and XMass need is reordered now; the other fields follow right
+            # before their first use (_finish_reorder), by which time a host-resident caller has them uploaded
+            self._wait_upload("m")
+            srcs = [pending[k] for k in self.EARLY]
             grown = [t.empty(self.n_total, dtype=a.dtype, device=self.dev) for a in srcs]
             ops.gatherGpu(self.ctx, perm, srcs, [g[self.start:self.end] for g in grown])
-            for k, g in zip(self.CONSERVED, grown):
+            for k, g in zip(self.EARLY, grown):
                 f[k] = g
+            self._late = (perm, pending, self.start, self.end, self.n_total)
         else:
             for k in self.CONSERVED:
                 a = t.empty(self.n_total, dtype=f[k].dtype, device=self.dev)
@@ -342,6 +357,29 @@ class DistHydroVeProp:
         self.stree = self._update_tree(self.stree, self.all_keys, self.bucket_focus, False)
         self.tree = ops.Octree(self.ctx, self.stree[0], self.box, self.stree[1])
         self._st("search tree")
+
+    EARLY = ["x", "y", "z", "h", "m"]
+
+    def _wait_upload(self, name):
+        """step_host: make the compute stream wait for the upload group `name` (no-op otherwise)"""
+        ev = getattr(self, "_upload_events", {}).pop(name, None)
+        if ev is not None:
+            self.torch.cuda.current_stream().wait_event(ev)
+
+    def _finish_reorder(self):
+        """reorder of the conserved fields that sync() deferred, into the [halos | owned | halos] arrays"""
+        if getattr(self, "_late", None) is None:
+            return
+        t, ops, f = self.torch, self.ops, self.f
+        perm, pending, a, b, n = self._late
+        self._late = None
+        self._wait_upload("late")
+        keys = [k for k in self.CONSERVED if k not in self.EARLY]
+        srcs = [pending[k] for k in keys]
+        grown = [t.empty(n, dtype=x.dtype, device=self.dev) for x in srcs]
+        ops.gatherGpu(self.ctx, perm, srcs, [g[a:b] for g in grown])
+        for k, g in zip(keys, grown):
+            f[k] = g
 
     def exchange_halos(self, names):
         """haloExchangeGpu (halos/exchange_halos_gpu.cuh:50-143): pack ranges per peer with one kernel, one NCCL
@@ -366,7 +404,7 @@ class DistHydroVeProp:
         t, ops, f = self.torch, self.ops, self.f
         T = self._tick
         T(None)
-        self.sync()
+        self.sync(lazy=True)
         T("domain::sync")
         n, a, b = self.n_total, self.start, self.end
         for k in self.DEPENDENT:
@@ -384,6 +422,7 @@ class DistHydroVeProp:
         T("halo")
         ops.computeVeDefGradh(self.ctx, a, b, f, self.box, hc, self.nb)
         T("Normalization & Gradh")
+        self._finish_reorder()
         ops.computeEOS(self.ctx, a, b, f, hc)
         T("EquationOfState")
         self.exchange_halos(["vx", "vy", "vz", "prho", "c", "kx"])
@@ -440,6 +479,102 @@ class DistHydroVeProp:
     def step(self):
         self.computeForces()
         self.integrate()
+
+    def step_host(self, host, n_in, ranges=16):
+        """one step on host-resident state: `host[k]` are pinned tensors holding this rank's n_in owned particles; on
+        return they hold the (possibly different number of) owned particles after the step.  Returns that number.
+
+        Same schedule as sphb200_sim_step_host (api.cu) with the halo exchanges in between: uploads in order of first
+        use on a copy stream, m / next-step h / alpha sent back as soon as they are final, the Courant step evaluated
+        with AVswitches and all-reduced before momentumEnergy, which then runs range by range with each range
+        integrated and sent back while the next one computes.  Results are bit-identical to upload + step + download."""
+        t, ops, f, dist, B = self.torch, self.ops, self.f, self.dist, self.B
+        cur = t.cuda.current_stream()
+        if not hasattr(self, "_copy_in"):
+            self._copy_in, self._copy_out = t.cuda.Stream(), t.cuda.Stream()
+        cin, cout = self._copy_in, self._copy_out
+        late = [k for k in self.CONSERVED if k not in self.EARLY]
+        groups = [("xyz", ["x", "y", "z"]), ("h", ["h"]), ("m", ["m"]), ("late", late)]
+        cin.wait_stream(cur)
+        cout.wait_stream(cur)
+        events = {}
+        with t.cuda.stream(cin):
+            for name, keys in groups:
+                for k in keys:
+                    f[k] = host[k][:n_in].to(self.dev, non_blocking=True)
+                    f[k].record_stream(cur)
+                events[name] = cin.record_event()
+        cout.wait_event(events["late"])  # the host buffers are reused for the results
+        cur.wait_event(events.pop("xyz"))
+        self._upload_events = events
+
+        def send(k, src, lo, hi):
+            """host[k][lo:hi] <- src, once everything issued so far on the compute stream is done"""
+            ev = cur.record_event()
+            with t.cuda.stream(cout):
+                cout.wait_event(ev)
+                host[k][lo:hi].copy_(src, non_blocking=True)
+                src.record_stream(cout)
+
+        self.sync(lazy=True)
+        n, a, b = self.n_total, self.start, self.end
+        n_own = b - a
+        if any(host[k].numel() < n_own for k in self.CONSERVED):
+            raise RuntimeError("step_host: host buffers too small for the particles this rank owns now")
+        if self.world == 1:
+            self._finish_reorder()
+        send("m", f["m"][a:b], 0, n_own)
+        for k in self.DEPENDENT:
+            f[k] = t.zeros(n, dtype=self.real_t, device=self.dev)
+        f["du"] = t.zeros(n, dtype=t.float64, device=self.dev)
+        f["nc"] = t.zeros(n, dtype=t.int32, device=self.dev)
+        hc = self._hc()
+        self.nb, nc, self.fails = ops.findNeighbors(self.ctx, self.tree, f["x"], f["y"], f["z"], f["h"], a, b, self.box,
+                                                    self.ng0, self.ngmax, True)
+        f["nc"][a:b] = nc
+        h_new = t.empty_like(f["h"])
+        ops.updateSmoothingLengthInto(self.ctx, a, b, self.ng0, f["nc"], f["h"], h_new)
+        send("h", h_new[a:b], 0, n_own)
+        ops.computeXMass(self.ctx, a, b, f, self.box, hc, self.nb)
+        self.exchange_halos(["xm"])
+        ops.computeVeDefGradh(self.ctx, a, b, f, self.box, hc, self.nb)
+        self._finish_reorder()
+        ops.computeEOS(self.ctx, a, b, f, hc)
+        self.exchange_halos(["vx", "vy", "vz", "prho", "c", "kx"])
+        ops.computeIadDivvCurlv(self.ctx, a, b, f, self.box, hc, self.nb)
+        self.exchange_halos(["c11", "c12", "c13", "c22", "c23", "c33", "divv"])
+        ops.computeAVswitchesCourant(self.ctx, a, b, f, self.box, hc, self.nb)
+        # computeTimestep (ts_global.hpp:96-112) before the last pair kernel
+        f_struct = ops.fields_struct(f)
+        B.check(B.lib.sphb200_timestep(self.ctx.h, self.dtype, C.c_uint32(a), C.c_uint32(b), C.byref(hc),
+                                       C.byref(f_struct), None))
+        dt_dev = self._dt_view(B.lib.sphb200_timestep_device_ptr(self.ctx.h))
+        if self.world > 1:
+            dist.all_reduce(dt_dev[2:3], op=dist.ReduceOp.MIN, group=self.group)
+        dt = float(dt_dev[2].item())
+        self.ttot += dt
+        self.minDt_m1, self.minDt = self.minDt, dt
+        send("alpha", f["alpha"][a:b], 0, n_own)
+        self.exchange_halos(["alpha"])
+        rest = [k for k in self.CONSERVED if k not in ("m", "h", "alpha")]
+        per = ((n_own + ranges - 1) // ranges + 127) // 128 * 128
+        for r in range(ranges):
+            rb, re = min(b, a + r * per), min(b, a + (r + 1) * per)
+            if re <= rb:
+                break
+            ops.computeMomentumEnergyRange(self.ctx, a, b, rb, re, r == 0, f, self.box, hc, self.nb)
+            ops.computePositionsAndH(self.ctx, rb, re, f, self.box, hc, self.minDt, self.minDt_m1)
+            ev = cur.record_event()
+            with t.cuda.stream(cout):
+                cout.wait_event(ev)
+                for k in rest:
+                    host[k][rb - a:re - a].copy_(f[k][rb:re], non_blocking=True)
+        for k in self.CONSERVED:
+            f[k].record_stream(cout)
+            f[k] = f[k][a:b]
+        cout.synchronize()
+        self._upload_events = {}
+        return n_own
 
     def conserved(self):
         """computeConservedQuantities (conserved_quantities.hpp:113-180): local fp64 reduction on the device, then one
@@ -633,17 +768,10 @@ def bench_main(args, pkg, METRIC, UNIT, ALGO_BYTES, load_peaks, ClockSampler):
                 barrier()
                 h2d = d2h = 0
                 t0 = time.perf_counter()
-            for k in sim.CONSERVED:
-                sim.f[k] = host[k][:n_h].to(sim.dev, non_blocking=True)
-                h2d += n_h * host[k].element_size()
-            sim.step()
-            n_h = sim.end - sim.start
-            if n_h > cap:
-                raise RuntimeError("e2e host buffers too small")
-            for k in sim.CONSERVED:
-                host[k][:n_h].copy_(sim.f[k][:n_h], non_blocking=True)
-                d2h += n_h * host[k].element_size()
-            torch.cuda.synchronize()
+            esz = sum(host[k].element_size() for k in sim.CONSERVED)
+            h2d += n_h * esz
+            n_h = sim.step_host(host, n_h)
+            d2h += n_h * esz
         barrier()
         dt_e = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
         dist.all_reduce(dt_e, op=dist.ReduceOp.MAX)

@@ -82,6 +82,34 @@ def main():
             if bad or abs(sim.minDt - ref_sim.minDt) > 1e-12 * ref_sim.minDt:
                 ok = False
                 print("MISMATCH", bad, flush=True)
+    # ---- step_host (host-resident state, overlapped transfers) == upload + step + download, bit for bit
+    own = sim.download_owned()
+    n_own = len(own["x"])
+    sim_a = D.DistHydroVeProp(pkg, ctx, box, s, B.F64, rank, world, n)
+    sim_b = D.DistHydroVeProp(pkg, ctx, box, s, B.F64, rank, world, n)
+    for q in (sim_a, sim_b):
+        q.upload(own)
+        q.minDt, q.minDt_m1, q.ttot = sim.minDt, sim.minDt_m1, sim.ttot
+    cap = int(n_own * 1.3) + 1024
+    host = {k: torch.empty(cap, dtype=sim_b.f[k].dtype).pin_memory() for k in sim_b.CONSERVED}
+    for k in sim_b.CONSERVED:
+        host[k][:n_own].copy_(sim_b.f[k])
+    n_h = n_own
+    same = True
+    for _ in range(2):
+        sim_a.step()
+        n_h = sim_b.step_host(host, n_h)
+        want_a = sim_a.download_owned()
+        same = same and n_h == len(want_a["x"]) and sim_a.minDt == sim_b.minDt and sim_a.ttot == sim_b.ttot
+        for k in sim_b.CONSERVED:
+            same = same and np.array_equal(host[k][:n_h].numpy(), want_a[k])
+    flags = [None] * world
+    dist.all_gather_object(flags, bool(same))
+    if rank == 0:
+        print(f"step_host == step on {world} ranks, bit-identical per rank: {flags}", flush=True)
+    ok = ok and all(flags)
+    del sim_a, sim_b, host
+
     # ---- restart: dump, reload on the same ranks (bit-identical continuation) and on one rank (same particles)
     import tempfile
     base = [tempfile.mkdtemp(prefix="sphb200_restart_") if rank == 0 else None]
