@@ -195,6 +195,7 @@ class RefBdtSim:
         self.nb = np.zeros((self.n, rs.ngmax), np.uint32)
         self.nc = np.zeros(self.n, np.uint32)
         self.group_dt = None
+        self.turb = None  # a ref.RefTurbulence makes this TurbVeBdtProp
 
     # ---- sync
     def full_sync(self):
@@ -282,6 +283,10 @@ class RefBdtSim:
             gdt[g] = min(gdt[g], np.float32(dtc))
         gdt[:na] = group_acc_timestep(self.eta_acc_eps, self.active[0], self.active[1], f["ax"], f["ay"], f["az"],
                                       gdt[:na])
+        if self.turb is not None:
+            # TurbVeBdtProp::computeForces (main/src/propagator/turb_ve.hpp:68-73): stir the active rungs afterwards
+            self.turb.drive_groups(self.active[0], self.active[1], f["x"], f["y"], f["z"], f["ax"], f["ay"], f["az"],
+                                   rs.minDt)
 
     # ---- time-step hierarchy
     def _sort_group_dt(self, num):

@@ -313,6 +313,13 @@ class RefTurbulence:
         fn = lib().ref_turb_drive_f64 if ax.dtype == np.float64 else lib().ref_turb_drive_f32
         fn(self.h, C.c_uint32(first), C.c_uint32(last), P(x), P(y), P(z), P(ax), P(ay), P(az), C.c_double(dt))
 
+    def drive_groups(self, starts, ends, x, y, z, ax, ay, az, dt):
+        """driveTurbulence with a GroupView of the given groups (TurbVeBdtProp: the active rungs); one noise update"""
+        fn = lib().ref_turb_drive_groups_f64 if ax.dtype == np.float64 else lib().ref_turb_drive_groups_f32
+        starts = np.ascontiguousarray(starts, np.uint32)
+        ends = np.ascontiguousarray(ends, np.uint32)
+        fn(self.h, C.c_uint32(starts.size), P(starts), P(ends), P(x), P(y), P(z), P(ax), P(ay), P(az), C.c_double(dt))
+
     def close(self):
         if self.h:
             lib().ref_turb_destroy(self.h)

@@ -687,6 +687,30 @@ static void refTurbDrive(void* tp, uint32_t first, uint32_t last, const double* 
     sph::computeStirring(grp, t->numDim, x, y, z, ax, ay, az, t->numModes, t->modes.data(), t->phasesReal.data(),
                          t->phasesImag.data(), t->amplitudes.data(), t->solWeightNorm);
 }
+//! @brief driveTurbulence (driver.hpp:101-128) with the caller's groups, as TurbVeBdtProp passes its active rungs
+template<class Ta>
+static void refTurbDriveGroups(void* tp, uint32_t numGroups, const uint32_t* starts, const uint32_t* ends,
+                               const double* x, const double* y, const double* z, Ta* ax, Ta* ay, Ta* az, double dt)
+{
+    auto* t = static_cast<RefTurb*>(tp);
+    sph::updateNoise(t->phases, t->variance, dt, t->decayTime, t->gen);
+    sph::computePhases(t->numModes, t->numDim, t->phases, t->solWeight, t->modes, t->phasesReal, t->phasesImag);
+    cstone::GroupView grp{0, 0, numGroups, starts, ends};
+    sph::computeStirring(grp, t->numDim, x, y, z, ax, ay, az, t->numModes, t->modes.data(), t->phasesReal.data(),
+                         t->phasesImag.data(), t->amplitudes.data(), t->solWeightNorm);
+}
+extern "C" void ref_turb_drive_groups_f64(void* t, uint32_t numGroups, const uint32_t* starts, const uint32_t* ends,
+                                          const double* x, const double* y, const double* z, double* ax, double* ay,
+                                          double* az, double dt)
+{
+    refTurbDriveGroups<double>(t, numGroups, starts, ends, x, y, z, ax, ay, az, dt);
+}
+extern "C" void ref_turb_drive_groups_f32(void* t, uint32_t numGroups, const uint32_t* starts, const uint32_t* ends,
+                                          const double* x, const double* y, const double* z, float* ax, float* ay,
+                                          float* az, double dt)
+{
+    refTurbDriveGroups<float>(t, numGroups, starts, ends, x, y, z, ax, ay, az, dt);
+}
 extern "C" void ref_turb_drive_f64(void* t, uint32_t first, uint32_t last, const double* x, const double* y,
                                    const double* z, double* ax, double* ay, double* az, double dt)
 {

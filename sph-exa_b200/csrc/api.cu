@@ -1207,6 +1207,10 @@ extern "C" int sphb200_sim_bdt_compute_forces(sphb200_sim* s)
         scope.active = b.active;
     }
     CHECK_RC(sphb200_set_scope(ctx, &scope));
+    // TurbVeBdtProp (turb_ve.hpp:68-73) stirs the active rungs after the whole of HydroVeBdtProp::computeForces, i.e.
+    // after the acceleration time step has been taken: keep the stirring out of forces phase 4
+    sphb200_turb* turb = s->turb;
+    s->turb            = nullptr;
     int rc = 0;
     try
     {
@@ -1221,12 +1225,15 @@ extern "C" int sphb200_sim_bdt_compute_forces(sphb200_sim* s)
         // Courant minimum per group (momentum_energy_gpu.cu:98-104), then groupAccTimestep (ve_hydro_bdt.hpp:282)
         CHECK_RC(sphb200_group_min_timestep(ctx, dt, &b.activeRungs, b.dtParticle, b.groupDt));
         CHECK_RC(sphb200_group_acc_timestep(ctx, dt, b.etaAccEps, &b.activeRungs, f.ax, f.ay, f.az, b.groupDt));
+        if (turb)
+            CHECK_RC(sphb200_turb_drive(turb, ctx, dt, s->start, s->end, f.x, f.y, f.z, f.ax, f.ay, f.az, s->minDt));
     }
     catch (std::exception& e)
     {
         setError(e.what());
         rc = 1;
     }
+    s->turb = turb;
     sphb200_set_scope(ctx, nullptr);
     if (rc) throw std::runtime_error(sphb200_last_error());
     SPHB200_CATCH

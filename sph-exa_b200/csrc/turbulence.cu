@@ -32,7 +32,8 @@ __global__ void __launch_bounds__(kStirBlock)
     stirringKernel(uint32_t first, uint32_t last, const double* __restrict__ x, const double* __restrict__ y,
                    const double* __restrict__ z, Ta* __restrict__ ax, Ta* __restrict__ ay, Ta* __restrict__ az,
                    int numModes, const double* __restrict__ modes, const double* __restrict__ phaseReal,
-                   const double* __restrict__ phaseImag, const double* __restrict__ amplitudes, double solWeightNorm)
+                   const double* __restrict__ phaseImag, const double* __restrict__ amplitudes, double solWeightNorm,
+                   const uint8_t* __restrict__ activeMask)
 {
     extern __shared__ double sm[];
     double* sModes = sm;
@@ -50,7 +51,7 @@ __global__ void __launch_bounds__(kStirBlock)
     __syncthreads();
 
     uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= last) return;
+    if (i >= last || (activeMask && !activeMask[i])) return; // GroupView scope (TurbVeBdtProp stirs the active rungs)
     double xi = x[i], yi = y[i], zi = z[i];
     // stirParticle (stirring.hpp:43-81): accumulators in the type of the accelerations
     Ta tx = 0, ty = 0, tz = 0;
@@ -85,7 +86,8 @@ __global__ void __launch_bounds__(kStirBlock)
                          const double* __restrict__ z, Ta* __restrict__ ax, Ta* __restrict__ ay, Ta* __restrict__ az,
                          int numModes, UniqueK uk, const unsigned char* __restrict__ idx,
                          const double* __restrict__ phaseReal, const double* __restrict__ phaseImag,
-                         const double* __restrict__ amplitudes, double solWeightNorm)
+                         const double* __restrict__ amplitudes, double solWeightNorm,
+                         const uint8_t* __restrict__ activeMask)
 {
     extern __shared__ double sm[];
     double* sRe  = sm;
@@ -104,7 +106,7 @@ __global__ void __launch_bounds__(kStirBlock)
         sAmp[k] = amplitudes[k];
 
     uint32_t i   = first + blockIdx.x * blockDim.x + threadIdx.x;
-    bool active  = i < last;
+    bool active  = i < last && (!activeMask || activeMask[i]);
     double p[3]  = {0, 0, 0};
     if (active)
     {
@@ -155,7 +157,7 @@ static void launchStirring(sphb200_ctx* ctx, uint32_t first, uint32_t last, cons
         SPHB200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
     kern<<<gridFor(last - first, kStirBlock), kStirBlock, smem, ctx->stream>>>(
         first, last, x, y, z, static_cast<Ta*>(ax), static_cast<Ta*>(ay), static_cast<Ta*>(az), numModes, modes, pr, pi,
-        amp, solWeightNorm);
+        amp, solWeightNorm, ctx->scopeActive);
     ctx->launches++;
     SPHB200_CUDA(cudaGetLastError());
 }
@@ -485,7 +487,8 @@ extern "C" int sphb200_turb_drive(sphb200_turb* t, sphb200_ctx* ctx, int dtype, 
             SPHB200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
             kern<<<grid, kStirBlock, smem, ctx->stream>>>(first, last, x, y, z, static_cast<double*>(ax),
                                                          static_cast<double*>(ay), static_cast<double*>(az), t->numModes,
-                                                         t->uk, t->dIdx, t->dRe, t->dIm, t->dAmp, t->solWeightNorm);
+                                                         t->uk, t->dIdx, t->dRe, t->dIm, t->dAmp, t->solWeightNorm,
+                                                         ctx->scopeActive);
         }
         else
         {
@@ -493,7 +496,8 @@ extern "C" int sphb200_turb_drive(sphb200_turb* t, sphb200_ctx* ctx, int dtype, 
             SPHB200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
             kern<<<grid, kStirBlock, smem, ctx->stream>>>(first, last, x, y, z, static_cast<float*>(ax),
                                                          static_cast<float*>(ay), static_cast<float*>(az), t->numModes,
-                                                         t->uk, t->dIdx, t->dRe, t->dIm, t->dAmp, t->solWeightNorm);
+                                                         t->uk, t->dIdx, t->dRe, t->dIm, t->dAmp, t->solWeightNorm,
+                                                         ctx->scopeActive);
         }
         ctx->launches++;
         SPHB200_CUDA(cudaGetLastError());

@@ -291,3 +291,38 @@ def test_bdt_single_rung(pkg, ctx, ref, case, side, safety):
         e0 = e0 or c["etot"]
         assert abs(c["etot"] - e0) < 1e-4 * abs(e0)
     gs.close()
+
+
+def test_turb_ve_bdt_propagator(pkg, ctx, ref):
+    """TurbVeBdtProp (main/src/propagator/turb_ve.hpp:52-96): block time steps with the stirring applied to the active
+    rungs after the acceleration time step was taken; Sedov IC so that several rungs and partial syncs occur"""
+    from oracle.bdt import RefBdtSim
+    from sph_exa_b200 import sim as S
+    from sph_exa_b200.turbulence import Turbulence
+    f, box, s = pkg.ic.sedov(16)
+    rs = RefBdtSim(f, box, s)
+    rs.turb = ref.RefTurbulence()
+    gt = Turbulence()
+    gs = S.HydroVeBdtProp(ctx, box, s, capacity=f["x"].size, tables=(rs.rs.wh, rs.rs.whd, rs.rs.K))
+    gs.attachTurbulence(gt)
+    gs.upload(f)
+    partial = 0
+    for step in range(10):
+        partial += not gs.isSynced()
+        rs.step()
+        gs.step()
+        info = gs.timestep()
+        assert info.numRungs == rs.ts.numRungs and list(info.rungRanges) == list(rs.ts.rungRanges), step
+        out = gs.download(names=["x", "y", "z", "vx", "vy", "vz", "temp", "ax", "ay", "az"])
+        acc = max(np.abs(rs.rs.f[k]).max() for k in ("ax", "ay", "az"))
+        for k in ("ax", "ay", "az"):
+            assert np.abs(out[k] - rs.rs.f[k]).max() <= 1e-9 * acc, (step, k)
+        for k in ("x", "y", "z", "vx", "vy", "vz", "temp"):
+            assert rel_err(out[k], rs.rs.f[k]) < 1e-9, (step, k)
+    assert partial >= 5
+    # the OU process advanced once per substep on both sides
+    st_g, st_r = gt.state(), rs.turb.state()
+    assert np.array_equal(st_g["phases"], st_r["phases"])
+    gs.close()
+    gt.close()
+    rs.turb.close()
