@@ -290,6 +290,58 @@ def main():
                                "fp64_vector_peak_nominal_tflops": 37.0,
                                "l1_wavefront_pct_of_peak": ncu_column(dom, args, "l1_data_wavefronts_pct [%]")}
 
+    # ---------------- the HBM-bound kernels of the step, one by one (north star: >= 70 % of the HBM roofline on the
+    # gather kernels): the operators of Domain::sync replayed through the tier-1 ABI on the current particle state,
+    # CUDA events on the launching stream, inputs (>= 192 MB each) larger than L2
+    hbm_kernels = None
+    try:
+        from sph_exa_b200 import ops
+        real_t = torch.float64 if args.dtype == "f64" else torch.float32
+        state = gs.download()
+        dev = {k: torch.from_numpy(np.ascontiguousarray(v)).cuda() for k, v in state.items()}
+        bx = pkg.make_box(*box)
+        ev = lambda: torch.cuda.Event(enable_timing=True)
+
+        def timed(fn, reps=5):
+            fn()
+            sync()
+            a, b = ev(), ev()
+            a.record()
+            for _ in range(reps):
+                fn()
+            b.record()
+            sync()
+            return a.elapsed_time(b) / reps
+
+        keys = ops.computeSfcKeysGpu(ctx, dev["x"], dev["y"], dev["z"], bx)
+        t_keys = timed(lambda: ops.computeSfcKeysGpu(ctx, dev["x"], dev["y"], dev["z"], bx, keys))
+        # the state of a running simulation: SFC-sorted one step ago, every particle moved by v dt since (what the
+        # sort and the gather of the next Domain::sync see)
+        keys0 = keys.clone()
+        work = keys0.clone()
+        perm = ops.sortByKeyGpu(ctx, work)
+
+        def sort_once():
+            work.copy_(keys0)
+            ops.sortByKeyGpu(ctx, work)
+
+        t_copy = timed(lambda: work.copy_(keys0))
+        t_sort = timed(sort_once) - t_copy
+        srcs = [dev[k] for k in B.CONSERVED]
+        dsts = [torch.empty_like(a) for a in srcs]
+        t_gather = timed(lambda: ops.gatherGpu(ctx, perm, srcs, dsts))
+        col = 0 if args.dtype == "f64" else 1
+        rows = {"sfcKeys": (t_keys, 32), "radixSort (8 passes)": (t_sort, 204),
+                "gatherFields (14 fields)": (t_gather, (228, 148)[col]),
+                "eos": (phase_ms["EquationOfState"], ALGO_BYTES["EquationOfState"][col]),
+                "positions+updateH": (phase_ms["Timestep+UpdateQuantities"], ALGO_BYTES["Timestep+UpdateQuantities"][col])}
+        hbm_kernels = {k: {"ms": ms, "algorithmic_bytes_per_particle": bpp, "achieved_gbs": bpp * n / (ms * 1e-3) / 1e9,
+                           "frac": bpp * n / (ms * 1e-3) / 1e9 / peak} for k, (ms, bpp) in rows.items()}
+        del dev, srcs, dsts, keys0, work, perm, keys
+        torch.cuda.empty_cache()
+    except Exception as ex:  # diagnostics only: never let them take the headline down
+        hbm_kernels = {"error": str(ex)}
+
     # ---------------- end to end through the C ABI with host buffers
     e2e = None
     if not args.no_e2e:
@@ -377,7 +429,7 @@ def main():
         "find_neighbors_ms": phase_ms.get("FindNeighbors"),
         "phase_ms": phase_ms, "total_neighbors": total_nb, "leaves": gs.numLeaves,
         "clocks": clocks, "gpu_launches": launches, "roofline": roofline, "e2e": e2e, "cpu_baseline": cpu,
-        "block_time_steps": bdt,
+        "hbm_kernels": hbm_kernels, "block_time_steps": bdt,
     }
     print(json.dumps(line), flush=True)
     gs.close()
