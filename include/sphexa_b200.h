@@ -477,6 +477,10 @@ typedef struct sphb200_op_scope
     float searchExtFactor;  /* <= 0: 1.  > 1 while particles have drifted since the tree was built */
     void* dtParticle;       /* device T[...] indexed like the fields or NULL: Courant step of every processed target,
                                written by sphb200_momentum_energy */
+    uint8_t* gatherMask;    /* device, one byte per particle (f->n), zeroed by the caller, or NULL.  With `active` set,
+                               sphb200_find_neighbors marks every target it processes and every particle on its list;
+                               the pair operators then refresh their gather records for the marked particles only
+                               (a partial sync touches a few per cent of them) */
 } sphb200_op_scope;
 int sphb200_set_scope(sphb200_ctx*, const sphb200_op_scope* scope_h);
 /* active[0..n) = 0, then active[i] = 1 for the members of the groups */

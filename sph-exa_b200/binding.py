@@ -71,7 +71,7 @@ class GroupView(C.Structure):
 
 class OpScope(C.Structure):
     """sphb200_op_scope: the GroupView argument / searchExtFactor of the reference's GPU operators"""
-    _fields_ = [("active", vp), ("searchExtFactor", C.c_float), ("dtParticle", vp)]
+    _fields_ = [("active", vp), ("searchExtFactor", C.c_float), ("dtParticle", vp), ("gatherMask", vp)]
 
 
 class BdtInfo(C.Structure):

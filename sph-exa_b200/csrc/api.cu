@@ -256,7 +256,7 @@ struct sphb200_sim
         sphb200_group_view groups{}, tsGroups{}, activeRungs{}, rungs[4]{};
         float* groupDt         = nullptr;
         uint32_t* groupIndices = nullptr;
-        uint8_t *rung = nullptr, *rungAlt = nullptr, *active = nullptr;
+        uint8_t *rung = nullptr, *rungAlt = nullptr, *active = nullptr, *gather = nullptr;
         void* dtParticle     = nullptr;
         float searchExt      = 1.0f;
         bool allActive       = true;
@@ -392,7 +392,7 @@ extern "C" void sphb200_sim_destroy(sphb200_sim* s)
     cudaFree(s->layout);
     for (auto p : s->bdt.buf) cudaFree(p);
     cudaFree(s->bdt.groupDt); cudaFree(s->bdt.groupIndices); cudaFree(s->bdt.rung); cudaFree(s->bdt.rungAlt);
-    cudaFree(s->bdt.active); cudaFree(s->bdt.dtParticle);
+    cudaFree(s->bdt.active); cudaFree(s->bdt.gather); cudaFree(s->bdt.dtParticle);
     for (auto& e : s->ev) cudaEventDestroy(e);
     if (s->copyIn)
     {
@@ -1173,6 +1173,7 @@ extern "C" int sphb200_sim_bdt_enable(sphb200_sim* s, int safetySteps, double et
         b.rung       = devAlloc<uint8_t>(s->capacity);
         b.rungAlt    = devAlloc<uint8_t>(s->capacity);
         b.active     = devAlloc<uint8_t>(s->capacity);
+        b.gather     = devAlloc<uint8_t>(s->capacity);
         b.dtParticle = devAlloc<char>(s->capacity * size_t(s->cfg.dtype == SPHB200_F64 ? 8 : 4));
         SPHB200_CUDA(cudaMemset(b.rung, 0, s->capacity));
         SPHB200_CUDA(cudaMemset(b.rungAlt, 0, s->capacity));
@@ -1200,11 +1201,13 @@ extern "C" int sphb200_sim_bdt_compute_forces(sphb200_sim* s)
     if (activeRung(b.ts.substep, b.ts.numRungs) == 0) bdtFullSync(s);
     else bdtPartialSync(s);
 
-    sphb200_op_scope scope{nullptr, b.searchExt, b.dtParticle};
+    sphb200_op_scope scope{nullptr, b.searchExt, b.dtParticle, nullptr};
     if (!b.allActive)
     {
         CHECK_RC(sphb200_mark_groups(ctx, &b.activeRungs, s->n, b.active));
         scope.active = b.active;
+        SPHB200_CUDA(cudaMemsetAsync(b.gather, 0, s->n, ctx->stream));
+        scope.gatherMask = b.gather;
     }
     CHECK_RC(sphb200_set_scope(ctx, &scope));
     // TurbVeBdtProp (turb_ve.hpp:68-73) stirs the active rungs after the whole of HydroVeBdtProp::computeForces, i.e.

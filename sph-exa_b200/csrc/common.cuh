@@ -104,6 +104,7 @@ struct sphb200_ctx
     const uint8_t* scopeActive = nullptr;
     float searchExtFactor      = 1.0f;
     void* scopeDtParticle      = nullptr;
+    uint8_t* scopeGather       = nullptr;
 };
 
 namespace sphb200

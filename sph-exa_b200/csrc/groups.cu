@@ -382,6 +382,8 @@ extern "C" int sphb200_set_scope(sphb200_ctx* ctx, const sphb200_op_scope* scope
     ctx->scopeActive     = scope ? scope->active : nullptr;
     ctx->searchExtFactor = (scope && scope->searchExtFactor > 0) ? scope->searchExtFactor : 1.0f;
     ctx->scopeDtParticle = scope ? scope->dtParticle : nullptr;
+    ctx->scopeGather     = (scope && scope->active) ? scope->gatherMask : nullptr;
+    ctx->packValid       = 0; // records packed under another scope are not complete
     GROUPS_CATCH
 }
 

@@ -198,10 +198,12 @@ __device__ __forceinline__ Rec2<T> ldHalf(const Rec4<T>* __restrict__ p, uint32_
 template<class T>
 __global__ void __launch_bounds__(256) packPosKernel(size_t n, const double* __restrict__ x,
                                                      const double* __restrict__ y, const double* __restrict__ z,
-                                                     const T* __restrict__ m, PosRec<T>* __restrict__ out)
+                                                     const T* __restrict__ m, PosRec<T>* __restrict__ out,
+                                                     const uint8_t* __restrict__ mask)
 {
+    // mask (sphb200_op_scope::gatherMask): only the particles some active target gathers from are refreshed
     size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
-    if (i >= n) return;
+    if (i >= n || (mask && !mask[i])) return;
     PosRec<T> r;
     r.x = x[i]; r.y = y[i]; r.z = z[i]; r.m = m[i];
     out[i] = r;
@@ -210,10 +212,10 @@ __global__ void __launch_bounds__(256) packPosKernel(size_t n, const double* __r
 template<class T>
 __global__ void __launch_bounds__(256) pack4Kernel(size_t n, const T* __restrict__ a, const T* __restrict__ b,
                                                    const T* __restrict__ c, const T* __restrict__ d,
-                                                   Rec4<T>* __restrict__ out)
+                                                   Rec4<T>* __restrict__ out, const uint8_t* __restrict__ mask)
 {
     size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
-    if (i >= n) return;
+    if (i >= n || (mask && !mask[i])) return;
     Rec4<T> r;
     r.a = a ? a[i] : T(0); r.b = b ? b[i] : T(0); r.c = c ? c[i] : T(0); r.d = d ? d[i] : T(0);
     out[i] = r;
@@ -223,20 +225,22 @@ __global__ void __launch_bounds__(256) pack4Kernel(size_t n, const T* __restrict
 template<class T>
 __global__ void __launch_bounds__(256) packVelVolKernel(size_t n, const T* __restrict__ vx, const T* __restrict__ vy,
                                                         const T* __restrict__ vz, const T* __restrict__ xm,
-                                                        const T* __restrict__ kx, Rec4<T>* __restrict__ out)
+                                                        const T* __restrict__ kx, Rec4<T>* __restrict__ out,
+                                                        const uint8_t* __restrict__ mask)
 {
     size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
-    if (i >= n) return;
+    if (i >= n || (mask && !mask[i])) return;
     out[i] = {vx[i], vy[i], vz[i], xm[i] / kx[i]};
 }
 
 //! @brief momentum records M1, M2, M4 with the j-only terms of momentum_energy_kern.hpp:96-97,116-117,165
 template<class T>
 __global__ void __launch_bounds__(256) packMomentumKernel(size_t n, F<T> f, Rec4<T>* __restrict__ m1,
-                                                          Rec4<T>* __restrict__ m2, Rec4<T>* __restrict__ m4)
+                                                          Rec4<T>* __restrict__ m2, Rec4<T>* __restrict__ m4,
+                                                          const uint8_t* __restrict__ mask)
 {
     size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
-    if (i >= n) return;
+    if (i >= n || (mask && !mask[i])) return;
     T m = f.m[i], xm = f.xm[i];
     T rho = f.kx[i] * m / xm;
     m1[i] = {f.vx[i], f.vy[i], f.vz[i], T(1) / f.h[i]};
@@ -1181,7 +1185,7 @@ static const void* ensureRec(sphb200_ctx* ctx, int k, const sphb200_fields& f)
     F<T> t   = typed<T>(f);
     int grid = gridFor(n, 256);
     auto p4  = [&](const T* a, const T* b, const T* c, const T* d)
-    { SPHB200_LAUNCH(ctx, pack4Kernel<T>, grid, 256, 0, n, a, b, c, d, static_cast<Rec4<T>*>(out)); };
+    { SPHB200_LAUNCH(ctx, pack4Kernel<T>, grid, 256, 0, n, a, b, c, d, static_cast<Rec4<T>*>(out), ctx->scopeGather); };
     switch (k)
     {
         case R_POS:
@@ -1189,12 +1193,13 @@ static const void* ensureRec(sphb200_ctx* ctx, int k, const sphb200_fields& f)
         case R_PDIVV:
         {
             const T* fourth = k == R_POS ? t.m : (k == R_PXM ? t.xm : t.divv);
-            SPHB200_LAUNCH(ctx, packPosKernel<T>, grid, 256, 0, n, t.x, t.y, t.z, fourth, static_cast<PosRec<T>*>(out));
+            SPHB200_LAUNCH(ctx, packPosKernel<T>, grid, 256, 0, n, t.x, t.y, t.z, fourth, static_cast<PosRec<T>*>(out),
+                           ctx->scopeGather);
             break;
         }
         case R_VV:
             SPHB200_LAUNCH(ctx, packVelVolKernel<T>, grid, 256, 0, n, t.vx, t.vy, t.vz, t.xm, t.kx,
-                           static_cast<Rec4<T>*>(out));
+                           static_cast<Rec4<T>*>(out), ctx->scopeGather);
             break;
         case R_CA: p4(t.c11, t.c12, t.c13, t.c22); break;
         case R_GA: p4(t.dV11, t.dV12, t.dV13, t.dV22); break;
@@ -1231,7 +1236,7 @@ static void packMomentum(sphb200_ctx* ctx, const sphb200_fields& f, MomRecs<T>& 
     auto* m1 = static_cast<Rec4<T>*>(ctx->rec[R_MVEL].get(n * sizeof(Rec4<T>)));
     auto* m2 = static_cast<Rec4<T>*>(ctx->rec[R_MSTATE].get(n * sizeof(Rec4<T>)));
     auto* m4 = static_cast<Rec4<T>*>(ctx->rec[R_MCB].get(n * sizeof(Rec4<T>)));
-    SPHB200_LAUNCH(ctx, packMomentumKernel<T>, gridFor(n, 256), 256, 0, n, typed<T>(f), m1, m2, m4);
+    SPHB200_LAUNCH(ctx, packMomentumKernel<T>, gridFor(n, 256), 256, 0, n, typed<T>(f), m1, m2, m4, ctx->scopeGather);
     rec.r1 = m1;
     rec.r2 = m2;
     rec.r4 = m4;

@@ -352,7 +352,7 @@ __global__ void __launch_bounds__(kNbWarps * 32)
                         const double* __restrict__ z, Th* __restrict__ h, LocalIndex first, LocalIndex last,
                         sphb200_box box, unsigned ng0, unsigned ngmax, int iterateH, uint32_t* __restrict__ nidx,
                         uint32_t* __restrict__ nc, unsigned* __restrict__ numFails,
-                        const uint8_t* __restrict__ activeMask, double extFactor)
+                        const uint8_t* __restrict__ activeMask, double extFactor, uint8_t* __restrict__ gatherMask)
 {
     __shared__ TreeNodeIndex stackMem[kNbWarps][kStackSize];
     __shared__ double candMem[kNbWarps][96];
@@ -525,6 +525,14 @@ __global__ void __launch_bounds__(kNbWarps * 32)
 
     if (valid)
     {
+        if (gatherMask)
+        {
+            // what the pair operators will gather for this target: itself and its list
+            gatherMask[i] = 1;
+            unsigned stored = min(count, ngmax);
+            for (unsigned k = 0; k < stored; ++k)
+                gatherMask[myList[size_t(k) * 32]] = 1;
+        }
         nc[i - first] = count + 1;
         if (iterateH)
         {
@@ -578,11 +586,11 @@ extern "C" int sphb200_find_neighbors(sphb200_ctx* ctx, const sphb200_tree_view*
         if (dtype == SPHB200_F64)
             SPHB200_LAUNCH(ctx, findNeighborsKernel<double>, grid, kNbWarps * 32, 0, tree, x, y, z,
                            static_cast<double*>(h), first, last, *box, ng0, ngmax, iterateH, neighbors, nc, dFails,
-                           ctx->scopeActive, double(ctx->searchExtFactor));
+                           ctx->scopeActive, double(ctx->searchExtFactor), ctx->scopeGather);
         else
             SPHB200_LAUNCH(ctx, findNeighborsKernel<float>, grid, kNbWarps * 32, 0, tree, x, y, z,
                            static_cast<float*>(h), first, last, *box, ng0, ngmax, iterateH, neighbors, nc, dFails,
-                           ctx->scopeActive, double(ctx->searchExtFactor));
+                           ctx->scopeActive, double(ctx->searchExtFactor), ctx->scopeGather);
         if (numFails_h)
         {
             SPHB200_CUDA(cudaMemcpyAsync(ctx->hostScalars + 4, dFails, sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->stream));

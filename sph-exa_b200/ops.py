@@ -414,13 +414,14 @@ class scope:
     """with ops.scope(ctx, active=mask, searchExtFactor=f, dtParticle=t): the GroupView argument of the reference's GPU
     operators (sph_gpu.hpp:13-82) and OctreeNsView::searchExtFactor as context state (sphb200_set_scope)"""
 
-    def __init__(self, ctx, active=None, searchExtFactor=1.0, dtParticle=None):
+    def __init__(self, ctx, active=None, searchExtFactor=1.0, dtParticle=None, gatherMask=None):
         self.ctx = ctx
         self.s = B.OpScope()
         self.s.active = active.data_ptr() if active is not None else None
         self.s.searchExtFactor = searchExtFactor
         self.s.dtParticle = dtParticle.data_ptr() if dtParticle is not None else None
-        self.keep = (active, dtParticle)
+        self.s.gatherMask = gatherMask.data_ptr() if gatherMask is not None else None
+        self.keep = (active, dtParticle, gatherMask)
 
     def __enter__(self):
         check(lib.sphb200_set_scope(self.ctx.h, C.byref(self.s)))

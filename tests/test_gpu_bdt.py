@@ -163,10 +163,18 @@ def test_scoped_operators_touch_only_active_targets(pkg, ctx, ref):
     nb2 = torch.full_like(nb_all, -1)
     nc2 = torch.full_like(nc_all, 77)
     dtp = torch.full((n,), -1.0, dtype=torch.float64, device="cuda")
-    with ops.scope(ctx, active=mask, searchExtFactor=1.0, dtParticle=dtp):
+    gmask = torch.zeros(n, dtype=torch.uint8, device="cuda")
+    with ops.scope(ctx, active=mask, searchExtFactor=1.0, dtParticle=dtp, gatherMask=gmask):
         h2 = to_dev(sim.f["h"])
         lib_find(pkg, ctx, tree, part, h2, n, b, sim, nb2, nc2)
         assert np.array_equal(to_host(nc2)[m], to_host(nc_all)[m]) and np.all(to_host(nc2)[~m] == 77)
+        # the gather mask = the active targets and everything on their lists (the reference lists give the same sets)
+        want_g = np.zeros(n, bool)
+        want_g[m] = True
+        for i in np.nonzero(m)[0]:
+            want_g[sim.nb[i, :min(sim.nc[i] - 1, ngmax)]] = True
+        assert np.array_equal(to_host(gmask).astype(bool), want_g)
+        assert want_g.sum() < n
         part["nc"] = torch.where(mask.bool(), nc2, nc_all)
         for k in ("xm",):
             part[k] = torch.full_like(full[k], -7.0)
