@@ -116,6 +116,7 @@ class DistHydroVeProp:
         self.assignment = None
         self.times = {}
         self.halo_bytes = 0
+        self.halo_factor = 1.0
         self._sync_profile = bool(int(os.environ.get("SPHB200_SYNC_PROFILE", "0")))
         self.sync_times = {}
 
@@ -267,7 +268,9 @@ class DistHydroVeProp:
         leaf_c = ftree.centers[l2i].contiguous()
         leaf_s = ftree.sizes[l2i].contiguous()
         occupied = self.ftree[1] > 0
-        half = leaf_s + (2.0 * hmax * (1 + 1e-9)).unsqueeze(1)
+        # Domain::setHaloFactor (domain.hpp): block time steps widen the halo search so that the halos stay valid while
+        # particles drift between two full syncs
+        half = leaf_s + (2.0 * self.halo_factor * hmax * (1 + 1e-9)).unsqueeze(1)
         lo, hi = leaf_c - half, leaf_c + half
         # union of the halo boxes per coarse SFC block so that at most MAX_QUERY_BOXES boxes are published
         lk = self.ftree[0][:-1]

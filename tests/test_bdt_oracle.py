@@ -143,3 +143,19 @@ def test_reference_sequence_hierarchy_invariants(pkg, ref):
     assert abs(rs.rs.ttot - t_sum) < 1e-12
     tot = pkg.ic.conserved_totals(rs.rs.f, s)["etot"]
     assert abs(tot - tot0) < 2e-3 * abs(tot0)
+
+
+def test_product_host_logic_matches_oracle(pkg):
+    """the host-side rung arithmetic of the distributed propagator (sph-exa_b200/dist_bdt.py) against the oracle's"""
+    from oracle import bdt
+    from sph_exa_b200 import dist_bdt
+    for i in range(64):
+        assert dist_bdt.butterfly(i) == bdt.butterfly(i)
+        for nr in range(1, 5):
+            assert dist_bdt.active_rung(i, nr) == bdt.active_rung(i, nr)
+    a, b = dist_bdt.Timestep(), bdt.Timestep()
+    assert a.numRungs == b.numRungs and a.substep == b.substep and list(a.rungRanges) == list(b.rungRanges)
+    c = a.copy()
+    c.dt_m1[0] = 1
+    c.rungRanges[1] = 5
+    assert a.dt_m1[0] == 0 and a.rungRanges[1] == 0

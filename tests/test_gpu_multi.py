@@ -23,3 +23,15 @@ def test_two_ranks_equal_one_rank(case, side):
            "--side", str(side), "--steps", "3"]
     res = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
     assert res.returncode == 0 and "DIST_CHECK PASS" in res.stdout, res.stdout[-3000:] + res.stderr[-3000:]
+
+
+def test_two_ranks_block_time_steps():
+    """DistHydroVeBdtProp on 2 ranks == the one-rank tier-2 block-time-step propagator, bit for bit, over two
+    hierarchies (full syncs with migration-capable reorder of the rung field, partial syncs with halo-only exchanges)"""
+    if _ngpu() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+           "127.0.0.1", "--master-port", "29534", os.path.join(ROOT, "tests", "dist_check.py"), "--case", "sedov",
+           "--side", "40", "--steps", "10", "--bdt"]
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
+    assert res.returncode == 0 and "DIST_CHECK PASS" in res.stdout, res.stdout[-3000:] + res.stderr[-3000:]
