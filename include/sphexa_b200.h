@@ -413,8 +413,22 @@ typedef struct sphb200_restart_info
  * turb may be NULL */
 int sphb200_restart_write(const char* path, const sphb200_restart_info* info, const sphb200_hydro_const* hc,
                           const sphb200_turb* turb, int rank, int numRanks, const sphb200_fields* host_fields);
+/* block-time-step state of a dump: HydroVeBdtProp::save writes Timestep::loadOrStore with the prefix "ts::"
+ * (ve_hydro_bdt.hpp:153, sph/include/sph/timestep.h:29-33) and "rung" is one of its conserved fields
+ * (ve_hydro_bdt.hpp:94).  rung: one byte per particle of the file, host memory. */
+typedef struct sphb200_restart_bdt
+{
+    int numRungs;
+    float dt_m1[4];
+    const uint8_t* rung;
+} sphb200_restart_bdt;
+/* sphb200_restart_write plus the attributes ts::numRungs, ts::dt_m1 and the particle field "rung"; bdt may be NULL */
+int sphb200_restart_write_bdt(const char* path, const sphb200_restart_info* info, const sphb200_hydro_const* hc,
+                              const sphb200_turb* turb, int rank, int numRanks, const sphb200_fields* host_fields,
+                              const sphb200_restart_bdt* bdt);
 /* write the owned particles [startIndex,endIndex): attributes + the 14 conserved fields (+ turbulence state when a
- * driver is attached).  iteration / numParticlesGlobal are the caller's (they live in the reference's main loop). */
+ * driver is attached, + the block-time-step state after sphb200_sim_bdt_enable).  iteration / numParticlesGlobal are
+ * the caller's (they live in the reference's main loop). */
 int sphb200_sim_save(sphb200_sim*, const char* path, uint64_t iteration, uint64_t numParticlesGlobal);
 
 int sphb200_restart_open(const char* path, sphb200_restart** out);
@@ -428,8 +442,12 @@ int64_t sphb200_restart_attribute(const sphb200_restart*, const char* name, void
  * offsetting the pointers */
 int sphb200_restart_read_fields(const sphb200_restart*, uint64_t first, uint64_t count, int dtype,
                                 const sphb200_fields* host_fields);
-/* time, minDt, minDt_m1, the optional constants found in the file, the box, and the turbulence state (when the file
- * has one and a driver is attached) */
+/* particles [first, first+count) of a one-byte-per-particle field ("rung"); an error when the file has none */
+int sphb200_restart_read_bytes(const sphb200_restart*, const char* name, uint64_t first, uint64_t count, uint8_t* out);
+/* time, minDt, minDt_m1, the optional constants found in the file, the box, the turbulence state (when the file
+ * has one and a driver is attached) and ts::numRungs / ts::dt_m1 (when the file has them and block time steps are
+ * enabled on the sim: HydroVeBdtProp::load, ve_hydro_bdt.hpp:155-168).  The "rung" field travels with the particle
+ * slices: sphb200_restart_read_bytes + sphb200_sim_bdt_upload_rungs. */
 int sphb200_restart_apply(const sphb200_restart*, sphb200_sim*);
 
 /* ---- f3: block time steps (HydroVeBdtProp, main/src/propagator/ve_hydro_bdt.hpp) ----
@@ -534,6 +552,11 @@ int sphb200_sim_bdt_compute_forces(sphb200_sim*); /* sync (full or partial) + fo
 int sphb200_sim_bdt_integrate(sphb200_sim*);      /* computeRungs + advance/drift + updateSmoothingLength */
 int sphb200_sim_bdt_step(sphb200_sim*);
 int sphb200_sim_bdt_info(const sphb200_sim*, sphb200_bdt_info* out);
+/* restart support: the time-step record a new hierarchy starts from (substep 0), and the rung of the particles of
+ * the last sphb200_sim_upload [0,n) / of the owned range */
+int sphb200_sim_bdt_restore(sphb200_sim*, int numRungs, const float dt_m1[4]);
+int sphb200_sim_bdt_upload_rungs(sphb200_sim*, const uint8_t* host, size_t n);
+int sphb200_sim_bdt_download_rungs(sphb200_sim*, uint8_t* host);
 /* device views for tests: per-particle rung [nWithHalos], groupDt [numGroups], and the active-target mask */
 const uint8_t* sphb200_sim_bdt_rungs(const sphb200_sim*);
 const float* sphb200_sim_bdt_group_dt(const sphb200_sim*);

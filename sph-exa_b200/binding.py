@@ -82,6 +82,11 @@ class BdtInfo(C.Structure):
                 ("searchExtFactor", C.c_float), ("isSynced", C.c_int)]
 
 
+class RestartBdt(C.Structure):
+    """sphb200_restart_bdt: ts::numRungs, ts::dt_m1 and the host pointer of the rung bytes"""
+    _fields_ = [("numRungs", C.c_int), ("dt_m1", C.c_float * 4), ("rung", vp)]
+
+
 class RestartInfo(C.Structure):
     _fields_ = [("iteration", C.c_uint64), ("numParticlesGlobal", C.c_uint64), ("numParticles", C.c_uint64),
                 ("dtype", C.c_int), ("hasTurbulence", C.c_int), ("time", C.c_double), ("minDt", C.c_double),
@@ -117,7 +122,8 @@ SYMBOLS = [
     "sphb200_drift_positions", "sphb200_compute_positions_groups", "sphb200_update_h_groups",
     "sphb200_sim_bdt_enable", "sphb200_sim_bdt_compute_forces", "sphb200_sim_bdt_integrate", "sphb200_sim_bdt_step",
     "sphb200_sim_bdt_info", "sphb200_sim_bdt_rungs", "sphb200_sim_bdt_group_dt", "sphb200_sim_bdt_active",
-    "sphb200_sim_bdt_groups", "sphb200_momentum_energy_range", "sphb200_av_switches_courant", "sphb200_update_h_into", "sphb200_mach_square_sum", "sphb200_mach_device_ptr",
+    "sphb200_sim_bdt_groups", "sphb200_sim_bdt_restore", "sphb200_sim_bdt_upload_rungs", "sphb200_sim_bdt_download_rungs",
+    "sphb200_restart_write_bdt", "sphb200_restart_read_bytes", "sphb200_momentum_energy_range", "sphb200_av_switches_courant", "sphb200_update_h_into", "sphb200_mach_square_sum", "sphb200_mach_device_ptr",
     "sphb200_sim_mach_rms",
 ]
 
@@ -156,6 +162,8 @@ lib.sphb200_sim_set_box.restype = None
 lib.sphb200_sim_set_box.argtypes = [vp, vp]
 lib.sphb200_sim_save.argtypes = [vp, C.c_char_p, C.c_uint64, C.c_uint64]
 lib.sphb200_restart_write.argtypes = [C.c_char_p, vp, vp, vp, C.c_int, C.c_int, vp]
+lib.sphb200_restart_write_bdt.argtypes = [C.c_char_p, vp, vp, vp, C.c_int, C.c_int, vp, vp]
+lib.sphb200_restart_read_bytes.argtypes = [vp, C.c_char_p, C.c_uint64, C.c_uint64, vp]
 lib.sphb200_restart_open.argtypes = [C.c_char_p, vp]
 lib.sphb200_restart_close.restype = None
 lib.sphb200_restart_close.argtypes = [vp]
@@ -186,6 +194,9 @@ for _n in ("sphb200_sim_bdt_compute_forces", "sphb200_sim_bdt_integrate", "sphb2
     getattr(lib, _n).argtypes = [vp]
 lib.sphb200_sim_bdt_info.argtypes = [vp, vp]
 lib.sphb200_sim_bdt_groups.argtypes = [vp, vp]
+lib.sphb200_sim_bdt_restore.argtypes = [vp, C.c_int, vp]
+lib.sphb200_sim_bdt_upload_rungs.argtypes = [vp, vp, C.c_size_t]
+lib.sphb200_sim_bdt_download_rungs.argtypes = [vp, vp]
 for _n in ("sphb200_sim_bdt_rungs", "sphb200_sim_bdt_group_dt", "sphb200_sim_bdt_active"):
     getattr(lib, _n).restype = vp
     getattr(lib, _n).argtypes = [vp]

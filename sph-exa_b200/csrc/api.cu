@@ -1325,6 +1325,42 @@ extern "C" int sphb200_sim_bdt_info(const sphb200_sim* s, sphb200_bdt_info* out)
     SPHB200_CATCH
 }
 
+extern "C" int sphb200_sim_bdt_restore(sphb200_sim* s, int numRungs, const float dt_m1[4])
+{
+    SPHB200_TRY
+    auto& b = s->bdt;
+    if (!b.enabled) throw std::runtime_error("bdt_restore: call sphb200_sim_bdt_enable first");
+    if (numRungs < 1 || numRungs > 4) throw std::runtime_error("bdt_restore: numRungs out of range");
+    // Timestep::loadOrStore restores numRungs and dt_m1 only; everything else keeps its initial value and the next
+    // computeForces starts a new hierarchy (substep 0)
+    b.ts          = sphb200_sim::Timestep{};
+    b.ts.numRungs = numRungs;
+    std::copy(dt_m1, dt_m1 + 4, b.ts.dt_m1);
+    b.prev = b.ts;
+    SPHB200_CATCH
+}
+
+extern "C" int sphb200_sim_bdt_upload_rungs(sphb200_sim* s, const uint8_t* host, size_t n)
+{
+    SPHB200_TRY
+    auto& b = s->bdt;
+    if (!b.enabled) throw std::runtime_error("bdt_upload_rungs: call sphb200_sim_bdt_enable first");
+    if (n > s->capacity) throw std::runtime_error("bdt_upload_rungs: n exceeds capacity");
+    SPHB200_CUDA(cudaMemcpyAsync(b.rung, host, n, cudaMemcpyHostToDevice, s->ctx->stream));
+    SPHB200_CUDA(cudaStreamSynchronize(s->ctx->stream));
+    SPHB200_CATCH
+}
+
+extern "C" int sphb200_sim_bdt_download_rungs(sphb200_sim* s, uint8_t* host)
+{
+    SPHB200_TRY
+    auto& b = s->bdt;
+    if (!b.enabled) throw std::runtime_error("bdt_download_rungs: call sphb200_sim_bdt_enable first");
+    SPHB200_CUDA(cudaMemcpyAsync(host, b.rung + s->start, s->end - s->start, cudaMemcpyDeviceToHost, s->ctx->stream));
+    SPHB200_CUDA(cudaStreamSynchronize(s->ctx->stream));
+    SPHB200_CATCH
+}
+
 extern "C" const uint8_t* sphb200_sim_bdt_rungs(const sphb200_sim* s) { return s->bdt.rung; }
 extern "C" const float* sphb200_sim_bdt_group_dt(const sphb200_sim* s) { return s->bdt.groupDt; }
 extern "C" const uint8_t* sphb200_sim_bdt_active(const sphb200_sim* s) { return s->bdt.allActive ? nullptr : s->bdt.active; }

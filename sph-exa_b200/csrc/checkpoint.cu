@@ -233,9 +233,9 @@ using sphb200::setError;
         if ((call) != 0) throw std::runtime_error(sphb200_last_error());                                              \
     } while (0)
 
-extern "C" int sphb200_restart_write(const char* path, const sphb200_restart_info* info,
-                                     const sphb200_hydro_const* hcIn, const sphb200_turb* t, int rank, int numRanks,
-                                     const sphb200_fields* host)
+extern "C" int sphb200_restart_write_bdt(const char* path, const sphb200_restart_info* info,
+                                         const sphb200_hydro_const* hcIn, const sphb200_turb* t, int rank,
+                                         int numRanks, const sphb200_fields* host, const sphb200_restart_bdt* bdt)
 {
     RESTART_TRY
     const sphb200_hydro_const& hc = *hcIn;
@@ -304,8 +304,23 @@ extern "C" int sphb200_restart_write(const char* path, const sphb200_restart_inf
         if (!src && n) throw std::runtime_error(std::string("restart: conserved field missing: ") + kConserved[k].name);
         w.add(kConserved[k].name, B_FIELD, (kConserved[k].alwaysF64 || eb == 8) ? T_F64 : T_F32, n, src);
     }
+    if (bdt)
+    {
+        // Timestep::loadOrStore with the prefix "ts::" (timestep.h:29-33), and the conserved field "rung"
+        if (!bdt->rung && n) throw std::runtime_error("restart: conserved field missing: rung");
+        w.i64("ts::numRungs", bdt->numRungs);
+        w.add("ts::dt_m1", B_ATTRIBUTE, T_F32, 4, bdt->dt_m1);
+        w.add("rung", B_FIELD, T_BYTES, n, bdt->rung);
+    }
     w.write(path);
     RESTART_CATCH
+}
+
+extern "C" int sphb200_restart_write(const char* path, const sphb200_restart_info* info,
+                                     const sphb200_hydro_const* hc, const sphb200_turb* t, int rank, int numRanks,
+                                     const sphb200_fields* host)
+{
+    return sphb200_restart_write_bdt(path, info, hc, t, rank, numRanks, host, nullptr);
 }
 
 extern "C" int sphb200_sim_save(sphb200_sim* s, const char* path, uint64_t iteration, uint64_t numParticlesGlobal)
@@ -338,7 +353,23 @@ extern "C" int sphb200_sim_save(sphb200_sim* s, const char* path, uint64_t itera
         setHostPtr(table, kConserved[k], host[k].data());
     }
     RESTART_RC(sphb200_sim_download(s, &table, nullptr));
-    RESTART_RC(sphb200_restart_write(path, &info, &cfg.hc, sphb200_sim_turbulence(s), cfg.rank, cfg.numRanks, &table));
+
+    // HydroVeBdtProp::save (ve_hydro_bdt.hpp:153)
+    sphb200_bdt_info bi;
+    RESTART_RC(sphb200_sim_bdt_info(s, &bi));
+    sphb200_restart_bdt bdt;
+    std::vector<uint8_t> rung;
+    bool haveBdt = sphb200_sim_bdt_rungs(s) != nullptr;
+    if (haveBdt)
+    {
+        rung.resize(std::max<size_t>(n, 1));
+        RESTART_RC(sphb200_sim_bdt_download_rungs(s, rung.data()));
+        bdt.numRungs = bi.numRungs;
+        std::copy(bi.dt_m1, bi.dt_m1 + 4, bdt.dt_m1);
+        bdt.rung = rung.data();
+    }
+    RESTART_RC(sphb200_restart_write_bdt(path, &info, &cfg.hc, sphb200_sim_turbulence(s), cfg.rank, cfg.numRanks,
+                                         &table, haveBdt ? &bdt : nullptr));
     RESTART_CATCH
 }
 
@@ -453,6 +484,17 @@ extern "C" int sphb200_restart_read_fields(const sphb200_restart* r, uint64_t fi
     RESTART_CATCH
 }
 
+extern "C" int sphb200_restart_read_bytes(const sphb200_restart* r, const char* name, uint64_t first, uint64_t count,
+                                          uint8_t* out)
+{
+    RESTART_TRY
+    const BlockHeader* b = r->find(name, B_FIELD);
+    if (!b || b->type != T_BYTES) throw std::runtime_error(std::string("restart: field missing in ") + r->path + ": " + name);
+    if (first + count > b->count) throw std::runtime_error(std::string("restart: range beyond the end of field ") + b->name);
+    r->read(b->offset + first, out, count);
+    RESTART_CATCH
+}
+
 extern "C" int sphb200_restart_apply(const sphb200_restart* r, sphb200_sim* s)
 {
     RESTART_TRY
@@ -495,6 +537,16 @@ extern "C" int sphb200_restart_apply(const sphb200_restart* r, sphb200_sim* s)
         std::string rng(size_t(len), '\0');
         sphb200_restart_attribute(r, "rngEngineState", rng.data(), rng.size());
         RESTART_RC(sphb200_turb_set_state(t, phases.data(), rng.c_str()));
+    }
+
+    // HydroVeBdtProp::load (ve_hydro_bdt.hpp:155-168): optional, a dump of the global-time-step propagator has none
+    const BlockHeader* dtm1 = r->find("ts::dt_m1", B_ATTRIBUTE);
+    if (sphb200_sim_bdt_rungs(s) && dtm1 && r->i64("ts::numRungs", &iv))
+    {
+        if (dtm1->type != T_F32 || dtm1->count != 4) throw std::runtime_error("restart: ts::dt_m1 has the wrong shape");
+        float dt_m1[4];
+        r->read(dtm1->offset, dt_m1, sizeof(dt_m1));
+        RESTART_RC(sphb200_sim_bdt_restore(s, int(iv), dt_m1));
     }
     RESTART_CATCH
 }

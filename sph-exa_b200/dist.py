@@ -643,15 +643,22 @@ class DistHydroVeProp:
         for k in B.FIELD_NAMES:
             setattr(fs, k, None)
         keep = []
-        for k in self.CONSERVED:
+        for k in DistHydroVeProp.CONSERVED:
             a = np.ascontiguousarray(own[k])
             keep.append(a)
             setattr(fs, k, a.ctypes.data)
         p = restart.rank_path(path, self.rank, self.world)
         hc = self._hc()
-        B.check(B.lib.sphb200_restart_write(p.encode(), C.byref(info), C.byref(hc), None, self.rank, self.world,
-                                            C.byref(fs)))
+        bdt = self._restart_bdt(own)  # block-time-step propagators: ts:: attributes and the rung field
+        B.check(B.lib.sphb200_restart_write_bdt(p.encode(), C.byref(info), C.byref(hc), None, self.rank, self.world,
+                                                C.byref(fs), C.byref(bdt) if bdt is not None else None))
         return p
+
+    def _restart_bdt(self, own):
+        return None
+
+    def _restart_extra(self, files, pieces, arrays):
+        """load_restart hook: pieces = [(file, first, count, offset)] of this rank's slice"""
 
     def load_restart(self, path):
         """this rank's share of a dump written by any number of ranks (file_init.hpp:93-140); the next sync
@@ -669,14 +676,17 @@ class DistHydroVeProp:
             else:
                 first, count = restart.slice_for_rank(total, self.rank, self.world)
             real = np.float64 if self.dtype == B.F64 else np.float32
-            arrays = {k: np.empty(count, np.float64 if k in B.ALWAYS_F64 else real) for k in self.CONSERVED}
-            filled, start = 0, 0
+            arrays = {k: np.empty(count, np.float64 if k in B.ALWAYS_F64 else real)
+                      for k in DistHydroVeProp.CONSERVED}
+            filled, start, pieces = 0, 0, []
             for f, c in zip(files, counts):
                 lo, hi = max(first, start), min(first + count, start + c)
                 if hi > lo:
                     f.read_fields(lo - start, hi - lo, self.dtype, arrays, offset=filled)
+                    pieces.append((f, lo - start, hi - lo, filled))
                     filled += hi - lo
                 start += c
+            self._restart_extra(files, pieces, arrays)
             info = files[0].info
             self.n_global = total
             self.minDt, self.minDt_m1, self.ttot = info.minDt, info.minDt_m1, info.time

@@ -13,6 +13,7 @@ import ctypes as C
 
 import numpy as np
 
+from .binding import RestartBdt
 from .dist import DistHydroVeProp
 
 MAX_RUNGS = 4  # Timestep::maxNumRungs (sph/include/sph/timestep.h:44)
@@ -81,11 +82,25 @@ class DistHydroVeBdtProp(DistHydroVeProp):
         self.f["rung"] = (t.zeros(n, dtype=t.int32, device=self.dev) if rung is None
                           else t.from_numpy(np.ascontiguousarray(rung, np.int32)).to(self.dev))
 
-    def save_restart(self, path, iteration):
-        raise NotImplementedError("restart files of the block-time-step propagator are not implemented")
+    # ---- HydroVeBdtProp::save / load (ve_hydro_bdt.hpp:153-168): Timestep::loadOrStore with the prefix "ts::"
+    def _restart_bdt(self, own):
+        rung = np.ascontiguousarray(own["rung"], np.uint8)
+        self._keep_rung = rung  # the struct holds a raw pointer
+        return RestartBdt(int(self.ts.numRungs), (C.c_float * MAX_RUNGS)(*self.ts.dt_m1), rung.ctypes.data)
 
-    def load_restart(self, path):
-        raise NotImplementedError("restart files of the block-time-step propagator are not implemented")
+    def _restart_extra(self, files, pieces, arrays):
+        count = len(arrays["x"])
+        if not all(f.has_field("rung") for f in files):
+            return  # a dump of the global-time-step propagator: rung 0 everywhere, time-step record as constructed
+        rung = np.zeros(count, np.uint8)
+        for f, first, cnt, offset in pieces:
+            f.read_bytes("rung", first, cnt, rung, offset=offset)
+        arrays["rung"] = rung
+        self.ts = Timestep()
+        self.ts.numRungs = int(files[0].attribute("ts::numRungs", np.int64)[0])
+        self.ts.dt_m1[:] = files[0].attribute("ts::dt_m1", np.float32)
+        self.prev = self.ts.copy()
+        self._halo_layout = False
 
     def isSynced(self):
         """Propagator::isSynced (ve_hydro_bdt.hpp:220)"""

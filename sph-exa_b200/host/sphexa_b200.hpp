@@ -251,6 +251,13 @@ public:
         }
         check(sphb200_restart_read_fields(r, first, count, dtype, &h));
         check(sphb200_sim_upload(sim_, count, &h));
+        // block time steps: the conserved field "rung" (ve_hydro_bdt.hpp:94), absent in dumps of HydroVeProp
+        if (sphb200_sim_bdt_rungs(sim_) && sphb200_restart_read_bytes(r, "rung", 0, 0, nullptr) == 0)
+        {
+            std::vector<uint8_t> rung(std::max<uint64_t>(count, 1));
+            check(sphb200_restart_read_bytes(r, "rung", first, count, rung.data()));
+            check(sphb200_sim_bdt_upload_rungs(sim_, rung.data(), count));
+        }
         ctx_.sync();
         check(sphb200_restart_apply(r, sim_));
         return info.iteration;

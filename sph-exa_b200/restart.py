@@ -95,6 +95,15 @@ class RestartFile:
         check(lib.sphb200_restart_read_fields(self.h, C.c_uint64(first), C.c_uint64(count), C.c_int(dtype),
                                               C.byref(f)))
 
+    def has_field(self, name):
+        return lib.sphb200_restart_read_bytes(self.h, name.encode(), C.c_uint64(0), C.c_uint64(0), None) == 0
+
+    def read_bytes(self, name, first, count, out, offset=0):
+        """particles [first, first+count) of a byte field ("rung") into out[offset:]"""
+        dst = out[offset:offset + count]
+        check(lib.sphb200_restart_read_bytes(self.h, name.encode(), C.c_uint64(first), C.c_uint64(count),
+                                             dst.ctypes.data_as(vp)))
+
     def apply(self, sim):
         """time, time steps, constants, box and turbulence state -> sim"""
         check(lib.sphb200_restart_apply(self.h, sim.h))
@@ -124,15 +133,22 @@ def load(sim, path, rank=0, num_ranks=1):
             first, count = slice_for_rank(total, rank, num_ranks)
         real = sim.real
         arrays = {n: np.empty(count, np.float64 if n in B.ALWAYS_F64 else real) for n in B.CONSERVED}
+        # "rung" is a conserved field of the block-time-step propagators only (ve_hydro_bdt.hpp:94)
+        bdt = hasattr(sim, "uploadRungs") and all(f.has_field("rung") for f in files)
+        rung = np.zeros(count, np.uint8) if bdt else None
         filled, start = 0, 0
         for f, c in zip(files, counts):
             lo, hi = max(first, start), min(first + count, start + c)
             if hi > lo:
                 f.read_fields(lo - start, hi - lo, sim.dtype, arrays, offset=filled)
+                if bdt:
+                    f.read_bytes("rung", lo - start, hi - lo, rung, offset=filled)
                 filled += hi - lo
             start += c
         assert filled == count
         sim.upload(arrays)
+        if bdt:
+            sim.uploadRungs(rung)
         files[0].apply(sim)
         return int(files[0].info.iteration), n_glob
     finally:

@@ -263,6 +263,11 @@ class HydroVeBdtProp(HydroVeProp):
         p = lib.sphb200_sim_bdt_rungs(self.h)
         return self._d2h(p + self.startIndex, self.endIndex - self.startIndex, np.uint8)
 
+    def uploadRungs(self, rung):
+        """rung of the particles of the last upload() (restart: the conserved field "rung", ve_hydro_bdt.hpp:94)"""
+        rung = np.ascontiguousarray(rung, np.uint8)
+        check(lib.sphb200_sim_bdt_upload_rungs(self.h, rung.ctypes.data_as(C.c_void_p), C.c_size_t(rung.size)))
+
     def groupDt(self):
         return self._d2h(lib.sphb200_sim_bdt_group_dt(self.h), self.timestep().numGroups, np.float32)
 

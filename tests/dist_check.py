@@ -223,6 +223,39 @@ def main_bdt(args, pkg):
     if rank == 0:
         ok = ok and partial >= 3 and max(rungs_seen) >= 2
         one.close()
+
+    # ---- restart (HydroVeBdtProp::save / load, ve_hydro_bdt.hpp:153-168): dump where the hierarchy is synced, reload
+    # on the same ranks, run one more hierarchy on both
+    import tempfile
+    extra = 0
+    while not sim.isSynced():
+        sim.step()
+        extra += 1
+    base = [tempfile.mkdtemp(prefix="sphb200_restart_") if rank == 0 else None]
+    dist.broadcast_object_list(base, 0)
+    path = os.path.join(base[0], "dump")
+    sim.save_restart(path, args.steps + extra)
+    dist.barrier()
+    again = DistHydroVeBdtProp(pkg, ctx, box, s, B.F64, rank, world, n)
+    it = again.load_restart(path)
+    same = (it == args.steps + extra and again.ts.numRungs == sim.ts.numRungs
+            and np.array_equal(again.ts.dt_m1, sim.ts.dt_m1) and again.isSynced()
+            and (again.minDt, again.ttot) == (sim.minDt, sim.ttot))
+    for p in (sim, again):
+        p.step()
+        while not p.isSynced():
+            p.step()
+    a, b = sim.download_owned(), again.download_owned()
+    same = same and all(a[k].shape == b[k].shape and np.array_equal(a[k], b[k]) for k in a)
+    same = same and (again.ts.numRungs, again.minDt, again.ttot) == (sim.ts.numRungs, sim.minDt, sim.ttot)
+    flags = [None] * world
+    dist.all_gather_object(flags, bool(same))
+    if rank == 0:
+        print(f"bdt restart on {world} ranks ({sim.ts.numRungs} rungs after), bit-identical per rank: {flags}",
+              flush=True)
+        ok = ok and all(flags)
+        import shutil
+        shutil.rmtree(base[0], ignore_errors=True)
     flag = torch.tensor([1 if ok else 0], device="cuda")
     dist.broadcast(flag, 0)
     dist.barrier()

@@ -98,3 +98,61 @@ def test_restart_into_other_precision(pkg, ctx, tmp_path):
     c.close()
     for k in B.CONSERVED:
         assert np.array_equal(got[k], want[k]), k
+
+
+def test_block_time_step_restart(pkg, ctx, tmp_path):
+    """HydroVeBdtProp::save / load (ve_hydro_bdt.hpp:153-168): a dump written where the hierarchy is synced carries
+    ts::numRungs, ts::dt_m1 and the conserved field "rung"; the reloaded run starts a new hierarchy from them."""
+    from sph_exa_b200 import sim as S, restart, binding as B
+    f, box, s = pkg.ic.sedov(16, "f64")
+    n = f["x"].size
+    a = S.HydroVeBdtProp(ctx, box, s, capacity=n, dtype=pkg.F64)
+    a.upload(f)
+    # run until at least two hierarchies with more than one rung are complete
+    hierarchies, steps = 0, 0
+    while hierarchies < 3 or not a.isSynced():
+        a.step()
+        steps += 1
+        if a.isSynced():
+            hierarchies += 1
+        assert steps < 200
+    ts = a.timestep()
+    assert ts.numRungs > 1
+    path = str(tmp_path / "bdt")
+    restart.save(a, path, iteration=steps, num_particles_global=n)
+    rung_a = a.rungs()
+    with restart.RestartFile(path) as rf:
+        assert rf.attribute("ts::numRungs", np.int64)[0] == ts.numRungs
+        assert list(rf.attribute("ts::dt_m1", np.float32)) == list(ts.dt_m1)
+        got = np.empty(n, np.uint8)
+        rf.read_bytes("rung", 0, n, got)
+        assert np.array_equal(got, rung_a)
+
+    def advance(p):
+        # one full hierarchy
+        p.step()
+        k = 1
+        while not p.isSynced():
+            p.step()
+            k += 1
+        return k
+
+    ka = advance(a)
+    want = a.download(with_keys=True)
+
+    b = S.HydroVeBdtProp(ctx, box, s, capacity=n, dtype=pkg.F64)
+    it, n_glob = restart.load(b, path)
+    assert (it, n_glob) == (steps, n)
+    tb = b.timestep()
+    assert (tb.numRungs, list(tb.dt_m1), tb.substep) == (ts.numRungs, list(ts.dt_m1), 0)
+    kb = advance(b)
+    assert ka == kb
+    got = b.download(with_keys=True)
+    for k in list(B.CONSERVED) + ["keys"]:
+        assert np.array_equal(got[k], want[k]), k
+    assert np.array_equal(b.rungs(), a.rungs())
+    ta, tb = a.timestep(), b.timestep()
+    assert (ta.numRungs, list(ta.dt_m1), ta.totDt) == (tb.numRungs, list(tb.dt_m1), tb.totDt)
+    assert (b.minDt, b.ttot) == (a.minDt, a.ttot)
+    a.close()
+    b.close()

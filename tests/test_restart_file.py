@@ -149,3 +149,42 @@ def test_turbulence_state_in_file(pkg, ctx, tmp_path):
         assert f.attribute("turbulence::variance")[0] == st["variance"]
         rng = bytes(f.attribute("rngEngineState", np.uint8)).rstrip(b"\0").decode()
         assert rng == t.rngState()
+
+
+def test_block_time_step_state_round_trip(pkg, tmp_path):
+    """ts::numRungs, ts::dt_m1 (Timestep::loadOrStore, sph/include/sph/timestep.h:29-33) and the byte field "rung"
+    (conserved field of HydroVeBdtProp, ve_hydro_bdt.hpp:94)"""
+    B = pkg.binding
+    from sph_exa_b200 import restart
+
+    n = 777
+    arrays = make_fields(B, n, np.float64)
+    rung = (np.arange(n) % 4).astype(np.uint8)
+    info = B.RestartInfo()
+    info.iteration, info.numParticlesGlobal, info.numParticles, info.dtype = 3, n, n, B.F64
+    info.box = pkg.make_box([0, 1, 0, 1, 0, 1], [1, 1, 1])
+    hc = B.HydroConst()
+    f = B.Fields()
+    for name in B.FIELD_NAMES:
+        setattr(f, name, None)
+    for name, a in arrays.items():
+        setattr(f, name, a.ctypes.data)
+    bdt = B.RestartBdt(3, (C.c_float * 4)(1e-3, 2e-3, 4e-3, 0.0), rung.ctypes.data)
+    p = str(tmp_path / "bdt.bin")
+    B.check(B.lib.sphb200_restart_write_bdt(p.encode(), C.byref(info), C.byref(hc), None, 0, 1, C.byref(f),
+                                            C.byref(bdt)))
+    with restart.RestartFile(p) as rf:
+        assert rf.attribute("ts::numRungs", np.int64)[0] == 3
+        assert list(rf.attribute("ts::dt_m1", np.float32)) == list(np.float32([1e-3, 2e-3, 4e-3, 0.0]))
+        assert rf.has_field("rung")
+        got = np.full(100, 255, np.uint8)
+        rf.read_bytes("rung", 600, 100, got)
+        assert np.array_equal(got, rung[600:700])
+        with pytest.raises(B.SphError):
+            rf.read_bytes("rung", 700, 100, got)
+    # a dump of the global-time-step propagator has no rung field
+    q = str(tmp_path / "plain.bin")
+    write_file(pkg, q, arrays, B.F64)
+    with restart.RestartFile(q) as rf:
+        assert not rf.has_field("rung")
+        assert rf.attribute("ts::numRungs", np.int64) is None
