@@ -105,6 +105,7 @@ struct sphb200_ctx
     float searchExtFactor      = 1.0f;
     void* scopeDtParticle      = nullptr;
     uint8_t* scopeGather       = nullptr;
+    bool hilbertTabReady       = false; // sfc.cu: the 3-level Hilbert transition table is on this device
 };
 
 namespace sphb200

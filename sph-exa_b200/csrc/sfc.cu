@@ -1,6 +1,8 @@
 // SFC layer: 63-bit Hilbert keys, node geometry, bounding box reduction.
 // Compiled with --fmad=false: integer coordinates and node centers must match the
 // reference CPU build (compiled -ffp-contract=off) bit for bit.
+#include <algorithm>
+
 #include "common.cuh"
 
 namespace sphb200
@@ -103,8 +105,9 @@ __device__ __forceinline__ unsigned iCoord(double x, double xmin, double m)
     return unsigned(max(ix, 0)); // reference asserts ix >= 0
 }
 
-/*! @brief one thread per particle, grid-stride; 24 B read + 8 B written per particle (HBM-bound) */
-__global__ void __launch_bounds__(256) sfcKeysKernel(const double* __restrict__ x, const double* __restrict__ y,
+/*! @brief one thread per particle, grid-stride, bit recurrence: ~650 integer instructions per key, ALU-bound
+ *         (ncu: alu pipe 96 %).  Used for short ranges, where loading the transition table does not pay. */
+__global__ void __launch_bounds__(256) sfcKeysBitwiseKernel(const double* __restrict__ x, const double* __restrict__ y,
                                                      const double* __restrict__ z, size_t n, KeyParams p,
                                                      KeyType* __restrict__ keys)
 {
@@ -190,6 +193,137 @@ __global__ void __launch_bounds__(256) minmax3Kernel(const double* __restrict__ 
     }
 }
 
+// ---------------------------------------------------------------- table-driven Hilbert keys
+/* The recurrence of hilbertKey only ever applies an axis permutation and per-axis complements to the low bits, so the
+ * remaining work at any level is a function of (state, octant) with state = one of the 24 signed axis permutations
+ * reachable from the identity.  Three levels at a time: entry [state][x3 y3 z3] = 9 key bits | next state << 9,
+ * 24 * 512 uint16 = 24 KB in shared memory; 7 lookups per key instead of 21 rounds of bit logic. */
+//! @brief bank swizzle of the table index: lanes of a warp tend to share y3, z3 (particles along a lattice row, one
+//!        leaf) and differ in x3 and the state, which would all fall into one bank (bits 6.. of a uint16 index)
+__host__ __device__ inline unsigned hilbertSwizzle(unsigned idx) { return idx ^ ((idx >> 5) & 0x3Eu); }
+
+constexpr int kHilbertStates  = 24;
+constexpr int kHilbertTabSize = kHilbertStates * 512;
+__device__ uint16_t gHilbertTab[kHilbertTabSize];
+
+namespace
+{
+
+struct HilbertState
+{
+    int perm[3]; // current axis a reads original axis perm[a] ...
+    int flip[3]; // ... complemented when flip[a]
+    bool operator==(const HilbertState& o) const
+    {
+        return std::equal(perm, perm + 3, o.perm) && std::equal(flip, flip + 3, o.flip);
+    }
+};
+
+//! @brief one level of hilbertKey on the original octant bits under @p s: Hilbert digit and the state of the levels below
+int hilbertLevel(const HilbertState& s, const int orig[3], HilbertState& next)
+{
+    constexpr int digitOf[8] = {0, 1, 3, 2, 7, 6, 4, 5};
+    int xi = orig[s.perm[0]] ^ s.flip[0], yi = orig[s.perm[1]] ^ s.flip[1], zi = orig[s.perm[2]] ^ s.flip[2];
+    int nyi = yi ^ 1, nzi = zi ^ 1;
+    int f[3]   = {xi & (nyi | zi), (xi & (yi | zi)) | (yi & nzi), (xi & nyi & nzi) | (yi & nzi)};
+    int rot[3] = {1, 2, 0}, swp[3] = {2, 1, 0}, idn[3] = {0, 1, 2};
+    const int* sig = zi ? rot : (!yi ? swp : idn); // new axis a = old axis sig[a]
+    for (int a = 0; a < 3; ++a)
+    {
+        next.perm[a] = s.perm[sig[a]];
+        next.flip[a] = s.flip[sig[a]] ^ f[sig[a]];
+    }
+    return digitOf[(xi << 2) | (yi << 1) | zi];
+}
+
+std::vector<uint16_t> buildHilbertTable()
+{
+    std::vector<HilbertState> states{HilbertState{{0, 1, 2}, {0, 0, 0}}};
+    auto idOf = [&](const HilbertState& s)
+    {
+        for (size_t k = 0; k < states.size(); ++k)
+            if (states[k] == s) return int(k);
+        states.push_back(s);
+        return int(states.size()) - 1;
+    };
+    for (size_t k = 0; k < states.size(); ++k) // closure of the identity under the 8 octant transitions
+        for (int o = 0; o < 8; ++o)
+        {
+            int orig[3] = {(o >> 2) & 1, (o >> 1) & 1, o & 1};
+            HilbertState next;
+            hilbertLevel(HilbertState(states[k]), orig, next);
+            idOf(next);
+        }
+    if (int(states.size()) != kHilbertStates) throw std::runtime_error("sfc: unexpected number of Hilbert states");
+
+    std::vector<uint16_t> tab(kHilbertTabSize);
+    for (int st = 0; st < kHilbertStates; ++st)
+        for (int in = 0; in < 512; ++in)
+        {
+            int x3 = in >> 6, y3 = (in >> 3) & 7, z3 = in & 7;
+            HilbertState cur = states[st];
+            int digits       = 0;
+            for (int b = 2; b >= 0; --b)
+            {
+                int orig[3] = {(x3 >> b) & 1, (y3 >> b) & 1, (z3 >> b) & 1};
+                HilbertState next;
+                digits = (digits << 3) | hilbertLevel(cur, orig, next);
+                cur    = next;
+            }
+            tab[hilbertSwizzle(unsigned(st * 512 + in))] = uint16_t(digits | (idOf(cur) << 9));
+        }
+    return tab;
+}
+
+} // namespace
+
+/*! @brief Hilbert keys through the transition table; same keys as sfcKeysBitwiseKernel
+ *
+ * 24 B read + 8 B written per particle.  Per key: 3 coordinate conversions, 7 shared-memory lookups with ~12 integer
+ * instructions each.  The entry keeps the next state in bits 9..15, i.e. already shifted to its place in the index.
+ */
+__global__ void __launch_bounds__(256) sfcKeysKernel(const double* __restrict__ x, const double* __restrict__ y,
+                                                     const double* __restrict__ z, size_t n, KeyParams p,
+                                                     KeyType* __restrict__ keys)
+{
+    __shared__ __align__(16) uint16_t tab[kHilbertTabSize];
+    {
+        const uint4* src = reinterpret_cast<const uint4*>(gHilbertTab);
+        uint4* dst       = reinterpret_cast<uint4*>(tab);
+        for (int k = threadIdx.x; k < kHilbertTabSize / 8; k += blockDim.x)
+            dst[k] = src[k];
+    }
+    __syncthreads();
+    size_t stride = size_t(gridDim.x) * blockDim.x;
+    for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride)
+    {
+        unsigned ix = iCoord(x[i], p.xmin, p.mx);
+        unsigned iy = iCoord(y[i], p.ymin, p.my);
+        unsigned iz = iCoord(z[i], p.zmin, p.mz);
+        // groups of three levels, top first; x3 lands in bits 6..8, y3 in 3..5, z3 in 0..2 of the index
+        unsigned e, idx;
+        unsigned part[3]; // 27 + 27 + 9 key bits
+#pragma unroll
+        for (int q = 0; q < 3; ++q)
+        {
+            unsigned acc = 0;
+#pragma unroll
+            for (int g = (q == 0 ? 6 : (q == 1 ? 3 : 0)); g >= (q == 0 ? 4 : (q == 1 ? 1 : 0)); --g)
+            {
+                unsigned xs = (3 * g >= 6) ? (ix >> (3 * g - 6)) : (ix << (6 - 3 * g));
+                unsigned ys = (3 * g >= 3) ? (iy >> (3 * g - 3)) : (iy << (3 - 3 * g));
+                unsigned zs = iz >> (3 * g);
+                idx         = (xs & 0x1C0u) | (ys & 0x38u) | (zs & 7u);
+                if (g != 6) idx |= e & 0xFE00u;
+                e   = tab[hilbertSwizzle(idx)];
+                acc = (acc << 9) | (e & 511u);
+            }
+            part[q] = acc;
+        }
+        keys[i] = (KeyType(part[0]) << 36) | (KeyType(part[1]) << 9) | KeyType(part[2]);
+    }
+}
+
 } // namespace sphb200
 
 using namespace sphb200;
@@ -204,8 +338,19 @@ extern "C" int sphb200_sfc_keys(sphb200_ctx* ctx, const double* x, const double*
         // sfc.hpp:188-192: cubeLength * box.ilx() evaluated once on the host, in double
         KeyParams p{box->lim[0], box->lim[2], box->lim[4], cubeLength * box->inv[0], cubeLength * box->inv[1],
                     cubeLength * box->inv[2]};
-        int grid = persistentGrid(n, 256, 16);
-        SPHB200_LAUNCH(ctx, sfcKeysKernel, grid, 256, 0, x, y, z, n, p, keys);
+        if (n < size_t(1) << 16)
+        {
+            SPHB200_LAUNCH(ctx, sfcKeysBitwiseKernel, persistentGrid(n, 256, 16), 256, 0, x, y, z, n, p, keys);
+            return 0;
+        }
+        if (!ctx->hilbertTabReady)
+        {
+            static const std::vector<uint16_t> table = buildHilbertTable();
+            SPHB200_CUDA(cudaMemcpyToSymbolAsync(gHilbertTab, table.data(), kHilbertTabSize * sizeof(uint16_t), 0,
+                                                 cudaMemcpyHostToDevice, ctx->stream));
+            ctx->hilbertTabReady = true;
+        }
+        SPHB200_LAUNCH(ctx, sfcKeysKernel, persistentGrid(n, 256, 8), 256, 0, x, y, z, n, p, keys);
         return 0;
     }
     catch (std::exception& e)

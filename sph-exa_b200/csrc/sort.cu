@@ -139,117 +139,268 @@ void exclusiveScan(sphb200_ctx* ctx, const uint32_t* in, uint32_t* out, size_t n
 }
 
 // ---------------------------------------------------------------- radix sort
-constexpr int kSortThreads = 256;
-constexpr int kSortWarps   = kSortThreads / 32;
-constexpr int kSortItems   = 16;                        // keys per thread
-constexpr int kSortTile    = kSortThreads * kSortItems; // 4096 keys per CTA
 constexpr int kRadixBits   = 8;
 constexpr int kRadix       = 1 << kRadixBits;
+constexpr int kSortTile    = 4096; // keys per CTA, count and scatter kernels alike
+constexpr int kCountThreads = 256;
+constexpr int kCountItems   = kSortTile / kCountThreads;
+constexpr int kSortThreads = 512;
+constexpr int kSortWarps   = kSortThreads / 32;
+constexpr int kSortItems   = kSortTile / kSortThreads; // keys per thread
+static_assert(kCountThreads == kRadix, "one histogram bin per thread");
+
+// shared memory of the scatter kernel (dynamic, above the 48 KB static limit)
+constexpr size_t kStageKeysOff = 0;
+constexpr size_t kStageValsOff = kStageKeysOff + kSortTile * sizeof(KeyType);
+constexpr size_t kWarpHistOff  = kStageValsOff + kSortTile * sizeof(uint32_t);
+constexpr size_t kBinDeltaOff  = kWarpHistOff + kSortWarps * kRadix * sizeof(uint16_t);
+constexpr size_t kScanOff      = kBinDeltaOff + kRadix * sizeof(uint32_t);
+constexpr size_t kScatterSmem  = kScanOff + 36 * sizeof(uint32_t);
 
 //! @brief per-tile digit histogram, written digit-major: hist[digit * numTiles + tile]
-__global__ void __launch_bounds__(kSortThreads) radixCountKernel(const KeyType* __restrict__ keys, size_t n, int shift,
-                                                                 uint32_t* __restrict__ hist, int numTiles)
+__global__ void __launch_bounds__(kCountThreads) radixCountKernel(const KeyType* __restrict__ keys, size_t n, int shift,
+                                                                  uint32_t* __restrict__ hist, int numTiles)
 {
     __shared__ uint32_t sh[kRadix];
-    sh[threadIdx.x] = 0; // kSortThreads == kRadix
+    sh[threadIdx.x] = 0;
     __syncthreads();
     size_t base = size_t(blockIdx.x) * kSortTile;
-#pragma unroll 4
-    for (int k = 0; k < kSortItems; ++k)
+    if (base + kSortTile <= n && (reinterpret_cast<uintptr_t>(keys) & 15) == 0)
     {
-        size_t i = base + size_t(k) * kSortThreads + threadIdx.x;
-        if (i < n) atomicAdd(&sh[(keys[i] >> shift) & (kRadix - 1)], 1u);
+        // all loads of the tile in flight before the first shared-memory atomic
+        const ulonglong2* k2 = reinterpret_cast<const ulonglong2*>(keys + base);
+        ulonglong2 v[kCountItems / 2];
+#pragma unroll
+        for (int k = 0; k < kCountItems / 2; ++k)
+            v[k] = k2[k * kCountThreads + threadIdx.x];
+#pragma unroll
+        for (int k = 0; k < kCountItems / 2; ++k)
+        {
+            atomicAdd(&sh[(v[k].x >> shift) & (kRadix - 1)], 1u);
+            atomicAdd(&sh[(v[k].y >> shift) & (kRadix - 1)], 1u);
+        }
+    }
+    else
+    {
+        for (int k = 0; k < kCountItems; ++k)
+        {
+            size_t i = base + size_t(k) * kCountThreads + threadIdx.x;
+            if (i < n) atomicAdd(&sh[(keys[i] >> shift) & (kRadix - 1)], 1u);
+        }
     }
     __syncthreads();
     hist[size_t(threadIdx.x) * numTiles + blockIdx.x] = sh[threadIdx.x];
 }
 
-/*! @brief stable scatter of one tile
+/*! @brief stable scatter of one tile, staged through shared memory
  *
  * Order inside a tile is (warp, chunk, lane); each warp ranks its 32-key chunks with
  * __match_any_sync (peers with the same digit), keeping a private digit counter row in
  * shared memory, so no atomics are needed and the ranking is deterministic and stable.
+ *
+ * Keys and payload are then placed at their slot of the digit-sorted tile in shared memory, and slot s
+ * goes to binStart[d] + (s - tileStart[d]): consecutive threads write consecutive addresses inside a
+ * digit's run (4096 keys over 256 digits: runs of ~16 keys = 128 B) instead of 32 scattered 8-byte
+ * stores per warp instruction.  Full = the tile has all kSortTile keys (every tile but the last).
  */
-__global__ void __launch_bounds__(kSortThreads)
-    radixScatterKernel(const KeyType* __restrict__ keysIn, const uint32_t* __restrict__ valsIn,
-                       KeyType* __restrict__ keysOut, uint32_t* __restrict__ valsOut, size_t n, int shift,
-                       const uint32_t* __restrict__ scannedHist, int numTiles)
+template<bool Full>
+__device__ __forceinline__ void radixScatterTile(const KeyType* __restrict__ keysIn, const uint32_t* __restrict__ valsIn,
+                                                 KeyType* __restrict__ keysOut, uint32_t* __restrict__ valsOut, size_t n,
+                                                 int shift, const uint32_t* __restrict__ rowScan,
+                                                 const uint32_t* __restrict__ rowTotal, int numTiles)
 {
-    __shared__ uint32_t warpHist[kSortWarps][kRadix];
+    extern __shared__ __align__(16) unsigned char sortSmem[];
+    KeyType* stageK    = reinterpret_cast<KeyType*>(sortSmem + kStageKeysOff);
+    uint32_t* stageV   = reinterpret_cast<uint32_t*>(sortSmem + kStageValsOff);
+    uint16_t* warpHist = reinterpret_cast<uint16_t*>(sortSmem + kWarpHistOff); // [kSortWarps][kRadix]
+    uint32_t* binDelta = reinterpret_cast<uint32_t*>(sortSmem + kBinDeltaOff); // global run start - start in the tile
+    uint32_t* scanSmem = reinterpret_cast<uint32_t*>(sortSmem + kScanOff);
+
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
-    for (int k = threadIdx.x; k < kSortWarps * kRadix; k += kSortThreads)
-        (&warpHist[0][0])[k] = 0;
-    __syncthreads();
+    const int tile = blockIdx.x;
+    // this tile's offset inside the run of digit threadIdx.x and the size of the whole run: needed after the ranking
+    uint32_t inRow = 0, rowSize = 0;
+    if (threadIdx.x < kRadix)
+    {
+        inRow   = rowScan[size_t(threadIdx.x) * numTiles + tile];
+        rowSize = rowTotal[threadIdx.x];
+    }
+    {
+        uint32_t* z = reinterpret_cast<uint32_t*>(warpHist);
+        for (int k = threadIdx.x; k < kSortWarps * kRadix / 2; k += kSortThreads)
+            z[k] = 0;
+    }
 
-    const size_t warpBase = size_t(blockIdx.x) * kSortTile + size_t(warp) * (32 * kSortItems);
+    const size_t tileBase    = size_t(tile) * kSortTile;
+    const uint32_t tileCount = Full ? uint32_t(kSortTile) : uint32_t(n - tileBase);
+    const uint32_t warpOff   = uint32_t(warp) * (32 * kSortItems) + lane;
+    const KeyType* kIn       = keysIn + tileBase;
     KeyType key[kSortItems];
-    uint32_t rank[kSortItems];
-    const unsigned ltMask = (1u << lane) - 1;
+    uint32_t val[kSortItems];
+    uint16_t rank[kSortItems];
 
 #pragma unroll
     for (int c = 0; c < kSortItems; ++c)
     {
-        size_t i      = warpBase + size_t(c) * 32 + lane;
-        bool valid    = i < n;
-        key[c]        = valid ? keysIn[i] : ~KeyType(0);
-        unsigned d    = (key[c] >> shift) & (kRadix - 1);
-        unsigned act  = __ballot_sync(0xffffffffu, valid);
-        unsigned peer = __match_any_sync(0xffffffffu, valid ? d : (kRadix + lane)) & act;
-        if (valid)
+        uint32_t e = warpOff + c * 32;
+        key[c]     = (Full || e < tileCount) ? kIn[e] : ~KeyType(0);
+    }
+#pragma unroll
+    for (int c = 0; c < kSortItems; ++c)
+    {
+        uint32_t e = warpOff + c * 32;
+        if (valsIn) { val[c] = (Full || e < tileCount) ? valsIn[tileBase + e] : 0u; }
+        else { val[c] = uint32_t(tileBase) + e; }
+    }
+    __syncthreads();
+
+    const unsigned ltMask = (1u << lane) - 1;
+    uint16_t* myHist      = warpHist + warp * kRadix;
+#pragma unroll
+    for (int c = 0; c < kSortItems; ++c)
+    {
+        bool valid    = Full || (warpOff + c * 32 < tileCount);
+        unsigned d    = unsigned(key[c] >> shift) & (kRadix - 1);
+        // lanes holding the same digit: one ballot per digit bit (__match_any_sync serialises over the distinct
+        // values of the warp, ~110 cycles of the ADU pipe when all 32 digits differ)
+        unsigned peer = Full ? 0xffffffffu : __ballot_sync(0xffffffffu, valid);
+#pragma unroll
+        for (int b = 0; b < kRadixBits; ++b)
         {
-            int leader    = __ffs(peer) - 1;
-            uint32_t base = 0;
-            if (lane == leader)
-            {
-                base           = warpHist[warp][d];
-                warpHist[warp][d] = base + __popc(peer);
-            }
-            base    = __shfl_sync(peer, base, leader);
-            rank[c] = base + __popc(peer & ltMask);
+            bool bit   = (d >> b) & 1u;
+            unsigned m = __ballot_sync(0xffffffffu, bit);
+            peer &= bit ? m : ~m;
         }
+        // the first lane of every peer group bumps the warp's counter of that digit; full-mask shuffle (a shuffle
+        // under the peer masks would be issued once per group)
+        int leader    = valid ? __ffs(peer) - 1 : lane;
+        uint32_t base = 0;
+        if (valid && lane == leader)
+        {
+            base      = myHist[d];
+            myHist[d] = uint16_t(base + __popc(peer));
+        }
+        base    = __shfl_sync(0xffffffffu, base, leader);
+        rank[c] = uint16_t(base + __popc(peer & ltMask));
         __syncwarp();
     }
     __syncthreads();
     {
-        // digit = threadIdx.x: exclusive scan over the warps of this tile on top of the global offset
-        int d            = threadIdx.x;
-        uint32_t running = scannedHist[size_t(d) * numTiles + blockIdx.x];
-#pragma unroll
-        for (int w = 0; w < kSortWarps; ++w)
+        // digit = threadIdx.x: exclusive scan over the warps of this tile, on top of the digit's start inside the tile
+        int d          = threadIdx.x;
+        uint32_t total = 0;
+        if (d < kRadix)
         {
-            uint32_t t     = warpHist[w][d];
-            warpHist[w][d] = running;
-            running += t;
+#pragma unroll
+            for (int w = 0; w < kSortWarps; ++w)
+                total += warpHist[w * kRadix + d];
+        }
+        uint32_t blockTotal;
+        uint32_t tileStart = blockExclusiveScan(total, scanSmem, &blockTotal);
+        uint32_t digitBase = blockExclusiveScan(rowSize, scanSmem, &blockTotal); // start of the digit's run in the output
+        if (d < kRadix)
+        {
+            uint32_t running = tileStart;
+#pragma unroll
+            for (int w = 0; w < kSortWarps; ++w)
+            {
+                uint32_t t               = warpHist[w * kRadix + d];
+                warpHist[w * kRadix + d] = uint16_t(running);
+                running += t;
+            }
+            binDelta[d] = digitBase + inRow - tileStart;
         }
     }
     __syncthreads();
 #pragma unroll
     for (int c = 0; c < kSortItems; ++c)
     {
-        size_t i = warpBase + size_t(c) * 32 + lane;
-        if (i < n)
+        if (Full || (warpOff + c * 32 < tileCount))
         {
-            unsigned d    = (key[c] >> shift) & (kRadix - 1);
-            uint32_t pos  = warpHist[warp][d] + rank[c];
-            keysOut[pos]  = key[c];
-            valsOut[pos]  = valsIn ? valsIn[i] : uint32_t(i);
+            unsigned d    = unsigned(key[c] >> shift) & (kRadix - 1);
+            uint32_t slot = uint32_t(myHist[d]) + rank[c];
+            stageK[slot]  = key[c];
+            stageV[slot]  = val[c];
         }
     }
+    __syncthreads();
+#pragma unroll
+    for (int c = 0; c < kSortItems; ++c)
+    {
+        uint32_t sl = uint32_t(c) * kSortThreads + threadIdx.x;
+        if (Full || sl < tileCount)
+        {
+            KeyType k    = stageK[sl];
+            uint32_t pos = binDelta[unsigned(k >> shift) & (kRadix - 1)] + sl;
+            keysOut[pos] = k;
+            valsOut[pos] = stageV[sl];
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kSortThreads, 2)
+    radixScatterKernel(const KeyType* __restrict__ keysIn, const uint32_t* __restrict__ valsIn,
+                       KeyType* __restrict__ keysOut, uint32_t* __restrict__ valsOut, size_t n, int shift,
+                       const uint32_t* __restrict__ rowScan, const uint32_t* __restrict__ rowTotal, int numTiles)
+{
+    // the last tile may be ragged: same launch, predicated body
+    if (size_t(blockIdx.x + 1) * kSortTile <= n)
+        radixScatterTile<true>(keysIn, valsIn, keysOut, valsOut, n, shift, rowScan, rowTotal, numTiles);
+    else
+        radixScatterTile<false>(keysIn, valsIn, keysOut, valsOut, n, shift, rowScan, rowTotal, numTiles);
+}
+
+/*! @brief exclusive scan of every digit row of the tile histogram (in place) and the row totals
+ *
+ * hist is digit-major [kRadix][numTiles]: one CTA per digit.  The scatter kernel turns the 256 row totals into the
+ * digit bases itself, so a pass needs three launches (count, row scan, scatter).
+ */
+__global__ void __launch_bounds__(kScanThreads) radixRowScanKernel(uint32_t* __restrict__ hist, int numTiles,
+                                                                   uint32_t* __restrict__ rowTotal)
+{
+    __shared__ uint32_t smem[33];
+    uint32_t* row    = hist + size_t(blockIdx.x) * numTiles;
+    uint32_t carry   = 0;
+    for (int base = 0; base < numTiles; base += kScanTile)
+    {
+        int i0 = base + threadIdx.x * kScanItems;
+        uint32_t v[kScanItems];
+        uint32_t sum = 0;
+#pragma unroll
+        for (int k = 0; k < kScanItems; ++k)
+        {
+            v[k] = (i0 + k < numTiles) ? row[i0 + k] : 0;
+            sum += v[k];
+        }
+        uint32_t total;
+        uint32_t off = carry + blockExclusiveScan(sum, smem, &total);
+#pragma unroll
+        for (int k = 0; k < kScanItems; ++k)
+        {
+            if (i0 + k < numTiles) row[i0 + k] = off;
+            off += v[k];
+        }
+        carry += total;
+    }
+    if (threadIdx.x == 0) rowTotal[blockIdx.x] = carry;
 }
 
 void radixSortPairs(sphb200_ctx* ctx, KeyType* keys, uint32_t* vals, size_t n, bool valsAreIota, int beginBit,
                     int endBit)
 {
     if (n == 0) return;
+    // per device and cheap: no caching
+    SPHB200_CUDA(cudaFuncSetAttribute(radixScatterKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kScatterSmem)));
     int numTiles    = int((n + kSortTile - 1) / kSortTile);
     size_t histSize = size_t(kRadix) * numTiles;
-    // temp: alt keys, alt vals, hist
-    size_t bytes = n * sizeof(KeyType) + n * sizeof(uint32_t) + histSize * sizeof(uint32_t) + 512;
+    // temp: alt keys, alt vals, hist, row totals
+    size_t bytes = n * sizeof(KeyType) + n * sizeof(uint32_t) + (histSize + kRadix) * sizeof(uint32_t) + 512;
     char* tmp    = static_cast<char*>(ctx->sortTmp.get(bytes));
     KeyType* keysAlt  = reinterpret_cast<KeyType*>(tmp);
     uint32_t* valsAlt = reinterpret_cast<uint32_t*>(tmp + n * sizeof(KeyType));
     uint32_t* hist    = reinterpret_cast<uint32_t*>(tmp + n * sizeof(KeyType) + ((n * sizeof(uint32_t) + 255) & ~size_t(255)));
+    uint32_t* rowTotal = hist + histSize;
 
     int numPasses = (endBit - beginBit + kRadixBits - 1) / kRadixBits;
     KeyType* kIn  = keys;
@@ -259,11 +410,11 @@ void radixSortPairs(sphb200_ctx* ctx, KeyType* keys, uint32_t* vals, size_t n, b
     for (int p = 0; p < numPasses; ++p)
     {
         int shift = beginBit + p * kRadixBits;
-        SPHB200_LAUNCH(ctx, radixCountKernel, numTiles, kSortThreads, 0, kIn, n, shift, hist, numTiles);
-        exclusiveScan(ctx, hist, hist, histSize, nullptr);
+        SPHB200_LAUNCH(ctx, radixCountKernel, numTiles, kCountThreads, 0, kIn, n, shift, hist, numTiles);
+        SPHB200_LAUNCH(ctx, radixRowScanKernel, kRadix, kScanThreads, 0, hist, numTiles, rowTotal);
         const uint32_t* vSrc = (p == 0 && valsAreIota) ? nullptr : vIn;
-        SPHB200_LAUNCH(ctx, radixScatterKernel, numTiles, kSortThreads, 0, kIn, vSrc, kOut, vOut, n, shift, hist,
-                       numTiles);
+        SPHB200_LAUNCH(ctx, radixScatterKernel, numTiles, kSortThreads, kScatterSmem, kIn, vSrc, kOut, vOut, n, shift,
+                       hist, rowTotal, numTiles);
         std::swap(kIn, kOut);
         std::swap(vIn, vOut);
     }

@@ -59,6 +59,21 @@ def test_sfc_keys_sedov_lattice(pkg, ctx, ref):
     assert np.unique(got).size == got.size
 
 
+def test_sfc_keys_table_and_bit_recurrence_agree(pkg, ctx, ref):
+    """long ranges go through the 24-state transition table (7 lookups of three levels), short ones through the bit
+    recurrence of iHilbert (hilbert.hpp:58-110): same keys, both equal to the reference"""
+    from sph_exa_b200 import ops
+    box = BOXES[2]
+    n = 150_000
+    x, y, z = random_coords(n, box, 5)
+    bx = pkg.make_box(*box)
+    whole = to_host(ops.computeSfcKeysGpu(ctx, to_dev(x), to_dev(y), to_dev(z), bx), np.uint64)
+    parts = [to_host(ops.computeSfcKeysGpu(ctx, to_dev(x[a:a + 50_000]), to_dev(y[a:a + 50_000]),
+                                           to_dev(z[a:a + 50_000]), bx), np.uint64) for a in range(0, n, 50_000)]
+    assert np.array_equal(whole, np.concatenate(parts))
+    assert np.array_equal(whole, ref.compute_sfc_keys(x, y, z, box))
+
+
 def test_sfc_keys_empty(pkg, ctx):
     import torch
     from sph_exa_b200 import ops
