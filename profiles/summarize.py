@@ -1,7 +1,7 @@
 #!/usr/bin/env python3
 """Turn the raw ncu outputs of profiles/capture.sh into the committed summaries.
 
-  python profiles/summarize.py launches gpurun_out/launches_r01e.csv profiles/launches_r01e_summary.csv [last_step_launches]
+  python profiles/summarize.py launches gpurun_out/launches_r01e.csv profiles/launches_r01e_summary.csv [last_step_launches | step]
   python profiles/summarize.py full gpurun_out/full_r01e.ncu-rep [more.ncu-rep ...] profiles/ncu_full_r01e_summary.csv
 
 `launches`: per-kernel totals and shares of the last `last_step_launches` launches of the list (one step), template
@@ -28,6 +28,9 @@ COLUMNS = [  # (summary column, substring of the ncu raw-page metric name)
     ("stall_long_scoreboard [warps/issue]", "smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio"),
     ("stall_math_pipe [warps/issue]", "smsp__average_warps_issue_stalled_math_pipe_throttle_per_issue_active.ratio"),
     ("stall_not_selected [warps/issue]", "smsp__average_warps_issue_stalled_not_selected_per_issue_active.ratio"),
+    ("alu_pipe_pct [%]", "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active"),
+    ("adu_pipe_pct [%]", "sm__inst_executed_pipe_adu.avg.pct_of_peak_sustained_active"),
+    ("smem_wavefronts_pct [%]", "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum.pct_of_peak_sustained_elapsed"),
     ("dram_read [Gbyte]", "dram__bytes_read.sum"),
     ("dram_write [Gbyte]", "dram__bytes_write.sum"),
 ]
@@ -35,7 +38,7 @@ TO_GBYTE = {"byte": 1e-9, "Kbyte": 1e-6, "Mbyte": 1e-3, "Gbyte": 1.0, "Tbyte": 1
 TO_MS = {"ns": 1e-6, "us": 1e-3, "ms": 1.0, "s": 1e3}
 
 
-def launches(src, dst, last=117):
+def launches(src, dst, last="step"):
     rows = []
     with open(src) as fh:
         lines = [ln for ln in fh if ln.startswith('"')]
@@ -44,7 +47,15 @@ def launches(src, dst, last=117):
             continue
         v = float(r["Metric Value"].replace(",", "")) * TO_MS.get(r["Metric Unit"], 1e-6)
         rows.append((r["Kernel Name"], v))
-    rows = rows[-last:]
+    if last == "step":
+        # one step = from one sfcKeysKernel launch to the next; take the last pair at the usual distance
+        marks = [i for i, (k, _) in enumerate(rows) if k.startswith("sfcKeys") or "::sfcKeys" in k]
+        gaps = [b - a for a, b in zip(marks, marks[1:])]
+        usual = max(set(gaps), key=gaps.count)
+        a = [m for m, g in zip(marks, gaps) if g == usual][-1]
+        rows = rows[a:a + usual]
+    else:
+        rows = rows[-int(last):]
     tot, cnt = {}, {}
     for k, v in rows:
         tot[k] = tot.get(k, 0.0) + v
@@ -90,6 +101,6 @@ def full(reps, dst):
 
 if __name__ == "__main__":
     if sys.argv[1] == "launches":
-        launches(sys.argv[2], sys.argv[3], int(sys.argv[4]) if len(sys.argv) > 4 else 117)
+        launches(sys.argv[2], sys.argv[3], sys.argv[4] if len(sys.argv) > 4 else "step")
     else:
         full(sys.argv[2:-1], sys.argv[-1])
