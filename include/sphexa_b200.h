@@ -115,6 +115,18 @@ void sphb200_make_box(const double lim_h[6], const int bc_h[3], sphb200_box* out
 /* ---- a2: computeSfcKeysGpu  (domain/include/cstone/sfc/sfc_gpu.h:39, sfc_gpu.cu:38-55) ---- */
 int sphb200_sfc_keys(sphb200_ctx*, const double* x, const double* y, const double* z, size_t n, const sphb200_box* box_h,
                      uint64_t* keys);
+/* ---- §8f row 4: initial conditions from a glass (template) block, main/src/init/grid.hpp ----
+ * assembleCuboid (grid.hpp:238-264): the global box is tiled by multiplicity[0] x [1] x [2] copies of a template block
+ * whose coordinates lie in [0,1)^3 (device arrays of blockSize); the call writes the copies that fall into the octree
+ * cells spanning the SFC range [keyStart, keyEnd) (a rank's share: equal slices of [0, 2^63)), in the reference's
+ * order (cell, tile, position in the block), and returns their number in *count_h.  SPHB200_ERR_CAPACITY with the
+ * needed count in *count_h when x, y, z (capacity elements each) are too small; nothing is written then. */
+int sphb200_assemble_cuboid(sphb200_ctx*, uint64_t keyStart, uint64_t keyEnd, const sphb200_box* globalBox_h,
+                            const int multiplicity_h[3], const double* xBlock, const double* yBlock,
+                            const double* zBlock, size_t blockSize, double* x, double* y, double* z, size_t capacity,
+                            uint64_t* count_h);
+/* cutSphere (grid.hpp:267-300): keep the particles with sqrt(x^2+y^2+z^2) <= radius, in place, order preserved */
+int sphb200_cut_sphere(sphb200_ctx*, double radius, double* x, double* y, double* z, size_t n, uint64_t* count_h);
 /* a1: MinMaxGpu / makeGlobalBox for open axes (primitives_gpu.h:52, box_mpi.hpp:84-119); minmax_h[6] host out */
 int sphb200_minmax3(sphb200_ctx*, const double* x, const double* y, const double* z, size_t n, double* minmax_h);
 

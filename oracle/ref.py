@@ -77,6 +77,37 @@ def compute_sfc_keys(x, y, z, box):
     return keys
 
 
+def assemble_cuboid(key_start, key_end, box, multiplicity, xb, yb, zb):
+    """sphexa::assembleCuboid (main/src/init/grid.hpp:238-264): x, y, z in the reference's output order"""
+    lim, bc = _box(box)
+    m = np.ascontiguousarray(multiplicity, dtype=np.int32)
+    xb, yb, zb = (np.ascontiguousarray(a, dtype=np.float64) for a in (xb, yb, zb))
+    f = lib().ref_assemble_cuboid
+    f.restype = C.c_size_t
+    cap = int(xb.size) * int(m[0]) * int(m[1]) * int(m[2]) + 16
+    x, y, z = (np.empty(cap, np.float64) for _ in range(3))
+    n = f(C.c_uint64(int(key_start)), C.c_uint64(int(key_end)), P(lim), P(bc), P(m), P(xb), P(yb), P(zb),
+          C.c_size_t(xb.size), P(x), P(y), P(z), C.c_size_t(cap))
+    assert n <= cap
+    return x[:n].copy(), y[:n].copy(), z[:n].copy()
+
+
+def equi_distant_sfc_segment(rank, num_ranks, leaves_per_rank=100):
+    """sphexa::equiDistantSfcSegments (main/src/init/grid.hpp:80-88)"""
+    out = np.zeros(2, np.uint64)
+    lib().ref_equidistant_sfc_segment(C.c_int(rank), C.c_int(num_ranks), C.c_int(leaves_per_rank), P(out))
+    return int(out[0]), int(out[1])
+
+
+def cut_sphere(radius, x, y, z):
+    """sphexa::cutSphere (grid.hpp:267-300)"""
+    x, y, z = (np.array(a, dtype=np.float64, copy=True) for a in (x, y, z))
+    f = lib().ref_cut_sphere
+    f.restype = C.c_size_t
+    n = f(C.c_double(radius), P(x), P(y), P(z), C.c_size_t(x.size))
+    return x[:n].copy(), y[:n].copy(), z[:n].copy()
+
+
 def sort_by_key(keys):
     k = np.array(keys, dtype=np.uint64, copy=True)
     perm = np.empty(k.size, np.uint32)

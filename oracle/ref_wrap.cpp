@@ -68,6 +68,7 @@
 #include "sph/hydro_turb/phases.hpp"
 #include "sph/hydro_turb/stirring.hpp"
 #include "sph/hydro_turb/driver.hpp"
+#include "init/grid.hpp"
 
 using KeyType = uint64_t;
 using SfcKey  = cstone::HilbertKey<KeyType>;
@@ -175,6 +176,43 @@ void ref_node_centers(const uint64_t* prefixes, int numNodes, const double* lim,
     auto box = makeBox(lim, bc);
     cstone::nodeFpCenters<KeyType>({prefixes, size_t(numNodes)}, reinterpret_cast<cstone::Vec3<double>*>(centers),
                                    reinterpret_cast<cstone::Vec3<double>*>(sizes), box);
+}
+
+/* ---------------- glass-block assembly (main/src/init/grid.hpp:238-300) ---------------- */
+size_t ref_assemble_cuboid(uint64_t keyStart, uint64_t keyEnd, const double* lim, const int* bc, const int* multiplicity,
+                           const double* xBlock, const double* yBlock, const double* zBlock, size_t blockSize,
+                           double* x, double* y, double* z, size_t capacity)
+{
+    auto box = makeBox(lim, bc);
+    std::vector<double> ox, oy, oz;
+    sphexa::assembleCuboid<double>(KeyType(keyStart), KeyType(keyEnd), box,
+                                   cstone::Vec3<int>{multiplicity[0], multiplicity[1], multiplicity[2]},
+                                   gsl::span<const double>(xBlock, blockSize), gsl::span<const double>(yBlock, blockSize),
+                                   gsl::span<const double>(zBlock, blockSize), ox, oy, oz);
+    if (ox.size() <= capacity)
+    {
+        std::copy(ox.begin(), ox.end(), x);
+        std::copy(oy.begin(), oy.end(), y);
+        std::copy(oz.begin(), oz.end(), z);
+    }
+    return ox.size();
+}
+
+void ref_equidistant_sfc_segment(int rank, int numRanks, int numLeavesPerRank, uint64_t* out)
+{
+    auto [a, b] = sphexa::equiDistantSfcSegments<KeyType>(rank, numRanks, numLeavesPerRank);
+    out[0] = a;
+    out[1] = b;
+}
+
+size_t ref_cut_sphere(double radius, double* x, double* y, double* z, size_t n)
+{
+    std::vector<double> vx(x, x + n), vy(y, y + n), vz(z, z + n);
+    sphexa::cutSphere(radius, vx, vy, vz);
+    std::copy(vx.begin(), vx.end(), x);
+    std::copy(vy.begin(), vy.end(), y);
+    std::copy(vz.begin(), vz.end(), z);
+    return vx.size();
 }
 
 } // extern "C"

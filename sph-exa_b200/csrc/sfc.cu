@@ -4,6 +4,7 @@
 #include <algorithm>
 
 #include "common.cuh"
+#include "primitives.cuh"
 
 namespace sphb200
 {
@@ -52,7 +53,7 @@ __device__ __forceinline__ KeyType hilbertKey(unsigned px, unsigned py, unsigned
 }
 
 //! @brief inverse of hilbertKey, cstone::decodeHilbert (hilbert.hpp:146-188)
-__device__ __forceinline__ void hilbertDecode(KeyType key, unsigned& ox, unsigned& oy, unsigned& oz)
+__host__ __device__ __forceinline__ void hilbertDecode(KeyType key, unsigned& ox, unsigned& oy, unsigned& oz)
 {
     unsigned px = 0, py = 0, pz = 0;
     for (unsigned level = 0; level < kMaxTreeLevel; ++level)
@@ -324,9 +325,272 @@ __global__ void __launch_bounds__(256) sfcKeysKernel(const double* __restrict__ 
     }
 }
 
+// ---------------------------------------------------------------- glass-block assembly (init/grid.hpp:152-300)
+/* A template block with coordinates in [0,1)^3 is stacked multiplicity[d] times per dimension into the global box; a
+ * rank keeps the copies that fall into the octree cells spanning its SFC range.  The host lists the (cell, tile)
+ * pairs in the reference's loop order, two kernels count and write the selected particles, so that the output has the
+ * reference's order: cell, tile (x, y, z nested), position in the block. */
+struct AssemblePair
+{
+    double sel[6];    // xmin xmax ymin ymax zmin zmax of the cell (createFpBox, box.hpp:361-370)
+    double origin[3]; // globalOrigin + blockOrigin of the tile (scaleBlockToGlobal, grid.hpp:168-184)
+};
+
+constexpr int kAssembleChunk = 256;
+
+//! @brief scaleBlockToGlobal + the half-open box test of extractBlock (grid.hpp:201-222)
+__device__ __forceinline__ bool blockToGlobal(const AssemblePair& p, double sx, double sy, double sz, double ux,
+                                              double uy, double uz, double& gx, double& gy, double& gz)
+{
+    gx = __dadd_rn(__dmul_rn(ux, sx), p.origin[0]);
+    gy = __dadd_rn(__dmul_rn(uy, sy), p.origin[1]);
+    gz = __dadd_rn(__dmul_rn(uz, sz), p.origin[2]);
+    return p.sel[0] <= gx && gx < p.sel[1] && p.sel[2] <= gy && gy < p.sel[3] && p.sel[4] <= gz && gz < p.sel[5];
+}
+
+template<bool Write>
+__global__ void __launch_bounds__(kAssembleChunk)
+    assembleKernel(const AssemblePair* __restrict__ pairs, uint32_t numChunks, double sx, double sy, double sz,
+                   const double* __restrict__ xb, const double* __restrict__ yb, const double* __restrict__ zb,
+                   size_t blockSize, uint32_t* __restrict__ counts, const uint32_t* __restrict__ offsets,
+                   double* __restrict__ x, double* __restrict__ y, double* __restrict__ z)
+{
+    __shared__ uint32_t warpCount[kAssembleChunk / 32];
+    uint32_t pairIdx = blockIdx.x / numChunks, chunk = blockIdx.x % numChunks;
+    size_t i         = size_t(chunk) * kAssembleChunk + threadIdx.x;
+    const AssemblePair& p = pairs[pairIdx];
+    double gx = 0, gy = 0, gz = 0;
+    bool sel = i < blockSize && blockToGlobal(p, sx, sy, sz, xb[i], yb[i], zb[i], gx, gy, gz);
+    unsigned ballot = __ballot_sync(0xffffffffu, sel);
+    int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) warpCount[warp] = __popc(ballot);
+    __syncthreads();
+    if (!Write)
+    {
+        if (threadIdx.x == 0)
+        {
+            uint32_t c = 0;
+            for (int w = 0; w < kAssembleChunk / 32; ++w)
+                c += warpCount[w];
+            counts[blockIdx.x] = c;
+        }
+        return;
+    }
+    if (sel)
+    {
+        uint32_t pos = offsets[blockIdx.x] + __popc(ballot & ((1u << lane) - 1));
+        for (int w = 0; w < warp; ++w)
+            pos += warpCount[w];
+        x[pos] = gx;
+        y[pos] = gy;
+        z[pos] = gz;
+    }
+}
+
+//! @brief cutSphere (grid.hpp:267-300): keep sqrt(x^2 + y^2 + z^2) <= radius, order preserved
+template<bool Write>
+__global__ void __launch_bounds__(kAssembleChunk)
+    cutSphereKernel(double radius, const double* __restrict__ x, const double* __restrict__ y,
+                    const double* __restrict__ z, size_t n, uint32_t* __restrict__ counts,
+                    const uint32_t* __restrict__ offsets, double* __restrict__ ox, double* __restrict__ oy,
+                    double* __restrict__ oz)
+{
+    __shared__ uint32_t warpCount[kAssembleChunk / 32];
+    size_t i  = size_t(blockIdx.x) * kAssembleChunk + threadIdx.x;
+    double xi = 0, yi = 0, zi = 0;
+    bool sel  = false;
+    if (i < n)
+    {
+        xi  = x[i], yi = y[i], zi = z[i];
+        sel = sqrt(__dadd_rn(__dadd_rn(__dmul_rn(xi, xi), __dmul_rn(yi, yi)), __dmul_rn(zi, zi))) <= radius;
+    }
+    unsigned ballot = __ballot_sync(0xffffffffu, sel);
+    int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) warpCount[warp] = __popc(ballot);
+    __syncthreads();
+    if (!Write)
+    {
+        if (threadIdx.x == 0)
+        {
+            uint32_t c = 0;
+            for (int w = 0; w < kAssembleChunk / 32; ++w)
+                c += warpCount[w];
+            counts[blockIdx.x] = c;
+        }
+        return;
+    }
+    if (sel)
+    {
+        uint32_t pos = offsets[blockIdx.x] + __popc(ballot & ((1u << lane) - 1));
+        for (int w = 0; w < warp; ++w)
+            pos += warpCount[w];
+        ox[pos] = xi;
+        oy[pos] = yi;
+        oz[pos] = zi;
+    }
+}
+
+namespace
+{
+
+//! @brief cstone::spanSfcRange (sfc/common.hpp:362-400): octree cells covering [a, b), cells.back() == b
+std::vector<KeyType> spanKeyRange(KeyType a, KeyType b)
+{
+    auto digit   = [](KeyType k, int pos) { return unsigned(k >> (3 * (kMaxTreeLevel - pos))) & 7u; };
+    auto power   = [](int pos) { return KeyType(1) << (3 * (kMaxTreeLevel - pos)); };
+    auto lastNz  = [](KeyType k) { return k ? int(kMaxTreeLevel) - int(__builtin_ctzll(k)) / 3 : int(kMaxTreeLevel); };
+    std::vector<KeyType> cells;
+    int firstDiff = (int(clz64(a ^ b)) + 3 - 1) / 3; // first octal place where a and b differ
+    int aLast = lastNz(a), bLast = lastNz(b);
+    for (int pos = aLast; pos > firstDiff; --pos) // climb: finish the octants a starts inside
+        for (unsigned k = (8 - digit(a, pos)) % 8; k > 0; --k, a += power(pos))
+            cells.push_back(a);
+    for (int pos = firstDiff; pos <= bLast; ++pos) // descend towards b
+        for (int k = int(digit(b, pos)) - int(digit(a, pos)); k > 0; --k, a += power(pos))
+            cells.push_back(a);
+    cells.push_back(b);
+    return cells;
+}
+
+} // namespace
+
 } // namespace sphb200
 
 using namespace sphb200;
+
+extern "C" int sphb200_assemble_cuboid(sphb200_ctx* ctx, uint64_t keyStart, uint64_t keyEnd, const sphb200_box* box,
+                                       const int* multiplicity, const double* xBlock, const double* yBlock,
+                                       const double* zBlock, size_t blockSize, double* x, double* y, double* z,
+                                       size_t capacity, uint64_t* count_h)
+{
+    try
+    {
+        *count_h = 0;
+        if (keyEnd <= keyStart || blockSize == 0) return 0;
+        const int* m = multiplicity;
+        if (m[0] < 1 || m[1] < 1 || m[2] < 1) throw std::runtime_error("assemble_cuboid: multiplicity must be >= 1");
+        std::vector<KeyType> cells = spanKeyRange(keyStart, keyEnd);
+
+        constexpr int maxCoord = 1 << kMaxTreeLevel;
+        constexpr double uL    = 1.0 / maxCoord;
+        std::vector<AssemblePair> pairs;
+        for (size_t c = 0; c + 1 < cells.size(); ++c)
+        {
+            // hilbertIBox (hilbert.hpp:264-281) of the cell
+            unsigned level      = treeLevel(cells[c + 1] - cells[c]);
+            unsigned cubeLength = (1u << kMaxTreeLevel) >> level;
+            unsigned lo[3];
+            hilbertDecode(cells[c], lo[0], lo[1], lo[2]);
+            double sel[6], unit[6];
+            for (int d = 0; d < 3; ++d)
+            {
+                lo[d] &= ~(cubeLength - 1);
+                int imin = int(lo[d]), imax = int(lo[d] + cubeLength);
+                // centerAndSize + createFpBox (box.hpp:334-370) in the global box and in the unit cube
+                double half   = 0.5 * uL * box->len[d];
+                double center = box->lim[2 * d] + (imax + imin) * half;
+                double size   = (imax - imin) * half;
+                sel[2 * d]     = center - size;
+                sel[2 * d + 1] = center + size;
+                double halfU   = 0.5 * uL * 1.0;
+                double centerU = 0.0 + (imax + imin) * halfU;
+                double sizeU   = (imax - imin) * halfU;
+                unit[2 * d]     = centerU - sizeU;
+                unit[2 * d + 1] = centerU + sizeU;
+            }
+            // gridIntersection (grid.hpp:141-151)
+            int first[3], last[3];
+            for (int d = 0; d < 3; ++d)
+            {
+                first[d] = int(unit[2 * d] * m[d]);
+                last[d]  = int(std::ceil(unit[2 * d + 1] * m[d]));
+            }
+            for (int ix = first[0]; ix < last[0]; ++ix)
+                for (int iy = first[1]; iy < last[1]; ++iy)
+                    for (int iz = first[2]; iz < last[2]; ++iz)
+                    {
+                        AssemblePair p;
+                        std::copy(sel, sel + 6, p.sel);
+                        int g[3] = {ix, iy, iz};
+                        for (int d = 0; d < 3; ++d)
+                            p.origin[d] = box->lim[2 * d] + g[d] * box->len[d] / m[d];
+                        pairs.push_back(p);
+                    }
+        }
+        if (pairs.empty()) return 0;
+
+        uint32_t numChunks = uint32_t((blockSize + kAssembleChunk - 1) / kAssembleChunk);
+        size_t numBlocks   = pairs.size() * numChunks;
+        if (numBlocks > 0x7fffffffull) throw std::runtime_error("assemble_cuboid: too many (cell, tile) pairs");
+        size_t pairBytes = (pairs.size() * sizeof(AssemblePair) + 255) & ~size_t(255);
+        char* tmp        = static_cast<char*>(ctx->miscTmp.get(pairBytes + (2 * numBlocks + 2) * sizeof(uint32_t)));
+        auto* dPairs     = reinterpret_cast<AssemblePair*>(tmp);
+        auto* counts     = reinterpret_cast<uint32_t*>(tmp + pairBytes);
+        uint32_t* offs   = counts + numBlocks;
+        uint32_t* total  = offs + numBlocks;
+        SPHB200_CUDA(cudaMemcpyAsync(dPairs, pairs.data(), pairs.size() * sizeof(AssemblePair), cudaMemcpyHostToDevice,
+                                     ctx->stream));
+        double sx = box->len[0] / m[0], sy = box->len[1] / m[1], sz = box->len[2] / m[2];
+        SPHB200_LAUNCH(ctx, assembleKernel<false>, unsigned(numBlocks), kAssembleChunk, 0, dPairs, numChunks, sx, sy, sz,
+                       xBlock, yBlock, zBlock, blockSize, counts, (const uint32_t*)nullptr, (double*)nullptr,
+                       (double*)nullptr, (double*)nullptr);
+        exclusiveScan(ctx, counts, offs, numBlocks, total);
+        uint32_t total_h = 0;
+        SPHB200_CUDA(cudaMemcpyAsync(&total_h, total, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+        SPHB200_CUDA(cudaStreamSynchronize(ctx->stream)); // also keeps `pairs` alive until the upload is done
+        *count_h = total_h;
+        if (total_h > capacity) return SPHB200_ERR_CAPACITY;
+        if (total_h)
+            SPHB200_LAUNCH(ctx, assembleKernel<true>, unsigned(numBlocks), kAssembleChunk, 0, dPairs, numChunks, sx, sy,
+                           sz, xBlock, yBlock, zBlock, blockSize, counts, offs, x, y, z);
+        return 0;
+    }
+    catch (std::exception& e)
+    {
+        setError(e.what());
+        return 1;
+    }
+}
+
+extern "C" int sphb200_cut_sphere(sphb200_ctx* ctx, double radius, double* x, double* y, double* z, size_t n,
+                                  uint64_t* count_h)
+{
+    try
+    {
+        *count_h = 0;
+        if (n == 0) return 0;
+        size_t numBlocks = (n + kAssembleChunk - 1) / kAssembleChunk;
+        size_t coordBytes = (n * sizeof(double) + 255) & ~size_t(255);
+        char* tmp        = static_cast<char*>(ctx->miscTmp.get(3 * coordBytes + (2 * numBlocks + 2) * sizeof(uint32_t)));
+        double* ox       = reinterpret_cast<double*>(tmp);
+        double* oy       = reinterpret_cast<double*>(tmp + coordBytes);
+        double* oz       = reinterpret_cast<double*>(tmp + 2 * coordBytes);
+        auto* counts     = reinterpret_cast<uint32_t*>(tmp + 3 * coordBytes);
+        uint32_t* offs   = counts + numBlocks;
+        uint32_t* total  = offs + numBlocks;
+        SPHB200_LAUNCH(ctx, cutSphereKernel<false>, unsigned(numBlocks), kAssembleChunk, 0, radius, x, y, z, n, counts,
+                       (const uint32_t*)nullptr, (double*)nullptr, (double*)nullptr, (double*)nullptr);
+        exclusiveScan(ctx, counts, offs, numBlocks, total);
+        SPHB200_LAUNCH(ctx, cutSphereKernel<true>, unsigned(numBlocks), kAssembleChunk, 0, radius, x, y, z, n, counts,
+                       offs, ox, oy, oz);
+        uint32_t total_h = 0;
+        SPHB200_CUDA(cudaMemcpyAsync(&total_h, total, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+        SPHB200_CUDA(cudaStreamSynchronize(ctx->stream));
+        *count_h = total_h;
+        if (total_h)
+        {
+            SPHB200_CUDA(cudaMemcpyAsync(x, ox, total_h * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream));
+            SPHB200_CUDA(cudaMemcpyAsync(y, oy, total_h * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream));
+            SPHB200_CUDA(cudaMemcpyAsync(z, oz, total_h * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream));
+        }
+        return 0;
+    }
+    catch (std::exception& e)
+    {
+        setError(e.what());
+        return 1;
+    }
+}
 
 extern "C" int sphb200_sfc_keys(sphb200_ctx* ctx, const double* x, const double* y, const double* z, size_t n,
                                 const sphb200_box* box, uint64_t* keys)

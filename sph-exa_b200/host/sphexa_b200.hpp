@@ -76,6 +76,27 @@ inline void computeSfcKeysGpu(const Context& c, const double* x, const double* y
     check(sphb200_sfc_keys(c.get(), x, y, z, n, &box, keys));
 }
 
+/*! @brief sphexa::assembleCuboid (main/src/init/grid.hpp:238-264) on device arrays: the copies of the template block
+ *         (coordinates in [0,1)^3) that tile the global box and fall into the SFC range [keyStart, keyEnd).
+ *  @return number of particles written to x, y, z (reference order); throws when capacity is too small */
+inline size_t assembleCuboid(const Context& c, uint64_t keyStart, uint64_t keyEnd, const Box& globalBox,
+                             const int multiplicity[3], const double* xBlock, const double* yBlock,
+                             const double* zBlock, size_t blockSize, double* x, double* y, double* z, size_t capacity)
+{
+    uint64_t count = 0;
+    check(sphb200_assemble_cuboid(c.get(), keyStart, keyEnd, &globalBox, multiplicity, xBlock, yBlock, zBlock,
+                                  blockSize, x, y, z, capacity, &count));
+    return size_t(count);
+}
+
+//! @brief sphexa::cutSphere (grid.hpp:267-300), in place on device arrays; returns the new size
+inline size_t cutSphere(const Context& c, double radius, double* x, double* y, double* z, size_t n)
+{
+    uint64_t count = 0;
+    check(sphb200_cut_sphere(c.get(), radius, x, y, z, n, &count));
+    return size_t(count);
+}
+
 //! @brief cstone::sortByKeyGpu with a sequence payload (primitives_gpu.h:87-111)
 inline void sortByKeyGpu(const Context& c, uint64_t* keys, uint32_t* ordering, size_t n)
 {

@@ -88,19 +88,15 @@ def _real(dtype):
     return np.float64 if dtype in (0, "f64", np.float64) else np.float32
 
 
-def sedov(side, dtype="f64"):
-    """Sedov blast wave on a side^3 lattice, periodic box [-0.5,0.5]^3 (sedov_init.hpp:48-133).
-
-    returns (fields dict of conserved arrays, box (lim, bc), settings)"""
-    T = _real(dtype)
+def _sedov_fields(x, y, z, n_glob, T):
+    """initSedovFields (sedov_init.hpp:48-92) for given coordinates; n_glob = numParticlesGlobal"""
     c = dict(SEDOV)
     ener0 = c["energyTotal"] / math.pow(math.pi, 1.5) / 1.0 / math.pow(c["width"], 3.0)
-    n = side ** 3
     r = c["r1"]
-    x, y, z = regular_grid(r, side)
+    n = x.size
     total_volume = math.pow(2 * r, 3)
-    h_init = np.cbrt(3.0 / (4 * math.pi) * c["ng0"] * total_volume / n) * 0.5
-    m_part = c["mTotal"] / n
+    h_init = np.cbrt(3.0 / (4 * math.pi) * c["ng0"] * total_volume / n_glob) * 0.5
+    m_part = c["mTotal"] / n_glob
     width2 = c["width"] * c["width"]
     cv = float(ideal_gas_cv(c["mui"], c["gamma"], T))
     r2 = x * x + y * y + z * z
@@ -109,8 +105,16 @@ def sedov(side, dtype="f64"):
              vz=np.zeros(n, T), x_m1=np.zeros(n, T), y_m1=np.zeros(n, T), z_m1=np.zeros(n, T), temp=temp,
              du_m1=np.zeros(n, T), alpha=np.full(n, 0.05, T))
     box = ([-r, r, -r, r, -r, r], [1, 1, 1])
-    settings = dict(c, Kcour=0.2, Krho=0.06, numParticlesGlobal=n)
+    settings = dict(c, Kcour=0.2, Krho=0.06, numParticlesGlobal=n_glob)
     return f, box, settings
+
+
+def sedov(side, dtype="f64"):
+    """Sedov blast wave on a side^3 lattice, periodic box [-0.5,0.5]^3 (sedov_init.hpp:48-133).
+
+    returns (fields dict of conserved arrays, box (lim, bc), settings)"""
+    x, y, z = regular_grid(SEDOV["r1"], side)
+    return _sedov_fields(x, y, z, side ** 3, _real(dtype))
 
 
 def sedov_range(side, first, last, dtype="f64"):
@@ -155,29 +159,112 @@ def _jittered_lattice(side, lo, hi, jitter, seed):
     return out
 
 
-def noh(side, dtype="f64", seed=42):
-    """Noh implosion (noh_init.hpp:66-102) on a jittered lattice cut to the sphere r <= 0.5; open box"""
-    T = _real(dtype)
+def _noh_fields(x, y, z, n_glob, T):
+    """initNohFields (noh_init.hpp:66-102) for given coordinates inside the sphere; n_glob = numParticlesGlobal"""
     gamma, mui, r1 = 5.0 / 3.0, 10.0, 0.5
-    x, y, z = _jittered_lattice(side, -r1, r1, 0.2, seed)
     rad = np.sqrt(x * x + y * y + z * z)
-    keep = rad <= r1
-    x, y, z, rad = x[keep], y[keep], z[keep], rad[keep]
     n = x.size
     total_volume = 4.0 * math.pi / 3.0 * r1 ** 3
-    h_init = np.cbrt(3.0 / (4 * math.pi) * 100 * total_volume / n) * 0.5
+    h_init = np.cbrt(3.0 / (4 * math.pi) * 100 * total_volume / n_glob) * 0.5
     cv = float(ideal_gas_cv(mui, gamma, T))
     rs = np.maximum(rad, 1e-10)
     vy = (-(y / rs)).astype(T)
     vz = (-(z / rs)).astype(T)
     dt0 = 1e-4
-    f = dict(x=x, y=y, z=z, h=np.full(n, h_init, T), m=np.full(n, 1.0 / n, T), vx=(-(x / rs)).astype(T), vy=vy, vz=vz,
-             x_m1=(-(x / rs) * dt0).astype(T), y_m1=(-(y / rs) * dt0).astype(T), z_m1=(-(z / rs) * dt0).astype(T),
-             temp=np.full(n, 1e-20 / cv), du_m1=np.zeros(n, T), alpha=np.full(n, 0.05, T))
+    f = dict(x=x, y=y, z=z, h=np.full(n, h_init, T), m=np.full(n, 1.0 / n_glob, T), vx=(-(x / rs)).astype(T), vy=vy,
+             vz=vz, x_m1=(-(x / rs) * dt0).astype(T), y_m1=(-(y / rs) * dt0).astype(T),
+             z_m1=(-(z / rs) * dt0).astype(T), temp=np.full(n, 1e-20 / cv), du_m1=np.zeros(n, T),
+             alpha=np.full(n, 0.05, T))
     box = ([-r1, r1, -r1, r1, -r1, r1], [0, 0, 0])
     settings = dict(gamma=gamma, mui=mui, minDt=dt0, minDt_m1=dt0, ng0=100, ngmax=150, Kcour=0.2, Krho=0.06,
-                    numParticlesGlobal=n)
+                    numParticlesGlobal=n_glob)
     return f, box, settings
+
+
+def noh(side, dtype="f64", seed=42):
+    """Noh implosion (noh_init.hpp:66-102) on a jittered lattice cut to the sphere r <= 0.5; open box"""
+    r1 = 0.5
+    x, y, z = _jittered_lattice(side, -r1, r1, 0.2, seed)
+    keep = np.sqrt(x * x + y * y + z * z) <= r1
+    x, y, z = x[keep], y[keep], z[keep]
+    return _noh_fields(x, y, z, x.size, _real(dtype))
+
+
+# ---------------------------------------------------------------- glass-block initial conditions (init/grid.hpp)
+def equi_distant_sfc_segments(rank, num_ranks, leaves_per_rank=100):
+    """equiDistantSfcSegments (main/src/init/grid.hpp:80-88): this rank's slice of [0, 2^63), boundaries rounded down
+    to octree nodes of level log8ceil(leaves_per_rank * num_ranks) (initialDomainSplits, domaindecomp.hpp:243-256)"""
+    n = leaves_per_rank * num_ranks
+    level = 0
+    while 8 ** level < n:
+        level += 1
+    full = 1 << 63
+    delta = full // num_ranks
+    mask = ~((1 << (3 * (21 - level))) - 1)
+    bounds = [0] + [(i * delta) & mask for i in range(1, num_ranks)] + [full]
+    return bounds[rank], bounds[rank + 1]
+
+
+def write_template_block(path, x, y, z):
+    """a glass block (coordinates in [0,1)^3) in the container of csrc/checkpoint.cu; the reference keeps its blocks
+    in H5Part files with the datasets x, y, z (readTemplateBlock, init/utils.hpp:71-85)"""
+    from . import binding as B
+    import ctypes as C
+    n = len(x)
+    arrays = {k: np.zeros(n, np.float64) for k in B.CONSERVED}
+    arrays["x"], arrays["y"], arrays["z"] = (np.ascontiguousarray(a, np.float64) for a in (x, y, z))
+    info = B.RestartInfo()
+    info.numParticlesGlobal = info.numParticles = n
+    info.dtype = B.F64
+    info.box = B.make_box([0, 1, 0, 1, 0, 1], [0, 0, 0])
+    hc = B.HydroConst()
+    f = B.Fields()
+    for name in B.FIELD_NAMES:
+        setattr(f, name, None)
+    for name, a in arrays.items():
+        setattr(f, name, a.ctypes.data)
+    B.check(B.lib.sphb200_restart_write(str(path).encode(), C.byref(info), C.byref(hc), None, 0, 1, C.byref(f)))
+
+
+def read_template_block(path):
+    """readTemplateBlock (init/utils.hpp:71-85): x, y, z of the block"""
+    from . import restart
+    with restart.RestartFile(str(path)) as rf:
+        n = int(rf.info.numParticles)
+        out = {k: np.empty(n, np.float64) for k in "xyz"}
+        rf.read_fields(0, n, rf.info.dtype, out)
+    return out["x"], out["y"], out["z"]
+
+
+def _assemble(ctx, block, box, multiplicity, rank, num_ranks):
+    import torch
+    from . import ops, binding as B
+    key_start, key_end = equi_distant_sfc_segments(rank, num_ranks)
+    bx = B.make_box(*box)
+    dev = [torch.from_numpy(np.ascontiguousarray(a, np.float64)).cuda() for a in block]
+    return ops.assembleCuboid(ctx, key_start, key_end, bx, multiplicity, *dev)
+
+
+def sedov_glass(ctx, block, cbrt_num_part, rank=0, num_ranks=1, dtype="f64"):
+    """SedovGlass::init (sedov_init.hpp:155-190): the periodic box tiled with rint(cbrtNumPart / cbrt(blockSize))^3
+    copies of the glass block, this rank's SFC segment of it; block = (x, y, z) in [0,1)^3"""
+    multi = int(np.rint(cbrt_num_part / np.cbrt(len(block[0]))))
+    r = SEDOV["r1"]
+    box = ([-r, r, -r, r, -r, r], [1, 1, 1])
+    x, y, z = (a.cpu().numpy() for a in _assemble(ctx, block, box, [multi] * 3, rank, num_ranks))
+    return _sedov_fields(x, y, z, multi ** 3 * len(block[0]), _real(dtype))
+
+
+def noh_glass(ctx, block, cbrt_num_part, rank=0, num_ranks=1, dtype="f64", n_glob=None):
+    """NohGlassSphere::init (noh_init.hpp:110-150): tiled open box cut to the sphere r <= r1.  numParticlesGlobal is
+    the sum of the ranks' counts (MPI_Allreduce in the reference): pass n_glob when num_ranks > 1"""
+    from . import ops
+    multi = int(np.rint(cbrt_num_part / np.cbrt(len(block[0]))))
+    r1 = 0.5
+    box = ([-r1, r1, -r1, r1, -r1, r1], [0, 0, 0])
+    x, y, z = _assemble(ctx, block, box, [multi] * 3, rank, num_ranks)
+    x, y, z = (a.cpu().numpy() for a in ops.cutSphere(ctx, r1, x, y, z))
+    return _noh_fields(x, y, z, x.size if n_glob is None else n_glob, _real(dtype))
 
 
 def turbulence(side, dtype="f64", seed=7):

@@ -29,6 +29,37 @@ def computeSfcKeysGpu(ctx, x, y, z, box, keys=None):
     return keys
 
 
+def assembleCuboid(ctx, key_start, key_end, box, multiplicity, x_block, y_block, z_block):
+    """sphexa::assembleCuboid (main/src/init/grid.hpp:238-264): the part of the global box, tiled by `multiplicity`
+    copies of a template block in [0,1)^3, that lies in the SFC range [key_start, key_end); reference order"""
+    m = (C.c_int * 3)(*[int(v) for v in multiplicity])
+    nb = x_block.numel()
+    count = C.c_uint64(0)
+    # first call sizes the output (nothing is written when the capacity is too small)
+    rc = lib.sphb200_assemble_cuboid(ctx.h, C.c_uint64(int(key_start)), C.c_uint64(int(key_end)), C.byref(box), m,
+                                     ptr(x_block), ptr(y_block), ptr(z_block), C.c_size_t(nb), None, None, None,
+                                     C.c_size_t(0), C.byref(count))
+    if rc not in (0, B.ERR_CAPACITY):
+        check(rc)
+    n = int(count.value)
+    x, y, z = (torch.empty(n, dtype=torch.float64, device=x_block.device) for _ in range(3))
+    if n:
+        check(lib.sphb200_assemble_cuboid(ctx.h, C.c_uint64(int(key_start)), C.c_uint64(int(key_end)), C.byref(box), m,
+                                          ptr(x_block), ptr(y_block), ptr(z_block), C.c_size_t(nb), ptr(x), ptr(y),
+                                          ptr(z), C.c_size_t(n), C.byref(count)))
+    return x, y, z
+
+
+def cutSphere(ctx, radius, x, y, z):
+    """sphexa::cutSphere (grid.hpp:267-300): the particles with |r| <= radius, order preserved (new tensors)"""
+    x, y, z = x.clone(), y.clone(), z.clone()
+    count = C.c_uint64(0)
+    check(lib.sphb200_cut_sphere(ctx.h, C.c_double(radius), ptr(x), ptr(y), ptr(z), C.c_size_t(x.numel()),
+                                 C.byref(count)))
+    n = int(count.value)
+    return x[:n].clone(), y[:n].clone(), z[:n].clone()
+
+
 def minMaxGpu(ctx, x, y, z):
     """MinMaxGpu per axis (primitives_gpu.h:52) -> [xmin,xmax,ymin,ymax,zmin,zmax]"""
     out = (C.c_double * 6)()

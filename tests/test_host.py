@@ -31,6 +31,15 @@ def test_sedov_ic_formulas(pkg):
         assert np.array_equal(g[k], f[k][1000:5000]), k
 
 
+def test_equi_distant_sfc_segments(pkg, ref):
+    """the SFC slice a rank assembles its glass-block IC in (main/src/init/grid.hpp:80-88), against the reference"""
+    for num_ranks in (1, 2, 3, 7, 8, 64, 100, 1000):
+        for rank in sorted({0, 1 % num_ranks, num_ranks // 2, num_ranks - 1}):
+            assert pkg.ic.equi_distant_sfc_segments(rank, num_ranks) == ref.equi_distant_sfc_segment(rank, num_ranks)
+    assert pkg.ic.equi_distant_sfc_segments(0, 1) == (0, 1 << 63)
+    assert pkg.ic.equi_distant_sfc_segments(2, 5, 10) == ref.equi_distant_sfc_segment(2, 5, 10)
+
+
 def test_other_ics_are_seeded_and_inside_box(pkg):
     for case, side in (("noh", 20), ("turbulence", 16), ("kh", 32)):
         a, box, s = pkg.ic.CASES[case](side)
