@@ -194,6 +194,50 @@ def ncu_column(phase, args, column):
     return None
 
 
+def other_config(pkg, ctx, S, torch, case, side, what, dtype, dtype_name, steps=5, warmup=3):
+    """a few steps of one of the other BASELINE.json configs on one GPU: step time, phase times, neighbor-count
+    spread, leaf-array changes per step (the octree rebalancing the KH config is there to exercise)"""
+    import numpy as np
+    f, box, s = pkg.ic.CASES[case](side, dtype_name)
+    n = f["x"].size
+    gs = S.HydroVeProp(ctx, box, s, capacity=n, dtype=dtype)
+    turb = None
+    if case == "turbulence":
+        from sph_exa_b200.turbulence import Turbulence
+        turb = Turbulence()
+        gs.attachTurbulence(turb)
+    gs.upload(f)
+    for _ in range(warmup):
+        gs.step()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(steps):
+        gs.step()
+    b.record()
+    torch.cuda.synchronize()
+    ms = a.elapsed_time(b) / steps
+    phase, changed = {}, []
+    prev = gs.leaves()
+    for _ in range(3):
+        gs.step()
+        for k, v in gs.phaseTimes().items():
+            phase[k] = phase.get(k, 0.0) + v / 3
+        cur = gs.leaves()
+        changed.append(int(np.setxor1d(prev, cur).size))
+        prev = cur
+    nc = gs.download(names=["nc"])["nc"].astype(np.int64) - 1
+    out = {"workload": what, "particles": int(n), "ms_per_step": ms, "particle_steps_per_s": n / (ms * 1e-3),
+           "phase_ms": phase, "leaves": int(gs.numLeaves), "leaf_keys_changed_per_step": changed,
+           "neighbors": {"min": int(nc.min()), "mean": float(nc.mean()), "max": int(nc.max()),
+                         "std": float(nc.std())}, "box": gs.boxLimits()}
+    gs.close()
+    if turb is not None:
+        turb.close()
+    torch.cuda.empty_cache()
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -206,6 +250,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-bdt", action="store_true", help="skip the block-time-step (ve-bdt) hierarchy report")
+    ap.add_argument("--no-configs", action="store_true", help="skip the Noh / turbulence / KH reports")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else max(args.warmup, 1)
 
@@ -262,6 +307,7 @@ def main():
     ms_per_step = total_ms / args.steps
     value = n * args.steps / (total_ms * 1e-3)
     total_nb = gs.totalNeighbors()
+    num_leaves = gs.numLeaves
 
     # ---------------- roofline of the dominant kernel
     peak, peak_src = load_peaks()
@@ -419,6 +465,24 @@ def main():
                "global_dt_equivalent_ms": len(last) * ms_per_step,
                "speedup_vs_global_dt": len(last) * ms_per_step / hier_ms if hier_ms > 0 else None}
 
+    # ---------------- the other BASELINE.json configs at their per-GPU size (parity-test cases in tests/; here only how
+    # the same path behaves on them: open box, stirred turbulence, density contrast).  Not bench lines.
+    other = None
+    if not args.no_configs:
+        gs.close()
+        gs = None
+        torch.cuda.empty_cache()
+        other = {}
+        for name, side, what in (("noh", 150, "Noh implosion, per-GPU share of configs[2] (300^3 lattice cut to the "
+                                              "sphere over 8 GPUs), open box: bounding-box reduction every step"),
+                                 ("turbulence", 250, "configs[3] per GPU: 250^3, gamma 1.001, turbulence-ve "
+                                                     "(global dt) with the stirring driver attached"),
+                                 ("kh", 160, "configs[4]: Kelvin-Helmholtz slab, 2:1 density contrast, alpha = 1")):
+            try:
+                other[name] = other_config(pkg, ctx, S, torch, name, side, what, dtype, args.dtype)
+            except Exception as ex:  # diagnostics only
+                other[name] = {"error": str(ex)}
+
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -427,12 +491,13 @@ def main():
                    "l2": "inputs larger than L2 (particle state >= 2.5 GB, neighbor lists 4.8 GB)",
                    "ng0": 100, "ngmax": 150, "bucket_focus": 64},
         "find_neighbors_ms": phase_ms.get("FindNeighbors"),
-        "phase_ms": phase_ms, "total_neighbors": total_nb, "leaves": gs.numLeaves,
+        "phase_ms": phase_ms, "total_neighbors": total_nb, "leaves": num_leaves,
         "clocks": clocks, "gpu_launches": launches, "roofline": roofline, "e2e": e2e, "cpu_baseline": cpu,
-        "hbm_kernels": hbm_kernels, "block_time_steps": bdt,
+        "hbm_kernels": hbm_kernels, "block_time_steps": bdt, "other_configs": other,
     }
     print(json.dumps(line), flush=True)
-    gs.close()
+    if gs is not None:
+        gs.close()
     ctx.close()
     return 0
 

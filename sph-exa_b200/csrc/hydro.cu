@@ -835,10 +835,15 @@ __global__ void __launch_bounds__(kHydroBlock, kMomentumMinBlocks)
             }
             else
             {
+                // xm_i^(2-s) xm_j^s = xm_i^2 q^s and xm_j^(2-s) xm_i^s = xm_j^2 / q^s with q = xm_j / xm_i: one
+                // log + exp instead of four pow.  One lane in the ramp stalls its whole warp for the branch, and on
+                // jittered data (turbulence, Noh) some lane is in it in most iterations: 4 pow made the kernel 2.9x
+                // slower than on the Sedov lattice.  |s log q| << 1, so the result stays within a few ulp of pow's.
                 T Atwood   = rhoDiff / rhoSum;
                 T sigma_ij = ramp * (Atwood - Atmin);
-                a_mom      = pow(xmassi, T(2) - sigma_ij) * pow(xmassj, sigma_ij);
-                b_mom      = pow(xmassj, T(2) - sigma_ij) * pow(xmassi, sigma_ij);
+                T qs       = exp(sigma_ij * log(xmassj / xmassi));
+                a_mom      = xmassi * xmassi * qs;
+                b_mom      = xmassj * xmassj / qs;
             }
 
             T a_visc   = mj * rhoiInv * viscosity_ij; // m_j / rho_i with the reciprocal taken once per target

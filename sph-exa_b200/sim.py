@@ -181,6 +181,12 @@ class HydroVeProp:
     def ttot(self):
         return lib.sphb200_sim_ttot(self.h)
 
+    def boxLimits(self):
+        """Domain::box(): [xmin, xmax, ymin, ymax, zmin, zmax] (open axes follow the particles)"""
+        b = B.Box()
+        lib.sphb200_sim_get_box(self.h, C.byref(b))
+        return list(b.lim)
+
     def totalNeighbors(self):
         return lib.sphb200_sim_total_neighbors(self.h)
 
