@@ -158,7 +158,8 @@ __device__ __forceinline__ int warpInclusiveScan(int v, int lane)
  * Both culls are conservative in floating point: for lo <= x_i <= hi, |fl(x_j - x_i)| >= fl(max(lo - x_j, x_j - hi, 0))
  * since rounding is monotone, and squaring and the left-associated sum of distSq preserve the ordering, so a computed
  * box distance never exceeds the computed distance to any target inside the box.
- * With periodic folding (UsePbc) the node tests fold like the DFS and the leaf cull of step 2 is skipped.
+ * With periodic folding (UsePbc) the node tests fold like the DFS and the leaf cull of step 2 takes the nearest of the
+ * leaf's periodic images per axis.
  * @return false if the frontier overflowed (nothing usable was written; the caller runs the DFS instead)
  */
 template<bool UsePbc>
@@ -230,10 +231,13 @@ __device__ __forceinline__ bool searchBfs(const DevTree& tree, const double* __r
         if (!anyInternal) break;
     }
 
-    // ---- 2. leaves -> particle ranges, culled against the target box
+    // ---- 2. leaves -> particle ranges, culled against the target box; leaves that follow each other in the particle
+    // array are merged into one range (SFC neighbors are mostly kept together), so that the 32-particle chunks of
+    // step 3 are full instead of one partly filled chunk per leaf
     int* rb = nxt;
     int* re = bufC;
     int nR  = 0;
+    int prevEnd = -1; // end of the last range written so far
     for (int b = 0; b < n; b += 32)
     {
         int e     = b + lane;
@@ -248,17 +252,43 @@ __device__ __forceinline__ bool searchBfs(const DevTree& tree, const double* __r
             double ex = fmax(fmax(lb[0] - tg.hi[0], tg.lo[0] - lb[3]), 0.0);
             double ey = fmax(fmax(lb[1] - tg.hi[1], tg.lo[1] - lb[4]), 0.0);
             double ez = fmax(fmax(lb[2] - tg.hi[2], tg.lo[2] - lb[5]), 0.0);
-            // (periodic folding: leaf extents are not folded, the per-candidate prefilter below does the work)
-            keep      = je > jb && (UsePbc || ex * ex + ey * ey + ez * ez < tg.rmaxSq);
+            double rCull = tg.rmaxSq;
+            if (UsePbc)
+            {
+                // periodic axes: the nearest of the leaf's three images, per axis (a lower bound of the folded distance
+                // of every particle in the leaf to every target in the box); margin as in the candidate prefilter
+                double e[3] = {ex, ey, ez};
+#pragma unroll
+                for (int d = 0; d < 3; ++d)
+                    if (box.bc[d] == SPHB200_PERIODIC)
+                    {
+                        double l  = box.len[d];
+                        double em = fmax(fmax(lb[d] - l - tg.hi[d], tg.lo[d] - (lb[3 + d] - l)), 0.0);
+                        double ep = fmax(fmax(lb[d] + l - tg.hi[d], tg.lo[d] - (lb[3 + d] + l)), 0.0);
+                        e[d]      = fmin(e[d], fmin(em, ep));
+                    }
+                ex = e[0], ey = e[1], ez = e[2];
+                rCull = tg.rmaxSq * (1.0 + 1e-9);
+            }
+            keep = je > jb && ex * ex + ey * ey + ez * ez < rCull;
         }
-        unsigned m = __ballot_sync(0xffffffffu, keep);
+        unsigned m      = __ballot_sync(0xffffffffu, keep);
+        unsigned below  = m & ((1u << lane) - 1);
+        int prevLane    = below ? 31 - __clz(below) : -1;
+        int prevJe      = __shfl_sync(0xffffffffu, int(je), prevLane < 0 ? 0 : prevLane);
+        if (prevLane < 0) prevJe = prevEnd;
+        bool start      = keep && prevJe != int(jb);
+        unsigned starts = __ballot_sync(0xffffffffu, start);
         if (keep)
         {
-            int pos = nR + __popc(m & ((1u << lane) - 1));
-            rb[pos] = int(jb);
-            re[pos] = int(je);
+            int idx = nR + __popc(starts & (0xffffffffu >> (31 - lane))) - 1; // the range this leaf belongs to
+            if (start) rb[idx] = int(jb);
+            unsigned above = lane == 31 ? 0u : (m & (0xffffffffu << (lane + 1)));
+            bool closes    = above == 0u || ((starts >> (__ffs(above) - 1)) & 1u);
+            if (closes) re[idx] = int(je);
         }
-        nR += __popc(m);
+        nR += __popc(starts);
+        if (m) prevEnd = __shfl_sync(0xffffffffu, int(je), 31 - __clz(m));
     }
     __syncwarp();
     if (nR == 0) return true;
@@ -270,7 +300,7 @@ __device__ __forceinline__ bool searchBfs(const DevTree& tree, const double* __r
     const double tgc[3]  = {0.5 * (tg.lo[0] + tg.hi[0]), 0.5 * (tg.lo[1] + tg.hi[1]), 0.5 * (tg.lo[2] + tg.hi[2])};
     const double rFilter = UsePbc ? tg.rmaxSq * (1.0 + 1e-9) : tg.rmaxSq;
     int* candIdx         = cur; // the frontier is no longer needed
-    int li = 0;
+    int li = 0, nBuf = 0;
     LocalIndex base = LocalIndex(rb[0]), end = LocalIndex(re[0]);
     double X = 0, Y = 0, Z = 0;
     bool have = base + lane < end;
@@ -301,13 +331,13 @@ __device__ __forceinline__ bool searchBfs(const DevTree& tree, const double* __r
         unsigned survivors = __ballot_sync(0xffffffffu, pass);
         if (pass)
         {
-            int pos       = __popc(survivors & ((1u << lane) - 1));
-            cand[pos]      = X;
-            cand[32 + pos] = Y;
-            cand[64 + pos] = Z;
-            candIdx[pos]   = int(base + lane);
+            int pos         = nBuf + __popc(survivors & ((1u << lane) - 1));
+            cand[pos]       = X;
+            cand[64 + pos]  = Y;
+            cand[128 + pos] = Z;
+            candIdx[pos]    = int(base + lane);
         }
-        int ns = __popc(survivors);
+        nBuf += __popc(survivors);
 
         // issue the next chunk's loads
         base += 32;
@@ -329,20 +359,56 @@ __device__ __forceinline__ bool searchBfs(const DevTree& tree, const double* __r
         }
         __syncwarp();
 
-        if (active)
+        // survivors are tested in full batches of 32 (about a third of a chunk survives the prefilter)
+        if (nBuf >= 32)
         {
-#pragma unroll 4
-            for (int k = 0; k < ns; ++k)
+            if (active)
             {
-                double d2     = distSq<UsePbc>(cand[k], cand[32 + k], cand[64 + k], xi, yi, zi, box);
-                LocalIndex jj = LocalIndex(candIdx[k]);
-                bool in       = d2 < radiusSq && jj != i;
-                if (in && count < ngmax) myList[size_t(count) * 32] = jj;
-                count += in;
+#pragma unroll 8
+                for (int k = 0; k < 32; ++k)
+                {
+                    double d2     = distSq<UsePbc>(cand[k], cand[64 + k], cand[128 + k], xi, yi, zi, box);
+                    LocalIndex jj = LocalIndex(candIdx[k]);
+                    bool in       = d2 < radiusSq && jj != i;
+                    if (in && count < ngmax) myList[size_t(count) * 32] = jj;
+                    count += in;
+                }
             }
+            __syncwarp();
+            int rem = nBuf - 32;
+            double tx = 0, ty = 0, tz = 0;
+            int ti = 0;
+            if (lane < rem)
+            {
+                tx = cand[32 + lane];
+                ty = cand[96 + lane];
+                tz = cand[160 + lane];
+                ti = candIdx[32 + lane];
+            }
+            __syncwarp();
+            if (lane < rem)
+            {
+                cand[lane]       = tx;
+                cand[64 + lane]  = ty;
+                cand[128 + lane] = tz;
+                candIdx[lane]    = ti;
+            }
+            nBuf = rem;
+            __syncwarp();
         }
-        __syncwarp();
     }
+    if (active)
+    {
+        for (int k = 0; k < nBuf; ++k)
+        {
+            double d2     = distSq<UsePbc>(cand[k], cand[64 + k], cand[128 + k], xi, yi, zi, box);
+            LocalIndex jj = LocalIndex(candIdx[k]);
+            bool in       = d2 < radiusSq && jj != i;
+            if (in && count < ngmax) myList[size_t(count) * 32] = jj;
+            count += in;
+        }
+    }
+    __syncwarp();
     return true;
 }
 
@@ -355,7 +421,7 @@ __global__ void __launch_bounds__(kNbWarps * 32)
                         const uint8_t* __restrict__ activeMask, double extFactor, uint8_t* __restrict__ gatherMask)
 {
     __shared__ TreeNodeIndex stackMem[kNbWarps][kStackSize];
-    __shared__ double candMem[kNbWarps][96];
+    __shared__ double candMem[kNbWarps][192];
     __shared__ int frontierMem[kNbWarps][3][kFrontier];
 
     const int lane  = threadIdx.x & 31;
