@@ -162,10 +162,10 @@ NCU_KERNEL = {"MomentumAndEnergy": "momentumEnergyKernel", "AVswitches": "avSwit
 
 def ncu_traffic(phase, args):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed
-    `ncu --set full` capture of this same workload (profiles/ncu_full_r01g_summary.csv: Sedov 200^3, f64).
+    `ncu --set full` capture of this same workload (profiles/ncu_full_r01h_summary.csv: Sedov 200^3, f64).
     None for any other workload: the capture does not transfer."""
     import csv
-    path = os.path.join(ROOT, "profiles", "ncu_full_r01g_summary.csv")
+    path = os.path.join(ROOT, "profiles", "ncu_full_r01h_summary.csv")
     if args.side != 200 or args.dtype != "f64" or phase not in NCU_KERNEL or not os.path.exists(path):
         return None, None
     with open(path) as fh:
@@ -174,14 +174,14 @@ def ncu_traffic(phase, args):
     ir, iw = hdr.index("dram_read [Gbyte]"), hdr.index("dram_write [Gbyte]")
     for r in rows[1:]:
         if NCU_KERNEL[phase] in r[0]:
-            return (float(r[ir]) + float(r[iw])) * 1e9, "profiles/ncu_full_r01g_summary.csv"
+            return (float(r[ir]) + float(r[iw])) * 1e9, "profiles/ncu_full_r01h_summary.csv"
     return None, None
 
 
 def ncu_column(phase, args, column):
     """one column of the committed ncu summary for the dominant kernel (None for other workloads)"""
     import csv
-    path = os.path.join(ROOT, "profiles", "ncu_full_r01g_summary.csv")
+    path = os.path.join(ROOT, "profiles", "ncu_full_r01h_summary.csv")
     if args.side != 200 or args.dtype != "f64" or phase not in NCU_KERNEL or not os.path.exists(path):
         return None
     with open(path) as fh:
@@ -482,6 +482,14 @@ def main():
                 other[name] = other_config(pkg, ctx, S, torch, name, side, what, dtype, args.dtype)
             except Exception as ex:  # diagnostics only
                 other[name] = {"error": str(ex)}
+        if args.dtype == "f64":
+            # the reference's default build is mixed precision (float fields, double coordinates and energy)
+            try:
+                other["sedov_mixed_precision"] = other_config(
+                    pkg, ctx, S, torch, "sedov", args.side, "the headline workload in the reference's default mixed "
+                    "precision (HydroType = float): 16-byte gather records", B.MIXED, "mixed")
+            except Exception as ex:
+                other["sedov_mixed_precision"] = {"error": str(ex)}
 
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,

@@ -7,7 +7,7 @@
 # (SFC keys, field gather, one radix pass).  profiles/summarize.py turns them into the committed summaries.
 set -u
 TAG=${1:-r01e}
-CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-bdt"
+CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-bdt --no-configs"
 $CMD --no-e2e > gpurun_out/plain_$TAG.log 2>&1 || exit 1
 ncu --metrics gpu__time_duration.sum --clock-control none -c 700 --csv --log-file gpurun_out/launches_$TAG.csv \
     $CMD --no-e2e > gpurun_out/ncu_launches_$TAG.log 2>&1
