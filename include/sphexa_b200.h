@@ -258,6 +258,11 @@ int sphb200_turb_get(const sphb200_turb*, double* scalars4, double* modes, doubl
 /* restart (TurbulenceData::loadOrStore): OU state and/or the text form of the random engine */
 int sphb200_turb_set_state(sphb200_turb*, const double* phases, const char* rngState);
 int sphb200_turb_rng_state(const sphb200_turb*, char* buf, size_t bufSize); /* returns the size needed */
+/* the two halves of driveTurbulence, for callers that stir range by range (sphb200_sim_step_host, the multi-rank
+ * host): advance = OU step by dt + projection + upload of the phases (once per step), stir = the kernel on [first,last) */
+int sphb200_turb_advance(sphb200_turb*, sphb200_ctx*, double dt);
+int sphb200_turb_stir(sphb200_turb*, sphb200_ctx*, int dtype, uint32_t first, uint32_t last, const double* x,
+                      const double* y, const double* z, void* ax, void* ay, void* az);
 /* driveTurbulence: advance the OU phases by dt, project, upload, add the stirring accelerations on [first,last) */
 int sphb200_turb_drive(sphb200_turb*, sphb200_ctx*, int dtype, uint32_t first, uint32_t last, const double* x,
                        const double* y, const double* z, void* ax, void* ay, void* az, double dt);

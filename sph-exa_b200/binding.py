@@ -108,7 +108,7 @@ SYMBOLS = [
     "sphb200_sim_num_global_leaves", "sphb200_sim_min_dt", "sphb200_sim_ttot", "sphb200_sim_total_neighbors",
     "sphb200_pack_ranges_peers", "sphb200_unpack_ranges_peers", "sphb200_sim_step_host", "sphb200_sim_conserved", "sphb200_sim_attach_turbulence", "sphb200_stirring", "sphb200_turb_create",
     "sphb200_turb_destroy", "sphb200_turb_num_modes", "sphb200_turb_get", "sphb200_turb_set_state",
-    "sphb200_turb_rng_state", "sphb200_turb_drive", "sphb200_conserved_quantities",
+    "sphb200_turb_rng_state", "sphb200_turb_drive", "sphb200_turb_advance", "sphb200_turb_stir", "sphb200_conserved_quantities",
     "sphb200_conserved_device_ptr", "sphb200_sim_fields", "sphb200_sim_tree", "sphb200_sim_keys", "sphb200_sim_neighbors",
     "sphb200_sim_phase_times", "sphb200_sim_set_layout", "sphb200_sim_local_timestep", "sphb200_sim_global_leaves",
     "sphb200_sim_global_counts", "sphb200_sim_leaf_counts", "sphb200_sim_get_box", "sphb200_sim_set_dt",

@@ -796,13 +796,14 @@ extern "C" int sphb200_sim_step_host(sphb200_sim* s, size_t n, const sphb200_fie
         if (!s->evRange[0])
             for (auto& e : s->evRange) SPHB200_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         uint32_t per = ((b - a + kRanges - 1) / kRanges + 127) / 128 * 128;
+        if (s->turb) CHECK_RC(sphb200_turb_advance(s->turb, ctx, dtStir)); // one OU step per time step
         for (int r = 0; r < kRanges; ++r)
         {
             uint32_t rb = std::min(b, a + r * per), re = std::min(b, rb + per);
             if (re <= rb) break;
             CHECK_RC(sphb200_momentum_energy_range(ctx, dtype, a, b, rb, re, r == 0, &s->box, &hc, s->neighbors, &f));
             if (s->turb)
-                CHECK_RC(sphb200_turb_drive(s->turb, ctx, dtype, rb, re, f.x, f.y, f.z, f.ax, f.ay, f.az, dtStir));
+                CHECK_RC(sphb200_turb_stir(s->turb, ctx, dtype, rb, re, f.x, f.y, f.z, f.ax, f.ay, f.az));
             CHECK_RC(sphb200_positions_update_h(ctx, dtype, rb, re, &s->box, &hc, s->minDt, s->minDt_m1, &f));
             SPHB200_CUDA(cudaEventRecord(s->evRange[r], ctx->stream));
             if (r == 0) stamp("range 0 computed", ctx->stream);

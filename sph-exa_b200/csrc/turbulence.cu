@@ -462,9 +462,7 @@ extern "C" int sphb200_turb_rng_state(const sphb200_turb* t, char* buf, size_t b
 
 /*! @brief driveTurbulence (driver.hpp:101-128): advance the OU phases by dt, project, upload, add the stirring
  *         accelerations to ax, ay, az of the particles [first, last) */
-extern "C" int sphb200_turb_drive(sphb200_turb* t, sphb200_ctx* ctx, int dtype, uint32_t first, uint32_t last,
-                                  const double* x, const double* y, const double* z, void* ax, void* ay, void* az,
-                                  double dt)
+extern "C" int sphb200_turb_advance(sphb200_turb* t, sphb200_ctx* ctx, double dt)
 {
     try
     {
@@ -474,6 +472,20 @@ extern "C" int sphb200_turb_drive(sphb200_turb* t, sphb200_ctx* ctx, int dtype, 
         // pageable source: the copies complete (w.r.t. the host vectors) before cudaMemcpyAsync returns
         SPHB200_CUDA(cudaMemcpyAsync(t->dRe, t->phasesReal.data(), bytes, cudaMemcpyHostToDevice, ctx->stream));
         SPHB200_CUDA(cudaMemcpyAsync(t->dIm, t->phasesImag.data(), bytes, cudaMemcpyHostToDevice, ctx->stream));
+        return 0;
+    }
+    catch (std::exception& e)
+    {
+        setError(e.what());
+        return 1;
+    }
+}
+
+extern "C" int sphb200_turb_stir(sphb200_turb* t, sphb200_ctx* ctx, int dtype, uint32_t first, uint32_t last,
+                                 const double* x, const double* y, const double* z, void* ax, void* ay, void* az)
+{
+    try
+    {
         if (last <= first || t->numModes == 0) return 0;
         if (!t->tabled || t->numModes > kMaxModesSm)
             return sphb200_stirring(ctx, dtype, first, last, x, y, z, ax, ay, az, t->numModes, t->dModes, t->dRe,
@@ -508,4 +520,12 @@ extern "C" int sphb200_turb_drive(sphb200_turb* t, sphb200_ctx* ctx, int dtype, 
         setError(e.what());
         return 1;
     }
+}
+
+extern "C" int sphb200_turb_drive(sphb200_turb* t, sphb200_ctx* ctx, int dtype, uint32_t first, uint32_t last,
+                                  const double* x, const double* y, const double* z, void* ax, void* ay, void* az,
+                                  double dt)
+{
+    if (int rc = sphb200_turb_advance(t, ctx, dt)) return rc;
+    return sphb200_turb_stir(t, ctx, dtype, first, last, x, y, z, ax, ay, az);
 }

@@ -117,6 +117,7 @@ class DistHydroVeProp:
         self.times = {}
         self.halo_bytes = 0
         self.halo_factor = 1.0
+        self.turb = None
         self._sync_profile = bool(int(os.environ.get("SPHB200_SYNC_PROFILE", "0")))
         self.sync_times = {}
 
@@ -443,7 +444,16 @@ class DistHydroVeProp:
         self.B.check(self.B.lib.sphb200_momentum_energy(self.ctx.h, self.dtype, C.c_uint32(a), C.c_uint32(b),
                                                         C.byref(self.box), C.byref(hc), self.B.ptr(self.nb),
                                                         C.byref(f_struct), None))
+        if self.turb is not None:
+            # TurbVeProp::computeForces (turb_ve.hpp:99-119): every rank advances the same OU sequence (same seed) and
+            # stirs its own particles with the time step of the previous iteration; no communication
+            self.turb.drive(self.ctx, a, b, f, self.minDt)
         T("MomentumAndEnergy")
+
+    def attachTurbulence(self, turb):
+        """turbulence-ve on P ranks: `turb` (turbulence.Turbulence) must be built from the same constants and seed on
+        every rank, as the reference's TurbulenceData is"""
+        self.turb = turb
 
     def integrate(self):
         t, ops, f, dist = self.torch, self.ops, self.f, self.dist
@@ -556,7 +566,10 @@ class DistHydroVeProp:
             dist.all_reduce(dt_dev[2:3], op=dist.ReduceOp.MIN, group=self.group)
         dt = float(dt_dev[2].item())
         self.ttot += dt
+        dt_stir = self.minDt
         self.minDt_m1, self.minDt = self.minDt, dt
+        if self.turb is not None:
+            self.turb.advance(self.ctx, dt_stir)
         send("alpha", f["alpha"][a:b], 0, n_own)
         self.exchange_halos(["alpha"])
         rest = [k for k in self.CONSERVED if k not in ("m", "h", "alpha")]
@@ -566,6 +579,8 @@ class DistHydroVeProp:
             if re <= rb:
                 break
             ops.computeMomentumEnergyRange(self.ctx, a, b, rb, re, r == 0, f, self.box, hc, self.nb)
+            if self.turb is not None:
+                self.turb.stir(self.ctx, rb, re, f)
             ops.computePositionsAndH(self.ctx, rb, re, f, self.box, hc, self.minDt, self.minDt_m1)
             ev = cur.record_event()
             with t.cuda.stream(cout):
@@ -650,7 +665,8 @@ class DistHydroVeProp:
         p = restart.rank_path(path, self.rank, self.world)
         hc = self._hc()
         bdt = self._restart_bdt(own)  # block-time-step propagators: ts:: attributes and the rung field
-        B.check(B.lib.sphb200_restart_write_bdt(p.encode(), C.byref(info), C.byref(hc), None, self.rank, self.world,
+        B.check(B.lib.sphb200_restart_write_bdt(p.encode(), C.byref(info), C.byref(hc),
+                                                self.turb.h if self.turb is not None else None, self.rank, self.world,
                                                 C.byref(fs), C.byref(bdt) if bdt is not None else None))
         return p
 
@@ -687,6 +703,12 @@ class DistHydroVeProp:
                     filled += hi - lo
                 start += c
             self._restart_extra(files, pieces, arrays)
+            if self.turb is not None:
+                # TurbulenceData::loadOrStore (turbulence_data.hpp:90-125): OU phases and the random engine
+                phases = files[0].attribute("turbulence::phases")
+                rng = files[0].attribute("rngEngineState", np.uint8)
+                if phases is not None and rng is not None:
+                    self.turb.setState(phases=phases, rng_state=rng.tobytes().rstrip(b"\0").decode())
             info = files[0].info
             self.n_global = total
             self.minDt, self.minDt_m1, self.ttot = info.minDt, info.minDt_m1, info.time

@@ -55,6 +55,18 @@ class Turbulence:
         check(lib.sphb200_turb_drive(self.h, ctx.h, dtype, C.c_uint32(first), C.c_uint32(last), ptr(d["x"]), ptr(d["y"]),
                                      ptr(d["z"]), ptr(d["ax"]), ptr(d["ay"]), ptr(d["az"]), C.c_double(dt)))
 
+    def advance(self, ctx, dt):
+        """the host half of driveTurbulence: one Ornstein-Uhlenbeck step by dt, projection, upload of the phases"""
+        check(lib.sphb200_turb_advance(self.h, ctx.h, C.c_double(dt)))
+
+    def stir(self, ctx, first, last, d):
+        """the device half: stirring accelerations of the current phases added on [first, last)"""
+        import torch
+        dtype = B.F64 if d["ax"].dtype == torch.float64 else B.MIXED
+        ptr = lambda t: C.c_void_p(t.data_ptr())
+        check(lib.sphb200_turb_stir(self.h, ctx.h, dtype, C.c_uint32(first), C.c_uint32(last), ptr(d["x"]), ptr(d["y"]),
+                                    ptr(d["z"]), ptr(d["ax"]), ptr(d["ay"]), ptr(d["az"])))
+
     def close(self):
         if self.h:
             lib.sphb200_turb_destroy(self.h)

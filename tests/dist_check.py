@@ -25,6 +25,7 @@ def main():
     ap.add_argument("--side", type=int, default=40)
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--bdt", action="store_true", help="block time steps: P ranks vs the one-rank tier-2 propagator")
+    ap.add_argument("--stir", action="store_true", help="turbulence-ve: attach the stirring driver on every rank")
     args = ap.parse_args()
     pkg = sphexa_b200_loader.load()
     from sph_exa_b200 import dist as D, binding as B
@@ -42,10 +43,17 @@ def main():
     ctx = pkg.Context(local)
     sim = D.DistHydroVeProp(pkg, ctx, box, s, B.F64, rank, world, n)
     sim.upload(mine)
+    make_turb = None
+    if args.stir:
+        from sph_exa_b200.turbulence import Turbulence
+        make_turb = Turbulence  # same constants and seed everywhere: every instance produces the same OU sequence
+        sim.attachTurbulence(make_turb())
     ref_sim = None
     if rank == 0:
         ref_sim = D.DistHydroVeProp(pkg, ctx, box, s, B.F64, 0, 1, n)
         ref_sim.upload(f)
+        if make_turb:
+            ref_sim.attachTurbulence(make_turb())
     names = ["x", "y", "z", "h", "vx", "vy", "vz", "temp", "alpha", "du", "xm", "kx", "divv", "ax", "nc"]
     ok = True
     for step in range(args.steps):
@@ -93,6 +101,10 @@ def main():
     for q in (sim_a, sim_b):
         q.upload(own)
         q.minDt, q.minDt_m1, q.ttot = sim.minDt, sim.minDt_m1, sim.ttot
+        if make_turb:
+            tq = make_turb()
+            tq.setState(phases=sim.turb.state()["phases"], rng_state=sim.turb.rngState())
+            q.attachTurbulence(tq)
     cap = int(n_own * 1.3) + 1024
     host = {k: torch.empty(cap, dtype=sim_b.f[k].dtype).pin_memory() for k in sim_b.CONSERVED}
     for k in sim_b.CONSERVED:
@@ -121,6 +133,8 @@ def main():
     sim.save_restart(path, args.steps)
     dist.barrier()
     again = D.DistHydroVeProp(pkg, ctx, box, s, B.F64, rank, world, n)
+    if make_turb:
+        again.attachTurbulence(make_turb())  # the dump carries the OU phases and the random engine
     it = again.load_restart(path)
     ok = ok and it == args.steps and (again.minDt, again.minDt_m1, again.ttot) == (sim.minDt, sim.minDt_m1, sim.ttot)
     for _ in range(2):
@@ -136,6 +150,8 @@ def main():
         print(f"restart on {world} ranks bit-identical per rank: {flags}", flush=True)
         ok = ok and all(flags)
         one = D.DistHydroVeProp(pkg, ctx, box, s, B.F64, 0, 1, n)
+        if make_turb:
+            one.attachTurbulence(make_turb())
         one.load_restart(path)  # reads both files
         for _ in range(2):
             one.step()

@@ -35,3 +35,15 @@ def test_two_ranks_block_time_steps():
            "--side", "40", "--steps", "10", "--bdt"]
     res = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
     assert res.returncode == 0 and "DIST_CHECK PASS" in res.stdout, res.stdout[-3000:] + res.stderr[-3000:]
+
+
+def test_two_ranks_stirred_turbulence():
+    """turbulence-ve on 2 ranks (every rank advances the same OU sequence and stirs its own particles) == 1 rank;
+    step_host with the stirring kernel per range == step; restart carries the driver state"""
+    if _ngpu() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+           "127.0.0.1", "--master-port", "29535", os.path.join(ROOT, "tests", "dist_check.py"), "--case", "turbulence",
+           "--side", "40", "--steps", "3", "--stir"]
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
+    assert res.returncode == 0 and "DIST_CHECK PASS" in res.stdout, res.stdout[-3000:] + res.stderr[-3000:]

@@ -114,3 +114,48 @@ def test_turb_ve_propagator(pkg, ctx, ref):
     gs.close()
     gt.close()
     rt.close()
+
+
+def test_step_host_with_stirring_equals_step(pkg, ctx):
+    """TurbVeProp through sphb200_sim_step_host: the last stage runs in 16 ranges, each stirred by its own kernel launch,
+    but the Ornstein-Uhlenbeck sequence must advance once per time step — state and driver bit-identical to
+    upload + step + download"""
+    import torch
+    from sph_exa_b200 import sim as S, binding as B
+    from sph_exa_b200.turbulence import Turbulence
+    f, box, s = pkg.ic.turbulence(24)
+    n = f["x"].size
+    assert n >= 16 * 128  # the ranged path
+    a = S.HydroVeProp(ctx, box, s, capacity=n)
+    b = S.HydroVeProp(ctx, box, s, capacity=n)
+    ta, tb = Turbulence(), Turbulence()
+    a.attachTurbulence(ta)
+    b.attachTurbulence(tb)
+    a.upload(f)
+    bufs = []
+    for _ in range(2):
+        d = {k: torch.empty(n, dtype=torch.float64).pin_memory() for k in B.CONSERVED}
+        bufs.append(d)
+    for k in B.CONSERVED:
+        bufs[0][k].numpy()[:] = f[k]
+
+    def struct(d):
+        st = B.Fields()
+        for k in B.FIELD_NAMES:
+            setattr(st, k, d[k].data_ptr() if k in d else None)
+        return st
+
+    for step in range(3):
+        a.step()
+        want = a.download()
+        b.step_host(struct(bufs[0]), struct(bufs[1]), n)
+        for k in B.CONSERVED:
+            assert np.array_equal(bufs[1][k].numpy(), want[k]), (step, k)
+        assert b.minDt == a.minDt
+        assert np.array_equal(ta.state()["phases"], tb.state()["phases"]), step
+        assert ta.rngState() == tb.rngState()
+        bufs.reverse()
+    a.close()
+    b.close()
+    ta.close()
+    tb.close()
