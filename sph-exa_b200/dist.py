@@ -236,11 +236,33 @@ class DistHydroVeProp:
                 for k, a in zip(self.CONSERVED, out):
                     f[k] = a
                 pending = None
+                # only the leaving particles travel: in the sorted arrays they are the ranges below and above the one
+                # this rank keeps.  Fields of one element type go through one all-to-all, peer-major
+                # [fields x count_q] blocks (the self block is empty).
+                lo_keep, hi_keep = splits[me], splits[me + 1]
+                send_x = [0 if q == me else send[q] for q in range(P)]
+                recv_x = [0 if q == me else recv[q] for q in range(P)]
+                groups = {}
                 for k in self.CONSERVED:
-                    src = f[k]
-                    dst = t.empty(sum(recv), dtype=src.dtype, device=self.dev)
-                    dist.all_to_all_single(dst, src, output_split_sizes=recv, input_split_sizes=send, group=self.group)
-                    f[k] = dst
+                    groups.setdefault(f[k].dtype, []).append(k)
+                for dt_, names in groups.items():
+                    nf = len(names)
+                    stacked = t.stack([t.cat([f[k][:lo_keep], f[k][hi_keep:]]) for k in names])  # [nf, leaving]
+                    off, blocks = 0, []
+                    for q in range(P):
+                        blocks.append(stacked[:, off:off + send_x[q]].reshape(-1))
+                        off += send_x[q]
+                    sendbuf = t.cat(blocks) if blocks else stacked.reshape(-1)
+                    recvbuf = t.empty(nf * sum(recv_x), dtype=dt_, device=self.dev)
+                    dist.all_to_all_single(recvbuf, sendbuf, output_split_sizes=[nf * c for c in recv_x],
+                                           input_split_sizes=[nf * c for c in send_x], group=self.group)
+                    off, parts = 0, []
+                    for q in range(P):
+                        parts.append(recvbuf[off:off + nf * recv_x[q]].reshape(nf, recv_x[q]))
+                        off += nf * recv_x[q]
+                    got = t.cat(parts, dim=1)  # [nf, arriving]
+                    for i, k in enumerate(names):
+                        f[k] = t.cat([f[k][lo_keep:hi_keep], got[i]])
                 keys = ops.computeSfcKeysGpu(self.ctx, f["x"], f["y"], f["z"], self.box)
                 perm = ops.sortByKeyGpu(self.ctx, keys)
                 out = ops.gatherGpu(self.ctx, perm, [f[k] for k in self.CONSERVED])
@@ -744,9 +766,19 @@ def bench_main(args, pkg, METRIC, UNIT, ALGO_BYTES, load_peaks, ClockSampler):
     side = int(round(args.side * world ** (1.0 / 3.0)))
     n_global = side ** 3
     first, last = partition_range(n_global, rank, world)
-    f, box, s = pkg.ic.sedov_range(side, first, last, args.dtype)
+    case = getattr(args, "case", "sedov")
+    if case == "turbulence":
+        # BASELINE.json configs[3]: stirred subsonic turbulence, weak scaling
+        f, box, s = pkg.ic.turbulence_range(side, first, last, args.dtype)
+    elif case == "sedov":
+        f, box, s = pkg.ic.sedov_range(side, first, last, args.dtype)
+    else:
+        raise SystemExit("--case on more than one GPU: sedov or turbulence")
     ctx = pkg.Context(local_rank)
     sim = DistHydroVeProp(pkg, ctx, box, s, dtype, rank, world, n_global)
+    if case == "turbulence":
+        from .turbulence import Turbulence
+        sim.attachTurbulence(Turbulence())
     sim.upload(f)
     del f
 
@@ -828,7 +860,9 @@ def bench_main(args, pkg, METRIC, UNIT, ALGO_BYTES, load_peaks, ClockSampler):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
-            "config": {"workload": f"Sedov blast wave {side}^3 ({n_global} particles) SFC-partitioned over {world} B200 "
+            "config": {"workload": ("Stirred subsonic turbulence (turbulence-ve)" if case == "turbulence"
+                                    else "Sedov blast wave") +
+                                   f" {side}^3 ({n_global} particles) SFC-partitioned over {world} B200 "
                                    f"({args.side}^3 per GPU), NCCL halo exchange, full step",
                        "l2": "inputs larger than L2", "parallelism": f"sfc{world}"},
             "find_neighbors_ms": phase_ms.get("FindNeighbors"), "phase_ms": phase_ms,

@@ -284,6 +284,33 @@ def turbulence(side, dtype="f64", seed=7):
     return f, box, settings
 
 
+def turbulence_range(side, first, last, dtype="f64", seed=7):
+    """lattice sites [first, last) of the side^3 turbulence IC for one rank of a weak-scaling run: same lattice, h, m
+    and temperature as turbulence(); the jitter stream is seeded per slice (seed, first), so the particle set depends
+    on the partition — a synthetic stand-in for the glass blocks either way"""
+    T = _real(dtype)
+    gamma, mui = 1.001, 0.62
+    n_glob = side ** 3
+    step = 1.0 / side
+    idx = np.arange(first, last, dtype=np.int64)
+    rng = np.random.Generator(np.random.MT19937([seed, first]))
+    out = []
+    for c in (idx % side, (idx // side) % side, idx // (side * side)):
+        a = -0.5 + (c.astype(np.float64) + 0.5) * step + rng.uniform(-0.2 * step, 0.2 * step, idx.size)
+        out.append(np.clip(a, np.nextafter(-0.5, 0.5), np.nextafter(0.5, -0.5)))
+    x, y, z = out
+    n = idx.size
+    h_init = np.cbrt(3.0 / (4 * math.pi) * 100 * 1.0 / n_glob) * 0.5
+    cv = float(ideal_gas_cv(mui, gamma, T))
+    f = dict(x=x, y=y, z=z, h=np.full(n, h_init, T), m=np.full(n, 1.0 / n_glob, T), vx=np.zeros(n, T),
+             vy=np.zeros(n, T), vz=np.zeros(n, T), x_m1=np.zeros(n, T), y_m1=np.zeros(n, T), z_m1=np.zeros(n, T),
+             temp=np.full(n, 1000.0 / cv), du_m1=np.zeros(n, T), alpha=np.full(n, 0.05, T))
+    box = ([-0.5, 0.5] * 3, [1, 1, 1])
+    settings = dict(gamma=gamma, mui=mui, minDt=1e-4, minDt_m1=1e-4, ng0=100, ngmax=150, Kcour=0.4, Krho=0.06,
+                    numParticlesGlobal=n_glob)
+    return f, box, settings
+
+
 def kelvin_helmholtz(side, dtype="f64", seed=11):
     """Kelvin-Helmholtz slab (kelvin_helmholtz_init.hpp:60-181), synthetic: periodic (0,1)x(0,1)x(0,1/16),
     inner band 0.25<y<0.75 at twice the particle density, shear +-0.5 with exp(-|dy|/0.025) blend"""
