@@ -251,7 +251,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-bdt", action="store_true", help="skip the block-time-step (ve-bdt) hierarchy report")
     ap.add_argument("--no-configs", action="store_true", help="skip the Noh / turbulence / KH reports")
-    ap.add_argument("--case", default="sedov", choices=["sedov", "turbulence"],
+    ap.add_argument("--case", default="sedov", choices=["sedov", "turbulence", "noh"],
                     help="--gpus > 1 only: turbulence = BASELINE.json configs[3] (stirred, weak scaling); the headline "
                          "metric is the default")
     args = ap.parse_args()

@@ -770,10 +770,17 @@ def bench_main(args, pkg, METRIC, UNIT, ALGO_BYTES, load_peaks, ClockSampler):
     if case == "turbulence":
         # BASELINE.json configs[3]: stirred subsonic turbulence, weak scaling
         f, box, s = pkg.ic.turbulence_range(side, first, last, args.dtype)
+    elif case == "noh":
+        # BASELINE.json configs[2]: the lattice is cut to the sphere, numParticlesGlobal is the sum over the ranks
+        xyz = pkg.ic.noh_range_coords(side, first, last)
+        cnt = torch.tensor([xyz[0].size], dtype=torch.int64, device="cuda")
+        dist.all_reduce(cnt)
+        n_global = int(cnt.item())
+        f, box, s = pkg.ic.noh_range_fields(*xyz, n_global, args.dtype)
     elif case == "sedov":
         f, box, s = pkg.ic.sedov_range(side, first, last, args.dtype)
     else:
-        raise SystemExit("--case on more than one GPU: sedov or turbulence")
+        raise SystemExit("--case on more than one GPU: sedov, noh or turbulence")
     ctx = pkg.Context(local_rank)
     sim = DistHydroVeProp(pkg, ctx, box, s, dtype, rank, world, n_global)
     if case == "turbulence":
@@ -860,8 +867,9 @@ def bench_main(args, pkg, METRIC, UNIT, ALGO_BYTES, load_peaks, ClockSampler):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
-            "config": {"workload": ("Stirred subsonic turbulence (turbulence-ve)" if case == "turbulence"
-                                    else "Sedov blast wave") +
+            "config": {"workload": {"turbulence": "Stirred subsonic turbulence (turbulence-ve)",
+                                    "noh": "Noh implosion (lattice cut to the sphere, open box)"}.get(
+                                        case, "Sedov blast wave") +
                                    f" {side}^3 ({n_global} particles) SFC-partitioned over {world} B200 "
                                    f"({args.side}^3 per GPU), NCCL halo exchange, full step",
                        "l2": "inputs larger than L2", "parallelism": f"sfc{world}"},

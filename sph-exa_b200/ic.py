@@ -267,6 +267,26 @@ def noh_glass(ctx, block, cbrt_num_part, rank=0, num_ranks=1, dtype="f64", n_glo
     return _noh_fields(x, y, z, x.size if n_glob is None else n_glob, _real(dtype))
 
 
+def noh_range_coords(side, first, last, seed=42):
+    """lattice sites [first, last) of the side^3 jittered Noh lattice that lie inside the sphere r <= 0.5 (one rank's
+    share; the jitter stream is seeded per slice).  The fields need the global in-sphere count: noh_range_fields"""
+    r1 = 0.5
+    step = 2 * r1 / side
+    idx = np.arange(first, last, dtype=np.int64)
+    rng = np.random.Generator(np.random.MT19937([seed, first]))
+    out = []
+    for c in (idx % side, (idx // side) % side, idx // (side * side)):
+        a = -r1 + (c.astype(np.float64) + 0.5) * step + rng.uniform(-0.2 * step, 0.2 * step, idx.size)
+        out.append(np.clip(a, np.nextafter(-r1, r1), np.nextafter(r1, -r1)))
+    x, y, z = out
+    keep = np.sqrt(x * x + y * y + z * z) <= r1
+    return x[keep], y[keep], z[keep]
+
+
+def noh_range_fields(x, y, z, n_glob, dtype="f64"):
+    return _noh_fields(x, y, z, n_glob, _real(dtype))
+
+
 def turbulence(side, dtype="f64", seed=7):
     """subsonic turbulence IC (turbulence_init.hpp:48-97) on a jittered lattice; periodic unit box; stirring off"""
     T = _real(dtype)
