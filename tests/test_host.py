@@ -40,6 +40,39 @@ def test_equi_distant_sfc_segments(pkg, ref):
     assert pkg.ic.equi_distant_sfc_segments(2, 5, 10) == ref.equi_distant_sfc_segment(2, 5, 10)
 
 
+def test_per_rank_slices_of_the_weak_scaling_ics(pkg):
+    """turbulence_range / noh_range_coords: a rank's lattice slab for the multi-GPU runs of configs[2] and [3]"""
+    side, P = 20, 3
+    n = side ** 3
+    from sph_exa_b200.dist import partition_range
+    tot, xs = 0, []
+    for r in range(P):
+        a, b = partition_range(n, r, P)
+        f, box, s = pkg.ic.turbulence_range(side, a, b)
+        g, _, _ = pkg.ic.turbulence_range(side, a, b)
+        assert all(np.array_equal(f[k], g[k]) for k in f)            # seeded
+        assert f["x"].size == b - a and s["numParticlesGlobal"] == n
+        for k in "xyz":
+            assert f[k].min() > -0.5 and f[k].max() < 0.5
+        assert f["m"][0] == 1.0 / n
+        tot += f["x"].size
+        xs.append(f["x"])
+    assert tot == n
+    whole, _, sw = pkg.ic.turbulence(side)
+    assert whole["h"][0] == f["h"][0] and sw["Kcour"] == s["Kcour"]      # same h, m, constants as the global IC
+    cnt = 0
+    for r in range(P):
+        a, b = partition_range(n, r, P)
+        x, y, z = pkg.ic.noh_range_coords(side, a, b)
+        assert np.all(np.sqrt(x * x + y * y + z * z) <= 0.5)
+        cnt += x.size
+    assert 0.45 * n < cnt < 0.6 * n                                    # pi/6 of the cube
+    f, box, s = pkg.ic.noh_range_fields(x, y, z, cnt)
+    assert f["m"][0] == 1.0 / cnt and box[1] == [0, 0, 0] and s["numParticlesGlobal"] == cnt
+    r = np.sqrt(x * x + y * y + z * z)
+    assert np.allclose(f["vx"], -x / r) and np.allclose(f["x_m1"], f["vx"] * 1e-4)
+
+
 def test_other_ics_are_seeded_and_inside_box(pkg):
     for case, side in (("noh", 20), ("turbulence", 16), ("kh", 32)):
         a, box, s = pkg.ic.CASES[case](side)
