@@ -379,8 +379,28 @@ def main():
         srcs = [dev[k] for k in B.CONSERVED]
         dsts = [torch.empty_like(a) for a in srcs]
         t_gather = timed(lambda: ops.gatherGpu(ctx, perm, srcs, dsts))
+        # halo pack / unpack (gatherRanges / scatterRanges, halos/gather_halos_gpu.cu:41-117): the x,y,z,h,m exchange of
+        # a 200^3 rank among 8, i.e. ~10 % of the particles in ~4000 ranges of ~200 particles, 5 fields
+        eb = 8 if args.dtype == "f64" else 4
+        n_ranges, per_range = 4096, 200
+        total_h = n_ranges * per_range
+        begins = (torch.arange(n_ranges, device="cuda", dtype=torch.int64) * (n // n_ranges)).int()
+        scan = (torch.arange(n_ranges, device="cuda", dtype=torch.int64) * per_range).int()
+        hsrc = [dev[k] for k in ("x", "y", "z", "h", "m")]
+        packed = torch.empty(ops.packedBytes(total_h, hsrc), dtype=torch.uint8, device="cuda")
+        # one launch moves 0.8 M particles only: repeat over shifted ranges so that the sources do not sit in L2
+        shifts = [begins + 250 * j for j in range(8)]
+        t_pack = timed(lambda: [ops.packRanges(ctx, scan, b_, total_h, hsrc, packed) for b_ in shifts]) / len(shifts)
+        t_unpack = timed(lambda: [ops.unpackRanges(ctx, scan, b_, total_h, hsrc, packed) for b_ in shifts]) / len(shifts)
+        halo_bpp = 2 * (3 * 8 + 2 * eb)  # read + write per halo particle
+        # the observable reduction that runs every step (conserved_quantities.hpp:113-180): 9 values per particle
+        t_cons = timed(lambda: gs.conserved())
+        cons_bpp = 4 * 8 + 4 * eb + 4  # x, y, z, temp (f64) + m, vx, vy, vz + nc
         col = 0 if args.dtype == "f64" else 1
         rows = {"sfcKeys": (t_keys, 32), "radixSort (8 passes)": (t_sort, 204),
+                "haloPack (5 fields, 4096 ranges)": (t_pack * n / total_h, halo_bpp),
+                "haloUnpack (5 fields, 4096 ranges)": (t_unpack * n / total_h, halo_bpp),
+                "conservedQuantities (reduction)": (t_cons, cons_bpp),
                 "gatherFields (14 fields)": (t_gather, (228, 148)[col]),
                 "eos": (phase_ms["EquationOfState"], ALGO_BYTES["EquationOfState"][col]),
                 "positions+updateH": (phase_ms["Timestep+UpdateQuantities"], ALGO_BYTES["Timestep+UpdateQuantities"][col])}
