@@ -56,7 +56,8 @@ class HydroVeProp:
         hc.Kcour, hc.Krho = settings.get("Kcour", 0.2), settings.get("Krho", 0.06)
         hc.gamma, hc.muiConst = settings["gamma"], settings["mui"]
         hc.alphamin, hc.alphamax, hc.decay_constant = 0.05, 1.0, 0.2
-        hc.Atmin, hc.Atmax, hc.ramp = 0.1, 0.2, 1.0 / (0.2 - 0.1)
+        at0, at1 = settings.get("Atmin", 0.1), settings.get("Atmax", 0.2)  # ParticlesData::Atmin / Atmax
+        hc.Atmin, hc.Atmax, hc.ramp = at0, at1, 1.0 / (at1 - at0)
         hc.minDt, hc.minDt_m1 = settings["minDt"], settings["minDt_m1"]
         hc.wh, hc.whd = self._tables[0].ctypes.data, self._tables[1].ctypes.data
         hc.avClean = int(av_clean)
