@@ -105,6 +105,9 @@ def reference_arm(args):
     from oracle.ref_pipeline import RefSim
     import numpy as np
     real = np.float64 if args.dtype == "f64" else np.float32
+    # all host threads: torchrun exports OMP_NUM_THREADS=1 to its workers, which would turn the reference's OpenMP
+    # loops into a single-thread run on every N > 1 launch
+    ref.set_num_threads(len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1))
     side = args.ref_side
     f, box, s = pkg.ic.sedov(side, args.dtype)
     n = f["x"].size
@@ -141,6 +144,7 @@ def cpu_baseline(pkg, dtype, side=80, steps=2):
     from oracle import ref
     from oracle.ref_pipeline import RefSim
     real = np.float64 if dtype == "f64" else np.float32
+    ref.set_num_threads(len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1))
     f, box, s = pkg.ic.sedov(side, dtype)
     sim = RefSim(f, box, s, real=real)
     sim.step()  # warm-up: tree convergence from scratch, page faults
