@@ -55,6 +55,40 @@ def key_splits(sorted_keys, boundaries):
     return np.searchsorted(np.asarray(sorted_keys, np.uint64), np.asarray(boundaries, np.uint64), side="left")
 
 
+def migrate_fields(t, f, splits, send, recv, me, a2a):
+    """exchangeParticles (domaindecomp_mpi.hpp:85-173) on key-sorted arrays: rank q gets the range
+    [splits[q], splits[q+1]) of every array in `f`.  Only the leaving particles travel — the ranges below and above
+    the one this rank keeps; fields of one element type go through ONE all-to-all as peer-major [fields x count_q]
+    blocks (the self block is empty).  Returns the new arrays: kept range first, arrivals behind it in peer order (the
+    caller sorts by key afterwards).  a2a(recvbuf, sendbuf, output_split_sizes, input_split_sizes) is the collective."""
+    P = len(send)
+    lo_keep, hi_keep = splits[me], splits[me + 1]
+    send_x = [0 if q == me else int(send[q]) for q in range(P)]
+    recv_x = [0 if q == me else int(recv[q]) for q in range(P)]
+    groups = {}
+    for k, a in f.items():
+        groups.setdefault(a.dtype, []).append(k)
+    out = {}
+    for dt_, names in groups.items():
+        nf = len(names)
+        stacked = t.stack([t.cat([f[k][:lo_keep], f[k][hi_keep:]]) for k in names])  # [nf, leaving]
+        off, blocks = 0, []
+        for q in range(P):
+            blocks.append(stacked[:, off:off + send_x[q]].reshape(-1))
+            off += send_x[q]
+        sendbuf = t.cat(blocks)
+        recvbuf = t.empty(nf * sum(recv_x), dtype=dt_, device=stacked.device)
+        a2a(recvbuf, sendbuf, [nf * c for c in recv_x], [nf * c for c in send_x])
+        off, parts = 0, []
+        for q in range(P):
+            parts.append(recvbuf[off:off + nf * recv_x[q]].reshape(nf, recv_x[q]))
+            off += nf * recv_x[q]
+        got = t.cat(parts, dim=1)  # [nf, arriving]
+        for i, k in enumerate(names):
+            out[k] = t.cat([f[k][lo_keep:hi_keep], got[i]])
+    return out
+
+
 def halo_layout(rank, n_own, recv_counts):
     """[halos from ranks < me | owned | halos from ranks > me]: (start, end, n_total, offset of every peer's halos)"""
     recv = list(int(c) for c in recv_counts)
@@ -236,33 +270,11 @@ class DistHydroVeProp:
                 for k, a in zip(self.CONSERVED, out):
                     f[k] = a
                 pending = None
-                # only the leaving particles travel: in the sorted arrays they are the ranges below and above the one
-                # this rank keeps.  Fields of one element type go through one all-to-all, peer-major
-                # [fields x count_q] blocks (the self block is empty).
-                lo_keep, hi_keep = splits[me], splits[me + 1]
-                send_x = [0 if q == me else send[q] for q in range(P)]
-                recv_x = [0 if q == me else recv[q] for q in range(P)]
-                groups = {}
-                for k in self.CONSERVED:
-                    groups.setdefault(f[k].dtype, []).append(k)
-                for dt_, names in groups.items():
-                    nf = len(names)
-                    stacked = t.stack([t.cat([f[k][:lo_keep], f[k][hi_keep:]]) for k in names])  # [nf, leaving]
-                    off, blocks = 0, []
-                    for q in range(P):
-                        blocks.append(stacked[:, off:off + send_x[q]].reshape(-1))
-                        off += send_x[q]
-                    sendbuf = t.cat(blocks) if blocks else stacked.reshape(-1)
-                    recvbuf = t.empty(nf * sum(recv_x), dtype=dt_, device=self.dev)
-                    dist.all_to_all_single(recvbuf, sendbuf, output_split_sizes=[nf * c for c in recv_x],
-                                           input_split_sizes=[nf * c for c in send_x], group=self.group)
-                    off, parts = 0, []
-                    for q in range(P):
-                        parts.append(recvbuf[off:off + nf * recv_x[q]].reshape(nf, recv_x[q]))
-                        off += nf * recv_x[q]
-                    got = t.cat(parts, dim=1)  # [nf, arriving]
-                    for i, k in enumerate(names):
-                        f[k] = t.cat([f[k][lo_keep:hi_keep], got[i]])
+                def a2a(recvbuf, sendbuf, out_splits, in_splits):
+                    dist.all_to_all_single(recvbuf, sendbuf, output_split_sizes=out_splits,
+                                           input_split_sizes=in_splits, group=self.group)
+
+                f.update(migrate_fields(t, {k: f[k] for k in self.CONSERVED}, splits, send, recv, me, a2a))
                 keys = ops.computeSfcKeysGpu(self.ctx, f["x"], f["y"], f["z"], self.box)
                 perm = ops.sortByKeyGpu(self.ctx, keys)
                 out = ops.gatherGpu(self.ctx, perm, [f[k] for k in self.CONSERVED])

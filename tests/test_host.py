@@ -168,3 +168,78 @@ def test_two_rank_bookkeeping_gloo(pkg):
         assert lay == (0, own, own)
         total += own
     assert total == 16 ** 3
+
+
+def _migrate_worker(rank, world, port, q):
+    import torch
+    import torch.distributed as dist
+    sys.path.insert(0, ROOT)
+    import sphexa_b200_loader
+    sphexa_b200_loader.load()
+    from sph_exa_b200 import dist as D
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+
+    def a2a(recvbuf, sendbuf, out_splits, in_splits):
+        # all_to_all_single written with all_gather_object (gloo has no all-to-all)
+        blocks, off = [], 0
+        for c in in_splits:
+            blocks.append(sendbuf[off:off + c].clone())
+            off += c
+        everyone = [None] * world
+        dist.all_gather_object(everyone, blocks)
+        off = 0
+        for src in range(world):
+            part = everyone[src][rank]
+            assert part.numel() == out_splits[src]
+            recvbuf[off:off + part.numel()] = part
+            off += part.numel()
+
+    # rank r holds sorted keys; boundaries move so that particles leave in both directions
+    rng = np.random.Generator(np.random.MT19937(100 + rank))
+    n = 1000 + 37 * rank
+    keys = np.sort(rng.integers(0, 3000, n)).astype(np.int64)
+    bounds = np.array([0, 900, 2100, 3000])          # key range of rank q: [bounds[q], bounds[q+1])
+    splits = [int(np.searchsorted(keys, b)) for b in bounds[:-1]] + [n]
+    send = [splits[k + 1] - splits[k] for k in range(world)]
+    mat = [None] * world
+    dist.all_gather_object(mat, send)
+    recv = [mat[src][rank] for src in range(world)]
+    f = {"key": torch.from_numpy(keys), "val": torch.from_numpy(keys * 2.5 + rank * 0.125),
+         "tag": torch.full((n,), rank, dtype=torch.int32), "w": torch.from_numpy((keys % 7).astype(np.float64))}
+    out = D.migrate_fields(torch, f, splits, send, recv, rank, a2a)
+    k = out["key"].numpy()
+    assert k.size == sum(recv)
+    assert np.all((k >= bounds[rank]) & (k < bounds[rank + 1]))
+    # the kept range comes first and is untouched; every arrival kept its own fields together
+    kept = splits[rank + 1] - splits[rank]
+    assert np.array_equal(k[:kept], keys[splits[rank]:splits[rank + 1]])
+    tag = out["tag"].numpy()
+    assert np.all(tag[:kept] == rank) and np.all(tag[kept:] != rank)
+    assert np.array_equal(out["val"].numpy(), k * 2.5 + tag * 0.125)
+    assert np.array_equal(out["w"].numpy(), (k % 7).astype(np.float64))
+    totals = [None] * world
+    dist.all_gather_object(totals, (n, int(k.size), int(k.sum())))
+    q.put((rank, totals, int(keys.sum())))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_migration_moves_only_the_leaving_ranges_gloo(pkg):
+    """dist.migrate_fields on 3 ranks (CPU tensors, all-to-all emulated over gloo): every particle ends on the rank
+    owning its key, fields of a particle stay together, nothing is lost or duplicated"""
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29900 + os.getpid() % 90
+    world = 3
+    procs = [ctx.Process(target=_migrate_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=180) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    totals = res[0][1]
+    assert sum(t[0] for t in totals) == sum(t[1] for t in totals)          # particle count conserved
+    assert sum(t[2] for t in totals) == sum(r[2] for r in res)              # key checksum conserved
