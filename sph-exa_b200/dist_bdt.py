@@ -102,6 +102,11 @@ class DistHydroVeBdtProp(DistHydroVeProp):
         self.prev = self.ts.copy()
         self._halo_layout = False
 
+    def attachTurbulence(self, turb):
+        # TurbVeBdtProp on P ranks would stir the active rungs after computeForces (turb_ve.hpp:68-73); only the
+        # one-rank propagator does that so far (sphb200_sim_bdt_* with a driver attached)
+        raise NotImplementedError("stirring with block time steps is available on one rank only")
+
     def isSynced(self):
         """Propagator::isSynced (ve_hydro_bdt.hpp:220)"""
         return active_rung(self.ts.substep, self.ts.numRungs) == 0
