@@ -102,11 +102,6 @@ class DistHydroVeBdtProp(DistHydroVeProp):
         self.prev = self.ts.copy()
         self._halo_layout = False
 
-    def attachTurbulence(self, turb):
-        # TurbVeBdtProp on P ranks would stir the active rungs after computeForces (turb_ve.hpp:68-73); only the
-        # one-rank propagator does that so far (sphb200_sim_bdt_* with a driver attached)
-        raise NotImplementedError("stirring with block time steps is available on one rank only")
-
     def isSynced(self):
         """Propagator::isSynced (ve_hydro_bdt.hpp:220)"""
         return active_rung(self.ts.substep, self.ts.numRungs) == 0
@@ -191,6 +186,11 @@ class DistHydroVeBdtProp(DistHydroVeProp):
                                                   None))
             ops.groupMinTimestep(self.ctx, self.active_view, self.dt_particle, gdt)
             ops.groupAccTimestep(self.ctx, self.eta_acc_eps, self.active_view, f["ax"], f["ay"], f["az"], gdt)
+            if self.turb is not None:
+                # TurbVeBdtProp (turb_ve.hpp:68-73): the active rungs are stirred after the whole of computeForces, i.e.
+                # after the acceleration time step was taken; the kernel honours the scope's active mask, every rank
+                # advances the same OU sequence once per substep
+                self.turb.drive(self.ctx, a, b, f, self.minDt)
 
     # ---- ts_rungs.hpp:77-157 with the two all-reduces
     def _global_min(self, values):

@@ -193,9 +193,16 @@ def main_bdt(args, pkg):
     ctx = pkg.Context(local)
     sim = DistHydroVeBdtProp(pkg, ctx, box, s, B.F64, rank, world, n)
     sim.upload({k: v[first:last] for k, v in f.items()})
+    make_turb = None
+    if args.stir:
+        from sph_exa_b200.turbulence import Turbulence
+        make_turb = Turbulence
+        sim.attachTurbulence(make_turb())
     one = None
     if rank == 0:
         one = S.HydroVeBdtProp(ctx, box, s, capacity=n)
+        if make_turb:
+            one.attachTurbulence(make_turb())
         one.upload(f)
     names = ["x", "y", "z", "h", "vx", "vy", "vz", "temp", "alpha", "x_m1", "du_m1", "rung"]
     ok, partial, rungs_seen = True, 0, set()
@@ -253,6 +260,8 @@ def main_bdt(args, pkg):
     sim.save_restart(path, args.steps + extra)
     dist.barrier()
     again = DistHydroVeBdtProp(pkg, ctx, box, s, B.F64, rank, world, n)
+    if make_turb:
+        again.attachTurbulence(make_turb())
     it = again.load_restart(path)
     same = (it == args.steps + extra and again.ts.numRungs == sim.ts.numRungs
             and np.array_equal(again.ts.dt_m1, sim.ts.dt_m1) and again.isSynced()

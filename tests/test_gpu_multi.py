@@ -47,3 +47,15 @@ def test_two_ranks_stirred_turbulence():
            "--side", "40", "--steps", "3", "--stir"]
     res = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
     assert res.returncode == 0 and "DIST_CHECK PASS" in res.stdout, res.stdout[-3000:] + res.stderr[-3000:]
+
+
+def test_two_ranks_block_time_steps_with_stirring():
+    """TurbVeBdtProp on 2 ranks == the one-rank tier-2 propagator with a driver attached (the active rungs are stirred
+    after the acceleration time step, one OU step per substep on every rank); restart carries the driver state"""
+    if _ngpu() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+           "127.0.0.1", "--master-port", "29536", os.path.join(ROOT, "tests", "dist_check.py"), "--case", "sedov",
+           "--side", "40", "--steps", "10", "--bdt", "--stir"]
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
+    assert res.returncode == 0 and "DIST_CHECK PASS" in res.stdout, res.stdout[-3000:] + res.stderr[-3000:]
