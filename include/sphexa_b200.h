@@ -112,6 +112,11 @@ uint64_t sphb200_launch_count(const sphb200_ctx* ctx);
 /* host helper: fill len/inv like the cstone::Box constructor (box.hpp:128-141) */
 void sphb200_make_box(const double lim_h[6], const int bc_h[3], sphb200_box* out);
 
+/* The transition table behind sphb200_sfc_keys (host copy, for inspection and tests; no device needed): 24 states x 512
+ * inputs, entry = 9 key bits | next state << 9 for the three levels whose coordinate bits are x3 << 6 | y3 << 3 | z3,
+ * stored at the bank-swizzled position idx ^ ((idx >> 5) & 0x3E) of idx = state * 512 + input.  Returns the number of
+ * states, -1 on error. */
+int sphb200_hilbert_table(uint16_t* table_h, size_t capacity);
 /* ---- a2: computeSfcKeysGpu  (domain/include/cstone/sfc/sfc_gpu.h:39, sfc_gpu.cu:38-55) ---- */
 int sphb200_sfc_keys(sphb200_ctx*, const double* x, const double* y, const double* z, size_t n, const sphb200_box* box_h,
                      uint64_t* keys);

@@ -592,6 +592,22 @@ extern "C" int sphb200_cut_sphere(sphb200_ctx* ctx, double radius, double* x, do
     }
 }
 
+extern "C" int sphb200_hilbert_table(uint16_t* table_h, size_t capacity)
+{
+    try
+    {
+        static const std::vector<uint16_t> table = buildHilbertTable();
+        if (capacity < table.size()) throw std::runtime_error("hilbert_table: capacity < 24 * 512");
+        std::copy(table.begin(), table.end(), table_h);
+        return int(kHilbertStates);
+    }
+    catch (std::exception& e)
+    {
+        setError(e.what());
+        return -1;
+    }
+}
+
 extern "C" int sphb200_sfc_keys(sphb200_ctx* ctx, const double* x, const double* y, const double* z, size_t n,
                                 const sphb200_box* box, uint64_t* keys)
 {

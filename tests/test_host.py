@@ -73,6 +73,31 @@ def test_per_rank_slices_of_the_weak_scaling_ics(pkg):
     assert np.allclose(f["vx"], -x / r) and np.allclose(f["x_m1"], f["vx"] * 1e-4)
 
 
+def test_hilbert_transition_table(pkg, ref):
+    """the 24-state, three-levels-per-lookup table of the GPU key kernel (csrc/sfc.cu), walked on the host: seven
+    lookups reproduce iHilbert (domain/include/cstone/sfc/hilbert.hpp:58-110) for random and extreme coordinates"""
+    import ctypes as C
+    B = pkg.binding
+    tab = np.zeros(24 * 512, np.uint16)
+    assert B.lib.sphb200_hilbert_table(tab.ctypes.data_as(C.c_void_p), C.c_size_t(tab.size)) == 24
+    assert B.lib.sphb200_hilbert_table(tab.ctypes.data_as(C.c_void_p), C.c_size_t(100)) == -1
+    rng = np.random.Generator(np.random.MT19937(21))
+    n = 200_000
+    ix, iy, iz = (rng.integers(0, 1 << 21, n, dtype=np.uint32) for _ in range(3))
+    for k, v in enumerate([0, (1 << 21) - 1, 1 << 20, (1 << 20) - 1]):
+        ix[k], iy[k], iz[k] = v, v, v
+        ix[4 + k], iy[4 + k], iz[4 + k] = v, 0, (1 << 21) - 1 - v
+    key = np.zeros(n, np.uint64)
+    state = np.zeros(n, np.uint32)  # entry & 0xFE00 of the previous lookup = next state << 9
+    for g in range(6, -1, -1):
+        idx = state | (((ix >> (3 * g)) & 7) << 6) | (((iy >> (3 * g)) & 7) << 3) | ((iz >> (3 * g)) & 7)
+        e = tab[idx ^ ((idx >> 5) & 0x3E)].astype(np.uint32)
+        key = (key << np.uint64(9)) | (e & 511).astype(np.uint64)
+        state = e & 0xFE00
+    assert (state >> 9).max() < 24
+    assert np.array_equal(key, ref.hilbert_encode(ix, iy, iz))
+
+
 def test_other_ics_are_seeded_and_inside_box(pkg):
     for case, side in (("noh", 20), ("turbulence", 16), ("kh", 32)):
         a, box, s = pkg.ic.CASES[case](side)
