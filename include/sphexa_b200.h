@@ -130,6 +130,9 @@ int sphb200_assemble_cuboid(sphb200_ctx*, uint64_t keyStart, uint64_t keyEnd, co
                             const int multiplicity_h[3], const double* xBlock, const double* yBlock,
                             const double* zBlock, size_t blockSize, double* x, double* y, double* z, size_t capacity,
                             uint64_t* count_h);
+/* the octree cells sphb200_assemble_cuboid works through: cstone::spanSfcRange (sfc/common.hpp:362-400) of
+ * [keyStart, keyEnd), host only.  cells_h[0..n] with cells_h[n] = keyEnd; returns n, -1 on error. */
+int sphb200_span_sfc_range(uint64_t keyStart, uint64_t keyEnd, uint64_t* cells_h, size_t capacity);
 /* cutSphere (grid.hpp:267-300): keep the particles with sqrt(x^2+y^2+z^2) <= radius, in place, order preserved */
 int sphb200_cut_sphere(sphb200_ctx*, double radius, double* x, double* y, double* z, size_t n, uint64_t* count_h);
 /* a1: MinMaxGpu / makeGlobalBox for open axes (primitives_gpu.h:52, box_mpi.hpp:84-119); minmax_h[6] host out */

@@ -99,6 +99,13 @@ def equi_distant_sfc_segment(rank, num_ranks, leaves_per_rank=100):
     return int(out[0]), int(out[1])
 
 
+def span_sfc_range(a, b):
+    """cstone::spanSfcRange (domain/include/cstone/sfc/common.hpp:362-400): cells + the end key"""
+    out = np.zeros(200, np.uint64)
+    n = lib().ref_span_sfc_range(C.c_uint64(int(a)), C.c_uint64(int(b)), P(out))
+    return out[:n + 1].copy()
+
+
 def cut_sphere(radius, x, y, z):
     """sphexa::cutSphere (grid.hpp:267-300)"""
     x, y, z = (np.array(a, dtype=np.float64, copy=True) for a in (x, y, z))

@@ -205,6 +205,14 @@ void ref_equidistant_sfc_segment(int rank, int numRanks, int numLeavesPerRank, u
     out[1] = b;
 }
 
+int ref_span_sfc_range(uint64_t a, uint64_t b, uint64_t* out)
+{
+    int n = cstone::spanSfcRange(KeyType(a), KeyType(b));
+    cstone::spanSfcRange(KeyType(a), KeyType(b), out);
+    out[n] = b;
+    return n;
+}
+
 size_t ref_cut_sphere(double radius, double* x, double* y, double* z, size_t n)
 {
     std::vector<double> vx(x, x + n), vy(y, y + n), vz(z, z + n);

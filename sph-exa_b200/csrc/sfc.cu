@@ -592,6 +592,23 @@ extern "C" int sphb200_cut_sphere(sphb200_ctx* ctx, double radius, double* x, do
     }
 }
 
+extern "C" int sphb200_span_sfc_range(uint64_t keyStart, uint64_t keyEnd, uint64_t* cells_h, size_t capacity)
+{
+    try
+    {
+        if (keyEnd <= keyStart) return 0;
+        std::vector<KeyType> cells = spanKeyRange(keyStart, keyEnd);
+        if (cells.size() > capacity) throw std::runtime_error("span_sfc_range: capacity too small");
+        std::copy(cells.begin(), cells.end(), cells_h);
+        return int(cells.size()) - 1;
+    }
+    catch (std::exception& e)
+    {
+        setError(e.what());
+        return -1;
+    }
+}
+
 extern "C" int sphb200_hilbert_table(uint16_t* table_h, size_t capacity)
 {
     try

@@ -98,6 +98,30 @@ def test_hilbert_transition_table(pkg, ref):
     assert np.array_equal(key, ref.hilbert_encode(ix, iy, iz))
 
 
+def test_span_sfc_range(pkg, ref):
+    """the octree cells a rank's glass-block assembly works through, against cstone::spanSfcRange"""
+    import ctypes as C
+    B = pkg.binding
+    full = 1 << 63
+    rng = np.random.Generator(np.random.MT19937(8))
+    cases = [(0, full), (0, 1), (1, 2), (full - 1, full), (0o1234567 << 42, 0o1234571 << 42),
+             (12345678901234567, 0o7 << 60), (0o3 << 60, (0o3 << 60) + (1 << 30))]
+    for _ in range(200):
+        a, b = sorted(int(v) for v in rng.integers(0, full, 2, dtype=np.uint64))
+        if a < b:
+            cases.append((a, b))
+    for num_ranks in (2, 3, 7, 8):
+        cases += [pkg.ic.equi_distant_sfc_segments(r, num_ranks) for r in range(num_ranks)]
+    out = np.zeros(256, np.uint64)
+    for a, b in cases:
+        n = B.lib.sphb200_span_sfc_range(C.c_uint64(a), C.c_uint64(b), out.ctypes.data_as(C.c_void_p), C.c_size_t(256))
+        want = ref.span_sfc_range(a, b)
+        assert n == want.size - 1, (a, b)
+        assert np.array_equal(out[:n + 1], want), (a, b)
+        assert out[0] == a and out[n] == b and np.all(out[1:n + 1] > out[:n])
+    assert B.lib.sphb200_span_sfc_range(C.c_uint64(5), C.c_uint64(5), out.ctypes.data_as(C.c_void_p), C.c_size_t(256)) == 0
+
+
 def test_other_ics_are_seeded_and_inside_box(pkg):
     for case, side in (("noh", 20), ("turbulence", 16), ("kh", 32)):
         a, box, s = pkg.ic.CASES[case](side)
