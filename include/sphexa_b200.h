@@ -175,6 +175,15 @@ int sphb200_node_centers(sphb200_ctx*, const uint64_t* prefixes, int numNodes, c
                          double* centers, double* sizes);
 /* computeNodeLayout for one rank: exclusive scan of counts, layout[numLeaves+1] (domain/layout.hpp:150-163) */
 int sphb200_layout(sphb200_ctx*, const uint32_t* counts, int numLeaves, uint32_t* layout);
+/* The same scan for callers that must not allocate device memory (CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  No counterpart in the reference.  The tile
+ * sums live in a file-scope `static __device__` array of the library (16 KB per GPU that loads it, held until exit)
+ * instead of the context's grow-only arena; the call issues no cudaMalloc/cudaFree.  Limit: numLeaves <=
+ * SPHB200_LAYOUT_NOALLOC_MAX (16 777 216 = 4096 tiles of 4096 counts), beyond it the call fails with an error message
+ * and touches nothing.  All calls on one GPU share the array: calls that overlap on the device (two streams or two
+ * contexts) race; calls on one stream are safe.  Same results as sphb200_layout, bit for bit. */
+#define SPHB200_LAYOUT_NOALLOC_MAX 16777216
+int sphb200_layout_noalloc(sphb200_ctx*, const uint32_t* counts, int numLeaves, uint32_t* layout);
 
 /* ---- a13: neighbor search (traversal/find_neighbors.cuh:436-498 + xmass_gpu.cu:82-92 h iteration) ----
  * For every i in [first,last): all j != i with PBC-folded |r_ij|^2 < (2 h_i)^2 (findneighbors.hpp:95-165),

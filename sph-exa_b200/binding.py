@@ -124,7 +124,7 @@ SYMBOLS = [
     "sphb200_sim_bdt_info", "sphb200_sim_bdt_rungs", "sphb200_sim_bdt_group_dt", "sphb200_sim_bdt_active",
     "sphb200_sim_bdt_groups", "sphb200_sim_bdt_restore", "sphb200_sim_bdt_upload_rungs", "sphb200_sim_bdt_download_rungs",
     "sphb200_restart_write_bdt", "sphb200_restart_read_bytes", "sphb200_assemble_cuboid", "sphb200_cut_sphere", "sphb200_hilbert_table", "sphb200_span_sfc_range", "sphb200_momentum_energy_range", "sphb200_av_switches_courant", "sphb200_update_h_into", "sphb200_mach_square_sum", "sphb200_mach_device_ptr",
-    "sphb200_sim_mach_rms",
+    "sphb200_sim_mach_rms", "sphb200_layout_noalloc",
 ]
 
 lib.sphb200_last_error.restype = C.c_char_p

@@ -707,3 +707,79 @@ extern "C" int sphb200_unpack_ranges(sphb200_ctx* ctx, const uint32_t* rangeScan
     return rangesImpl(ctx, false, rangeScan, rangeBegin, numRanges, total, nfields, dst, elemBytes,
                       const_cast<void*>(packed));
 }
+
+// ---------------------------------------------------------------- scan without device allocation
+// sphb200_layout_noalloc: the exclusive scan behind sphb200_layout for callers that must not allocate (CUDA graph
+// capture, tight serving loops).  No counterpart in the reference.
+// The tile sums of the two-level scan live in the file-scope device array below (16 KB + 8 bytes, held by every GPU
+// that loads this library until exit) instead of the context's grow-only arena.  One level of tile sums covers
+// kNoAllocMaxTiles tiles of kScanTile counts = 16 777 216 leaves; larger inputs are rejected.  Every entry of the
+// scratch that a call reads is written by the same call first (scanTileSumsKernel fills tile sums [0, numTiles)
+// before the top-level scan reads them), so nothing has to be cleared between calls; the array keeps the last call's
+// contents and calls that overlap on the GPU (different streams or contexts of one device) race on it.
+namespace sphb200
+{
+constexpr int kNoAllocMaxTiles       = kScanTile; // the top level is scanned by ONE tile
+constexpr size_t kNoAllocMaxElements = size_t(kNoAllocMaxTiles) * kScanTile;
+static __device__ __align__(256) uint32_t g_noAllocScanScratch[kNoAllocMaxTiles + 2];
+
+constexpr int kNoAllocMaxDevices = 64;
+//! @brief device address of g_noAllocScanScratch on `device` (looked up once per device with that device current);
+//!        the symbol's name in host code is a host-side stand-in, never a device address
+static uint32_t* noAllocScratch(int device)
+{
+    static uint32_t* addr[kNoAllocMaxDevices] = {};
+    if (device < 0 || device >= kNoAllocMaxDevices) throw std::runtime_error("layout_noalloc: device id out of range");
+    uint32_t* p = __atomic_load_n(&addr[device], __ATOMIC_ACQUIRE);
+    if (p) return p;
+    int current = -1;
+    SPHB200_CUDA(cudaGetDevice(&current));
+    if (current != device) SPHB200_CUDA(cudaSetDevice(device));
+    void* sym       = nullptr;
+    cudaError_t err = cudaGetSymbolAddress(&sym, g_noAllocScanScratch);
+    if (current != device && current >= 0) cudaSetDevice(current);
+    if (err != cudaSuccess || sym == nullptr)
+        throw CudaError(std::string("layout_noalloc: cudaGetSymbolAddress failed: ") + cudaGetErrorString(err));
+    p = static_cast<uint32_t*>(sym);
+    __atomic_store_n(&addr[device], p, __ATOMIC_RELEASE); // the address is a property of the device: racing setters agree
+    return p;
+}
+} // namespace sphb200
+
+extern "C" int sphb200_layout_noalloc(sphb200_ctx* ctx, const uint32_t* counts, int numLeaves, uint32_t* layout)
+{
+    using namespace sphb200;
+    try
+    {
+        if (!ctx) throw std::runtime_error("layout_noalloc: no context");
+        if (numLeaves < 0) throw std::runtime_error("layout_noalloc: numLeaves < 0");
+        if (size_t(numLeaves) > kNoAllocMaxElements)
+            throw std::runtime_error("layout_noalloc: numLeaves = " + std::to_string(numLeaves) +
+                                     " exceeds the static scratch limit of " + std::to_string(kNoAllocMaxElements) +
+                                     " (use sphb200_layout)");
+        size_t n          = size_t(numLeaves);
+        uint32_t* total   = layout + n;
+        if (n == 0)
+        {
+            SPHB200_CUDA(cudaMemsetAsync(total, 0, sizeof(uint32_t), ctx->stream));
+            return 0;
+        }
+        size_t numTiles = (n + kScanTile - 1) / kScanTile;
+        if (numTiles == 1)
+        {
+            SPHB200_LAUNCH(ctx, scanTilesKernel, 1, kScanThreads, 0, counts, n, (const uint32_t*)nullptr, layout, total);
+            return 0;
+        }
+        uint32_t* sums = noAllocScratch(ctx->device);
+        SPHB200_LAUNCH(ctx, scanTileSumsKernel, int(numTiles), kScanThreads, 0, counts, n, sums);
+        SPHB200_LAUNCH(ctx, scanTilesKernel, 1, kScanThreads, 0, sums, numTiles, (const uint32_t*)nullptr, sums,
+                       (uint32_t*)nullptr);
+        SPHB200_LAUNCH(ctx, scanTilesKernel, int(numTiles), kScanThreads, 0, counts, n, sums, layout, total);
+        return 0;
+    }
+    catch (std::exception& e)
+    {
+        setError(e.what());
+        return 1;
+    }
+}
