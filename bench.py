@@ -94,43 +94,99 @@ class ClockSampler:
         return {"sm_mhz": med, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def host_threads():
+    return len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+
+
+SPHEXA_BIN = os.path.join(ROOT, "baseline", "_ref", "sphexa")
+
+
+def run_sphexa(side, iterations, timeout=1500):
+    """the reference's own CPU front-end (main/src/sphexa/sphexa.cpp, built by oracle/build_sphexa.sh into
+    baseline/_ref/sphexa): `sphexa --init sedov -n <side> -s <iterations> --ascii` on all host threads.  Returns
+    (seconds per iteration [list], phase seconds of the last iteration, neighbors per particle, threads)."""
+    import re
+    import tempfile
+    threads = host_threads()
+    env = dict(os.environ)
+    # torchrun exports OMP_NUM_THREADS=1 to its workers; the CPU arm gets every core of the box
+    env.update(OMP_NUM_THREADS=str(threads), OMP_PROC_BIND="close", OMP_PLACES="cores")
+    with tempfile.TemporaryDirectory() as tmp:
+        res = subprocess.run([SPHEXA_BIN, "--init", "sedov", "-n", str(side), "-s", str(iterations), "--ascii"], cwd=tmp,
+                             env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=timeout)
+    if res.returncode != 0:
+        raise RuntimeError(f"sphexa exited with {res.returncode}: {res.stdout[-400:]}")
+    it_s, phases, cur, nb = [], {}, {}, None
+    for line in res.stdout.splitlines():
+        m = re.match(r"# ([^:]+(?:::[^:]+)?): ([0-9.eE+-]+)s", line)
+        if m and not line.startswith("# Total execution"):
+            cur[m.group(1)] = cur.get(m.group(1), 0.0) + float(m.group(2))
+        m = re.match(r"=== Total time for iteration\((\d+)\) ([0-9.eE+-]+)s", line)
+        if m:
+            it_s.append(float(m.group(2)))
+            phases, cur = cur, {}
+        m = re.search(r"Avg neighbor count per particle: ([0-9.]+)", line)
+        if m:
+            nb = float(m.group(1))
+    if len(it_s) != iterations:
+        raise RuntimeError(f"sphexa printed {len(it_s)} iterations, expected {iterations}")
+    return it_s, phases, nb, threads
+
+
 def reference_arm(args):
-    """the reference's CPU implementation of the path (oracle/_ref), all host threads, bounded sample"""
+    """the reference's CPU implementation of the path on this box's host cores, all threads: the reference's own
+    `sphexa` binary on the arm's configuration (Sedov, --side^3 particles, full step).  No repo kernel, no repo module
+    and no Python inside the timed region: the times are the ones the reference prints per iteration."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    import sphexa_b200_loader
-    pkg = sphexa_b200_loader.load()
-    from oracle import ref
-    from oracle.ref_pipeline import RefSim
-    import numpy as np
-    real = np.float64 if args.dtype == "f64" else np.float32
-    # all host threads: torchrun exports OMP_NUM_THREADS=1 to its workers, which would turn the reference's OpenMP
-    # loops into a single-thread run on every N > 1 launch
-    ref.set_num_threads(len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1))
     side = args.ref_side
-    f, box, s = pkg.ic.sedov(side, args.dtype)
-    n = f["x"].size
-    sim = RefSim(f, box, s, real=real)
-    for _ in range(args.warmup):
-        sim.step()
-    t0 = time.perf_counter()
-    nb_ms = 0.0
-    for _ in range(args.steps):
-        sim.step()
-        nb_ms += sim.times["FindNeighbors"] * 1e3
-    dt = time.perf_counter() - t0
-    value = n * args.steps / dt
-    cores = ref.num_threads()
-    sample = (f"Sedov {side}^3 ({n} particles, same IC formulas, {args.dtype} types) per step instead of 200^3: "
-              f"particle-steps/s is size-independent to within the log N of the tree")
+    n = side ** 3
+    if os.path.exists(SPHEXA_BIN):
+        its, phases, nb, cores = run_sphexa(side, args.warmup + args.steps)
+        timed = its[args.warmup:]
+        dt = sum(timed)
+        value = n * len(timed) / dt
+        how = (f"baseline/_ref/sphexa --init sedov -n {side} -s {args.warmup + args.steps} --ascii (the reference's own "
+               f"front-end and CPU operators, g++ -O3 -fopenmp, OMP_PROC_BIND=close OMP_PLACES=cores), iterations "
+               f"{args.warmup + 1}..{args.warmup + args.steps} as printed by the program; the reference has one "
+               f"precision, mixed (HydroType = float, sph/types.hpp:39-46): its fp64 equivalent would be slower")
+        phase_ms = {k: v * 1e3 for k, v in phases.items()}
+        nb_ms = phase_ms.get("FindNeighbors")
+        program = "sphexa (reference front-end)"
+    else:
+        # the binary did not travel: the reference's operators behind the veneer of oracle/ref_pipeline.py
+        import numpy as np
+        os.environ.setdefault("OMP_PROC_BIND", "close")
+        os.environ.setdefault("OMP_PLACES", "cores")
+        from oracle import ref, ic_ref
+        from oracle.ref_pipeline import RefSim
+        ref.set_num_threads(host_threads())
+        f, box, s = ic_ref.sedov(side)
+        sim = RefSim(f, box, s, real=np.float64)
+        for _ in range(args.warmup):
+            sim.step()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            sim.step()
+        dt = time.perf_counter() - t0
+        value = n * args.steps / dt
+        cores = ref.num_threads()
+        phase_ms = {k: v * 1e3 for k, v in sim.times.items()}
+        nb_ms = phase_ms.get("FindNeighbors")
+        how = f"oracle/_ref operators sequenced by oracle/ref_pipeline.py, fp64, Sedov {side}^3"
+        program = "oracle/_ref veneer"
+    same = side == args.side
+    sample = (f"Sedov {side}^3 ({n} particles)" + ("" if same else f" instead of {args.side}^3") + f": {how}")
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
-        "config": {"workload": f"Sedov blast wave 200^3 SPH-VE full step; reference CPU arm timed on a {side}^3 sample",
-                   "l2": "n/a (CPU)"},
-        "find_neighbors_ms": nb_ms / args.steps,
+        "vs_baseline": None, "dtype": "mixed (reference default)" if program.startswith("sphexa") else "f64",
+        "data": "synthetic",
+        "config": {"workload": f"Sedov blast wave {side}^3 ({n} particles) SPH-VE, full step, reference CPU build on "
+                               f"{cores} host threads", "l2": "n/a (CPU)", "program": program,
+                   "same_size_as_gpu_arm": same},
+        "find_neighbors_ms": nb_ms, "phase_ms": phase_ms,
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
@@ -138,25 +194,24 @@ def reference_arm(args):
     return 0
 
 
-def cpu_baseline(pkg, dtype, side=80, steps=2):
-    """bounded CPU sample for the default run's JSON line (rank 0, N=1)"""
-    import numpy as np
-    from oracle import ref
-    from oracle.ref_pipeline import RefSim
-    real = np.float64 if dtype == "f64" else np.float32
-    ref.set_num_threads(len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1))
-    f, box, s = pkg.ic.sedov(side, dtype)
-    sim = RefSim(f, box, s, real=real)
-    sim.step()  # warm-up: tree convergence from scratch, page faults
-    t0 = time.perf_counter()
-    for _ in range(steps):
-        sim.step()
-    dt = time.perf_counter() - t0
-    n = f["x"].size
-    return {"value": n * steps / dt, "unit": UNIT, "cores": ref.num_threads(), "kind": "reference",
-            "sample": f"{steps} steps of Sedov {side}^3 ({n} particles) after 1 warm-up step, oracle/_ref (reference "
-                      f"headers, g++ -O3 -fopenmp), all host threads",
-            "find_neighbors_ms": sim.times["FindNeighbors"] * 1e3}
+def cpu_baseline(dtype):
+    """bounded CPU sample for the default run's JSON line (rank 0, N=1): the reference's own binary on 100^3 particles
+    (about 10-20 s of CPU work), plus BASELINE.json configs[0] literally (`sphexa --init sedov -n 50 -s 10`)"""
+    if not os.path.exists(SPHEXA_BIN):
+        raise RuntimeError("baseline/_ref/sphexa is missing (oracle/build_sphexa.sh builds it where /root/reference exists)")
+    its, phases, nb, cores = run_sphexa(100, 4)
+    n = 100 ** 3
+    value = n * 3 / sum(its[1:])
+    its0, _, _, _ = run_sphexa(50, 10)
+    return {"value": value, "unit": UNIT, "cores": cores, "kind": "reference",
+            "sample": "iterations 2..4 of `baseline/_ref/sphexa --init sedov -n 100 -s 4 --ascii` (1.0 M particles; the "
+                      "reference's own front-end and CPU operators, mixed precision, g++ -O3 -fopenmp, all host "
+                      "threads, OMP_PROC_BIND=close OMP_PLACES=cores)",
+            "find_neighbors_ms": phases.get("FindNeighbors", 0.0) * 1e3,
+            "phase_ms": {k: v * 1e3 for k, v in phases.items()},
+            "configs0": {"command": "sphexa --init sedov -n 50 -s 10 --ascii", "particles": 125000,
+                         "total_s": sum(its0), "iteration_s": its0,
+                         "particle_steps_per_s": 125000 * 9 / sum(its0[1:])}}
 
 
 NCU_KERNEL = {"MomentumAndEnergy": "momentumEnergyKernel", "AVswitches": "avSwitchesKernel",
@@ -250,7 +305,7 @@ def main():
     ap.add_argument("--side", type=int, default=200, help="lattice side per GPU (200 -> 8.0 M particles)")
     ap.add_argument("--dtype", default="f64", choices=["f64", "mixed"])
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--ref-side", type=int, default=100, help="lattice side of the CPU reference sample")
+    ap.add_argument("--ref-side", type=int, default=200, help="lattice side of the CPU reference arm (the arm's own 200)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-bdt", action="store_true", help="skip the block-time-step (ve-bdt) hierarchy report")
@@ -454,7 +509,7 @@ def main():
     cpu = None
     if not args.no_cpu_baseline:
         try:
-            cpu = cpu_baseline(pkg, args.dtype)
+            cpu = cpu_baseline(args.dtype)
         except Exception as ex:  # the checker library is absent: report it, never substitute
             cpu = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": f"unavailable: {ex}"}
 

@@ -417,6 +417,76 @@ void sphb200_sim_set_dt(sphb200_sim*, double minDt, double minDt_m1);
 /* set layout for multi-rank: arrays hold n particles, assigned = [start,end) */
 int sphb200_sim_set_layout(sphb200_sim*, uint32_t start, uint32_t end, uint32_t nWithHalos);
 
+/* ======================= multi-rank domain (SFC-partitioned run over several GPUs) =======================
+ * cstone::Domain<uint64_t,double,GpuTag> for P ranks (domain/include/cstone/domain/domain.hpp:65-683) with the
+ * collectives issued from C++ on the context's stream.  Two transports:
+ *  - NCCL (one process per GPU): rank 0 calls sphb200_comm_unique_id, the front-end broadcasts the 128 bytes
+ *    (MPI_Bcast in the reference's main), every rank calls sphb200_comm_create_nccl;
+ *  - loopback: P virtual ranks inside ONE process on ONE GPU, exchanges are device-to-device copies.  It exists so
+ *    that every multi-rank code path can be tested on a single GPU.
+ * Collective entry points take the handles of ALL ranks the calling process drives: one with NCCL, all P in rank
+ * order with the loopback (all on one stream). */
+typedef struct sphb200_comm sphb200_comm;
+int sphb200_comm_create_loopback(int numRanks, sphb200_comm** out);
+int sphb200_comm_unique_id(void* id128);
+int sphb200_comm_create_nccl(int device, int rank, int numRanks, const void* id128, sphb200_comm** out);
+void sphb200_comm_destroy(sphb200_comm*);
+int sphb200_comm_num_ranks(const sphb200_comm*);
+int sphb200_comm_is_loopback(const sphb200_comm*);
+
+/* Domain(rank, nRanks, bucketSize, bucketSizeFocus, theta, box) (domain.hpp:97-113): cfg.rank / cfg.numRanks name the
+ * rank; the handle is a sphb200_sim (it owns the particle arrays), so upload / download / getters / sphb200_sim_fields
+ * work on it.  The communicator must outlive the handle. */
+int sphb200_domain_create(sphb200_ctx*, const sphb200_sim_config* cfg, sphb200_comm* comm, sphb200_sim** out);
+/* Domain::sync (domain.hpp:196-244): global box, keys, sort, replicated global tree (counts all-reduced,
+ * tree/update_mpi.hpp:81-104), assignment with limitBoundaryShifts (domaindecomp.hpp:115-181), migration
+ * (domaindecomp_mpi_gpu.cuh:85-186), focus tree, halo discovery (findHalos criterion, traversal/collisions.hpp:78-105,
+ * evaluated by the owner), layout [halos | assigned | halos], exchange of x, y, z, h, m, search tree */
+int sphb200_domain_sync(sphb200_sim* const* local, int numLocal);
+/* Domain::exchangeHalos (domain.hpp:375-379, halos/exchange_halos_gpu.cuh:50-143) for the given fields;
+ * field id = position of the member in sphb200_fields (0 = x, 1 = y, ... 14 = xm, ... 31 = nc) */
+int sphb200_domain_exchange_halos(sphb200_sim* const* local, int numLocal, const int* fieldIds, int numFields);
+/* HydroVeProp on P ranks (main/src/propagator/ve_hydro.hpp:132-217): sync + computeForces with the four halo
+ * exchanges between the operators; integrate with the MIN all-reduce of the time step (ts_global.hpp:104-106) */
+int sphb200_domain_compute_forces(sphb200_sim* const* local, int numLocal);
+int sphb200_domain_integrate(sphb200_sim* const* local, int numLocal);
+int sphb200_domain_step(sphb200_sim* const* local, int numLocal);
+/* computeConservedQuantities summed over the ranks (conserved_quantities.hpp:113-180) */
+int sphb200_domain_conserved(sphb200_sim* const* local, int numLocal, double* out10_h);
+/* Domain::setHaloFactor (domain.hpp): widens the halo search radius (block time steps) */
+void sphb200_domain_set_halo_factor(sphb200_sim*, float factor);
+typedef struct sphb200_domain_info_t
+{
+    int rank, numRanks;
+    uint32_t startIndex, endIndex, nWithHalos;
+    int numGlobalLeaves, numFocusLeaves, numSearchLeaves;
+    uint32_t numSurfaceBoxes; /* halo boxes this rank published in the last sync */
+    uint32_t numSendRanges;
+    uint32_t migratedIn, migratedOut;
+    uint64_t haloBytes;       /* bytes sent in halo exchanges since creation */
+    uint32_t haloSend[32], haloRecv[32]; /* particles per peer */
+    uint64_t assignment[33];  /* SfcAssignment: rank r owns keys [assignment[r], assignment[r+1]) */
+} sphb200_domain_info_t;
+int sphb200_domain_info(const sphb200_sim*, sphb200_domain_info_t* out);
+
+/* host-only pieces of the assignment (no device needed):
+ * makeSfcAssignment + limitBoundaryShifts (domaindecomp.hpp:115-181); oldBounds_h may be NULL (first call) */
+int sphb200_sfc_assignment(int numRanks, const uint32_t* counts_h, const uint64_t* leaves_h, int numLeaves,
+                           const uint64_t* oldBounds_h, uint64_t* bounds_h, uint32_t* rankCounts_h);
+/* the tree GlobalAssignment starts from: computeSpanningTree(initialDomainSplits(P, log8ceil(100 P)))
+ * (assignment.hpp:62-69); returns the number of leaves (leaves_h gets one more key), -needed if capacity is too small */
+int sphb200_initial_global_tree(int numRanks, uint64_t* leaves_h, int capacity);
+/* findHalosGpu (traversal/collisions_gpu.h:59, collisions.hpp:78-105) on one linked octree: flags[leaf] = 1 for every
+ * leaf outside [firstLeaf, lastLeaf) whose box overlaps the halo box of a leaf inside; radii: float per leaf;
+ * flags zeroed by the caller; *numBoxes_h (may be NULL) = leaves whose halo box leaves the range */
+int sphb200_find_halos(sphb200_ctx*, const uint64_t* prefixes, const int32_t* childOffsets, const int32_t* internalToLeaf,
+                       const uint64_t* leaves, const float* radii, const sphb200_box* box_h, int firstLeaf, int lastLeaf,
+                       int* flags, int* numBoxes_h);
+/* per-leaf halo radius as Halos::discover computes it (halos/halos.hpp:166-188): float(max h of the leaf * 2 *
+ * searchExt), 0 for empty leaves */
+int sphb200_halo_radii(sphb200_ctx*, const void* h, int dtype, const uint32_t* layout, int firstLeaf, int lastLeaf,
+                       float searchExt, float* radii);
+
 /* ---- f4: restart files ----
  * The reference checkpoints through H5Part/HDF5 (main/src/io/ifile_io_hdf5.cpp, sphexa.cpp:232-246): per dump one
  * "Step#k" group with the step attributes of ParticlesData::loadOrStoreAttributes (sph/particles_data.hpp:142-193),

@@ -362,3 +362,49 @@ class RefTurbulence:
         if self.h:
             lib().ref_turb_destroy(self.h)
             self.h = None
+
+
+# ---- multi-rank domain pieces (host functions of cstone)
+def sfc_assignment(num_ranks, counts, leaves, old_bounds=None):
+    """makeSfcAssignment + limitBoundaryShifts (domaindecomp.hpp:115-181): (bounds[P+1], rank counts[P])"""
+    counts = np.ascontiguousarray(counts, np.uint32)
+    leaves = np.ascontiguousarray(leaves, np.uint64)
+    bounds = np.zeros(num_ranks + 1, np.uint64)
+    rc = np.zeros(num_ranks, np.uint32)
+    old = np.ascontiguousarray(old_bounds, np.uint64) if old_bounds is not None else None
+    lib().ref_sfc_assignment(num_ranks, P(counts), P(leaves), counts.size, P(old), P(bounds), P(rc))
+    return bounds, rc
+
+
+def initial_global_tree(num_ranks):
+    buf = np.zeros(1 << 16, np.uint64)
+    n = lib().ref_initial_global_tree(num_ranks, P(buf), buf.size)
+    assert n > 0
+    return buf[:n + 1].copy()
+
+
+def halo_radii(h, layout, first, last, search_ext=1.0):
+    h = np.ascontiguousarray(h, np.float64)
+    layout = np.ascontiguousarray(layout, np.uint32)
+    radii = np.zeros(layout.size - 1, np.float32)
+    lib().ref_halo_radii(P(h), P(layout), first, last, C.c_float(search_ext), P(radii))
+    return radii
+
+
+def find_halos(tree, leaves, radii, box, first, last):
+    """findHalos (traversal/collisions.hpp:78-105) on a linked octree from build_octree: int flags per leaf"""
+    lim, bc = _box(box)
+    leaves = np.ascontiguousarray(leaves, np.uint64)
+    radii = np.ascontiguousarray(radii, np.float32)
+    flags = np.zeros(leaves.size - 1, np.int32)
+    lib().ref_find_halos(P(tree["prefixes"]), P(tree["childOffsets"]), P(tree["internalToLeaf"]), P(leaves), P(radii),
+                         P(lim), P(bc), first, last, P(flags))
+    return flags
+
+
+def node_layout(counts, halo_flags, first, last):
+    counts = np.ascontiguousarray(counts, np.uint32)
+    halo_flags = np.ascontiguousarray(halo_flags, np.int32)
+    layout = np.zeros(counts.size + 1, np.uint32)
+    lib().ref_node_layout(P(counts), P(halo_flags), counts.size, first, last, P(layout))
+    return layout

@@ -767,3 +767,69 @@ extern "C" void ref_turb_drive_f32(void* t, uint32_t first, uint32_t last, const
 {
     refTurbDrive<float>(t, first, last, x, y, z, ax, ay, az, dt);
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// multi-rank domain pieces (header-only on the host): assignment, halo discovery, layout
+//   makeSfcAssignment / limitBoundaryShifts   domain/include/cstone/domain/domaindecomp.hpp:115-181
+//   initialDomainSplits / computeSpanningTree  domaindecomp.hpp:243-256, tree/csarray.hpp:511-534
+//   findHalos                                  traversal/collisions.hpp:78-105
+//   computeNodeLayout                          domain/layout.hpp:150-164
+#include "cstone/domain/domaindecomp.hpp"
+#include "cstone/domain/layout.hpp"
+#include "cstone/traversal/collisions.hpp"
+
+extern "C" void ref_sfc_assignment(int numRanks, const unsigned* counts, const uint64_t* leaves, int numLeaves,
+                                   const uint64_t* oldBounds, uint64_t* bounds, unsigned* rankCounts)
+{
+    std::vector<unsigned> cnt(counts, counts + numLeaves);
+    // uniformBins runs exclusive_scan(begin, end + 1): one readable element past the counts
+    cnt.reserve(numLeaves + 1);
+    auto assignment = cstone::makeSfcAssignment<KeyType>(numRanks, cnt, leaves);
+    if (oldBounds)
+    {
+        cstone::SfcAssignment<KeyType> old(numRanks);
+        for (int r = 0; r <= numRanks; ++r)
+            old.set(r, oldBounds[r], 0);
+        cstone::limitBoundaryShifts<KeyType>(old, assignment, {leaves, size_t(numLeaves) + 1}, {cnt.data(), cnt.size()});
+    }
+    for (int r = 0; r <= numRanks; ++r)
+        bounds[r] = assignment[r];
+    for (int r = 0; r < numRanks; ++r)
+        rankCounts[r] = assignment.totalCount(r);
+}
+
+extern "C" int ref_initial_global_tree(int numRanks, uint64_t* out, int capacity)
+{
+    unsigned level = cstone::log8ceil<KeyType>(100 * numRanks);
+    auto splits    = cstone::initialDomainSplits<KeyType>(numRanks, level);
+    auto tree      = cstone::computeSpanningTree<KeyType>(splits);
+    if (int(tree.size()) > capacity) return -int(tree.size());
+    std::copy(tree.begin(), tree.end(), out);
+    return int(tree.size()) - 1;
+}
+
+extern "C" void ref_find_halos(const uint64_t* prefixes, const int* childOffsets, const int* internalToLeaf,
+                               const uint64_t* leaves, const float* radii, const double* lim, const int* bc,
+                               int firstNode, int lastNode, int* flags)
+{
+    auto box = makeBox(lim, bc);
+    cstone::findHalos(prefixes, childOffsets, internalToLeaf, leaves, radii, box, firstNode, lastNode, flags);
+}
+
+//! the radii as Halos::discover prepares them on the host (halos/halos.hpp:176-188)
+extern "C" void ref_halo_radii(const double* h, const unsigned* layout, int firstNode, int lastNode, float searchExt,
+                               float* radii)
+{
+    for (int i = firstNode; i < lastNode; ++i)
+    {
+        radii[i] = 0.0f;
+        if (layout[i + 1] > layout[i]) { radii[i] = *std::max_element(h + layout[i], h + layout[i + 1]) * 2 * searchExt; }
+    }
+}
+
+extern "C" void ref_node_layout(const unsigned* counts, const int* haloFlags, int numLeaves, int firstAssigned,
+                                int lastAssigned, unsigned* layout)
+{
+    cstone::computeNodeLayout({counts, size_t(numLeaves)}, {haloFlags, size_t(numLeaves)}, firstAssigned, lastAssigned,
+                              {layout, size_t(numLeaves) + 1});
+}

@@ -125,6 +125,11 @@ SYMBOLS = [
     "sphb200_sim_bdt_groups", "sphb200_sim_bdt_restore", "sphb200_sim_bdt_upload_rungs", "sphb200_sim_bdt_download_rungs",
     "sphb200_restart_write_bdt", "sphb200_restart_read_bytes", "sphb200_assemble_cuboid", "sphb200_cut_sphere", "sphb200_hilbert_table", "sphb200_span_sfc_range", "sphb200_momentum_energy_range", "sphb200_av_switches_courant", "sphb200_update_h_into", "sphb200_mach_square_sum", "sphb200_mach_device_ptr",
     "sphb200_sim_mach_rms", "sphb200_layout_noalloc",
+    "sphb200_comm_create_loopback", "sphb200_comm_unique_id", "sphb200_comm_create_nccl", "sphb200_comm_destroy",
+    "sphb200_comm_num_ranks", "sphb200_comm_is_loopback", "sphb200_domain_create", "sphb200_domain_sync",
+    "sphb200_domain_exchange_halos", "sphb200_domain_compute_forces", "sphb200_domain_integrate", "sphb200_domain_step",
+    "sphb200_domain_conserved", "sphb200_domain_set_halo_factor", "sphb200_domain_info", "sphb200_sfc_assignment",
+    "sphb200_initial_global_tree", "sphb200_find_halos", "sphb200_halo_radii",
 ]
 
 lib.sphb200_last_error.restype = C.c_char_p

@@ -30,7 +30,8 @@ __global__ void nodeCountsKernel(const KeyType* __restrict__ leaves, int numLeav
  */
 __global__ void rebalanceDecisionKernel(const KeyType* __restrict__ leaves, const uint32_t* __restrict__ counts,
                                         int numLeaves, unsigned bucket, uint32_t* __restrict__ ops,
-                                        int* __restrict__ changed)
+                                        int* __restrict__ changed, const KeyType* __restrict__ guide = nullptr,
+                                        int numGuide = 0)
 {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i > numLeaves) return;
@@ -53,9 +54,29 @@ __global__ void rebalanceDecisionKernel(const KeyType* __restrict__ leaves, cons
         if (!siblings) siblingIdx = -1;
     }
 
+    // guide != NULL: the tree must resolve the leaves of a coarser "guide" tree (the replicated global tree of a
+    // multi-rank run, whose leaf keys are the rank boundaries): a leaf that spans more than one guide leaf is split
+    // whatever it holds, and siblings only merge into a parent that still lies inside one guide leaf.  This is what
+    // cstone's focus tree obtains with enforceKeys (focus/rebalance.hpp:189-258) plus exact foreign counts.
+    bool forceSplit = false;
+    if (guide)
+    {
+        int gi          = int(upperBound(guide, size_t(numGuide) + 1, node)) - 1;
+        KeyType gEnd    = guide[gi + 1];
+        unsigned gLevel = treeLevel(gEnd - guide[gi]);
+        if (leaves[i + 1] > gEnd) forceSplit = true;
+        if (level <= gLevel) siblingIdx = -1; // the parent would reach beyond the guide leaf
+    }
+
     uint32_t op = 1;
     bool done   = false;
-    if (siblingIdx > 0)
+    if (forceSplit)
+    {
+        op   = 8;
+        done = true;
+        changed[2] = 1;
+    }
+    if (!done && siblingIdx > 0)
     {
         const uint32_t* g = counts + i - siblingIdx;
         size_t parentCount = size_t(g[0]) + g[1] + g[2] + g[3] + g[4] + g[5] + g[6] + g[7];
@@ -190,7 +211,8 @@ __global__ void initRootKernel(KeyType* leaves, uint32_t* counts, uint32_t n)
 }
 
 static void updateOctreeImpl(sphb200_ctx* ctx, const KeyType* keys, size_t n, unsigned bucket, KeyType* leaves,
-                             uint32_t* counts, int capacity, int* numLeaves, int* converged)
+                             uint32_t* counts, int capacity, int* numLeaves, int* converged,
+                             const KeyType* guide = nullptr, int numGuide = 0, int* forced = nullptr)
 {
     int L = *numLeaves;
     // scratch: ops[L+1] | newLeaves (up to capacity+1)
@@ -201,15 +223,17 @@ static void updateOctreeImpl(sphb200_ctx* ctx, const KeyType* keys, size_t n, un
 
     int* dFlag      = ctx->devScalars;
     uint32_t* dTotal = reinterpret_cast<uint32_t*>(ctx->devScalars + 1);
-    SPHB200_CUDA(cudaMemsetAsync(dFlag, 0, 2 * sizeof(int), ctx->stream));
-    SPHB200_LAUNCH(ctx, rebalanceDecisionKernel, gridFor(L + 1, 256), 256, 0, leaves, counts, L, bucket, ops, dFlag);
+    SPHB200_CUDA(cudaMemsetAsync(dFlag, 0, 3 * sizeof(int), ctx->stream));
+    SPHB200_LAUNCH(ctx, rebalanceDecisionKernel, gridFor(L + 1, 256), 256, 0, leaves, counts, L, bucket, ops, dFlag,
+                   guide, numGuide);
     exclusiveScan(ctx, ops, ops, size_t(L) + 1, nullptr);
     // ops[L] now holds the new leaf count; fetch it together with the change flag
     SPHB200_CUDA(cudaMemcpyAsync(dTotal, ops + L, sizeof(uint32_t), cudaMemcpyDeviceToDevice, ctx->stream));
-    SPHB200_CUDA(cudaMemcpyAsync(ctx->hostScalars, ctx->devScalars, 2 * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    SPHB200_CUDA(cudaMemcpyAsync(ctx->hostScalars, ctx->devScalars, 3 * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
     SPHB200_CUDA(cudaStreamSynchronize(ctx->stream));
     int changed = ctx->hostScalars[0];
     int newL    = ctx->hostScalars[1];
+    if (forced) *forced = ctx->hostScalars[2];
     if (newL > capacity)
     {
         // nothing has been modified yet: report the required size so that the caller can retry with larger arrays
@@ -225,6 +249,18 @@ static void updateOctreeImpl(sphb200_ctx* ctx, const KeyType* keys, size_t n, un
     SPHB200_LAUNCH(ctx, nodeCountsKernel, gridFor(newL, 256), 256, 0, leaves, newL, keys, n, 0xffffffffu, counts);
     *numLeaves = newL;
     *converged = !changed;
+}
+
+void updateOctreeGuided(sphb200_ctx* ctx, const KeyType* keys, size_t n, unsigned bucket, KeyType* leaves,
+                        uint32_t* counts, int capacity, int* numLeaves, int* converged, const KeyType* guide,
+                        int numGuide, int* forced)
+{
+    updateOctreeImpl(ctx, keys, n, bucket, leaves, counts, capacity, numLeaves, converged, guide, numGuide, forced);
+}
+
+void initRootTree(sphb200_ctx* ctx, KeyType* leaves, uint32_t* counts, uint32_t n)
+{
+    SPHB200_LAUNCH(ctx, initRootKernel, 1, 1, 0, leaves, counts, n);
 }
 
 } // namespace sphb200

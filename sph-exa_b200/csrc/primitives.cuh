@@ -9,4 +9,10 @@ void exclusiveScan(sphb200_ctx* ctx, const uint32_t* in, uint32_t* out, size_t n
 //! @brief stable LSD radix sort of (key, payload) on bits [beginBit, endBit); payload = iota if valsAreIota
 void radixSortPairs(sphb200_ctx* ctx, KeyType* keys, uint32_t* vals, size_t n, bool valsAreIota, int beginBit,
                     int endBit);
+//! @brief one updateOctree step (rebalance + recount) that keeps the tree a refinement of the `guide` leaf array
+void updateOctreeGuided(sphb200_ctx* ctx, const KeyType* keys, size_t n, unsigned bucket, KeyType* leaves,
+                        uint32_t* counts, int capacity, int* numLeaves, int* converged, const KeyType* guide,
+                        int numGuide, int* forced);
+//! @brief leaves = {0, 2^63}, counts = {n}
+void initRootTree(sphb200_ctx* ctx, KeyType* leaves, uint32_t* counts, uint32_t n);
 } // namespace sphb200

@@ -36,7 +36,7 @@ class HydroVeProp:
     """one rank of an SPH-VE run; data stays resident on the GPU between steps"""
 
     def __init__(self, ctx, box, settings, capacity, dtype=B.F64, rank=0, num_ranks=1, bucket_size=None,
-                 bucket_size_focus=64, av_clean=False, tables=None):
+                 bucket_size_focus=64, av_clean=False, tables=None, creator=None):
         self.ctx = ctx
         self.dtype = dtype
         self.real = np.float64 if dtype == B.F64 else np.float32
@@ -64,7 +64,10 @@ class HydroVeProp:
         self.K = K
         self.capacity = capacity
         self.h = vp()
-        check(lib.sphb200_sim_create(ctx.h, C.byref(cfg), C.byref(self.h)))
+        if creator is None:
+            check(lib.sphb200_sim_create(ctx.h, C.byref(cfg), C.byref(self.h)))
+        else:
+            check(creator(ctx.h, C.byref(cfg), C.byref(self.h)))
 
     def close(self):
         if self.h:
