@@ -329,7 +329,7 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if args.gpus > 1 or world > 1:
-        from sph_exa_b200 import dist as D
+        from sph_exa_b200 import domain as D
         return D.bench_main(args, pkg, METRIC, UNIT, ALGO_BYTES, load_peaks, ClockSampler)
 
     torch.cuda.set_device(local_rank)

@@ -451,6 +451,11 @@ int sphb200_domain_exchange_halos(sphb200_sim* const* local, int numLocal, const
 int sphb200_domain_compute_forces(sphb200_sim* const* local, int numLocal);
 int sphb200_domain_integrate(sphb200_sim* const* local, int numLocal);
 int sphb200_domain_step(sphb200_sim* const* local, int numLocal);
+/* one step on host-resident state (the call a host-resident front-end makes): upload of the owned conserved fields
+ * from pinned memory, sync + forces + integrate, download of the owned range after the step.  n_in / host_in / host_out
+ * / n_out: one entry per local rank; host_out arrays hold hostCapacity elements each (ownership moves between ranks) */
+int sphb200_domain_step_host(sphb200_sim* const* local, int numLocal, const size_t* n_in, const sphb200_fields* host_in,
+                             const sphb200_fields* host_out, size_t* n_out, size_t hostCapacity);
 /* computeConservedQuantities summed over the ranks (conserved_quantities.hpp:113-180) */
 int sphb200_domain_conserved(sphb200_sim* const* local, int numLocal, double* out10_h);
 /* Domain::setHaloFactor (domain.hpp): widens the halo search radius (block time steps) */

@@ -129,7 +129,7 @@ SYMBOLS = [
     "sphb200_comm_num_ranks", "sphb200_comm_is_loopback", "sphb200_domain_create", "sphb200_domain_sync",
     "sphb200_domain_exchange_halos", "sphb200_domain_compute_forces", "sphb200_domain_integrate", "sphb200_domain_step",
     "sphb200_domain_conserved", "sphb200_domain_set_halo_factor", "sphb200_domain_info", "sphb200_sfc_assignment",
-    "sphb200_initial_global_tree", "sphb200_find_halos", "sphb200_halo_radii",
+    "sphb200_initial_global_tree", "sphb200_find_halos", "sphb200_halo_radii", "sphb200_domain_step_host",
 ]
 
 lib.sphb200_last_error.restype = C.c_char_p

@@ -360,6 +360,14 @@ extern "C" int sphb200_sim_save(sphb200_sim* s, const char* path, uint64_t itera
     sphb200_restart_bdt bdt;
     std::vector<uint8_t> rung;
     bool haveBdt = sphb200_sim_bdt_rungs(s) != nullptr;
+    // Only ts::numRungs, ts::dt_m1 and the rung field travel (like HydroVeBdtProp::save): substep, elapsed time, drift
+    // times and rung ranges do not, and the higher rungs sit at drifted positions in the middle of a hierarchy.  The
+    // reference only writes output when Propagator::isSynced() holds (sphexa.cpp:153-181); a dump taken anywhere
+    // else would resume into a different run without any error, so it is refused.
+    if (haveBdt && !bi.isSynced)
+        throw std::runtime_error("restart: the block-time-step hierarchy is at substep " + std::to_string(bi.substep) +
+                                 " of " + std::to_string(1 << std::max(bi.numRungs - 1, 0)) +
+                                 "; dumps are only taken where the propagator is synced (isSynced)");
     if (haveBdt)
     {
         rung.resize(std::max<size_t>(n, 1));

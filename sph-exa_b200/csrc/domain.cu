@@ -1388,3 +1388,41 @@ extern "C" int sphb200_halo_radii(sphb200_ctx* ctx, const void* h, int dtype, co
                        layout, firstLeaf, lastLeaf, searchExt, radii);
     SPHB200_CATCH
 }
+
+/*! @brief one step on host-resident state for the ranks this process drives: upload of the owned conserved fields
+ *         (pinned host memory), sync + forces + integrate, download of the new owned range.  n_in[l] particles in,
+ *         n_out[l] out (the assignment moves particles between ranks); host_out arrays must hold capacity elements.
+ *         Transfers go through the compute stream (H2D first, D2H last); the single-rank sphb200_sim_step_host stages
+ *         them beside the kernels.
+ */
+extern "C" int sphb200_domain_step_host(sphb200_sim* const* sims, int numLocal, const size_t* n_in,
+                                        const sphb200_fields* host_in, const sphb200_fields* host_out, size_t* n_out,
+                                        size_t hostCapacity)
+{
+    SPHB200_TRY
+    Group g = makeGroup(sims, numLocal);
+    for (int l = 0; l < numLocal; ++l)
+        CHECK_RC(sphb200_sim_upload(g.sims[l], n_in[l], &host_in[l]));
+    domainSync(g);
+    domainForces(g);
+    domainIntegrate(g);
+    for (int l = 0; l < numLocal; ++l)
+    {
+        sphb200_sim* s = g.sims[l];
+        size_t cnt     = s->end - s->start;
+        if (cnt > hostCapacity) throw std::runtime_error("domain_step_host: host buffers too small for the owned particles");
+        sphb200_fields h = host_out[l];
+        for (int id = 0; id < kNumConserved; ++id)
+        {
+            void* dst = *fieldSlot(h, id);
+            if (!dst) continue;
+            size_t eb = s->elemBytes(id);
+            SPHB200_CUDA(cudaMemcpyAsync(dst, static_cast<char*>(s->field[id]) + size_t(s->start) * eb, cnt * eb,
+                                         cudaMemcpyDeviceToHost, s->ctx->stream));
+        }
+        n_out[l] = cnt;
+    }
+    for (auto* s : g.sims)
+        syncStream(s);
+    SPHB200_CATCH
+}

@@ -84,6 +84,11 @@ class DistHydroVeBdtProp(DistHydroVeProp):
 
     # ---- HydroVeBdtProp::save / load (ve_hydro_bdt.hpp:153-168): Timestep::loadOrStore with the prefix "ts::"
     def _restart_bdt(self, own):
+        if not self.isSynced():
+            # like sphb200_sim_save: only numRungs, dt_m1 and the rungs travel, so a dump from the middle of a
+            # hierarchy would resume into a different run (the reference writes output only when isSynced())
+            raise self.B.SphError("restart: the block-time-step hierarchy is not synced; dumps are only taken where "
+                                  "isSynced() holds")
         rung = np.ascontiguousarray(own["rung"], np.uint8)
         self._keep_rung = rung  # the struct holds a raw pointer
         return RestartBdt(int(self.ts.numRungs), (C.c_float * MAX_RUNGS)(*self.ts.dt_m1), rung.ctypes.data)

@@ -160,3 +160,202 @@ def initial_global_tree(num_ranks):
     if n <= 0:
         raise B.SphError("initial_global_tree failed")
     return buf[:n + 1].copy()
+
+
+lib.sphb200_domain_step_host.argtypes = [vp, C.c_int, vp, vp, vp, vp, C.c_size_t]
+
+
+def step_host(group, n_in, fin, fout, capacity):
+    """sphb200_domain_step_host for a group with ONE local rank: fin / fout are binding.Fields of pinned host pointers;
+    returns the number of particles this rank owns after the step"""
+    nin = (C.c_size_t * 1)(n_in)
+    nout = (C.c_size_t * 1)(0)
+    check(lib.sphb200_domain_step_host(group._arr, group.n, nin, C.byref(fin), C.byref(fout), nout, C.c_size_t(capacity)))
+    return int(nout[0])
+
+
+def nccl_comm(rank, world, local_rank):
+    """NCCL transport for a torchrun launch: the unique id travels through torch.distributed (the reference's front-end
+    would MPI_Bcast it)"""
+    import torch
+    import torch.distributed as dist
+
+    def bcast(raw):
+        t = torch.tensor(list(raw), dtype=torch.uint8, device="cuda")
+        dist.broadcast(t, 0)
+        return bytes(t.cpu().tolist())
+
+    return Comm.nccl(rank, world, local_rank, bcast)
+
+
+# ---------------------------------------------------------------------------------------------- bench entry (N > 1)
+def bench_main(args, pkg, METRIC, UNIT, ALGO_BYTES, load_peaks, ClockSampler):
+    """python bench.py --gpus N under torchrun: one rank per GPU, the C++ multi-rank domain over NCCL"""
+    import json
+    import os
+    import time
+
+    import torch
+    import torch.distributed as dist
+    from .dist import partition_range
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} needs torchrun with {args.gpus} ranks (WORLD_SIZE={world})")
+    torch.cuda.set_device(local_rank)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    dtype = B.F64 if args.dtype == "f64" else B.MIXED
+
+    side = int(round(args.side * world ** (1.0 / 3.0)))  # weak scaling: args.side^3 particles per GPU
+    n_global = side ** 3
+    first, last = partition_range(n_global, rank, world)
+    case = getattr(args, "case", "sedov")
+    if case == "turbulence":
+        f, box, s = pkg.ic.turbulence_range(side, first, last, args.dtype)
+    elif case == "noh":
+        xyz = pkg.ic.noh_range_coords(side, first, last)
+        cnt = torch.tensor([xyz[0].size], dtype=torch.int64, device="cuda")
+        dist.all_reduce(cnt)
+        n_global = int(cnt.item())
+        f, box, s = pkg.ic.noh_range_fields(*xyz, n_global, args.dtype)
+    elif case == "sedov":
+        f, box, s = pkg.ic.sedov_range(side, first, last, args.dtype)
+    else:
+        raise SystemExit("--case on more than one GPU: sedov, noh or turbulence")
+    s = dict(s)
+    s["numParticlesGlobal"] = n_global
+    n_mine = f["x"].size
+    ctx = pkg.Context(local_rank)
+    comm = nccl_comm(rank, world, local_rank)
+    capacity = int(1.3 * n_global / world) + 65536
+    sim = DomainRank(ctx, box, s, capacity, comm, rank, dtype=dtype)
+    turb = None
+    if case == "turbulence":
+        from .turbulence import Turbulence
+        turb = Turbulence()
+        sim.attachTurbulence(turb)
+    sim.upload(f)
+    del f
+    group = DistHydroVe([sim])
+
+    def barrier():
+        dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        group.step()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    launches0 = ctx.launches
+    halo0 = sim.info().haloBytes
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        group.step()
+    e1.record()
+    barrier()
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
+    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    total_ms = float(ms.item())
+    launches = ctx.launches - launches0
+    info = sim.info()
+    halo_bytes = (info.haloBytes - halo0) / args.steps
+    clocks = sampler.stop() if rank == 0 else None
+    own = torch.tensor([info.endIndex - info.startIndex, info.nWithHalos, info.numFocusLeaves, info.numSearchLeaves,
+                        info.numSurfaceBoxes], dtype=torch.int64, device="cuda")
+    gathered = [torch.zeros_like(own) for _ in range(world)]
+    dist.all_gather(gathered, own)
+
+    # per-phase device times (cudaEvents recorded by the library; a halo exchange is counted with the operator after it)
+    phase_ms = {}
+    reps = 3
+    for _ in range(reps):
+        group.step()
+        for k, v in sim.phaseTimes().items():
+            phase_ms[k] = phase_ms.get(k, 0.0) + v / reps
+
+    e2e = None
+    if not getattr(args, "no_e2e", False):
+        real = np.float64 if args.dtype == "f64" else np.float32
+        e2e_steps = max(2, min(args.steps, 5))
+        cap = capacity
+        state = sim.download()
+        n_h = state["x"].size
+        host_in, host_out = {}, {}
+        for k in B.CONSERVED:
+            want = torch.float64 if (k in B.ALWAYS_F64 or real == np.float64) else torch.float32
+            host_in[k] = torch.empty(cap, dtype=want).pin_memory()
+            host_out[k] = torch.empty(cap, dtype=want).pin_memory()
+            host_in[k].numpy()[:n_h] = state[k]
+        del state
+
+        def structs():
+            fi, fo = B.Fields(), B.Fields()
+            for k in B.FIELD_NAMES:
+                setattr(fi, k, host_in[k].data_ptr() if k in host_in else None)
+                setattr(fo, k, host_out[k].data_ptr() if k in host_out else None)
+            return fi, fo
+
+        esz = sum(host_in[k].element_size() for k in B.CONSERVED)
+        h2d = d2h = 0
+        for it in range(1 + e2e_steps):
+            if it == 1:
+                barrier()
+                h2d = d2h = 0
+                t0 = time.perf_counter()
+            fi, fo = structs()
+            h2d += n_h * esz
+            n_h = step_host(group, n_h, fi, fo, cap)
+            d2h += n_h * esz
+            host_in, host_out = host_out, host_in
+        barrier()
+        dt_e = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+        dist.all_reduce(dt_e, op=dist.ReduceOp.MAX)
+        dt_e = float(dt_e.item())
+        e2e = {"value": n_global * e2e_steps / dt_e, "unit": UNIT, "h2d_bytes_per_step": h2d // e2e_steps,
+               "d2h_bytes_per_step": d2h // e2e_steps, "ms_per_step": dt_e / e2e_steps * 1e3, "steps": e2e_steps,
+               "note": "bytes are rank 0's; every rank moves its own share through sphb200_domain_step_host"}
+
+    if rank == 0:
+        peak, peak_src = load_peaks()
+        value = n_global * args.steps / (total_ms * 1e-3)
+        kernels = {k: v for k, v in phase_ms.items() if k not in ("domain::sync",)}
+        dom = max(kernels, key=kernels.get)
+        col = 0 if args.dtype == "f64" else 1
+        n_own = int(gathered[0][0])
+        algo = ALGO_BYTES[dom][col] * n_own
+        achieved = algo / (phase_ms[dom] * 1e-3) / 1e9
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
+            "config": {"workload": {"turbulence": "Stirred subsonic turbulence (turbulence-ve)",
+                                    "noh": "Noh implosion (lattice cut to the sphere, open box)"}.get(
+                                        case, "Sedov blast wave") +
+                                   f" {side}^3 ({n_global} particles) SFC-partitioned over {world} B200 "
+                                   f"({args.side}^3 per GPU), multi-rank domain in C++ (sphb200_domain_*), NCCL halo "
+                                   f"exchange and reductions issued from C++, full step",
+                       "l2": "inputs larger than L2", "parallelism": f"sfc{world}"},
+            "find_neighbors_ms": phase_ms.get("FindNeighbors"), "phase_ms": phase_ms,
+            "particles_per_rank": [[int(g[0]), int(g[1])] for g in gathered],
+            "focus_leaves_per_rank": [int(g[2]) for g in gathered],
+            "search_tree_leaves_per_rank": [int(g[3]) for g in gathered],
+            "halo_boxes_published_per_rank": [int(g[4]) for g in gathered],
+            "halo_bytes_per_step_rank0": halo_bytes, "clocks": clocks, "gpu_launches": launches,
+            "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "kernel_ms": phase_ms[dom]},
+            "e2e": e2e, "cpu_baseline": None,
+        }
+        print(json.dumps(line), flush=True)
+    barrier()
+    group.close()
+    comm.close()
+    if turb is not None:
+        turb.close()
+    dist.destroy_process_group()
+    return 0

@@ -14,6 +14,20 @@ def _ngpu():
     return torch.cuda.device_count() if torch.cuda.is_available() else 0
 
 
+@pytest.mark.parametrize("case,side", [("sedov", 40), ("noh", 40), ("turbulence", 36)])
+def test_two_ranks_nccl_domain_equals_reference(case, side):
+    """the C++ multi-rank domain over NCCL (sphb200_domain_*): every rank's owned particles == the reference's
+    single-rank CPU run (tests/domain_check.py); the same code path runs on one GPU through the loopback transport in
+    tests/test_gpu_domain_dist.py"""
+    if _ngpu() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+           "127.0.0.1", "--master-port", "29541", os.path.join(ROOT, "tests", "domain_check.py"), "--case", case,
+           "--side", str(side), "--steps", "3"]
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
+    assert res.returncode == 0 and "DOMAIN_CHECK PASS" in res.stdout, res.stdout[-3000:] + res.stderr[-3000:]
+
+
 @pytest.mark.parametrize("case,side", [("sedov", 40), ("noh", 40), ("kh", 64)])
 def test_two_ranks_equal_one_rank(case, side):
     if _ngpu() < 2:

@@ -137,7 +137,15 @@ def test_block_time_step_restart(pkg, ctx, tmp_path):
             k += 1
         return k
 
-    ka = advance(a)
+    # a dump from the middle of a hierarchy would lose substep / drift state: refused
+    a.step()
+    ka = 1
+    assert not a.isSynced()
+    with pytest.raises(B.SphError, match="synced"):
+        restart.save(a, str(tmp_path / "mid"), iteration=steps + 1, num_particles_global=n)
+    while not a.isSynced():
+        a.step()
+        ka += 1
     want = a.download(with_keys=True)
 
     b = S.HydroVeBdtProp(ctx, box, s, capacity=n, dtype=pkg.F64)
