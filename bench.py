@@ -41,6 +41,15 @@ def load_peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def measured_peaks():
+    """DFMA rate and record-gather cost measured on a B200 of this pool by profiles/microbench/peaks.cu"""
+    p = os.path.join(ROOT, "profiles", "peaks_r02.json")
+    if not os.path.exists(p):
+        return None
+    with open(p) as f:
+        return json.load(f)
+
+
 class ClockSampler:
     """samples nvidia-smi clocks / throttle reasons during the timed region"""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
@@ -214,6 +223,7 @@ def cpu_baseline(dtype):
                          "particle_steps_per_s": 125000 * 9 / sum(its0[1:])}}
 
 
+NCU_SUMMARY = "ncu_full_r01h_summary.csv"  # replaced by this round's capture when it exists
 NCU_KERNEL = {"MomentumAndEnergy": "momentumEnergyKernel", "AVswitches": "avSwitchesKernel",
               "IadVelocityDivCurl": "iadDivvCurlvKernel", "FindNeighbors": "findNeighborsKernel",
               "XMass": "xmassKernel", "Normalization & Gradh": "veDefGradhKernel"}
@@ -224,7 +234,7 @@ def ncu_traffic(phase, args):
     `ncu --set full` capture of this same workload (profiles/ncu_full_r01h_summary.csv: Sedov 200^3, f64).
     None for any other workload: the capture does not transfer."""
     import csv
-    path = os.path.join(ROOT, "profiles", "ncu_full_r01h_summary.csv")
+    path = os.path.join(ROOT, "profiles", NCU_SUMMARY)
     if args.side != 200 or args.dtype != "f64" or phase not in NCU_KERNEL or not os.path.exists(path):
         return None, None
     with open(path) as fh:
@@ -233,14 +243,14 @@ def ncu_traffic(phase, args):
     ir, iw = hdr.index("dram_read [Gbyte]"), hdr.index("dram_write [Gbyte]")
     for r in rows[1:]:
         if NCU_KERNEL[phase] in r[0]:
-            return (float(r[ir]) + float(r[iw])) * 1e9, "profiles/ncu_full_r01h_summary.csv"
+            return (float(r[ir]) + float(r[iw])) * 1e9, "profiles/" + NCU_SUMMARY
     return None, None
 
 
 def ncu_column(phase, args, column):
     """one column of the committed ncu summary for the dominant kernel (None for other workloads)"""
     import csv
-    path = os.path.join(ROOT, "profiles", "ncu_full_r01h_summary.csv")
+    path = os.path.join(ROOT, "profiles", NCU_SUMMARY)
     if args.side != 200 or args.dtype != "f64" or phase not in NCU_KERNEL or not os.path.exists(path):
         return None
     with open(path) as fh:
@@ -372,31 +382,55 @@ def main():
     num_leaves = gs.numLeaves
 
     # ---------------- roofline of the dominant kernel
+    # The pair kernels are gathers: one 32-byte record per (pair, record type) through the L1 data stage, which is what
+    # saturates (ncu: l1tex data-stage wavefronts 90-95 % of peak, DRAM 3-16 %), then the fp64 pipe.  Their roof is
+    # therefore the MEASURED gather rate and the MEASURED DFMA rate of this GPU (profiles/microbench/peaks.cu ->
+    # profiles/peaks_r02.json), not HBM; the HBM roofline is quoted for the HBM-bound kernels (hbm_kernels below) and for
+    # the step as a whole.
     peak, peak_src = load_peaks()
+    mp = measured_peaks()
     kernels = {k: v for k, v in phase_ms.items() if k not in ("domain::sync",)}
     dom = max(kernels, key=kernels.get)
     col = 0 if args.dtype == "f64" else 1
     algo = ALGO_BYTES[dom][col] * n
-    achieved = algo / (phase_ms[dom] * 1e-3) / 1e9
+    achieved_hbm = algo / (phase_ms[dom] * 1e-3) / 1e9
     traffic, traffic_src = ncu_traffic(dom, args)
-    roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
-                "algorithmic_bytes_per_launch": algo, "kernel_ms": phase_ms[dom],
-                "share_of_step": phase_ms[dom] / sum(phase_ms.values())}
-    # whole-step algorithmic traffic (1360 B f64 / 920 B mixed per particle-step)
+    pair_flop = {"XMass": 22, "Normalization & Gradh": 36, "IadVelocityDivCurl": 96, "AVswitches": 58,
+                 "MomentumAndEnergy": 150}
+    # 32-byte (f64) / 16-byte (mixed) records gathered per neighbor pair
+    pair_records = {"XMass": 1, "Normalization & Gradh": 1, "IadVelocityDivCurl": 2, "AVswitches": 2,
+                    "MomentumAndEnergy": 5}
+    pairs = float(total_nb) - n  # nc counts the particle itself
+    if dom in pair_records and mp is not None and args.dtype == "f64":
+        rec_per_s = pair_records[dom] * pairs / (phase_ms[dom] * 1e-3)
+        cyc = mp["gather_32B_record"]["lattice_neighbor_lists"]["ldg256_aos"]
+        sm_hz = (clocks.get("sm_mhz") or mp["sm_clock_max_mhz"]) * 1e6
+        rec_peak = mp["sms"] * sm_hz / cyc * 32
+        tf = pair_flop[dom] * pairs / (phase_ms[dom] * 1e-3) / 1e12
+        roofline = {"bound": "l1_gather", "kernel": dom, "achieved": rec_per_s / 1e9, "peak": rec_peak / 1e9,
+                    "unit": "G records/s (32-byte gather records through the L1 data stage)",
+                    "frac": rec_per_s / rec_peak,
+                    "peak_source": f"measured: profiles/peaks_r02.json, {cyc} SM cycles per warp-level 32-byte record "
+                                   f"gather over real neighbor lists, {mp['sms']} SMs at the sampled clock",
+                    "traffic": traffic, "traffic_source": traffic_src,
+                    "fp64": {"achieved_tflops": tf, "peak_tflops": mp["dfma_tflops"], "frac": tf / mp["dfma_tflops"],
+                             "peak_source": "measured DFMA rate (profiles/peaks_r02.json)",
+                             "flop_per_pair": pair_flop[dom]},
+                    "hbm": {"achieved": achieved_hbm, "peak": peak, "unit": "GB/s", "frac": achieved_hbm / peak,
+                            "peak_source": peak_src, "algorithmic_bytes_per_launch": algo,
+                            "note": "algorithmic field bytes only: this kernel is not HBM-bound"},
+                    "l1_wavefront_pct_of_peak_ncu": ncu_column(dom, args, "l1_data_wavefronts_pct [%]"),
+                    "fp64_pipe_pct_ncu": ncu_column(dom, args, "fp64_pipe_pct [%]"),
+                    "kernel_ms": phase_ms[dom], "share_of_step": phase_ms[dom] / sum(phase_ms.values())}
+    else:
+        roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved_hbm, "peak": peak, "unit": "GB/s",
+                    "frac": achieved_hbm / peak, "traffic": traffic, "traffic_source": traffic_src,
+                    "peak_source": peak_src, "algorithmic_bytes_per_launch": algo, "kernel_ms": phase_ms[dom],
+                    "share_of_step": phase_ms[dom] / sum(phase_ms.values())}
+    # whole-step algorithmic traffic (1360 B f64 / 920 B mixed per particle-step) against the HBM peak
     step_bytes = (1360 if args.dtype == "f64" else 920) * n
     roofline["step_achieved_gbs"] = step_bytes / (ms_per_step * 1e-3) / 1e9
     roofline["step_frac"] = roofline["step_achieved_gbs"] / peak
-    # what actually limits the pair kernels: the L1 gather stage and the fp64 pipe.  Pair math
-    # per SURVEY 8d (flop per neighbor pair); L1 figure from the committed ncu capture of this workload.
-    pair_flop = {"XMass": 22, "Normalization & Gradh": 36, "IadVelocityDivCurl": 96, "AVswitches": 58,
-                 "MomentumAndEnergy": 150}
-    if dom in pair_flop:
-        tf = pair_flop[dom] * float(total_nb) / (phase_ms[dom] * 1e-3) / 1e12
-        roofline["limiter"] = {"unit": "L1 data-stage wavefronts (gather) + fp64 pipe",
-                               "pair_tflops": tf, "precision": "fp64" if args.dtype == "f64" else "fp32+fp64",
-                               "fp64_vector_peak_nominal_tflops": 37.0,
-                               "l1_wavefront_pct_of_peak": ncu_column(dom, args, "l1_data_wavefronts_pct [%]")}
 
     # ---------------- the HBM-bound kernels of the step, one by one (north star: >= 70 % of the HBM roofline on the
     # gather kernels): the operators of Domain::sync replayed through the tier-1 ABI on the current particle state,
@@ -583,7 +617,10 @@ def main():
         "find_neighbors_ms": phase_ms.get("FindNeighbors"),
         "phase_ms": phase_ms, "total_neighbors": total_nb, "leaves": num_leaves,
         "clocks": clocks, "gpu_launches": launches, "roofline": roofline, "e2e": e2e, "cpu_baseline": cpu,
-        "hbm_kernels": hbm_kernels, "block_time_steps": bdt, "other_configs": other,
+        "hbm_kernels": hbm_kernels,
+        "hbm_fracs": ({k: round(v["frac"], 3) for k, v in hbm_kernels.items() if isinstance(v, dict) and "frac" in v}
+                      if isinstance(hbm_kernels, dict) else None),
+        "block_time_steps": bdt, "other_configs": other,
     }
     print(json.dumps(line), flush=True)
     if gs is not None:

@@ -243,9 +243,8 @@ def stirring(first, last, x, y, z, ax, ay, az, modes, pr, pi, amplitudes, sol_we
 
 def mach_square_sum(vx, vy, vz, c):
     """localMachSquareSum (main/src/observables/turbulence_mach_rms.hpp:38-56): sum of norm2(V) / (c*c) with V in
-    double and c*c in the storage type of c.  Restated (5 lines): the header pulls in sph/particles_data.hpp, which
-    does not compile in this fork (stray #endif, :270), so it cannot be built into oracle/_ref; no reference test
-    holds a value for it (parity unpinned)."""
+    double and c*c in the storage type of c.  Restated (5 lines); pinned against the reference's own template compiled
+    into oracle/_ref (ref.mach, tests/test_oracle.py::test_mach_restatement_equals_reference)."""
     v2 = vx.astype(np.float64) ** 2 + vy.astype(np.float64) ** 2 + vz.astype(np.float64) ** 2
     return float(np.sum(v2 / (c * c).astype(np.float64)))
 

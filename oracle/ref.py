@@ -408,3 +408,14 @@ def node_layout(counts, halo_flags, first, last):
     layout = np.zeros(counts.size + 1, np.uint32)
     lib().ref_node_layout(P(counts), P(halo_flags), counts.size, first, last, P(layout))
     return layout
+
+
+def mach(vx, vy, vz, c, num_particles_global):
+    """(localMachSquareSum, calculateMachRMS) of main/src/observables/turbulence_mach_rms.hpp:38-83, the reference's own
+    templates instantiated on a four-vector dataset"""
+    real = c.dtype
+    fn = lib().ref_mach_f64 if real == np.float64 else lib().ref_mach_f32
+    a = [np.ascontiguousarray(v, real) for v in (vx, vy, vz, c)]
+    out = np.zeros(2)
+    fn(P(a[0]), P(a[1]), P(a[2]), P(a[3]), C.c_size_t(c.size), C.c_uint64(num_particles_global), P(out))
+    return float(out[0]), float(out[1])

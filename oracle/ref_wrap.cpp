@@ -833,3 +833,36 @@ extern "C" void ref_node_layout(const unsigned* counts, const int* haloFlags, in
     cstone::computeNodeLayout({counts, size_t(numLeaves)}, {haloFlags, size_t(numLeaves)}, firstAssigned, lastAssigned,
                               {layout, size_t(numLeaves) + 1});
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// TurbulenceMachRMS (main/src/observables/turbulence_mach_rms.hpp:38-83): localMachSquareSum / calculateMachRMS are
+// templates on the dataset; they only touch vx, vy, vz, c and numParticlesGlobal, so a four-vector stand-in
+// instantiates the reference's own code (no ParticlesData needed)
+#include "observables/turbulence_mach_rms.hpp"
+
+template<class T>
+struct MachDataset
+{
+    using AcceleratorType = cstone::CpuTag;
+    std::vector<T> vx, vy, vz, c;
+    uint64_t numParticlesGlobal;
+};
+
+template<class T>
+static void refMach(const T* vx, const T* vy, const T* vz, const T* c, size_t n, uint64_t numParticlesGlobal, double* out2)
+{
+    MachDataset<T> d{{vx, vx + n}, {vy, vy + n}, {vz, vz + n}, {c, c + n}, numParticlesGlobal};
+    out2[0] = sphexa::localMachSquareSum(0, n, d);
+    out2[1] = sphexa::calculateMachRMS(0, n, d, MPI_COMM_WORLD);
+}
+
+extern "C" void ref_mach_f64(const double* vx, const double* vy, const double* vz, const double* c, size_t n,
+                             uint64_t numParticlesGlobal, double* out2)
+{
+    refMach(vx, vy, vz, c, n, numParticlesGlobal, out2);
+}
+extern "C" void ref_mach_f32(const float* vx, const float* vy, const float* vz, const float* c, size_t n,
+                             uint64_t numParticlesGlobal, double* out2)
+{
+    refMach(vx, vy, vz, c, n, numParticlesGlobal, out2);
+}

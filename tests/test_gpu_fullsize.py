@@ -126,3 +126,65 @@ def test_step_at_full_size(pkg, ctx, sedov200):
         assert out[k].min() >= -0.5 and out[k].max() < 0.5
     assert out["h"].min() > 0 and gs.minDt > 0
     gs.close()
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# fields against the reference at the BASELINE sizes (field parity used to stop at 48^3)
+FIELDS_FULL = ["x", "y", "z", "h", "vx", "vy", "vz", "temp", "alpha", "xm", "kx", "gradh", "prho", "c", "c11", "c12",
+               "c13", "c22", "c23", "c33", "divv", "curlv", "ax", "ay", "az", "du"]
+SCALE_GROUP = {"ax": ("ax", "ay", "az"), "ay": ("ax", "ay", "az"), "az": ("ax", "ay", "az"),
+               "c12": ("c11", "c22", "c33"), "c13": ("c11", "c22", "c33"), "c23": ("c11", "c22", "c33"),
+               "vx": ("vx", "vy", "vz"), "vy": ("vx", "vy", "vz"), "vz": ("vx", "vy", "vz")}
+
+
+def _one_reference_step(pkg, ctx, ref, f, box, s, tol=1e-10, turb=False):
+    """one computeForces + integrate of the reference's CPU operators (all host threads) against the GPU propagator:
+    keys and neighbor counts exact, every field <= tol (scaled by the magnitude of the field / its vector / tensor)"""
+    import os
+    from oracle.ref_pipeline import RefSim
+    from sph_exa_b200 import sim as S
+    ref.set_num_threads(len(os.sched_getaffinity(0)))
+    n = f["x"].size
+    gs = S.HydroVeProp(ctx, box, s, capacity=n)
+    gs.upload(f)
+    rs = RefSim(f, box, s)
+    gs.computeForces()
+    rs.computeForces()
+    out = gs.download(names=FIELDS_FULL + ["nc"], with_keys=True)
+    assert np.array_equal(out["keys"], rs.keys)
+    assert np.array_equal(out["nc"], rs.nc)
+    worst = {}
+    for k in FIELDS_FULL:
+        scale = max(max(np.abs(rs.f[g]).max() for g in SCALE_GROUP.get(k, (k,))), 1e-300)
+        worst[k] = float(np.abs(out[k] - rs.f[k]).max() / scale)
+    bad = {k: v for k, v in worst.items() if not v < tol}
+    assert not bad, f"fields beyond {tol}: {bad}"
+    gs.integrate()
+    rs.integrate()
+    assert abs(gs.minDt - rs.minDt) <= 1e-12 * rs.minDt
+    out = gs.download(names=["x", "y", "z", "h", "vx", "vy", "vz", "temp", "x_m1", "du_m1"])
+    for k, v in out.items():
+        scale = max(np.abs(rs.f[k]).max(), 1e-300)
+        assert np.abs(v - rs.f[k]).max() / scale < tol, k
+    gs.close()
+    return worst
+
+
+def test_fields_equal_reference_sedov_200(pkg, ctx, ref, sedov200):
+    """BASELINE.json configs[1], all 8 M particles: every field of one full step against the reference"""
+    f, box, s = sedov200
+    _one_reference_step(pkg, ctx, ref, f, box, s)
+
+
+def test_fields_equal_reference_noh_share(pkg, ctx, ref):
+    """BASELINE.json configs[2]: the per-GPU share of Noh 300^3 over 8 GPUs (150^3 lattice cut to the sphere, 1.77 M
+    particles, open box)"""
+    f, box, s = pkg.ic.noh(150)
+    _one_reference_step(pkg, ctx, ref, f, box, s)
+
+
+def test_fields_equal_reference_turbulence_250(pkg, ctx, ref):
+    """BASELINE.json configs[3] per GPU: 250^3 = 15.6 M jittered particles (the h iteration and the Atwood ramp are
+    active here, unlike on the Sedov lattice)"""
+    f, box, s = pkg.ic.turbulence(250)
+    _one_reference_step(pkg, ctx, ref, f, box, s)

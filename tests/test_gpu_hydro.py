@@ -89,7 +89,7 @@ def test_operators_one_by_one(pkg, ctx, ref, real, case, side, steps):
     for k in outs:
         scale = cscale if k.startswith("c") and k != "curlv" else max(np.abs(want[k]).max(), 1e-300)
         err = np.abs(to_host(d[k]).astype(np.float64) - want[k]).max() / scale
-        assert err < tol * 10, (k, err)
+        assert err < tol, (k, err)
 
     # AV switches update alpha in place: start from the pre-force alpha
     d = fresh([])
@@ -101,14 +101,14 @@ def test_operators_one_by_one(pkg, ctx, ref, real, case, side, steps):
     dt_c = ops.computeMomentumEnergy(ctx, 0, n, d, b, hc, nb)
     acc_scale = max(np.abs(want[k]).max() for k in ("ax", "ay", "az"))
     for k in ("ax", "ay", "az"):
-        assert np.abs(to_host(d[k]).astype(np.float64) - want[k]).max() / acc_scale < tol * 10, k
-    assert rel_err(to_host(d["du"]), want["du"]) < tol * 10
+        assert np.abs(to_host(d[k]).astype(np.float64) - want[k]).max() / acc_scale < tol, k
+    assert rel_err(to_host(d["du"]), want["du"]) < tol
     assert abs(dt_c - sim.minDtCourant) <= tol * abs(sim.minDtCourant)
 
     dts = ops.computeTimestep(ctx, 0, n, d, hc)
     assert abs(dts[0] - sim.minDtCourant) <= tol * abs(sim.minDtCourant)
-    assert abs(dts[1] - sim.minDtRho) <= tol * 10 * abs(sim.minDtRho)
-    assert abs(dts[2] - min(sim.minDtCourant, sim.minDtRho, 1.1 * pre_dt[0])) <= tol * 10 * dts[2]
+    assert abs(dts[1] - sim.minDtRho) <= tol * abs(sim.minDtRho)
+    assert abs(dts[2] - min(sim.minDtCourant, sim.minDtRho, 1.1 * pre_dt[0])) <= tol * dts[2]
 
     # integrate
     sim.integrate()
@@ -226,17 +226,17 @@ def test_full_steps_sedov(pkg, ctx, ref, real):
             assert gs.totalNeighbors() == int(rs.nc.sum())
         assert abs(gs.minDt - rs.minDt) <= tol * rs.minDt
         for k in ("x", "y", "z", "h", "vx", "vy", "vz", "temp", "alpha", "du", "xm", "kx", "c11", "divv"):
-            assert rel_err(out[k], rs.f[k]) < tol * 10, (step, k)
+            assert rel_err(out[k], rs.f[k]) < tol * (step + 1), (step, k)
         acc = max(np.abs(rs.f[k]).max() for k in ("ax", "ay", "az"))
         for k in ("ax", "ay", "az"):
-            assert np.abs(out[k].astype(np.float64) - rs.f[k]).max() / acc < tol * 10, (step, k)
+            assert np.abs(out[k].astype(np.float64) - rs.f[k]).max() / acc < tol * (step + 1), (step, k)
     # conserved totals (conserved_quantities.hpp:50-110)
     got = gs.download()
     tg, tr = pkg.ic.conserved_totals(got, s), pkg.ic.conserved_totals(rs.f, s)
     assert abs(tg["etot"] - tr["etot"]) <= tol * abs(tr["etot"])
     assert abs(tg["mass"] - tr["mass"]) <= 1e-12
     pscale = float(np.sum(np.abs(rs.f["m"].astype(np.float64) * rs.f["vx"].astype(np.float64)))) + 1e-300
-    assert abs(tg["px"] - tr["px"]) / pscale < tol * 10
+    assert abs(tg["px"] - tr["px"]) / pscale < tol * 3
     gs.close()
 
 
@@ -259,7 +259,7 @@ def test_full_steps_other_cases(pkg, ctx, ref, case, side):
         assert np.array_equal(out["nc"], rs.nc), (case, step)
         assert abs(gs.minDt - rs.minDt) <= 1e-10 * rs.minDt
         for k in ("x", "h", "vx", "temp", "alpha", "du"):
-            assert rel_err(out[k], rs.f[k]) < 1e-9, (case, step, k)
+            assert rel_err(out[k], rs.f[k]) < 1e-10 * (step + 1), (case, step, k)
     gs.close()
 
 
@@ -436,14 +436,14 @@ def test_early_courant_and_ranged_momentum(pkg, ctx, ref, real, case, side):
 
 @pytest.mark.parametrize("real", [np.float64, np.float32])
 def test_mach_rms(pkg, ctx, ref, real):
-    """machSquareSumGpu / TurbulenceMachRMS against the restated localMachSquareSum; run-to-run reproducible"""
-    from oracle import orc
+    """machSquareSumGpu / TurbulenceMachRMS against the reference's own localMachSquareSum / calculateMachRMS
+    (turbulence_mach_rms.hpp:38-83 compiled into oracle/_ref); run-to-run reproducible"""
     from sph_exa_b200 import ops, sim as S
     sim, pre, pre_dt, box, s = ref_state(pkg, "turbulence", 20, real, 2)
     n = sim.n
     d = device_fields(sim, ["x", "h", "vx", "vy", "vz", "c"], real)
     first, last = 37, n - 11
-    want = orc.mach_square_sum(*(sim.f[k][first:last] for k in ("vx", "vy", "vz", "c")))
+    want, _ = ref.mach(*(sim.f[k][first:last].astype(real) for k in ("vx", "vy", "vz", "c")), n)
     got = ops.machSquareSum(ctx, first, last, d)
     assert abs(got - want) <= (1e-13 if real == np.float64 else 1e-6) * want
     assert ops.machSquareSum(ctx, first, last, d) == got
@@ -455,7 +455,7 @@ def test_mach_rms(pkg, ctx, ref, real):
     gs.step()
     gs.step()
     out = gs.download(names=["vx", "vy", "vz", "c"])
-    want = orc.mach_rms(out["vx"], out["vy"], out["vz"], out["c"], f["x"].size)
+    _, want = ref.mach(out["vx"], out["vy"], out["vz"], out["c"], f["x"].size)
     assert abs(gs.machRMS() - want) <= 1e-6 * want
     assert abs(gs.machRMS(8 * f["x"].size) - want / np.sqrt(8)) <= 1e-6 * want
     gs.close()
