@@ -19,7 +19,9 @@ sed -e 's/using Tdu *= *decltype(d.du\[0\]);/using Tdu = std::decay_t<decltype(d
 printf '#pragma once\n#define GIT_BRANCH "reference"\n#define GIT_COMMIT_HASH "snapshot"\n' > "$B/gen/version.h"
 INC="-I$B/overlay -I$HERE/sphexa_cpu -I$B/gen -I$REF/domain/include -I$REF/sph/include -I$REF/sph/include/sph \
  -I$REF/ryoanji/src -I$REF/physics/cooling/include -I$REF/main/src -I/usr/local/cuda/include"
-CXXFLAGS="-std=c++20 -O3 -march=x86-64-v3 -DNDEBUG -DUSE_CUDA -fopenmp -w -include map -include sstream"
+# host TUs see thrust::device_vector in signatures: thrust's inline ABI namespace embeds __CUDA_ARCH_LIST__, which only
+# nvcc defines (1000 for sm_100a) -- give g++ the same value or the two halves do not link
+CXXFLAGS="-std=c++20 -O3 -march=x86-64-v3 -DNDEBUG -DUSE_CUDA -D__CUDA_ARCH_LIST__=1000 -fopenmp -w -include map -include sstream"
 CUFLAGS="-std=c++17 -O3 -DNDEBUG -DUSE_CUDA -w -gencode arch=compute_100a,code=sm_100a --expt-relaxed-constexpr \
  --extended-lambda -ccbin /usr/bin/g++ -Xcompiler -fopenmp -include map -include sstream"
 CU="domain/include/cstone/focus/rebalance_gpu.cu domain/include/cstone/focus/source_center_gpu.cu
@@ -30,11 +32,13 @@ CU="domain/include/cstone/focus/rebalance_gpu.cu domain/include/cstone/focus/sou
  ryoanji/src/ryoanji/interface/ewald.cu ryoanji/src/ryoanji/interface/multipole_holder.cu
  ryoanji/src/ryoanji/interface/treebuilder.cu sph/include/sph/groups.cu sph/include/sph/hydro_std/eos_gpu.cu
  sph/include/sph/hydro_std/iad_gpu.cu sph/include/sph/hydro_std/momentum_energy_gpu.cu
- sph/include/sph/hydro_turb/stirring_gpu.cu sph/include/sph/hydro_ve/additional_fields.cu
+ sph/include/sph/hydro_turb/stirring_gpu.cu
  sph/include/sph/hydro_ve/av_switches_gpu.cu sph/include/sph/hydro_ve/eos_gpu.cu
  sph/include/sph/hydro_ve/iad_divv_curlv_gpu.cu sph/include/sph/hydro_ve/momentum_energy_gpu.cu
  sph/include/sph/hydro_ve/ve_def_gradh_gpu.cu sph/include/sph/hydro_ve/xmass_gpu.cu sph/include/sph/positions_gpu.cu
  sph/include/sph/ts_groups.cu sph/include/sph/update_h_gpu.cu"
+# (sph/include/sph/hydro_ve/additional_fields.cu, a fork-specific markRamp helper, does not compile in this snapshot;
+#  nothing under main/src calls it)
 CPP="sphexa/sphexa.cpp init/sim_init.cpp io/ifile_io_ascii.cpp io/ifile_io_hdf5.cpp observables/observables.cpp"
 JOBS=${JOBS:-8}
 fail=0
@@ -46,15 +50,20 @@ export -f run
 n=0
 for f in $CU; do
   o=$B/obj/$(echo $f | tr '/' '_').o
+  [ -s "$o" ] && continue
   ( run "$(basename $f)" $NVCC $CUFLAGS $INC -c "$REF/$f" -o "$o" ) &
   n=$((n+1)); if [ $((n % JOBS)) -eq 0 ]; then wait; fi
 done
 for f in $CPP; do
   o=$B/obj/$(echo $f | tr '/' '_').o
-  ( run "$(basename $f)" /usr/bin/g++ $CXXFLAGS $INC -c "$REF/main/src/$f" -o "$o" ) &
+  [ -s "$o" ] && continue
+  # the host TUs go through nvcc as well (-x cu): they instantiate thrust::device_vector operations, and a g++-compiled
+  # thrust CUDA backend has no kernels to launch (cudaErrorInvalidDevice in parallel_for at run time)
+  ( run "$(basename $f)" $NVCC -x cu ${CUFLAGS/-std=c++17/-std=c++20} $INC -c "$REF/main/src/$f" -o "$o" ) &
   n=$((n+1)); if [ $((n % JOBS)) -eq 0 ]; then wait; fi
 done
 wait
 ls $B/obj/*.o | wc -l
 $NVCC -gencode arch=compute_100a,code=sm_100a -Xcompiler -fopenmp $B/obj/*.o -o "$OUT/sphexa-cuda" -lcudart -lgomp
+rm -rf "$B"
 echo "built $OUT/sphexa-cuda"

@@ -17,7 +17,9 @@
 //     bucket-64 leaves instead of the requester's MAC-coarsened image of them.
 //   8 layout [halos of lower ranks | owned | halos of higher ranks], final reorder straight into it
 //   9 halo exchange of x, y, z, h, m; keys of the halos; bucket-64 tree over all local keys for the neighbor search
+#include <chrono>
 #include <cmath>
+#include <cstdlib>
 #include <numeric>
 #include "sim.cuh"
 #include "comm.cuh"
@@ -922,7 +924,9 @@ void discoverHalos(Group& g)
 }
 
 // ---- 8. layout + final reorder
-void layoutAndReorder(sphb200_sim* s, size_t srcOff)
+extern const int kEarlyIds[6];
+extern const int kLateIds[8];
+void layoutAndReorder(sphb200_sim* s, size_t srcOff, bool earlyOnly = false)
 {
     DistState* d = s->dist;
     auto* ctx    = s->ctx;
@@ -967,7 +971,8 @@ void layoutAndReorder(sphb200_sim* s, size_t srcOff)
     if (d->numSendRanges > 0 && start > 0)
         SPHB200_LAUNCH(ctx, addOffsetKernel, gridFor(d->numSendRanges, 256), 256, 0, d->dSendBegin, d->numSendRanges, start);
     // every conserved field straight to its final place (domain.hpp:532-560 updateLayout)
-    gatherInto(s, kAllConserved, kNumConserved, d->numOwn, srcOff, start, true);
+    if (earlyOnly) gatherInto(s, kEarlyIds, 6, d->numOwn, srcOff, start, true);
+    else gatherInto(s, kAllConserved, kNumConserved, d->numOwn, srcOff, start, true);
     SPHB200_CUDA(cudaMemcpyAsync(s->keys + start, d->keysTmp, size_t(d->numOwn) * sizeof(uint64_t),
                                  cudaMemcpyDeviceToDevice, ctx->stream));
     s->start = start;
@@ -1056,8 +1061,47 @@ void searchTree(sphb200_sim* s)
     CHECK_RC(sphb200_layout(ctx, d->search.counts, L, s->layout));
 }
 
-void domainSync(Group& g)
+/*! @brief hooks of the host-resident step (sphb200_domain_step_host): the sync waits for the upload groups right where it
+ *         first needs them and leaves the fields nothing needs before IAD un-reordered (lateIds) until finishReorder */
+struct SyncStaging
 {
+    bool active = false;
+    std::vector<size_t> lateSrcOff; // per local rank: where the un-reordered late fields sit
+    std::vector<bool> latePending;
+};
+
+extern const int kEarlyIds[6] = {F_x, F_y, F_z, F_h, F_m, F_temp};
+extern const int kLateIds[8]  = {F_vx, F_vy, F_vz, F_x_m1, F_y_m1, F_z_m1, F_du_m1, F_alpha};
+
+void waitUpload(sphb200_sim* s, int group)
+{
+    SPHB200_CUDA(cudaStreamWaitEvent(s->ctx->stream, s->evUp[group], 0));
+}
+
+void domainSync(Group& g, SyncStaging* st = nullptr)
+{
+    // SPHB200_SYNC_PROFILE=1: wall time of every stage (a stream synchronisation closes each one), printed by rank 0
+    static const bool profile = std::getenv("SPHB200_SYNC_PROFILE") != nullptr;
+    static double acc[16];
+    static int calls = 0;
+    auto now = []() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    double t0 = 0;
+    int stage = 0;
+    auto tick = [&]()
+    {
+        if (!profile) return;
+        for (auto* s : g.sims)
+            syncStream(s);
+        double t = now();
+        acc[stage++] += t - t0;
+        t0 = t;
+    };
+    if (profile)
+    {
+        for (auto* s : g.sims)
+            syncStream(s);
+        t0 = now();
+    }
     for (auto* s : g.sims)
     {
         s->ctx->packValid = 0;
@@ -1065,29 +1109,72 @@ void domainSync(Group& g)
         s->dist->numOwn = s->end - s->start;
     }
     syncBox(g);
+    tick(); // 0 box
     for (auto* s : g.sims)
         keysAndSort(s, s->start, s->dist->numOwn);
+    tick(); // 1 keys + sort
     syncGlobalTree(g);
+    tick(); // 2 global tree
     std::vector<uint32_t> matrix = assign(g);
+    tick(); // 3 assignment
     uint64_t moved = 0;
     for (int a = 0; a < g.P; ++a)
         for (int q = 0; q < g.P; ++q)
             if (a != q) moved += matrix[size_t(a) * g.P + q];
-    if (moved) migrate(g, matrix);
+    if (moved)
+    {
+        if (st)
+            for (auto* s : g.sims)
+                for (int k = 1; k < 4; ++k)
+                    waitUpload(s, k); // the leaving particles take all their fields along
+        migrate(g, matrix);
+    }
     else
         for (auto* s : g.sims)
             s->dist->numMigratedIn = s->dist->numMigratedOut = 0;
+    tick(); // 4 migration
     for (auto* s : g.sims)
+    {
+        if (st) waitUpload(s, 1); // h
         focusAndBoxes(s, s->start);
+    }
+    tick(); // 5 focus tree
     discoverHalos(g);
-    for (auto* s : g.sims)
-        layoutAndReorder(s, s->start);
+    tick(); // 6 halo discovery
+    for (size_t l = 0; l < g.sims.size(); ++l)
+    {
+        sphb200_sim* s = g.sims[l];
+        bool late      = st && !moved;
+        if (st)
+        {
+            waitUpload(s, 3); // m, temp
+            st->lateSrcOff[l]  = s->start;
+            st->latePending[l] = late;
+        }
+        layoutAndReorder(s, s->start, late);
+    }
+    tick(); // 7 layout + reorder
     const int early[5] = {F_x, F_y, F_z, F_h, F_m};
     exchangeHalos(g, early, 5);
+    tick(); // 8 halo exchange
     for (auto* s : g.sims)
     {
         searchTree(s);
         s->mark(1);
+    }
+    tick(); // 9 search tree
+    if (profile && g.sims[0]->dist->rank == 0 && ++calls % 8 == 0)
+    {
+        static const char* names[10] = {"box", "keys+sort", "global tree", "assignment", "migration", "focus tree",
+                                        "halo discovery", "layout+reorder", "halo x,y,z,h,m", "search tree"};
+        std::string line = "domain sync profile (ms per call over " + std::to_string(calls) + " calls):";
+        for (int k = 0; k < 10; ++k)
+        {
+            char buf[64];
+            std::snprintf(buf, sizeof(buf), " %s %.3f |", names[k], acc[k] / calls);
+            line += buf;
+        }
+        std::fprintf(stderr, "%s\n", line.c_str());
     }
 }
 
@@ -1389,11 +1476,14 @@ extern "C" int sphb200_halo_radii(sphb200_ctx* ctx, const void* h, int dtype, co
     SPHB200_CATCH
 }
 
-/*! @brief one step on host-resident state for the ranks this process drives: upload of the owned conserved fields
- *         (pinned host memory), sync + forces + integrate, download of the new owned range.  n_in[l] particles in,
- *         n_out[l] out (the assignment moves particles between ranks); host_out arrays must hold capacity elements.
- *         Transfers go through the compute stream (H2D first, D2H last); the single-rank sphb200_sim_step_host stages
- *         them beside the kernels.
+/*! @brief one step on host-resident state for the ranks this process drives (the call a host-resident front-end makes)
+ *
+ * Same results as upload + step + download, with the PCIe transfers staged beside the kernels like the single-rank
+ * sphb200_sim_step_host: uploads in order of first use on a copy stream ({x,y,z} | h | {m,temp} | the other eight
+ * fields, which are only reordered right before IAD), m / next-step h / alpha go back as soon as they are final, the
+ * Courant step is evaluated with AVswitches and all-reduced before MomentumEnergy, which then runs in 16 particle
+ * ranges, each integrated and sent to the host while the next one computes.  n_in[l] particles in, n_out[l] out (the
+ * assignment moves particles between ranks); host_out arrays hold hostCapacity elements.
  */
 extern "C" int sphb200_domain_step_host(sphb200_sim* const* sims, int numLocal, const size_t* n_in,
                                         const sphb200_fields* host_in, const sphb200_fields* host_out, size_t* n_out,
@@ -1401,28 +1491,208 @@ extern "C" int sphb200_domain_step_host(sphb200_sim* const* sims, int numLocal, 
 {
     SPHB200_TRY
     Group g = makeGroup(sims, numLocal);
-    for (int l = 0; l < numLocal; ++l)
-        CHECK_RC(sphb200_sim_upload(g.sims[l], n_in[l], &host_in[l]));
-    domainSync(g);
-    domainForces(g);
-    domainIntegrate(g);
-    for (int l = 0; l < numLocal; ++l)
+    const int NL = g.numLocal();
+    constexpr int kRanges = 16;
+    static const int groupA[]  = {F_x, F_y, F_z};
+    static const int groupH[]  = {F_h};
+    static const int groupMT[] = {F_m, F_temp};
+    for (int l = 0; l < NL; ++l)
     {
         sphb200_sim* s = g.sims[l];
-        size_t cnt     = s->end - s->start;
-        if (cnt > hostCapacity) throw std::runtime_error("domain_step_host: host buffers too small for the owned particles");
-        sphb200_fields h = host_out[l];
-        for (int id = 0; id < kNumConserved; ++id)
+        if (n_in[l] > s->capacity) throw std::runtime_error("domain_step_host: n exceeds capacity");
+        if (!s->copyIn)
         {
-            void* dst = *fieldSlot(h, id);
-            if (!dst) continue;
-            size_t eb = s->elemBytes(id);
-            SPHB200_CUDA(cudaMemcpyAsync(dst, static_cast<char*>(s->field[id]) + size_t(s->start) * eb, cnt * eb,
-                                         cudaMemcpyDeviceToHost, s->ctx->stream));
+            SPHB200_CUDA(cudaStreamCreateWithFlags(&s->copyIn, cudaStreamNonBlocking));
+            SPHB200_CUDA(cudaStreamCreateWithFlags(&s->copyOut, cudaStreamNonBlocking));
+            for (auto& e : s->evUp) SPHB200_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            for (auto& e : s->evDown) SPHB200_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         }
-        n_out[l] = cnt;
-    }
-    for (auto* s : g.sims)
+        if (!s->evRange[0])
+            for (auto& e : s->evRange) SPHB200_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         syncStream(s);
+        s->ctx->packValid = 0;
+        size_t n = n_in[l];
+        s->start = 0;
+        s->n = s->end = uint32_t(n);
+        sphb200_fields hin = host_in[l];
+        auto upload = [&](const int* ids, int count, cudaEvent_t done)
+        {
+            for (int k = 0; k < count; ++k)
+            {
+                void* src = *fieldSlot(hin, ids[k]);
+                if (!src) throw std::runtime_error("domain_step_host: all conserved fields are required in host_in");
+                SPHB200_CUDA(cudaMemcpyAsync(s->field[ids[k]], src, n * s->elemBytes(ids[k]), cudaMemcpyHostToDevice,
+                                             s->copyIn));
+            }
+            SPHB200_CUDA(cudaEventRecord(done, s->copyIn));
+        };
+        upload(groupA, 3, s->evUp[0]);
+        upload(groupH, 1, s->evUp[1]);
+        upload(groupMT, 2, s->evUp[3]);
+        upload(kLateIds, 8, s->evUp[2]);
+        waitUpload(s, 0);
+    }
+    SyncStaging st;
+    st.active = true;
+    st.lateSrcOff.assign(NL, 0);
+    st.latePending.assign(NL, false);
+    domainSync(g, &st);
+
+    auto download = [&](sphb200_sim* s, const sphb200_fields& hout, int id, const void* devBase, cudaEvent_t after)
+    {
+        // owned range [start, end) of devBase (indexed like the fields) -> host array [0, end - start)
+        sphb200_fields h = hout;
+        void* dst        = *fieldSlot(h, id);
+        if (!dst) return;
+        size_t eb = s->elemBytes(id);
+        SPHB200_CUDA(cudaEventRecord(after, s->ctx->stream));
+        SPHB200_CUDA(cudaStreamWaitEvent(s->copyOut, after, 0));
+        SPHB200_CUDA(cudaMemcpyAsync(dst, static_cast<const char*>(devBase) + size_t(s->start) * eb,
+                                     size_t(s->end - s->start) * eb, cudaMemcpyDeviceToHost, s->copyOut));
+    };
+    for (int l = 0; l < NL; ++l)
+    {
+        sphb200_sim* s = g.sims[l];
+        if (size_t(s->end - s->start) > hostCapacity)
+            throw std::runtime_error("domain_step_host: host buffers too small for the owned particles");
+        // the uploads of this call must have landed before results overwrite the same host arrays
+        SPHB200_CUDA(cudaStreamWaitEvent(s->copyOut, s->evUp[2], 0));
+        download(s, host_out[l], F_m, s->field[F_m], s->evDown[0]); // m is final after the reorder
+    }
+    const bool ranged = !g.sims[0]->cfg.hc.avClean;
+    auto phase = [&](int p)
+    {
+        for (auto* s : g.sims)
+            CHECK_RC(sphb200_sim_forces_phase(s, p));
+    };
+    const int ex1[2] = {F_xm, F_h};
+    const int ex2[6] = {F_vx, F_vy, F_vz, F_prho, F_c, F_kx};
+    const int ex3[7] = {F_c11, F_c12, F_c13, F_c22, F_c23, F_c33, F_divv};
+    const int ex4[1] = {F_alpha};
+    phase(0);
+    for (int l = 0; l < NL; ++l)
+    {
+        // next step's h = updateH(ng0, nc, h) is known once the neighbors are counted: into the spare buffer of h and
+        // off to the host; the position update recomputes the same value in place
+        sphb200_sim* s   = g.sims[l];
+        sphb200_fields f = s->table();
+        CHECK_RC(sphb200_update_h_into(s->ctx, s->cfg.dtype, s->start, s->end, s->cfg.hc.ng0, f.nc, f.h, s->fieldAlt[F_h]));
+        download(s, host_out[l], F_h, s->fieldAlt[F_h], s->evDown[2]);
+    }
+    exchangeHalos(g, ex1, 2);
+    phase(1);
+    for (int l = 0; l < NL; ++l)
+    {
+        sphb200_sim* s = g.sims[l];
+        if (!st.latePending[l]) continue;
+        waitUpload(s, 2);
+        gatherInto(s, kLateIds, 8, s->dist->numOwn, st.lateSrcOff[l], s->start, true);
+        s->ctx->packValid = 0;
+    }
+    exchangeHalos(g, ex2, 6);
+    phase(2);
+    exchangeHalos(g, ex3, 7);
+    if (!ranged)
+    {
+        phase(3);
+        for (int l = 0; l < NL; ++l)
+            download(g.sims[l], host_out[l], F_alpha, g.sims[l]->field[F_alpha], g.sims[l]->evDown[1]);
+        exchangeHalos(g, ex4, 1);
+        const int ex5[6] = {F_dV11, F_dV12, F_dV13, F_dV22, F_dV23, F_dV33};
+        exchangeHalos(g, ex5, 6);
+        phase(4);
+        domainIntegrate(g);
+        for (int l = 0; l < NL; ++l)
+        {
+            sphb200_sim* s = g.sims[l];
+            SPHB200_CUDA(cudaEventRecord(s->evRange[0], s->ctx->stream));
+            SPHB200_CUDA(cudaStreamWaitEvent(s->copyOut, s->evRange[0], 0));
+            sphb200_fields h = host_out[l];
+            for (int id = 0; id < kNumConserved; ++id)
+            {
+                if (id == F_m || id == F_alpha || id == F_h) continue;
+                void* dst = *fieldSlot(h, id);
+                if (!dst) continue;
+                size_t eb = s->elemBytes(id);
+                SPHB200_CUDA(cudaMemcpyAsync(dst, static_cast<char*>(s->field[id]) + size_t(s->start) * eb,
+                                             size_t(s->end - s->start) * eb, cudaMemcpyDeviceToHost, s->copyOut));
+            }
+            // h was sent from the spare buffer before the position update: identical values, nothing to resend
+        }
+    }
+    else
+    {
+        // AVswitches + the Courant step of momentumEnergy, then computeTimestep (ts_global.hpp:96-112) across the ranks
+        std::vector<void*> ptr;
+        for (auto* s : g.sims)
+        {
+            sphb200_fields f       = s->table();
+            sphb200_hydro_const hc = s->hydroConst();
+            CHECK_RC(sphb200_av_switches_courant(s->ctx, s->cfg.dtype, s->start, s->end, &s->box, &hc, s->neighbors, &f));
+            s->mark(7);
+            CHECK_RC(sphb200_timestep(s->ctx, s->cfg.dtype, s->start, s->end, &hc, &f, nullptr));
+            ptr.push_back(sphb200_timestep_device_ptr(s->ctx) + 2);
+        }
+        commAllReduce(g.comm, g.rs, ptr.data(), 1, COMM_F64, COMM_MIN);
+        for (auto* s : g.sims)
+            SPHB200_CUDA(cudaMemcpyAsync(s->ctx->hostDt, sphb200_timestep_device_ptr(s->ctx), 3 * sizeof(double),
+                                         cudaMemcpyDeviceToHost, s->ctx->stream));
+        for (int l = 0; l < NL; ++l)
+            download(g.sims[l], host_out[l], F_alpha, g.sims[l]->field[F_alpha], g.sims[l]->evDown[1]);
+        exchangeHalos(g, ex4, 1);
+        for (int l = 0; l < NL; ++l)
+        {
+            sphb200_sim* s = g.sims[l];
+            syncStream(s);
+            for (int k = 0; k < 3; ++k)
+                s->dtLocal[k] = s->ctx->hostDt[k];
+            double dt     = s->ctx->hostDt[2];
+            double dtStir = s->minDt; // TurbVeProp stirs with the time step of the previous iteration
+            s->ttot += dt;
+            s->minDt_m1 = s->minDt;
+            s->minDt    = dt;
+            if (s->turb) CHECK_RC(sphb200_turb_advance(s->turb, s->ctx, dtStir));
+        }
+        for (int l = 0; l < NL; ++l)
+        {
+            sphb200_sim* s         = g.sims[l];
+            auto* ctx              = s->ctx;
+            sphb200_fields f       = s->table();
+            sphb200_hydro_const hc = s->hydroConst();
+            int dtype              = s->cfg.dtype;
+            uint32_t a = s->start, b = s->end;
+            uint32_t per = ((b - a + kRanges - 1) / kRanges + 127) / 128 * 128;
+            sphb200_fields h = host_out[l];
+            for (int r = 0; r < kRanges; ++r)
+            {
+                uint32_t rb = std::min(b, a + r * per), re = std::min(b, rb + per);
+                if (re <= rb) break;
+                CHECK_RC(sphb200_momentum_energy_range(ctx, dtype, a, b, rb, re, r == 0, &s->box, &hc, s->neighbors, &f));
+                if (s->turb) CHECK_RC(sphb200_turb_stir(s->turb, ctx, dtype, rb, re, f.x, f.y, f.z, f.ax, f.ay, f.az));
+                CHECK_RC(sphb200_positions_update_h(ctx, dtype, rb, re, &s->box, &hc, s->minDt, s->minDt_m1, &f));
+                SPHB200_CUDA(cudaEventRecord(s->evRange[r], ctx->stream));
+                SPHB200_CUDA(cudaStreamWaitEvent(s->copyOut, s->evRange[r], 0));
+                for (int id = 0; id < kNumConserved; ++id)
+                {
+                    if (id == F_m || id == F_alpha || id == F_h) continue;
+                    void* dst = *fieldSlot(h, id);
+                    if (!dst) continue;
+                    size_t eb = s->elemBytes(id);
+                    SPHB200_CUDA(cudaMemcpyAsync(static_cast<char*>(dst) + size_t(rb - a) * eb,
+                                                 static_cast<char*>(s->field[id]) + size_t(rb) * eb, size_t(re - rb) * eb,
+                                                 cudaMemcpyDeviceToHost, s->copyOut));
+                }
+            }
+            s->mark(8);
+            s->mark(9);
+        }
+    }
+    for (int l = 0; l < NL; ++l)
+    {
+        sphb200_sim* s = g.sims[l];
+        n_out[l]       = s->end - s->start;
+        syncStream(s);
+        SPHB200_CUDA(cudaStreamSynchronize(s->copyOut));
+    }
     SPHB200_CATCH
 }

@@ -166,12 +166,19 @@ lib.sphb200_domain_step_host.argtypes = [vp, C.c_int, vp, vp, vp, vp, C.c_size_t
 
 
 def step_host(group, n_in, fin, fout, capacity):
-    """sphb200_domain_step_host for a group with ONE local rank: fin / fout are binding.Fields of pinned host pointers;
-    returns the number of particles this rank owns after the step"""
-    nin = (C.c_size_t * 1)(n_in)
-    nout = (C.c_size_t * 1)(0)
-    check(lib.sphb200_domain_step_host(group._arr, group.n, nin, C.byref(fin), C.byref(fout), nout, C.c_size_t(capacity)))
-    return int(nout[0])
+    """sphb200_domain_step_host: fin / fout are binding.Fields of pinned host pointers (one per local rank, or a single
+    one for a group with one local rank); returns the number of particles every local rank owns after the step"""
+    single = not isinstance(n_in, (list, tuple))
+    if single:
+        n_in, fin, fout = [n_in], [fin], [fout]
+    k = group.n
+    nin = (C.c_size_t * k)(*n_in)
+    nout = (C.c_size_t * k)()
+    fi = (B.Fields * k)(*fin)
+    fo = (B.Fields * k)(*fout)
+    check(lib.sphb200_domain_step_host(group._arr, k, nin, fi, fo, nout, C.c_size_t(capacity)))
+    out = [int(v) for v in nout]
+    return out[0] if single else out
 
 
 def nccl_comm(rank, world, local_rank):
