@@ -57,13 +57,12 @@ done
 for f in $CPP; do
   o=$B/obj/$(echo $f | tr '/' '_').o
   [ -s "$o" ] && continue
-  # the host TUs go through nvcc as well (-x cu): they instantiate thrust::device_vector operations, and a g++-compiled
-  # thrust CUDA backend has no kernels to launch (cudaErrorInvalidDevice in parallel_for at run time)
-  ( run "$(basename $f)" $NVCC -x cu ${CUFLAGS/-std=c++17/-std=c++20} $INC -c "$REF/main/src/$f" -o "$o" ) &
+  # (nvcc's front-end does not get through these C++20 translation units, so they stay with g++ like in the
+  #  reference's own CMake build)
+  ( run "$(basename $f)" /usr/bin/g++ $CXXFLAGS $INC -c "$REF/main/src/$f" -o "$o" ) &
   n=$((n+1)); if [ $((n % JOBS)) -eq 0 ]; then wait; fi
 done
 wait
 ls $B/obj/*.o | wc -l
 $NVCC -gencode arch=compute_100a,code=sm_100a -Xcompiler -fopenmp $B/obj/*.o -o "$OUT/sphexa-cuda" -lcudart -lgomp
-rm -rf "$B"
 echo "built $OUT/sphexa-cuda"
