@@ -110,7 +110,42 @@ def host_threads():
 SPHEXA_BIN = os.path.join(ROOT, "baseline", "_ref", "sphexa")
 
 
-def run_sphexa(side, iterations, timeout=1500):
+SPHEXA_CUDA_BIN = os.path.join(ROOT, "baseline", "_ref", "sphexa-cuda")
+
+
+def reference_gpu(side, phase_ms_ours, ms_ours, mixed_ours=None, iterations=10):
+    """BASELINE.md section 3b, the second on-box baseline: the reference's own GPU build (`sphexa-cuda`, its generic CUDA
+    kernels recompiled for sm_100a by oracle/build_sphexa_cuda.sh) on the same workload on this GPU.  Test
+    infrastructure, never linked into the product.  The reference has one precision (mixed: float hydro fields)."""
+    if not os.path.exists(SPHEXA_CUDA_BIN):
+        return {"unavailable": "baseline/_ref/sphexa-cuda was not built (oracle/build_sphexa_cuda.sh needs /root/reference)"}
+    its, phases_all, nb, _ = run_sphexa(side, iterations, binary=SPHEXA_CUDA_BIN, all_phases=True)
+    skip = 3
+    timed = sorted(its[skip:])
+    med = timed[len(timed) // 2]
+    names = ["domain::sync", "FindNeighbors", "XMass", "Normalization & Gradh", "EquationOfState",
+             "IadVelocityDivCurl", "AVswitches", "MomentumAndEnergy"]
+    ref_ms = {}
+    for k in names:
+        v = sorted(p.get(k, 0.0) for p in phases_all[skip:])
+        ref_ms[k] = v[len(v) // 2] * 1e3
+    n = side ** 3
+    out = {"program": f"baseline/_ref/sphexa-cuda --init sedov -n {side} -s {iterations} --ascii (reference GPU build, "
+                      f"sm_100a, mixed precision), iterations {skip + 1}..{iterations}, median",
+           "ms_per_step": med * 1e3, "particle_steps_per_s": n / med,
+           "ms_per_step_min_max": [timed[0] * 1e3, timed[-1] * 1e3],
+           "phase_ms": ref_ms,
+           "ours_fp64": {"ms_per_step": ms_ours, "speedup_vs_reference_gpu": med * 1e3 / ms_ours,
+                         "phase_speedup": {k: ref_ms[k] / phase_ms_ours[k] for k in names
+                                           if phase_ms_ours.get(k) and ref_ms.get(k)}},
+           "note": "the reference traverses the tree inside every pair kernel (FindNeighbors is only its first "
+                   "traversal); ours searches once and stores the lists"}
+    if mixed_ours:
+        out["ours_mixed"] = {"ms_per_step": mixed_ours, "speedup_vs_reference_gpu": med * 1e3 / mixed_ours}
+    return out
+
+
+def run_sphexa(side, iterations, timeout=1500, binary=None, all_phases=False):
     """the reference's own CPU front-end (main/src/sphexa/sphexa.cpp, built by oracle/build_sphexa.sh into
     baseline/_ref/sphexa): `sphexa --init sedov -n <side> -s <iterations> --ascii` on all host threads.  Returns
     (seconds per iteration [list], phase seconds of the last iteration, neighbors per particle, threads)."""
@@ -121,11 +156,12 @@ def run_sphexa(side, iterations, timeout=1500):
     # torchrun exports OMP_NUM_THREADS=1 to its workers; the CPU arm gets every core of the box
     env.update(OMP_NUM_THREADS=str(threads), OMP_PROC_BIND="close", OMP_PLACES="cores")
     with tempfile.TemporaryDirectory() as tmp:
-        res = subprocess.run([SPHEXA_BIN, "--init", "sedov", "-n", str(side), "-s", str(iterations), "--ascii"], cwd=tmp,
+        res = subprocess.run([binary or SPHEXA_BIN, "--init", "sedov", "-n", str(side), "-s", str(iterations), "--ascii"],
+                             cwd=tmp,
                              env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=timeout)
     if res.returncode != 0:
         raise RuntimeError(f"sphexa exited with {res.returncode}: {res.stdout[-400:]}")
-    it_s, phases, cur, nb = [], {}, {}, None
+    it_s, phases, cur, nb, every = [], {}, {}, None, []
     for line in res.stdout.splitlines():
         m = re.match(r"# ([^:]+(?:::[^:]+)?): ([0-9.eE+-]+)s", line)
         if m and not line.startswith("# Total execution"):
@@ -133,13 +169,14 @@ def run_sphexa(side, iterations, timeout=1500):
         m = re.match(r"=== Total time for iteration\((\d+)\) ([0-9.eE+-]+)s", line)
         if m:
             it_s.append(float(m.group(2)))
+            every.append(cur)
             phases, cur = cur, {}
         m = re.search(r"Avg neighbor count per particle: ([0-9.]+)", line)
         if m:
             nb = float(m.group(1))
     if len(it_s) != iterations:
         raise RuntimeError(f"sphexa printed {len(it_s)} iterations, expected {iterations}")
-    return it_s, phases, nb, threads
+    return it_s, (every if all_phases else phases), nb, threads
 
 
 def reference_arm(args):
@@ -320,6 +357,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-bdt", action="store_true", help="skip the block-time-step (ve-bdt) hierarchy report")
     ap.add_argument("--no-configs", action="store_true", help="skip the Noh / turbulence / KH reports")
+    ap.add_argument("--no-reference-gpu", action="store_true", help="skip the run of the reference's own GPU build")
     ap.add_argument("--case", default="sedov", choices=["sedov", "turbulence", "noh"],
                     help="--gpus > 1 only: turbulence = BASELINE.json configs[3] (stirred, weak scaling); the headline "
                          "metric is the default")
@@ -607,6 +645,18 @@ def main():
             except Exception as ex:
                 other["sedov_mixed_precision"] = {"error": str(ex)}
 
+    ref_gpu = None
+    if not args.no_reference_gpu:
+        try:
+            if gs is not None:
+                gs.close()
+                gs = None
+            torch.cuda.empty_cache()
+            mixed = (other or {}).get("sedov_mixed_precision", {}).get("ms_per_step") if isinstance(other, dict) else None
+            ref_gpu = reference_gpu(args.side, phase_ms, ms_per_step, mixed)
+        except Exception as ex:  # diagnostics only
+            ref_gpu = {"error": str(ex)[-300:]}
+
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -620,7 +670,7 @@ def main():
         "hbm_kernels": hbm_kernels,
         "hbm_fracs": ({k: round(v["frac"], 3) for k, v in hbm_kernels.items() if isinstance(v, dict) and "frac" in v}
                       if isinstance(hbm_kernels, dict) else None),
-        "block_time_steps": bdt, "other_configs": other,
+        "block_time_steps": bdt, "other_configs": other, "reference_gpu": ref_gpu,
     }
     print(json.dumps(line), flush=True)
     if gs is not None:

@@ -64,5 +64,8 @@ for f in $CPP; do
 done
 wait
 ls $B/obj/*.o | wc -l
-$NVCC -gencode arch=compute_100a,code=sm_100a -Xcompiler -fopenmp $B/obj/*.o -o "$OUT/sphexa-cuda" -lcudart -lgomp
+/usr/bin/g++ -O2 -I/usr/local/cuda/include -c "$HERE/sphexa_cpu/launch_guard.cpp" -o "$B/obj/zz_launch_guard.o"
+$NVCC -gencode arch=compute_100a,code=sm_100a -Xcompiler -fopenmp -Xlinker --wrap=cudaLaunchKernel $B/obj/*.o \
+      -o "$OUT/sphexa-cuda" -lcudart -lgomp
+rm -rf "$B"
 echo "built $OUT/sphexa-cuda"
