@@ -11,7 +11,7 @@ HERE=$(cd "$(dirname "$0")" && pwd)
 OUT=$HERE/../baseline/_ref
 NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
 [ -d "$REF/main/src/sphexa" ] || { echo "reference tree $REF absent: keeping prebuilt $OUT/sphexa-cuda"; exit 0; }
-B=$OUT/build_cuda
+B=$OUT/obj_cuda   # kept (git- and gpurun-ignored): the drop-in link below reuses the objects
 mkdir -p "$B/overlay/sph" "$B/gen" "$B/obj"
 sed '270d' "$REF/sph/include/sph/particles_data.hpp" > "$B/overlay/sph/particles_data.hpp"
 sed -e 's/using Tdu *= *decltype(d.du\[0\]);/using Tdu = std::decay_t<decltype(d.du[0])>;/' \
@@ -67,5 +67,18 @@ ls $B/obj/*.o | wc -l
 /usr/bin/g++ -O2 -I/usr/local/cuda/include -c "$HERE/sphexa_cpu/launch_guard.cpp" -o "$B/obj/zz_launch_guard.o"
 $NVCC -gencode arch=compute_100a,code=sm_100a -Xcompiler -fopenmp -Xlinker --wrap=cudaLaunchKernel $B/obj/*.o \
       -o "$OUT/sphexa-cuda" -lcudart -lgomp
-rm -rf "$B"
 echo "built $OUT/sphexa-cuda"
+
+# ---- drop-in link: the SAME reference front-end, Domain and propagators, with the six SPH-VE operator objects of the
+# reference (sph/include/sph/hydro_ve/*_gpu.cu) replaced by the forwarding definitions of
+# sph-exa_b200/host/b200_forward.cu, which are compiled against the reference's own declarations (sph/sph_gpu.hpp) and
+# call the C ABI of libsphexa_b200.so
+LIB=$HERE/../sph-exa_b200
+if [ -f "$LIB/libsphexa_b200.so" ] && [ -f "$LIB/host/b200_forward.cu" ]; then
+  $NVCC $CUFLAGS $INC -I$HERE/../include -c "$LIB/host/b200_forward.cu" -o "$B/b200_forward.o"
+  KEEP=$(ls $B/obj/*.o | grep -v -E "hydro_ve_(xmass|ve_def_gradh|iad_divv_curlv|av_switches|momentum_energy|eos)_gpu")
+  $NVCC -gencode arch=compute_100a,code=sm_100a -Xcompiler -fopenmp -Xlinker --wrap=cudaLaunchKernel $KEEP \
+        "$B/b200_forward.o" -o "$OUT/sphexa-cuda-b200" -L"$LIB" -lsphexa_b200 -Xlinker -rpath -Xlinker '$ORIGIN/../../sph-exa_b200' \
+        -lcudart -lgomp
+  echo "built $OUT/sphexa-cuda-b200"
+fi

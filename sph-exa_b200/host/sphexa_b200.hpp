@@ -199,6 +199,41 @@ inline std::array<double, 10> conservedQuantities(const Context& c, int dtype, u
 // ---- propagator level -------------------------------------------------------------------------------------------------
 
 //! @brief sphexa::HydroVeProp + cstone::Domain for one rank; owns the device state
+//! @brief transport of a multi-rank run: NCCL (one process per GPU) or the single-GPU loopback over P virtual ranks
+class Comm
+{
+public:
+    static Comm loopback(int numRanks)
+    {
+        Comm c;
+        check(sphb200_comm_create_loopback(numRanks, &c.comm_));
+        return c;
+    }
+    //! @brief id128: the 128 bytes rank 0 got from uniqueId(), broadcast by the front-end (MPI_Bcast in sphexa.cpp)
+    static Comm nccl(int device, int rank, int numRanks, const void* id128)
+    {
+        Comm c;
+        check(sphb200_comm_create_nccl(device, rank, numRanks, id128, &c.comm_));
+        return c;
+    }
+    static std::array<char, 128> uniqueId()
+    {
+        std::array<char, 128> id{};
+        check(sphb200_comm_unique_id(id.data()));
+        return id;
+    }
+    Comm(Comm&& o) noexcept : comm_(std::exchange(o.comm_, nullptr)) {}
+    Comm(const Comm&)            = delete;
+    Comm& operator=(const Comm&) = delete;
+    ~Comm() { sphb200_comm_destroy(comm_); }
+    sphb200_comm* get() const { return comm_; }
+    int numRanks() const { return sphb200_comm_num_ranks(comm_); }
+
+private:
+    Comm() = default;
+    sphb200_comm* comm_{nullptr};
+};
+
 class HydroVeProp
 {
 public:
@@ -207,6 +242,14 @@ public:
     {
         check(sphb200_sim_create(c.get(), &cfg, &sim_));
     }
+    //! @brief one rank of a multi-rank run: cstone::Domain(rank, nRanks, bucketSize, bucketSizeFocus, theta, box)
+    //!        (domain.hpp:97-113) with the communicator attached; collective calls go through DistHydroVeProp
+    HydroVeProp(const Context& c, const sphb200_sim_config& cfg, const Comm& comm)
+        : ctx_(c)
+    {
+        check(sphb200_domain_create(c.get(), &cfg, comm.get(), &sim_));
+    }
+    sphb200_sim* handle() const { return sim_; }
     ~HydroVeProp() { sphb200_sim_destroy(sim_); }
     HydroVeProp(const HydroVeProp&)            = delete;
     HydroVeProp& operator=(const HydroVeProp&) = delete;
@@ -343,6 +386,46 @@ public:
         check(sphb200_sim_bdt_info(sim_, &info));
         return info;
     }
+};
+
+/*! @brief HydroVeProp over the ranks this process drives (one with NCCL, all P in rank order with the loopback):
+ *         Domain::sync + computeForces with the halo exchanges in between + integrate with the MIN all-reduce of dt
+ *         (main/src/propagator/ve_hydro.hpp:116-217 on P ranks)
+ */
+class DistHydroVeProp
+{
+public:
+    explicit DistHydroVeProp(std::vector<HydroVeProp*> ranks)
+        : ranks_(std::move(ranks))
+    {
+        for (auto* r : ranks_)
+            handles_.push_back(r->handle());
+    }
+    void sync() { check(sphb200_domain_sync(handles_.data(), int(handles_.size()))); }
+    void computeForces() { check(sphb200_domain_compute_forces(handles_.data(), int(handles_.size()))); }
+    void integrate() { check(sphb200_domain_integrate(handles_.data(), int(handles_.size()))); }
+    void step() { check(sphb200_domain_step(handles_.data(), int(handles_.size()))); }
+    //! @brief Domain::exchangeHalos (domain.hpp:375-379); field id = position in sphb200_fields
+    void exchangeHalos(const std::vector<int>& fieldIds)
+    {
+        check(sphb200_domain_exchange_halos(handles_.data(), int(handles_.size()), fieldIds.data(), int(fieldIds.size())));
+    }
+    std::array<double, 10> conserved()
+    {
+        std::array<double, 10> q{};
+        check(sphb200_domain_conserved(handles_.data(), int(handles_.size()), q.data()));
+        return q;
+    }
+    sphb200_domain_info_t info(size_t localRank) const
+    {
+        sphb200_domain_info_t i;
+        check(sphb200_domain_info(handles_[localRank], &i));
+        return i;
+    }
+
+private:
+    std::vector<HydroVeProp*> ranks_;
+    std::vector<sphb200_sim*> handles_;
 };
 
 } // namespace sphb200::host

@@ -98,6 +98,50 @@ int main(int argc, char** argv)
                         ts.numGroups, double(ts.nextDt));
             if (substeps != (1 << (ts.numRungs - 1))) return 4;
         }
+        // two virtual ranks on this GPU (loopback transport): the same problem through the multi-rank Domain; the time
+        // step and the neighbor total must equal the single-rank propagator's after the same number of steps
+        {
+            Comm comm = Comm::loopback(2);
+            Context c0(0, nullptr), c1(0, nullptr); // one context per virtual rank, one stream
+            sphb200_sim_config cr = cfg;
+            cr.numRanks = 2;
+            cr.capacity = 2 * n;
+            cr.rank     = 0;
+            HydroVeProp r0(c0, cr, comm);
+            cr.rank = 1;
+            HydroVeProp r1(c1, cr, comm);
+            auto slice = [&](size_t first) {
+                sphb200_fields g = f;
+                g.x += first; g.y += first; g.z += first; g.temp += first;
+                for (void** p : {&g.h, &g.m, &g.vx, &g.vy, &g.vz, &g.x_m1, &g.y_m1, &g.z_m1, &g.du_m1, &g.alpha})
+                    *p = static_cast<double*>(*p) + first;
+                return g;
+            };
+            r0.upload(n / 2, slice(0));
+            r1.upload(n - n / 2, slice(n / 2));
+            HydroVeProp one(ctx, cfg);
+            one.upload(n, f);
+            DistHydroVeProp dist({&r0, &r1});
+            for (int s = 0; s < 3; ++s)
+            {
+                dist.step();
+                one.computeForces();
+                one.integrate();
+            }
+            auto i0 = dist.info(0), i1 = dist.info(1);
+            bool same = r0.minDt() == one.minDt() && r1.minDt() == one.minDt() &&
+                        r0.totalNeighbors() + r1.totalNeighbors() == one.totalNeighbors() &&
+                        (i0.endIndex - i0.startIndex) + (i1.endIndex - i1.startIndex) == n;
+            std::printf("two virtual ranks: owned %u + %u, halos %u + %u, dt %.6e\n", i0.endIndex - i0.startIndex,
+                        i1.endIndex - i1.startIndex, i0.nWithHalos - (i0.endIndex - i0.startIndex),
+                        i1.nWithHalos - (i1.endIndex - i1.startIndex), r0.minDt());
+            if (!same)
+            {
+                std::fprintf(stderr, "2 virtual ranks differ from 1 rank: dt %.17g vs %.17g\n", r0.minDt(), one.minDt());
+                return 5;
+            }
+            std::printf("domain ok\n");
+        }
         // error path: precondition violation -> std::runtime_error
         bool threw = false;
         try

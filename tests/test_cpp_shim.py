@@ -32,6 +32,7 @@ def test_shim_runs_two_steps(pkg, ctx, tmp_path):
     assert "shim ok: n=1728" in res.stdout
     assert "restart ok" in res.stdout
     assert "bdt ok: rungs=" in res.stdout
+    assert "domain ok" in res.stdout  # 2 virtual ranks through sphb200::host::DistHydroVeProp == 1 rank
     # 12^3 lattice with h from ng0=100: every particle sees the same neighbor count (parity with tests/golden)
     import numpy as np
     g = np.load(os.path.join(ROOT, "tests", "golden", "sedov12_steps.npz"))
