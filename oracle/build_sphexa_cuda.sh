@@ -69,14 +69,14 @@ $NVCC -gencode arch=compute_100a,code=sm_100a -Xcompiler -fopenmp -Xlinker --wra
       -o "$OUT/sphexa-cuda" -lcudart -lgomp
 echo "built $OUT/sphexa-cuda"
 
-# ---- drop-in link: the SAME reference front-end, Domain and propagators, with the six SPH-VE operator objects of the
+# ---- drop-in link: the SAME reference front-end, Domain and propagators, with the five SPH-VE pair-operator objects of the
 # reference (sph/include/sph/hydro_ve/*_gpu.cu) replaced by the forwarding definitions of
 # sph-exa_b200/host/b200_forward.cu, which are compiled against the reference's own declarations (sph/sph_gpu.hpp) and
 # call the C ABI of libsphexa_b200.so
 LIB=$HERE/../sph-exa_b200
 if [ -f "$LIB/libsphexa_b200.so" ] && [ -f "$LIB/host/b200_forward.cu" ]; then
   $NVCC $CUFLAGS $INC -I$HERE/../include -c "$LIB/host/b200_forward.cu" -o "$B/b200_forward.o"
-  KEEP=$(ls $B/obj/*.o | grep -v -E "hydro_ve_(xmass|ve_def_gradh|iad_divv_curlv|av_switches|momentum_energy|eos)_gpu")
+  KEEP=$(ls $B/obj/*.o | grep -v -E "hydro_ve_(xmass|ve_def_gradh|iad_divv_curlv|av_switches|momentum_energy)_gpu")
   $NVCC -gencode arch=compute_100a,code=sm_100a -Xcompiler -fopenmp -Xlinker --wrap=cudaLaunchKernel $KEEP \
         "$B/b200_forward.o" -o "$OUT/sphexa-cuda-b200" -L"$LIB" -lsphexa_b200 -Xlinker -rpath -Xlinker '$ORIGIN/../../sph-exa_b200' \
         -lcudart -lgomp

@@ -215,7 +215,11 @@ def bench_main(args, pkg, METRIC, UNIT, ALGO_BYTES, load_peaks, ClockSampler):
     dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     dtype = B.F64 if args.dtype == "f64" else B.MIXED
 
-    side = int(round(args.side * world ** (1.0 / 3.0)))  # weak scaling: args.side^3 particles per GPU
+    # weak scaling: args.side^3 particles per GPU.  The global lattice side is kept even: an odd side puts a plane of
+    # particles exactly on the mid-planes of the box, which are octree (and rank) boundaries, and round-off flips their
+    # keys across it every step (a few thousand migrating particles per step that no real initial condition has)
+    side = int(round(args.side * world ** (1.0 / 3.0)))
+    side += side % 2
     n_global = side ** 3
     first, last = partition_range(n_global, rank, world)
     case = getattr(args, "case", "sedov")
@@ -236,7 +240,8 @@ def bench_main(args, pkg, METRIC, UNIT, ALGO_BYTES, load_peaks, ClockSampler):
     n_mine = f["x"].size
     ctx = pkg.Context(local_rank)
     comm = nccl_comm(rank, world, local_rank)
-    capacity = int(1.3 * n_global / world) + 65536
+    # room for the balanced share plus halos; the slabs the ranks start from can be larger than that (Noh: cut sphere)
+    capacity = int(max(1.3 * n_global / world, 1.05 * n_mine)) + 65536
     sim = DomainRank(ctx, box, s, capacity, comm, rank, dtype=dtype)
     turb = None
     if case == "turbulence":
