@@ -1,0 +1,44 @@
+"""Operator-level drop-in, proven end to end: `baseline/_ref/sphexa-cuda-b200` is the reference's own GPU front-end
+(main/src/sphexa/sphexa.cpp, its initial conditions, cstone::Domain, HydroVeProp, observables -- unmodified sources,
+built by oracle/build_sphexa_cuda.sh) linked with sph-exa_b200/host/b200_forward.cu + libsphexa_b200.so in place of
+the reference's five hydro_ve/*_gpu.cu pair-operator objects.  Its run must print the same `### Check ###` lines as
+`baseline/_ref/sphexa-cuda`, the reference's own GPU build, on the same problem."""
+import os
+import re
+import subprocess
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF = os.path.join(ROOT, "baseline", "_ref", "sphexa-cuda")
+OURS = os.path.join(ROOT, "baseline", "_ref", "sphexa-cuda-b200")
+
+
+def run(binary, case, side, steps, tmp):
+    res = subprocess.run([binary, "--init", case, "-n", str(side), "-s", str(steps), "--ascii"], cwd=tmp,
+                         capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-2000:]
+    checks = [l for l in res.stdout.splitlines() if l.startswith("### Check ###")]
+    its = [float(m.group(1)) for m in re.finditer(r"=== Total time for iteration\(\d+\) ([0-9.eE+-]+)s", res.stdout)]
+    return checks, its
+
+
+@pytest.mark.parametrize("side,steps", [(50, 10), (100, 6)])
+def test_reference_front_end_with_our_operators_prints_the_reference_check_lines(ctx, tmp_path, side, steps):
+    if not (os.path.exists(REF) and os.path.exists(OURS)):
+        pytest.skip("baseline/_ref/sphexa-cuda[-b200] not built (oracle/build_sphexa_cuda.sh needs /root/reference)")
+    a = tmp_path / "ref"
+    b = tmp_path / "ours"
+    a.mkdir()
+    b.mkdir()
+    ref_checks, ref_its = run(REF, "sedov", side, steps, a)
+    our_checks, our_its = run(OURS, "sedov", side, steps, b)
+    keep = ("Particles:", "Computational domain", "Total Neighbors", "Total time", "Total energy")
+    ref_lines = [l for l in ref_checks if any(k in l for k in keep)]
+    our_lines = [l for l in our_checks if any(k in l for k in keep)]
+    assert len(ref_lines) == 5 * steps
+    # particle count, box, neighbor total, simulated time and time step, total / internal / kinetic energy of every
+    # iteration, as printed by the reference (6 significant digits)
+    assert our_lines == ref_lines
+    assert len(our_its) == steps
