@@ -398,6 +398,11 @@ def main():
         return D.bench_main(args, pkg, METRIC, UNIT, ALGO_BYTES, load_peaks, ClockSampler)
 
     torch.cuda.set_device(local_rank)
+    # the host-resident step copies through pinned buffers: allocate them on the GPU's own NUMA node (restored before
+    # the CPU baselines, which get every core)
+    all_cpus = os.sched_getaffinity(0) if hasattr(os, "sched_getaffinity") else None
+    from sph_exa_b200.domain import bind_to_gpu_numa_node
+    bind_to_gpu_numa_node(local_rank)
     dtype = B.F64 if args.dtype == "f64" else B.MIXED
     f, box, s = pkg.ic.sedov(args.side, args.dtype)
     n = f["x"].size
@@ -595,6 +600,8 @@ def main():
         e2e = {"value": n * e2e_steps / dt, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                "ms_per_step": dt / e2e_steps * 1e3, "steps": e2e_steps}
 
+    if all_cpus is not None:
+        os.sched_setaffinity(0, all_cpus)
     cpu = None
     if not args.no_cpu_baseline:
         try:

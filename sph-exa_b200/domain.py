@@ -181,6 +181,23 @@ def step_host(group, n_in, fin, fout, capacity):
     return out[0] if single else out
 
 
+def bind_to_gpu_numa_node(local_rank):
+    """pin this process to the CPUs closest to its GPU (nvmlDeviceSetCpuAffinity) so that the pinned host buffers of the
+    host-resident step are first-touched on the GPU's own NUMA node -- what `numactl` / the batch system does for a
+    production rank.  Returns the number of CPUs in the new affinity mask (None when NVML is unavailable)."""
+    import os
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        visible = os.environ.get("CUDA_VISIBLE_DEVICES")
+        index = int(visible.split(",")[local_rank]) if visible and visible.split(",")[local_rank].isdigit() else local_rank
+        handle = pynvml.nvmlDeviceGetHandleByIndex(index)
+        pynvml.nvmlDeviceSetCpuAffinity(handle)
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return None
+
+
 def nccl_comm(rank, world, local_rank):
     """NCCL transport for a torchrun launch: the unique id travels through torch.distributed (the reference's front-end
     would MPI_Bcast it)"""
@@ -212,6 +229,7 @@ def bench_main(args, pkg, METRIC, UNIT, ALGO_BYTES, load_peaks, ClockSampler):
     if world != args.gpus:
         raise SystemExit(f"--gpus {args.gpus} needs torchrun with {args.gpus} ranks (WORLD_SIZE={world})")
     torch.cuda.set_device(local_rank)
+    numa_cpus = bind_to_gpu_numa_node(local_rank)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     dtype = B.F64 if args.dtype == "f64" else B.MIXED
 
@@ -330,7 +348,8 @@ def bench_main(args, pkg, METRIC, UNIT, ALGO_BYTES, load_peaks, ClockSampler):
         dt_e = float(dt_e.item())
         e2e = {"value": n_global * e2e_steps / dt_e, "unit": UNIT, "h2d_bytes_per_step": h2d // e2e_steps,
                "d2h_bytes_per_step": d2h // e2e_steps, "ms_per_step": dt_e / e2e_steps * 1e3, "steps": e2e_steps,
-               "note": "bytes are rank 0's; every rank moves its own share through sphb200_domain_step_host"}
+               "note": "bytes are rank 0's; every rank moves its own share through sphb200_domain_step_host",
+               "cpus_in_numa_affinity_rank0": numa_cpus}
 
     if rank == 0:
         peak, peak_src = load_peaks()
