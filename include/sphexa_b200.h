@@ -305,6 +305,14 @@ double* sphb200_mach_device_ptr(sphb200_ctx*);
  * at a later time than the getter call itself. */
 void sphb200_invalidate_records(sphb200_ctx*);
 
+/* The pair operators that interpolate the kernel table once or twice per pair (XMass, IadDivvCurlv, AVswitches,
+ * MomentumEnergy) exist in two variants that return the same bits: the table read through L1 (fastest on lattices)
+ * and the table staged in shared memory of a persistent CTA (fastest on disordered particle sets).  By default the
+ * context times both on the caller's data and keeps the faster one (variant -1); 0 / 1 pin the L1 / shared-memory
+ * variant (tests, profiling; also SPHB200_TABLE=l1|smem in the environment).  No counterpart in the reference, whose
+ * kernels read the table from global memory (sph/table_lookup.hpp:13-25). */
+int sphb200_set_table_variant(sphb200_ctx*, int variant);
+
 /* ---- a21: computePositionsGpu + updateSmoothingLengthGpu (positions_gpu.cu:119-192, update_h_gpu.cu:40-62) ---- */
 int sphb200_positions_update_h(sphb200_ctx*, int dtype, uint32_t first, uint32_t last, const sphb200_box* box_h,
                                const sphb200_hydro_const* hc_h, double dt, double dt_m1, const sphb200_fields* f_h);

@@ -95,7 +95,7 @@ class RestartInfo(C.Structure):
 
 # every symbol include/sphexa_b200.h declares (checked by tests/test_abi.py)
 SYMBOLS = [
-    "sphb200_create", "sphb200_destroy", "sphb200_invalidate_records", "sphb200_last_error", "sphb200_sync", "sphb200_launch_count",
+    "sphb200_create", "sphb200_destroy", "sphb200_invalidate_records", "sphb200_set_table_variant", "sphb200_last_error", "sphb200_sync", "sphb200_launch_count",
     "sphb200_make_box", "sphb200_sfc_keys", "sphb200_minmax3", "sphb200_sort_by_key", "sphb200_gather",
     "sphb200_node_counts", "sphb200_update_octree", "sphb200_compute_octree", "sphb200_rebalance_decision",
     "sphb200_build_octree", "sphb200_node_centers", "sphb200_layout", "sphb200_neighbors_size", "sphb200_neighbors_from_rowmajor",
@@ -135,6 +135,7 @@ SYMBOLS = [
 lib.sphb200_last_error.restype = C.c_char_p
 lib.sphb200_launch_count.restype = C.c_uint64
 lib.sphb200_launch_count.argtypes = [vp]
+lib.sphb200_set_table_variant.argtypes = [vp, C.c_int]
 lib.sphb200_neighbors_size.restype = C.c_size_t
 lib.sphb200_neighbors_size.argtypes = [C.c_size_t, C.c_uint]
 lib.sphb200_timestep_device_ptr.restype = vp
@@ -264,6 +265,10 @@ class Context:
 
     def sync(self):
         check(lib.sphb200_sync(self.h))
+
+    def setTableVariant(self, variant):
+        """kernel-table variant of the pair operators: -1 timed on the data (default), 0 L1, 1 shared memory"""
+        check(lib.sphb200_set_table_variant(self.h, C.c_int(variant)))
 
     @property
     def launches(self):

@@ -82,6 +82,9 @@ extern "C" void sphb200_destroy(sphb200_ctx* ctx)
     for (auto& a : ctx->rec)
         a.release();
     ctx->tabPairs.release();
+    for (auto& t : ctx->tabTune)
+        for (auto& e : t.ev)
+            if (e) cudaEventDestroy(e);
     ctx->tabQuads.release();
     cudaFreeHost(ctx->hostScalars);
     cudaFree(ctx->devScalars);

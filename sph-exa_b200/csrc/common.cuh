@@ -105,6 +105,21 @@ struct sphb200_ctx
     float searchExtFactor      = 1.0f;
     void* scopeDtParticle      = nullptr;
     uint8_t* scopeGather       = nullptr;
+    // kernel-table variant of the pair operators (hydro.cu): -1 decided from timed launches, 0 L1, 1 shared memory
+    int tabForce = -1;
+    struct TabTune
+    {
+        int phase   = 0;  // 0: time the L1 variant next, 1: time the shared-memory variant next, 2: decided
+        int calls   = 0;  // launches since the decision
+        int pending = -1; // variant whose launch is bracketed by ev[0], ev[1] and not read back yet
+        bool closed = false;
+        size_t pendingTargets = 0;
+        double perTarget[2] = {0, 0};
+        bool smem = false;
+        cudaEvent_t ev[2] = {nullptr, nullptr};
+    };
+    static constexpr int kMaxTabOps = 8;
+    TabTune tabTune[kMaxTabOps];
     bool hilbertTabReady       = false; // sfc.cu: the 3-level Hilbert transition table is on this device
 };
 

@@ -102,6 +102,46 @@ __device__ __forceinline__ void applyPBC(const PbcBox& b, T r, T& xx, T& yy, T& 
     else if (b.pz && zz < -r) zz += b.lz;
 }
 
+// ---------------------------------------------------------------- explicit contractions
+// Sums of products are written with explicit multiply-adds wherever the order of contraction is ambiguous, so that
+// every variant of a kernel rounds alike.  The Courant signal velocity can be evaluated in either kernel (sphb200_av_switches_courant lets the step know its
+// time step before momentumEnergy starts); explicit fused multiply-adds make both evaluations the same bits.
+__device__ __forceinline__ double fmaT(double a, double b, double c) { return __fma_rn(a, b, c); }
+__device__ __forceinline__ float fmaT(float a, float b, float c) { return __fmaf_rn(a, b, c); }
+
+template<class T>
+__device__ __forceinline__ T dot3(T ax, T ay, T az, T bx, T by, T bz)
+{
+    return fmaT(az, bz, fmaT(ay, by, ax * bx));
+}
+
+//! @brief a b + c d with the contraction spelled out.  Left to the compiler, which of the two products is rounded before
+//!        the add depends on the code around the expression, and the L1-table and shared-memory-table variants of a
+//!        kernel (same source) came out one bit apart in such sums.
+template<class T>
+__device__ __forceinline__ T sum2(T a, T b, T c, T d)
+{
+    return fmaT(c, d, a * b);
+}
+
+//! @brief vijsignal of momentum_energy_kern.hpp: 0.5 (c_i + c_j) - 2 w_ij
+template<class T>
+__device__ __forceinline__ T courantSignal(T ci, T cj, T wij)
+{
+    return fmaT(T(-2), wij, T(0.5) * (ci + cj));
+}
+
+/*! @brief v - idx * dx of sph::lt::lookup (table_lookup.hpp:21).  v is itself a product (dist / h), and whether the
+ *         compiler fuses that product or idx * dx into the subtraction was seen to differ between two instances of the
+ *         same source line; here v is always rounded first.
+ */
+template<class T>
+__device__ __forceinline__ T tableFraction(T v, int idx)
+{
+    constexpr T dx = T(2.0) / (kTableSize - 1);
+    return fmaT(-T(idx), dx, v);
+}
+
 //! @brief tabulated kernel with linear interpolation, sph::lt::lookup (sph/table_lookup.hpp:13-25)
 template<class T>
 __device__ __forceinline__ T lookup(const T* __restrict__ table, T v)
@@ -116,7 +156,7 @@ __device__ __forceinline__ T lookup(const T* __restrict__ table, T v)
     T t0         = __ldg(table + idx);
     T t1         = __ldg(table + idx + 1);
     T derivative = (t1 - t0) * invDx;
-    return t0 + derivative * (v - T(idx) * dx);
+    return fmaT(derivative, tableFraction(v, idx), t0);
 }
 
 // ---------------------------------------------------------------- gather records
@@ -276,7 +316,7 @@ __device__ __forceinline__ T lookup(const Rec2<T>* __restrict__ table, T v)
     int idx = v * invDx;
     if (idx >= numIntervals) return T(0);
     Rec2<T> t = ldRec(table, idx); // {t[idx], derivative}
-    return t.a + t.b * (v - T(idx) * dx);
+    return fmaT(t.b, tableFraction(v, idx), t.a);
 }
 
 //! @brief both tables at the same abscissa (wh and whd), one load
@@ -292,9 +332,85 @@ __device__ __forceinline__ void lookup2(const Rec4<T>* __restrict__ table, T v, 
     w = dw = T(0);
     if (idx >= numIntervals) return;
     Rec4<T> t = ldRec(table, idx);
-    T frac    = v - T(idx) * dx;
-    w         = t.a + t.b * frac;
-    dw        = t.c + t.d * frac;
+    T frac    = tableFraction(v, idx);
+    w         = fmaT(t.b, frac, t.a);
+    dw        = fmaT(t.d, frac, t.c);
+}
+
+//! @brief the packed {t, slope} table in global memory (read through L1)
+template<class T>
+struct GlobalTab
+{
+    const Rec2<T>* pairs;
+    __device__ __forceinline__ T operator()(T v) const { return lookup(pairs, v); }
+};
+
+/*! @brief the plain table resident in shared memory (160 KB in f64): on jittered particle sets the pair abscissae of a
+ *         warp are spread over the whole table, so a lookup through L1 costs one tag cycle per lane and mostly misses;
+ *         the same 32 lanes read shared memory in a few wavefronts.  Same arithmetic as packTableKernel + lookup: the
+ *         slope is the rounded product (t1 - t0) * invDx, then one multiply-add, hence the same bits.
+ */
+template<class T>
+struct SharedTab
+{
+    const T* t;
+    __device__ __forceinline__ T operator()(T v) const
+    {
+        constexpr int numIntervals = kTableSize - 1;
+        constexpr T support        = 2.0;
+        constexpr T dx             = support / numIntervals;
+        constexpr T invDx          = T(1) / dx;
+
+        int idx = v * invDx;
+        if (idx >= numIntervals) return T(0);
+        T t0    = t[idx];
+        T slope = (t[idx + 1] - t0) * invDx;
+        return fmaT(slope, tableFraction(v, idx), t0);
+    }
+};
+
+constexpr int kTabChunks = 10; // bulk copies per table (16 KB / 8 KB each)
+
+/*! @brief bring the kernel table into shared memory with bulk async copies (TMA, cp.async.bulk) that complete on an
+ *         mbarrier; every thread of the CTA returns once the table is readable
+ */
+template<class T>
+__device__ __forceinline__ const T* stageTable(const T* __restrict__ table)
+{
+    extern __shared__ __align__(128) unsigned char tabSmem[];
+    __shared__ __align__(8) unsigned long long tabBar;
+    constexpr uint32_t bytes = kTableSize * sizeof(T);
+    constexpr uint32_t chunk = bytes / kTabChunks;
+    static_assert(bytes % kTabChunks == 0 && chunk % 16 == 0, "bulk copies move multiples of 16 bytes");
+
+    uint32_t bar = uint32_t(__cvta_generic_to_shared(&tabBar));
+    uint32_t dst = uint32_t(__cvta_generic_to_shared(tabSmem));
+    if (threadIdx.x == 0)
+    {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (threadIdx.x == 0)
+    {
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+        const char* src = reinterpret_cast<const char*>(table);
+#pragma unroll 1
+        for (int c = 0; c < kTabChunks; ++c)
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                         ::"r"(dst + c * chunk), "l"(src + size_t(c) * chunk), "r"(chunk), "r"(bar)
+                         : "memory");
+    }
+    asm volatile("{\n"
+                 ".reg .pred p;\n"
+                 "TAB_WAIT:\n"
+                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], 0;\n"
+                 "@p bra TAB_DONE;\n"
+                 "bra TAB_WAIT;\n"
+                 "TAB_DONE:\n"
+                 "}" ::"r"(bar)
+                 : "memory");
+    return reinterpret_cast<const T*>(tabSmem);
 }
 
 #define LD(p, j) __ldg((p) + (j))
@@ -328,13 +444,11 @@ __device__ __forceinline__ NbList nbList(const uint32_t* nidx, const uint32_t* n
 #ifndef SPHB200_XMASS_MIN_BLOCKS
 #define SPHB200_XMASS_MIN_BLOCKS 1
 #endif
-template<bool Pbc, class T>
-__global__ void __launch_bounds__(kHydroBlock, SPHB200_XMASS_MIN_BLOCKS)
-    xmassKernel(uint32_t first, uint32_t last, unsigned ngmax, double K, PbcBox box, const uint32_t* __restrict__ nidx,
-                F<T> f, const PosRec<T>* __restrict__ r0, const Rec2<T>* __restrict__ wh)
+template<bool Pbc, class T, class Tab>
+__device__ __forceinline__ void xmassTarget(uint32_t i, uint32_t first, unsigned ngmax, double K, const PbcBox& box,
+                                            const uint32_t* __restrict__ nidx, const F<T>& f,
+                                            const PosRec<T>* __restrict__ r0, Tab wh)
 {
-    uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= last || (f.active && !f.active[i])) return;
     NbList nb = nbList(nidx, f.nc, first, i, ngmax);
 
     PosRec<T> pi = r0[i];
@@ -350,12 +464,46 @@ __global__ void __launch_bounds__(kHydroBlock, SPHB200_XMASS_MIN_BLOCKS)
         PosRec<T> pj_ = ldRec(r0, j);
         T xx = xi - pj_.x, yy = yi - pj_.y, zz = zi - pj_.z;
         if (pbcI) applyPBC(box, T(2) * hi, xx, yy, zz);
-        T dist = sqrt(xx * xx + yy * yy + zz * zz);
+        T dist = sqrt(dot3(xx, yy, zz, xx, yy, zz));
         T vloc = dist * hInv;
-        T w    = lookup(wh, vloc);
+        T w    = wh(vloc);
         rho0i += w * pj_.m;
     }
     f.xm[i] = T(mi / (rho0i * K * h3Inv));
+}
+
+template<bool Pbc, class T>
+__global__ void __launch_bounds__(kHydroBlock, SPHB200_XMASS_MIN_BLOCKS)
+    xmassKernel(uint32_t first, uint32_t last, unsigned ngmax, double K, PbcBox box, const uint32_t* __restrict__ nidx,
+                F<T> f, const PosRec<T>* __restrict__ r0, const Rec2<T>* __restrict__ wh)
+{
+    uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= last || (f.active && !f.active[i])) return;
+    xmassTarget<Pbc, T>(i, first, ngmax, K, box, nidx, f, r0, GlobalTab<T>{wh});
+}
+
+// ---- persistent variants with the kernel table in shared memory ---------------------------------------------------
+// One CTA per SM holds the whole table; its warps walk the 32-target groups of the neighbor lists with a grid stride
+// (adjacent warps take adjacent groups, so the gathered records stay as local in L1 as with 128-target blocks).
+// Which variant runs is decided per operator from the first timed launches of each (sphb200_ctx::tabTune): lattices,
+// whose warps share a handful of table lines, are faster through L1; jittered sets are faster through shared memory.
+#define FOR_TARGET_GROUPS(i, begin, last)                                                                             \
+    for (uint32_t g__ = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), i = (begin) + g__ * 32 + (threadIdx.x & 31); \
+         g__ < ((last) - (begin) + 31) / 32; g__ += gridDim.x * (blockDim.x >> 5), i = (begin) + g__ * 32 + (threadIdx.x & 31))
+
+constexpr int kXmassSmemBlock = 1024;
+template<bool Pbc, class T>
+__global__ void __launch_bounds__(kXmassSmemBlock, 1)
+    xmassSmemKernel(uint32_t first, uint32_t last, unsigned ngmax, double K, PbcBox box,
+                    const uint32_t* __restrict__ nidx, F<T> f, const PosRec<T>* __restrict__ r0,
+                    const T* __restrict__ table)
+{
+    SharedTab<T> wh{stageTable(table)};
+    FOR_TARGET_GROUPS(i, first, last)
+    {
+        if (i >= last || (f.active && !f.active[i])) continue;
+        xmassTarget<Pbc, T>(i, first, ngmax, K, box, nidx, f, r0, wh);
+    }
 }
 
 // ---------------------------------------------------------------- VeDefGradh (ve_def_gradh_kern.hpp:43-90)
@@ -437,14 +585,12 @@ __global__ void eosKernel(uint32_t first, uint32_t last, F<T> f, T muiConst, dou
 #ifndef SPHB200_IAD_MIN_BLOCKS
 #define SPHB200_IAD_MIN_BLOCKS 6 // <= 80 registers: 24 warps/SM instead of 16 (measured 6.9 -> 5.75 ms)
 #endif
-template<bool Pbc, class T>
-__global__ void __launch_bounds__(kHydroBlock, SPHB200_IAD_MIN_BLOCKS)
-    iadDivvCurlvKernel(uint32_t first, uint32_t last, unsigned ngmax, double K, PbcBox box,
-                       const uint32_t* __restrict__ nidx, F<T> f, const PosRec<T>* __restrict__ r0,
-                       const Rec4<T>* __restrict__ r1, const Rec2<T>* __restrict__ wh, bool doGradV)
+template<bool Pbc, class T, class Tab>
+__device__ __forceinline__ void iadTarget(uint32_t i, uint32_t first, unsigned ngmax, double K, const PbcBox& box,
+                                          const uint32_t* __restrict__ nidx, const F<T>& f,
+                                          const PosRec<T>* __restrict__ r0, const Rec4<T>* __restrict__ r1, Tab wh,
+                                          bool doGradV)
 {
-    uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= last || (f.active && !f.active[i])) return;
     NbList nb = nbList(nidx, f.nc, first, i, ngmax);
 
     PosRec<T> pi = r0[i]; // {x, y, z, xm}
@@ -463,9 +609,9 @@ __global__ void __launch_bounds__(kHydroBlock, SPHB200_IAD_MIN_BLOCKS)
         T xmassj = pj_.m, volj = vj.d; // 4th slots: xm_j and V_j = xm_j / kx_j
         T rx = xi - pj_.x, ry = yi - pj_.y, rz = zi - pj_.z;
         if (pbcI) applyPBC(box, T(2) * hi, rx, ry, rz);
-        T dist   = sqrt(rx * rx + ry * ry + rz * rz);
+        T dist   = sqrt(dot3(rx, ry, rz, rx, ry, rz));
         T vloc   = dist * hiInv;
-        T w      = lookup(wh, vloc);
+        T w      = wh(vloc);
         T volj_w = volj * w;
 
         tau11 += rx * rx * volj_w;
@@ -493,25 +639,26 @@ __global__ void __launch_bounds__(kHydroBlock, SPHB200_IAD_MIN_BLOCKS)
     tau23 *= normalization;
     tau33 *= normalization;
 
-    T det = tau11 * tau22 * tau33 + T(2) * tau12 * tau23 * tau13 - tau11 * tau23 * tau23 - tau22 * tau13 * tau13 -
-            tau33 * tau12 * tau12;
+    T det = fmaT(-(tau33 * tau12), tau12,
+                 fmaT(-(tau22 * tau13), tau13,
+                      fmaT(-(tau11 * tau23), tau23, fmaT(T(2) * tau12 * tau23, tau13, tau11 * tau22 * tau33))));
     T factor = normalization * (hi * hi * hi) / (det * K);
 
-    T c11i = (tau22 * tau33 - tau23 * tau23) * factor;
-    T c12i = (tau13 * tau23 - tau33 * tau12) * factor;
-    T c13i = (tau12 * tau23 - tau22 * tau13) * factor;
-    T c22i = (tau11 * tau33 - tau13 * tau13) * factor;
-    T c23i = (tau13 * tau12 - tau11 * tau23) * factor;
-    T c33i = (tau11 * tau22 - tau12 * tau12) * factor;
+    T c11i = sum2(tau22, tau33, -tau23, tau23) * factor;
+    T c12i = sum2(tau13, tau23, -tau33, tau12) * factor;
+    T c13i = sum2(tau12, tau23, -tau22, tau13) * factor;
+    T c22i = sum2(tau11, tau33, -tau13, tau13) * factor;
+    T c23i = sum2(tau13, tau12, -tau11, tau23) * factor;
+    T c33i = sum2(tau11, tau22, -tau12, tau12) * factor;
     f.c11[i] = c11i; f.c12[i] = c12i; f.c13[i] = c13i; f.c22[i] = c22i; f.c23[i] = c23i; f.c33[i] = c33i;
 
     // dV_a[b] = -(C_i S_a)_b
     T dVx[3], dVy[3], dVz[3];
     auto applyC = [&](const T* S, T* dV)
     {
-        dV[0] = -(c11i * S[0] + c12i * S[1] + c13i * S[2]);
-        dV[1] = -(c12i * S[0] + c22i * S[1] + c23i * S[2]);
-        dV[2] = -(c13i * S[0] + c23i * S[1] + c33i * S[2]);
+        dV[0] = -dot3(c11i, c12i, c13i, S[0], S[1], S[2]);
+        dV[1] = -dot3(c12i, c22i, c23i, S[0], S[1], S[2]);
+        dV[2] = -dot3(c13i, c23i, c33i, S[0], S[1], S[2]);
     };
     applyC(Sx, dVx);
     applyC(Sy, dVy);
@@ -524,7 +671,7 @@ __global__ void __launch_bounds__(kHydroBlock, SPHB200_IAD_MIN_BLOCKS)
     if (f.curlv)
     {
         T cx = dVz[1] - dVy[2], cy = dVx[2] - dVz[0], cz = dVy[0] - dVx[1];
-        f.curlv[i] = norm_kxi * sqrt(cx * cx + cy * cy + cz * cz);
+        f.curlv[i] = norm_kxi * sqrt(dot3(cx, cy, cz, cx, cy, cz));
     }
     if (doGradV)
     {
@@ -537,23 +684,30 @@ __global__ void __launch_bounds__(kHydroBlock, SPHB200_IAD_MIN_BLOCKS)
     }
 }
 
-// ---------------------------------------------------------------- pair quantities shared by AVswitches and momentum
-// The Courant signal velocity can be evaluated in either kernel (sphb200_av_switches_courant lets the step know its
-// time step before momentumEnergy starts); explicit fused multiply-adds make both evaluations the same bits.
-__device__ __forceinline__ double fmaT(double a, double b, double c) { return __fma_rn(a, b, c); }
-__device__ __forceinline__ float fmaT(float a, float b, float c) { return __fmaf_rn(a, b, c); }
-
-template<class T>
-__device__ __forceinline__ T dot3(T ax, T ay, T az, T bx, T by, T bz)
+template<bool Pbc, class T>
+__global__ void __launch_bounds__(kHydroBlock, SPHB200_IAD_MIN_BLOCKS)
+    iadDivvCurlvKernel(uint32_t first, uint32_t last, unsigned ngmax, double K, PbcBox box,
+                       const uint32_t* __restrict__ nidx, F<T> f, const PosRec<T>* __restrict__ r0,
+                       const Rec4<T>* __restrict__ r1, const Rec2<T>* __restrict__ wh, bool doGradV)
 {
-    return fmaT(az, bz, fmaT(ay, by, ax * bx));
+    uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= last || (f.active && !f.active[i])) return;
+    iadTarget<Pbc, T>(i, first, ngmax, K, box, nidx, f, r0, r1, GlobalTab<T>{wh}, doGradV);
 }
 
-//! @brief vijsignal of momentum_energy_kern.hpp: 0.5 (c_i + c_j) - 2 w_ij
-template<class T>
-__device__ __forceinline__ T courantSignal(T ci, T cj, T wij)
+constexpr int kIadSmemBlock = SPHB200_IAD_MIN_BLOCKS * kHydroBlock; // same registers per thread as the L1 variant
+template<bool Pbc, class T>
+__global__ void __launch_bounds__(kIadSmemBlock, 1)
+    iadDivvCurlvSmemKernel(uint32_t first, uint32_t last, unsigned ngmax, double K, PbcBox box,
+                           const uint32_t* __restrict__ nidx, F<T> f, const PosRec<T>* __restrict__ r0,
+                           const Rec4<T>* __restrict__ r1, const T* __restrict__ table, bool doGradV)
 {
-    return fmaT(T(-2), wij, T(0.5) * (ci + cj));
+    SharedTab<T> wh{stageTable(table)};
+    FOR_TARGET_GROUPS(i, first, last)
+    {
+        if (i >= last || (f.active && !f.active[i])) continue;
+        iadTarget<Pbc, T>(i, first, ngmax, K, box, nidx, f, r0, r1, wh, doGradV);
+    }
 }
 
 // ---------------------------------------------------------------- AV switches (av_switches_kern.hpp:44-137)
@@ -561,12 +715,12 @@ __device__ __forceinline__ T courantSignal(T ci, T cj, T wij)
 #ifndef SPHB200_AV_MIN_BLOCKS
 #define SPHB200_AV_MIN_BLOCKS 7 // <= 72 registers: 28 warps/SM (measured 6.6 -> 6.2 ms)
 #endif
-template<bool Pbc, bool Courant, class T>
+template<bool Pbc, bool Courant, class T, class Tab>
 __device__ __forceinline__ void avSwitchesBody(uint32_t i, uint32_t first, unsigned ngmax, double K, const PbcBox& box,
                                                const uint32_t* __restrict__ nidx, const F<T>& f,
                                                const PosRec<T>* __restrict__ r0, const Rec4<T>* __restrict__ r1,
-                                               const Rec2<T>* __restrict__ wh, double dt, T alphamin, T alphamax,
-                                               T decay_constant, T& maxvsignal_i)
+                                               Tab wh, double dt, T alphamin, T alphamax, T decay_constant,
+                                               T& maxvsignal_i)
 {
     NbList nb = nbList(nidx, f.nc, first, i, ngmax);
 
@@ -611,7 +765,7 @@ __device__ __forceinline__ void avSwitchesBody(uint32_t i, uint32_t first, unsig
         vijsignal_i = max(vijsignal_i, vijsignal_ij);
 
         T v1 = dist * hiInv;
-        T w  = lookup(wh, v1);
+        T w  = wh(v1);
 
         T volj   = vj.d;
         T factor = volj * (divv_i - divv_j) * w;
@@ -623,17 +777,17 @@ __device__ __forceinline__ void avSwitchesBody(uint32_t i, uint32_t first, unsig
 
     T c11i = f.c11[i], c12i = f.c12[i], c13i = f.c13[i], c22i = f.c22[i], c23i = f.c23[i], c33i = f.c33[i];
     T Kh3        = K * hiInv3;
-    T graddivv_x = -(c11i * gx + c12i * gy + c13i * gz) * Kh3;
-    T graddivv_y = -(c12i * gx + c22i * gy + c23i * gz) * Kh3;
-    T graddivv_z = -(c13i * gx + c23i * gy + c33i * gz) * Kh3;
-    T graddivv   = sqrt(graddivv_x * graddivv_x + graddivv_y * graddivv_y + graddivv_z * graddivv_z);
+    T graddivv_x = -dot3(c11i, c12i, c13i, gx, gy, gz) * Kh3;
+    T graddivv_y = -dot3(c12i, c22i, c23i, gx, gy, gz) * Kh3;
+    T graddivv_z = -dot3(c13i, c23i, c33i, gx, gy, gz) * Kh3;
+    T graddivv   = sqrt(dot3(graddivv_x, graddivv_y, graddivv_z, graddivv_x, graddivv_y, graddivv_z));
 
     T alpha_i  = f.alpha[i];
     T alphaloc = 0.0;
     if (divv_i < T(0))
     {
         T a_const = hi * hi * graddivv;
-        alphaloc  = alphamax * a_const / (a_const + hi * abs(divv_i) + T(0.05) * ci);
+        alphaloc  = alphamax * a_const / fmaT(T(0.05), ci, fmaT(hi, abs(divv_i), a_const));
     }
 
     if (alphaloc >= alpha_i) { alpha_i = alphaloc; }
@@ -658,8 +812,26 @@ __global__ void __launch_bounds__(kHydroBlock, SPHB200_AV_MIN_BLOCKS)
     uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= last || (f.active && !f.active[i])) return;
     T unused = 0;
-    avSwitchesBody<Pbc, false, T>(i, first, ngmax, K, box, nidx, f, r0, r1, wh, dt, alphamin, alphamax, decay_constant,
-                                  unused);
+    avSwitchesBody<Pbc, false, T>(i, first, ngmax, K, box, nidx, f, r0, r1, GlobalTab<T>{wh}, dt, alphamin, alphamax,
+                                  decay_constant, unused);
+}
+
+constexpr int kAvSmemBlock = SPHB200_AV_MIN_BLOCKS * kHydroBlock;
+template<bool Pbc, class T>
+__global__ void __launch_bounds__(kAvSmemBlock, 1)
+    avSwitchesSmemKernel(uint32_t first, uint32_t last, unsigned ngmax, double K, PbcBox box,
+                         const uint32_t* __restrict__ nidx, F<T> f, const PosRec<T>* __restrict__ r0,
+                         const Rec4<T>* __restrict__ r1, const T* __restrict__ table, double dt, T alphamin, T alphamax,
+                         T decay_constant)
+{
+    SharedTab<T> wh{stageTable(table)};
+    FOR_TARGET_GROUPS(i, first, last)
+    {
+        if (i >= last || (f.active && !f.active[i])) continue;
+        T unused = 0;
+        avSwitchesBody<Pbc, false, T>(i, first, ngmax, K, box, nidx, f, r0, r1, wh, dt, alphamin, alphamax,
+                                      decay_constant, unused);
+    }
 }
 
 /*! @brief AVswitches that also evaluates the Courant time step of momentumEnergy (tsKCourant over the same
@@ -678,7 +850,7 @@ __global__ void __launch_bounds__(kHydroBlock, 5)
     if (i < last && (!f.active || f.active[i]))
     {
         T maxvsignal = 0;
-        avSwitchesBody<Pbc, true, T>(i, first, ngmax, K, box, nidx, f, r0, r1, wh, dt, alphamin, alphamax,
+        avSwitchesBody<Pbc, true, T>(i, first, ngmax, K, box, nidx, f, r0, r1, GlobalTab<T>{wh}, dt, alphamin, alphamax,
                                      decay_constant, maxvsignal);
         T v  = maxvsignal > T(0) ? maxvsignal : f.c[i];
         dt_i = T(Kcour * f.h[i] / v);
@@ -689,15 +861,40 @@ __global__ void __launch_bounds__(kHydroBlock, 5)
     if ((threadIdx.x & 31) == 0) atomicMin(minDtKey, orderedKey(double(dt_i)));
 }
 
+constexpr int kAvCourantSmemBlock = 5 * kHydroBlock;
+template<bool Pbc, class T>
+__global__ void __launch_bounds__(kAvCourantSmemBlock, 1)
+    avSwitchesCourantSmemKernel(uint32_t first, uint32_t last, unsigned ngmax, double K, PbcBox box,
+                                const uint32_t* __restrict__ nidx, F<T> f, const PosRec<T>* __restrict__ r0,
+                                const Rec4<T>* __restrict__ r1, const T* __restrict__ table, double dt, T alphamin,
+                                T alphamax, T decay_constant, float Kcour, unsigned long long* __restrict__ minDtKey)
+{
+    SharedTab<T> wh{stageTable(table)};
+    T dtMin = INFINITY;
+    FOR_TARGET_GROUPS(i, first, last)
+    {
+        if (i >= last || (f.active && !f.active[i])) continue;
+        T maxvsignal = 0;
+        avSwitchesBody<Pbc, true, T>(i, first, ngmax, K, box, nidx, f, r0, r1, wh, dt, alphamin, alphamax,
+                                     decay_constant, maxvsignal);
+        T v   = maxvsignal > T(0) ? maxvsignal : f.c[i];
+        dtMin = min(dtMin, T(Kcour * f.h[i] / v));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+        dtMin = min(dtMin, __shfl_xor_sync(0xffffffffu, dtMin, o));
+    if ((threadIdx.x & 31) == 0) atomicMin(minDtKey, orderedKey(double(dtMin)));
+}
+
 // ---------------------------------------------------------------- momentum + energy (momentum_energy_kern.hpp:43-222)
 template<class T>
 __device__ __forceinline__ T avRvCorrection(T rx, T ry, T rz, T eta_ab, T eta_crit, const T* gi, const T* gj)
 {
     // symv: upper-triangular product as written in sph/kernels.hpp:86-94
-    T s0 = gi[0] * rx + gi[1] * ry + gi[2] * rz, s1 = gi[3] * ry + gi[4] * rz, s2 = gi[5] * rz;
-    T dmy1 = rx * s0 + ry * s1 + rz * s2;
-    T t0 = gj[0] * rx + gj[1] * ry + gj[2] * rz, t1 = gj[3] * ry + gj[4] * rz, t2 = gj[5] * rz;
-    T dmy2 = rx * t0 + ry * t1 + rz * t2;
+    T s0 = dot3(gi[0], gi[1], gi[2], rx, ry, rz), s1 = sum2(gi[3], ry, gi[4], rz), s2 = gi[5] * rz;
+    T dmy1 = dot3(rx, ry, rz, s0, s1, s2);
+    T t0 = dot3(gj[0], gj[1], gj[2], rx, ry, rz), t1 = sum2(gj[3], ry, gj[4], rz), t2 = gj[5] * rz;
+    T dmy2 = dot3(rx, ry, rz, t0, t1, t2);
     T dmy3 = T(1);
     if (eta_ab < eta_crit)
     {
@@ -746,6 +943,158 @@ struct MomRecs
     const Rec4<T>*r1, *r2, *r3, *r4, *r5, *r6;
 };
 
+//! @brief momentum and energy sums of target i; returns its Courant time step
+template<bool Pbc, bool avClean, class T, class Tab>
+__device__ __forceinline__ T momentumTarget(uint32_t i, uint32_t first, unsigned ngmax, double K, const PbcBox& box,
+                                            const uint32_t* __restrict__ nidx, const F<T>& f, const MomRecs<T>& rec,
+                                            Tab wh, T Atmin, T Atmax, T ramp, float Kcour)
+{
+    NbList nb = nbList(nidx, f.nc, first, i, ngmax);
+
+    PosRec<T> pi = rec.r0[i];
+    Rec4<T> vi   = rec.r1[i]; // {v, 1/h}
+    Rec4<T> si   = rec.r2[i]; // {xm, c, prho, rho}
+    double xi = pi.x, yi = pi.y, zi = pi.z;
+    T vxi = vi.a, vyi = vi.b, vzi = vi.c, hi = f.h[i];
+    T xmassi = si.a, ci = si.b, prhoi = si.c, rhoi = si.d;
+    T alpha_i = f.alpha[i];
+
+    T hiInv  = vi.d;
+    T hiInv3 = hiInv * hiInv * hiInv;
+    T rhoiInv = T(1) / rhoi;
+
+    T maxvsignali = 0.0;
+    T momentum_x = 0.0, momentum_y = 0.0, momentum_z = 0.0, energy = 0.0;
+    T a_visc_energy = 0.0;
+
+    T c11i = f.c11[i], c12i = f.c12[i], c13i = f.c13[i], c22i = f.c22[i], c23i = f.c23[i], c33i = f.c33[i];
+
+    T gradV_i[6];
+    if (avClean)
+    {
+        gradV_i[0] = f.dV11[i]; gradV_i[1] = f.dV12[i]; gradV_i[2] = f.dV13[i];
+        gradV_i[3] = f.dV22[i]; gradV_i[4] = f.dV23[i]; gradV_i[5] = f.dV33[i];
+    }
+
+    T eta_crit = cbrt(T(32) * M_PI / T(3) / T(nb.count + 1));
+
+    const bool pbcI = Pbc && reachesPeriodicFace(box, xi, yi, zi, T(2) * hi);
+    FOR_NEIGHBORS(nb, j)
+    {
+        PosRec<T> pj_ = ldRec(rec.r0, j);
+        Rec4<T> vj    = ldRec(rec.r1, j);
+        Rec4<T> sj    = ldRec(rec.r2, j);
+        Rec4<T> ca    = ldRec(rec.r3, j);
+        Rec4<T> cb    = ldRec(rec.r4, j);
+
+        T rx = xi - pj_.x, ry = yi - pj_.y, rz = zi - pj_.z;
+        T vxj = vj.a, vyj = vj.b, vzj = vj.c;
+        if (pbcI) applyPBC(box, T(2) * hi, rx, ry, rz);
+
+        T r2_  = dot3(rx, ry, rz, rx, ry, rz);
+        T dist = sqrt(r2_);
+
+        T vx_ij = vxi - vxj, vy_ij = vyi - vyj, vz_ij = vzi - vzj;
+
+        T hjInv = vj.d;
+
+        T v1 = dist * hiInv;
+        T v2 = dist * hjInv;
+
+        T hjInv3 = hjInv * hjInv * hjInv;
+        T Wi     = hiInv3 * wh(v1);
+        T Wj     = hjInv3 * wh(v2);
+
+        T termA1_i = -dot3(c11i, c12i, c13i, rx, ry, rz) * Wi;
+        T termA2_i = -dot3(c12i, c22i, c23i, rx, ry, rz) * Wi;
+        T termA3_i = -dot3(c13i, c23i, c33i, rx, ry, rz) * Wi;
+
+        T c11j = ca.a, c12j = ca.b, c13j = ca.c, c22j = ca.d, c23j = cb.a, c33j = cb.b;
+
+        T termA1_j = -dot3(c11j, c12j, c13j, rx, ry, rz) * Wj;
+        T termA2_j = -dot3(c12j, c22j, c23j, rx, ry, rz) * Wj;
+        T termA3_j = -dot3(c13j, c23j, c33j, rx, ry, rz) * Wj;
+
+        T mj = pj_.m, cj = sj.b, xmassj = sj.a, rhoj = sj.d;
+
+        T rv = dot3(rx, ry, rz, vx_ij, vy_ij, vz_ij);
+        if (avClean)
+        {
+            Rec4<T> ga = ldRec(rec.r5, j);
+            Rec2<T> gb = ldHalf(rec.r6, j);
+            T gradV_j[6] = {ga.a, ga.b, ga.c, ga.d, gb.a, gb.b};
+            rv += avRvCorrection(rx, ry, rz, min(v1, v2), eta_crit, gradV_i, gradV_j);
+        }
+
+        T wij = rv / dist;
+        // artificial_viscosity (sph/kernels.hpp:70-83), beta = 2
+        T viscosity_ij = 0.0;
+        if (wij < 0.0)
+        {
+            T vij_signal = fmaT(T(-2.0), wij, (alpha_i + cb.c) / 4.0 * (ci + cj));
+            viscosity_ij = -vij_signal * wij;
+        }
+
+        T vijsignal = courantSignal(ci, cj, wij);
+        maxvsignali = (vijsignal > maxvsignali) ? vijsignal : maxvsignali;
+
+        // Atwood = |rho_i - rho_j| / (rho_i + rho_j) selects the branch; the quotient itself is only needed inside
+        // the ramp, so the two common branches compare against Atmin/Atmax * (rho_i + rho_j) without dividing
+        // (the ramp is continuous at both ends, a tie decided the other way changes nothing beyond rounding)
+        T a_mom, b_mom;
+        T rhoDiff = abs(rhoi - rhoj), rhoSum = rhoi + rhoj;
+        if (rhoDiff < Atmin * rhoSum)
+        {
+            a_mom = xmassi * xmassi;
+            b_mom = xmassj * xmassj;
+        }
+        else if (rhoDiff > Atmax * rhoSum)
+        {
+            a_mom = xmassi * xmassj;
+            b_mom = a_mom;
+        }
+        else
+        {
+            // xm_i^(2-s) xm_j^s = xm_i^2 q^s and xm_j^(2-s) xm_i^s = xm_j^2 / q^s with q = xm_j / xm_i: one
+            // log + exp instead of four pow.  One lane in the ramp stalls its whole warp for the branch, and on
+            // jittered data (turbulence, Noh) some lane is in it in most iterations: 4 pow made the kernel 2.9x
+            // slower than on the Sedov lattice.  |s log q| << 1, so the result stays within a few ulp of pow's.
+            T Atwood   = rhoDiff / rhoSum;
+            T sigma_ij = ramp * (Atwood - Atmin);
+            T qs       = rampPower(xmassi, xmassj, sigma_ij);
+            a_mom      = xmassi * xmassi * qs;
+            b_mom      = xmassj * xmassj / qs;
+        }
+
+        T a_visc   = mj * rhoiInv * viscosity_ij; // m_j / rho_i with the reciprocal taken once per target
+        T b_visc   = cb.d * viscosity_ij; // (m_j / rho_j) * viscosity_ij
+        T a_visc_x = T(0.5) * sum2(a_visc, termA1_i, b_visc, termA1_j);
+        T a_visc_y = T(0.5) * sum2(a_visc, termA2_i, b_visc, termA2_j);
+        T a_visc_z = T(0.5) * sum2(a_visc, termA3_i, b_visc, termA3_j);
+        a_visc_energy += dot3(a_visc_x, a_visc_y, a_visc_z, vx_ij, vy_ij, vz_ij);
+
+        energy += mj * a_mom * dot3(vx_ij, vy_ij, vz_ij, termA1_i, termA2_i, termA3_i);
+
+        T momentum_i = mj * prhoi * a_mom;
+        T momentum_j = mj * sj.c * b_mom;
+        momentum_x += sum2(momentum_i, termA1_i, momentum_j, termA1_j) + a_visc_x;
+        momentum_y += sum2(momentum_i, termA2_i, momentum_j, termA2_j) + a_visc_y;
+        momentum_z += sum2(momentum_i, termA3_i, momentum_j, termA3_j) + a_visc_z;
+    }
+
+    a_visc_energy = max(T(0), a_visc_energy);
+    f.du[i]       = K * fmaT(prhoi, energy, T(0.5) * a_visc_energy);
+    f.ax[i]       = -K * momentum_x;
+    f.ay[i]       = -K * momentum_y;
+    f.az[i]       = -K * momentum_z;
+
+    // tsKCourant (sph/kernels.hpp:10-16)
+    T v  = maxvsignali > T(0) ? maxvsignali : ci;
+    T dt_i = T(Kcour * hi / v);
+    if (f.dtParticle) f.dtParticle[i] = dt_i;
+    return dt_i;
+}
+
 template<bool Pbc, bool avClean, class T>
 __global__ void __launch_bounds__(kHydroBlock, kMomentumMinBlocks)
     momentumEnergyKernel(uint32_t first, uint32_t last, unsigned ngmax, double K, PbcBox box,
@@ -757,157 +1106,36 @@ __global__ void __launch_bounds__(kHydroBlock, kMomentumMinBlocks)
     uint32_t i  = begin + blockIdx.x * blockDim.x + threadIdx.x;
     T dt_i      = INFINITY;
     if (i < last && (!f.active || f.active[i]))
-    {
-        NbList nb = nbList(nidx, f.nc, first, i, ngmax);
-
-        PosRec<T> pi = rec.r0[i];
-        Rec4<T> vi   = rec.r1[i]; // {v, 1/h}
-        Rec4<T> si   = rec.r2[i]; // {xm, c, prho, rho}
-        double xi = pi.x, yi = pi.y, zi = pi.z;
-        T vxi = vi.a, vyi = vi.b, vzi = vi.c, hi = f.h[i];
-        T xmassi = si.a, ci = si.b, prhoi = si.c, rhoi = si.d;
-        T alpha_i = f.alpha[i];
-
-        T hiInv  = vi.d;
-        T hiInv3 = hiInv * hiInv * hiInv;
-        T rhoiInv = T(1) / rhoi;
-
-        T maxvsignali = 0.0;
-        T momentum_x = 0.0, momentum_y = 0.0, momentum_z = 0.0, energy = 0.0;
-        T a_visc_energy = 0.0;
-
-        T c11i = f.c11[i], c12i = f.c12[i], c13i = f.c13[i], c22i = f.c22[i], c23i = f.c23[i], c33i = f.c33[i];
-
-        T gradV_i[6];
-        if (avClean)
-        {
-            gradV_i[0] = f.dV11[i]; gradV_i[1] = f.dV12[i]; gradV_i[2] = f.dV13[i];
-            gradV_i[3] = f.dV22[i]; gradV_i[4] = f.dV23[i]; gradV_i[5] = f.dV33[i];
-        }
-
-        T eta_crit = cbrt(T(32) * M_PI / T(3) / T(nb.count + 1));
-
-        const bool pbcI = Pbc && reachesPeriodicFace(box, xi, yi, zi, T(2) * hi);
-        FOR_NEIGHBORS(nb, j)
-        {
-            PosRec<T> pj_ = ldRec(rec.r0, j);
-            Rec4<T> vj    = ldRec(rec.r1, j);
-            Rec4<T> sj    = ldRec(rec.r2, j);
-            Rec4<T> ca    = ldRec(rec.r3, j);
-            Rec4<T> cb    = ldRec(rec.r4, j);
-
-            T rx = xi - pj_.x, ry = yi - pj_.y, rz = zi - pj_.z;
-            T vxj = vj.a, vyj = vj.b, vzj = vj.c;
-            if (pbcI) applyPBC(box, T(2) * hi, rx, ry, rz);
-
-            T r2_  = dot3(rx, ry, rz, rx, ry, rz);
-            T dist = sqrt(r2_);
-
-            T vx_ij = vxi - vxj, vy_ij = vyi - vyj, vz_ij = vzi - vzj;
-
-            T hjInv = vj.d;
-
-            T v1 = dist * hiInv;
-            T v2 = dist * hjInv;
-
-            T hjInv3 = hjInv * hjInv * hjInv;
-            T Wi     = hiInv3 * lookup(wh, v1);
-            T Wj     = hjInv3 * lookup(wh, v2);
-
-            T termA1_i = -(c11i * rx + c12i * ry + c13i * rz) * Wi;
-            T termA2_i = -(c12i * rx + c22i * ry + c23i * rz) * Wi;
-            T termA3_i = -(c13i * rx + c23i * ry + c33i * rz) * Wi;
-
-            T c11j = ca.a, c12j = ca.b, c13j = ca.c, c22j = ca.d, c23j = cb.a, c33j = cb.b;
-
-            T termA1_j = -(c11j * rx + c12j * ry + c13j * rz) * Wj;
-            T termA2_j = -(c12j * rx + c22j * ry + c23j * rz) * Wj;
-            T termA3_j = -(c13j * rx + c23j * ry + c33j * rz) * Wj;
-
-            T mj = pj_.m, cj = sj.b, xmassj = sj.a, rhoj = sj.d;
-
-            T rv = dot3(rx, ry, rz, vx_ij, vy_ij, vz_ij);
-            if (avClean)
-            {
-                Rec4<T> ga = ldRec(rec.r5, j);
-                Rec2<T> gb = ldHalf(rec.r6, j);
-                T gradV_j[6] = {ga.a, ga.b, ga.c, ga.d, gb.a, gb.b};
-                rv += avRvCorrection(rx, ry, rz, min(v1, v2), eta_crit, gradV_i, gradV_j);
-            }
-
-            T wij = rv / dist;
-            // artificial_viscosity (sph/kernels.hpp:70-83), beta = 2
-            T viscosity_ij = 0.0;
-            if (wij < 0.0)
-            {
-                T vij_signal = (alpha_i + cb.c) / 4.0 * (ci + cj) - T(2.0) * wij;
-                viscosity_ij = -vij_signal * wij;
-            }
-
-            T vijsignal = courantSignal(ci, cj, wij);
-            maxvsignali = (vijsignal > maxvsignali) ? vijsignal : maxvsignali;
-
-            // Atwood = |rho_i - rho_j| / (rho_i + rho_j) selects the branch; the quotient itself is only needed inside
-            // the ramp, so the two common branches compare against Atmin/Atmax * (rho_i + rho_j) without dividing
-            // (the ramp is continuous at both ends, a tie decided the other way changes nothing beyond rounding)
-            T a_mom, b_mom;
-            T rhoDiff = abs(rhoi - rhoj), rhoSum = rhoi + rhoj;
-            if (rhoDiff < Atmin * rhoSum)
-            {
-                a_mom = xmassi * xmassi;
-                b_mom = xmassj * xmassj;
-            }
-            else if (rhoDiff > Atmax * rhoSum)
-            {
-                a_mom = xmassi * xmassj;
-                b_mom = a_mom;
-            }
-            else
-            {
-                // xm_i^(2-s) xm_j^s = xm_i^2 q^s and xm_j^(2-s) xm_i^s = xm_j^2 / q^s with q = xm_j / xm_i: one
-                // log + exp instead of four pow.  One lane in the ramp stalls its whole warp for the branch, and on
-                // jittered data (turbulence, Noh) some lane is in it in most iterations: 4 pow made the kernel 2.9x
-                // slower than on the Sedov lattice.  |s log q| << 1, so the result stays within a few ulp of pow's.
-                T Atwood   = rhoDiff / rhoSum;
-                T sigma_ij = ramp * (Atwood - Atmin);
-                T qs       = rampPower(xmassi, xmassj, sigma_ij);
-                a_mom      = xmassi * xmassi * qs;
-                b_mom      = xmassj * xmassj / qs;
-            }
-
-            T a_visc   = mj * rhoiInv * viscosity_ij; // m_j / rho_i with the reciprocal taken once per target
-            T b_visc   = cb.d * viscosity_ij; // (m_j / rho_j) * viscosity_ij
-            T a_visc_x = T(0.5) * (a_visc * termA1_i + b_visc * termA1_j);
-            T a_visc_y = T(0.5) * (a_visc * termA2_i + b_visc * termA2_j);
-            T a_visc_z = T(0.5) * (a_visc * termA3_i + b_visc * termA3_j);
-            a_visc_energy += a_visc_x * vx_ij + a_visc_y * vy_ij + a_visc_z * vz_ij;
-
-            energy += mj * a_mom * (vx_ij * termA1_i + vy_ij * termA2_i + vz_ij * termA3_i);
-
-            T momentum_i = mj * prhoi * a_mom;
-            T momentum_j = mj * sj.c * b_mom;
-            momentum_x += momentum_i * termA1_i + momentum_j * termA1_j + a_visc_x;
-            momentum_y += momentum_i * termA2_i + momentum_j * termA2_j + a_visc_y;
-            momentum_z += momentum_i * termA3_i + momentum_j * termA3_j + a_visc_z;
-        }
-
-        a_visc_energy = max(T(0), a_visc_energy);
-        f.du[i]       = K * (prhoi * energy + T(0.5) * a_visc_energy);
-        f.ax[i]       = -K * momentum_x;
-        f.ay[i]       = -K * momentum_y;
-        f.az[i]       = -K * momentum_z;
-
-        // tsKCourant (sph/kernels.hpp:10-16)
-        T v  = maxvsignali > T(0) ? maxvsignali : ci;
-        dt_i = T(Kcour * hi / v);
-        if (f.dtParticle) f.dtParticle[i] = dt_i;
-    }
+        dt_i = momentumTarget<Pbc, avClean, T>(i, first, ngmax, K, box, nidx, f, rec, GlobalTab<T>{wh}, Atmin, Atmax,
+                                               ramp, Kcour);
 
     // block minimum -> one ordered-key atomic per warp
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1)
         dt_i = min(dt_i, __shfl_xor_sync(0xffffffffu, dt_i, o));
     if ((threadIdx.x & 31) == 0) atomicMin(minDtKey, orderedKey(double(dt_i)));
+}
+
+constexpr int kMomentumSmemBlock = 32 * kMomentumMinBlocks * (kHydroBlock / 32); // same registers per thread
+template<bool Pbc, bool avClean, class T>
+__global__ void __launch_bounds__(kMomentumSmemBlock, 1)
+    momentumEnergySmemKernel(uint32_t first, uint32_t last, unsigned ngmax, double K, PbcBox box,
+                             const uint32_t* __restrict__ nidx, F<T> f, MomRecs<T> rec, const T* __restrict__ table,
+                             T Atmin, T Atmax, T ramp, float Kcour, unsigned long long* __restrict__ minDtKey,
+                             uint32_t begin)
+{
+    SharedTab<T> wh{stageTable(table)};
+    T dtMin = INFINITY;
+    FOR_TARGET_GROUPS(i, begin, last)
+    {
+        if (i >= last || (f.active && !f.active[i])) continue;
+        dtMin = min(dtMin, momentumTarget<Pbc, avClean, T>(i, first, ngmax, K, box, nidx, f, rec, wh, Atmin, Atmax, ramp,
+                                                           Kcour));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+        dtMin = min(dtMin, __shfl_xor_sync(0xffffffffu, dtMin, o));
+    if ((threadIdx.x & 31) == 0) atomicMin(minDtKey, orderedKey(double(dtMin)));
 }
 
 // ---------------------------------------------------------------- timestep (ts_global.hpp:71-112)
@@ -1261,6 +1489,100 @@ static void ensureTables(sphb200_ctx* ctx, const sphb200_hydro_const* hc, const 
     quads = q;
 }
 
+// ---- which table variant runs ------------------------------------------------------------------------------------
+// Both variants of an operator produce the same bits, so the choice is a matter of speed only and is made from
+// measurements on the data at hand: the first launch of an operator runs (and times, with events on the context's
+// stream) the L1 variant, the second the shared-memory variant, and the faster one per target is kept for the next
+// kRetuneCalls launches, after which both are timed again (a lattice turns into a disordered set as a run evolves).
+// Reading a timing back waits for a launch made one call earlier, which has long finished in a stepping simulation.
+enum TabOp { TAB_XMASS, TAB_IAD, TAB_AV, TAB_AVC, TAB_MOMENTUM, TAB_MOMENTUM_RANGE, kNumTabOps };
+static_assert(kNumTabOps <= sphb200_ctx::kMaxTabOps, "table tuners");
+constexpr int kRetuneCalls       = 256;
+constexpr size_t kSmemMinTargets = size_t(kNumSms) * 1024 * 2; // below two waves of a persistent grid: L1 variant
+
+template<class T, class Kernel>
+static void allowTableSmem(Kernel kernel)
+{
+    SPHB200_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kTableSize * sizeof(T))));
+}
+
+static int forcedTabVariant()
+{
+    static int v = []
+    {
+        const char* e = std::getenv("SPHB200_TABLE");
+        if (!e) return -1;
+        return std::string(e) == "smem" ? 1 : (std::string(e) == "l1" ? 0 : -1);
+    }();
+    return v;
+}
+
+//! @brief true if the launch that follows shall use the shared-memory table; pair with tabLaunched() after the launch
+static bool useSmemTable(sphb200_ctx* ctx, const sphb200_hydro_const* hc, int op, size_t numTargets)
+{
+    if (reinterpret_cast<uintptr_t>(hc->wh) % 16 != 0) return false; // bulk copies need a 16-byte aligned source
+    int forced = ctx->tabForce >= 0 ? ctx->tabForce : forcedTabVariant();
+    if (forced >= 0) return forced == 1;
+    if (numTargets < kSmemMinTargets) return false;
+
+    auto& t = ctx->tabTune[op];
+    if (t.pending >= 0)
+    {
+        float ms   = 0;
+        bool valid = t.closed && cudaEventSynchronize(t.ev[1]) == cudaSuccess &&
+                     cudaEventElapsedTime(&ms, t.ev[0], t.ev[1]) == cudaSuccess;
+        cudaGetLastError();
+        if (valid) t.perTarget[t.pending] = double(ms) / double(t.pendingTargets);
+        else t.phase = 0; // a launch failed in between: measure again
+        if (valid && t.pending == 1)
+        {
+            t.smem  = t.perTarget[1] < 0.97 * t.perTarget[0];
+            t.phase = 2;
+            t.calls = 0;
+        }
+        t.pending = -1;
+    }
+    if (t.phase == 2)
+    {
+        if (++t.calls < kRetuneCalls) return t.smem;
+        t.phase = 0;
+    }
+    for (auto& e : t.ev)
+        if (!e) SPHB200_CUDA(cudaEventCreate(&e));
+    t.pending        = t.phase;
+    t.pendingTargets = numTargets;
+    t.closed         = false;
+    t.phase++;
+    SPHB200_CUDA(cudaEventRecord(t.ev[0], ctx->stream));
+    return t.pending == 1;
+}
+
+static void tabLaunched(sphb200_ctx* ctx, int op)
+{
+    auto& t = ctx->tabTune[op];
+    if (t.pending < 0 || t.closed) return;
+    SPHB200_CUDA(cudaEventRecord(t.ev[1], ctx->stream));
+    t.closed = true;
+}
+
+//! @brief KERNEL<Pbc, T> as one persistent CTA per SM with the table in dynamic shared memory
+#define LAUNCH_PBC_SMEM(ctx, box, KERNEL, block, numTargets, ...)                                                     \
+    do                                                                                                                \
+    {                                                                                                                 \
+        PbcBox pb__ = pbcBox(box);                                                                                    \
+        int grid__  = persistentGrid(numTargets, block, 1);                                                           \
+        if (pb__.px || pb__.py || pb__.pz)                                                                            \
+        {                                                                                                             \
+            allowTableSmem<T>(KERNEL<true, T>);                                                                       \
+            SPHB200_LAUNCH(ctx, (KERNEL<true, T>), grid__, block, kTableSize * sizeof(T), __VA_ARGS__);               \
+        }                                                                                                             \
+        else                                                                                                          \
+        {                                                                                                             \
+            allowTableSmem<T>(KERNEL<false, T>);                                                                      \
+            SPHB200_LAUNCH(ctx, (KERNEL<false, T>), grid__, block, kTableSize * sizeof(T), __VA_ARGS__);              \
+        }                                                                                                             \
+    } while (0)
+
 //! @brief the three momentum-only records, always repacked (momentum is their only reader, once per step)
 template<class T>
 static void packMomentum(sphb200_ctx* ctx, const sphb200_fields& f, MomRecs<T>& rec)
@@ -1285,7 +1607,7 @@ static void packMomentum(sphb200_ctx* ctx, const sphb200_fields& f, MomRecs<T>& 
 template<class T>
 static void launchMomentum(sphb200_ctx* ctx, uint32_t first, uint32_t begin, uint32_t end, bool pack,
                            const sphb200_box* box, const sphb200_hydro_const* hc, const uint32_t* neighbors,
-                           const sphb200_fields* f, const Rec2<T>* wh)
+                           const sphb200_fields* f, const Rec2<T>* wh, int tabOp)
 {
     MomRecs<T> rec;
     size_t n = f->n;
@@ -1318,13 +1640,37 @@ static void launchMomentum(sphb200_ctx* ctx, uint32_t first, uint32_t begin, uin
         SPHB200_LAUNCH(ctx, kernel, grid, kHydroBlock, 0, first, end, hc->ngmax, hc->K, pb, neighbors, scoped<T>(ctx, *f),
                        rec, wh, T(hc->Atmin), T(hc->Atmax), T(hc->ramp), float(hc->Kcour), dtKeys(ctx), begin);
     };
-    if (pbc && hc->avClean) go(momentumEnergyKernel<true, true, T>);
+    auto goSmem = [&](auto kernel)
+    {
+        allowTableSmem<T>(kernel);
+        SPHB200_LAUNCH(ctx, kernel, persistentGrid(end - begin, kMomentumSmemBlock, 1), kMomentumSmemBlock,
+                       kTableSize * sizeof(T), first, end, hc->ngmax, hc->K, pb, neighbors, scoped<T>(ctx, *f), rec,
+                       static_cast<const T*>(hc->wh), T(hc->Atmin), T(hc->Atmax), T(hc->ramp), float(hc->Kcour),
+                       dtKeys(ctx), begin);
+    };
+    if (useSmemTable(ctx, hc, tabOp, end - begin))
+    {
+        if (pbc && hc->avClean) goSmem(momentumEnergySmemKernel<true, true, T>);
+        else if (pbc) goSmem(momentumEnergySmemKernel<true, false, T>);
+        else if (hc->avClean) goSmem(momentumEnergySmemKernel<false, true, T>);
+        else goSmem(momentumEnergySmemKernel<false, false, T>);
+    }
+    else if (pbc && hc->avClean) go(momentumEnergyKernel<true, true, T>);
     else if (pbc) go(momentumEnergyKernel<true, false, T>);
     else if (hc->avClean) go(momentumEnergyKernel<false, true, T>);
     else go(momentumEnergyKernel<false, false, T>);
+    tabLaunched(ctx, tabOp);
 }
 
 extern "C" void sphb200_invalidate_records(sphb200_ctx* ctx) { ctx->packValid = 0; }
+
+extern "C" int sphb200_set_table_variant(sphb200_ctx* ctx, int variant)
+{
+    SPHB200_TRY
+    if (variant < -1 || variant > 1) throw std::runtime_error("set_table_variant: -1 (timed), 0 (L1) or 1 (shared memory)");
+    ctx->tabForce = variant;
+    SPHB200_CATCH
+}
 
 extern "C" int sphb200_xmass(sphb200_ctx* ctx, int dtype, uint32_t first, uint32_t last, const sphb200_box* box,
                              const sphb200_hydro_const* hc, const uint32_t* neighbors, const sphb200_fields* f)
@@ -1334,8 +1680,13 @@ extern "C" int sphb200_xmass(sphb200_ctx* ctx, int dtype, uint32_t first, uint32
     beginOp(ctx);
     DISPATCH(dtype, const Rec2<T>* wh; const Rec4<T>* whq; ensureTables<T>(ctx, hc, wh, whq);
              auto* r0 = static_cast<const PosRec<T>*>(ensureRec<T>(ctx, R_POS, *f));
-             LAUNCH_PBC(ctx, *box, xmassKernel, gridFor(last - first, kHydroBlock), first, last, hc->ngmax, hc->K,
-                        pbcBox(*box), neighbors, scoped<T>(ctx, *f), r0, wh););
+             if (useSmemTable(ctx, hc, TAB_XMASS, last - first))
+                 LAUNCH_PBC_SMEM(ctx, *box, xmassSmemKernel, kXmassSmemBlock, last - first, first, last, hc->ngmax,
+                                 hc->K, pbcBox(*box), neighbors, scoped<T>(ctx, *f), r0, static_cast<const T*>(hc->wh));
+             else
+                 LAUNCH_PBC(ctx, *box, xmassKernel, gridFor(last - first, kHydroBlock), first, last, hc->ngmax, hc->K,
+                            pbcBox(*box), neighbors, scoped<T>(ctx, *f), r0, wh);
+             tabLaunched(ctx, TAB_XMASS););
     invalidate(ctx, {R_PXM, R_VV}); // xm rewritten
     SPHB200_CATCH
 }
@@ -1376,8 +1727,14 @@ extern "C" int sphb200_iad_divv_curlv(sphb200_ctx* ctx, int dtype, uint32_t firs
     DISPATCH(dtype, const Rec2<T>* wh; const Rec4<T>* whq; ensureTables<T>(ctx, hc, wh, whq);
              auto* r0 = static_cast<const PosRec<T>*>(ensureRec<T>(ctx, R_PXM, *f));
              auto* r1 = static_cast<const Rec4<T>*>(ensureRec<T>(ctx, R_VV, *f));
-             LAUNCH_PBC(ctx, *box, iadDivvCurlvKernel, gridFor(last - first, kHydroBlock), first, last, hc->ngmax,
-                        hc->K, pbcBox(*box), neighbors, scoped<T>(ctx, *f), r0, r1, wh, doGradV););
+             if (useSmemTable(ctx, hc, TAB_IAD, last - first))
+                 LAUNCH_PBC_SMEM(ctx, *box, iadDivvCurlvSmemKernel, kIadSmemBlock, last - first, first, last, hc->ngmax,
+                                 hc->K, pbcBox(*box), neighbors, scoped<T>(ctx, *f), r0, r1,
+                                 static_cast<const T*>(hc->wh), doGradV);
+             else
+                 LAUNCH_PBC(ctx, *box, iadDivvCurlvKernel, gridFor(last - first, kHydroBlock), first, last, hc->ngmax,
+                            hc->K, pbcBox(*box), neighbors, scoped<T>(ctx, *f), r0, r1, wh, doGradV);
+             tabLaunched(ctx, TAB_IAD););
     invalidate(ctx, {R_PDIVV, R_CA, R_GA, R_GB}); // divv and c_ab rewritten
     SPHB200_CATCH
 }
@@ -1391,9 +1748,16 @@ extern "C" int sphb200_av_switches(sphb200_ctx* ctx, int dtype, uint32_t first, 
     DISPATCH(dtype, const Rec2<T>* wh; const Rec4<T>* whq; ensureTables<T>(ctx, hc, wh, whq);
              auto* r0 = static_cast<const PosRec<T>*>(ensureRec<T>(ctx, R_PDIVV, *f));
              auto* r1 = static_cast<const Rec4<T>*>(ensureRec<T>(ctx, R_VV, *f));
-             LAUNCH_PBC(ctx, *box, avSwitchesKernel, gridFor(last - first, kHydroBlock), first, last, hc->ngmax, hc->K,
-                        pbcBox(*box), neighbors, scoped<T>(ctx, *f), r0, r1, wh, hc->minDt, T(hc->alphamin),
-                        T(hc->alphamax), T(hc->decay_constant)););
+             if (useSmemTable(ctx, hc, TAB_AV, last - first))
+                 LAUNCH_PBC_SMEM(ctx, *box, avSwitchesSmemKernel, kAvSmemBlock, last - first, first, last, hc->ngmax,
+                                 hc->K, pbcBox(*box), neighbors, scoped<T>(ctx, *f), r0, r1,
+                                 static_cast<const T*>(hc->wh), hc->minDt, T(hc->alphamin), T(hc->alphamax),
+                                 T(hc->decay_constant));
+             else
+                 LAUNCH_PBC(ctx, *box, avSwitchesKernel, gridFor(last - first, kHydroBlock), first, last, hc->ngmax,
+                            hc->K, pbcBox(*box), neighbors, scoped<T>(ctx, *f), r0, r1, wh, hc->minDt, T(hc->alphamin),
+                            T(hc->alphamax), T(hc->decay_constant));
+             tabLaunched(ctx, TAB_AV););
     SPHB200_CATCH
 }
 
@@ -1408,7 +1772,7 @@ extern "C" int sphb200_momentum_energy(sphb200_ctx* ctx, int dtype, uint32_t fir
         beginOp(ctx);
         if (hc->avClean && !f->dV11) throw std::runtime_error("momentum_energy: avClean requires dV11..dV33");
         DISPATCH(dtype, const Rec2<T>* wh; const Rec4<T>* whq; ensureTables<T>(ctx, hc, wh, whq);
-                 launchMomentum<T>(ctx, first, first, last, true, box, hc, neighbors, f, wh););
+                 launchMomentum<T>(ctx, first, first, last, true, box, hc, neighbors, f, wh, TAB_MOMENTUM););
     }
     if (minDtCourant_h)
     {
@@ -1431,7 +1795,7 @@ extern "C" int sphb200_momentum_energy_range(sphb200_ctx* ctx, int dtype, uint32
     if (end <= begin) return 0;
     beginOp(ctx);
     DISPATCH(dtype, const Rec2<T>* wh; const Rec4<T>* whq; ensureTables<T>(ctx, hc, wh, whq);
-             launchMomentum<T>(ctx, first, begin, end, pack != 0, box, hc, neighbors, f, wh););
+             launchMomentum<T>(ctx, first, begin, end, pack != 0, box, hc, neighbors, f, wh, TAB_MOMENTUM_RANGE););
     SPHB200_CATCH
 }
 
@@ -1447,9 +1811,16 @@ extern "C" int sphb200_av_switches_courant(sphb200_ctx* ctx, int dtype, uint32_t
     DISPATCH(dtype, const Rec2<T>* wh; const Rec4<T>* whq; ensureTables<T>(ctx, hc, wh, whq);
              auto* r0 = static_cast<const PosRec<T>*>(ensureRec<T>(ctx, R_PDIVV, *f));
              auto* r1 = static_cast<const Rec4<T>*>(ensureRec<T>(ctx, R_VV, *f));
-             LAUNCH_PBC(ctx, *box, avSwitchesCourantKernel, gridFor(last - first, kHydroBlock), first, last, hc->ngmax,
-                        hc->K, pbcBox(*box), neighbors, scoped<T>(ctx, *f), r0, r1, wh, hc->minDt, T(hc->alphamin),
-                        T(hc->alphamax), T(hc->decay_constant), float(hc->Kcour), dtKeys(ctx)););
+             if (useSmemTable(ctx, hc, TAB_AVC, last - first))
+                 LAUNCH_PBC_SMEM(ctx, *box, avSwitchesCourantSmemKernel, kAvCourantSmemBlock, last - first, first, last,
+                                 hc->ngmax, hc->K, pbcBox(*box), neighbors, scoped<T>(ctx, *f), r0, r1,
+                                 static_cast<const T*>(hc->wh), hc->minDt, T(hc->alphamin), T(hc->alphamax),
+                                 T(hc->decay_constant), float(hc->Kcour), dtKeys(ctx));
+             else
+                 LAUNCH_PBC(ctx, *box, avSwitchesCourantKernel, gridFor(last - first, kHydroBlock), first, last,
+                            hc->ngmax, hc->K, pbcBox(*box), neighbors, scoped<T>(ctx, *f), r0, r1, wh, hc->minDt,
+                            T(hc->alphamin), T(hc->alphamax), T(hc->decay_constant), float(hc->Kcour), dtKeys(ctx));
+             tabLaunched(ctx, TAB_AVC););
     SPHB200_CATCH
 }
 
