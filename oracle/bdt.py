@@ -3,8 +3,11 @@
 PARITY UNPINNED for the pieces marked (gpu-only): the reference implements them only as CUDA kernels
 (`HydroVeBdtProp` throws on CPUs, ve_hydro_bdt.hpp:118), which cannot run where this oracle is built, and its tests
 hold no golden vectors for them.  They are restated here from the kernel sources, function by function, with the
-file:line each one follows.  Pieces built from host-callable reference functions (positionUpdate, energyUpdate,
-findRungRanges) are pinned through oracle/_ref instead (oracle/ref.py).
+file:line each one follows.  PINNED through oracle/_ref (tests/test_bdt_oracle.py): the per-particle updates built
+from the reference's positionUpdate / energyUpdate, and the time-step hierarchy -- rung_timestep, minimum_group_dt,
+find_rung_ranges are checked against the reference's own sph/ts_rungs.hpp compiled for host memory
+(oracle/ref_bdt.cpp).  What stays sequenced by this module alone: the order in which HydroVeBdtProp calls those pieces
+(ve_hydro_bdt.hpp:280-420: which rungs drift, which advance, when groups are re-extracted).
 
 Only tests/ may import this module.
 """
@@ -122,6 +125,41 @@ class Timestep:
         t.rungRanges = list(self.rungRanges)
         t.dt_m1, t.dt_drift = self.dt_m1.copy(), self.dt_drift.copy()
         return t
+
+
+def sort_group_dt(group_dt, num):
+    """sortGroupDt (ts_rungs.hpp:55-66): group_dt[:num] ascending in place (stable), returns the ordering"""
+    order = np.argsort(group_dt[:num], kind="stable").astype(np.uint32)
+    group_dt[:num] = group_dt[:num][order]
+    return order
+
+
+def rung_timestep(group_dt, num_groups, max_dt):
+    """rungTimestep (ts_rungs.hpp:131-145) with computeMinTimestep (:78-101, fastFraction 0.4) on one rank; sorts
+    group_dt[:num_groups] in place; returns (ordering, Timestep)"""
+    indices = sort_group_dt(group_dt, num_groups)
+    gd = group_dt
+    m0, m1 = gd[0], gd[int(np.float32(0.4) * np.float32(num_groups))]
+    num_rungs = min(int(np.log2(np.float32(m1 / m0))) + 1, MAX_RUNGS)
+    rr = find_rung_ranges(m0, gd[:num_groups], num_rungs)
+    m0 = min(np.float32(max_dt), m0)
+    ts = Timestep()
+    ts.nextDt, ts.totDt = np.float32(m0), np.float32(m0 * np.float32(1 << num_rungs))
+    ts.numRungs, ts.rungRanges = num_rungs, rr
+    return indices, ts
+
+
+def minimum_group_dt(ts, group_dt, num_groups, num_groups_tot):
+    """minimumGroupDt (ts_rungs.hpp:147-157): sorts group_dt[:num_groups] in place, the ordering is continued by a
+    sequence up to num_groups_tot (computeMinTimestep :97); returns (ordering, dt, rungRanges)"""
+    indices = np.concatenate([sort_group_dt(group_dt, num_groups),
+                              np.arange(num_groups, num_groups_tot, dtype=np.uint32)])
+    m0 = group_dt[0]
+    rr = find_rung_ranges(m0, group_dt[:num_groups], MAX_RUNGS)
+    time_left = np.float32(ts.totDt - ts.elapsedDt)
+    substeps_left = (1 << ts.numRungs) - ts.substep
+    dt = min(m0, np.float32(time_left / np.float32(substeps_left)))
+    return indices, dt, rr
 
 
 def find_rung_ranges(min_dt, group_dt, num_rungs):
@@ -289,11 +327,6 @@ class RefBdtSim:
                                    rs.minDt)
 
     # ---- time-step hierarchy
-    def _sort_group_dt(self, num):
-        order = np.argsort(self.group_dt[:num], kind="stable").astype(np.uint32)
-        self.group_dt[:num] = self.group_dt[:num][order]
-        return order
-
     def compute_rungs(self):
         ts = self.ts
         high = active_rung(ts.substep, ts.numRungs)
@@ -301,30 +334,16 @@ class RefBdtSim:
         if high == 0:
             self.prev = ts.copy()
             max_dt = np.float32(ts.dt_m1[0] * np.float32(1.1))
-            # rungTimestep (ts_rungs.hpp:131-145)
             ng = self.groups[0].size
-            indices = self._sort_group_dt(ng)
-            gd = self.group_dt
-            m0, m1 = gd[0], gd[int(np.float32(0.4) * np.float32(ng))]
-            num_rungs = min(int(np.log2(np.float32(m1 / m0))) + 1, MAX_RUNGS)
-            rr = find_rung_ranges(m0, gd[:ng], num_rungs)
-            m0 = min(max_dt, m0)
-            ts = Timestep()
-            ts.nextDt, ts.totDt, ts.numRungs, ts.rungRanges = np.float32(m0), np.float32(m0 * np.float32(1 << num_rungs)), num_rungs, rr
+            indices, ts = rung_timestep(self.group_dt, ng, max_dt)
             if self.safety_steps > 0:
                 ts.numRungs = 1
                 ts.rungRanges[1:] = [ng] * MAX_RUNGS
                 self.safety_steps -= 1
             self.ts = ts
         else:
-            # minimumGroupDt (ts_rungs.hpp:147-157)
             ng = ts.rungRanges[high]
-            indices = np.concatenate([self._sort_group_dt(ng), np.arange(ng, num_tot, dtype=np.uint32)])
-            m0 = self.group_dt[0]
-            rr = find_rung_ranges(m0, self.group_dt[:ng], MAX_RUNGS)
-            time_left = np.float32(ts.totDt - ts.elapsedDt)
-            substeps_left = (1 << ts.numRungs) - ts.substep
-            ts.nextDt = min(m0, np.float32(time_left / np.float32(substeps_left)))
+            indices, ts.nextDt, rr = minimum_group_dt(ts, self.group_dt, ng, num_tot)
             ts.rungRanges[:high] = rr[:high]
         ts = self.ts
         if high == 0 or high > 1:

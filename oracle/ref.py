@@ -293,6 +293,39 @@ def drift(idx, dt, dt_back, dt_m1, rung, x, y, z, vx, vy, vz, x_m1, y_m1, z_m1, 
                                                   C.c_double(mui), C.c_double(gamma))
 
 
+def find_rung_ranges(min_dt, group_dt, num_rungs):
+    """sph::findRungRanges<false> (sph/include/sph/ts_rungs.hpp:115-129) on sorted float32 group_dt"""
+    gd = np.ascontiguousarray(group_dt, np.float32)
+    out = np.zeros(5, np.uint32)
+    lib().ref_find_rung_ranges(C.c_float(min_dt), P(gd), C.c_uint32(gd.size), C.c_int(num_rungs), P(out))
+    return [int(v) for v in out]
+
+
+def rung_timestep(group_dt, max_dt):
+    """sph::rungTimestep (ts_rungs.hpp:131-145), the reference's own code on one rank (oracle/ref_bdt.cpp supplies
+    the five device primitives it calls for host memory).  Returns (sorted group_dt, ordering, nextDt, totDt,
+    numRungs, rungRanges)"""
+    gd = np.ascontiguousarray(group_dt, np.float32).copy()
+    idx = np.zeros(gd.size, np.uint32)
+    next_dt, tot_dt, num_rungs, rr = C.c_float(0), C.c_float(0), C.c_int(0), np.zeros(5, np.uint32)
+    lib().ref_rung_timestep(P(gd), P(idx), C.c_uint32(gd.size), C.c_float(max_dt), C.byref(next_dt), C.byref(tot_dt),
+                            C.byref(num_rungs), P(rr))
+    return gd, idx, np.float32(next_dt.value), np.float32(tot_dt.value), num_rungs.value, [int(v) for v in rr]
+
+
+def minimum_group_dt(tot_dt, elapsed_dt, num_rungs, substep, ts_rung_ranges, group_dt, num_groups):
+    """sph::minimumGroupDt (ts_rungs.hpp:147-157) as HydroVeBdtProp calls it inside a hierarchy
+    (ve_hydro_bdt.hpp:312-313): group_dt[:num_groups] is sorted, the ordering is continued by a sequence up to
+    ts_rung_ranges[4].  Returns (group_dt with its head sorted, ordering, dt, rungRanges)"""
+    gd = np.ascontiguousarray(group_dt, np.float32).copy()
+    tr = np.ascontiguousarray(ts_rung_ranges, np.uint32)
+    idx = np.zeros(max(int(tr[4]), num_groups), np.uint32)
+    dt, rr = C.c_float(0), np.zeros(5, np.uint32)
+    lib().ref_minimum_group_dt(C.c_float(tot_dt), C.c_float(elapsed_dt), C.c_int(num_rungs), C.c_int(substep), P(tr),
+                               P(gd), P(idx), C.c_uint32(num_groups), C.byref(dt), P(rr))
+    return gd, idx, np.float32(dt.value), [int(v) for v in rr]
+
+
 def positions_rung(idx, dt, dt_m1, rung, box, x, y, z, vx, vy, vz, x_m1, y_m1, z_m1, ax, ay, az, temp, du, du_m1, h,
                    mui, gamma):
     """computePositionsKernel (positions_gpu.cu:118-161) for the particles idx"""

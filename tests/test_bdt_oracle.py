@@ -4,7 +4,8 @@ What pins it: ref.positions_rung == the reference's own positionUpdate/energyUpd
 pinned by sph/test and the 3-step goldens) when all rungs are 0; drift obeys the time-reversibility the reference
 documents for positionUpdate (sph/include/sph/positions.hpp:74-75); the all-pairs search equals cstone::findNeighbors
 (findneighbors.hpp:95-165); butterfly / activeRung sequences follow cstone/primitives/math.hpp:26-31 and
-ve_hydro_bdt.hpp:106-110; findRungRanges is std::lower_bound (ts_rungs.hpp:115-129).
+ve_hydro_bdt.hpp:106-110; the time-step hierarchy (rungTimestep, minimumGroupDt, findRungRanges) equals the reference's
+own sph/ts_rungs.hpp run on host memory (oracle/ref_bdt.cpp).
 """
 import numpy as np
 import pytest
@@ -35,6 +36,52 @@ def test_find_rung_ranges_is_lower_bound():
     assert bdt.find_rung_ranges(dt[0], dt, 4) == [0, 3, 6, 8, 10]
     assert bdt.find_rung_ranges(dt[0], dt, 2) == [0, 3, 10, 10, 10]
     assert bdt.find_rung_ranges(dt[0], dt, 1) == [0, 10, 10, 10, 10]
+
+
+def test_find_rung_ranges_equals_reference(ref):
+    from oracle import bdt
+    rng = np.random.Generator(np.random.MT19937(5))
+    for n in (1, 2, 33, 1000):
+        dt = np.sort(np.exp(rng.uniform(np.log(1e-6), np.log(1e-4), n)).astype(np.float32))
+        for num_rungs in (1, 2, 3, 4):
+            assert bdt.find_rung_ranges(dt[0], dt, num_rungs) == ref.find_rung_ranges(dt[0], dt, num_rungs)
+
+
+def test_time_step_hierarchy_equals_reference_ts_rungs(ref):
+    """rung_timestep / minimum_group_dt of the oracle against sph::rungTimestep / sph::minimumGroupDt themselves
+    (ts_rungs.hpp:131-157, compiled with host stand-ins for the five device primitives they call)"""
+    from oracle import bdt
+    rng = np.random.Generator(np.random.MT19937(6))
+    seen_rungs = set()
+    for trial in range(60):
+        n = int(rng.integers(1, 3000))
+        spread = rng.choice([1.5, 3.0, 10.0, 100.0])
+        dt = np.exp(rng.uniform(np.log(1e-6), np.log(1e-6 * spread), n)).astype(np.float32)
+        if n > 10:
+            dt[rng.integers(0, n, n // 8)] = dt[1]  # ties
+        max_dt = np.float32(rng.choice([1.0, float(dt.min()) * 0.7]))
+        w_dt, w_idx, w_next, w_tot, w_rungs, w_rr = ref.rung_timestep(dt, max_dt)
+        gd = dt.copy()
+        idx, ts = bdt.rung_timestep(gd, n, max_dt)
+        assert np.array_equal(gd, w_dt) and np.array_equal(idx, w_idx)
+        assert (ts.nextDt, ts.totDt, ts.numRungs, ts.rungRanges) == (w_next, w_tot, w_rungs, w_rr), trial
+        seen_rungs.add(ts.numRungs)
+        # a substep inside the hierarchy: the groups of the rungs that were due got new time steps
+        for substep in range(1, 1 << (ts.numRungs - 1)):
+            high = bdt.active_rung(substep, ts.numRungs)
+            ng = ts.rungRanges[high]
+            if ng == 0:
+                continue
+            gd2 = gd.copy()
+            gd2[:ng] = (gd2[:ng] * rng.uniform(0.5, 1.5, ng).astype(np.float32))[rng.permutation(ng)]
+            t2 = ts.copy()
+            t2.substep, t2.elapsedDt = substep, np.float32(ts.nextDt * np.float32(substep))
+            w_gd, w_idx2, w_dt2, w_rr2 = ref.minimum_group_dt(t2.totDt, t2.elapsedDt, t2.numRungs, substep,
+                                                              ts.rungRanges, gd2, ng)
+            idx2, dt2, rr2 = bdt.minimum_group_dt(t2, gd2, ng, ts.rungRanges[4])
+            assert np.array_equal(gd2, w_gd) and np.array_equal(idx2, w_idx2[:idx2.size])
+            assert dt2 == w_dt2 and rr2 == w_rr2, (trial, substep)
+    assert seen_rungs == {1, 2, 3, 4}
 
 
 def test_positions_rung_equals_reference_host_path(pkg, ref):

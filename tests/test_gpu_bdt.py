@@ -15,6 +15,37 @@ from conftest import to_dev, to_host, slab_from_rowmajor, rel_err
 pytestmark = pytest.mark.gpu
 
 
+def test_sort_group_dt_and_rung_ranges_equal_reference_hierarchy(pkg, ctx, ref):
+    """sphb200_sort_group_dt + sphb200_rung_ranges against the reference's own rungTimestep / minimumGroupDt
+    (sph/ts_rungs.hpp:131-157 compiled for host memory, oracle/ref_bdt.cpp)"""
+    from sph_exa_b200 import ops
+    rng = np.random.Generator(np.random.MT19937(12))
+    for n in (3, 640, 40_000):
+        dt = np.exp(rng.uniform(np.log(1e-6), np.log(3e-5), n)).astype(np.float32)
+        dt[rng.integers(0, n, n // 10)] = dt[0]
+        want_dt, want_idx, next_dt, tot_dt, num_rungs, want_rr = ref.rung_timestep(dt, 1.0)
+        d = to_dev(dt)
+        idx = to_host(ops.sortGroupDt(ctx, d), np.uint32)
+        assert np.array_equal(idx, want_idx) and np.array_equal(to_host(d), want_dt)
+        _, mdt = ops.rungRanges(ctx, -1.0, d, n, 1)
+        got_rungs = min(int(np.log2(np.float32(mdt[1]) / np.float32(mdt[0]))) + 1, 4)  # api.cu: bdtComputeRungs
+        assert got_rungs == num_rungs and np.float32(mdt[0]) == next_dt
+        rr, _ = ops.rungRanges(ctx, float(mdt[0]), d, n, got_rungs)
+        assert rr == want_rr
+        # inside the hierarchy: the head of the array is sorted again, boundaries for all rungs
+        head = want_rr[2] if want_rr[2] > 2 else n
+        dt2 = want_dt.copy()
+        dt2[:head] = dt2[:head][rng.permutation(head)] * np.float32(0.9)
+        d2 = to_dev(dt2)
+        idx2 = to_host(ops.sortGroupDt(ctx, d2, head), np.uint32)
+        w_dt, w_idx, w_min, w_rr = ref.minimum_group_dt(tot_dt, next_dt, num_rungs, 1, want_rr, dt2, head)
+        assert np.array_equal(idx2, w_idx[:head]) and np.array_equal(to_host(d2), w_dt)
+        rr2, mdt2 = ops.rungRanges(ctx, -1.0, d2, head, 4)
+        assert rr2 == w_rr
+        time_left, substeps_left = np.float32(tot_dt - next_dt), (1 << num_rungs) - 1
+        assert min(np.float32(mdt2[0]), np.float32(time_left / np.float32(substeps_left))) == w_min
+
+
 def test_sort_group_dt_and_rung_ranges(pkg, ctx):
     from oracle import bdt
     from sph_exa_b200 import ops
