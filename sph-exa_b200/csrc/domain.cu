@@ -277,15 +277,13 @@ __global__ void haloBoxesKernel(const KeyType* __restrict__ leaves, const float*
  * (the owner's key range: everything else in its tree is empty).  Leaves that are reached get `bit` or-ed into their
  * mask (flags[leaf] = 1 when mask is NULL); counts != NULL: empty leaves are not marked.
  */
-__global__ void markCollisionsKernel(const KeyType* __restrict__ prefixes, const TreeNodeIndex* __restrict__ childOffsets,
-                                     const TreeNodeIndex* __restrict__ internalToLeaf,
-                                     const uint32_t* __restrict__ counts, const int* __restrict__ boxes, int numBoxes,
-                                     uint32_t bit, KeyType exLo, KeyType exHi, KeyType visitLo, KeyType visitHi,
-                                     uint32_t* __restrict__ mask, int* __restrict__ flags)
+__device__ __forceinline__ void markBox(const KeyType* __restrict__ prefixes,
+                                        const TreeNodeIndex* __restrict__ childOffsets,
+                                        const TreeNodeIndex* __restrict__ internalToLeaf,
+                                        const uint32_t* __restrict__ counts, const int* __restrict__ bx, uint32_t bit,
+                                        KeyType exLo, KeyType exHi, KeyType visitLo, KeyType visitHi,
+                                        uint32_t* __restrict__ mask, int* __restrict__ flags)
 {
-    int k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= numBoxes) return;
-    const int* bx = boxes + size_t(k) * 8;
     IBox target;
     target.lo[0] = bx[0]; target.hi[0] = bx[1]; target.lo[1] = bx[2]; target.hi[1] = bx[3];
     target.lo[2] = bx[4]; target.hi[2] = bx[5];
@@ -320,6 +318,37 @@ __global__ void markCollisionsKernel(const KeyType* __restrict__ prefixes, const
         for (int c = 0; c < 8; ++c)
             if (enters(child + c)) stack[top++] = child + c;
     }
+}
+
+__global__ void markCollisionsKernel(const KeyType* __restrict__ prefixes, const TreeNodeIndex* __restrict__ childOffsets,
+                                     const TreeNodeIndex* __restrict__ internalToLeaf,
+                                     const uint32_t* __restrict__ counts, const int* __restrict__ boxes, int numBoxes,
+                                     uint32_t bit, KeyType exLo, KeyType exHi, KeyType visitLo, KeyType visitHi,
+                                     uint32_t* __restrict__ mask, int* __restrict__ flags)
+{
+    int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= numBoxes) return;
+    markBox(prefixes, childOffsets, internalToLeaf, counts, boxes + size_t(k) * 8, bit, exLo, exHi, visitLo, visitHi,
+            mask, flags);
+}
+
+/*! @brief the boxes of all peers in one launch: block q of the gathered array (stride boxes, boxCount[q] of them valid)
+ *         marks bit q.  One thread walks one box depth-first, so a launch lasts as long as its deepest walk; one launch
+ *         per sender paid that P - 1 times (1.5 ms of an 8-rank sync)
+ */
+__global__ void markCollisionsAllKernel(const KeyType* __restrict__ prefixes,
+                                        const TreeNodeIndex* __restrict__ childOffsets,
+                                        const TreeNodeIndex* __restrict__ internalToLeaf,
+                                        const uint32_t* __restrict__ counts, const int* __restrict__ boxes, int stride,
+                                        int numRanks, int myRank, const uint32_t* __restrict__ boxCount,
+                                        KeyType visitLo, KeyType visitHi, uint32_t* __restrict__ mask)
+{
+    size_t k = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (k >= size_t(stride) * numRanks) return;
+    int q = int(k / stride), b = int(k % stride);
+    if (q == myRank || b >= int(boxCount[q])) return;
+    markBox(prefixes, childOffsets, internalToLeaf, counts, boxes + k * 8, 1u << q, KeyType(0), KeyType(0), visitLo,
+            visitHi, mask, nullptr);
 }
 
 //! @brief per (peer, leaf): does the leaf go to that peer, and with how many particles
@@ -715,6 +744,56 @@ void migrate(Group& g, const std::vector<uint32_t>& matrix)
     }
 }
 
+// ---- SPHB200_SYNC_PROFILE=1: wall time of every stage of a sync (a stream synchronisation closes each one), averaged
+// over the calls after a warm-up of 4 (communicator set-up, arena growth) and printed by rank 0 every 8 calls
+struct SyncProfile
+{
+    bool on = std::getenv("SPHB200_SYNC_PROFILE") != nullptr;
+    std::vector<std::pair<std::string, double>> acc;
+    int calls = 0;
+    double t0 = 0;
+    static double now()
+    {
+        return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
+    }
+    void begin(Group& g)
+    {
+        if (!on) return;
+        for (auto* s : g.sims)
+            syncStream(s);
+        t0 = now();
+    }
+    void tick(Group& g, const char* name)
+    {
+        if (!on) return;
+        for (auto* s : g.sims)
+            syncStream(s);
+        double t = now();
+        if (calls >= 4)
+        {
+            auto it = std::find_if(acc.begin(), acc.end(), [&](auto& e) { return e.first == name; });
+            if (it == acc.end()) acc.emplace_back(name, t - t0);
+            else it->second += t - t0;
+        }
+        t0 = t;
+    }
+    void end(Group& g)
+    {
+        if (!on) return;
+        ++calls;
+        if (g.sims[0]->dist->rank != 0 || calls <= 4 || (calls - 4) % 8 != 0) return;
+        std::string line = "domain sync profile (ms per call over " + std::to_string(calls - 4) + " calls):";
+        for (auto& e : acc)
+        {
+            char buf[96];
+            std::snprintf(buf, sizeof(buf), " %s %.3f |", e.first.c_str(), e.second / (calls - 4));
+            line += buf;
+        }
+        std::fprintf(stderr, "%s\n", line.c_str());
+    }
+};
+SyncProfile gSyncProfile;
+
 // ---- 6. focus tree over the owned keys + halo boxes of the surface leaves
 void focusAndBoxes(sphb200_sim* s, size_t srcOff)
 {
@@ -808,6 +887,7 @@ void discoverHalos(Group& g)
         firstLeaf.push_back(int(s->dist->pinned[OFF_META]));
         lastLeaf.push_back(int(s->dist->pinned[OFF_META + 1]));
     }
+    gSyncProfile.tick(g, "hd: leaf range");
     std::vector<const void*> sendPtr;
     std::vector<void*> recvPtr;
     for (int l = 0; l < g.numLocal(); ++l)
@@ -838,6 +918,7 @@ void discoverHalos(Group& g)
         boxCount[q] = int(g.sims[0]->dist->pinned[OFF_BOXCNT + q]);
         maxBoxes    = std::max(maxBoxes, boxCount[q]);
     }
+    gSyncProfile.tick(g, "hd: boxes + count gather");
     // all-gather of the boxes, padded to the largest count
     size_t blk = size_t(std::max(maxBoxes, 1)) * 8 * sizeof(int);
     sendPtr.clear();
@@ -862,6 +943,7 @@ void discoverHalos(Group& g)
     }
     commAllGather(g.comm, g.rs, sendPtr.data(), recvPtr.data(), blk);
 
+    gSyncProfile.tick(g, "hd: box gather");
 
     // owner-side marking (findCollisions on my own linked octree, one launch per sender) + send lists
     sendPtr.clear();
@@ -874,14 +956,17 @@ void discoverHalos(Group& g)
         int L        = s->focus.numLeaves;
         int me       = d->rank;
         SPHB200_CUDA(cudaMemsetAsync(d->leafMask, 0, size_t(L) * sizeof(uint32_t), ctx->stream));
-        for (int q = 0; q < P; ++q)
-        {
-            if (q == me || boxCount[q] == 0) continue;
-            const int* qBoxes = static_cast<const int*>(d->allBoxArena.ptr) + size_t(q) * stride * 8;
-            SPHB200_LAUNCH(ctx, markCollisionsKernel, gridFor(boxCount[q], 64), 64, 0, d->fPrefixes, d->fChild, d->fI2L,
-                           s->focus.counts, qBoxes, boxCount[q], 1u << q, KeyType(0), KeyType(0), d->bounds[me],
-                           d->bounds[me + 1], d->leafMask, (int*)nullptr);
-        }
+        SPHB200_LAUNCH(ctx, markCollisionsAllKernel, gridFor(size_t(stride) * P, 64), 64, 0, d->fPrefixes, d->fChild,
+                       d->fI2L, s->focus.counts, static_cast<const int*>(d->allBoxArena.ptr), stride, P, me,
+                       d->dSmall + OFF_BOXCNT, d->bounds[me], d->bounds[me + 1], d->leafMask);
+    }
+    gSyncProfile.tick(g, "hd: marking");
+    for (auto* s : g.sims)
+    {
+        DistState* d = s->dist;
+        auto* ctx    = s->ctx;
+        int L        = s->focus.numLeaves;
+        int me       = d->rank;
         // (peer, leaf) flags -> ranges in peer-major order
         size_t PL        = size_t(P) * L;
         auto* base       = static_cast<uint32_t*>(d->listArena.get((4 * PL + 8) * sizeof(uint32_t)));
@@ -902,6 +987,7 @@ void discoverHalos(Group& g)
         sendPtr.push_back(d->dSmall + OFF_HALOCNT);
         recvPtr.push_back(d->dSmall + OFF_HALOMAT);
     }
+    gSyncProfile.tick(g, "hd: send lists");
     commAllGather(g.comm, g.rs, sendPtr.data(), recvPtr.data(), size_t(P + 1) * sizeof(uint32_t));
     for (auto* s : g.sims)
         SPHB200_CUDA(cudaMemcpyAsync(s->dist->pinned + OFF_HALOMAT, s->dist->dSmall + OFF_HALOMAT,
@@ -1080,28 +1166,8 @@ void waitUpload(sphb200_sim* s, int group)
 
 void domainSync(Group& g, SyncStaging* st = nullptr)
 {
-    // SPHB200_SYNC_PROFILE=1: wall time of every stage (a stream synchronisation closes each one), printed by rank 0
-    static const bool profile = std::getenv("SPHB200_SYNC_PROFILE") != nullptr;
-    static double acc[16];
-    static int calls = 0;
-    auto now = []() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
-    double t0 = 0;
-    int stage = 0;
-    auto tick = [&]()
-    {
-        if (!profile) return;
-        for (auto* s : g.sims)
-            syncStream(s);
-        double t = now();
-        acc[stage++] += t - t0;
-        t0 = t;
-    };
-    if (profile)
-    {
-        for (auto* s : g.sims)
-            syncStream(s);
-        t0 = now();
-    }
+    gSyncProfile.begin(g);
+    auto tick = [&](const char* name) { gSyncProfile.tick(g, name); };
     for (auto* s : g.sims)
     {
         s->ctx->packValid = 0;
@@ -1109,14 +1175,14 @@ void domainSync(Group& g, SyncStaging* st = nullptr)
         s->dist->numOwn = s->end - s->start;
     }
     syncBox(g);
-    tick(); // 0 box
+    tick("box");
     for (auto* s : g.sims)
         keysAndSort(s, s->start, s->dist->numOwn);
-    tick(); // 1 keys + sort
+    tick("keys+sort");
     syncGlobalTree(g);
-    tick(); // 2 global tree
+    tick("global tree");
     std::vector<uint32_t> matrix = assign(g);
-    tick(); // 3 assignment
+    tick("assignment");
     uint64_t moved = 0;
     for (int a = 0; a < g.P; ++a)
         for (int q = 0; q < g.P; ++q)
@@ -1132,15 +1198,15 @@ void domainSync(Group& g, SyncStaging* st = nullptr)
     else
         for (auto* s : g.sims)
             s->dist->numMigratedIn = s->dist->numMigratedOut = 0;
-    tick(); // 4 migration
+    tick("migration");
     for (auto* s : g.sims)
     {
         if (st) waitUpload(s, 1); // h
         focusAndBoxes(s, s->start);
     }
-    tick(); // 5 focus tree
+    tick("focus tree");
     discoverHalos(g);
-    tick(); // 6 halo discovery
+    tick("halo discovery");
     for (size_t l = 0; l < g.sims.size(); ++l)
     {
         sphb200_sim* s = g.sims[l];
@@ -1153,29 +1219,17 @@ void domainSync(Group& g, SyncStaging* st = nullptr)
         }
         layoutAndReorder(s, s->start, late);
     }
-    tick(); // 7 layout + reorder
+    tick("layout+reorder");
     const int early[5] = {F_x, F_y, F_z, F_h, F_m};
     exchangeHalos(g, early, 5);
-    tick(); // 8 halo exchange
+    tick("halo x,y,z,h,m");
     for (auto* s : g.sims)
     {
         searchTree(s);
         s->mark(1);
     }
-    tick(); // 9 search tree
-    if (profile && g.sims[0]->dist->rank == 0 && ++calls % 8 == 0)
-    {
-        static const char* names[10] = {"box", "keys+sort", "global tree", "assignment", "migration", "focus tree",
-                                        "halo discovery", "layout+reorder", "halo x,y,z,h,m", "search tree"};
-        std::string line = "domain sync profile (ms per call over " + std::to_string(calls) + " calls):";
-        for (int k = 0; k < 10; ++k)
-        {
-            char buf[64];
-            std::snprintf(buf, sizeof(buf), " %s %.3f |", names[k], acc[k] / calls);
-            line += buf;
-        }
-        std::fprintf(stderr, "%s\n", line.c_str());
-    }
+    tick("search tree");
+    gSyncProfile.end(g);
 }
 
 void domainForces(Group& g)
