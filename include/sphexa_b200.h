@@ -479,6 +479,10 @@ typedef struct sphb200_domain_info_t
     uint64_t haloBytes;       /* bytes sent in halo exchanges since creation */
     uint32_t haloSend[32], haloRecv[32]; /* particles per peer */
     uint64_t assignment[33];  /* SfcAssignment: rank r owns keys [assignment[r], assignment[r+1]) */
+    /* device time of the halo exchanges of the last sync + compute_forces (pack, transfer, unpack; CUDA events on
+     * the rank's stream): [0] x,y,z,h,m inside the sync, [1..4] the exchanges before gradh, IAD, AVswitches and
+     * MomentumEnergy (ve_hydro.hpp:149-192), [5] their sum; 0 before the first step */
+    float haloExchangeMs[6];
 } sphb200_domain_info_t;
 int sphb200_domain_info(const sphb200_sim*, sphb200_domain_info_t* out);
 

@@ -277,13 +277,23 @@ __global__ void haloBoxesKernel(const KeyType* __restrict__ leaves, const float*
  * (the owner's key range: everything else in its tree is empty).  Leaves that are reached get `bit` or-ed into their
  * mask (flags[leaf] = 1 when mask is NULL); counts != NULL: empty leaves are not marked.
  */
+constexpr int kMarkWarps = 4;    // boxes per CTA
+constexpr int kMarkStack = 1280; // node stack per warp (shared memory)
+constexpr int kMarkWide  = 1024; // below this fill four nodes are expanded per step, above it one (plain depth-first)
+
+/*! @brief one warp walks one halo box through the linked octree: up to four nodes are popped per step and their 32
+ *         children tested by the 32 lanes.  A thread per box with a private stack walked a box that overlaps many
+ *         leaves one dependent load after the other, and a launch lasts as long as its longest walk.
+ */
 __device__ __forceinline__ void markBox(const KeyType* __restrict__ prefixes,
                                         const TreeNodeIndex* __restrict__ childOffsets,
                                         const TreeNodeIndex* __restrict__ internalToLeaf,
                                         const uint32_t* __restrict__ counts, const int* __restrict__ bx, uint32_t bit,
                                         KeyType exLo, KeyType exHi, KeyType visitLo, KeyType visitHi,
-                                        uint32_t* __restrict__ mask, int* __restrict__ flags)
+                                        uint32_t* __restrict__ mask, int* __restrict__ flags,
+                                        TreeNodeIndex* __restrict__ stack)
 {
+    const int lane = threadIdx.x & 31;
     IBox target;
     target.lo[0] = bx[0]; target.hi[0] = bx[1]; target.lo[1] = bx[2]; target.hi[1] = bx[3];
     target.lo[2] = bx[4]; target.hi[2] = bx[5];
@@ -299,56 +309,77 @@ __device__ __forceinline__ void markBox(const KeyType* __restrict__ prefixes,
         return overlapIBox(nodeIBox(nodeKey, level), target);
     };
 
-    TreeNodeIndex stack[160];
-    int top = 0;
-    if (!enters(0)) return;
-    stack[top++] = 0;
+    if (!enters(0)) return; // same answer in every lane
+    if (lane == 0) stack[0] = 0;
+    int top = 1;
+    __syncwarp();
     while (top > 0)
     {
-        TreeNodeIndex node  = stack[--top];
-        TreeNodeIndex child = childOffsets[node];
-        if (child == 0)
+        int take = top > kMarkWide ? 1 : min(top, 4);
+        int slot = lane >> 3;
+        TreeNodeIndex node = slot < take ? stack[top - 1 - slot] : -1;
+        __syncwarp();
+        top -= take;
+        bool push       = false;
+        TreeNodeIndex c = 0;
+        if (node >= 0)
         {
-            TreeNodeIndex leaf = internalToLeaf[node];
-            if (counts && counts[leaf] == 0) continue;
-            if (mask) atomicOr(mask + leaf, bit);
-            else flags[leaf] = 1;
-            continue;
+            TreeNodeIndex child = childOffsets[node];
+            if (child == 0)
+            {
+                if ((lane & 7) == 0)
+                {
+                    TreeNodeIndex leaf = internalToLeaf[node];
+                    if (!(counts && counts[leaf] == 0))
+                    {
+                        if (mask) atomicOr(mask + leaf, bit);
+                        else flags[leaf] = 1;
+                    }
+                }
+            }
+            else
+            {
+                c    = child + (lane & 7);
+                push = enters(c);
+            }
         }
-        for (int c = 0; c < 8; ++c)
-            if (enters(child + c)) stack[top++] = child + c;
+        unsigned m = __ballot_sync(0xffffffffu, push);
+        if (push) stack[top + __popc(m & ((1u << lane) - 1))] = c;
+        top += __popc(m);
+        __syncwarp();
     }
 }
 
-__global__ void markCollisionsKernel(const KeyType* __restrict__ prefixes, const TreeNodeIndex* __restrict__ childOffsets,
-                                     const TreeNodeIndex* __restrict__ internalToLeaf,
-                                     const uint32_t* __restrict__ counts, const int* __restrict__ boxes, int numBoxes,
-                                     uint32_t bit, KeyType exLo, KeyType exHi, KeyType visitLo, KeyType visitHi,
-                                     uint32_t* __restrict__ mask, int* __restrict__ flags)
+__global__ void __launch_bounds__(kMarkWarps * 32)
+    markCollisionsKernel(const KeyType* __restrict__ prefixes, const TreeNodeIndex* __restrict__ childOffsets,
+                         const TreeNodeIndex* __restrict__ internalToLeaf, const uint32_t* __restrict__ counts,
+                         const int* __restrict__ boxes, int numBoxes, uint32_t bit, KeyType exLo, KeyType exHi,
+                         KeyType visitLo, KeyType visitHi, uint32_t* __restrict__ mask, int* __restrict__ flags)
 {
-    int k = blockIdx.x * blockDim.x + threadIdx.x;
+    __shared__ TreeNodeIndex stacks[kMarkWarps][kMarkStack];
+    int k = blockIdx.x * kMarkWarps + (threadIdx.x >> 5);
     if (k >= numBoxes) return;
     markBox(prefixes, childOffsets, internalToLeaf, counts, boxes + size_t(k) * 8, bit, exLo, exHi, visitLo, visitHi,
-            mask, flags);
+            mask, flags, stacks[threadIdx.x >> 5]);
 }
 
 /*! @brief the boxes of all peers in one launch: block q of the gathered array (stride boxes, boxCount[q] of them valid)
- *         marks bit q.  One thread walks one box depth-first, so a launch lasts as long as its deepest walk; one launch
- *         per sender paid that P - 1 times (1.5 ms of an 8-rank sync)
+ *         marks bit q (one launch per sender cost P - 1 times the longest walk)
  */
-__global__ void markCollisionsAllKernel(const KeyType* __restrict__ prefixes,
-                                        const TreeNodeIndex* __restrict__ childOffsets,
-                                        const TreeNodeIndex* __restrict__ internalToLeaf,
-                                        const uint32_t* __restrict__ counts, const int* __restrict__ boxes, int stride,
-                                        int numRanks, int myRank, const uint32_t* __restrict__ boxCount,
-                                        KeyType visitLo, KeyType visitHi, uint32_t* __restrict__ mask)
+__global__ void __launch_bounds__(kMarkWarps * 32)
+    markCollisionsAllKernel(const KeyType* __restrict__ prefixes, const TreeNodeIndex* __restrict__ childOffsets,
+                            const TreeNodeIndex* __restrict__ internalToLeaf, const uint32_t* __restrict__ counts,
+                            const int* __restrict__ boxes, int stride, int numRanks, int myRank,
+                            const uint32_t* __restrict__ boxCount, KeyType visitLo, KeyType visitHi,
+                            uint32_t* __restrict__ mask)
 {
-    size_t k = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    __shared__ TreeNodeIndex stacks[kMarkWarps][kMarkStack];
+    size_t k = size_t(blockIdx.x) * kMarkWarps + (threadIdx.x >> 5);
     if (k >= size_t(stride) * numRanks) return;
     int q = int(k / stride), b = int(k % stride);
     if (q == myRank || b >= int(boxCount[q])) return;
     markBox(prefixes, childOffsets, internalToLeaf, counts, boxes + k * 8, 1u << q, KeyType(0), KeyType(0), visitLo,
-            visitHi, mask, nullptr);
+            visitHi, mask, nullptr, stacks[threadIdx.x >> 5]);
 }
 
 //! @brief per (peer, leaf): does the leaf go to that peer, and with how many particles
@@ -794,6 +825,14 @@ struct SyncProfile
 };
 SyncProfile gSyncProfile;
 
+//! @brief arena pointer with half as much again when it has to grow: the sizes of the halo bookkeeping (boxes, send
+//!        lists, exchange buffers) creep up from step to step, and every regrowth is a cudaFree + cudaMalloc in the sync
+inline void* roomy(Arena& a, size_t bytes)
+{
+    if (bytes > a.capacity) a.get(bytes + bytes / 2);
+    return a.ptr;
+}
+
 // ---- 6. focus tree over the owned keys + halo boxes of the surface leaves
 void focusAndBoxes(sphb200_sim* s, size_t srcOff)
 {
@@ -898,7 +937,7 @@ void discoverHalos(Group& g)
         int nl         = lastLeaf[l] - firstLeaf[l];
         d->numFocusLeavesOwned = nl;
         int* dMeta     = reinterpret_cast<int*>(d->dSmall + OFF_META);
-        int* boxes     = static_cast<int*>(d->boxArena.get(size_t(std::max(nl, 1)) * 8 * sizeof(int)));
+        int* boxes     = static_cast<int*>(roomy(d->boxArena, size_t(std::max(nl, 1)) * 8 * sizeof(int)));
         if (nl > 0)
             SPHB200_LAUNCH(ctx, haloBoxesKernel, gridFor(nl, 128), 128, 0, s->focus.leaves, d->radii, firstLeaf[l],
                            lastLeaf[l], s->box, boxes, nl, dMeta + 2);
@@ -931,7 +970,7 @@ void discoverHalos(Group& g)
         if (d->boxArena.capacity < blk)
         {
             Arena bigger;
-            void* p = bigger.get(blk);
+            void* p = bigger.get(blk + blk / 2);
             SPHB200_CUDA(cudaMemcpyAsync(p, d->boxArena.ptr, size_t(boxCount[d->rank]) * 8 * sizeof(int),
                                          cudaMemcpyDeviceToDevice, s->ctx->stream));
             syncStream(s);
@@ -939,7 +978,7 @@ void discoverHalos(Group& g)
             d->boxArena = bigger;
         }
         sendPtr.push_back(d->boxArena.ptr);
-        recvPtr.push_back(d->allBoxArena.get(blk * P));
+        recvPtr.push_back(roomy(d->allBoxArena, blk * P));
     }
     commAllGather(g.comm, g.rs, sendPtr.data(), recvPtr.data(), blk);
 
@@ -956,7 +995,7 @@ void discoverHalos(Group& g)
         int L        = s->focus.numLeaves;
         int me       = d->rank;
         SPHB200_CUDA(cudaMemsetAsync(d->leafMask, 0, size_t(L) * sizeof(uint32_t), ctx->stream));
-        SPHB200_LAUNCH(ctx, markCollisionsAllKernel, gridFor(size_t(stride) * P, 64), 64, 0, d->fPrefixes, d->fChild,
+        SPHB200_LAUNCH(ctx, markCollisionsAllKernel, gridFor(size_t(stride) * P, kMarkWarps), kMarkWarps * 32, 0, d->fPrefixes, d->fChild,
                        d->fI2L, s->focus.counts, static_cast<const int*>(d->allBoxArena.ptr), stride, P, me,
                        d->dSmall + OFF_BOXCNT, d->bounds[me], d->bounds[me + 1], d->leafMask);
     }
@@ -969,7 +1008,7 @@ void discoverHalos(Group& g)
         int me       = d->rank;
         // (peer, leaf) flags -> ranges in peer-major order
         size_t PL        = size_t(P) * L;
-        auto* base       = static_cast<uint32_t*>(d->listArena.get((4 * PL + 8) * sizeof(uint32_t)));
+        auto* base       = static_cast<uint32_t*>(roomy(d->listArena, (4 * PL + 8) * sizeof(uint32_t)));
         uint32_t* flags  = base;
         uint32_t* lens   = base + PL;
         uint32_t* rScan  = base + 2 * PL; // ranges: element prefix
@@ -1067,6 +1106,25 @@ void layoutAndReorder(sphb200_sim* s, size_t srcOff, bool earlyOnly = false)
 }
 
 // ---- haloExchangeGpu (halos/exchange_halos_gpu.cuh:50-143): one pack kernel, one message per peer, one unpack kernel
+//! @brief exchangeHalos bracketed by the events of timer slot `slot` (sphb200_domain_info_t::haloExchangeMs)
+void exchangeHalos(Group& g, const int* ids, int count);
+void exchangeHalosTimed(Group& g, const int* ids, int count, int slot)
+{
+    for (auto* s : g.sims)
+    {
+        DistState* d = s->dist;
+        for (int k = 2 * slot; k < 2 * slot + 2; ++k)
+            if (!d->haloEv[k]) SPHB200_CUDA(cudaEventCreate(&d->haloEv[k]));
+        SPHB200_CUDA(cudaEventRecord(d->haloEv[2 * slot], s->ctx->stream));
+    }
+    exchangeHalos(g, ids, count);
+    for (auto* s : g.sims)
+    {
+        SPHB200_CUDA(cudaEventRecord(s->dist->haloEv[2 * slot + 1], s->ctx->stream));
+        s->dist->haloEvValid[slot] = true;
+    }
+}
+
 void exchangeHalos(Group& g, const int* ids, int count)
 {
     const int P = g.P, NL = g.numLocal();
@@ -1102,8 +1160,8 @@ void exchangeHalos(Group& g, const int* ids, int count)
             so += sb[q];
             ro += rb[q];
         }
-        void* sendBuf = d->sendArena.get(std::max<size_t>(so, 8));
-        void* recvBuf = d->recvArena.get(std::max<size_t>(ro, 8));
+        void* sendBuf = roomy(d->sendArena, std::max<size_t>(so, 8));
+        void* recvBuf = roomy(d->recvArena, std::max<size_t>(ro, 8));
         CHECK_RC(sphb200_pack_ranges_peers(s->ctx, d->dSendScan, d->dSendBegin, d->numSendRanges, P, d->sendCount.data(),
                                            count, src, eb, sendBuf, nullptr));
         sendBase[l] = sendBuf;
@@ -1221,7 +1279,7 @@ void domainSync(Group& g, SyncStaging* st = nullptr)
     }
     tick("layout+reorder");
     const int early[5] = {F_x, F_y, F_z, F_h, F_m};
-    exchangeHalos(g, early, 5);
+    exchangeHalosTimed(g, early, 5, 0);
     tick("halo x,y,z,h,m");
     for (auto* s : g.sims)
     {
@@ -1248,13 +1306,13 @@ void domainForces(Group& g)
     const int ex3[7] = {F_c11, F_c12, F_c13, F_c22, F_c23, F_c33, F_divv};
     const int ex4[1] = {F_alpha};
     phase(0);
-    exchangeHalos(g, ex1, 2);
+    exchangeHalosTimed(g, ex1, 2, 1);
     phase(1);
-    exchangeHalos(g, ex2, 6);
+    exchangeHalosTimed(g, ex2, 6, 2);
     phase(2);
-    exchangeHalos(g, ex3, 7);
+    exchangeHalosTimed(g, ex3, 7, 3);
     phase(3);
-    exchangeHalos(g, ex4, 1);
+    exchangeHalosTimed(g, ex4, 1, 4);
     if (g.sims[0]->cfg.hc.avClean)
     {
         const int ex5[6] = {F_dV11, F_dV12, F_dV13, F_dV22, F_dV23, F_dV33};
@@ -1301,6 +1359,8 @@ void destroyDist(sphb200_sim* s)
     d->recvArena.release(); d->scanArena.release();
     cudaFreeHost(d->pinned);
     cudaFree(d->dSmall);
+    for (auto& e : d->haloEv)
+        if (e) cudaEventDestroy(e);
     delete d;
     s->dist = nullptr;
 }
@@ -1451,6 +1511,17 @@ extern "C" int sphb200_domain_info(const sphb200_sim* s, sphb200_domain_info_t* 
     }
     for (int q = 0; q <= d->P && q < 33; ++q)
         out->assignment[q] = q < int(d->bounds.size()) ? d->bounds[q] : 0;
+    for (int k = 0; k < 5; ++k)
+    {
+        float ms = 0;
+        if (d->haloEvValid[k] && cudaEventSynchronize(d->haloEv[2 * k + 1]) == cudaSuccess &&
+            cudaEventElapsedTime(&ms, d->haloEv[2 * k], d->haloEv[2 * k + 1]) == cudaSuccess)
+        {
+            out->haloExchangeMs[k] = ms;
+            out->haloExchangeMs[5] += ms;
+        }
+    }
+    cudaGetLastError();
     SPHB200_CATCH
 }
 
@@ -1507,7 +1578,7 @@ extern "C" int sphb200_find_halos(sphb200_ctx* ctx, const uint64_t* prefixes, co
     int nb = ctx->hostScalars[0];
     if (numBoxes_h) *numBoxes_h = nb;
     if (nb > 0)
-        SPHB200_LAUNCH(ctx, markCollisionsKernel, gridFor(nb, 64), 64, 0, prefixes, childOffsets, internalToLeaf,
+        SPHB200_LAUNCH(ctx, markCollisionsKernel, gridFor(nb, kMarkWarps), kMarkWarps * 32, 0, prefixes, childOffsets, internalToLeaf,
                        (const uint32_t*)nullptr, boxes, nb, 1u, range[0], range[1], KeyType(0), nodeRange(0),
                        (uint32_t*)nullptr, flags);
     SPHB200_CATCH

@@ -101,6 +101,9 @@ enum Phase { P_sync, P_neighbors, P_xmass, P_gradh, P_eos, P_iad, P_av, P_moment
  */
 struct DistState
 {
+    // halo exchange timers: event pairs around the exchange inside the sync and the four of compute_forces
+    cudaEvent_t haloEv[10] = {};
+    bool haloEvValid[5]    = {};
     sphb200_comm* comm = nullptr;
     int rank = 0, P = 1;
     // SfcAssignment (domaindecomp.hpp:74-113): rank r owns keys [bounds[r], bounds[r+1])

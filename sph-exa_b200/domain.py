@@ -24,7 +24,8 @@ class DomainInfo(C.Structure):
                 ("nWithHalos", C.c_uint32), ("numGlobalLeaves", C.c_int), ("numFocusLeaves", C.c_int),
                 ("numSearchLeaves", C.c_int), ("numSurfaceBoxes", C.c_uint32), ("numSendRanges", C.c_uint32),
                 ("migratedIn", C.c_uint32), ("migratedOut", C.c_uint32), ("haloBytes", C.c_uint64),
-                ("haloSend", C.c_uint32 * 32), ("haloRecv", C.c_uint32 * 32), ("assignment", C.c_uint64 * 33)]
+                ("haloSend", C.c_uint32 * 32), ("haloRecv", C.c_uint32 * 32), ("assignment", C.c_uint64 * 33),
+                ("haloExchangeMs", C.c_float * 6)]
 
 
 lib.sphb200_comm_create_loopback.argtypes = [C.c_int, vp]
@@ -376,7 +377,10 @@ def bench_main(args, pkg, METRIC, UNIT, ALGO_BYTES, load_peaks, ClockSampler):
             "focus_leaves_per_rank": [int(g[2]) for g in gathered],
             "search_tree_leaves_per_rank": [int(g[3]) for g in gathered],
             "halo_boxes_published_per_rank": [int(g[4]) for g in gathered],
-            "halo_bytes_per_step_rank0": halo_bytes, "clocks": clocks, "gpu_launches": launches,
+            "halo_bytes_per_step_rank0": halo_bytes,
+            "halo_exchange_ms_rank0": {k: round(float(v), 4) for k, v in zip(
+                ("sync_xyzhm", "before_gradh", "before_iad", "before_av", "before_momentum", "sum"),
+                sim.info().haloExchangeMs)}, "clocks": clocks, "gpu_launches": launches,
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                          "kernel_ms": phase_ms[dom]},
