@@ -404,7 +404,8 @@ extern "C" int sphb200_restart_open(const char* path, sphb200_restart** out)
     for (auto& b : r->blocks)
     {
         b.name[kNameSize - 1] = 0;
-        if (b.type > T_F32 || b.offset + b.count * typeBytes(b.type) > r->fileSize)
+        // no sums or products of untrusted sizes: they would wrap for a corrupt directory entry
+        if (b.type > T_F32 || b.offset > r->fileSize || b.count > (r->fileSize - b.offset) / typeBytes(b.type))
             throw std::runtime_error(std::string("restart: truncated or corrupt block: ") + b.name);
     }
     *out = r.release();
@@ -464,7 +465,8 @@ extern "C" int sphb200_restart_read_fields(const sphb200_restart* r, uint64_t fi
         if (!dst) continue;
         const BlockHeader* b = r->find(kConserved[k].name, B_FIELD);
         if (!b) throw std::runtime_error(std::string("restart: field missing in ") + r->path + ": " + kConserved[k].name);
-        if (first + count > b->count) throw std::runtime_error(std::string("restart: range beyond the end of field ") + b->name);
+        if (first > b->count || count > b->count - first)
+            throw std::runtime_error(std::string("restart: range beyond the end of field ") + b->name);
         size_t want = (kConserved[k].alwaysF64 || dtype == SPHB200_F64) ? 8 : 4;
         size_t have = typeBytes(b->type);
         if (want == have) { r->read(b->offset + first * have, dst, count * have); }
@@ -498,7 +500,8 @@ extern "C" int sphb200_restart_read_bytes(const sphb200_restart* r, const char* 
     RESTART_TRY
     const BlockHeader* b = r->find(name, B_FIELD);
     if (!b || b->type != T_BYTES) throw std::runtime_error(std::string("restart: field missing in ") + r->path + ": " + name);
-    if (first + count > b->count) throw std::runtime_error(std::string("restart: range beyond the end of field ") + b->name);
+    if (first > b->count || count > b->count - first)
+        throw std::runtime_error(std::string("restart: range beyond the end of field ") + b->name);
     r->read(b->offset + first, out, count);
     RESTART_CATCH
 }
@@ -540,6 +543,27 @@ extern "C" int sphb200_restart_apply(const sphb200_restart* r, sphb200_sim* s)
         std::vector<double> phases(6 * size_t(nm));
         if (sphb200_restart_attribute(r, "turbulence::phases", phases.data(), phases.size()) != int64_t(phases.size()))
             throw std::runtime_error("restart: turbulence::phases has the wrong size");
+        // TurbulenceData::loadOrStore (sph/hydro_turb/turbulence_data.hpp) reloads the forcing constants and the mode
+        // table from the file; here the attached driver was built from the run's settings, so they must be the file's:
+        // a driver with the same number of modes but another spectrum or Mach velocity would resume silently wrong
+        {
+            double have[4], want;
+            std::vector<double> modes(3 * size_t(nm)), amps(1 * size_t(nm)), ph(6 * size_t(nm));
+            std::vector<double> fileModes(modes.size()), fileAmps(amps.size());
+            RESTART_RC(sphb200_turb_get(t, have, modes.data(), amps.data(), ph.data(), nullptr, nullptr));
+            const char* names[4] = {"turbulence::variance", "turbulence::decayTime", "turbulence::solWeight",
+                                    "turbulence::solWeightNorm"};
+            for (int k = 0; k < 4; ++k)
+                if (r->f64(names[k], &want) && want != have[k])
+                    throw std::runtime_error(std::string("restart: ") + names[k] +
+                                             " of the attached turbulence driver differs from the file");
+            bool sameTable =
+                sphb200_restart_attribute(r, "turbulence::modes", fileModes.data(), fileModes.size()) == int64_t(modes.size()) &&
+                sphb200_restart_attribute(r, "turbulence::amplitudes", fileAmps.data(), fileAmps.size()) == int64_t(amps.size()) &&
+                fileModes == modes && fileAmps == amps;
+            if (!sameTable)
+                throw std::runtime_error("restart: mode table of the attached turbulence driver differs from the file");
+        }
         int64_t len = sphb200_restart_attribute(r, "rngEngineState", nullptr, 0);
         if (len <= 0) throw std::runtime_error("restart: rngEngineState missing");
         std::string rng(size_t(len), '\0');

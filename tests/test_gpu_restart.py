@@ -68,6 +68,30 @@ def test_turbulence_restart_carries_the_driver_state(pkg, ctx, tmp_path):
     run_and_compare(pkg, ctx, tmp_path, f, box, s, pkg.F64, before=2, after=3, turb_factory=Turbulence)
 
 
+def test_turbulence_restart_refuses_a_driver_with_other_constants(pkg, ctx, tmp_path):
+    """same number of modes, another Mach velocity: the forcing would resume silently wrong
+    (TurbulenceData::loadOrStore reloads the constants from the file, turbulence_data.hpp:92-115)"""
+    from sph_exa_b200 import sim as S, restart
+    from sph_exa_b200.turbulence import Turbulence
+    f, box, s = pkg.ic.turbulence(16)
+    n = f["x"].size
+    a = S.HydroVeProp(ctx, box, s, capacity=n)
+    ta = Turbulence()
+    a.attachTurbulence(ta)
+    a.upload(f)
+    a.step()
+    path = str(tmp_path / "turb")
+    restart.save(a, path, iteration=1, num_particles_global=n)
+    b = S.HydroVeProp(ctx, box, s, capacity=n)
+    tb = Turbulence(stMachVelocity=0.123)
+    assert tb.numModes == ta.numModes
+    b.attachTurbulence(tb)
+    with pytest.raises(pkg.SphError, match="differs from the file"):
+        restart.load(b, path)
+    for o in (a, b, ta, tb):
+        o.close()
+
+
 def test_restart_into_other_precision(pkg, ctx, tmp_path):
     """an f64 dump starts a mixed-precision run: the reader converts, and the result equals a mixed run started from
     the rounded state"""
