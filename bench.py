@@ -277,7 +277,7 @@ def cpu_baseline(dtype):
                          "particle_steps_per_s": 125000 * 9 / sum(its0[1:])}}
 
 
-NCU_SUMMARY = "ncu_full_r02_summary.csv"  # replaced by this round's capture when it exists
+NCU_SUMMARY = "ncu_full_r02c_summary.csv"  # replaced by this round's capture when it exists
 NCU_KERNEL = {"MomentumAndEnergy": "momentumEnergyKernel", "AVswitches": "avSwitchesKernel",
               "IadVelocityDivCurl": "iadDivvCurlvKernel", "FindNeighbors": "findNeighborsKernel",
               "XMass": "xmassKernel", "Normalization & Gradh": "veDefGradhKernel"}

@@ -133,6 +133,7 @@ extern "C" int sphb200_sim_create(sphb200_ctx* ctx, const sphb200_sim_config* cf
     ctx->packReuse = true;
     ctx->packValid = 0;
     ctx->tabValid  = false;
+    ctx->resetTableTuners(); // a new simulation: time the table variants on its data
     s->cfg      = *cfg;
     s->capacity = cfg->capacity;
     s->box      = cfg->box;

@@ -114,12 +114,22 @@ struct sphb200_ctx
         int pending = -1; // variant whose launch is bracketed by ev[0], ev[1] and not read back yet
         bool closed = false;
         size_t pendingTargets = 0;
+        size_t tunedTargets   = 0; // launch size the decision was taken at
         double perTarget[2] = {0, 0};
         bool smem = false;
         cudaEvent_t ev[2] = {nullptr, nullptr};
     };
     static constexpr int kMaxTabOps = 8;
     TabTune tabTune[kMaxTabOps];
+    //! @brief forget the decisions: the next launches time both variants again (a new simulation uses this context)
+    void resetTableTuners()
+    {
+        for (auto& t : tabTune)
+        {
+            t.phase   = 0;
+            t.pending = -1;
+        }
+    }
     bool hilbertTabReady       = false; // sfc.cu: the 3-level Hilbert transition table is on this device
 };
 

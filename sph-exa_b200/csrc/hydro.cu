@@ -1536,15 +1536,18 @@ static bool useSmemTable(sphb200_ctx* ctx, const sphb200_hydro_const* hc, int op
         else t.phase = 0; // a launch failed in between: measure again
         if (valid && t.pending == 1)
         {
-            t.smem  = t.perTarget[1] < 0.97 * t.perTarget[0];
-            t.phase = 2;
-            t.calls = 0;
+            t.smem         = t.perTarget[1] < 0.97 * t.perTarget[0];
+            t.phase        = 2;
+            t.calls        = 0;
+            t.tunedTargets = t.pendingTargets;
         }
         t.pending = -1;
     }
     if (t.phase == 2)
     {
-        if (++t.calls < kRetuneCalls) return t.smem;
+        // another launch size is another workload (a context can serve several simulations)
+        size_t diff = numTargets > t.tunedTargets ? numTargets - t.tunedTargets : t.tunedTargets - numTargets;
+        if (++t.calls < kRetuneCalls && diff <= t.tunedTargets / 64) return t.smem;
         t.phase = 0;
     }
     for (auto& e : t.ev)
