@@ -244,13 +244,35 @@ __global__ void haloRadiiKernel(const T* __restrict__ h, const uint32_t* __restr
  */
 __global__ void haloBoxesKernel(const KeyType* __restrict__ leaves, const float* __restrict__ radii, int firstLeaf,
                                 int lastLeaf, sphb200_box box, int* __restrict__ boxes, int capacity,
-                                int* __restrict__ numBoxes)
+                                int* __restrict__ numBoxes, const uint32_t* __restrict__ counts, int* __restrict__ extent)
 {
-    int leaf = firstLeaf + blockIdx.x * blockDim.x + threadIdx.x;
-    if (leaf >= lastLeaf) return;
+    int leaf   = firstLeaf + blockIdx.x * blockDim.x + threadIdx.x;
+    bool valid = leaf < lastLeaf;
+    IBox nb;
+    if (valid)
+    {
+        KeyType a = leaves[leaf], b = leaves[leaf + 1];
+        nb = nodeIBox(a, treeLevel(b - a));
+    }
+    if (extent)
+    {
+        // integer bounding box of the non-empty leaves of the range (extent = {xlo, xhi, ylo, yhi, zlo, zhi}, preset to
+        // {INT_MAX, INT_MIN, ...}): a halo box of a peer that misses it needs no walk through this rank's tree
+        bool mine = valid && counts[leaf] > 0;
+#pragma unroll
+        for (int d = 0; d < 3; ++d)
+        {
+            int lo = __reduce_min_sync(0xffffffffu, mine ? nb.lo[d] : INT_MAX);
+            int hi = __reduce_max_sync(0xffffffffu, mine ? nb.hi[d] : INT_MIN);
+            if ((threadIdx.x & 31) == 0 && lo <= hi)
+            {
+                atomicMin(extent + 2 * d, lo);
+                atomicMax(extent + 2 * d + 1, hi);
+            }
+        }
+    }
+    if (!valid) return;
     float radius = radii[leaf];
-    KeyType a = leaves[leaf], b = leaves[leaf + 1];
-    IBox nb = nodeIBox(a, treeLevel(b - a));
     IBox hb;
     constexpr int maxCoord = 1 << kMaxTreeLevel;
 #pragma unroll
@@ -371,13 +393,26 @@ __global__ void __launch_bounds__(kMarkWarps * 32)
                             const TreeNodeIndex* __restrict__ internalToLeaf, const uint32_t* __restrict__ counts,
                             const int* __restrict__ boxes, int stride, int numRanks, int myRank,
                             const uint32_t* __restrict__ boxCount, KeyType visitLo, KeyType visitHi,
-                            uint32_t* __restrict__ mask)
+                            uint32_t* __restrict__ mask, const int* __restrict__ extent)
 {
     __shared__ TreeNodeIndex stacks[kMarkWarps][kMarkStack];
     size_t k = size_t(blockIdx.x) * kMarkWarps + (threadIdx.x >> 5);
     if (k >= size_t(stride) * numRanks) return;
     int q = int(k / stride), b = int(k % stride);
     if (q == myRank || b >= int(boxCount[q])) return;
+    {
+        // most boxes of most peers are nowhere near this rank: test against the extent of its non-empty leaves first
+        const int* bx = boxes + k * 8;
+        IBox target, mine;
+        for (int d = 0; d < 3; ++d)
+        {
+            target.lo[d] = bx[2 * d];
+            target.hi[d] = bx[2 * d + 1];
+            mine.lo[d]   = extent[2 * d];
+            mine.hi[d]   = extent[2 * d + 1];
+        }
+        if (mine.lo[0] > mine.hi[0] || !overlapIBox(mine, target)) return;
+    }
     markBox(prefixes, childOffsets, internalToLeaf, counts, boxes + k * 8, 1u << q, KeyType(0), KeyType(0), visitLo,
             visitHi, mask, nullptr, stacks[threadIdx.x >> 5]);
 }
@@ -899,6 +934,11 @@ __global__ void leafRangeKernel(const KeyType* __restrict__ leaves, int numLeave
     int b  = int(upperBound(leaves, size_t(numLeaves) + 1, hi)) - 1;
     out[1] = max(b, out[0]);
     out[2] = 0; // box counter
+    for (int d = 0; d < 3; ++d)
+    {
+        out[4 + 2 * d] = INT_MAX; // extent of the owned leaves, see haloBoxesKernel
+        out[5 + 2 * d] = INT_MIN;
+    }
 }
 } // namespace sphb200
 
@@ -940,7 +980,7 @@ void discoverHalos(Group& g)
         int* boxes     = static_cast<int*>(roomy(d->boxArena, size_t(std::max(nl, 1)) * 8 * sizeof(int)));
         if (nl > 0)
             SPHB200_LAUNCH(ctx, haloBoxesKernel, gridFor(nl, 128), 128, 0, s->focus.leaves, d->radii, firstLeaf[l],
-                           lastLeaf[l], s->box, boxes, nl, dMeta + 2);
+                           lastLeaf[l], s->box, boxes, nl, dMeta + 2, s->focus.counts, dMeta + 4);
         sendPtr.push_back(dMeta + 2);
         recvPtr.push_back(d->dSmall + OFF_BOXCNT);
     }
@@ -997,7 +1037,8 @@ void discoverHalos(Group& g)
         SPHB200_CUDA(cudaMemsetAsync(d->leafMask, 0, size_t(L) * sizeof(uint32_t), ctx->stream));
         SPHB200_LAUNCH(ctx, markCollisionsAllKernel, gridFor(size_t(stride) * P, kMarkWarps), kMarkWarps * 32, 0, d->fPrefixes, d->fChild,
                        d->fI2L, s->focus.counts, static_cast<const int*>(d->allBoxArena.ptr), stride, P, me,
-                       d->dSmall + OFF_BOXCNT, d->bounds[me], d->bounds[me + 1], d->leafMask);
+                       d->dSmall + OFF_BOXCNT, d->bounds[me], d->bounds[me + 1], d->leafMask,
+                       reinterpret_cast<const int*>(d->dSmall + OFF_META) + 4);
     }
     gSyncProfile.tick(g, "hd: marking");
     for (auto* s : g.sims)
@@ -1569,7 +1610,7 @@ extern "C" int sphb200_find_halos(sphb200_ctx* ctx, const uint64_t* prefixes, co
     int* boxes = reinterpret_cast<int*>(tmp + 64);
     SPHB200_CUDA(cudaMemsetAsync(cnt, 0, sizeof(int), ctx->stream));
     SPHB200_LAUNCH(ctx, haloBoxesKernel, gridFor(nl, 128), 128, 0, leaves, radii, firstLeaf, lastLeaf, *box, boxes, nl,
-                   cnt);
+                   cnt, (const uint32_t*)nullptr, (int*)nullptr);
     uint64_t range[2];
     SPHB200_CUDA(cudaMemcpyAsync(ctx->hostScalars, cnt, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
     SPHB200_CUDA(cudaMemcpyAsync(&range[0], leaves + firstLeaf, sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
