@@ -6,9 +6,10 @@ kernels + integrate) on synthetic Sedov ICs, BASELINE.json's metric.
 
 N = 1: Sedov 200^3 (8.0 M particles, BASELINE.json configs[1]) on one B200.
 N > 1: launched by torchrun, one rank per GPU; the particle set is partitioned by SFC key ranges
-       (sph-exa_b200/dist.py), weak scaling: 200^3 particles per GPU (global lattice side = round(200 * N^(1/3))).
---impl reference: the reference's own OpenMP CPU path (oracle/_ref = the reference headers compiled where they
-       lie) on the host cores of this box, on a bounded sample of the same workload.
+       by the C++ multi-rank domain (sphb200_domain_*, sph-exa_b200/domain.py); weak scaling: 200^3 particles per GPU
+       (global lattice side = round(200 * N^(1/3)), made even).
+--impl reference: the reference's own `sphexa` CPU binary (baseline/_ref/sphexa, built from its sources where they
+       lie) on all host cores of this box, Sedov at --ref-side (200).
 One JSON line on stdout (rank 0).
 """
 import argparse
