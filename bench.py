@@ -30,7 +30,7 @@ UNIT = "particle-steps/s"
 ALGO_BYTES = {
     "domain::sync": (464, 384), "FindNeighbors": (32 + 4, 28 + 4), "XMass": (60, 44),
     "Normalization & Gradh": (64, 44), "EquationOfState": (56, 32), "IadVelocityDivCurl": (136, 80),
-    "AVswitches": (152, 88), "MomentumAndEnergy": (184, 108), "Timestep+UpdateQuantities": (244, 140),
+    "AVswitches": (152, 88), "MomentumAndEnergy": (184, 108), "Timestep+UpdateQuantities": (204, 140),  # f64: 108 B read + 96 B written (positionUpdate rebuilds v from dx / dt_m1)
 }
 
 
