@@ -22,7 +22,7 @@ GROUP_SCALE = {"ax": ("ax", "ay", "az"), "ay": ("ax", "ay", "az"), "az": ("ax", 
                "vx": ("vx", "vy", "vz"), "vy": ("vx", "vy", "vz"), "vz": ("vx", "vy", "vz")}
 
 
-def make_group(pkg, ctx, case, side, P, capacity_factor=3.0, shuffle_seed=None):
+def make_group(pkg, ctx, case, side, P, capacity_factor=3.0, shuffle_seed=None, shares=None):
     from sph_exa_b200 import domain as D
     f, box, s = pkg.ic.CASES[case](side)
     n = f["x"].size
@@ -34,8 +34,9 @@ def make_group(pkg, ctx, case, side, P, capacity_factor=3.0, shuffle_seed=None):
     if shuffle_seed is not None:
         order = np.random.default_rng(shuffle_seed).permutation(n)
     bucket = max(64, n // (100 * P))
+    cuts = [(n * r) // P for r in range(P + 1)] if shares is None else [int(round(n * c)) for c in np.cumsum([0] + shares)]
     for r in range(P):
-        first, last = (n * r) // P, (n * (r + 1)) // P
+        first, last = cuts[r], cuts[r + 1]
         mine = {k: v[order[first:last]] for k, v in f.items()}
         # every virtual rank has its own context (scratch, gather records, time-step scalars) on the shared stream
         rctx = pkg.Context(0)
@@ -117,6 +118,26 @@ def test_migration_from_a_shuffled_start(pkg, ctx, ref):
         group.computeForces()
         rs.computeForces()
         compare(group, rs, FIELDS + ["nc"])
+    finally:
+        group.close()
+        comm.close()
+
+
+def test_ranks_that_start_empty_or_overfull(pkg, ctx, ref):
+    """the file reader of one rank holds everything, another holds nothing: the first sync hands every rank its share
+    (the reference's `domain.sync` accepts any initial distribution, domain.hpp:143-160)"""
+    from oracle.ref_pipeline import RefSim
+    group, comm, f, box, s = make_group(pkg, ctx, "sedov", 20, 3, capacity_factor=3.5, shares=[0.0, 1.0, 0.0])
+    try:
+        rs = RefSim(f, box, s)
+        for _ in range(2):
+            group.step()
+            rs.step()
+        group.computeForces()
+        rs.computeForces()
+        compare(group, rs, FIELDS + ["nc"])
+        own = [i.endIndex - i.startIndex for i in (r.info() for r in group.ranks)]
+        assert min(own) > 0.25 * f["x"].size and sum(own) == f["x"].size
     finally:
         group.close()
         comm.close()
