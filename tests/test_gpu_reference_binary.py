@@ -24,8 +24,8 @@ REF = os.path.join(ROOT, "baseline", "_ref", "sphexa-cuda")
 NUM = r"([-+0-9.eE]+|nan|inf)"
 
 
-def reference_log(side, steps, prop, tmp):
-    res = subprocess.run([REF, "--init", "sedov", "--prop", prop, "-n", str(side), "-s", str(steps), "--ascii"],
+def reference_log(side, steps, prop, tmp, extra=()):
+    res = subprocess.run([REF, "--init", "sedov", "--prop", prop, "-n", str(side), "-s", str(steps), "--ascii", *extra],
                          cwd=tmp, capture_output=True, text=True, timeout=900)
     assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-2000:]
     out = res.stdout
@@ -53,14 +53,15 @@ def close(a, b, rel, floor=0.0):
     return abs(a - b) <= rel * max(abs(a), abs(b)) + floor
 
 
-def test_ve_run_equals_the_reference_application(pkg, ctx, tmp_path):
+@pytest.mark.parametrize("av_clean", [False, True])
+def test_ve_run_equals_the_reference_application(pkg, ctx, tmp_path, av_clean):
     if not os.path.exists(REF):
         pytest.skip("baseline/_ref/sphexa-cuda not built (oracle/build_sphexa_cuda.sh needs /root/reference)")
     from sph_exa_b200 import sim as S
     side, steps = 50, 10
-    ref, _ = reference_log(side, steps, "ve", tmp_path)
+    ref, _ = reference_log(side, steps, "ve", tmp_path, ("--avclean",) if av_clean else ())
     f, box, s = pkg.ic.sedov(side, "mixed")
-    gs = S.HydroVeProp(ctx, box, s, capacity=f["x"].size, dtype=pkg.MIXED)
+    gs = S.HydroVeProp(ctx, box, s, capacity=f["x"].size, dtype=pkg.MIXED, av_clean=av_clean)
     gs.upload(f)
     t = 0.0
     for i, r in enumerate(ref):
