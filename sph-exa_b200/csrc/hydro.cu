@@ -1524,6 +1524,9 @@ static bool useSmemTable(sphb200_ctx* ctx, const sphb200_hydro_const* hc, int op
     int forced = ctx->tabForce >= 0 ? ctx->tabForce : forcedTabVariant();
     if (forced >= 0) return forced == 1;
     if (numTargets < kSmemMinTargets) return false;
+    // launches under an active-target mask (block time steps, partial substeps) are sparse and short: their timings
+    // say nothing about the full launches of the same size, and they are not worth a persistent grid
+    if (ctx->scopeActive) return false;
 
     auto& t = ctx->tabTune[op];
     if (t.pending >= 0)
