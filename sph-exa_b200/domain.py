@@ -333,8 +333,9 @@ def bench_main(args, pkg, METRIC, UNIT, ALGO_BYTES, load_peaks, ClockSampler):
 
         esz = sum(host_in[k].element_size() for k in B.CONSERVED)
         h2d = d2h = 0
-        for it in range(1 + e2e_steps):
-            if it == 1:
+        e2e_warm = 3  # untimed: first touch of the pinned buffers, the timed choice of the kernel-table variants
+        for it in range(e2e_warm + e2e_steps):
+            if it == e2e_warm:
                 barrier()
                 h2d = d2h = 0
                 t0 = time.perf_counter()
