@@ -54,6 +54,9 @@ __global__ void __launch_bounds__(256)
     int maxLevel = 0;
     for (int l = l0; l <= l1; ++l)
     {
+        // only leaves that hold a body of the run count (the reference takes the leaf of each lane's body): an empty
+        // leaf in between can be deeper than all of them when the bucket size is below the run length
+        if (layout[l + 1] == layout[l]) continue;
         KeyType range = leaves[l + 1] - leaves[l];
         int level     = 21 - (63 - int(clz64(range))) / 3;
         maxLevel      = max(maxLevel, level);
