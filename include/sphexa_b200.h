@@ -504,6 +504,84 @@ int sphb200_find_halos(sphb200_ctx*, const uint64_t* prefixes, const int32_t* ch
 int sphb200_halo_radii(sphb200_ctx*, const void* h, int dtype, const uint32_t* layout, int firstLeaf, int lastLeaf,
                        float searchExt, float* radii);
 
+/* ---- a10: the locally essential ("focused") octree: particle counts decide inside the focus key range, a
+ * minimum-distance multipole acceptance criterion (MAC) decides outside (csrc/focus.cu) ----
+ * Tier 1, device arrays of a linked octree as sphb200_build_octree makes them (numNodes = leaves + internal nodes):
+ *
+ * computeMinMacR2 (traversal/macs.hpp:58-71) per node: centers4[4i..4i+2] = geometric center, [4i+3] = squared
+ * acceptance radius (2 max(size) invThetaEff)^2; invThetaEff = 1/theta + 0.5 (invThetaMinMac, macs.hpp:44) */
+int sphb200_min_mac_r2(sphb200_ctx*, const uint64_t* prefixes, int numNodes, float invThetaEff, const sphb200_box* box_h,
+                       double* centers4);
+/* markMacs / markMacsGpu (traversal/macs.hpp:240-264, macs_gpu.cu): markings[i] = 1 iff node i fails evaluateMacPbc
+ * paired with a cell of [focusStart, focusEnd) -- for one spanSfcRange cell of the focus the node and all its
+ * ancestors violate the MAC and none of them lies inside the focus; all other entries are set to 0.  Takes the
+ * `parents` array where the reference's traversal takes childOffsets. */
+int sphb200_mark_macs(sphb200_ctx*, const uint64_t* prefixes, const int32_t* parents, const double* centers4, int numNodes,
+                      const sphb200_box* box_h, uint64_t focusStart, uint64_t focusEnd, char* markings);
+/* rebalanceDecisionEssential[Gpu] (focus/rebalance.hpp:144-160, mergeCountAndMacOp :49-90): nodeOps[i] = 0 merge,
+ * 1 keep, 8 split, for ALL nodes; counts/macs per node */
+int sphb200_rebalance_decision_essential(sphb200_ctx*, const uint64_t* prefixes, const int32_t* childOffsets,
+                                         const int32_t* parents, const uint32_t* counts, const char* macs,
+                                         uint64_t focusStart, uint64_t focusEnd, unsigned bucketSize, int numNodes,
+                                         int32_t* nodeOps);
+/* enforceKeys[Gpu] (focus/rebalance.hpp:189-258): keys (device) that the next tree must contain; cancels merges of
+ * their supporting ancestors and splits the closest leaf by one level.  *status_h = ResolutionStatus: 0 converged,
+ * 1 cancelMerge, 2 rebalance, 3 failed (a key lies more than one level below the closest leaf) */
+int sphb200_enforce_keys(sphb200_ctx*, const uint64_t* keys, int numKeys, const uint64_t* prefixes,
+                         const int32_t* childOffsets, const int32_t* parents, int32_t* nodeOps, int* status_h);
+/* protectAncestors[Gpu] (focus/rebalance.hpp:103-176): a merged node that is the left-most descendant of its closest
+ * non-zero ancestor takes that ancestor's op; *converged_h = 1 if every node ends with op 1 */
+int sphb200_protect_ancestors(sphb200_ctx*, const uint64_t* prefixes, const int32_t* parents, int numNodes,
+                              int32_t* nodeOps, int* converged_h);
+/* findPeersMac (traversal/peers.hpp:63-120), host only: peers_h[r] = 1 for every rank that owns a leaf of the
+ * replicated global tree which fails the mutual min-distance MAC paired with a leaf of myRank's segment (dual
+ * traversal, the reference's split rule); bounds_h = SfcAssignment, numRanks + 1 keys that are leaf keys */
+int sphb200_find_peers_mac(int myRank, int numRanks, const uint64_t* bounds_h, const uint64_t* leaves_h, int numLeaves,
+                           const sphb200_box* box_h, float invThetaEff, int* peers_h);
+
+/* Tier 2: the tree object.  sphb200_focus_update == FocusedOctreeSingleNode::update (focus/octree_focus.hpp:236-266)
+ * = CombinedUpdate::updateFocusGpu (:158-213: decision, enforceKeys on {focusStart, focusEnd, mandatoryKeys},
+ * protectAncestors, rebalanceTree, injectKeys when enforcing failed, linked octree) with the counts and MACs of the
+ * previous call, then MACs (computeMinMacR2 + markMacs) and counts of the new tree from `keys` (sorted, device: ALL
+ * particles the counts shall see).  The three stages are also callable one by one in the order of
+ * FocusedOctree::converge (octree_focus_mpi.hpp:498-516: updateMinMac, updateTree, updateCounts), with
+ * sphb200_focus_set_leaf_counts for counts that were reduced over ranks.  *converged_h = 1 if the tree structure did
+ * not change.  Starts as the root node with count bucketSize + 1 and MAC 1, like the reference. */
+typedef struct sphb200_focus sphb200_focus;
+typedef struct sphb200_focus_view
+{
+    int numLeaves, numNodes;
+    int lastStatus;             /* ResolutionStatus of the last update_tree */
+    const uint64_t* leaves;     /* numLeaves + 1 */
+    const uint32_t* leafCounts; /* numLeaves */
+    const uint64_t* prefixes;   /* linked octree, numNodes */
+    const int32_t *childOffsets, *parents, *levelRange, *internalToLeaf, *leafToInternal;
+    const uint32_t* counts; /* numNodes, NULL while stale */
+    const char* macs;       /* numNodes, NULL while stale */
+    const double* centers;  /* 4 x numNodes, NULL while stale */
+} sphb200_focus_view;
+int sphb200_focus_create(sphb200_ctx*, unsigned bucketSize, float theta, sphb200_focus** out);
+void sphb200_focus_destroy(sphb200_focus*);
+int sphb200_focus_update(sphb200_focus*, const sphb200_box* box_h, const uint64_t* keys, size_t n, uint64_t focusStart,
+                         uint64_t focusEnd, const uint64_t* mandatoryKeys_h, int numMandatory, int* converged_h);
+int sphb200_focus_update_tree(sphb200_focus*, uint64_t focusStart, uint64_t focusEnd, const uint64_t* mandatoryKeys_h,
+                              int numMandatory, int* converged_h);
+int sphb200_focus_update_min_mac(sphb200_focus*, const sphb200_box* box_h, uint64_t focusStart, uint64_t focusEnd);
+int sphb200_focus_update_counts(sphb200_focus*, const uint64_t* keys, size_t n);
+int sphb200_focus_set_leaf_counts(sphb200_focus*, const uint32_t* leafCounts);
+int sphb200_focus_get_view(sphb200_focus*, sphb200_focus_view* out);
+/* The same tree for every rank of a multi-rank domain, on request (the step path does not need it: halo discovery is
+ * owner-side on the guided tree).  One call = one round of what Domain::sync does with its FocusedOctree
+ * (domain.hpp:214-227): findPeersMac on the replicated global tree, updateMinMac, updateTree with the peers' boundaries
+ * enforced, updateCounts with GLOBAL counts (one all-gather of the ranks' leaf arrays, each rank counts its own
+ * particles in all of them, one all-reduce -- in place of the treelet exchange, exchange_focus.hpp:113-198); the first
+ * call iterates until every rank has converged (FocusedOctree::converge, octree_focus_mpi.hpp:498-516).  Collective:
+ * pass the handles as for sphb200_domain_sync, after a sync.  *converged_h = 1 if no rank's tree changed.
+ * sphb200_domain_focus_view: the tree of one rank (device pointers, valid until the next update) and, if peers_h is
+ * not NULL, the numRanks flags of findPeersMac.  focusTransfer (exchange_focus.hpp:219-290) is not carried out. */
+int sphb200_domain_update_focus(sphb200_sim* const* sims, int numLocal, float theta, int* converged_h);
+int sphb200_domain_focus_view(const sphb200_sim*, sphb200_focus_view* out, int* peers_h);
+
 /* ---- f4: restart files ----
  * The reference checkpoints through H5Part/HDF5 (main/src/io/ifile_io_hdf5.cpp, sphexa.cpp:232-246): per dump one
  * "Step#k" group with the step attributes of ParticlesData::loadOrStoreAttributes (sph/particles_data.hpp:142-193),

@@ -452,3 +452,87 @@ def mach(vx, vy, vz, c, num_particles_global):
     out = np.zeros(2)
     fn(P(a[0]), P(a[1]), P(a[2]), P(a[3]), C.c_size_t(c.size), C.c_uint64(num_particles_global), P(out))
     return float(out[0]), float(out[1])
+
+
+# ---- focus tree (oracle/ref_focus.cpp): the reference's own CPU functions -----------------------------------------
+def min_mac_r2(prefixes, inv_theta_eff, box):
+    """computeMinMacR2 (traversal/macs.hpp:58-71) per node: [n, 4] = center, squared acceptance radius"""
+    lim, bc = _box(box)
+    prefixes = np.ascontiguousarray(prefixes, np.uint64)
+    out = np.zeros((prefixes.size, 4), np.float64)
+    lib().ref_min_mac_r2(P(prefixes), prefixes.size, C.c_float(inv_theta_eff), P(lim), P(bc), P(out))
+    return out
+
+
+def mark_macs(tree, centers4, box, focus_start, focus_end):
+    """markMacs (traversal/macs.hpp:240-264) on a linked octree from build_octree: int8 per node"""
+    lim, bc = _box(box)
+    centers4 = np.ascontiguousarray(centers4, np.float64)
+    out = np.zeros(tree["numNodes"], np.int8)
+    lib().ref_mark_macs(P(tree["prefixes"]), P(tree["childOffsets"]), P(tree["parents"]), P(tree["levelRange"]),
+                        P(tree["internalToLeaf"]), P(tree["leafToInternal"]), tree["numLeaves"], tree["numInternal"],
+                        P(centers4), P(lim), P(bc), C.c_uint64(int(focus_start)), C.c_uint64(int(focus_end)), P(out))
+    return out
+
+
+def rebalance_decision_essential(tree, counts, macs, focus_start, focus_end, bucket):
+    counts = np.ascontiguousarray(counts, np.uint32)
+    macs = np.ascontiguousarray(macs, np.int8)
+    ops = np.zeros(tree["numNodes"], np.int32)
+    lib().ref_rebalance_decision_essential(P(tree["prefixes"]), tree["numNodes"], P(tree["childOffsets"]),
+                                           P(tree["parents"]), P(counts), P(macs), C.c_uint64(int(focus_start)),
+                                           C.c_uint64(int(focus_end)), C.c_uint(bucket), P(ops))
+    return ops
+
+
+def enforce_keys(keys, tree, ops):
+    """enforceKeys (focus/rebalance.hpp:245-258): modifies ops in place, returns the ResolutionStatus"""
+    keys = np.ascontiguousarray(keys, np.uint64)
+    assert ops.dtype == np.int32
+    return lib().ref_enforce_keys(P(keys), keys.size, P(tree["prefixes"]), P(tree["childOffsets"]), P(tree["parents"]),
+                                  P(ops))
+
+
+def protect_ancestors(tree, ops):
+    assert ops.dtype == np.int32
+    return bool(lib().ref_protect_ancestors(P(tree["prefixes"]), tree["numNodes"], P(tree["parents"]), P(ops)))
+
+
+class FocusedOctreeSingleNode:
+    """cstone::FocusedOctreeSingleNode<uint64_t> (focus/octree_focus.hpp:219-288), the reference's own class"""
+
+    def __init__(self, bucket, theta):
+        lib().ref_focus_create.restype = C.c_void_p
+        self.h = C.c_void_p(lib().ref_focus_create(C.c_uint(bucket), C.c_float(theta)))
+
+    def update(self, box, keys, focus_start, focus_end, mandatory=()):
+        lim, bc = _box(box)
+        keys = np.ascontiguousarray(keys, np.uint64)
+        mk = np.ascontiguousarray(np.asarray(mandatory, np.uint64))
+        return bool(lib().ref_focus_update(self.h, P(lim), P(bc), P(keys), C.c_size_t(keys.size),
+                                           C.c_uint64(int(focus_start)), C.c_uint64(int(focus_end)),
+                                           P(mk) if mk.size else None, mk.size))
+
+    def leaves_counts(self):
+        n = lib().ref_focus_num_leaves(self.h)
+        leaves = np.zeros(n + 1, np.uint64)
+        counts = np.zeros(n, np.uint32)
+        lib().ref_focus_get(self.h, P(leaves), P(counts))
+        return leaves, counts
+
+    def __del__(self):
+        try:
+            lib().ref_focus_destroy(self.h)
+        except Exception:  # noqa: BLE001
+            pass
+
+
+def find_peers_mac(rank, bounds, leaves, box, inv_theta_eff):
+    """findPeersMac (traversal/peers.hpp:63-120): list of peer ranks"""
+    lim, bc = _box(box)
+    bounds = np.ascontiguousarray(bounds, np.uint64)
+    leaves = np.ascontiguousarray(leaves, np.uint64)
+    peers = np.zeros(bounds.size - 1, np.int32)
+    lib().ref_find_peers_mac(rank, bounds.size - 1, P(bounds), P(leaves), leaves.size - 1, P(lim), P(bc),
+                             C.c_float(inv_theta_eff), P(peers))
+    return np.nonzero(peers)[0].tolist()

@@ -130,6 +130,11 @@ SYMBOLS = [
     "sphb200_domain_exchange_halos", "sphb200_domain_compute_forces", "sphb200_domain_integrate", "sphb200_domain_step",
     "sphb200_domain_conserved", "sphb200_domain_set_halo_factor", "sphb200_domain_info", "sphb200_sfc_assignment",
     "sphb200_initial_global_tree", "sphb200_find_halos", "sphb200_halo_radii", "sphb200_domain_step_host",
+    "sphb200_min_mac_r2", "sphb200_mark_macs", "sphb200_rebalance_decision_essential", "sphb200_enforce_keys",
+    "sphb200_protect_ancestors", "sphb200_find_peers_mac", "sphb200_focus_create", "sphb200_focus_destroy",
+    "sphb200_focus_update", "sphb200_focus_update_tree", "sphb200_focus_update_min_mac", "sphb200_focus_update_counts",
+    "sphb200_focus_set_leaf_counts", "sphb200_focus_get_view", "sphb200_domain_update_focus",
+    "sphb200_domain_focus_view",
 ]
 
 lib.sphb200_last_error.restype = C.c_char_p

@@ -1398,6 +1398,8 @@ void destroyDist(sphb200_sim* s)
     cudaFree(d->fL2I); cudaFree(d->fLayout); cudaFree(d->keysTmp); cudaFree(d->leafMask); cudaFree(d->radii);
     d->boxArena.release(); d->allBoxArena.release(); d->listArena.release(); d->sendArena.release();
     d->recvArena.release(); d->scanArena.release();
+    if (d->macTree) sphb200_focus_destroy(d->macTree);
+    d->macSend.release(); d->macRecv.release(); d->macCounts.release();
     cudaFreeHost(d->pinned);
     cudaFree(d->dSmall);
     for (auto& e : d->haloEv)
@@ -1518,6 +1520,162 @@ extern "C" int sphb200_domain_conserved(sphb200_sim* const* sims, int numLocal, 
     syncStream(s0);
     for (int k = 0; k < 10; ++k)
         out10_h[k] = s0->ctx->hostDt[8 + k];
+    SPHB200_CATCH
+}
+
+// ---- a10: the locally essential tree of every rank, MAC-coarsened outside its key range -------------------------
+namespace
+{
+
+//! @brief out[0 .. stride) = leaves[0 .. numKeys) followed by 2^63 (a block of equal length for the all-gather)
+__global__ void padLeavesKernel(const uint64_t* __restrict__ leaves, int numKeys, int stride, uint64_t* __restrict__ out)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < stride) out[i] = i < numKeys ? leaves[i] : nodeRange(0);
+}
+
+/*! @brief one round of FocusedOctree::converge (focus/octree_focus_mpi.hpp:498-516) as Domain::sync runs it
+ *         (domain.hpp:216-227): updateMinMac, updateTree with the boundaries of the MAC peers enforced, updateCounts
+ *
+ * updateCounts in the reference: own leaves are counted locally, the leaves in a peer's range are counted by that
+ * peer (treelet exchange, exchange_focus.hpp:113-198), everything else is looked up in the replicated global tree.
+ * Here every rank's leaf array goes to every rank in ONE all-gather (a few MB over NVLink), each rank counts its own
+ * particles in all of them with one launch, and one all-reduce sums the counts: every leaf of every rank's tree
+ * gets its exact global count, also outside the peers' ranges.
+ */
+bool updateMacFocusOnce(Group& g, float theta)
+{
+    const int P       = g.P;
+    float invThetaEff = 1.0f / theta + 0.5f; // invThetaMinMac (traversal/macs.hpp:44)
+    std::vector<const void*> sendPtr;
+    std::vector<void*> recvPtr;
+    std::vector<int> converged(g.numLocal(), 0);
+    for (int l = 0; l < g.numLocal(); ++l)
+    {
+        sphb200_sim* s = g.sims[l];
+        DistState* d   = s->dist;
+        if (int(d->bounds.size()) != P + 1 || d->gLeavesH.empty())
+            throw std::runtime_error("domain_update_focus: call sphb200_domain_sync first");
+        if (d->macTree && d->macTheta != theta)
+        {
+            sphb200_focus_destroy(d->macTree);
+            d->macTree = nullptr;
+        }
+        if (!d->macTree)
+        {
+            CHECK_RC(sphb200_focus_create(s->ctx, s->cfg.bucketSizeFocus, theta, &d->macTree));
+            d->macTheta = theta;
+            d->macFirst = true;
+        }
+        uint64_t focusStart = d->bounds[d->rank], focusEnd = d->bounds[d->rank + 1];
+        if (focusEnd <= focusStart) throw std::runtime_error("domain_update_focus: rank without a key range");
+        // peers: data identical on all ranks, no communication (domain.hpp:216-217)
+        d->macPeers.assign(P, 0);
+        CHECK_RC(sphb200_find_peers_mac(d->rank, P, d->bounds.data(), d->gLeavesH.data(), int(d->gLeavesH.size()) - 1,
+                                        &s->box, invThetaEff, d->macPeers.data()));
+        std::vector<uint64_t> enforced;
+        for (int q = 0; q < P; ++q)
+            if (d->macPeers[q])
+            {
+                enforced.push_back(d->bounds[q]);
+                enforced.push_back(d->bounds[q + 1]);
+            }
+        CHECK_RC(sphb200_focus_update_min_mac(d->macTree, &s->box, focusStart, focusEnd));
+        CHECK_RC(sphb200_focus_update_tree(d->macTree, focusStart, focusEnd, enforced.data(), int(enforced.size()),
+                                           &converged[l]));
+        sphb200_focus_view v;
+        CHECK_RC(sphb200_focus_get_view(d->macTree, &v));
+        d->pinned[OFF_META + 8] = uint32_t(v.numLeaves);
+        d->pinned[OFF_META + 9] = uint32_t(converged[l]);
+        SPHB200_CUDA(cudaMemcpyAsync(d->dSmall + OFF_META + 8, d->pinned + OFF_META + 8, 2 * sizeof(uint32_t),
+                                     cudaMemcpyHostToDevice, s->ctx->stream));
+        sendPtr.push_back(d->dSmall + OFF_META + 8);
+        recvPtr.push_back(d->dSmall + OFF_HALOMAT); // free between syncs: P x {numLeaves, converged}
+    }
+    commAllGather(g.comm, g.rs, sendPtr.data(), recvPtr.data(), 2 * sizeof(uint32_t));
+    for (auto* s : g.sims)
+        SPHB200_CUDA(cudaMemcpyAsync(s->dist->pinned + OFF_HALOMAT, s->dist->dSmall + OFF_HALOMAT,
+                                     size_t(2 * P) * sizeof(uint32_t), cudaMemcpyDeviceToHost, s->ctx->stream));
+    for (auto* s : g.sims)
+        syncStream(s);
+    int maxLeaves = 0, numConverged = 0;
+    for (int q = 0; q < P; ++q)
+    {
+        maxLeaves = std::max(maxLeaves, int(g.sims[0]->dist->pinned[OFF_HALOMAT + 2 * q]));
+        numConverged += int(g.sims[0]->dist->pinned[OFF_HALOMAT + 2 * q + 1]);
+    }
+    const int stride = maxLeaves + 1;
+
+    sendPtr.clear();
+    recvPtr.clear();
+    for (auto* s : g.sims)
+    {
+        DistState* d = s->dist;
+        sphb200_focus_view v;
+        CHECK_RC(sphb200_focus_get_view(d->macTree, &v));
+        auto* send = static_cast<uint64_t*>(d->macSend.get(size_t(stride) * sizeof(uint64_t)));
+        SPHB200_LAUNCH(s->ctx, padLeavesKernel, gridFor(stride, 256), 256, 0, v.leaves, v.numLeaves + 1, stride, send);
+        sendPtr.push_back(send);
+        recvPtr.push_back(d->macRecv.get(size_t(stride) * P * sizeof(uint64_t)));
+    }
+    commAllGather(g.comm, g.rs, sendPtr.data(), recvPtr.data(), size_t(stride) * sizeof(uint64_t));
+    std::vector<void*> countPtr;
+    for (auto* s : g.sims)
+    {
+        DistState* d = s->dist;
+        auto* counts = static_cast<uint32_t*>(d->macCounts.get(size_t(stride) * P * sizeof(uint32_t)));
+        // the P padded leaf arrays as one array of P * stride - 1 key intervals: the interval between two blocks
+        // (2^63 followed by 0) yields a meaningless number in a slot nobody reads
+        CHECK_RC(sphb200_node_counts(s->ctx, static_cast<const uint64_t*>(d->macRecv.ptr), stride * P - 1,
+                                     s->keys + s->start, size_t(s->end - s->start), counts));
+        SPHB200_CUDA(cudaMemsetAsync(counts + size_t(stride) * P - 1, 0, sizeof(uint32_t), s->ctx->stream));
+        countPtr.push_back(counts);
+    }
+    commAllReduce(g.comm, g.rs, countPtr.data(), size_t(stride) * P, COMM_U32, COMM_SUM);
+    for (auto* s : g.sims)
+    {
+        DistState* d = s->dist;
+        CHECK_RC(sphb200_focus_set_leaf_counts(d->macTree,
+                                               static_cast<const uint32_t*>(d->macCounts.ptr) + size_t(stride) * d->rank));
+    }
+    return numConverged == P;
+}
+
+} // namespace
+
+extern "C" int sphb200_domain_update_focus(sphb200_sim* const* sims, int numLocal, float theta, int* converged_h)
+{
+    SPHB200_TRY
+    Group g = makeGroup(sims, numLocal);
+    if (!(theta > 0)) throw std::runtime_error("domain_update_focus: theta must be positive");
+    bool first = false;
+    for (auto* s : g.sims)
+        first = first || !s->dist->macTree || s->dist->macTheta != theta || s->dist->macFirst;
+    bool converged = updateMacFocusOnce(g, theta);
+    if (first)
+    {
+        // firstCall_: FocusedOctree::converge (domain.hpp:219-223), every rank iterates until all have converged
+        int guard = 0;
+        while (!converged)
+        {
+            converged = updateMacFocusOnce(g, theta);
+            if (++guard > 64) throw std::runtime_error("domain_update_focus: the focus trees do not converge");
+        }
+        for (auto* s : g.sims)
+            s->dist->macFirst = false;
+    }
+    if (converged_h) *converged_h = converged ? 1 : 0;
+    SPHB200_CATCH
+}
+
+extern "C" int sphb200_domain_focus_view(const sphb200_sim* s, sphb200_focus_view* out, int* peers_h)
+{
+    SPHB200_TRY
+    if (!s->dist || !s->dist->macTree) throw std::runtime_error("domain_focus_view: call sphb200_domain_update_focus first");
+    CHECK_RC(sphb200_focus_get_view(s->dist->macTree, out));
+    if (peers_h)
+        for (int q = 0; q < s->dist->P; ++q)
+            peers_h[q] = s->dist->macPeers[q];
     SPHB200_CATCH
 }
 

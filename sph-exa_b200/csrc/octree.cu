@@ -258,6 +258,11 @@ void updateOctreeGuided(sphb200_ctx* ctx, const KeyType* keys, size_t n, unsigne
     updateOctreeImpl(ctx, keys, n, bucket, leaves, counts, capacity, numLeaves, converged, guide, numGuide, forced);
 }
 
+void rebalanceTree(sphb200_ctx* ctx, const KeyType* oldLeaves, const uint32_t* opScan, int numLeaves, KeyType* newLeaves)
+{
+    SPHB200_LAUNCH(ctx, processNodesKernel, gridFor(numLeaves + 1, 256), 256, 0, oldLeaves, opScan, numLeaves, newLeaves);
+}
+
 void initRootTree(sphb200_ctx* ctx, KeyType* leaves, uint32_t* counts, uint32_t n)
 {
     SPHB200_LAUNCH(ctx, initRootKernel, 1, 1, 0, leaves, counts, n);

@@ -13,6 +13,9 @@ void radixSortPairs(sphb200_ctx* ctx, KeyType* keys, uint32_t* vals, size_t n, b
 void updateOctreeGuided(sphb200_ctx* ctx, const KeyType* keys, size_t n, unsigned bucket, KeyType* leaves,
                         uint32_t* counts, int capacity, int* numLeaves, int* converged, const KeyType* guide,
                         int numGuide, int* forced);
+//! @brief rebalanceTree (tree/csarray.hpp:390-415): emit the leaves of old leaf i at opScan[i]; opScan = exclusive scan
+//!        of the per-leaf ops {0, 1, 8, 64, ...} with numLeaves + 1 entries
+void rebalanceTree(sphb200_ctx* ctx, const KeyType* oldLeaves, const uint32_t* opScan, int numLeaves, KeyType* newLeaves);
 //! @brief leaves = {0, 2^63}, counts = {n}
 void initRootTree(sphb200_ctx* ctx, KeyType* leaves, uint32_t* counts, uint32_t n);
 } // namespace sphb200

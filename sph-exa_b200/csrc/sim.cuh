@@ -134,6 +134,13 @@ struct DistState
     uint64_t haloBytes = 0;
     uint32_t numSurfaceBoxes = 0, numMigratedOut = 0, numMigratedIn = 0;
     int numFocusLeavesOwned = 0;
+    // the reference-style focus tree (focus.cu; MAC-coarsened outside the own key range), built on request by
+    // sphb200_domain_update_focus
+    sphb200_focus* macTree = nullptr;
+    float macTheta         = 0;
+    bool macFirst          = true;
+    std::vector<int> macPeers;
+    sphb200::Arena macSend, macRecv, macCounts;
     static constexpr int kPinnedInts = 8192;
 };
 

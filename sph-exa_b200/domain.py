@@ -45,6 +45,8 @@ lib.sphb200_sfc_assignment.argtypes = [C.c_int, vp, vp, C.c_int, vp, vp, vp]
 lib.sphb200_initial_global_tree.argtypes = [C.c_int, vp, C.c_int]
 lib.sphb200_find_halos.argtypes = [vp, vp, vp, vp, vp, vp, vp, C.c_int, C.c_int, vp, vp]
 lib.sphb200_halo_radii.argtypes = [vp, vp, C.c_int, vp, C.c_int, C.c_int, C.c_float, vp]
+lib.sphb200_domain_update_focus.argtypes = [vp, C.c_int, C.c_float, vp]
+lib.sphb200_domain_focus_view.argtypes = [vp, vp, vp]
 
 
 class Comm:
@@ -100,6 +102,16 @@ class DomainRank(HydroVeProp):
     def setHaloFactor(self, f):
         lib.sphb200_domain_set_halo_factor(self.h, C.c_float(f))
 
+    def focusTree(self):
+        """(leaves, leaf counts, peer ranks) of this rank's MAC-coarsened focus tree (after DistHydroVe.updateFocus)"""
+        from .focus import FocusView
+        v = FocusView()
+        peers = (C.c_int * self._comm.num_ranks)()
+        check(lib.sphb200_domain_focus_view(self.h, C.byref(v), peers))
+        leaves = self._d2h(v.leaves, v.numLeaves + 1, np.uint64)
+        counts = self._d2h(v.leafCounts, v.numLeaves, np.uint32)
+        return leaves, counts, [q for q in range(self._comm.num_ranks) if peers[q]]
+
 
 class DistHydroVe:
     """HydroVeProp over the ranks this process drives (one with NCCL, all P with the loopback transport)"""
@@ -120,6 +132,13 @@ class DistHydroVe:
 
     def step(self):
         check(lib.sphb200_domain_step(self._arr, self.n))
+
+    def updateFocus(self, theta=1.0):
+        """one round of the reference's focus-tree update on every rank (sphb200_domain_update_focus); the default
+        theta is the reference's without self-gravity (sphexa.cpp:127)"""
+        conv = C.c_int(0)
+        check(lib.sphb200_domain_update_focus(self._arr, self.n, C.c_float(theta), C.byref(conv)))
+        return bool(conv.value)
 
     def exchangeHalos(self, names):
         ids = (C.c_int * len(names))(*[FIELD_ID[n] for n in names])
