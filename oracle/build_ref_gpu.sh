@@ -1,6 +1,6 @@
 #!/bin/bash
 # TEST INFRASTRUCTURE: baseline/_ref/libsphexa_ref_gpu.so = the reference's GPU-only block-time-step group kernels
-# (sph/include/sph/ts_groups.cu, cstone/traversal/groups.cuh) compiled for sm_100a from the sources where they lie,
+# (sph/include/sph/ts_groups.cu, cstone/traversal/groups.cuh; cstone/primitives/primitives_gpu.cu for the scans they call) compiled for sm_100a from the sources where they lie,
 # behind the C veneer oracle/ref_gpu_wrap.cu.  Loaded by tests/test_gpu_reference_kernels.py only.
 set -e
 REF=${REF:-/root/reference}
@@ -15,6 +15,6 @@ $NVCC -std=c++17 -O3 -DNDEBUG -DUSE_CUDA -w -gencode arch=compute_100a,code=sm_1
   --extended-lambda -ccbin /usr/bin/g++ -Xcompiler -fPIC -Xcompiler -fopenmp -shared -include map -include sstream \
   -I"$OUT/overlay_gpu" -I"$HERE/sphexa_cpu" -I"$REF/domain/include" -I"$REF/sph/include" -I"$REF/sph/include/sph" \
   -I"$REF/ryoanji/src" -I"$REF/physics/cooling/include" -I"$REF/main/src" \
-  "$HERE/ref_gpu_wrap.cu" "$REF/sph/include/sph/ts_groups.cu" -o "$OUT/libsphexa_ref_gpu.so"
+  "$HERE/ref_gpu_wrap.cu" "$REF/sph/include/sph/ts_groups.cu" "$REF/domain/include/cstone/primitives/primitives_gpu.cu" -o "$OUT/libsphexa_ref_gpu.so"
 rm -rf "$OUT/overlay_gpu"
 ls -la "$OUT/libsphexa_ref_gpu.so"
