@@ -739,6 +739,25 @@ extern "C" int sphb200_find_peers_mac(int myRank, int numRanks, const uint64_t* 
         peers_h[r] = 0;
     if (domainEnd <= domainStart) return 0;
     HostOctree tree(leaves_h, numLeaves);
+    const int numNodes = int(tree.start.size());
+    // geometry and the ranks each node touches, once per node (the reference recomputes them for every pair)
+    std::vector<GeoBox> geo(numNodes);
+    std::vector<int> rankLo(numNodes), rankHi(numNodes);
+    auto findRank = [&](KeyType key) // SfcAssignment::findRank (domaindecomp.hpp:104-108)
+    { return int(std::upper_bound(bounds_h, bounds_h + numRanks + 1, key) - bounds_h) - 1; };
+    for (int i = 0; i < numNodes; ++i)
+    {
+        geo[i]    = nodeGeometry(tree.start[i], unsigned(tree.level[i]), box);
+        rankLo[i] = findRank(tree.start[i]);
+        rankHi[i] = std::min(findRank(tree.codeEnd(i) - 1), numRanks - 1);
+    }
+    // a pair whose source only touches ranks that are peers already cannot change the result: not followed
+    auto allMarked = [&](int b)
+    {
+        for (int r = rankLo[b]; r <= rankHi[b]; ++r)
+            if (r != myRank && !peers_h[r]) return false;
+        return true;
+    };
 
     // crossFocusPairs (peers.hpp:72-86): continue while a touches the own segment, b is not inside it and the pair
     // fails the mutual min-distance MAC
@@ -747,16 +766,10 @@ extern "C" int sphb200_find_peers_mac(int myRank, int numRanks, const uint64_t* 
         bool aFocusOverlap = domainEnd > tree.start[a] && tree.codeEnd(a) > domainStart;
         bool bInFocus      = !(tree.start[b] < domainStart || tree.codeEnd(b) > domainEnd);
         if (!aFocusOverlap || bInFocus) return false;
-        GeoBox A = nodeGeometry(tree.start[a], unsigned(tree.level[a]), box);
-        GeoBox B = nodeGeometry(tree.start[b], unsigned(tree.level[b]), box);
-        return !minVecMacMutual(A, B, box, invThetaEff);
+        if (allMarked(b)) return false;
+        return !minVecMacMutual(geo[a], geo[b], box, invThetaEff);
     };
-    auto p2p = [&](int b)
-    {
-        // SfcAssignment::findRank (domaindecomp.hpp:104-108)
-        int r      = int(std::upper_bound(bounds_h, bounds_h + numRanks + 1, tree.start[b]) - bounds_h) - 1;
-        peers_h[r] = 1;
-    };
+    auto p2p = [&](int b) { peers_h[rankLo[b]] = 1; };
 
     std::vector<KeyType> span(512);
     int numSpan = sphb200_span_sfc_range(domainStart, domainEnd, span.data(), span.size());

@@ -5,7 +5,8 @@
 
 Every rank advances its SFC partition through sphb200_domain_* with the NCCL transport and compares its owned
 particles with the matching key range of the reference's single-rank CPU run (oracle/_ref, RefSim): keys and neighbor
-counts exactly, fields <= 1e-10.  Also: sphb200_domain_step_host == upload + step + download.
+counts exactly, fields <= 1e-10.  Also: the rank's MAC-coarsened focus tree == cstone::FocusedOctreeSingleNode on the
+global particle set, and sphb200_domain_step_host == upload + step + download.
 """
 import argparse
 import os
@@ -81,6 +82,37 @@ def main():
     if int(cnt.item()) != n:
         ok = False
         print(f"[rank {rank}] particles lost: {int(cnt.item())} != {n}", flush=True)
+
+    # the reference-style focus tree of this rank (sphb200_domain_update_focus: all-gather + all-reduce over NCCL)
+    # == cstone::FocusedOctreeSingleNode converged on the global particle set for this rank's segment and peers
+    from oracle import ref
+    from sph_exa_b200 import focus as F
+    theta = 1.0
+    group.sync()
+    if not group.updateFocus(theta):
+        ok = False
+        print(f"[rank {rank}] focus trees not converged after the first update", flush=True)
+    leaves, counts, peers = sim.focusTree()
+    parts = [None] * world
+    dist.all_gather_object(parts, sim.download(names=["x"], with_keys=True)["keys"])
+    gkeys = np.concatenate(parts)
+    info = sim.info()
+    bounds = np.array(info.assignment[:world + 1], np.uint64)
+    gbox = (sim.boxLimits(), list(box[1]))
+    want_peers = ref.find_peers_mac(rank, bounds, sim.globalLeaves(), gbox, F.invThetaMinMac(theta))
+    mand = np.array([bounds[p + d] for p in peers for d in (0, 1)], np.uint64)
+    theirs = ref.FocusedOctreeSingleNode(64, theta)
+    for _ in range(40):
+        if theirs.update(gbox, gkeys, bounds[rank], bounds[rank + 1], mand):
+            break
+    wl, wc = theirs.leaves_counts()
+    if peers != want_peers or not np.array_equal(leaves, wl) or not np.array_equal(counts, wc):
+        ok = False
+        print(f"[rank {rank}] focus tree differs from the reference: {leaves.size - 1} vs {wl.size - 1} leaves, peers "
+              f"{peers} vs {want_peers}", flush=True)
+    elif rank == 0:
+        print(f"focus tree of rank 0: {leaves.size - 1} leaves (guided tree: {info.numFocusLeaves}), peers {peers}",
+              flush=True)
 
     # host-resident step == upload + step + download
     state = sim.download()
