@@ -1,10 +1,12 @@
 """TEST INFRASTRUCTURE ONLY -- numpy restatement of the block-time-step building blocks of the reference.
 
-PARITY UNPINNED for the pieces marked (gpu-only): the reference implements them only as CUDA kernels
-(`HydroVeBdtProp` throws on CPUs, ve_hydro_bdt.hpp:118), which cannot run where this oracle is built, and its tests
-hold no golden vectors for them.  They are restated here from the kernel sources, function by function, with the
-file:line each one follows.  PINNED through oracle/_ref (tests/test_bdt_oracle.py): the per-particle updates built
-from the reference's positionUpdate / energyUpdate, and the time-step hierarchy -- rung_timestep, minimum_group_dt,
+The pieces marked (gpu-only) exist in the reference only as CUDA kernels (`HydroVeBdtProp` throws on CPUs,
+ve_hydro_bdt.hpp:118), which cannot run where this oracle is built, and its tests hold no golden vectors for them.
+They are restated here from the kernel sources, function by function, with the file:line each one follows, and are
+pinned INDIRECTLY on the GPU box: tests/test_gpu_reference_kernels.py compares the library with the reference's own
+kernels compiled for sm_100a (computeGroupSplits, groupDivvTimestepGpu, groupAccTimestepGpu) and
+tests/test_gpu_groups.py compares the same library functions with this restatement.  PINNED through oracle/_ref
+(tests/test_bdt_oracle.py): the per-particle updates built from the reference's positionUpdate / energyUpdate, and the time-step hierarchy -- rung_timestep, minimum_group_dt,
 find_rung_ranges are checked against the reference's own sph/ts_rungs.hpp compiled for host memory
 (oracle/ref_bdt.cpp).  What stays sequenced by this module alone: the order in which HydroVeBdtProp calls those pieces
 (ve_hydro_bdt.hpp:280-420: which rungs drift, which advance, when groups are re-extracted).

@@ -128,6 +128,64 @@ inline void buildOctreeGpu(const Context& c, const uint64_t* leaves, int numLeav
                                leafToInternal));
 }
 
+//! @brief cstone::findPeersMac (traversal/peers.hpp:63-120) on host arrays; assignment = numRanks + 1 keys
+inline std::vector<int> findPeersMac(int myRank, const std::vector<uint64_t>& assignment,
+                                     const std::vector<uint64_t>& globalLeaves, const Box& box, float invThetaEff)
+{
+    int numRanks = int(assignment.size()) - 1;
+    std::vector<int> flags(numRanks), peers;
+    check(sphb200_find_peers_mac(myRank, numRanks, assignment.data(), globalLeaves.data(), int(globalLeaves.size()) - 1,
+                                 &box, invThetaEff, flags.data()));
+    for (int r = 0; r < numRanks; ++r)
+        if (flags[r]) peers.push_back(r);
+    return peers;
+}
+
+//! @brief cstone::FocusedOctreeSingleNode / the tree part of cstone::FocusedOctree on the device
+//!        (focus/octree_focus.hpp:219-288, focus/octree_focus_mpi.hpp:107-240, 408-481)
+class FocusedOctree
+{
+public:
+    FocusedOctree(const Context& c, unsigned bucketSize, float theta)
+    {
+        check(sphb200_focus_create(c.get(), bucketSize, theta, &f_));
+    }
+    ~FocusedOctree() { sphb200_focus_destroy(f_); }
+    FocusedOctree(const FocusedOctree&)            = delete;
+    FocusedOctree& operator=(const FocusedOctree&) = delete;
+    //! @brief FocusedOctreeSingleNode::update; keys: sorted device array of all particles the counts shall see
+    bool update(const Box& box, const uint64_t* keys, size_t n, uint64_t focusStart, uint64_t focusEnd,
+                const std::vector<uint64_t>& mandatoryKeys = {})
+    {
+        int conv = 0;
+        check(sphb200_focus_update(f_, &box, keys, n, focusStart, focusEnd, mandatoryKeys.data(),
+                                   int(mandatoryKeys.size()), &conv));
+        return conv != 0;
+    }
+    void updateMinMac(const Box& box, uint64_t focusStart, uint64_t focusEnd)
+    {
+        check(sphb200_focus_update_min_mac(f_, &box, focusStart, focusEnd));
+    }
+    bool updateTree(uint64_t focusStart, uint64_t focusEnd, const std::vector<uint64_t>& enforcedKeys = {})
+    {
+        int conv = 0;
+        check(sphb200_focus_update_tree(f_, focusStart, focusEnd, enforcedKeys.data(), int(enforcedKeys.size()), &conv));
+        return conv != 0;
+    }
+    void updateCounts(const uint64_t* keys, size_t n) { check(sphb200_focus_update_counts(f_, keys, n)); }
+    void setLeafCounts(const uint32_t* leafCounts) { check(sphb200_focus_set_leaf_counts(f_, leafCounts)); }
+    //! @brief octreeViewAcc() / treeLeavesAcc() / leafCountsAcc(): device pointers, valid until the next update
+    sphb200_focus_view view() const
+    {
+        sphb200_focus_view v;
+        check(sphb200_focus_get_view(f_, &v));
+        return v;
+    }
+
+private:
+    sphb200_focus* f_{nullptr};
+};
+
 //! @brief sph::computeXMass ... computeMomentumEnergy (sph/sph_gpu.hpp:13-82) on [first,last)
 struct Hydro
 {
@@ -421,6 +479,26 @@ public:
         sphb200_domain_info_t i;
         check(sphb200_domain_info(handles_[localRank], &i));
         return i;
+    }
+    //! @brief one round of the focus-tree update of Domain::sync on every rank (domain.hpp:214-227); after sync()
+    bool updateFocus(float theta)
+    {
+        int conv = 0;
+        check(sphb200_domain_update_focus(handles_.data(), int(handles_.size()), theta, &conv));
+        return conv != 0;
+    }
+    sphb200_focus_view focusView(size_t localRank, std::vector<int>* peers = nullptr) const
+    {
+        sphb200_focus_view v;
+        std::vector<int> flags(64, 0);
+        check(sphb200_domain_focus_view(handles_[localRank], &v, flags.data()));
+        if (peers)
+        {
+            peers->clear();
+            for (int r = 0; r < int(flags.size()); ++r)
+                if (flags[r]) peers->push_back(r);
+        }
+        return v;
     }
 
 private:

@@ -140,6 +140,18 @@ int main(int argc, char** argv)
                 std::fprintf(stderr, "2 virtual ranks differ from 1 rank: dt %.17g vs %.17g\n", r0.minDt(), one.minDt());
                 return 5;
             }
+            // the reference-style focus tree of both ranks (FocusedOctree::converge on the first call)
+            dist.sync();
+            bool conv = dist.updateFocus(1.0f);
+            std::vector<int> peers;
+            auto v0 = dist.focusView(0, &peers), v1 = dist.focusView(1);
+            std::printf("focus trees: %d + %d leaves, rank 0 has %zu peer(s), converged %d\n", v0.numLeaves, v1.numLeaves,
+                        peers.size(), int(conv));
+            if (!conv || peers.size() != 1 || peers[0] != 1 || v0.numLeaves < 8 || !v0.counts || !v0.macs)
+            {
+                std::fprintf(stderr, "focus tree update failed\n");
+                return 6;
+            }
             std::printf("domain ok\n");
         }
         // error path: precondition violation -> std::runtime_error

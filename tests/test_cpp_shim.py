@@ -33,6 +33,7 @@ def test_shim_runs_two_steps(pkg, ctx, tmp_path):
     assert "restart ok" in res.stdout
     assert "bdt ok: rungs=" in res.stdout
     assert "domain ok" in res.stdout  # 2 virtual ranks through sphb200::host::DistHydroVeProp == 1 rank
+    assert "focus trees:" in res.stdout and "converged 1" in res.stdout  # DistHydroVeProp::updateFocus / focusView
     # 12^3 lattice with h from ng0=100: every particle sees the same neighbor count (parity with tests/golden)
     import numpy as np
     g = np.load(os.path.join(ROOT, "tests", "golden", "sedov12_steps.npz"))

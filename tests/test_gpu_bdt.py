@@ -1,8 +1,9 @@
 """Block time steps: the group operators of HydroVeBdtProp and the propagator itself on the GPU.
 
 Reference: main/src/propagator/ve_hydro_bdt.hpp, sph/include/sph/{ts_rungs.hpp,ts_groups.cu,positions_gpu.cu}.  The
-reference runs this propagator on GPUs only and its tests hold no vectors for it (parity unpinned for the sequencing,
-see oracle/bdt.py); drift/advance are checked against the reference's positionUpdate/energyUpdate through oracle/_ref,
+reference runs this propagator on GPUs only and its tests hold no vectors for it; the sequencing is pinned against the
+reference's own GPU application in tests/test_gpu_reference_binary.py and the group kernels against the reference's own
+kernels in tests/test_gpu_reference_kernels.py; here drift/advance are checked against the reference's positionUpdate/energyUpdate through oracle/_ref,
 the rung search against findRungRanges<false>'s std::lower_bound restated with numpy, the whole propagator against
 oracle/bdt.py::RefBdtSim, which sequences the reference's CPU operators over the active groups.
 Tolerance: 1e-10 relative (f64) per substep like the global-time-step propagator; integers and group tables exact.

@@ -1,5 +1,6 @@
 """Block-time-step building blocks on the GPU against the numpy restatement in oracle/bdt.py (the reference has only
-CUDA kernels for these: sph/include/sph/ts_groups.cu, cstone/traversal/groups.cuh; parity unpinned, see oracle/bdt.py)."""
+CUDA kernels for these: sph/include/sph/ts_groups.cu, cstone/traversal/groups.cuh; the same library functions are
+compared with those kernels themselves, built for sm_100a, in tests/test_gpu_reference_kernels.py)."""
 import numpy as np
 import pytest
 
