@@ -265,6 +265,7 @@ typedef struct sphb200_turb_config
     int stSpectForm; /* 0 band, 1 parabola, 2 power law */
 } sphb200_turb_config;
 typedef struct sphb200_turb sphb200_turb;
+/* host work only (mode table, initial OU state): no device needed; the device copies are made by the first stir */
 int sphb200_turb_create(const sphb200_turb_config*, sphb200_turb** out);
 void sphb200_turb_destroy(sphb200_turb*);
 int sphb200_turb_num_modes(const sphb200_turb*);
@@ -276,7 +277,8 @@ int sphb200_turb_get(const sphb200_turb*, double* scalars4, double* modes, doubl
 int sphb200_turb_set_state(sphb200_turb*, const double* phases, const char* rngState);
 int sphb200_turb_rng_state(const sphb200_turb*, char* buf, size_t bufSize); /* returns the size needed */
 /* the two halves of driveTurbulence, for callers that stir range by range (sphb200_sim_step_host, the multi-rank
- * host): advance = OU step by dt + projection + upload of the phases (once per step), stir = the kernel on [first,last) */
+ * host): advance = OU step by dt + projection + upload of the phases (once per step), stir = the kernel on [first,last).
+ * advance with ctx == NULL is the host half alone (the next stir uploads the phases) */
 int sphb200_turb_advance(sphb200_turb*, sphb200_ctx*, double dt);
 int sphb200_turb_stir(sphb200_turb*, sphb200_ctx*, int dtype, uint32_t first, uint32_t last, const double* x,
                       const double* y, const double* z, void* ax, void* ay, void* az);

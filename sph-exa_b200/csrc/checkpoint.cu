@@ -529,6 +529,10 @@ extern "C" int sphb200_restart_apply(const sphb200_restart* r, sphb200_sim* s)
     r->f64("Atmax", &hc.Atmax);
     r->f64("ramp", &hc.ramp);
     r->f64("kernelNormalization", &hc.K);
+    // avClean selects other kernels and another field set: fixed when the simulation is created, must agree
+    if (r->i64("avClean", &iv) && (iv != 0) != (hc.avClean != 0))
+        throw std::runtime_error("restart: the file was written with avClean = " + std::to_string(iv) +
+                                 ", the simulation was created with avClean = " + std::to_string(hc.avClean));
     RESTART_RC(sphb200_sim_set_constants(s, &hc));
     sphb200_sim_set_dt(s, info.minDt, info.minDt_m1);
     sphb200_sim_set_time(s, info.time);

@@ -14,6 +14,7 @@
 //    identical results.
 #include <algorithm>
 #include <cmath>
+#include <memory>
 #include <random>
 #include <sstream>
 
@@ -199,9 +200,12 @@ struct sphb200_turb
     int numModes = 0;
     std::vector<double> modes, amplitudes, phases, phasesReal, phasesImag;
     std::mt19937 gen;
-    // device copies
+    // device copies, made by the first call that launches a kernel (ensureDevice): creating the driver and advancing
+    // its Ornstein-Uhlenbeck sequence are host work and need no device
     double *dModes = nullptr, *dAmp = nullptr, *dRe = nullptr, *dIm = nullptr;
     unsigned char* dIdx = nullptr;
+    std::vector<unsigned char> idxHost;
+    bool onDevice = false, phasesStale = true;
     UniqueK uk;
     bool tabled = false;
 };
@@ -338,7 +342,8 @@ extern "C" int sphb200_turb_create(const sphb200_turb_config* c, sphb200_turb** 
 {
     try
     {
-        auto* t      = new sphb200_turb;
+        std::unique_ptr<sphb200_turb> owner(new sphb200_turb);
+        sphb200_turb* t = owner.get();
         t->cfg       = *c;
         t->solWeight = c->solWeight;
         t->gen.seed(size_t(c->rngSeed));
@@ -392,19 +397,38 @@ extern "C" int sphb200_turb_create(const sphb200_turb_config* c, sphb200_turb** 
                 idx[3 * m + a] = (unsigned char)u;
             }
         }
-        t->dModes = toDevice(t->modes);
-        t->dAmp   = toDevice(t->amplitudes);
-        t->dRe    = toDevice(t->phasesReal);
-        t->dIm    = toDevice(t->phasesImag);
-        SPHB200_CUDA(cudaMalloc(&t->dIdx, std::max<size_t>(1, idx.size())));
-        SPHB200_CUDA(cudaMemcpy(t->dIdx, idx.data(), idx.size(), cudaMemcpyHostToDevice));
-        *out = t;
+        t->idxHost = std::move(idx);
+        *out       = owner.release();
         return 0;
     }
     catch (std::exception& e)
     {
         setError(e.what());
         return 1;
+    }
+}
+
+//! @brief mode table and phases on the current device (once), phases refreshed if the host advanced them since
+static void ensureDevice(sphb200_turb* t, cudaStream_t stream)
+{
+    if (!t->onDevice)
+    {
+        t->dModes = toDevice(t->modes);
+        t->dAmp   = toDevice(t->amplitudes);
+        t->dRe    = toDevice(t->phasesReal);
+        t->dIm    = toDevice(t->phasesImag);
+        SPHB200_CUDA(cudaMalloc(&t->dIdx, std::max<size_t>(1, t->idxHost.size())));
+        SPHB200_CUDA(cudaMemcpy(t->dIdx, t->idxHost.data(), t->idxHost.size(), cudaMemcpyHostToDevice));
+        t->onDevice    = true;
+        t->phasesStale = false;
+    }
+    if (t->phasesStale)
+    {
+        size_t bytes = t->phasesReal.size() * sizeof(double);
+        // pageable source: the copies complete (w.r.t. the host vectors) before cudaMemcpyAsync returns
+        SPHB200_CUDA(cudaMemcpyAsync(t->dRe, t->phasesReal.data(), bytes, cudaMemcpyHostToDevice, stream));
+        SPHB200_CUDA(cudaMemcpyAsync(t->dIm, t->phasesImag.data(), bytes, cudaMemcpyHostToDevice, stream));
+        t->phasesStale = false;
     }
 }
 
@@ -468,10 +492,8 @@ extern "C" int sphb200_turb_advance(sphb200_turb* t, sphb200_ctx* ctx, double dt
     {
         advancePhases(t, dt);
         projectPhases(t);
-        size_t bytes = t->phasesReal.size() * sizeof(double);
-        // pageable source: the copies complete (w.r.t. the host vectors) before cudaMemcpyAsync returns
-        SPHB200_CUDA(cudaMemcpyAsync(t->dRe, t->phasesReal.data(), bytes, cudaMemcpyHostToDevice, ctx->stream));
-        SPHB200_CUDA(cudaMemcpyAsync(t->dIm, t->phasesImag.data(), bytes, cudaMemcpyHostToDevice, ctx->stream));
+        t->phasesStale = true;
+        if (ctx) ensureDevice(t, ctx->stream); // ctx == NULL: host only, the next stir uploads
         return 0;
     }
     catch (std::exception& e)
@@ -487,6 +509,7 @@ extern "C" int sphb200_turb_stir(sphb200_turb* t, sphb200_ctx* ctx, int dtype, u
     try
     {
         if (last <= first || t->numModes == 0) return 0;
+        ensureDevice(t, ctx->stream);
         if (!t->tabled || t->numModes > kMaxModesSm)
             return sphb200_stirring(ctx, dtype, first, last, x, y, z, ax, ay, az, t->numModes, t->dModes, t->dRe,
                                     t->dIm, t->dAmp, t->solWeightNorm);

@@ -31,6 +31,14 @@ def find_files(path):
         out.append(f"{path}.{len(out)}")
     if not out:
         raise FileNotFoundError(path)
+    # the dump says how many ranks wrote it: files with higher numbers are left-overs of an earlier dump with more
+    # ranks under the same name, fewer files than that is a truncated dump
+    with RestartFile(out[0]) as r:
+        ranks = r.attribute("numRanks", np.int64)
+    if ranks is not None and ranks.size:
+        if len(out) < int(ranks[0]):
+            raise B.SphError(f"restart: {path} was written by {int(ranks[0])} ranks, only {len(out)} files found")
+        out = out[:int(ranks[0])]
     return out
 
 

@@ -57,7 +57,7 @@ class Turbulence:
 
     def advance(self, ctx, dt):
         """the host half of driveTurbulence: one Ornstein-Uhlenbeck step by dt, projection, upload of the phases"""
-        check(lib.sphb200_turb_advance(self.h, ctx.h, C.c_double(dt)))
+        check(lib.sphb200_turb_advance(self.h, ctx.h if ctx is not None else None, C.c_double(dt)))
 
     def stir(self, ctx, first, last, d):
         """the device half: stirring accelerations of the current phases added on [first, last)"""

@@ -92,6 +92,25 @@ def test_turbulence_restart_refuses_a_driver_with_other_constants(pkg, ctx, tmp_
         o.close()
 
 
+def test_restart_refuses_another_avclean_setting(pkg, ctx, tmp_path):
+    """avClean selects other kernels and gradient fields; a dump of one setting must not resume under the other"""
+    from sph_exa_b200 import sim as S, restart
+    f, box, s = pkg.ic.sedov(12)
+    n = f["x"].size
+    a = S.HydroVeProp(ctx, box, s, capacity=n, av_clean=False)
+    a.upload(f)
+    a.step()
+    path = str(tmp_path / "noclean")
+    restart.save(a, path, iteration=1, num_particles_global=n)
+    b = S.HydroVeProp(ctx, box, s, capacity=n, av_clean=True)
+    with pytest.raises(pkg.SphError, match="avClean"):
+        restart.load(b, path)
+    c = S.HydroVeProp(ctx, box, s, capacity=n, av_clean=False)
+    assert restart.load(c, path) == (1, n)
+    for o in (a, b, c):
+        o.close()
+
+
 def test_restart_into_other_precision(pkg, ctx, tmp_path):
     """an f64 dump starts a mixed-precision run: the reader converts, and the result equals a mixed run started from
     the rounded state"""

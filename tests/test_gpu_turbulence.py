@@ -10,21 +10,6 @@ from conftest import to_dev, to_host
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("spect", [1, 0, 2])
-def test_mode_table_and_ou_stream(pkg, ref, spect):
-    from sph_exa_b200.turbulence import Turbulence
-    kw = dict(stSpectForm=spect, rngSeed=4711)
-    rt, gt = ref.RefTurbulence(**kw), Turbulence(**kw)
-    assert gt.numModes == rt.numModes
-    a, b = gt.state(), rt.state()
-    for k in ("variance", "decayTime", "solWeight", "solWeightNorm"):
-        assert a[k] == b[k], k
-    for k in ("modes", "amplitudes", "phases"):
-        assert np.array_equal(a[k], b[k]), k
-    rt.close()
-    gt.close()
-
-
 @pytest.mark.parametrize("real", [np.float64, np.float32])
 def test_drive_matches_reference(pkg, ctx, ref, real):
     """three OU steps: phases bit-identical, accelerations within tolerance; [first,last) is a sub-range"""

@@ -188,3 +188,25 @@ def test_block_time_step_state_round_trip(pkg, tmp_path):
     with restart.RestartFile(q) as rf:
         assert not rf.has_field("rung")
         assert rf.attribute("ts::numRungs", np.int64) is None
+
+
+def test_find_files_follows_the_rank_count_of_the_dump(pkg, tmp_path):
+    """left-over files of an earlier dump with more ranks are ignored, a dump with missing rank files is refused"""
+    B = pkg.binding
+    from sph_exa_b200 import restart
+    base = str(tmp_path / "dump.bin")
+    arrays = make_fields(B, 10, np.float64)
+    # an old 3-rank dump, then a 2-rank dump under the same name
+    for r in range(3):
+        write_file(pkg, f"{base}.{r}", arrays, B.F64, n_global=30, rank=r, num_ranks=3)
+    assert restart.find_files(base) == [f"{base}.{r}" for r in range(3)]
+    for r in range(2):
+        write_file(pkg, f"{base}.{r}", arrays, B.F64, iteration=9, n_global=20, rank=r, num_ranks=2)
+    assert restart.find_files(base) == [f"{base}.0", f"{base}.1"]
+    os.remove(f"{base}.1")
+    os.remove(f"{base}.2")
+    with pytest.raises(B.SphError):
+        restart.find_files(base)
+    # a single-file dump is found under its own name
+    write_file(pkg, base, arrays, B.F64)
+    assert restart.find_files(base) == [base]
