@@ -509,8 +509,7 @@ extern "C" int sphb200_mark_macs(sphb200_ctx* ctx, const uint64_t* prefixes, con
     }
     SPHB200_LAUNCH(ctx, markMacsKernel, gridFor(numNodes, 256), 256, size_t(numBoxes) * sizeof(GeoBox), prefixes,
                    parents, centers4, numNodes, *box_h, dBoxes, numBoxes, focusStart, focusEnd, markings);
-    // the staging copy of `codes` must be complete before the vector goes out of scope
-    SPHB200_CUDA(cudaStreamSynchronize(ctx->stream));
+    // `codes` is pageable: cudaMemcpyAsync has staged it before returning, the vector may go out of scope
     SPHB200_CATCH
 }
 
