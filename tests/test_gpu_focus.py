@@ -324,3 +324,27 @@ def test_ranks_of_a_domain_build_the_reference_focus_trees(pkg, ctx, ref, case, 
     finally:
         group.close()
         comm.close()
+
+
+@pytest.mark.parametrize("kind", ["empty", "one", "coincident", "whole_range"])
+def test_focus_tree_edge_cases(pkg, ctx, ref, kind):
+    """no particles, one particle, 200 coincident particles (the tree descends to the deepest level, one level per
+    update) and a focus that is the whole key range (one rank): every update equals the reference's"""
+    box = BOXES[1]
+    full = sorted_keys(ref, 30_000, box, 5, True)
+    if kind == "empty":
+        keys, fs, fe = np.zeros(0, np.uint64), np.uint64(1 << 60), np.uint64(1 << 61)
+    elif kind == "one":
+        keys, fs, fe = full[:1].copy(), np.uint64(0), np.uint64(1 << 62)
+    elif kind == "coincident":
+        keys = np.sort(np.concatenate([full[:2000], np.full(200, full[777], np.uint64)]))
+        fs, fe = np.uint64(0), np.uint64(1 << 62)
+    else:
+        keys, fs, fe = full, np.uint64(0), ROOT_END
+    updates = 26 if kind == "coincident" else 8
+    flags, leaves, counts = run_both(pkg, ctx, ref, box, 64, 0.5, [(keys, fs, fe, np.zeros(0, np.uint64))] * updates)
+    assert int(counts.sum()) == keys.size
+    if kind == "coincident":
+        assert np.diff(leaves).min() == 1 and flags[-1]  # a finest-level cell holds the coincident particles
+    if kind == "whole_range":
+        assert flags[-1] and counts.max() <= 64
