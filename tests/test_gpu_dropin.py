@@ -1,7 +1,8 @@
 """Operator-level drop-in, proven end to end: `baseline/_ref/sphexa-cuda-b200` is the reference's own GPU front-end
 (main/src/sphexa/sphexa.cpp, its initial conditions, cstone::Domain, HydroVeProp, observables -- unmodified sources,
 built by oracle/build_sphexa_cuda.sh) linked with sph-exa_b200/host/b200_forward.cu + libsphexa_b200.so in place of
-the reference's five hydro_ve/*_gpu.cu pair-operator objects.  Its run must print the same `### Check ###` lines as
+the reference's five hydro_ve/*_gpu.cu pair-operator objects, and with sph-exa_b200/host/b200_forward_focus.cu in place
+of its focus/rebalance_gpu.cu object (the decisions of its FocusedOctree).  Its run must print the same `### Check ###` lines as
 `baseline/_ref/sphexa-cuda`, the reference's own GPU build, on the same problem."""
 import os
 import re
@@ -34,10 +35,13 @@ def test_reference_front_end_with_our_operators_prints_the_reference_check_lines
     b.mkdir()
     ref_checks, ref_its = run(REF, "sedov", side, steps, a)
     our_checks, our_its = run(OURS, "sedov", side, steps, b)
-    keep = ("Particles:", "Computational domain", "Total Neighbors", "Total time", "Total energy")
-    ref_lines = [l for l in ref_checks if any(k in l for k in keep)]
-    our_lines = [l for l in our_checks if any(k in l for k in keep)]
-    assert len(ref_lines) == 5 * steps
+    # "Focus Tree Nodes: N, maxDepth D": the reference's FocusedOctree takes its split / merge decisions from this
+    # library's rebalanceDecisionEssential / enforceKeys / protectAncestors kernels (host/b200_forward_focus.cu)
+    keep = ("Particles:", "Computational domain", "Total Neighbors", "Total time", "Total energy", "Focus Tree Nodes")
+    # (the rest of that line, maxStackNc, is the stack use of the reference's own pair-kernel traversals)
+    ref_lines = [l.split(", maxStackNc")[0] for l in ref_checks if any(k in l for k in keep)]
+    our_lines = [l.split(", maxStackNc")[0] for l in our_checks if any(k in l for k in keep)]
+    assert len(ref_lines) == 6 * steps
     # particle count, box, neighbor total, simulated time and time step, total / internal / kinetic energy of every
     # iteration, as printed by the reference (6 significant digits)
     assert our_lines == ref_lines
