@@ -79,9 +79,13 @@ if [ -f "$LIB/libsphexa_b200.so" ] && [ -f "$LIB/host/b200_forward.cu" ]; then
   # ... and the reference's focus/rebalance_gpu.cu object (rebalanceDecisionEssentialGpu, enforceKeysGpu,
   # protectAncestorsGpu: the decisions of its FocusedOctree) replaced by host/b200_forward_focus.cu
   $NVCC $CUFLAGS $INC -I$HERE/../include -c "$LIB/host/b200_forward_focus.cu" -o "$B/b200_forward_focus.o"
+  # ... and host/b200_forward_domain.cu: explicit specializations (strong symbols) of the Cornerstone GPU functions the
+  # SPH front-end uses (keys, linked octree, node geometry, halo search, gather) override the reference's weak
+  # instantiations; its objects stay in the link for the instantiations that are not forwarded
+  $NVCC $CUFLAGS $INC -I$HERE/../include -c "$LIB/host/b200_forward_domain.cu" -o "$B/b200_forward_domain.o"
   KEEP=$(ls $B/obj/*.o | grep -v -E "hydro_ve_(xmass|ve_def_gradh|iad_divv_curlv|av_switches|momentum_energy)_gpu|focus_rebalance_gpu")
   $NVCC -gencode arch=compute_100a,code=sm_100a -Xcompiler -fopenmp -Xlinker --wrap=cudaLaunchKernel $KEEP \
-        "$B/b200_forward.o" "$B/b200_forward_focus.o" -o "$OUT/sphexa-cuda-b200" -L"$LIB" -lsphexa_b200 -Xlinker -rpath -Xlinker '$ORIGIN/../../sph-exa_b200' \
+        "$B/b200_forward.o" "$B/b200_forward_focus.o" "$B/b200_forward_domain.o" -o "$OUT/sphexa-cuda-b200" -L"$LIB" -lsphexa_b200 -Xlinker -rpath -Xlinker '$ORIGIN/../../sph-exa_b200' \
         -lcudart -lgomp
   echo "built $OUT/sphexa-cuda-b200"
 fi
