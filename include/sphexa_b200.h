@@ -141,6 +141,9 @@ int sphb200_minmax3(sphb200_ctx*, const double* x, const double* y, const double
 /* ---- a3: sortByKeyGpu + sequenceGpu (primitives_gpu.h:87-111, primitives_gpu.cu:228-298) ----
  * keys sorted ascending in place (stable), perm[i] = original index of sorted element i */
 int sphb200_sort_by_key(sphb200_ctx*, uint64_t* keys, uint32_t* perm, size_t n);
+/* the same sort carrying the caller's values along (sortByKeyGpu(first, last, values, keyBuf, valueBuf),
+ * primitives_gpu.h:96: the reference's GpuSfcSorter passes a sequence that starts at an offset); stable */
+int sphb200_sort_pairs(sphb200_ctx*, uint64_t* keys, uint32_t* values, size_t n);
 
 /* ---- a4: gatherGpu (primitives_gpu.h:62, primitives_gpu.cu:85-101), all fields in one launch ----
  * src_h/dst_h: host arrays of nfields device pointers; elem_bytes_h: 4 or 8 per field */

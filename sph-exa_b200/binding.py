@@ -134,7 +134,7 @@ SYMBOLS = [
     "sphb200_protect_ancestors", "sphb200_find_peers_mac", "sphb200_focus_create", "sphb200_focus_destroy",
     "sphb200_focus_update", "sphb200_focus_update_tree", "sphb200_focus_update_min_mac", "sphb200_focus_update_counts",
     "sphb200_focus_set_leaf_counts", "sphb200_focus_get_view", "sphb200_domain_update_focus",
-    "sphb200_domain_focus_view",
+    "sphb200_domain_focus_view", "sphb200_sort_pairs",
 ]
 
 lib.sphb200_last_error.restype = C.c_char_p

@@ -631,6 +631,20 @@ extern "C" int sphb200_sort_by_key(sphb200_ctx* ctx, uint64_t* keys, uint32_t* p
     }
 }
 
+extern "C" int sphb200_sort_pairs(sphb200_ctx* ctx, uint64_t* keys, uint32_t* values, size_t n)
+{
+    try
+    {
+        radixSortPairs(ctx, keys, values, n, false, 0, 64);
+        return 0;
+    }
+    catch (std::exception& e)
+    {
+        setError(e.what());
+        return 1;
+    }
+}
+
 extern "C" int sphb200_gather(sphb200_ctx* ctx, const uint32_t* perm, size_t n, int nfields, const void* const* src,
                               void* const* dst, const int* elemBytes)
 {

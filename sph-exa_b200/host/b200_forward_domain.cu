@@ -7,12 +7,13 @@
  * specialization is an ordinary (strong) definition, the reference's explicit instantiations are weak symbols, so
  * linking this object into the reference's GPU application replaces exactly these functions and leaves the other
  * instantiations of the same templates (32-bit keys, float coordinates: gravity) with the reference
- * (`sphexa-cuda-b200`, oracle/build_sphexa_cuda.sh; tests/test_gpu_dropin.py).
+ * (`sphexa-cuda-b200`, build_sphexa_cuda.sh of the test infrastructure; tests/test_gpu_dropin.py).
  *
  *   computeSfcKeysGpu<HilbertKey<uint64_t>, double>    sfc/sfc_gpu.h:39            -> sphb200_sfc_keys
  *   buildOctreeGpu<uint64_t>                           tree/octree_gpu.h:50        -> sphb200_build_octree
  *   computeGeoCentersGpu<uint64_t, double>             focus/source_center_gpu.h:75 -> sphb200_node_centers
  *   findHalosGpu<uint64_t, float, double>              traversal/collisions_gpu.h:59 -> sphb200_find_halos
+ *   sortByKeyGpu<uint64_t, unsigned> (with buffers)     primitives/primitives_gpu.h:96 -> sphb200_sort_pairs
  *   gatherGpu<double | float | unsigned, unsigned>     primitives/primitives_gpu.h:46 -> sphb200_gather
  */
 #include <cstdint>
@@ -105,6 +106,13 @@ void findHalosGpu(const uint64_t* prefixes, const TreeNodeIndex* childOffsets, c
     sphb200_box b = toBox(box);
     check(sphb200_find_halos(context(), prefixes, childOffsets, internalToLeaf, leaves, interactionRadii, &b, firstNode,
                              lastNode, collisionFlags, nullptr));
+}
+
+template<>
+void sortByKeyGpu(uint64_t* first, uint64_t* last, unsigned* values, uint64_t* /*keyBuf*/, unsigned* /*valueBuf*/)
+{
+    // the library sorts in its own grow-only scratch; the caller's buffers stay untouched
+    check(sphb200_sort_pairs(context(), first, values, size_t(last - first)));
 }
 
 template<>

@@ -7,7 +7,7 @@
  * instantiations by forwarding to the C ABI of libsphexa_b200.so (csrc/focus.cu).  Linked in place of the reference's
  * rebalance_gpu object it makes the reference's own FocusedOctree -- inside its own cstone::Domain, in its own GPU
  * application -- take its split / merge decisions from this repository's kernels (`sphexa-cuda-b200`,
- * oracle/build_sphexa_cuda.sh; checked by tests/test_gpu_dropin.py: identical `Focus Tree Nodes` of every iteration).
+ * build_sphexa_cuda.sh of the test infrastructure; checked by tests/test_gpu_dropin.py: identical `Focus Tree Nodes` of every iteration).
  *
  * markMacsGpu (traversal/collisions_gpu.h:70) is not forwarded: its signature carries neither the number of nodes nor
  * the parents array that sphb200_mark_macs works from.

@@ -75,6 +75,12 @@ def sortByKeyGpu(ctx, keys):
     return perm
 
 
+def sortPairsGpu(ctx, keys, values):
+    """sortByKeyGpu with caller-provided values (primitives_gpu.h:96): keys and values sorted in place by key, stable"""
+    lib.sphb200_sort_pairs.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]
+    check(lib.sphb200_sort_pairs(ctx.h, ptr(keys), ptr(values), C.c_size_t(keys.numel())))
+
+
 def gatherGpu(ctx, perm, srcs, dsts=None):
     """gatherGpu for a list of fields in one launch (primitives_gpu.h:62); dsts: optional preallocated outputs
     (contiguous views of perm.numel() elements)"""

@@ -101,6 +101,22 @@ def test_sort_by_key(pkg, ctx, ref, n):
     assert np.array_equal(perm, np.argsort(keys, kind="stable").astype(np.uint32))
 
 
+@pytest.mark.parametrize("n", [1, 4097, 300_001])
+def test_sort_pairs_carries_the_callers_values(pkg, ctx, n):
+    """sortByKeyGpu(first, last, values, keyBuf, valueBuf) as GpuSfcSorter calls it: a sequence with an offset"""
+    from sph_exa_b200 import ops
+    rng = np.random.Generator(np.random.MT19937(n + 1))
+    keys = rng.integers(0, 1 << 63, n, dtype=np.uint64)
+    if n > 100:
+        keys[n // 3:n // 3 + 70] = keys[5]
+    values = (np.arange(n, dtype=np.uint32) * np.uint32(7) + np.uint32(1234))
+    dk, dv = to_dev(keys.copy()), to_dev(values.copy())
+    ops.sortPairsGpu(ctx, dk, dv)
+    order = np.argsort(keys, kind="stable")
+    assert np.array_equal(to_host(dk, np.uint64), keys[order])
+    assert np.array_equal(to_host(dv, np.uint32), values[order])
+
+
 def test_gather(pkg, ctx):
     from sph_exa_b200 import ops
     n = 50_001
