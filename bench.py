@@ -156,7 +156,7 @@ def reference_gpu(side, phase_ms_ours, ms_ours, mixed_ours=None, iterations=10):
             v = sorted(p.get(k, 0.0) for p in ph2[skip:])
             d_ms[k] = v[len(v) // 2] * 1e3
         out["drop_in"] = {"program": "baseline/_ref/sphexa-cuda-b200: reference front-end + cstone::Domain + HydroVeProp, "
-                                     "pair operators, focus-tree decisions and Cornerstone keys / octree / halo-search / gather forwarded to libsphexa_b200.so (mixed precision)",
+                                     "pair operators, focus-tree decisions and Cornerstone keys / sort / octree / halo-search / gather forwarded to libsphexa_b200.so (mixed precision)",
                           "ms_per_step": med2 * 1e3, "particle_steps_per_s": n / med2, "phase_ms": d_ms,
                           "speedup_vs_reference_gpu": med / med2,
                           "note": "XMass includes the one neighbor search all five operators share"}

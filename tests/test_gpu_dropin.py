@@ -4,7 +4,7 @@ built by oracle/build_sphexa_cuda.sh) linked with sph-exa_b200/host/b200_forward
 the reference's five hydro_ve/*_gpu.cu pair-operator objects, and with sph-exa_b200/host/b200_forward_focus.cu in place
 of its focus/rebalance_gpu.cu object (the decisions of its FocusedOctree), and with the specializations of
 sph-exa_b200/host/b200_forward_domain.cu overriding the reference's computeSfcKeysGpu, buildOctreeGpu,
-computeGeoCentersGpu, findHalosGpu and gatherGpu inside its own cstone::Domain::sync.  Its run must print the same `### Check ###` lines as
+computeGeoCentersGpu, findHalosGpu, sortByKeyGpu and gatherGpu inside its own cstone::Domain::sync.  Its run must print the same `### Check ###` lines as
 `baseline/_ref/sphexa-cuda`, the reference's own GPU build, on the same problem."""
 import os
 import re
